@@ -1,0 +1,629 @@
+"""TEST INFRASTRUCTURE ONLY (oracle).
+
+NumPy restatement of the reference's Python op chains for the SparseStorage hot
+path, one function per reference routine, each citing the file:line it follows
+(paths relative to /root/reference).  ``ind2ptr``/``ptr2ind``/``sample_adj`` are not
+re-derived here: they call the reference's own compiled CPU code through
+``oracle.native`` (falling back to the plain-C port where oracle/_ref is absent).
+
+Third-party arithmetic that is NOT under /root/reference and is restated from its
+documented semantics:
+  * paddle_scatter (unpinned git clone, README.md:21-24): segment_csr, gather_csr,
+    scatter, scatter_add.  Empty segments / untouched outputs yield 0 for every
+    reduce (upstream torch_scatter convention) — "parity unpinned" for that detail.
+  * paddle (unpinned nightly): argsort (tie order unspecified -> we use a STABLE
+    argsort, a valid instance), cumsum, nonzero, boolean-mask select, gather.
+
+Pinned by tests/test_oracle.py against every golden vector the reference's tests
+hold for this path.
+"""
+from __future__ import annotations
+
+from typing import Optional, Tuple
+
+import numpy as np
+
+from . import native
+
+I64 = np.int64
+
+
+# =========================================================================== paddle_scatter
+def _reduce_name(reduce: str) -> str:
+    assert reduce in ("sum", "add", "mean", "min", "max"), reduce
+    return "sum" if reduce == "add" else reduce
+
+
+def _acc_dtype(dtype):
+    # float16 inputs accumulate in float32 (the bf16/f16 oracle of SURVEY.md hard-part 6)
+    return np.float32 if dtype == np.float16 else dtype
+
+
+def segment_csr(src: np.ndarray, indptr: np.ndarray, reduce: str = "sum") -> np.ndarray:
+    """paddle_scatter.segment_csr(src, indptr, None, reduce) along dim 0.
+    Call sites: storage.py:471, reduce.py:51, tensor.py:437."""
+    reduce = _reduce_name(reduce)
+    indptr = np.asarray(indptr, dtype=I64)
+    S = indptr.size - 1
+    out = np.zeros((S,) + src.shape[1:], dtype=src.dtype)
+    if S == 0:
+        return out
+    counts = indptr[1:] - indptr[:-1]
+    nz = np.nonzero(counts > 0)[0]
+    if nz.size == 0:
+        return out
+    starts = indptr[:-1][nz]
+    # reduceat over the non-empty segments only: consecutive non-empty starts delimit
+    # exactly the segments because empty ones contribute no elements in between.
+    lo, hi = int(indptr[0]), int(indptr[-1])
+    body = src[lo:hi].astype(_acc_dtype(src.dtype), copy=False)
+    rel = (starts - lo).astype(np.intp)
+    if reduce in ("sum", "mean"):
+        red = np.add.reduceat(body, rel, axis=0)
+        if reduce == "mean":
+            c = counts[nz].reshape((-1,) + (1,) * (src.ndim - 1))
+            if np.issubdtype(src.dtype, np.integer):
+                red = np.trunc(red / c).astype(src.dtype)  # C++ integer division
+            else:
+                red = red / c.astype(red.dtype)
+    elif reduce == "min":
+        red = np.minimum.reduceat(body, rel, axis=0)
+    else:
+        red = np.maximum.reduceat(body, rel, axis=0)
+    out[nz] = red.astype(src.dtype)
+    return out
+
+
+def gather_csr(src: np.ndarray, indptr: np.ndarray) -> np.ndarray:
+    """paddle_scatter.gather_csr(src, indptr): out[e] = src[s] for e in [indptr[s], indptr[s+1]).
+    Call sites: mul.py:16,79, index_select.py:29,65."""
+    indptr = np.asarray(indptr, dtype=I64)
+    return np.repeat(src, indptr[1:] - indptr[:-1], axis=0)
+
+
+def scatter(src: np.ndarray, index: np.ndarray, dim_size: int, reduce: str = "sum") -> np.ndarray:
+    """paddle_scatter.scatter(src, index, 0, None, dim_size, reduce).  Call site: reduce.py:42."""
+    reduce = _reduce_name(reduce)
+    out = np.zeros((dim_size,) + src.shape[1:], dtype=_acc_dtype(src.dtype))
+    if src.shape[0] == 0:
+        return out.astype(src.dtype)
+    if reduce in ("sum", "mean"):
+        np.add.at(out, index, src.astype(out.dtype, copy=False))
+        if reduce == "mean":
+            cnt = np.bincount(index, minlength=dim_size).astype(I64)
+            cnt = np.maximum(cnt, 1).reshape((-1,) + (1,) * (src.ndim - 1))
+            if np.issubdtype(src.dtype, np.integer):
+                out = np.floor_divide(out, cnt)  # rounding_mode="floor" upstream
+            else:
+                out = out / cnt.astype(out.dtype)
+    else:
+        touched = np.zeros(dim_size, dtype=bool)
+        touched[index] = True
+        if reduce == "min":
+            init = np.inf if np.issubdtype(out.dtype, np.floating) else np.iinfo(out.dtype).max
+            out[...] = init
+            np.minimum.at(out, index, src)
+        else:
+            init = -np.inf if np.issubdtype(out.dtype, np.floating) else np.iinfo(out.dtype).min
+            out[...] = init
+            np.maximum.at(out, index, src)
+        out[~touched] = 0
+    return out.astype(src.dtype)
+
+
+def scatter_add(src: np.ndarray, index: np.ndarray, dim_size: int) -> np.ndarray:
+    """paddle_scatter.scatter_add.  Call site: storage.py:414-418 (histogram of col)."""
+    out = np.zeros(dim_size, dtype=src.dtype)
+    np.add.at(out, index, src)
+    return out
+
+
+# =========================================================================== utils.py
+def index_sort(keys: np.ndarray) -> np.ndarray:
+    """utils.py:14-23 -> Tensor.argsort() (pyg_lib absent); only perm is consumed."""
+    return np.argsort(keys, kind="stable").astype(I64)
+
+
+# =========================================================================== storage.py
+class SparseStorage:
+    """Restates paddle_sparse/storage.py:31-521 on NumPy arrays."""
+
+    def __init__(self, row=None, rowptr=None, col=None, value=None, sparse_sizes=None,
+                 rowcount=None, colptr=None, colcount=None, csr2csc=None, csc2csr=None,
+                 is_sorted: bool = False, trust_data: bool = False):
+        assert row is not None or rowptr is not None
+        assert col is not None
+        col = np.ascontiguousarray(col)
+        assert col.dtype == I64 and col.ndim == 1
+
+        # storage.py:65-89 — infer / validate the sparse sizes
+        M = 0
+        if sparse_sizes is None or sparse_sizes[0] is None:
+            if rowptr is not None:
+                M = rowptr.size - 1
+            elif row is not None and row.size > 0:
+                M = int(row.max()) + 1
+        else:
+            M = sparse_sizes[0]
+            if rowptr is not None:
+                assert rowptr.size - 1 == M
+            elif row is not None and row.size > 0:
+                assert trust_data or int(row.max()) < M
+        N = 0
+        if sparse_sizes is None or sparse_sizes[1] is None:
+            if col.size > 0:
+                N = int(col.max()) + 1
+        else:
+            N = sparse_sizes[1]
+            if col.size > 0:
+                assert trust_data or int(col.max()) < N
+
+        if row is not None:
+            row = np.ascontiguousarray(row)
+            assert row.dtype == I64 and row.ndim == 1 and row.size == col.size
+        if rowptr is not None:
+            rowptr = np.ascontiguousarray(rowptr)
+            assert rowptr.dtype == I64 and rowptr.size - 1 == M
+        if value is not None:
+            value = np.ascontiguousarray(value)
+            assert value.shape[0] == col.shape[0]
+        for name, arr, n in (("rowcount", rowcount, M), ("colcount", colcount, N)):
+            if arr is not None:
+                assert arr.dtype == I64 and arr.size == n, name
+        if colptr is not None:
+            assert colptr.dtype == I64 and colptr.size - 1 == N
+        for arr in (csr2csc, csc2csr):
+            if arr is not None:
+                assert arr.dtype == I64 and arr.size == col.size
+
+        self._row, self._rowptr, self._col, self._value = row, rowptr, col, value
+        self._sparse_sizes = (M, N)
+        self._rowcount, self._colptr, self._colcount = rowcount, colptr, colcount
+        self._csr2csc, self._csc2csr = csr2csc, csc2csr
+
+        # storage.py:158-171 — sort on construct
+        if not is_sorted and col.size > 0:
+            idx = np.zeros(col.size + 1, dtype=I64)
+            idx[1:] = self.row()
+            idx[1:] *= N
+            idx[1:] += col
+            if (idx[1:] < idx[:-1]).any():
+                perm = index_sort(idx[1:])
+                self._row = self.row()[perm]
+                self._col = col[perm]
+                if value is not None:
+                    self._value = value[perm]
+                self._csr2csc = None
+                self._csc2csr = None
+
+    # -- accessors ---------------------------------------------------------
+    def row(self):  # storage.py:195-206
+        if self._row is None:
+            self._row = native.ptr2ind(self._rowptr, self._col.size)
+        return self._row
+
+    def rowptr(self):  # storage.py:211-222
+        if self._rowptr is None:
+            self._rowptr = native.ind2ptr(self._row, self._sparse_sizes[0])
+        return self._rowptr
+
+    def col(self):
+        return self._col
+
+    def value(self):
+        return self._value
+
+    def has_value(self):
+        return self._value is not None
+
+    def sparse_sizes(self):
+        return self._sparse_sizes
+
+    def sparse_size(self, dim):
+        return self._sparse_sizes[dim]
+
+    def set_value_(self, value, layout="coo"):  # storage.py:233-246
+        if value is not None and layout == "csc":
+            value = value[self.csc2csr()]
+        self._value = None if value is None else np.ascontiguousarray(value)
+        return self
+
+    def set_value(self, value, layout="coo"):  # storage.py:248-273
+        if value is not None and layout == "csc":
+            value = value[self.csc2csr()]
+        return SparseStorage(row=self._row, rowptr=self._rowptr, col=self._col, value=value,
+                             sparse_sizes=self._sparse_sizes, rowcount=self._rowcount,
+                             colptr=self._colptr, colcount=self._colcount,
+                             csr2csc=self._csr2csc, csc2csr=self._csc2csr,
+                             is_sorted=True, trust_data=True)
+
+    def rowcount(self):  # storage.py:373-381
+        if self._rowcount is None:
+            rp = self.rowptr()
+            self._rowcount = rp[1:] - rp[:-1]
+        return self._rowcount
+
+    def colptr(self):  # storage.py:386-400
+        if self._colptr is None:
+            if self._csr2csc is not None:
+                self._colptr = native.ind2ptr(self._col[self._csr2csc], self._sparse_sizes[1])
+            else:
+                cp = np.zeros(self._sparse_sizes[1] + 1, dtype=I64)
+                cp[1:] = np.cumsum(self.colcount())
+                self._colptr = cp
+        return self._colptr
+
+    def colcount(self):  # storage.py:405-420
+        if self._colcount is None:
+            if self._colptr is not None:
+                self._colcount = self._colptr[1:] - self._colptr[:-1]
+            else:
+                self._colcount = scatter_add(np.ones_like(self._col), self._col,
+                                             self._sparse_sizes[1])
+        return self._colcount
+
+    def csr2csc(self):  # storage.py:425-434
+        if self._csr2csc is None:
+            idx = self._sparse_sizes[0] * self._col + self.row()
+            self._csr2csc = index_sort(idx)
+        return self._csr2csc
+
+    def csc2csr(self):  # storage.py:439-447
+        if self._csc2csr is None:
+            self._csc2csr = index_sort(self.csr2csc())
+        return self._csc2csr
+
+    def is_coalesced(self) -> bool:  # storage.py:449-452
+        idx = np.full(self._col.size + 1, -1, dtype=I64)
+        idx[1:] = self._sparse_sizes[1] * self.row() + self._col
+        return bool((idx[1:] > idx[:-1]).all())
+
+    def coalesce(self, reduce: str = "add"):  # storage.py:454-486
+        idx = np.full(self._col.size + 1, -1, dtype=I64)
+        idx[1:] = self._sparse_sizes[1] * self.row() + self._col
+        mask = idx[1:] > idx[:-1]
+        if mask.all():
+            return self
+        row, col = self.row()[mask], self._col[mask]
+        value = self._value
+        if value is not None:
+            ptr = np.concatenate([np.nonzero(mask)[0].astype(I64),
+                                  np.array([value.shape[0]], dtype=I64)])
+            value = segment_csr(value, ptr, reduce)
+        return SparseStorage(row=row, col=col, value=value, sparse_sizes=self._sparse_sizes,
+                             is_sorted=True, trust_data=True)
+
+    def fill_cache_(self):  # storage.py:488-496
+        self.row(); self.rowptr(); self.rowcount(); self.colptr(); self.colcount()
+        self.csr2csc(); self.csc2csr()
+        return self
+
+    def clear_cache_(self):  # storage.py:498-504
+        self._rowcount = self._colptr = self._colcount = None
+        self._csr2csc = self._csc2csr = None
+        return self
+
+    def cached_keys(self):  # storage.py:506-518
+        return [k for k in ("rowcount", "colptr", "colcount", "csr2csc", "csc2csr")
+                if getattr(self, "_" + k) is not None]
+
+    def num_cached_keys(self):
+        return len(self.cached_keys())
+
+
+# =========================================================================== tensor.py (facade)
+class SparseTensor:
+    """The slice of paddle_sparse/tensor.py the hot path touches (:20-64, :246-257)."""
+
+    def __init__(self, row=None, rowptr=None, col=None, value=None, sparse_sizes=None,
+                 is_sorted=False, trust_data=False):
+        self.storage = SparseStorage(row=row, rowptr=rowptr, col=col, value=value,
+                                     sparse_sizes=sparse_sizes, is_sorted=is_sorted,
+                                     trust_data=trust_data)
+
+    @classmethod
+    def from_storage(cls, st: SparseStorage):  # tensor.py:48-64
+        out = cls(row=st._row, rowptr=st._rowptr, col=st._col, value=st._value,
+                  sparse_sizes=st._sparse_sizes, is_sorted=True, trust_data=True)
+        for k in ("_rowcount", "_colptr", "_colcount", "_csr2csc", "_csc2csr"):
+            setattr(out.storage, k, getattr(st, k))
+        return out
+
+    def coo(self):
+        return self.storage.row(), self.storage.col(), self.storage.value()
+
+    def csr(self):
+        return self.storage.rowptr(), self.storage.col(), self.storage.value()
+
+    def csc(self):  # tensor.py:252-257
+        perm = self.storage.csr2csc()
+        value = self.storage.value()
+        if value is not None:
+            value = value[perm]
+        return self.storage.colptr(), self.storage.row()[perm], value
+
+    def sparse_sizes(self):
+        return self.storage.sparse_sizes()
+
+    def sparse_size(self, d):
+        return self.storage.sparse_sizes()[d]
+
+    def sizes(self):
+        v = self.storage.value()
+        return list(self.sparse_sizes()) + (list(v.shape[1:]) if v is not None else [])
+
+    def size(self, d):
+        return self.sizes()[d]
+
+    def dim(self):
+        return len(self.sizes())
+
+    def nnz(self):
+        return self.storage.col().size
+
+    def dtype(self):  # tensor.py:503-505
+        v = self.storage.value()
+        return v.dtype if v is not None else np.dtype(np.float32)
+
+    def set_value(self, value, layout="coo"):
+        return self.from_storage(self.storage.set_value(value, layout))
+
+    def set_value_(self, value, layout="coo"):
+        self.storage.set_value_(value, layout)
+        return self
+
+    def coalesce(self, reduce="sum"):
+        return self.from_storage(self.storage.coalesce(reduce))
+
+    def is_coalesced(self):
+        return self.storage.is_coalesced()
+
+    def fill_cache_(self):
+        self.storage.fill_cache_()
+        return self
+
+    def to_dense(self):
+        row, col, value = self.coo()
+        v = value if value is not None else np.ones(self.nnz(), dtype=np.float32)
+        mat = np.zeros(tuple(self.sparse_sizes()) + v.shape[1:], dtype=v.dtype)
+        mat[row, col] = v
+        return mat
+
+
+# =========================================================================== coalesce.py / transpose.py
+def coalesce(index, value, m, n, op="add"):
+    """coalesce.py:8-29."""
+    st = SparseStorage(row=index[0], col=index[1], value=value, sparse_sizes=(m, n),
+                       is_sorted=False)
+    st = st.coalesce(reduce=op)
+    return np.stack([st.row(), st.col()], axis=0), st.value()
+
+
+def t(src: SparseTensor) -> SparseTensor:
+    """transpose.py:9-33."""
+    csr2csc = src.storage.csr2csc()
+    row, col, value = src.coo()
+    if value is not None:
+        value = value[csr2csc]
+    M, N = src.storage.sparse_sizes()
+    st = SparseStorage(row=col[csr2csc], rowptr=src.storage._colptr, col=row[csr2csc],
+                       value=value, sparse_sizes=(N, M), rowcount=src.storage._colcount,
+                       colptr=src.storage._rowptr, colcount=src.storage._rowcount,
+                       csr2csc=src.storage._csc2csr, csc2csr=csr2csc, is_sorted=True)
+    return SparseTensor.from_storage(st)
+
+
+def transpose(index, value, m, n, coalesced=True):
+    """transpose.py:41-65."""
+    row, col = index[1], index[0]
+    if coalesced:
+        st = SparseStorage(row=row, col=col, value=value, sparse_sizes=(n, m), is_sorted=False)
+        st = st.coalesce()
+        row, col, value = st.row(), st.col(), st.value()
+    return np.stack([row, col], axis=0), value
+
+
+# =========================================================================== reduce.py
+def reduction(src: SparseTensor, dim: Optional[int] = None, reduce: str = "sum"):
+    """reduce.py:12-71."""
+    value = src.storage.value()
+    if dim is None:
+        if value is not None:
+            r = _reduce_name(reduce)
+            return {"sum": value.sum, "mean": value.mean, "min": value.min, "max": value.max}[r]()
+        return np.array(src.nnz() if _reduce_name(reduce) == "sum" else 1, dtype=src.dtype())
+    if dim < 0:
+        dim = src.dim() + dim
+    r = _reduce_name(reduce)
+    if dim == 0 and value is not None:
+        return scatter(value, src.storage.col(), src.size(1), reduce)
+    if dim == 0:
+        if r == "sum":
+            return src.storage.colcount().astype(src.dtype())
+        return np.ones(src.size(1), dtype=src.dtype())
+    if dim == 1 and value is not None:
+        return segment_csr(value, src.storage.rowptr(), reduce)
+    if dim == 1:
+        if r == "sum":
+            return src.storage.rowcount().astype(src.dtype())
+        return np.ones(src.size(0), dtype=src.dtype())
+    if value is not None:
+        f = {"sum": np.sum, "mean": np.mean, "min": np.min, "max": np.max}[r]
+        return f(value, axis=dim - 1)
+    raise ValueError
+
+
+# =========================================================================== mul.py
+def mul_(src: SparseTensor, other: np.ndarray) -> SparseTensor:
+    """mul.py:76-93 (the out-of-place `mul` :12-33 intends the same arithmetic, see
+    SURVEY.md 3.4)."""
+    rowptr, col, value = src.csr()
+    if other.shape[0] == src.size(0) and other.shape[1] == 1:
+        other = gather_csr(other.squeeze(1), rowptr)
+    elif other.shape[0] == 1 and other.shape[1] == src.size(1):
+        other = other.squeeze(0)[col]
+    else:
+        raise ValueError("Size mismatch")
+    if value is not None:
+        value = value * other.astype(value.dtype)
+    else:
+        value = other
+    return src.set_value_(value, layout="coo")
+
+
+def mul(src: SparseTensor, other: np.ndarray) -> SparseTensor:
+    out = SparseTensor.from_storage(src.storage)
+    if out.storage._value is not None:
+        out.storage._value = out.storage._value.copy()
+    return mul_(out, other)
+
+
+# =========================================================================== index_select.py
+def index_select(src: SparseTensor, dim: int, idx: np.ndarray) -> SparseTensor:
+    """index_select.py:13-96."""
+    dim = src.dim() + dim if dim < 0 else dim
+    idx = np.asarray(idx, dtype=I64)
+    K = idx.shape[0]
+    if dim == 0:
+        old_rowptr, col, value = src.csr()
+        rowcount = src.storage.rowcount()[idx]
+        rowptr = np.zeros(K + 1, dtype=I64)
+        rowptr[1:] = np.cumsum(rowcount)
+        row = np.repeat(np.arange(K, dtype=I64), rowcount)
+        perm = np.arange(row.shape[0], dtype=I64)
+        perm += gather_csr(old_rowptr[idx] - rowptr[:-1], rowptr)
+        col = col[perm]
+        if value is not None:
+            value = value[perm]
+        st = SparseStorage(row=row, rowptr=rowptr, col=col, value=value,
+                           sparse_sizes=(K, src.sparse_size(1)), rowcount=rowcount,
+                           is_sorted=True)
+        return SparseTensor.from_storage(st)
+    if dim == 1:
+        old_colptr, row, value = src.csc()
+        colcount = src.storage.colcount()[idx]
+        colptr = np.zeros(K + 1, dtype=I64)
+        colptr[1:] = np.cumsum(colcount)
+        col = np.repeat(np.arange(K, dtype=I64), colcount)
+        perm = np.arange(col.shape[0], dtype=I64)
+        perm += gather_csr(old_colptr[idx] - colptr[:-1], colptr)
+        row = row[perm]
+        csc2csr = index_sort(K * row + col)
+        row, col = row[csc2csr], col[csc2csr]
+        if value is not None:
+            value = value[perm][csc2csr]
+        st = SparseStorage(row=row, col=col, value=value,
+                           sparse_sizes=(src.sparse_size(0), K), colptr=colptr,
+                           colcount=colcount, csc2csr=csc2csr, is_sorted=True)
+        return SparseTensor.from_storage(st)
+    value = src.storage.value()
+    if value is None:
+        raise ValueError
+    return src.set_value(np.take(value, idx, axis=dim - 1), layout="coo")
+
+
+def index_select_nnz(src: SparseTensor, idx: np.ndarray, layout: str = "coo") -> SparseTensor:
+    """index_select.py:99-120."""
+    if layout == "csc":
+        idx = src.storage.csc2csr()[idx]
+    row, col, value = src.coo()
+    row, col = row[idx], col[idx]
+    if value is not None:
+        value = value[idx]
+    return SparseTensor(row=row, col=col, value=value, sparse_sizes=src.sparse_sizes(),
+                        is_sorted=True)
+
+
+# =========================================================================== masked_select.py
+def masked_select(src: SparseTensor, dim: int, mask: np.ndarray) -> SparseTensor:
+    """masked_select.py:12-90."""
+    dim = src.dim() + dim if dim < 0 else dim
+    mask = np.asarray(mask, dtype=bool)
+    if dim == 0:
+        row, col, value = src.coo()
+        rowcount = src.storage.rowcount()[mask]
+        emask = mask[row]
+        row = np.repeat(np.arange(rowcount.shape[0], dtype=I64), rowcount)
+        col = col[emask]
+        if value is not None:
+            value = value[emask]
+        st = SparseStorage(row=row, col=col, value=value,
+                           sparse_sizes=(rowcount.shape[0], src.sparse_size(1)),
+                           rowcount=rowcount, is_sorted=True)
+        return SparseTensor.from_storage(st)
+    if dim == 1:
+        row, col, value = src.coo()
+        csr2csc = src.storage.csr2csc()
+        row, col = row[csr2csc], col[csr2csc]
+        colcount = src.storage.colcount()[mask]
+        emask = mask[col]
+        K = colcount.shape[0]
+        col = np.repeat(np.arange(K, dtype=I64), colcount)
+        row = row[emask]
+        csc2csr = index_sort(K * row + col)
+        row, col = row[csc2csr], col[csc2csr]
+        if value is not None:
+            value = value[csr2csc][emask][csc2csr]
+        st = SparseStorage(row=row, col=col, value=value,
+                           sparse_sizes=(src.sparse_size(0), K), colcount=colcount,
+                           csc2csr=csc2csr, is_sorted=True)
+        return SparseTensor.from_storage(st)
+    value = src.storage.value()
+    if value is None:
+        raise ValueError
+    return src.set_value(np.take(value, np.nonzero(mask)[0], axis=dim - 1), layout="coo")
+
+
+def masked_select_nnz(src: SparseTensor, mask: np.ndarray, layout: str = "coo") -> SparseTensor:
+    """masked_select.py:93-114."""
+    mask = np.asarray(mask, dtype=bool)
+    if layout == "csc":
+        mask = mask[src.storage.csc2csr()]
+    row, col, value = src.coo()
+    row, col = row[mask], col[mask]
+    if value is not None:
+        value = value[mask]
+    return SparseTensor(row=row, col=col, value=value, sparse_sizes=src.sparse_sizes(),
+                        is_sorted=True)
+
+
+# =========================================================================== sample.py
+def sample_adj(src: SparseTensor, subset: np.ndarray, num_neighbors: int,
+               replace: bool = False, seed: int = 0, which: str = "port"
+               ) -> Tuple[SparseTensor, np.ndarray]:
+    """sample.py:31-53.  which="ref" runs the reference's own sample_adj_cpu,
+    which="port" the plain-C restatement with the fixed n_id order."""
+    rowptr, col, value = src.csr()
+    fn = native.sample_adj_ref if which == "ref" else native.sample_adj_port
+    out_rowptr, out_col, n_id, e_id = fn(rowptr, col, subset, num_neighbors, replace, seed)
+    if value is not None:
+        value = value[e_id]
+    out = SparseTensor(rowptr=out_rowptr, col=out_col, value=value,
+                       sparse_sizes=(len(subset), n_id.size), is_sorted=True)
+    return out, n_id
+
+
+# =========================================================================== helpers for tests/bench
+def round_bf16(x: np.ndarray) -> np.ndarray:
+    """Round-to-nearest-even float32 -> bfloat16 -> float32 (NumPy has no bf16)."""
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    u = x.view(np.uint32).astype(np.uint64)
+    rounded = ((u + 0x7FFF + ((u >> 16) & 1)) >> 16) << 16
+    return rounded.astype(np.uint32).view(np.float32).reshape(x.shape)
+
+
+def build_pipeline(row, col, value, M, N):
+    """The BASELINE.json headline pipeline on the CPU: coalesce -> rowptr -> csr2csc ->
+    colptr -> csc2csr -> t().  Returns a dict of every array the GPU path must match."""
+    idx, val = coalesce(np.stack([row, col]), value, M, N, "add")
+    A = SparseTensor(row=idx[0], col=idx[1], value=val, sparse_sizes=(M, N),
+                     is_sorted=True, trust_data=True)
+    st = A.storage
+    out = dict(row=st.row(), col=st.col(), value=st.value(), rowptr=st.rowptr().copy())
+    out["csr2csc"] = st.csr2csc().copy()
+    out["colptr"] = st.colptr().copy()
+    out["csc2csr"] = st.csc2csr().copy()
+    st.rowcount(); st.colcount()
+    At = t(A)
+    out["t_row"], out["t_col"], out["t_value"] = At.coo()
+    return out

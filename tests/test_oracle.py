@@ -1,0 +1,229 @@
+"""Pins the CPU oracle (oracle/) against every golden vector the reference's own tests
+hold for the hot path, and the plain-C port against the reference's
+compiled CPU sources (oracle/_ref) where those are built.  CPU only."""
+import numpy as np
+import pytest
+
+from oracle import native, np_ref
+from tests.golden import reference_vectors as G
+
+I64 = np.int64
+DTYPES = [np.float16, np.float32, np.float64, np.int32, np.int64]  # testing.py:12
+WHICH = ["port"] + (["ref"] if native.have_ref() else [])
+
+
+def a(x, dt=I64):
+    return np.asarray(x, dtype=dt)
+
+
+@pytest.mark.parametrize("which", WHICH)
+def test_ind2ptr_ptr2ind_golden(which):
+    g = G.IND2PTR
+    rowptr = native.ind2ptr(a(g["row"]), g["M"], which)
+    assert rowptr.tolist() == g["rowptr"]
+    assert native.ptr2ind(rowptr, 6, which).tolist() == g["row"]
+    rowptr = native.ind2ptr(a([]), 8, which)
+    assert rowptr.tolist() == [0] * 9
+    assert native.ptr2ind(rowptr, 0, which).tolist() == []
+
+
+@pytest.mark.skipif(not native.have_ref(), reason="oracle/_ref not built")
+def test_port_matches_reference_convert_random():
+    rng = np.random.default_rng(0)
+    for M, nnz in [(1, 0), (1, 5), (7, 3), (100, 1000), (5000, 300), (3, 10000)]:
+        ind = np.sort(rng.integers(0, M, nnz)).astype(I64)
+        r = native.ind2ptr(ind, M, "ref")
+        p = native.ind2ptr(ind, M, "port")
+        assert np.array_equal(r, p)
+        assert np.array_equal(r, np.searchsorted(ind, np.arange(M + 1), side="left"))
+        assert np.array_equal(native.ptr2ind(r, nnz, "ref"), native.ptr2ind(r, nnz, "port"))
+        assert np.array_equal(native.ptr2ind(r, nnz, "ref"), ind)
+
+
+@pytest.mark.parametrize("dtype", DTYPES)
+def test_sort_on_construct_golden(dtype):
+    g = G.SORT_ON_CONSTRUCT
+    st = np_ref.SparseStorage(row=a(g["row"]), col=a(g["col"]), value=a(g["value"], dtype))
+    assert st.row().tolist() == g["out_row"]
+    assert st.col().tolist() == g["out_col"]
+    assert st.value().tolist() == g["out_value"]
+    assert st.sparse_sizes() == g["sizes"]
+
+
+def test_caching_golden():
+    g = G.CACHING
+    st = np_ref.SparseStorage(row=a(g["row"]), col=a(g["col"]))
+    assert st.num_cached_keys() == 0 and st._rowptr is None
+    st.fill_cache_()
+    for k in ("rowcount", "rowptr", "colcount", "colptr", "csr2csc", "csc2csr"):
+        assert getattr(st, "_" + k).tolist() == g[k], k
+    assert st.num_cached_keys() == 5
+    st.clear_cache_()
+    assert st._rowptr is not None and st.num_cached_keys() == 0
+
+
+@pytest.mark.parametrize("dtype", DTYPES)
+def test_set_value_golden(dtype):
+    g = G.SET_VALUE
+    v = a(g["value"], dtype)
+    st = np_ref.SparseStorage(row=a(g["row"]), col=a(g["col"]), value=v)
+    st.set_value_(v, layout="csc")
+    assert st.value().tolist() == g["csc_layout"]
+    st.set_value_(v, layout="coo")
+    assert st.value().tolist() == g["coo_layout"]
+    assert st.set_value(v, layout="csc").value().tolist() == g["csc_layout"]
+
+
+@pytest.mark.parametrize("dtype", DTYPES)
+def test_storage_coalesce_golden(dtype):
+    g = G.STORAGE_COALESCE
+    st = np_ref.SparseStorage(row=a(g["row"]), col=a(g["col"]), value=a(g["value"], dtype))
+    assert not st.is_coalesced()
+    st2 = st.coalesce()
+    assert st2.is_coalesced()
+    assert st2.row().tolist() == g["out_row"] and st2.col().tolist() == g["out_col"]
+    assert st2.value().tolist() == g["out_value"]
+    assert st2.coalesce() is st2  # storage.py:459-460
+
+
+def test_free_coalesce_golden():
+    g = G.COALESCE
+    index = np.stack([a(g["row"]), a(g["col"])])
+    idx, _ = np_ref.coalesce(index, None, g["m"], g["n"])
+    assert idx.tolist() == g["index"]
+    idx, val = np_ref.coalesce(index, a(g["value"]), g["m"], g["n"])
+    assert idx.tolist() == g["index"] and val.tolist() == g["add"]
+    idx, val = np_ref.coalesce(index, a(g["value"]), g["m"], g["n"], op="max")
+    assert idx.tolist() == g["index"] and val.tolist() == g["max"]
+
+
+@pytest.mark.parametrize("dtype", DTYPES)
+def test_transpose_golden(dtype):
+    g = G.TRANSPOSE_MATRIX
+    idx, val = np_ref.transpose(np.stack([a(g["row"]), a(g["col"])]), a(g["value"], dtype),
+                                g["m"], g["n"])
+    assert idx.tolist() == g["index"] and val.tolist() == g["out_value"]
+    g = G.TRANSPOSE
+    idx, val = np_ref.transpose(np.stack([a(g["row"]), a(g["col"])]), a(g["value"], dtype),
+                                g["m"], g["n"])
+    assert idx.tolist() == g["index"] and val.tolist() == g["out_value"]
+
+
+@pytest.mark.parametrize("which", WHICH)
+def test_sample_adj_golden(which):
+    g = G.SAMPLE_ADJ
+    A = np_ref.SparseTensor(row=a(g["row"]), col=a(g["col"]),
+                            value=np.arange(len(g["row"]), dtype=I64), sparse_sizes=g["sizes"])
+    out, n_id = np_ref.sample_adj(A, a(g["subset"]), -1, which=which)
+    assert n_id.tolist() == g["all_n_id"]
+    row, col, val = out.coo()
+    assert row.tolist() == g["all_row"] and col.tolist() == g["all_col"]
+    assert val.tolist() == g["all_val"]
+    out, _ = np_ref.sample_adj(A, a(g["subset"]), 2, replace=True, seed=3, which=which)
+    assert out.nnz() == g["nnz_replace_k2"]
+    out, _ = np_ref.sample_adj(A, a(g["subset"]), 2, replace=False, seed=3, which=which)
+    assert out.nnz() == g["nnz_noreplace_k2"]
+
+
+@pytest.mark.skipif(not native.have_ref(), reason="oracle/_ref not built")
+@pytest.mark.parametrize("k,replace", [(-1, False), (3, False), (3, True), (10, False), (1, True)])
+def test_port_sample_adj_matches_reference(k, replace):
+    """Same Philox draws -> identical per-row (global col, e_id) multisets, identical
+    rowptr, identical n_id set, seeds first (SURVEY.md 8c comparison rule)."""
+    rng = np.random.default_rng(5)
+    M, nnz = 300, 4000
+    key = np.sort(rng.choice(M * M, nnz, replace=False))  # coalesced: no duplicate edges
+    row, col = (key // M).astype(I64), (key % M).astype(I64)
+    rowptr = native.ind2ptr(row, M)
+    idx = rng.integers(0, M, 64).astype(I64)  # duplicate seeds allowed
+    for seed in (0, 1, 12345678901234567):
+        r = native.sample_adj_ref(rowptr, col, idx, k, replace, seed)
+        p = native.sample_adj_port(rowptr, col, idx, k, replace, seed)
+        assert np.array_equal(r[0], p[0])
+        assert np.array_equal(r[2][: idx.size], idx) and np.array_equal(p[2][: idx.size], idx)
+        assert sorted(r[2].tolist()) == sorted(p[2].tolist())
+        assert native.canonical_sample(*r) == native.canonical_sample(*p)
+        for res in (r, p):  # local ids ascending within each row (sample_cpu.cpp:134-139)
+            for i in range(idx.size):
+                seg = res[1][res[0][i]: res[0][i + 1]]
+                assert np.all(seg[1:] >= seg[:-1])
+        if k < 0:  # CSR order is deterministic on a coalesced graph: compare bit-exactly
+            for x, y in zip(r, p):
+                assert np.array_equal(x, y)
+
+
+@pytest.mark.skipif(not native.have_ref(), reason="oracle/_ref not built")
+def test_port_sample_adj_duplicate_edges_canonical():
+    """With duplicate (row, col) edges the reference's std::sort leaves equal local ids
+    unordered (sample_cpu.cpp:133-140); only the canonical form is comparable."""
+    rng = np.random.default_rng(6)
+    M, nnz = 50, 2000
+    row = np.sort(rng.integers(0, M, nnz)).astype(I64)
+    col = rng.integers(0, M, nnz).astype(I64)
+    rowptr = native.ind2ptr(row, M)
+    idx = rng.integers(0, M, 20).astype(I64)
+    for k, replace in [(-1, False), (7, False), (7, True)]:
+        r = native.sample_adj_ref(rowptr, col, idx, k, replace, 9)
+        p = native.sample_adj_port(rowptr, col, idx, k, replace, 9)
+        assert np.array_equal(r[0], p[0])
+        assert native.canonical_sample(*r) == native.canonical_sample(*p)
+
+
+def test_permute_golden():
+    g = G.PERMUTE
+    A = np_ref.SparseTensor(row=a(g["row"]), col=a(g["col"]), value=a(g["value"], np.float32))
+    P = np_ref.index_select(np_ref.index_select(A, 0, a(g["perm"])), 1, a(g["perm"]))
+    row, col, val = P.coo()
+    assert row.tolist() == g["out_row"] and col.tolist() == g["out_col"]
+    assert val.tolist() == g["out_value"]
+
+
+def test_paddle_scatter_restatement():
+    src = a([1, 2, 3, 4, 5, 6], np.float32)
+    ptr = a([0, 2, 2, 5, 6])
+    assert np_ref.segment_csr(src, ptr, "sum").tolist() == [3, 0, 12, 6]
+    assert np_ref.segment_csr(src, ptr, "mean").tolist() == [1.5, 0, 4, 6]
+    assert np_ref.segment_csr(src, ptr, "min").tolist() == [1, 0, 3, 6]
+    assert np_ref.segment_csr(src, ptr, "max").tolist() == [2, 0, 5, 6]
+    assert np_ref.gather_csr(a([7, 8, 9, 10]), ptr).tolist() == [7, 7, 9, 9, 9, 10]
+    idx = a([0, 2, 2, 0, 3, 2])
+    assert np_ref.scatter(src, idx, 5, "sum").tolist() == [5, 0, 11, 5, 0]
+    assert np.allclose(np_ref.scatter(src, idx, 5, "mean"), [2.5, 0, 11 / 3, 5, 0])
+    assert np_ref.scatter(src, idx, 5, "min").tolist() == [1, 0, 2, 5, 0]
+    assert np_ref.scatter(src, idx, 5, "max").tolist() == [4, 0, 6, 5, 0]
+    src2 = np.stack([src, -src], axis=1)
+    assert np_ref.segment_csr(src2, ptr, "max").tolist() == [[2, -1], [0, 0], [5, -3], [6, -6]]
+
+
+def test_reduction_mul_select_consistency_with_dense():
+    rng = np.random.default_rng(1)
+    M, N, nnz = 23, 17, 120
+    key = rng.choice(M * N, nnz, replace=False)
+    row, col = (key // N).astype(I64), (key % N).astype(I64)
+    val = rng.random(nnz).astype(np.float64) + 0.5
+    A = np_ref.SparseTensor(row=row, col=col, value=val, sparse_sizes=(M, N))
+    D = A.to_dense()
+    assert np.allclose(np_ref.reduction(A, 1, "sum"), D.sum(1))
+    assert np.allclose(np_ref.reduction(A, 0, "sum"), D.sum(0))
+    cnt1 = np.maximum((D != 0).sum(1), 1)
+    assert np.allclose(np_ref.reduction(A, 1, "mean"), D.sum(1) / cnt1)
+    assert np.allclose(np_ref.reduction(A, 0, "max"), D.max(0))
+    At = np_ref.t(A)
+    assert np.array_equal(At.to_dense(), D.T)
+    r = rng.random((M, 1))
+    assert np.allclose(np_ref.mul(A, r).to_dense(), D * r)
+    c = rng.random((1, N))
+    assert np.allclose(np_ref.mul(A, c).to_dense(), D * c)
+    idx = a([5, 5, 0, 22, 3])
+    assert np.array_equal(np_ref.index_select(A, 0, idx).to_dense(), D[idx])
+    idx = a([16, 0, 0, 4])
+    assert np.array_equal(np_ref.index_select(A, 1, idx).to_dense(), D[:, idx])
+    m0 = rng.random(M) < 0.5
+    assert np.array_equal(np_ref.masked_select(A, 0, m0).to_dense(), D[m0])
+    m1 = rng.random(N) < 0.5
+    assert np.array_equal(np_ref.masked_select(A, 1, m1).to_dense(), D[:, m1])
+
+
+def test_philox_known_answer():
+    # Random123 known-answer test for philox4x32-10: counter = key = 0.
+    assert native.philox_u64(0, 0, 0) == (0x6627E8D5 | (0xE169C58D << 32))
