@@ -1,0 +1,192 @@
+/* paddle_sparse_b200 — C ABI of libpaddle_sparse_b200.so
+ *
+ * The drop-in boundary for the SparseStorage hot path of PFCCLab/paddle_sparse
+ * (SURVEY.md section 8b).  Every entry point takes plain device pointers, sizes and
+ * a CUDA stream (passed as void* so the header needs no CUDA include) and returns an
+ * int status (PS_OK = 0).  On failure ps_last_error() holds a thread-local message.
+ * The library is GPU-only: there is no CPU fallback, and no torch / paddle type
+ * appears in any signature.
+ *
+ * Conventions
+ *   - index arrays are contiguous int64 on the device (the reference asserts int64
+ *     everywhere: paddle_sparse/storage.py:61,94,101);
+ *   - `value` arrays are contiguous [n, width] of `dtype` (PS_* below); value == NULL
+ *     means "no value tensor" (SparseStorage._value is None);
+ *   - fixed-size outputs are caller-allocated; data-dependent outputs are
+ *     caller-allocated at their upper bound and the true count is returned through a
+ *     HOST pointer (the call then synchronises the stream exactly once);
+ *   - inputs are never modified unless the function name ends in `_inplace`;
+ *   - kernels are enqueued on `stream`; scratch memory is stream-ordered
+ *     (cudaMallocAsync) so no call synchronises unless stated.
+ *
+ * Citations are file:line under the reference repository (PFCCLab/paddle_sparse).
+ */
+#ifndef PS_ABI_H
+#define PS_ABI_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PS_OK 0
+#define PS_ERR_ARG 1  /* bad argument (replaces PD_CHECK, csrc/cpu/utils.h:6-9) */
+#define PS_ERR_CUDA 2 /* CUDA runtime error */
+
+/* value dtypes: paddle_sparse/testing.py:12-17 */
+enum { PS_F32 = 0, PS_BF16 = 1, PS_F16 = 2, PS_F64 = 3, PS_I32 = 4, PS_I64 = 5, PS_U8 = 6 };
+/* reduce ops: paddle_sparse/testing.py:10 ("add" is a synonym of "sum") */
+enum { PS_SUM = 0, PS_MEAN = 1, PS_MIN = 2, PS_MAX = 3 };
+
+/* ------------------------------------------------------------------ library */
+/* csrc/version.cpp:8-33 `sparse_cuda_version` -> CUDA_VERSION the library was built with */
+int64_t ps_cuda_version(void);
+const char *ps_last_error(void);
+
+/* ------------------------------------------------------------------ convert */
+/* csrc/convert.cpp:13-23 `ind2ptr(ind, M)`; kernels csrc/cuda/convert_cuda.cu:6-40,
+ * csrc/cpu/convert_cpu.cpp:6-30.  ind sorted ascending, out_ptr[M+1]. */
+int ps_ind2ptr(const int64_t *ind, int64_t numel, int64_t M, int64_t *out_ptr, void *stream);
+/* csrc/convert.cpp:46-56 `ptr2ind(ptr, E)`; csrc/cuda/convert_cuda.cu:42-68. out_ind[E]. */
+int ps_ptr2ind(const int64_t *ptr, int64_t M, int64_t E, int64_t *out_ind, void *stream);
+/* storage.py:373-381 / 405-412: count[i] = ptr[i+1] - ptr[i]. */
+int ps_ptr2count(const int64_t *ptr, int64_t M, int64_t *out_count, void *stream);
+/* storage.py:395-398 (colptr = [0, cumsum(colcount)]) and index_select.py:21-23
+ * (rowptr' from rowcount[idx]): out_ptr[0]=0, out_ptr[i+1]=sum_{j<=i} count[idx ? idx[j] : j].
+ * host_total (nullable) receives out_ptr[n] (synchronises when non-NULL). */
+int ps_count2ptr(const int64_t *count, const int64_t *idx, int64_t n, int64_t *out_ptr,
+                 int64_t *host_total, void *stream);
+/* storage.py:413-418 colcount = scatter_add(ones_like(col), col, dim_size=N). */
+int ps_histogram(const int64_t *ind, int64_t numel, int64_t bins, int64_t *out_count, void *stream);
+
+/* ------------------------------------------------------------------ construct */
+/* storage.py:65-89 `int(row.max())`, `int(col.max())`: host_max[0] = max(a) (or -1 if
+ * na == 0), host_max[1] = max(b) (b nullable).  Synchronises. */
+int ps_index_max(const int64_t *a, int64_t na, const int64_t *b, int64_t nb, int64_t *host_max,
+                 void *stream);
+/* storage.py:158-163 sortedness test and storage.py:449-452 `is_coalesced`:
+ * host_flags[0] = 1 iff (row,col) is non-decreasing, host_flags[1] = 1 iff strictly
+ * increasing.  Synchronises. */
+int ps_coo_order(const int64_t *row, const int64_t *col, int64_t nnz, int32_t *host_flags,
+                 void *stream);
+/* storage.py:158-171 sort-on-construct (index_sort: utils.py:14-23): STABLE sort of the
+ * entries by key row*N+col.  out_row/out_col[nnz]; out_value (nullable iff value NULL)
+ * [nnz,width]; out_perm (nullable) receives the permutation (sorted[i] = in[perm[i]]). */
+int ps_sort_coo(const int64_t *row, const int64_t *col, int64_t nnz, int64_t M, int64_t N,
+                const void *value, int dtype, int64_t width, int64_t *out_row, int64_t *out_col,
+                void *out_value, int64_t *out_perm, void *stream);
+/* storage.py:454-486 `SparseStorage.coalesce(reduce)` on SORTED input: keep the first
+ * (row,col) of every run, value' = segment_csr(value, run_starts, reduce).
+ * Outputs sized nnz; *host_nnz_out = nnz'.  Synchronises once. */
+int ps_coalesce_sorted(const int64_t *row, const int64_t *col, int64_t nnz, const void *value,
+                       int dtype, int64_t width, int reduce, int64_t *out_row, int64_t *out_col,
+                       void *out_value, int64_t *host_nnz_out, void *stream);
+/* coalesce.py:8-29 free function = sort-on-construct + coalesce, fused: one radix sort
+ * of the packed keys followed by run detection + segmented reduce.  Synchronises once. */
+int ps_coalesce(const int64_t *row, const int64_t *col, int64_t nnz, int64_t M, int64_t N,
+                const void *value, int dtype, int64_t width, int reduce, int64_t *out_row,
+                int64_t *out_col, void *out_value, int64_t *host_nnz_out, void *stream);
+
+/* ------------------------------------------------------------------ CSC structures */
+/* storage.py:425-434 `csr2csc` = argsort(M*col + row); on CSR-ordered input this is a
+ * STABLE sort by col alone.  out_csr2csc[nnz]; out_colptr (nullable) [N+1] =
+ * storage.py:386-400; out_colcount (nullable) [N] = storage.py:405-420. */
+int ps_csr2csc(const int64_t *col, int64_t nnz, int64_t N, int64_t *out_csr2csc,
+               int64_t *out_colptr, int64_t *out_colcount, void *stream);
+/* storage.py:439-447 `csc2csr` = argsort(csr2csc) = inverse permutation. */
+int ps_invert_perm(const int64_t *perm, int64_t n, int64_t *out, void *stream);
+/* x[perm] for [n_src, row_bytes]-byte rows: storage.py:166-169,238-241, transpose.py:15,
+ * index_select.py:104-108.  out[n_out, row_bytes]. */
+int ps_gather_rows(const void *src, int64_t row_bytes, const int64_t *index, int64_t n_out,
+                   void *out, void *stream);
+/* transpose.py:9-33 `t()`: out_row = col[csr2csc] (streamed from colptr when given),
+ * out_col = row[csr2csc], out_value = value[csr2csc] in one pass. */
+int ps_transpose_gather(const int64_t *csr2csc, const int64_t *row, const int64_t *col,
+                        const void *value, int64_t row_bytes, int64_t nnz, const int64_t *colptr,
+                        int64_t N, int64_t *out_row, int64_t *out_col, void *out_value,
+                        void *stream);
+
+/* ------------------------------------------------------------------ paddle_scatter replacements */
+/* paddle_scatter.segment_csr(src, indptr, None, reduce): storage.py:471, reduce.py:51,
+ * tensor.py:437.  src [E, width], ptr[S+1], out [S, width]; empty segment -> 0. */
+int ps_segment_reduce(const void *src, int dtype, int64_t width, int64_t E, const int64_t *ptr,
+                      int64_t S, int reduce, void *out, void *stream);
+/* paddle_scatter.gather_csr(src, indptr): mul.py:16,79, index_select.py:29,65.
+ * src [S, row_bytes], out [E, row_bytes], out[e] = src[s] for e in [ptr[s], ptr[s+1]). */
+int ps_gather_csr(const void *src, int64_t row_bytes, const int64_t *ptr, int64_t S, int64_t E,
+                  void *out, void *stream);
+/* paddle_scatter.scatter(src, index, 0, None, dim_size, reduce): reduce.py:42.
+ * src [n, width], out [dim_size, width]; untouched rows -> 0. */
+int ps_scatter_reduce(const void *src, int dtype, int64_t width, const int64_t *index, int64_t n,
+                      int64_t dim_size, int reduce, void *out, void *stream);
+/* reduce.py:17-27 dim=None: out[1] = reduce over all n elements of src. */
+int ps_reduce_all(const void *src, int dtype, int64_t n, int reduce, void *out, void *stream);
+
+/* ------------------------------------------------------------------ broadcast mul */
+/* mul.py:76-93 row-wise branch: out[e,:] = value[e,:] * other[r,:] for e in row r
+ * (gather_csr fused with the multiply).  value/out [nnz,width] (may alias), other [M,width]. */
+int ps_mul_row(const void *value, int dtype, int64_t width, const int64_t *rowptr, int64_t M,
+               int64_t nnz, const void *other, void *out, void *stream);
+/* mul.py:81-82 col-wise branch: out[e,:] = value[e,:] * other[col[e],:]. */
+int ps_mul_col(const void *value, int dtype, int64_t width, const int64_t *col, int64_t nnz,
+               const void *other, void *out, void *stream);
+/* mul.py:96-119 `mul_nnz`: out = value * other, both [n]. */
+int ps_mul_nnz(const void *value, int dtype, int64_t n, const void *other, void *out, void *stream);
+
+/* ------------------------------------------------------------------ select */
+/* masked_select.py:18-24: indices of the set entries of a byte mask, ascending.
+ * out_idx sized n; *host_count = number selected.  Synchronises. */
+int ps_mask_to_index(const uint8_t *mask, int64_t n, int64_t *out_idx, int64_t *host_count,
+                     void *stream);
+/* masked_select.py:93-114 `masked_select_nnz`: entry mask via an indirection
+ * (mask[index[e]]) compacted to entry ids.  index nullable (then mask[e]).  Synchronises. */
+int ps_mask_entries(const uint8_t *mask, const int64_t *index, int64_t nnz, int64_t *out_idx,
+                    int64_t *host_count, void *stream);
+/* index_select.py:17-33 (dim 0) and :53-67 (dim 1, on the CSC arrays): given the new
+ * pointer out_ptr[K+1] (ps_count2ptr of the old counts at idx) write, for every output
+ * entry e of new row r: out_major[e] = r, out_perm[e] = old_ptr[idx[r]] + e - out_ptr[r],
+ * out_minor[e] = minor[out_perm[e]], out_value[e] = value[out_perm[e]].
+ * out_perm / out_value nullable. */
+int ps_index_select_fill(const int64_t *old_ptr, const int64_t *minor, const void *value,
+                         int64_t row_bytes, const int64_t *idx, int64_t K, const int64_t *out_ptr,
+                         int64_t E, int64_t *out_major, int64_t *out_minor, void *out_value,
+                         int64_t *out_perm, void *stream);
+
+/* ------------------------------------------------------------------ sample_adj */
+/* csrc/sample.cpp:8-24 -> csrc/cpu/sample_cpu.cpp:10-148 (the reference has NO GPU path:
+ * sample.cpp:13-15 throws).  Draw u of seed position p is Philox4x32-10(seed;(p,u))
+ * reduced as low + r % (high-low) (the "fixed seed mapping").  Upper bounds for the
+ * caller's allocations: ps_sample_adj_bound.  out_rowptr[S+1]; out_col/out_e_id[bound];
+ * out_n_id[S+bound]; host_sizes[0] = E, host_sizes[1] = |n_id|.  Synchronises. */
+int ps_sample_adj_bound(const int64_t *rowptr, const int64_t *idx, int64_t S, int64_t num_neighbors,
+                        int replace, int64_t *host_bound, void *stream);
+int ps_sample_adj(const int64_t *rowptr, const int64_t *col, int64_t M, const int64_t *idx, int64_t S,
+                  int64_t num_neighbors, int replace, uint64_t seed, int64_t bound,
+                  int64_t *out_rowptr, int64_t *out_col, int64_t *out_n_id, int64_t *out_e_id,
+                  int64_t *host_sizes, void *stream);
+
+/* ------------------------------------------------------------------ row-range partitioning (multi-GPU) */
+/* SURVEY.md 8e (the reference has no distributed code).  Coarse row histogram used to
+ * choose nnz-balanced, row-aligned splitters: out_hist[b] += #{e : row[e] >> shift == b}. */
+int ps_dist_row_histogram(const int64_t *row, int64_t nnz, int shift, int64_t buckets,
+                          int64_t *out_hist, void *stream);
+/* Stable partition of the local tuples by destination rank (row in
+ * [splitters[g], splitters[g+1])), G <= 64.  Outputs are grouped by rank in send order;
+ * out_counts[G] (device).  splitters is a DEVICE array of G+1 row ids. */
+int ps_dist_partition(const int64_t *row, const int64_t *col, const void *value, int64_t row_bytes,
+                      int64_t nnz, const int64_t *splitters, int G, int64_t *out_row,
+                      int64_t *out_col, void *out_value, int64_t *out_counts, void *stream);
+/* out[i] = in[i] + delta (local <-> global row ids of a shard). */
+int ps_add_scalar(const int64_t *in, int64_t n, int64_t delta, int64_t *out, void *stream);
+
+/* ------------------------------------------------------------------ synthetic inputs (bench / tests) */
+/* SURVEY.md 8d generator: h = splitmix64(seed + i); row = (h >> 32) % M; col = (h & 0xffffffff) % N;
+ * value = fp32((splitmix64((seed ^ 0x9e3779b97f4a7c15) + i) >> 40) * 2^-24).  i in [first, first+n). */
+int ps_synth_coo(uint64_t seed, int64_t first, int64_t n, int64_t M, int64_t N, int64_t *out_row,
+                 int64_t *out_col, float *out_value, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PS_ABI_H */

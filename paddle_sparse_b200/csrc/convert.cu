@@ -1,0 +1,305 @@
+// ind2ptr / ptr2ind and the small pointer/count utilities around them.
+//
+// Reference behaviour restated (not ported):
+//   ind2ptr  csrc/convert.cpp:13-23, csrc/cpu/convert_cpu.cpp:6-30, csrc/cuda/convert_cuda.cu:6-40
+//   ptr2ind  csrc/convert.cpp:46-56, csrc/cpu/convert_cpu.cpp:32-48, csrc/cuda/convert_cuda.cu:42-68
+// The reference kernels are thread-per-element with a serial head/tail fill on one
+// thread (ind2ptr) and thread-per-row serial expansion (ptr2ind).  Here:
+//   ind2ptr  = 128-bit coalesced boundary detection; gaps longer than a warp are filled
+//              warp-cooperatively; head [0, ind[0]] and tail (ind[last], M] are filled by
+//              dedicated blocks of the same launch with coalesced grid-stride stores.
+//   ptr2ind  = load-balanced over OUTPUT tiles: 32-ary warp search for the first/last row
+//              of the tile, row starts scattered into shared memory, block max-scan,
+//              coalesced 128-bit stores.  Degree skew cannot serialise a thread.
+#include "common.cuh"
+#include "convert.cuh"
+
+namespace ps {
+
+// ============================================================================= ind2ptr
+template <typename IndT>
+__device__ __forceinline__ int64_t ind_load(const IndT *p) { return (int64_t)*p; }
+
+template <typename IndT, int THREADS>
+__global__ void __launch_bounds__(THREADS)
+ind2ptr_kernel(const IndT *__restrict__ ind, int64_t numel, int64_t M, int64_t *__restrict__ out,
+               int elem_blocks, int fill_blocks, bool aligned16) {
+  if ((int)blockIdx.x >= elem_blocks) {
+    // ---- head / tail fill blocks
+    const int64_t first = (int64_t)ind[0], last = (int64_t)ind[numel - 1];
+    const int64_t fb = (int)blockIdx.x - elem_blocks;
+    const int64_t stride = (int64_t)fill_blocks * THREADS;
+    for (int64_t r = fb * THREADS + threadIdx.x; r <= first && r <= M; r += stride) out[r] = 0;
+    for (int64_t r = last + 1 + fb * THREADS + threadIdx.x; r <= M; r += stride) out[r] = numel;
+    return;
+  }
+  // ---- boundary detection: each thread owns 2 consecutive elements (one 128-bit load for int64)
+  const int64_t e0 = ((int64_t)blockIdx.x * THREADS + threadIdx.x) * 2;
+  int64_t v0 = 0, v1 = 0, prev = 0;
+  const bool has0 = e0 < numel, has1 = e0 + 1 < numel;
+  if (has0) {
+    if (sizeof(IndT) == 8 && has1 && aligned16) {
+      const longlong2 t = ld_stream2(reinterpret_cast<const int64_t *>(ind) + e0);
+      v0 = t.x;
+      v1 = t.y;
+    } else {
+      v0 = (int64_t)ind[e0];
+      v1 = has1 ? (int64_t)ind[e0 + 1] : v0;
+    }
+  }
+  // previous element: neighbour lane's v1, lane 0 reads it from memory
+  int64_t up = __shfl_up_sync(0xffffffffu, v1, 1);
+  if (has0) prev = (lane_id() == 0) ? (e0 == 0 ? v0 : (int64_t)ind[e0 - 1]) : up;
+  // rows r in (prev, v0] get e0 ; rows in (v0, v1] get e0+1   (head handled by fill blocks)
+  int64_t lo[2] = {prev + 1, v0 + 1}, hi[2] = {v0, v1};
+  if (!has0) { lo[0] = 1; hi[0] = 0; }
+  if (!has1) { lo[1] = 1; hi[1] = 0; }
+#pragma unroll
+  for (int k = 0; k < 2; ++k) {
+    const int64_t gap = hi[k] - lo[k] + 1;
+    const bool is_long = gap > 32;
+    if (!is_long)
+      for (int64_t r = lo[k]; r <= hi[k]; ++r) out[r] = e0 + k;
+    unsigned m = __ballot_sync(0xffffffffu, is_long);
+    while (m) {  // warp-cooperative fill of every long gap in this warp
+      const int src = __ffs(m) - 1;
+      m &= m - 1;
+      const int64_t l = __shfl_sync(0xffffffffu, lo[k], src);
+      const int64_t h = __shfl_sync(0xffffffffu, hi[k], src);
+      const int64_t val = __shfl_sync(0xffffffffu, e0 + k, src);
+      for (int64_t r = l + lane_id(); r <= h; r += 32) out[r] = val;
+    }
+  }
+}
+
+template <typename IndT>
+int ind2ptr_launch(const IndT *ind, int64_t numel, int64_t M, int64_t *out, cudaStream_t s) {
+  if (M < 0 || numel < 0) { set_error("ind2ptr: negative size"); return PS_ERR_ARG; }
+  if (numel == 0) {  // convert_cpu.cpp:9-11: empty input -> zeros(M+1)
+    PS_CUDA(cudaMemsetAsync(out, 0, sizeof(int64_t) * (size_t)(M + 1), s));
+    return PS_OK;
+  }
+  constexpr int THREADS = 256;
+  const int64_t elem_blocks = ceil_div(numel, THREADS * 2);
+  int64_t fill_blocks = ceil_div(M + 1, THREADS * 8);
+  const int64_t cap = 2 * (int64_t)sm_count();
+  if (fill_blocks > cap) fill_blocks = cap;
+  if (fill_blocks < 1) fill_blocks = 1;
+  if (elem_blocks + fill_blocks > 2147483647LL) { set_error("ind2ptr: input too large"); return PS_ERR_ARG; }
+  ind2ptr_kernel<IndT, THREADS><<<(unsigned)(elem_blocks + fill_blocks), THREADS, 0, s>>>(
+      ind, numel, M, out, (int)elem_blocks, (int)fill_blocks, (reinterpret_cast<uintptr_t>(ind) & 15) == 0);
+  PS_LAUNCH_OK();
+  return PS_OK;
+}
+template int ind2ptr_launch<int64_t>(const int64_t *, int64_t, int64_t, int64_t *, cudaStream_t);
+template int ind2ptr_launch<uint32_t>(const uint32_t *, int64_t, int64_t, int64_t *, cudaStream_t);
+
+// ============================================================================= ptr2ind
+template <int THREADS, int ITEMS>
+__global__ void __launch_bounds__(THREADS)
+ptr2ind_kernel(const int64_t *__restrict__ ptr, int64_t M, int64_t E, int64_t *__restrict__ out) {
+  constexpr int TILE = THREADS * ITEMS;
+  __shared__ int32_t seg[TILE];
+  __shared__ int32_t aux[40];
+  const int64_t e0 = (int64_t)blockIdx.x * TILE;
+  const int tile_n = (int)((E - e0) < TILE ? (E - e0) : TILE);
+  expand_tile<THREADS, ITEMS>(ptr, M, e0, tile_n, seg, aux);
+  for (int j = threadIdx.x; j < tile_n; j += THREADS) out[e0 + j] = (int64_t)seg[j];
+}
+
+// ============================================================================= small utilities
+__global__ void ptr2count_kernel(const int64_t *__restrict__ ptr, int64_t M, int64_t *__restrict__ out) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < M) out[i] = ptr[i + 1] - ptr[i];
+}
+
+// Single-pass inclusive scan (decoupled look-back) writing out_ptr[i+1]; out_ptr[0] = 0.
+template <int THREADS, int ITEMS>
+__global__ void __launch_bounds__(THREADS)
+count2ptr_kernel(const int64_t *__restrict__ count, const int64_t *__restrict__ idx, int64_t n,
+                 int64_t *__restrict__ out, uint64_t *state /* [0]=ticket, [1..]=tiles */) {
+  constexpr int TILE = THREADS * ITEMS;
+  __shared__ int64_t warp_sums[33];
+  __shared__ int64_t s_tile, s_excl;
+  if (threadIdx.x == 0) s_tile = (int64_t)atomicAdd((unsigned long long *)state, 1ull);
+  __syncthreads();
+  const int64_t tile = s_tile;
+  const int64_t base = tile * TILE + (int64_t)threadIdx.x * ITEMS;
+  int64_t v[ITEMS];
+  int64_t sum = 0;
+#pragma unroll
+  for (int k = 0; k < ITEMS; ++k) {
+    const int64_t i = base + k;
+    v[k] = i < n ? (idx ? count[idx[i]] : count[i]) : 0;
+    sum += v[k];
+  }
+  int64_t total;
+  int64_t excl = block_exclusive_scan<int64_t, THREADS>(sum, warp_sums, &total);
+  if (threadIdx.x < 32) {
+    const uint64_t p = warp_lookback(state + 1, tile, (uint64_t)total);
+    if (threadIdx.x == 0) s_excl = (int64_t)p;
+  }
+  __syncthreads();
+  excl += s_excl;
+  if (tile == 0 && threadIdx.x == 0) out[0] = 0;
+#pragma unroll
+  for (int k = 0; k < ITEMS; ++k) {
+    excl += v[k];
+    if (base + k < n) out[base + k + 1] = excl;
+  }
+}
+
+__global__ void histogram_kernel(const int64_t *__restrict__ ind, int64_t n, int64_t *__restrict__ out) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+    atomicAdd((unsigned long long *)&out[ld_stream(ind + i)], 1ull);
+}
+
+__global__ void index_max_kernel(const int64_t *__restrict__ a, int64_t na, const int64_t *__restrict__ b,
+                                 int64_t nb, long long *out2) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  long long ma = -1, mb = -1;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < na; i += stride) {
+    const long long v = ld_stream(a + i);
+    ma = v > ma ? v : ma;
+  }
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nb; i += stride) {
+    const long long v = ld_stream(b + i);
+    mb = v > mb ? v : mb;
+  }
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) {
+    const long long oa = __shfl_xor_sync(0xffffffffu, ma, d), ob = __shfl_xor_sync(0xffffffffu, mb, d);
+    ma = oa > ma ? oa : ma;
+    mb = ob > mb ? ob : mb;
+  }
+  if (lane_id() == 0) {
+    if (ma >= 0) atomicMax(&out2[0], ma);
+    if (mb >= 0) atomicMax(&out2[1], mb);
+  }
+}
+
+// flags[0] &= non-decreasing, flags[1] &= strictly increasing (lexicographic on (row,col))
+__global__ void coo_order_kernel(const int64_t *__restrict__ row, const int64_t *__restrict__ col, int64_t nnz,
+                                 int *flags) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  bool inv = false, eq = false;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x + 1; i < nnz; i += stride) {
+    const int64_t r0 = row[i - 1], r1 = row[i], c0 = col[i - 1], c1 = col[i];
+    inv |= (r1 < r0) || (r1 == r0 && c1 < c0);
+    eq |= (r1 == r0 && c1 == c0);
+  }
+  if (__any_sync(0xffffffffu, inv) && lane_id() == 0) { flags[0] = 0; flags[1] = 0; }
+  if (__any_sync(0xffffffffu, eq) && lane_id() == 0) flags[1] = 0;
+}
+
+__global__ void add_scalar_kernel(const int64_t *__restrict__ in, int64_t n, int64_t delta, int64_t *__restrict__ out) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = in[i] + delta;
+}
+
+int count2ptr_launch(const int64_t *count, const int64_t *idx, int64_t n, int64_t *out_ptr, cudaStream_t s) {
+  if (n == 0) {
+    PS_CUDA(cudaMemsetAsync(out_ptr, 0, sizeof(int64_t), s));
+    return PS_OK;
+  }
+  constexpr int THREADS = 256, ITEMS = 8;
+  const int64_t tiles = ceil_div(n, THREADS * ITEMS);
+  Scratch scratch(s);
+  PS_SCRATCH(state, scratch, uint64_t, tiles + 1);
+  PS_CUDA(cudaMemsetAsync(state, 0, sizeof(uint64_t) * (size_t)(tiles + 1), s));
+  count2ptr_kernel<THREADS, ITEMS><<<(unsigned)tiles, THREADS, 0, s>>>(count, idx, n, out_ptr, state);
+  PS_LAUNCH_OK();
+  return PS_OK;
+}
+
+static inline unsigned stream_grid(int64_t n, int threads) {
+  int64_t b = ceil_div(n, threads);
+  const int64_t cap = 16 * (int64_t)sm_count();
+  if (b > cap) b = cap;
+  if (b < 1) b = 1;
+  return (unsigned)b;
+}
+
+}  // namespace ps
+
+using namespace ps;
+
+extern "C" {
+
+int ps_ind2ptr(const int64_t *ind, int64_t numel, int64_t M, int64_t *out_ptr, void *stream) {
+  return ind2ptr_launch<int64_t>(ind, numel, M, out_ptr, (cudaStream_t)stream);
+}
+
+int ps_ptr2ind(const int64_t *ptr, int64_t M, int64_t E, int64_t *out_ind, void *stream) {
+  PS_CHECK(M >= 0 && E >= 0, "ptr2ind: negative size");
+  PS_CHECK(M < 2147483647LL, "ptr2ind: M=%lld exceeds the 2^31-1 rows this build supports", (long long)M);
+  if (E == 0) return PS_OK;
+  PS_CHECK(M > 0, "ptr2ind: E > 0 with no rows");
+  constexpr int THREADS = 256, ITEMS = 8;
+  const int64_t tiles = ceil_div(E, THREADS * ITEMS);
+  ptr2ind_kernel<THREADS, ITEMS><<<(unsigned)tiles, THREADS, 0, (cudaStream_t)stream>>>(ptr, M, E, out_ind);
+  PS_LAUNCH_OK();
+  return PS_OK;
+}
+
+int ps_ptr2count(const int64_t *ptr, int64_t M, int64_t *out_count, void *stream) {
+  if (M <= 0) return PS_OK;
+  ptr2count_kernel<<<(unsigned)ceil_div(M, 256), 256, 0, (cudaStream_t)stream>>>(ptr, M, out_count);
+  PS_LAUNCH_OK();
+  return PS_OK;
+}
+
+int ps_count2ptr(const int64_t *count, const int64_t *idx, int64_t n, int64_t *out_ptr, int64_t *host_total,
+                 void *stream) {
+  PS_CHECK(n >= 0, "count2ptr: negative size");
+  PS_TRY(count2ptr_launch(count, idx, n, out_ptr, (cudaStream_t)stream));
+  if (host_total) PS_TRY(read_back(host_total, out_ptr + n, sizeof(int64_t), (cudaStream_t)stream));
+  return PS_OK;
+}
+
+int ps_histogram(const int64_t *ind, int64_t numel, int64_t bins, int64_t *out_count, void *stream) {
+  PS_CHECK(numel >= 0 && bins >= 0, "histogram: negative size");
+  cudaStream_t s = (cudaStream_t)stream;
+  if (bins > 0) PS_CUDA(cudaMemsetAsync(out_count, 0, sizeof(int64_t) * (size_t)bins, s));
+  if (numel == 0) return PS_OK;
+  histogram_kernel<<<stream_grid(numel, 256), 256, 0, s>>>(ind, numel, out_count);
+  PS_LAUNCH_OK();
+  return PS_OK;
+}
+
+int ps_index_max(const int64_t *a, int64_t na, const int64_t *b, int64_t nb, int64_t *host_max, void *stream) {
+  cudaStream_t s = (cudaStream_t)stream;
+  Scratch scratch(s);
+  PS_SCRATCH(d, scratch, long long, 2);
+  PS_CUDA(cudaMemsetAsync(d, 0xff, 2 * sizeof(long long), s));  // -1, -1
+  if (!b) nb = 0;
+  const int64_t n = na > nb ? na : nb;
+  if (n > 0) {
+    index_max_kernel<<<stream_grid(n, 256), 256, 0, s>>>(a, na, b, nb, d);
+    PS_LAUNCH_OK();
+  }
+  return read_back(host_max, d, 2 * sizeof(long long), s);
+}
+
+int ps_coo_order(const int64_t *row, const int64_t *col, int64_t nnz, int32_t *host_flags, void *stream) {
+  cudaStream_t s = (cudaStream_t)stream;
+  Scratch scratch(s);
+  PS_SCRATCH(d, scratch, int, 2);
+  const int ones[2] = {1, 1};
+  PS_CUDA(cudaMemcpyAsync(d, ones, sizeof(ones), cudaMemcpyHostToDevice, s));
+  if (nnz > 1) {
+    coo_order_kernel<<<stream_grid(nnz, 256), 256, 0, s>>>(row, col, nnz, d);
+    PS_LAUNCH_OK();
+  }
+  return read_back(host_flags, d, 2 * sizeof(int), s);
+}
+
+int ps_add_scalar(const int64_t *in, int64_t n, int64_t delta, int64_t *out, void *stream) {
+  if (n <= 0) return PS_OK;
+  add_scalar_kernel<<<(unsigned)ceil_div(n, 256), 256, 0, (cudaStream_t)stream>>>(in, n, delta, out);
+  PS_LAUNCH_OK();
+  return PS_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,426 @@
+// In-repo replacements for the paddle_scatter calls on the hot path:
+//   segment_csr  storage.py:471, reduce.py:51, tensor.py:437
+//   gather_csr   mul.py:16,79, index_select.py:29,65
+//   scatter      reduce.py:42
+// plus the fused broadcast multiplies of mul.py:76-93 and the dense reduction of
+// reduce.py:17-27.  paddle_scatter's source is not part of the reference tree; semantics are
+// restated from its documented behaviour (empty segment / untouched row -> 0).
+#include "common.cuh"
+#include "convert.cuh"
+#include "segment.cuh"
+
+namespace ps {
+
+// ============================================================================= segment reduce
+// G lanes cooperate on one output (segment s, feature f); o = s*width + f.
+template <typename T, int RED, int G>
+__global__ void __launch_bounds__(256)
+segment_reduce_kernel(const T *__restrict__ src, int64_t width, const int64_t *__restrict__ ptr, int64_t S,
+                      T *__restrict__ out, const uint32_t *__restrict__ perm) {
+  using A = typename Acc<T>::type;
+  const int64_t gid = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / G;
+  const int sub = threadIdx.x % G;
+  const int64_t total = S * width;
+  const bool live = gid < total;
+  const int64_t sgm = live ? gid / width : 0;
+  const int64_t f = live ? gid - sgm * width : 0;
+  int64_t lo = 0, hi = 0;
+  if (live) {
+    lo = ptr[sgm];
+    hi = ptr[sgm + 1];
+  }
+  A acc = Red<RED, A>::init();
+  for (int64_t e = lo + sub; e < hi; e += G) {
+    const int64_t r = perm ? (int64_t)perm[e] : e;
+    acc = Red<RED, A>::op(acc, to_acc<T>(src[r * width + f]));
+  }
+#pragma unroll
+  for (int d = G / 2; d > 0; d >>= 1) acc = Red<RED, A>::op(acc, __shfl_xor_sync(0xffffffffu, acc, d));
+  if (live && sub == 0) out[gid] = from_acc<T>(Red<RED, A>::finish(acc, hi - lo));
+}
+
+template <typename T, int RED>
+static int segment_reduce_typed(const T *src, int64_t width, const int64_t *ptr, int64_t S, T *out,
+                                const uint32_t *perm, int64_t E_hint, cudaStream_t s) {
+  const int64_t outputs = S * width;
+  if (outputs == 0) return PS_OK;
+  const double avg = S > 0 ? (double)E_hint / (double)S : 0.0;
+  int G = 32;
+  if (width >= 4 || avg <= 2.0) G = 1;
+  else if (avg <= 12.0) G = 4;
+  else if (avg <= 48.0) G = 8;
+  const int64_t threads = outputs * G;
+  const unsigned blocks = (unsigned)ceil_div(threads, 256);
+  switch (G) {
+    case 1: segment_reduce_kernel<T, RED, 1><<<blocks, 256, 0, s>>>(src, width, ptr, S, out, perm); break;
+    case 4: segment_reduce_kernel<T, RED, 4><<<blocks, 256, 0, s>>>(src, width, ptr, S, out, perm); break;
+    case 8: segment_reduce_kernel<T, RED, 8><<<blocks, 256, 0, s>>>(src, width, ptr, S, out, perm); break;
+    default: segment_reduce_kernel<T, RED, 32><<<blocks, 256, 0, s>>>(src, width, ptr, S, out, perm); break;
+  }
+  PS_LAUNCH_OK();
+  return PS_OK;
+}
+
+int segment_reduce_launch(const void *src, int dtype, int64_t width, const int64_t *ptr, int64_t S, int reduce,
+                          void *out, const uint32_t *perm32, int64_t E_hint, cudaStream_t s) {
+  PS_DISPATCH_DTYPE(dtype, T,
+                    PS_DISPATCH_REDUCE(reduce, RED,
+                                       return (segment_reduce_typed<T, RED>(reinterpret_cast<const T *>(src), width, ptr,
+                                                                            S, reinterpret_cast<T *>(out), perm32,
+                                                                            E_hint, s))));
+  return PS_OK;
+}
+
+// ============================================================================= row gathers
+template <typename U, typename IndexT>
+__global__ void __launch_bounds__(256)
+gather_rows_kernel(const U *__restrict__ src, int64_t upr, const IndexT *__restrict__ index, int64_t n_units,
+                   U *__restrict__ out) {
+  const int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= n_units) return;
+  const int64_t r = q / upr, u = q - r * upr;
+  out[q] = src[(int64_t)index[r] * upr + u];
+}
+
+template <typename IndexT>
+int gather_rows_launch(const void *src, int64_t row_bytes, const IndexT *index, int64_t n_out, void *out,
+                       cudaStream_t s) {
+  if (n_out <= 0 || row_bytes <= 0) return PS_OK;
+  const int unit = copy_unit(row_bytes, src, out);
+  const int64_t upr = row_bytes / unit, n_units = n_out * upr;
+  const unsigned blocks = (unsigned)ceil_div(n_units, 256);
+#define PS_G(U) gather_rows_kernel<U, IndexT><<<blocks, 256, 0, s>>>((const U *)src, upr, index, n_units, (U *)out)
+  switch (unit) {
+    case 16: PS_G(uint4); break;
+    case 8: PS_G(uint64_t); break;
+    case 4: PS_G(uint32_t); break;
+    case 2: PS_G(uint16_t); break;
+    default: PS_G(uint8_t); break;
+  }
+#undef PS_G
+  PS_LAUNCH_OK();
+  return PS_OK;
+}
+template int gather_rows_launch<int64_t>(const void *, int64_t, const int64_t *, int64_t, void *, cudaStream_t);
+template int gather_rows_launch<uint32_t>(const void *, int64_t, const uint32_t *, int64_t, void *, cudaStream_t);
+
+// gather_csr: out[e,:] = src[segment(e),:], segment ids resolved per output tile
+template <typename U, int THREADS, int ITEMS>
+__global__ void __launch_bounds__(THREADS)
+gather_csr_kernel(const U *__restrict__ src, int64_t upr, const int64_t *__restrict__ ptr, int64_t S, int64_t E,
+                  U *__restrict__ out) {
+  constexpr int TILE = THREADS * ITEMS;
+  __shared__ int32_t seg[TILE];
+  __shared__ int32_t aux[40];
+  const int64_t e0 = (int64_t)blockIdx.x * TILE;
+  const int tile_n = (int)((E - e0) < TILE ? (E - e0) : TILE);
+  expand_tile<THREADS, ITEMS>(ptr, S, e0, tile_n, seg, aux);
+  const int64_t units = (int64_t)tile_n * upr;
+  for (int64_t q = threadIdx.x; q < units; q += THREADS) {
+    const int64_t j = q / upr, u = q - j * upr;
+    out[(e0 + j) * upr + u] = src[(int64_t)seg[j] * upr + u];
+  }
+}
+
+// ============================================================================= broadcast multiply
+template <typename T>
+__device__ __forceinline__ T mul_values(T a, T b) {
+  using A = typename Acc<T>::type;
+  return from_acc<T>(to_acc<T>(a) * to_acc<T>(b));
+}
+
+template <typename T, int THREADS, int ITEMS>
+__global__ void __launch_bounds__(THREADS)
+mul_row_kernel(const T *value, int64_t width, const int64_t *__restrict__ rowptr, int64_t M, int64_t nnz,
+               const T *__restrict__ other, T *out) {
+  constexpr int TILE = THREADS * ITEMS;
+  __shared__ int32_t seg[TILE];
+  __shared__ int32_t aux[40];
+  const int64_t e0 = (int64_t)blockIdx.x * TILE;
+  const int tile_n = (int)((nnz - e0) < TILE ? (nnz - e0) : TILE);
+  expand_tile<THREADS, ITEMS>(rowptr, M, e0, tile_n, seg, aux);
+  const int64_t units = (int64_t)tile_n * width;
+  for (int64_t q = threadIdx.x; q < units; q += THREADS) {
+    const int64_t j = q / width, f = q - j * width;
+    const int64_t o = (e0 + j) * width + f;
+    out[o] = mul_values<T>(value[o], other[(int64_t)seg[j] * width + f]);
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+mul_col_kernel(const T *value, int64_t width, const int64_t *__restrict__ col, int64_t n_units,
+               const T *__restrict__ other, T *out) {
+  const int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= n_units) return;
+  const int64_t e = q / width, f = q - e * width;
+  out[q] = mul_values<T>(value[q], other[col[e] * width + f]);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+mul_nnz_kernel(const T *value, int64_t n, const T *__restrict__ other, T *out) {
+  const int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (q < n) out[q] = mul_values<T>(value[q], other[q]);
+}
+
+// ============================================================================= scatter reduce (by col)
+template <typename A> __device__ __forceinline__ void atomic_red_add(A *p, A v) { atomicAdd(p, v); }
+template <> __device__ __forceinline__ void atomic_red_add<int64_t>(int64_t *p, int64_t v) {
+  atomicAdd(reinterpret_cast<unsigned long long *>(p), (unsigned long long)v);
+}
+__device__ __forceinline__ void atomic_red_min(int32_t *p, int32_t v) { atomicMin(p, v); }
+__device__ __forceinline__ void atomic_red_max(int32_t *p, int32_t v) { atomicMax(p, v); }
+__device__ __forceinline__ void atomic_red_min(int64_t *p, int64_t v) { atomicMin((long long *)p, (long long)v); }
+__device__ __forceinline__ void atomic_red_max(int64_t *p, int64_t v) { atomicMax((long long *)p, (long long)v); }
+// IEEE order == signed-int order for non-negative floats and reversed unsigned order for negatives
+__device__ __forceinline__ void atomic_red_min(float *p, float v) {
+  if (v >= 0.f) atomicMin(reinterpret_cast<int *>(p), __float_as_int(v));
+  else atomicMax(reinterpret_cast<unsigned int *>(p), __float_as_uint(v));
+}
+__device__ __forceinline__ void atomic_red_max(float *p, float v) {
+  if (v >= 0.f) atomicMax(reinterpret_cast<int *>(p), __float_as_int(v));
+  else atomicMin(reinterpret_cast<unsigned int *>(p), __float_as_uint(v));
+}
+__device__ __forceinline__ void atomic_red_min(double *p, double v) {
+  if (v >= 0.0) atomicMin(reinterpret_cast<long long *>(p), __double_as_longlong(v));
+  else atomicMax(reinterpret_cast<unsigned long long *>(p), (unsigned long long)__double_as_longlong(v));
+}
+__device__ __forceinline__ void atomic_red_max(double *p, double v) {
+  if (v >= 0.0) atomicMax(reinterpret_cast<long long *>(p), __double_as_longlong(v));
+  else atomicMin(reinterpret_cast<unsigned long long *>(p), (unsigned long long)__double_as_longlong(v));
+}
+
+template <typename A, int RED>
+__global__ void fill_init_kernel(A *p, int64_t n) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) p[i] = Red<RED, A>::init();
+}
+
+template <typename T, int RED>
+__global__ void __launch_bounds__(256)
+scatter_reduce_kernel(const T *__restrict__ src, int64_t width, const int64_t *__restrict__ index, int64_t n_units,
+                      typename Acc<T>::type *__restrict__ acc, int *__restrict__ cnt) {
+  using A = typename Acc<T>::type;
+  const int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= n_units) return;
+  const int64_t e = q / width, f = q - e * width;
+  const int64_t r = index[e];
+  const A v = to_acc<T>(src[q]);
+  if (RED == PS_SUM || RED == PS_MEAN) atomic_red_add<A>(&acc[r * width + f], v);
+  else if (RED == PS_MIN) atomic_red_min(&acc[r * width + f], v);
+  else atomic_red_max(&acc[r * width + f], v);
+  if (RED != PS_SUM && f == 0) atomicAdd(&cnt[r], 1);
+}
+
+template <typename T, int RED>
+__global__ void __launch_bounds__(256)
+scatter_finish_kernel(const typename Acc<T>::type *__restrict__ acc, const int *__restrict__ cnt, int64_t width,
+                      int64_t n_units, T *__restrict__ out) {
+  using A = typename Acc<T>::type;
+  const int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= n_units) return;
+  const int64_t c = RED == PS_SUM ? 1 : (int64_t)cnt[q / width];
+  out[q] = from_acc<T>(Red<RED, A>::finish(acc[q], c));
+}
+
+template <typename T, int RED>
+static int scatter_reduce_typed(const T *src, int64_t width, const int64_t *index, int64_t n, int64_t dim_size, T *out,
+                                cudaStream_t s) {
+  using A = typename Acc<T>::type;
+  const int64_t out_units = dim_size * width;
+  if (out_units == 0) return PS_OK;
+  Scratch scratch(s);
+  constexpr bool same = sizeof(A) == sizeof(T);  // accumulate in place unless T is a 16-bit float
+  A *acc = reinterpret_cast<A *>(out);
+  if (!same) {
+    PS_SCRATCH(tmp, scratch, A, out_units);
+    acc = tmp;
+  }
+  int *cnt = nullptr;
+  if (RED != PS_SUM) {
+    PS_SCRATCH(c, scratch, int, dim_size);
+    PS_CUDA(cudaMemsetAsync(c, 0, sizeof(int) * (size_t)dim_size, s));
+    cnt = c;
+  }
+  fill_init_kernel<A, RED><<<(unsigned)ceil_div(out_units, 256), 256, 0, s>>>(acc, out_units);
+  PS_LAUNCH_OK();
+  const int64_t n_units = n * width;
+  if (n_units > 0) {
+    scatter_reduce_kernel<T, RED><<<(unsigned)ceil_div(n_units, 256), 256, 0, s>>>(src, width, index, n_units, acc, cnt);
+    PS_LAUNCH_OK();
+  }
+  if (RED != PS_SUM || !same) {
+    scatter_finish_kernel<T, RED><<<(unsigned)ceil_div(out_units, 256), 256, 0, s>>>(acc, cnt, width, out_units, out);
+    PS_LAUNCH_OK();
+  }
+  return PS_OK;
+}
+
+// ============================================================================= dense reduction (dim=None)
+template <typename T> struct Wide { using type = double; };
+template <> struct Wide<int32_t> { using type = int64_t; };
+template <> struct Wide<int64_t> { using type = int64_t; };
+template <typename T> __device__ __forceinline__ typename Wide<T>::type to_wide(T v) { return (typename Wide<T>::type)to_acc<T>(v); }
+template <typename T> __device__ __forceinline__ T from_wide(typename Wide<T>::type v) {
+  return from_acc<T>((typename Acc<T>::type)v);
+}
+
+template <typename T, int RED, int THREADS>
+__global__ void __launch_bounds__(THREADS)
+reduce_all_kernel(const T *__restrict__ src, int64_t n, typename Wide<T>::type *__restrict__ partial) {
+  using W = typename Wide<T>::type;
+  __shared__ W sh[THREADS / 32];
+  W acc = Red<RED, W>::init();
+  const int64_t stride = (int64_t)gridDim.x * THREADS;
+  for (int64_t i = (int64_t)blockIdx.x * THREADS + threadIdx.x; i < n; i += stride)
+    acc = Red<RED, W>::op(acc, to_wide<T>(src[i]));
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) acc = Red<RED, W>::op(acc, __shfl_xor_sync(0xffffffffu, acc, d));
+  if (lane_id() == 0) sh[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    acc = threadIdx.x < THREADS / 32 ? sh[threadIdx.x] : Red<RED, W>::init();
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) acc = Red<RED, W>::op(acc, __shfl_xor_sync(0xffffffffu, acc, d));
+    if (threadIdx.x == 0) partial[blockIdx.x] = acc;
+  }
+}
+
+template <typename T, int RED>
+__global__ void reduce_all_finish_kernel(const typename Wide<T>::type *__restrict__ partial, int nblocks, int64_t n,
+                                         T *__restrict__ out) {
+  using W = typename Wide<T>::type;
+  W acc = Red<RED, W>::init();
+  for (int i = threadIdx.x; i < nblocks; i += 32) acc = Red<RED, W>::op(acc, partial[i]);
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) acc = Red<RED, W>::op(acc, __shfl_xor_sync(0xffffffffu, acc, d));
+  if (threadIdx.x == 0) out[0] = from_wide<T>(Red<RED, W>::finish(acc, n));
+}
+
+template <typename T, int RED>
+static int reduce_all_typed(const T *src, int64_t n, T *out, cudaStream_t s) {
+  using W = typename Wide<T>::type;
+  constexpr int THREADS = 256;
+  int64_t blocks = ceil_div(n > 0 ? n : 1, THREADS * 8);
+  const int64_t cap = 4 * (int64_t)sm_count();
+  if (blocks > cap) blocks = cap;
+  Scratch scratch(s);
+  PS_SCRATCH(partial, scratch, W, blocks);
+  reduce_all_kernel<T, RED, THREADS><<<(unsigned)blocks, THREADS, 0, s>>>(src, n, partial);
+  PS_LAUNCH_OK();
+  reduce_all_finish_kernel<T, RED><<<1, 32, 0, s>>>(partial, (int)blocks, n, out);
+  PS_LAUNCH_OK();
+  return PS_OK;
+}
+
+}  // namespace ps
+
+using namespace ps;
+
+extern "C" {
+
+int ps_segment_reduce(const void *src, int dtype, int64_t width, int64_t E, const int64_t *ptr, int64_t S, int reduce,
+                      void *out, void *stream) {
+  PS_CHECK(S >= 0 && width >= 1 && E >= 0, "segment_reduce: bad sizes");
+  if (S == 0) return PS_OK;
+  // E only steers the lanes-per-segment choice (average segment length)
+  return segment_reduce_launch(src, dtype, width, ptr, S, reduce, out, nullptr, E, (cudaStream_t)stream);
+}
+
+int ps_gather_rows(const void *src, int64_t row_bytes, const int64_t *index, int64_t n_out, void *out, void *stream) {
+  PS_CHECK(row_bytes >= 0 && n_out >= 0, "gather_rows: negative size");
+  return gather_rows_launch<int64_t>(src, row_bytes, index, n_out, out, (cudaStream_t)stream);
+}
+
+int ps_gather_csr(const void *src, int64_t row_bytes, const int64_t *ptr, int64_t S, int64_t E, void *out,
+                  void *stream) {
+  PS_CHECK(row_bytes >= 0 && S >= 0 && E >= 0, "gather_csr: negative size");
+  PS_CHECK(S < 2147483647LL, "gather_csr: too many segments");
+  if (E == 0 || row_bytes == 0) return PS_OK;
+  PS_CHECK(S > 0, "gather_csr: E > 0 with no segments");
+  constexpr int THREADS = 256, ITEMS = 8;
+  const unsigned blocks = (unsigned)ceil_div(E, THREADS * ITEMS);
+  const int unit = copy_unit(row_bytes, src, out);
+  const int64_t upr = row_bytes / unit;
+  cudaStream_t s = (cudaStream_t)stream;
+#define PS_G(U) gather_csr_kernel<U, THREADS, ITEMS><<<blocks, THREADS, 0, s>>>((const U *)src, upr, ptr, S, E, (U *)out)
+  switch (unit) {
+    case 16: PS_G(uint4); break;
+    case 8: PS_G(uint64_t); break;
+    case 4: PS_G(uint32_t); break;
+    case 2: PS_G(uint16_t); break;
+    default: PS_G(uint8_t); break;
+  }
+#undef PS_G
+  PS_LAUNCH_OK();
+  return PS_OK;
+}
+
+int ps_scatter_reduce(const void *src, int dtype, int64_t width, const int64_t *index, int64_t n, int64_t dim_size,
+                      int reduce, void *out, void *stream) {
+  PS_CHECK(n >= 0 && dim_size >= 0 && width >= 1, "scatter_reduce: bad sizes");
+  cudaStream_t s = (cudaStream_t)stream;
+  PS_DISPATCH_DTYPE(dtype, T,
+                    PS_DISPATCH_REDUCE(reduce, RED,
+                                       return (scatter_reduce_typed<T, RED>(reinterpret_cast<const T *>(src), width,
+                                                                            index, n, dim_size,
+                                                                            reinterpret_cast<T *>(out), s))));
+  return PS_OK;
+}
+
+int ps_reduce_all(const void *src, int dtype, int64_t n, int reduce, void *out, void *stream) {
+  PS_CHECK(n >= 0, "reduce_all: negative size");
+  cudaStream_t s = (cudaStream_t)stream;
+  PS_DISPATCH_DTYPE(dtype, T,
+                    PS_DISPATCH_REDUCE(reduce, RED,
+                                       return (reduce_all_typed<T, RED>(reinterpret_cast<const T *>(src), n,
+                                                                        reinterpret_cast<T *>(out), s))));
+  return PS_OK;
+}
+
+int ps_mul_row(const void *value, int dtype, int64_t width, const int64_t *rowptr, int64_t M, int64_t nnz,
+               const void *other, void *out, void *stream) {
+  PS_CHECK(width >= 1 && M >= 0 && nnz >= 0, "mul_row: bad sizes");
+  PS_CHECK(M < 2147483647LL, "mul_row: too many rows");
+  if (nnz == 0) return PS_OK;
+  constexpr int THREADS = 256, ITEMS = 8;
+  const unsigned blocks = (unsigned)ceil_div(nnz, THREADS * ITEMS);
+  cudaStream_t s = (cudaStream_t)stream;
+  PS_DISPATCH_DTYPE(dtype, T,
+                    (mul_row_kernel<T, THREADS, ITEMS><<<blocks, THREADS, 0, s>>>(
+                        reinterpret_cast<const T *>(value), width, rowptr, M, nnz, reinterpret_cast<const T *>(other),
+                        reinterpret_cast<T *>(out))));
+  PS_LAUNCH_OK();
+  return PS_OK;
+}
+
+int ps_mul_col(const void *value, int dtype, int64_t width, const int64_t *col, int64_t nnz, const void *other,
+               void *out, void *stream) {
+  PS_CHECK(width >= 1 && nnz >= 0, "mul_col: bad sizes");
+  const int64_t n_units = nnz * width;
+  if (n_units == 0) return PS_OK;
+  const unsigned blocks = (unsigned)ceil_div(n_units, 256);
+  cudaStream_t s = (cudaStream_t)stream;
+  PS_DISPATCH_DTYPE(dtype, T,
+                    (mul_col_kernel<T><<<blocks, 256, 0, s>>>(reinterpret_cast<const T *>(value), width, col, n_units,
+                                                              reinterpret_cast<const T *>(other),
+                                                              reinterpret_cast<T *>(out))));
+  PS_LAUNCH_OK();
+  return PS_OK;
+}
+
+int ps_mul_nnz(const void *value, int dtype, int64_t n, const void *other, void *out, void *stream) {
+  PS_CHECK(n >= 0, "mul_nnz: negative size");
+  if (n == 0) return PS_OK;
+  const unsigned blocks = (unsigned)ceil_div(n, 256);
+  cudaStream_t s = (cudaStream_t)stream;
+  PS_DISPATCH_DTYPE(dtype, T,
+                    (mul_nnz_kernel<T><<<blocks, 256, 0, s>>>(reinterpret_cast<const T *>(value), n,
+                                                              reinterpret_cast<const T *>(other),
+                                                              reinterpret_cast<T *>(out))));
+  PS_LAUNCH_OK();
+  return PS_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,125 @@
+// CSC structures and transpose.
+//
+// Reference behaviour restated (not ported):
+//   storage.py:425-434  csr2csc = argsort(M*col + row)      (a second full 64-bit sort)
+//   storage.py:439-447  csc2csr = argsort(csr2csc)          (a third full sort)
+//   storage.py:386-420  colptr / colcount
+//   transpose.py:9-33   t(): three separate gathers through csr2csc
+// Here: the entries are already in CSR order, so csr2csc is a STABLE radix sort on the
+// col bits alone with the entry index as payload (ties keep row order); colptr falls out
+// of the sorted col keys by boundary detection (the ind2ptr kernel on 32-bit keys);
+// csc2csr is one inverse-permutation scatter; t() is one fused gather.
+#include "common.cuh"
+#include "convert.cuh"
+#include "radix_sort.cuh"
+#include "segment.cuh"
+
+namespace ps {
+
+__global__ void __launch_bounds__(256)
+invert_perm_kernel(const int64_t *__restrict__ perm, int64_t n, int64_t *__restrict__ out) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[ld_stream(perm + i)] = i;
+}
+
+// out_col[j] = row[p], out_row[j] = col[p] (unless streamed from colptr), out_value[j] = value[p]
+template <typename U, bool WITH_ROW, bool WITH_VALUE>
+__global__ void __launch_bounds__(256)
+transpose_gather_kernel(const int64_t *__restrict__ csr2csc, const int64_t *__restrict__ row,
+                        const int64_t *__restrict__ col, const U *__restrict__ value, int64_t nnz,
+                        int64_t *__restrict__ out_row, int64_t *__restrict__ out_col, U *__restrict__ out_value) {
+  const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= nnz) return;
+  const int64_t p = ld_stream(csr2csc + j);
+  out_col[j] = row[p];
+  if (WITH_ROW) out_row[j] = col[p];
+  if (WITH_VALUE) out_value[j] = value[p];
+}
+
+}  // namespace ps
+
+using namespace ps;
+
+extern "C" {
+
+int ps_csr2csc(const int64_t *col, int64_t nnz, int64_t N, int64_t *out_csr2csc, int64_t *out_colptr,
+               int64_t *out_colcount, void *stream) {
+  PS_CHECK(nnz >= 0 && N >= 0, "csr2csc: negative size");
+  PS_CHECK(nnz < (int64_t(1) << 32), "csr2csc: nnz=%lld exceeds the 2^32-1 entries per call this build supports",
+           (long long)nnz);
+  PS_CHECK(N <= (int64_t(1) << 32), "csr2csc: N=%lld exceeds the 2^32 columns this build supports", (long long)N);
+  cudaStream_t s = (cudaStream_t)stream;
+  Scratch scratch(s);
+  const bool want_ptr = out_colptr || out_colcount;
+  int64_t *colptr = out_colptr;
+  if (want_ptr && !colptr) {
+    PS_SCRATCH(tmp, scratch, int64_t, N + 1);
+    colptr = tmp;
+  }
+  if (nnz == 0) {
+    if (want_ptr) PS_CUDA(cudaMemsetAsync(colptr, 0, sizeof(int64_t) * (size_t)(N + 1), s));
+    if (out_colcount && N > 0) PS_CUDA(cudaMemsetAsync(out_colcount, 0, sizeof(int64_t) * (size_t)N, s));
+    return PS_OK;
+  }
+  const int cbits = bits_for(N);
+  PS_SCRATCH(k0, scratch, uint32_t, nnz);
+  PS_SCRATCH(k1, scratch, uint32_t, nnz);
+  PS_SCRATCH(p0, scratch, uint32_t, nnz);
+  PS_SCRATCH(p1, scratch, uint32_t, nnz);
+  const int passes = make_sort_plan(cbits).passes;
+  uint32_t *sorted_col = (passes & 1) ? k0 : k1;
+  KeyDst kd = want_ptr ? KeyDst{sorted_col, nullptr, KDST_KEYS, 0} : KeyDst{nullptr, nullptr, KDST_NONE, 0};
+  PS_TRY(radix_sort_pairs<uint32_t>(KeySrc{col, nullptr, KSRC_I64, 0}, PaySrc{nullptr, PSRC_IOTA}, nnz, cbits, k0, k1,
+                                    p0, p1, kd, PayDst{out_csr2csc, PDST_I64}, scratch, s));
+  if (want_ptr) PS_TRY(ind2ptr_launch<uint32_t>(sorted_col, nnz, N, colptr, s));
+  if (out_colcount) PS_TRY(ps_ptr2count(colptr, N, out_colcount, stream));
+  return PS_OK;
+}
+
+int ps_invert_perm(const int64_t *perm, int64_t n, int64_t *out, void *stream) {
+  PS_CHECK(n >= 0, "invert_perm: negative size");
+  if (n == 0) return PS_OK;
+  invert_perm_kernel<<<(unsigned)ceil_div(n, 256), 256, 0, (cudaStream_t)stream>>>(perm, n, out);
+  PS_LAUNCH_OK();
+  return PS_OK;
+}
+
+int ps_transpose_gather(const int64_t *csr2csc, const int64_t *row, const int64_t *col, const void *value,
+                        int64_t row_bytes, int64_t nnz, const int64_t *colptr, int64_t N, int64_t *out_row,
+                        int64_t *out_col, void *out_value, void *stream) {
+  PS_CHECK(nnz >= 0 && N >= 0 && row_bytes >= 0, "transpose_gather: negative size");
+  if (nnz == 0) return PS_OK;
+  cudaStream_t s = (cudaStream_t)stream;
+  const bool with_row = colptr == nullptr;
+  if (!with_row) PS_TRY(ps_ptr2ind(colptr, N, nnz, out_row, stream));  // col[csr2csc] is just the sorted col
+  const unsigned blocks = (unsigned)ceil_div(nnz, 256);
+  int unit = value ? copy_unit(row_bytes, value, out_value) : 0;
+  const bool fused_value = value && unit == row_bytes;  // one 1/2/4/8/16-byte unit per entry
+#define PS_T(U, WR, WV)                                                                                     \
+  transpose_gather_kernel<U, WR, WV><<<blocks, 256, 0, s>>>(csr2csc, row, col, (const U *)value, nnz, out_row, \
+                                                           out_col, (U *)out_value)
+#define PS_TV(U)                     \
+  do {                               \
+    if (with_row) PS_T(U, true, true); \
+    else PS_T(U, false, true);       \
+  } while (0)
+  if (fused_value) {
+    switch (unit) {
+      case 16: PS_TV(uint4); break;
+      case 8: PS_TV(uint64_t); break;
+      case 4: PS_TV(uint32_t); break;
+      case 2: PS_TV(uint16_t); break;
+      default: PS_TV(uint8_t); break;
+    }
+  } else {
+    if (with_row) PS_T(uint32_t, true, false);
+    else PS_T(uint32_t, false, false);
+  }
+#undef PS_TV
+#undef PS_T
+  PS_LAUNCH_OK();
+  if (value && !fused_value) PS_TRY(gather_rows_launch<int64_t>(value, row_bytes, csr2csc, nnz, out_value, s));
+  return PS_OK;
+}
+
+}  // extern "C"
