@@ -161,14 +161,15 @@ int ps_index_select_fill(const int64_t *old_ptr, const int64_t *minor, const voi
  * out_n_id[S+bound]; host_sizes[0] = E, host_sizes[1] = |n_id|.  Synchronises. */
 int ps_sample_adj_bound(const int64_t *rowptr, const int64_t *idx, int64_t S, int64_t num_neighbors,
                         int replace, int64_t *host_bound, void *stream);
-int ps_sample_adj(const int64_t *rowptr, const int64_t *col, int64_t M, const int64_t *idx, int64_t S,
-                  int64_t num_neighbors, int replace, uint64_t seed, int64_t bound,
+int ps_sample_adj(const int64_t *rowptr, const int64_t *col, int64_t M, int64_t nnz, const int64_t *idx,
+                  int64_t S, int64_t num_neighbors, int replace, uint64_t seed, int64_t bound,
                   int64_t *out_rowptr, int64_t *out_col, int64_t *out_n_id, int64_t *out_e_id,
                   int64_t *host_sizes, void *stream);
 
 /* ------------------------------------------------------------------ row-range partitioning (multi-GPU) */
 /* SURVEY.md 8e (the reference has no distributed code).  Coarse row histogram used to
- * choose nnz-balanced, row-aligned splitters: out_hist[b] += #{e : row[e] >> shift == b}. */
+ * choose nnz-balanced, row-aligned splitters: out_hist[b] = #{e : row[e] >> shift == b}
+ * (row must be 16-byte aligned). */
 int ps_dist_row_histogram(const int64_t *row, int64_t nnz, int shift, int64_t buckets,
                           int64_t *out_hist, void *stream);
 /* Stable partition of the local tuples by destination rank (row in

@@ -1,0 +1,126 @@
+// Row-range partitioning for matrices that span several GPUs.  The reference
+// has no distributed code at all; this is the device half of the sample sort named by the
+// north star: coarse row histogram -> (host/NCCL: all-reduce, splitters) -> stable partition
+// of the local tuples by destination rank -> (NCCL all-to-all) -> local ps_coalesce.
+#include "common.cuh"
+#include "radix_sort.cuh"
+#include "segment.cuh"
+
+namespace ps {
+
+constexpr int DH_SMEM_BUCKETS = 32768;  // 128 KB of 32-bit counters per CTA
+
+// out[b] += #{e : row[e] >> shift == b}; counters privatised in shared memory
+__global__ void __launch_bounds__(512)
+row_hist_smem_kernel(const int64_t *__restrict__ row, int64_t nnz, int shift, int buckets,
+                     unsigned long long *__restrict__ out) {
+  extern __shared__ unsigned int sh_hist[];
+  for (int j = threadIdx.x; j < buckets; j += blockDim.x) sh_hist[j] = 0;
+  __syncthreads();
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x * 2;
+  for (int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 2; i < nnz; i += stride) {
+    if (i + 1 < nnz) {
+      const longlong2 v = ld_stream2(row + i);  // row is 16-B aligned (cudaMalloc / tensor base), i even
+      atomicAdd(&sh_hist[(unsigned)(v.x >> shift)], 1u);
+      atomicAdd(&sh_hist[(unsigned)(v.y >> shift)], 1u);
+    } else {
+      atomicAdd(&sh_hist[(unsigned)(ld_stream(row + i) >> shift)], 1u);
+    }
+  }
+  __syncthreads();
+  for (int j = threadIdx.x; j < buckets; j += blockDim.x)
+    if (sh_hist[j]) atomicAdd(&out[j], (unsigned long long)sh_hist[j]);
+}
+
+__global__ void __launch_bounds__(256)
+row_hist_global_kernel(const int64_t *__restrict__ row, int64_t nnz, int shift, unsigned long long *__restrict__ out) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nnz; i += stride)
+    atomicAdd(&out[ld_stream(row + i) >> shift], 1ull);
+}
+
+// dest[e] = g with splitters[g] <= row[e] < splitters[g+1]; counts[g] += 1
+__global__ void __launch_bounds__(256)
+dest_kernel(const int64_t *__restrict__ row, int64_t nnz, const int64_t *__restrict__ splitters, int G,
+            uint32_t *__restrict__ dest, unsigned long long *__restrict__ counts) {
+  __shared__ int64_t sp[65];
+  __shared__ unsigned int sc[64];
+  if (threadIdx.x <= G) sp[threadIdx.x] = splitters[threadIdx.x];
+  if (threadIdx.x < 64) sc[threadIdx.x] = 0;
+  __syncthreads();
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nnz; i += stride) {
+    const int64_t r = ld_stream(row + i);
+    int lo = 0, hi = G - 1;  // largest g with sp[g] <= r
+    while (lo < hi) {
+      const int mid = (lo + hi + 1) >> 1;
+      if (sp[mid] <= r) lo = mid;
+      else hi = mid - 1;
+    }
+    dest[i] = (uint32_t)lo;
+    atomicAdd(&sc[lo], 1u);
+  }
+  __syncthreads();
+  if (threadIdx.x < G && sc[threadIdx.x]) atomicAdd(&counts[threadIdx.x], (unsigned long long)sc[threadIdx.x]);
+}
+
+}  // namespace ps
+
+using namespace ps;
+
+extern "C" {
+
+int ps_dist_row_histogram(const int64_t *row, int64_t nnz, int shift, int64_t buckets, int64_t *out_hist,
+                          void *stream) {
+  PS_CHECK(nnz >= 0 && buckets > 0 && shift >= 0 && shift < 63, "dist_row_histogram: bad arguments");
+  PS_CHECK((reinterpret_cast<uintptr_t>(row) & 15) == 0 || nnz == 0, "dist_row_histogram: row must be 16-byte aligned");
+  cudaStream_t s = (cudaStream_t)stream;
+  PS_CUDA(cudaMemsetAsync(out_hist, 0, sizeof(int64_t) * (size_t)buckets, s));
+  if (nnz == 0) return PS_OK;
+  unsigned long long *out = reinterpret_cast<unsigned long long *>(out_hist);
+  if (buckets <= DH_SMEM_BUCKETS) {
+    const size_t smem = sizeof(unsigned int) * (size_t)buckets;
+    PS_CUDA(cudaFuncSetAttribute(row_hist_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)(sizeof(unsigned int) * DH_SMEM_BUCKETS)));
+    int64_t blocks = ceil_div(nnz, 512 * 2 * 8);
+    const int64_t cap = (smem > 100 * 1024 ? 1 : 2) * (int64_t)sm_count();
+    if (blocks > cap) blocks = cap;
+    row_hist_smem_kernel<<<(unsigned)blocks, 512, smem, s>>>(row, nnz, shift, (int)buckets, out);
+  } else {
+    int64_t blocks = ceil_div(nnz, 256 * 8);
+    const int64_t cap = 8 * (int64_t)sm_count();
+    if (blocks > cap) blocks = cap;
+    row_hist_global_kernel<<<(unsigned)blocks, 256, 0, s>>>(row, nnz, shift, out);
+  }
+  PS_LAUNCH_OK();
+  return PS_OK;
+}
+
+int ps_dist_partition(const int64_t *row, const int64_t *col, const void *value, int64_t row_bytes, int64_t nnz,
+                      const int64_t *splitters, int G, int64_t *out_row, int64_t *out_col, void *out_value,
+                      int64_t *out_counts, void *stream) {
+  PS_CHECK(nnz >= 0 && G >= 1 && G <= 64 && row_bytes >= 0, "dist_partition: bad arguments (G must be in [1, 64])");
+  PS_CHECK(nnz < (int64_t(1) << 32), "dist_partition: nnz=%lld exceeds 2^32-1 entries per call", (long long)nnz);
+  cudaStream_t s = (cudaStream_t)stream;
+  PS_CUDA(cudaMemsetAsync(out_counts, 0, sizeof(int64_t) * (size_t)G, s));
+  if (nnz == 0) return PS_OK;
+  Scratch scratch(s);
+  PS_SCRATCH(dest, scratch, uint32_t, nnz);
+  PS_SCRATCH(perm, scratch, uint32_t, nnz);
+  int64_t blocks = ceil_div(nnz, 256 * 8);
+  const int64_t cap = 8 * (int64_t)sm_count();
+  if (blocks > cap) blocks = cap;
+  dest_kernel<<<(unsigned)blocks, 256, 0, s>>>(row, nnz, splitters, G, dest,
+                                              reinterpret_cast<unsigned long long *>(out_counts));
+  PS_LAUNCH_OK();
+  // one stable counting pass on the destination id; the payload is the entry index
+  PS_TRY(radix_sort_pairs<uint32_t>(KeySrc{dest, nullptr, KSRC_KEYS, 0}, PaySrc{nullptr, PSRC_IOTA}, nnz,
+                                    G > 1 ? bits_for(G) : 1, nullptr, nullptr, nullptr, nullptr,
+                                    KeyDst{nullptr, nullptr, KDST_NONE, 0}, PayDst{perm, PDST_U32}, scratch, s));
+  PS_TRY(gather_rows_launch<uint32_t>(row, 8, perm, nnz, out_row, s));
+  PS_TRY(gather_rows_launch<uint32_t>(col, 8, perm, nnz, out_col, s));
+  if (value && row_bytes > 0) PS_TRY(gather_rows_launch<uint32_t>(value, row_bytes, perm, nnz, out_value, s));
+  return PS_OK;
+}
+
+}  // extern "C"
