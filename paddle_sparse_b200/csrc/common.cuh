@@ -156,13 +156,20 @@ struct Red {
   }
   __device__ static float mean_(float a, int64_t c) { return a / (float)c; }
   __device__ static double mean_(double a, int64_t c) { return a / (double)c; }
-  // integer mean: floor division (paddle_scatter / torch_scatter: div_(count, rounding_mode='floor'))
-  __device__ static int32_t mean_(int32_t a, int64_t c) {
-    int64_t q = a / c, r = a % c;
-    return (int32_t)((r != 0 && ((r < 0) != (c < 0))) ? q - 1 : q);
+  // integer mean: segment_csr divides in C++ (truncation, torch_scatter segment_csr_cpu.cpp: val / count)
+  __device__ static int32_t mean_(int32_t a, int64_t c) { return (int32_t)((int64_t)a / c); }
+  __device__ static int64_t mean_(int64_t a, int64_t c) { return a / c; }
+  // scatter(reduce="mean") divides with rounding_mode="floor" (torch_scatter scatter.py: scatter_mean)
+  __device__ static A finish_floor(A a, int64_t count) {
+    if (count == 0) return A(0);
+    if (RED == PS_MEAN) return floor_mean_(a, count);
+    return a;
   }
-  __device__ static int64_t mean_(int64_t a, int64_t c) {
-    int64_t q = a / c, r = a % c;
+  __device__ static float floor_mean_(float a, int64_t c) { return a / (float)c; }
+  __device__ static double floor_mean_(double a, int64_t c) { return a / (double)c; }
+  __device__ static int32_t floor_mean_(int32_t a, int64_t c) { return (int32_t)floor_mean_((int64_t)a, c); }
+  __device__ static int64_t floor_mean_(int64_t a, int64_t c) {
+    const int64_t q = a / c, r = a % c;
     return (r != 0 && ((r < 0) != (c < 0))) ? q - 1 : q;
   }
 };

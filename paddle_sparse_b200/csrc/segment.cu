@@ -221,7 +221,7 @@ scatter_finish_kernel(const typename Acc<T>::type *__restrict__ acc, const int *
   const int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (q >= n_units) return;
   const int64_t c = RED == PS_SUM ? 1 : (int64_t)cnt[q / width];
-  out[q] = from_acc<T>(Red<RED, A>::finish(acc[q], c));
+  out[q] = from_acc<T>(Red<RED, A>::finish_floor(acc[q], c));
 }
 
 template <typename T, int RED>

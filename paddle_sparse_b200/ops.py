@@ -1,0 +1,449 @@
+"""Operator layer: the callables the reference gets from ``paddle_sparse_ops`` (csrc/convert.cpp,
+csrc/sample.cpp, csrc/version.cpp), from ``paddle_scatter`` (segment_csr / gather_csr / scatter /
+scatter_add) and from ``index_sort`` (paddle_sparse/utils.py:14-23), plus the fused entry points
+SparseStorage uses instead of the reference's chains of stock tensor ops.
+
+Every function takes device tensors, allocates its outputs on the same device, launches on the
+current stream and calls straight into libpaddle_sparse_b200.so through ctypes with raw pointers
+(include/ps_abi.h).  torch is used only as the array library: allocation, ``data_ptr()`` and the
+current stream (the production adapter hands Paddle tensors over by DLPack).
+GPU only: a CPU tensor raises, exactly opposite to csrc/sample.cpp:13-15 which throws on GPU ones.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Optional, Tuple
+
+import torch
+
+from . import _lib
+
+PS_F32, PS_BF16, PS_F16, PS_F64, PS_I32, PS_I64, PS_U8 = range(7)
+_DTYPES = {
+    torch.float32: PS_F32, torch.bfloat16: PS_BF16, torch.float16: PS_F16, torch.float64: PS_F64,
+    torch.int32: PS_I32, torch.int64: PS_I64,
+}
+_REDUCE = {"sum": 0, "add": 0, "mean": 1, "min": 2, "max": 3}  # testing.py:10; "add" == "sum"
+
+
+def reduce_code(reduce: str) -> int:
+    try:
+        return _REDUCE[reduce]
+    except KeyError:
+        raise ValueError(f"unknown reduce '{reduce}'") from None
+
+
+def dtype_code(t: torch.Tensor) -> int:
+    try:
+        return _DTYPES[t.dtype]
+    except KeyError:
+        raise TypeError(f"value dtype {t.dtype} is not supported by paddle_sparse_b200") from None
+
+
+def _dev(t: torch.Tensor, name: str = "tensor") -> torch.Tensor:
+    if not isinstance(t, torch.Tensor) or not t.is_cuda:
+        raise RuntimeError(f"paddle_sparse_b200 is GPU-only (no CPU fallback): `{name}` is not a CUDA tensor")
+    return t.contiguous()
+
+
+def _idx(t: torch.Tensor, name: str = "index") -> torch.Tensor:
+    t = _dev(t, name)
+    if t.dtype != torch.int64:
+        raise TypeError(f"`{name}` must be int64, got {t.dtype}")
+    return t
+
+
+def _p(t: Optional[torch.Tensor]):
+    return None if t is None else ctypes.c_void_p(t.data_ptr())
+
+
+def _stream(t: torch.Tensor):
+    return ctypes.c_void_p(torch.cuda.current_stream(t.device).cuda_stream)
+
+
+def _width(value: torch.Tensor) -> int:
+    n = value.shape[0]
+    return (value.numel() // n) if n > 0 else int(torch.Size(value.shape[1:]).numel())
+
+
+def _row_bytes(value: torch.Tensor) -> int:
+    return _width(value) * value.element_size()
+
+
+def _new(ref: torch.Tensor, n, dtype=torch.int64) -> torch.Tensor:
+    return torch.empty(n, dtype=dtype, device=ref.device)
+
+
+def _host_i64(n: int = 1):
+    return (ctypes.c_int64 * n)()
+
+
+# ------------------------------------------------------------------ paddle_sparse_ops (csrc/)
+def sparse_cuda_version() -> torch.Tensor:
+    """csrc/version.cpp:8-33: [1] int64 CPU tensor with the CUDA_VERSION of the build."""
+    return torch.tensor([int(_lib.lib().ps_cuda_version())], dtype=torch.int64)
+
+
+def ind2ptr(ind: torch.Tensor, M: int) -> torch.Tensor:
+    """csrc/convert.cpp:13-23."""
+    ind = _idx(ind, "ind")
+    out = _new(ind, M + 1)
+    with torch.cuda.device(ind.device):
+        _lib.call("ps_ind2ptr", _p(ind), ind.numel(), M, _p(out), _stream(ind))
+    return out
+
+
+def ptr2ind(ptr: torch.Tensor, E: int) -> torch.Tensor:
+    """csrc/convert.cpp:46-56."""
+    ptr = _idx(ptr, "ptr")
+    out = _new(ptr, E)
+    with torch.cuda.device(ptr.device):
+        _lib.call("ps_ptr2ind", _p(ptr), ptr.numel() - 1, E, _p(out), _stream(ptr))
+    return out
+
+
+def sample_adj(rowptr, col, idx, num_neighbors: int, replace: bool, seed: int = 0):
+    """csrc/sample.cpp:8-24 (the reference throws on GPU tensors; this is the GPU path).
+    Returns [out_rowptr, out_col, n_id, e_id]."""
+    rowptr, col, idx = _idx(rowptr, "rowptr"), _idx(col, "col"), _idx(idx, "idx")
+    if idx.dim() != 1:
+        raise RuntimeError("sample_adj: idx must be 1-D")  # CHECK_INPUT, sample_cpu.cpp:19
+    S = idx.numel()
+    st = _stream(rowptr)
+    with torch.cuda.device(rowptr.device):
+        hb = _host_i64()
+        _lib.call("ps_sample_adj_bound", _p(rowptr), _p(idx), S, int(num_neighbors), int(bool(replace)), hb, st)
+        bound = int(hb[0])
+        out_rowptr = _new(rowptr, S + 1)
+        out_col = _new(rowptr, bound)
+        out_e_id = _new(rowptr, bound)
+        out_n_id = _new(rowptr, S + bound)
+        sizes = _host_i64(2)
+        _lib.call("ps_sample_adj", _p(rowptr), _p(col), rowptr.numel() - 1, col.numel(), _p(idx), S,
+                  int(num_neighbors), int(bool(replace)), ctypes.c_uint64(seed & (2**64 - 1)), bound,
+                  _p(out_rowptr), _p(out_col), _p(out_n_id), _p(out_e_id), sizes, st)
+    E, Nn = int(sizes[0]), int(sizes[1])
+    return [out_rowptr, out_col[:E], out_n_id[:Nn], out_e_id[:E]]
+
+
+# ------------------------------------------------------------------ pointers and counts
+def ptr2count(ptr: torch.Tensor) -> torch.Tensor:
+    """storage.py:373-381 / 405-412."""
+    ptr = _idx(ptr, "ptr")
+    M = ptr.numel() - 1
+    out = _new(ptr, M)
+    with torch.cuda.device(ptr.device):
+        _lib.call("ps_ptr2count", _p(ptr), M, _p(out), _stream(ptr))
+    return out
+
+
+def count2ptr(count: torch.Tensor, idx: Optional[torch.Tensor] = None, want_total: bool = False):
+    """[0, cumsum(count[idx])] (storage.py:395-398, index_select.py:21-23)."""
+    count = _idx(count, "count")
+    idx = None if idx is None else _idx(idx, "idx")
+    n = count.numel() if idx is None else idx.numel()
+    out = _new(count, n + 1)
+    tot = _host_i64() if want_total else None
+    with torch.cuda.device(count.device):
+        _lib.call("ps_count2ptr", _p(count), _p(idx), n, _p(out), tot, _stream(count))
+    return (out, int(tot[0])) if want_total else out
+
+
+def scatter_add_ones(index: torch.Tensor, dim_size: int) -> torch.Tensor:
+    """storage.py:413-418: scatter_add(ones_like(col), col, dim_size=N) == histogram."""
+    index = _idx(index)
+    out = _new(index, dim_size)
+    with torch.cuda.device(index.device):
+        _lib.call("ps_histogram", _p(index), index.numel(), dim_size, _p(out), _stream(index))
+    return out
+
+
+def index_max(a: torch.Tensor, b: Optional[torch.Tensor] = None) -> Tuple[int, int]:
+    """storage.py:65-89: (int(a.max()), int(b.max())) in one launch and one sync; -1 when empty."""
+    a = _idx(a, "a")
+    b = None if b is None else _idx(b, "b")
+    h = _host_i64(2)
+    with torch.cuda.device(a.device):
+        _lib.call("ps_index_max", _p(a), a.numel(), _p(b), 0 if b is None else b.numel(), h, _stream(a))
+    return int(h[0]), int(h[1])
+
+
+def coo_order(row: torch.Tensor, col: torch.Tensor) -> Tuple[bool, bool]:
+    """(is_sorted, is_coalesced) of the (row, col) sequence (storage.py:158-163, 449-452)."""
+    row, col = _idx(row, "row"), _idx(col, "col")
+    h = (ctypes.c_int32 * 2)()
+    with torch.cuda.device(row.device):
+        _lib.call("ps_coo_order", _p(row), _p(col), row.numel(), h, _stream(row))
+    return bool(h[0]), bool(h[1])
+
+
+# ------------------------------------------------------------------ construct / coalesce
+def _value_args(value: Optional[torch.Tensor]):
+    if value is None:
+        return None, 0, 1
+    return value, dtype_code(value), max(_width(value), 1)
+
+
+def sort_coo(row, col, value, M: int, N: int, want_perm: bool = False):
+    """Sort-on-construct (storage.py:158-171): stable sort by row*N + col.
+    Returns (row, col, value, perm|None)."""
+    row, col = _idx(row, "row"), _idx(col, "col")
+    value = None if value is None else _dev(value, "value")
+    v, dt, w = _value_args(value)
+    nnz = row.numel()
+    out_row, out_col = _new(row, nnz), _new(row, nnz)
+    out_value = None if value is None else torch.empty_like(value)
+    out_perm = _new(row, nnz) if want_perm else None
+    with torch.cuda.device(row.device):
+        _lib.call("ps_sort_coo", _p(row), _p(col), nnz, M, N, _p(v), dt, w, _p(out_row), _p(out_col),
+                  _p(out_value), _p(out_perm), _stream(row))
+    return out_row, out_col, out_value, out_perm
+
+
+def coalesce(row, col, value, M: int, N: int, reduce: str = "add"):
+    """coalesce.py:8-29 fused: packed-key radix sort + run detection + segmented reduce.
+    Returns (row', col', value')."""
+    row, col = _idx(row, "row"), _idx(col, "col")
+    value = None if value is None else _dev(value, "value")
+    v, dt, w = _value_args(value)
+    nnz = row.numel()
+    out_row, out_col = _new(row, nnz), _new(row, nnz)
+    out_value = None if value is None else torch.empty_like(value)
+    h = _host_i64()
+    with torch.cuda.device(row.device):
+        _lib.call("ps_coalesce", _p(row), _p(col), nnz, M, N, _p(v), dt, w, reduce_code(reduce), _p(out_row),
+                  _p(out_col), _p(out_value), h, _stream(row))
+    k = int(h[0])
+    return out_row[:k], out_col[:k], (None if out_value is None else out_value[:k])
+
+
+def coalesce_sorted(row, col, value, reduce: str = "add"):
+    """SparseStorage.coalesce on sorted input (storage.py:454-486).  Returns (row', col', value')."""
+    row, col = _idx(row, "row"), _idx(col, "col")
+    value = None if value is None else _dev(value, "value")
+    v, dt, w = _value_args(value)
+    nnz = row.numel()
+    out_row, out_col = _new(row, nnz), _new(row, nnz)
+    out_value = None if value is None else torch.empty_like(value)
+    h = _host_i64()
+    with torch.cuda.device(row.device):
+        _lib.call("ps_coalesce_sorted", _p(row), _p(col), nnz, _p(v), dt, w, reduce_code(reduce), _p(out_row),
+                  _p(out_col), _p(out_value), h, _stream(row))
+    k = int(h[0])
+    return out_row[:k], out_col[:k], (None if out_value is None else out_value[:k])
+
+
+# ------------------------------------------------------------------ CSC structures
+def csr2csc(col: torch.Tensor, N: int, want_colptr: bool = True, want_colcount: bool = False):
+    """storage.py:425-434 (+ colptr :386-400, colcount :405-420 as by-products).
+    Returns (csr2csc, colptr|None, colcount|None)."""
+    col = _idx(col, "col")
+    nnz = col.numel()
+    perm = _new(col, nnz)
+    colptr = _new(col, N + 1) if want_colptr else None
+    colcount = _new(col, N) if want_colcount else None
+    with torch.cuda.device(col.device):
+        _lib.call("ps_csr2csc", _p(col), nnz, N, _p(perm), _p(colptr), _p(colcount), _stream(col))
+    return perm, colptr, colcount
+
+
+def invert_perm(perm: torch.Tensor) -> torch.Tensor:
+    """storage.py:439-447: argsort of a permutation == its inverse."""
+    perm = _idx(perm, "perm")
+    out = _new(perm, perm.numel())
+    with torch.cuda.device(perm.device):
+        _lib.call("ps_invert_perm", _p(perm), perm.numel(), _p(out), _stream(perm))
+    return out
+
+
+def gather_rows(src: torch.Tensor, index: torch.Tensor) -> torch.Tensor:
+    """src[index] along dim 0 (storage.py:166-169, 238-241; transpose.py:15; index_select.py:104-108)."""
+    src, index = _dev(src, "src"), _idx(index, "index")
+    out = torch.empty((index.numel(),) + tuple(src.shape[1:]), dtype=src.dtype, device=src.device)
+    with torch.cuda.device(src.device):
+        _lib.call("ps_gather_rows", _p(src), _row_bytes(src) if src.shape[0] else src.element_size() * _width(src),
+                  _p(index), index.numel(), _p(out), _stream(src))
+    return out
+
+
+def transpose_gather(csr2csc_, row, col, value, colptr=None, N: int = 0):
+    """transpose.py:9-33: (col[csr2csc], row[csr2csc], value[csr2csc]) in one pass."""
+    perm, row, col = _idx(csr2csc_, "csr2csc"), _idx(row, "row"), _idx(col, "col")
+    value = None if value is None else _dev(value, "value")
+    nnz = row.numel()
+    out_row, out_col = _new(row, nnz), _new(row, nnz)
+    out_value = None if value is None else torch.empty_like(value)
+    colptr = None if colptr is None else _idx(colptr, "colptr")
+    with torch.cuda.device(row.device):
+        _lib.call("ps_transpose_gather", _p(perm), _p(row), _p(col), _p(value),
+                  0 if value is None else _row_bytes(value), nnz, _p(colptr), N, _p(out_row), _p(out_col),
+                  _p(out_value), _stream(row))
+    return out_row, out_col, out_value
+
+
+# ------------------------------------------------------------------ paddle_scatter replacements
+def segment_csr(src: torch.Tensor, indptr: torch.Tensor, out=None, reduce: str = "sum") -> torch.Tensor:
+    """paddle_scatter.segment_csr(src, indptr, None, reduce) along dim 0 (storage.py:471, reduce.py:51)."""
+    assert out is None, "segment_csr: `out` is not supported"
+    src, indptr = _dev(src, "src"), _idx(indptr, "indptr")
+    S = indptr.numel() - 1
+    res = torch.empty((S,) + tuple(src.shape[1:]), dtype=src.dtype, device=src.device)
+    with torch.cuda.device(src.device):
+        _lib.call("ps_segment_reduce", _p(src), dtype_code(src), max(_width(src), 1), src.shape[0], _p(indptr), S,
+                  reduce_code(reduce), _p(res), _stream(src))
+    return res
+
+
+def gather_csr(src: torch.Tensor, indptr: torch.Tensor, E: Optional[int] = None) -> torch.Tensor:
+    """paddle_scatter.gather_csr(src, indptr) (mul.py:16,79; index_select.py:29,65).  E = indptr[-1]
+    (pass it when known: it saves the device->host read)."""
+    src, indptr = _dev(src, "src"), _idx(indptr, "indptr")
+    S = indptr.numel() - 1
+    if E is None:
+        E = int(indptr[-1].item())
+    out = torch.empty((E,) + tuple(src.shape[1:]), dtype=src.dtype, device=src.device)
+    with torch.cuda.device(src.device):
+        _lib.call("ps_gather_csr", _p(src), src.element_size() * max(_width(src), 1), _p(indptr), S, E, _p(out),
+                  _stream(src))
+    return out
+
+
+def scatter(src: torch.Tensor, index: torch.Tensor, dim: int = 0, out=None, dim_size: Optional[int] = None,
+            reduce: str = "sum") -> torch.Tensor:
+    """paddle_scatter.scatter(src, index, 0, None, dim_size, reduce) (reduce.py:42)."""
+    assert dim == 0 and out is None and dim_size is not None
+    src, index = _dev(src, "src"), _idx(index, "index")
+    res = torch.empty((dim_size,) + tuple(src.shape[1:]), dtype=src.dtype, device=src.device)
+    with torch.cuda.device(src.device):
+        _lib.call("ps_scatter_reduce", _p(src), dtype_code(src), max(_width(src), 1), _p(index), index.numel(),
+                  dim_size, reduce_code(reduce), _p(res), _stream(src))
+    return res
+
+
+def reduce_all(src: torch.Tensor, reduce: str = "sum") -> torch.Tensor:
+    """reduce.py:17-27 dim=None: 0-d result of the dense reduction over every element."""
+    src = _dev(src, "src")
+    res = torch.empty(1, dtype=src.dtype, device=src.device)
+    with torch.cuda.device(src.device):
+        _lib.call("ps_reduce_all", _p(src), dtype_code(src), src.numel(), reduce_code(reduce), _p(res), _stream(src))
+    return res[0]
+
+
+# ------------------------------------------------------------------ broadcast multiply (mul.py:76-119)
+def mul_row(value, rowptr, other, out=None):
+    value, rowptr, other = _dev(value, "value"), _idx(rowptr, "rowptr"), _dev(other, "other")
+    out = torch.empty_like(value) if out is None else out
+    with torch.cuda.device(value.device):
+        _lib.call("ps_mul_row", _p(value), dtype_code(value), max(_width(value), 1), _p(rowptr), rowptr.numel() - 1,
+                  value.shape[0], _p(other), _p(out), _stream(value))
+    return out
+
+
+def mul_col(value, col, other, out=None):
+    value, col, other = _dev(value, "value"), _idx(col, "col"), _dev(other, "other")
+    out = torch.empty_like(value) if out is None else out
+    with torch.cuda.device(value.device):
+        _lib.call("ps_mul_col", _p(value), dtype_code(value), max(_width(value), 1), _p(col), value.shape[0],
+                  _p(other), _p(out), _stream(value))
+    return out
+
+
+def mul_nnz(value, other, out=None):
+    value, other = _dev(value, "value"), _dev(other, "other")
+    out = torch.empty_like(value) if out is None else out
+    with torch.cuda.device(value.device):
+        _lib.call("ps_mul_nnz", _p(value), dtype_code(value), value.numel(), _p(other), _p(out), _stream(value))
+    return out
+
+
+# ------------------------------------------------------------------ select building blocks
+def _mask_u8(mask: torch.Tensor) -> torch.Tensor:
+    mask = _dev(mask, "mask")
+    if mask.dtype == torch.bool:
+        return mask.view(torch.uint8)
+    if mask.dtype == torch.uint8:
+        return mask
+    raise TypeError(f"mask must be bool, got {mask.dtype}")
+
+
+def mask_to_index(mask: torch.Tensor) -> torch.Tensor:
+    """Ascending indices of the set entries (masked_select.py:18-24)."""
+    m = _mask_u8(mask)
+    out = _new(m, m.numel())
+    h = _host_i64()
+    with torch.cuda.device(m.device):
+        _lib.call("ps_mask_to_index", _p(m), m.numel(), _p(out), h, _stream(m))
+    return out[: int(h[0])]
+
+
+def mask_entries(mask: torch.Tensor, index: Optional[torch.Tensor], nnz: int) -> torch.Tensor:
+    """Entry ids e with mask[index[e]] (index None: mask[e]) (masked_select.py:28-30, 60-62, 93-114)."""
+    m = _mask_u8(mask)
+    index = None if index is None else _idx(index, "index")
+    out = _new(m, nnz)
+    h = _host_i64()
+    with torch.cuda.device(m.device):
+        _lib.call("ps_mask_entries", _p(m), _p(index), nnz, _p(out), h, _stream(m))
+    return out[: int(h[0])]
+
+
+def index_select_fill(old_ptr, minor, value, idx, out_ptr, E: int, want_perm: bool = False):
+    """index_select.py:17-33 / 53-67 in one launch.  Returns (major, minor', value', perm|None)."""
+    old_ptr, minor, idx, out_ptr = _idx(old_ptr), _idx(minor), _idx(idx), _idx(out_ptr)
+    value = None if value is None else _dev(value, "value")
+    K = idx.numel()
+    out_major, out_minor = _new(minor, E), _new(minor, E)
+    out_value = None if value is None else torch.empty((E,) + tuple(value.shape[1:]), dtype=value.dtype,
+                                                       device=value.device)
+    out_perm = _new(minor, E) if want_perm else None
+    with torch.cuda.device(minor.device):
+        _lib.call("ps_index_select_fill", _p(old_ptr), _p(minor), _p(value),
+                  0 if value is None else value.element_size() * max(_width(value), 1), _p(idx), K, _p(out_ptr), E,
+                  _p(out_major), _p(out_minor), _p(out_value), _p(out_perm), _stream(minor))
+    return out_major, out_minor, out_value, out_perm
+
+
+# ------------------------------------------------------------------ row-range partitioning
+def dist_row_histogram(row: torch.Tensor, shift: int, buckets: int) -> torch.Tensor:
+    row = _idx(row, "row")
+    out = _new(row, buckets)
+    with torch.cuda.device(row.device):
+        _lib.call("ps_dist_row_histogram", _p(row), row.numel(), shift, buckets, _p(out), _stream(row))
+    return out
+
+
+def dist_partition(row, col, value, splitters: torch.Tensor):
+    """Stable partition of the local tuples by destination rank.  Returns (row, col, value, counts[G])."""
+    row, col, splitters = _idx(row, "row"), _idx(col, "col"), _idx(splitters, "splitters")
+    value = None if value is None else _dev(value, "value")
+    G = splitters.numel() - 1
+    nnz = row.numel()
+    out_row, out_col = _new(row, nnz), _new(row, nnz)
+    out_value = None if value is None else torch.empty_like(value)
+    counts = _new(row, G)
+    with torch.cuda.device(row.device):
+        _lib.call("ps_dist_partition", _p(row), _p(col), _p(value),
+                  0 if value is None else value.element_size() * max(_width(value), 1), nnz, _p(splitters), G,
+                  _p(out_row), _p(out_col), _p(out_value), _p(counts), _stream(row))
+    return out_row, out_col, out_value, counts
+
+
+def add_scalar(x: torch.Tensor, delta: int) -> torch.Tensor:
+    x = _idx(x, "x")
+    out = torch.empty_like(x)
+    with torch.cuda.device(x.device):
+        _lib.call("ps_add_scalar", _p(x), x.numel(), int(delta), _p(out), _stream(x))
+    return out
+
+
+# ------------------------------------------------------------------ synthetic inputs (bench / tests)
+def synth_coo(seed: int, first: int, n: int, M: int, N: int, device, with_value: bool = True):
+    """SURVEY.md 8d counter-hash generator, on the device.  Returns (row, col, value|None)."""
+    device = torch.device(device)
+    row = torch.empty(n, dtype=torch.int64, device=device)
+    col = torch.empty(n, dtype=torch.int64, device=device)
+    value = torch.empty(n, dtype=torch.float32, device=device) if with_value else None
+    with torch.cuda.device(device):
+        _lib.call("ps_synth_coo", ctypes.c_uint64(seed & (2**64 - 1)), first, n, M, N, _p(row), _p(col), _p(value),
+                  _stream(row))
+    return row, col, value

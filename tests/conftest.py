@@ -19,3 +19,12 @@ def cuda():
     if not torch.cuda.is_available():
         pytest.skip("no CUDA device")
     return torch.device("cuda:0")
+
+
+@pytest.fixture(scope="session")
+def ops(cuda):
+    """The operator layer; importing it opens libpaddle_sparse_b200.so (no fallback)."""
+    from paddle_sparse_b200 import ops as _ops
+
+    _ops._lib.lib()
+    return _ops
