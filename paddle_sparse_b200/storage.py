@@ -1,0 +1,349 @@
+"""SparseStorage — same public surface as the reference's paddle_sparse/storage.py:31-762,
+rebuilt on the fused sm_100a kernels of libpaddle_sparse_b200.so.
+
+What differs underneath (never in the API):
+  * construction validates with ONE kernel + one sync (`ops.index_max`) instead of two
+    `int(x.max())` round trips (storage.py:65-89), and decides sortedness with one
+    boundary kernel (`ops.coo_order`) instead of a 4-pass key build (storage.py:158-163);
+  * sort-on-construct is one packed-key radix sort that carries the value as payload
+    (storage.py:165-169: argsort + three gathers);
+  * `coalesce` is one dedup + segmented-reduce kernel (storage.py:454-486: key rebuild,
+    two mask selects, nonzero, segment_csr);
+  * `csr2csc` is a stable radix sort on the column bits only and produces `colptr` /
+    `colcount` as by-products (storage.py:386-434: a second 64-bit argsort, a histogram, a
+    cumsum); `csc2csr` is one inverse-permutation scatter (storage.py:439-447: a third sort).
+Caches stay lazy and observable exactly as in the reference (`cached_keys`, test_storage.py:53-108).
+"""
+from __future__ import annotations
+
+import warnings
+from typing import List, Optional, Tuple
+
+import torch
+
+from . import ops
+
+layouts: List[str] = ["coo", "csr", "csc"]
+
+
+def get_layout(layout: Optional[str] = None) -> str:
+    """storage.py:20-28."""
+    if layout is None:
+        layout = "coo"
+        warnings.warn('`layout` argument unset, using default layout "coo". This may lead to unexpected behaviour.')
+    assert layout in ("coo", "csr", "csc")
+    return layout
+
+
+def _check_index(t: torch.Tensor, like: torch.Tensor, numel: Optional[int] = None) -> torch.Tensor:
+    assert t.dtype == torch.int64
+    assert t.device == like.device
+    assert t.dim() == 1
+    if numel is not None:
+        assert t.numel() == numel
+    return t.contiguous()
+
+
+class SparseStorage(object):
+    def __init__(self, row=None, rowptr=None, col=None, value=None, sparse_sizes=None, rowcount=None,
+                 colptr=None, colcount=None, csr2csc=None, csc2csr=None, is_sorted: bool = False,
+                 trust_data: bool = False):
+        assert row is not None or rowptr is not None
+        assert col is not None
+        assert col.dtype == torch.int64
+        assert col.dim() == 1
+        if not col.is_cuda:
+            raise RuntimeError("paddle_sparse_b200.SparseStorage is GPU-only (no CPU fallback): `col` is on the CPU")
+        col = col.contiguous()
+        nnz = col.numel()
+
+        # ---- sizes: one fused max kernel and one sync where the reference has two (storage.py:65-89)
+        need_m = rowptr is None and row is not None and row.numel() > 0 and (
+            sparse_sizes is None or sparse_sizes[0] is None or not trust_data)
+        need_n = nnz > 0 and (sparse_sizes is None or sparse_sizes[1] is None or not trust_data)
+        row_max = col_max = -1
+        if need_m or need_n:
+            if need_m and need_n:
+                row_max, col_max = ops.index_max(row, col)
+            elif need_m:
+                row_max, _ = ops.index_max(row)
+            else:
+                col_max, _ = ops.index_max(col)
+
+        M = 0
+        if sparse_sizes is None or sparse_sizes[0] is None:
+            if rowptr is not None:
+                M = rowptr.numel() - 1
+            elif need_m:
+                M = row_max + 1
+        else:
+            M = int(sparse_sizes[0])
+            if rowptr is not None:
+                assert rowptr.numel() - 1 == M
+            elif need_m:
+                assert row_max < M
+
+        N = 0
+        if sparse_sizes is None or sparse_sizes[1] is None:
+            if need_n:
+                N = col_max + 1
+        else:
+            N = int(sparse_sizes[1])
+            if need_n:
+                assert col_max < N
+
+        if row is not None:
+            row = _check_index(row, col, nnz)
+        if rowptr is not None:
+            rowptr = _check_index(rowptr, col, M + 1)
+        if value is not None:
+            assert value.device == col.device
+            assert value.shape[0] == nnz
+            value = value.contiguous()
+        if rowcount is not None:
+            rowcount = _check_index(rowcount, col, M)
+        if colptr is not None:
+            colptr = _check_index(colptr, col, N + 1)
+        if colcount is not None:
+            colcount = _check_index(colcount, col, N)
+        if csr2csc is not None:
+            csr2csc = _check_index(csr2csc, col, nnz)
+        if csc2csr is not None:
+            csc2csr = _check_index(csc2csr, col, nnz)
+
+        self._row = row
+        self._rowptr = rowptr
+        self._col = col
+        self._value = value
+        self._sparse_sizes = (M, N)
+        self._rowcount = rowcount
+        self._colptr = colptr
+        self._colcount = colcount
+        self._csr2csc = csr2csc
+        self._csc2csr = csc2csr
+
+        # ---- sort-on-construct (storage.py:158-171)
+        if not is_sorted and nnz > 0:
+            in_order, _ = ops.coo_order(self.row(), col)
+            if not in_order:
+                self._row, self._col, self._value, _ = ops.sort_coo(self.row(), col, value, M, N)
+                self._csr2csc = None
+                self._csc2csr = None
+
+    @classmethod
+    def empty(cls, device="cuda"):
+        e = torch.empty(0, dtype=torch.int64, device=device)
+        return cls(row=e, col=e.clone(), sparse_sizes=(0, 0), is_sorted=True, trust_data=True)
+
+    # ------------------------------------------------------------------ row / rowptr / col / value
+    def has_row(self) -> bool:
+        return self._row is not None
+
+    def row(self) -> torch.Tensor:
+        if self._row is None:
+            if self._rowptr is None:
+                raise ValueError
+            self._row = ops.ptr2ind(self._rowptr, self._col.numel())  # storage.py:202
+        return self._row
+
+    def has_rowptr(self) -> bool:
+        return self._rowptr is not None
+
+    def rowptr(self) -> torch.Tensor:
+        if self._rowptr is None:
+            if self._row is None:
+                raise ValueError
+            self._rowptr = ops.ind2ptr(self._row, self._sparse_sizes[0])  # storage.py:218
+        return self._rowptr
+
+    def col(self) -> torch.Tensor:
+        return self._col
+
+    def has_value(self) -> bool:
+        return self._value is not None
+
+    def value(self) -> Optional[torch.Tensor]:
+        return self._value
+
+    def _prepare_value(self, value, layout):
+        if value is not None:
+            if get_layout(layout) == "csc":
+                value = ops.gather_rows(value.contiguous(), self.csc2csr())  # storage.py:238-241
+            value = value.contiguous()
+            assert value.device == self._col.device
+            assert value.shape[0] == self._col.numel()
+        return value
+
+    def set_value_(self, value, layout: Optional[str] = None):
+        self._value = self._prepare_value(value, layout)
+        return self
+
+    def set_value(self, value, layout: Optional[str] = None):
+        return self._rewrap(value=self._prepare_value(value, layout))
+
+    def _rewrap(self, **changes):
+        kw = dict(row=self._row, rowptr=self._rowptr, col=self._col, value=self._value,
+                  sparse_sizes=self._sparse_sizes, rowcount=self._rowcount, colptr=self._colptr,
+                  colcount=self._colcount, csr2csc=self._csr2csc, csc2csr=self._csc2csr,
+                  is_sorted=True, trust_data=True)
+        kw.update(changes)
+        return SparseStorage(**kw)
+
+    def sparse_sizes(self) -> Tuple[int, int]:
+        return self._sparse_sizes
+
+    def sparse_size(self, dim: int) -> int:
+        return self._sparse_sizes[dim]
+
+    # ------------------------------------------------------------------ resize / reshape (storage.py:281-368)
+    def sparse_resize(self, sparse_sizes: Tuple[int, int]):
+        assert len(sparse_sizes) == 2
+        (old_m, old_n), nnz = self._sparse_sizes, self._col.numel()
+
+        def _grow_ptr(ptr, diff):
+            if ptr is None or diff == 0:
+                return ptr
+            if diff > 0:
+                return torch.cat([ptr, torch.full((diff,), nnz, dtype=ptr.dtype, device=ptr.device)])
+            return ptr[:diff]
+
+        def _grow_count(cnt, diff):
+            if cnt is None or diff == 0:
+                return cnt
+            if diff > 0:
+                return torch.cat([cnt, torch.zeros(diff, dtype=cnt.dtype, device=cnt.device)])
+            return cnt[:diff]
+
+        d0, d1 = sparse_sizes[0] - old_m, sparse_sizes[1] - old_n
+        return self._rewrap(sparse_sizes=tuple(sparse_sizes), rowptr=_grow_ptr(self._rowptr, d0),
+                            rowcount=_grow_count(self._rowcount, d0), colptr=_grow_ptr(self._colptr, d1),
+                            colcount=_grow_count(self._colcount, d1))
+
+    def sparse_reshape(self, num_rows: int, num_cols: int):
+        assert num_rows > 0 or num_rows == -1
+        assert num_cols > 0 or num_cols == -1
+        assert num_rows > 0 or num_cols > 0
+        total = self.sparse_size(0) * self.sparse_size(1)
+        if num_rows == -1:
+            num_rows = total // num_cols
+        if num_cols == -1:
+            num_cols = total // num_rows
+        assert num_rows * num_cols == total
+        idx = self.sparse_size(1) * self.row() + self._col
+        return SparseStorage(row=torch.div(idx, num_cols, rounding_mode="floor"), col=idx % num_cols,
+                             value=self._value, sparse_sizes=(num_rows, num_cols), is_sorted=True, trust_data=True)
+
+    # ------------------------------------------------------------------ lazy caches
+    def has_rowcount(self) -> bool:
+        return self._rowcount is not None
+
+    def rowcount(self) -> torch.Tensor:
+        if self._rowcount is None:
+            self._rowcount = ops.ptr2count(self.rowptr())  # storage.py:373-381
+        return self._rowcount
+
+    def has_colptr(self) -> bool:
+        return self._colptr is not None
+
+    def _build_csc(self) -> None:
+        """One stable radix sort on the column bits yields csr2csc and, as a by-product, colptr.
+        The by-product is parked in `_colptr_spare` (not a cache key) and promoted by colptr(),
+        so `cached_keys()` evolves exactly as in the reference."""
+        need_ptr = self._colptr is None
+        perm, colptr, _ = ops.csr2csc(self._col, self._sparse_sizes[1], need_ptr, False)
+        self._csr2csc = perm
+        if need_ptr:
+            self._colptr_spare = colptr
+
+    def colptr(self) -> torch.Tensor:
+        if self._colptr is None:
+            spare = getattr(self, "_colptr_spare", None)
+            if spare is not None:
+                self._colptr, self._colptr_spare = spare, None
+            elif self._csr2csc is not None:
+                # storage.py:392-393: ind2ptr(col[csr2csc], N)
+                self._colptr = ops.ind2ptr(ops.gather_rows(self._col, self._csr2csc), self._sparse_sizes[1])
+            else:
+                # storage.py:395-398: [0, cumsum(colcount)] — the histogram is scanned in one pass
+                self._colptr = ops.count2ptr(self.colcount())
+        return self._colptr
+
+    def has_colcount(self) -> bool:
+        return self._colcount is not None
+
+    def colcount(self) -> torch.Tensor:
+        if self._colcount is None:
+            if self._colptr is not None:
+                self._colcount = ops.ptr2count(self._colptr)  # storage.py:408-412
+            else:
+                self._colcount = ops.scatter_add_ones(self._col, self._sparse_sizes[1])  # storage.py:413-418
+        return self._colcount
+
+    def has_csr2csc(self) -> bool:
+        return self._csr2csc is not None
+
+    def csr2csc(self) -> torch.Tensor:
+        if self._csr2csc is None:
+            self._build_csc()  # storage.py:425-434 (+ colptr for free when it is not cached yet)
+        return self._csr2csc
+
+    def has_csc2csr(self) -> bool:
+        return self._csc2csr is not None
+
+    def csc2csr(self) -> torch.Tensor:
+        if self._csc2csr is None:
+            self._csc2csr = ops.invert_perm(self.csr2csc())  # storage.py:439-447
+        return self._csc2csr
+
+    def is_coalesced(self) -> bool:
+        """storage.py:449-452."""
+        if self._col.numel() <= 1:
+            return True
+        return ops.coo_order(self.row(), self._col)[1]
+
+    def coalesce(self, reduce: str = "add"):
+        """storage.py:454-486; returns `self` when nothing has to be merged (:459-460)."""
+        if self._col.numel() <= 1:
+            return self
+        row, col, value = ops.coalesce_sorted(self.row(), self._col, self._value, reduce)
+        if row.numel() == self._col.numel():
+            return self
+        return SparseStorage(row=row, col=col, value=value, sparse_sizes=self._sparse_sizes, is_sorted=True,
+                             trust_data=True)
+
+    def fill_cache_(self):
+        """storage.py:488-496 (same set of caches; csr2csc is built first so colptr comes with it)."""
+        self.row()
+        self.rowptr()
+        self.rowcount()
+        self.csr2csc()
+        self.colptr()
+        self.colcount()
+        self.csc2csr()
+        return self
+
+    def clear_cache_(self):
+        self._colptr_spare = None
+        self._rowcount = None
+        self._colptr = None
+        self._colcount = None
+        self._csr2csc = None
+        self._csc2csr = None
+        return self
+
+    def cached_keys(self) -> List[str]:
+        keys: List[str] = []
+        if self.has_rowcount():
+            keys.append("rowcount")
+        if self.has_colptr():
+            keys.append("colptr")
+        if self.has_colcount():
+            keys.append("colcount")
+        if self.has_csr2csc():
+            keys.append("csr2csc")
+        if self.has_csc2csr():
+            keys.append("csc2csr")
+        return keys
+
+    def num_cached_keys(self) -> int:
+        return len(self.cached_keys())

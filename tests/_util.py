@@ -32,7 +32,7 @@ def assert_values(got, want, dtype, exact=False):
 
 
 def _random_coo(rng, M, N, nnz, dup_frac=0.2):
-    base = int(nnz * (1 - dup_frac))
+    base = max(int(nnz * (1 - dup_frac)), 1)
     row = rng.integers(0, M, base)
     col = rng.integers(0, N, base)
     pick = rng.integers(0, max(base, 1), nnz - base)
