@@ -1,0 +1,345 @@
+"""GPU parity tests of the public API (SparseStorage / SparseTensor / free functions) against the
+NumPy restatement of the reference's Python layer (oracle/np_ref.py) and the reference's golden
+vectors.  These read like the reference's own test/test_storage.py, test_coalesce.py,
+test_transpose.py, test_permute.py and test_sample.py."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import np_ref
+from tests.golden import reference_vectors as G
+from tests._util import I64, _random_coo, dev, host
+
+pytestmark = pytest.mark.gpu
+DTYPES = [torch.float16, torch.float32, torch.float64, torch.int32, torch.int64, torch.bfloat16]  # testing.py:12-17
+
+
+@pytest.fixture(scope="module")
+def ps(ops):
+    import paddle_sparse_b200
+    return paddle_sparse_b200
+
+
+def ten(x, dtype=torch.int64):
+    return torch.tensor(x, dtype=dtype, device="cuda")
+
+
+def _pair(rng, M, N, nnz, dtype=np.float32, width=None, coalesced=True):
+    """The same matrix as an oracle SparseTensor and (constructor kwargs for) a GPU one."""
+    row, col = _random_coo(rng, M, N, nnz, 0.15)
+    if coalesced:
+        key = np.unique(row * N + col)
+        row, col = (key // N).astype(I64), (key % N).astype(I64)
+    shape = (row.size,) if width is None else (row.size, width)
+    val = rng.random(shape).astype(dtype)
+    return row, col, val
+
+
+def _same_storage(got, want, values_exact=True):
+    assert got.sparse_sizes() == tuple(want.sparse_sizes())
+    assert np.array_equal(host(got.storage.row()), want.storage.row())
+    assert np.array_equal(host(got.storage.col()), want.storage.col())
+    assert np.array_equal(host(got.storage.rowptr()), want.storage.rowptr())
+    if want.storage.value() is None:
+        assert got.storage.value() is None
+    elif values_exact:
+        assert np.array_equal(host(got.storage.value()), want.storage.value())
+    else:
+        np.testing.assert_allclose(host(got.storage.value()), want.storage.value(), rtol=1e-6)
+    for key in want.storage.cached_keys():  # every cache the reference carries over must agree
+        mine = getattr(got.storage, "_" + key)
+        if mine is not None:
+            assert np.array_equal(host(mine), getattr(want.storage, "_" + key)), key
+
+
+# ----------------------------------------------------------------------------- test_storage.py
+@pytest.mark.parametrize("dtype", DTYPES)
+def test_storage_sort_on_construct(ps, dtype):
+    g = G.SORT_ON_CONSTRUCT
+    st = ps.SparseStorage(row=ten(g["row"]), col=ten(g["col"]), value=ten(g["value"], dtype))
+    assert st.row().tolist() == g["out_row"] and st.col().tolist() == g["out_col"]
+    assert st.value().float().tolist() == g["out_value"]
+    assert st.sparse_sizes() == g["sizes"]
+
+
+def test_storage_caching(ps):
+    g = G.CACHING
+    st = ps.SparseStorage(row=ten(g["row"]), col=ten(g["col"]))
+    assert st._rowcount is None and st._rowptr is None and st._colcount is None and st._colptr is None
+    assert st._csr2csc is None and st.num_cached_keys() == 0
+    st.fill_cache_()
+    for k in ("rowcount", "rowptr", "colcount", "colptr", "csr2csc", "csc2csr"):
+        assert getattr(st, "_" + k).tolist() == g[k], k
+    assert st.num_cached_keys() == 5
+    st2 = ps.SparseStorage(row=st._row, rowptr=st._rowptr, col=st._col, value=st._value,
+                           sparse_sizes=st._sparse_sizes, rowcount=st._rowcount, colptr=st._colptr,
+                           colcount=st._colcount, csr2csc=st._csr2csc, csc2csr=st._csc2csr)
+    assert st2.num_cached_keys() == 5 and st2._csc2csr.tolist() == g["csc2csr"]
+    st2.clear_cache_()
+    assert st2._rowcount is None and st2._rowptr is not None and st2._colptr is None and st2.num_cached_keys() == 0
+    # lazy one at a time: cached_keys evolves as in the reference
+    st3 = ps.SparseStorage(row=ten(g["row"]), col=ten(g["col"]))
+    st3.csr2csc()
+    assert st3.cached_keys() == ["csr2csc"]
+    assert st3.colptr().tolist() == g["colptr"] and st3.cached_keys() == ["colptr", "csr2csc"]
+    st4 = ps.SparseStorage(row=ten(g["row"]), col=ten(g["col"]))
+    assert st4.colptr().tolist() == g["colptr"] and st4.cached_keys() == ["colptr", "colcount"]
+
+
+@pytest.mark.parametrize("dtype", DTYPES)
+def test_storage_set_value_and_copy(ps, dtype):
+    g = G.SET_VALUE
+    st = ps.SparseStorage(row=ten(g["row"]), col=ten(g["col"]), value=ten(g["value"], dtype))
+    st.set_value_(ten(g["value"], dtype), layout="csc")
+    assert st.value().float().tolist() == [float(v) for v in g["csc_layout"]]
+    st.set_value_(ten(g["value"], dtype), layout="coo")
+    assert st.value().float().tolist() == [float(v) for v in g["coo_layout"]]
+    out = st.set_value(ten(g["value"], dtype), layout="csc")
+    assert st.value().float().tolist() == [float(v) for v in g["coo_layout"]]
+    assert out.value().float().tolist() == [float(v) for v in g["csc_layout"]]
+    assert out.col().data_ptr() == st.col().data_ptr()
+    with pytest.warns(UserWarning):
+        st.set_value_(ten(g["value"], dtype))
+
+
+@pytest.mark.parametrize("dtype", DTYPES)
+def test_storage_coalesce(ps, dtype):
+    g = G.STORAGE_COALESCE
+    st = ps.SparseStorage(row=ten(g["row"]), col=ten(g["col"]), value=ten(g["value"], dtype))
+    assert st.row().tolist() == g["row"] and st.col().tolist() == g["col"]
+    assert not st.is_coalesced()
+    st2 = st.coalesce()
+    assert st2.is_coalesced() and st2.coalesce() is st2  # storage.py:459-460 returns self
+    assert st2.row().tolist() == g["out_row"] and st2.col().tolist() == g["out_col"]
+    assert st2.value().float().tolist() == [float(v) for v in g["out_value"]]
+    assert st2.num_cached_keys() == 0
+
+
+def test_storage_validation(ps):
+    with pytest.raises(AssertionError):
+        ps.SparseStorage(row=ten([0, 5]), col=ten([0, 1]), sparse_sizes=(3, 3))
+    with pytest.raises(AssertionError):
+        ps.SparseStorage(row=ten([0, 1]), col=ten([0, 9]), sparse_sizes=(3, 3))
+    with pytest.raises(RuntimeError):
+        ps.SparseStorage(row=torch.tensor([0]), col=torch.tensor([0]))  # CPU tensors: no fallback
+    st = ps.SparseStorage(rowptr=ten([0, 1, 1, 3]), col=ten([2, 0, 1]))
+    assert st.sparse_sizes() == (3, 3) and st.row().tolist() == [0, 2, 2]
+    e = ps.SparseStorage.empty()
+    assert e.sparse_sizes() == (0, 0) and e.rowptr().tolist() == [0]
+
+
+# ----------------------------------------------------------------------------- test_coalesce.py / test_transpose.py
+def test_free_coalesce_golden(ps):
+    g = G.COALESCE
+    index = ten([g["row"], g["col"]])
+    idx, val = ps.coalesce(index, None, m=g["m"], n=g["n"])
+    assert idx.tolist() == g["index"] and val is None
+    idx, val = ps.coalesce(index, ten(g["value"], torch.float32), m=g["m"], n=g["n"])
+    assert idx.tolist() == g["index"] and val.tolist() == g["add"]
+    idx, val = ps.coalesce(index, ten(g["value"], torch.float32), m=g["m"], n=g["n"], op="max")
+    assert idx.tolist() == g["index"] and val.tolist() == g["max"]
+
+
+@pytest.mark.parametrize("dtype", DTYPES)
+def test_transpose_golden(ps, dtype):
+    g = G.TRANSPOSE_MATRIX
+    mat = ps.SparseTensor(row=ten(g["row"]), col=ten(g["col"]), value=ten(g["value"], dtype),
+                          sparse_sizes=(g["m"], g["n"]))
+    mt = mat.t()
+    assert mt.sparse_sizes() == (g["n"], g["m"])
+    r, c, v = mt.coo()
+    assert [r.tolist(), c.tolist()] == g["index"] and v.float().tolist() == [float(x) for x in g["out_value"]]
+    g = G.TRANSPOSE
+    idx, val = ps.transpose(ten([g["row"], g["col"]]), ten(g["value"], dtype), m=g["m"], n=g["n"])
+    assert idx.tolist() == g["index"] and val.float().tolist() == [[float(x) for x in r] for r in g["out_value"]]
+
+
+def test_t_swaps_caches(ps):
+    rng = np.random.default_rng(0)
+    row, col, val = _pair(rng, 300, 200, 9000)
+    A = ps.SparseTensor(row=dev(row), col=dev(col), value=dev(val), sparse_sizes=(300, 200)).fill_cache_()
+    O = np_ref.SparseTensor(row=row, col=col, value=val, sparse_sizes=(300, 200))
+    O.fill_cache_()
+    At, Ot = A.t(), np_ref.t(O)
+    _same_storage(At, Ot)
+    assert sorted(At.storage.cached_keys()) == sorted(Ot.storage.cached_keys())
+    _same_storage(At.t(), O)
+    B = ps.SparseTensor(row=dev(row), col=dev(col), sparse_sizes=(300, 200))  # value-less, cold caches
+    _same_storage(B.t(), np_ref.t(np_ref.SparseTensor(row=row, col=col, sparse_sizes=(300, 200))))
+
+
+# ----------------------------------------------------------------------------- reduce.py / mul.py
+@pytest.mark.parametrize("reduce", ["sum", "mean", "min", "max"])
+@pytest.mark.parametrize("width", [None, 3])
+def test_reductions_all_dims(ps, reduce, width):
+    rng = np.random.default_rng(17)
+    M, N = 400, 250
+    row, col, val = _pair(rng, M, N, 12000, width=width)
+    A = ps.SparseTensor(row=dev(row), col=dev(col), value=dev(val), sparse_sizes=(M, N))
+    O = np_ref.SparseTensor(row=row, col=col, value=val.astype(np.float64), sparse_sizes=(M, N))
+    for dim in ([None, 0, 1, -1] if width is None else [None, 0, 1, 2, -1]):
+        got = getattr(A, reduce)(dim)
+        want = np_ref.reduction(O, dim, reduce)
+        np.testing.assert_allclose(host(got), want, rtol=0 if reduce in ("min", "max") else 2e-6)
+    # the test_reduce.py:13-62 identity
+    np.testing.assert_allclose(float(getattr(A, reduce)()), float(getattr(val.astype(np.float64), reduce)()), rtol=1e-6)
+    V = ps.SparseTensor(row=dev(row), col=dev(col), sparse_sizes=(M, N))  # value-less
+    OV = np_ref.SparseTensor(row=row, col=col, sparse_sizes=(M, N))
+    for dim in (None, 0, 1):
+        got, want = getattr(V, reduce)(dim), np_ref.reduction(OV, dim, reduce)
+        assert got.dtype == torch.float32 and np.array_equal(host(got), want)
+    with pytest.raises(ValueError):
+        ps.reduction(A, 0, "prod")
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16, torch.float64])
+def test_mul_broadcast(ps, dtype):
+    rng = np.random.default_rng(23)
+    M, N = 300, 500
+    row, col, val = _pair(rng, M, N, 20000)
+    tv = dev(val, dtype)
+    seen = tv.float().cpu().numpy().astype(np.float64) if dtype != torch.float64 else host(tv)
+    orow = dev(rng.random((M, 1)).astype(np.float32), dtype)
+    ocol = dev(rng.random((1, N)).astype(np.float32), dtype)
+    for other in (orow, ocol):
+        A = ps.SparseTensor(row=dev(row), col=dev(col), value=tv.clone(), sparse_sizes=(M, N))
+        O = np_ref.SparseTensor(row=row, col=col, value=seen.copy(), sparse_sizes=(M, N))
+        want = np_ref.mul(O, other.float().cpu().numpy().astype(np.float64)).storage.value()
+        rtol = {torch.float32: 1e-6, torch.bfloat16: 8e-3, torch.float64: 1e-12}[dtype]
+        out = A.mul(other)
+        np.testing.assert_allclose(host(out.storage.value()), want, rtol=rtol)
+        assert torch.equal(A.storage.value(), tv)  # out of place
+        assert torch.equal((A * other).storage.value(), out.storage.value())
+        B = A.mul_(other)
+        assert B is A and torch.equal(A.storage.value(), out.storage.value())
+    V = ps.SparseTensor(row=dev(row), col=dev(col), sparse_sizes=(M, N))  # test_overload.py: value-less
+    assert np.array_equal(host((V * orow).storage.value()), host(orow)[:, 0][row])
+    assert np.array_equal(host((V * ocol).storage.value()), host(ocol)[0][col])
+    with pytest.raises(ValueError):
+        V.mul(dev(np.ones((3, 3), np.float32)))
+    A = ps.SparseTensor(row=dev(row), col=dev(col), value=tv.clone(), sparse_sizes=(M, N))
+    w = dev(rng.random(row.size).astype(np.float32), dtype)
+    assert torch.equal(A.mul_nnz(w, layout="coo").storage.value(), tv * w)
+
+
+# ----------------------------------------------------------------------------- index_select / masked_select
+def test_permute_golden(ps):
+    g = G.PERMUTE
+    A = ps.SparseTensor(row=ten(g["row"]), col=ten(g["col"]), value=ten(g["value"], torch.float32))
+    perm = ten(g["perm"])
+    out = A.index_select(0, perm).index_select(1, perm)  # permute.py:8-13
+    r, c, v = out.coo()
+    assert r.tolist() == g["out_row"] and c.tolist() == g["out_col"] and v.tolist() == g["out_value"]
+
+
+@pytest.mark.parametrize("with_value", [True, False])
+@pytest.mark.parametrize("coalesced", [True, False])
+def test_index_and_masked_select(ps, with_value, coalesced):
+    rng = np.random.default_rng(31)
+    M, N = 350, 270
+    row, col, val = _pair(rng, M, N, 15000, coalesced=coalesced)
+    if not coalesced:
+        o = np.argsort(row * N + col, kind="stable")
+        row, col, val = row[o], col[o], val[o]
+    kw = dict(sparse_sizes=(M, N), is_sorted=True)
+    A = ps.SparseTensor(row=dev(row), col=dev(col), value=dev(val) if with_value else None, **kw)
+    O = np_ref.SparseTensor(row=row, col=col, value=val if with_value else None, **kw)
+    for dim, size in ((0, M), (1, N)):
+        idx = rng.integers(0, size, 500).astype(I64)  # duplicates allowed
+        got, want = A.index_select(dim, dev(idx)), np_ref.index_select(O, dim, idx)
+        _same_storage(got, want)
+        assert sorted(got.storage.cached_keys()) == sorted(want.storage.cached_keys())
+        mask = rng.random(size) < 0.4
+        got, want = A.masked_select(dim, dev(mask)), np_ref.masked_select(O, dim, mask)
+        _same_storage(got, want)
+        assert sorted(got.storage.cached_keys()) == sorted(want.storage.cached_keys())
+        assert A[dev(idx)].sparse_sizes()[0] == 500 if dim == 0 else True
+    eidx = np.sort(rng.choice(row.size, 700, replace=False)).astype(I64)
+    emask = rng.random(row.size) < 0.3
+    for layout in ("coo", "csc"):
+        _same_storage(A.index_select_nnz(dev(eidx), layout), np_ref.index_select_nnz(O, eidx, layout))
+        _same_storage(A.masked_select_nnz(dev(emask), layout), np_ref.masked_select_nnz(O, emask, layout))
+
+
+def test_getitem_and_to_dense(ps):
+    rng = np.random.default_rng(2)
+    mat = (rng.random((50, 40)) < 0.2) * rng.random((50, 40))
+    A = ps.SparseTensor.from_dense(dev(mat.astype(np.float32)))
+    assert np.array_equal(host(A.to_dense()), mat.astype(np.float32))
+    idx = dev(np.array([3, 1, 3, 7], I64))
+    assert np.array_equal(host(A[idx].to_dense()), mat.astype(np.float32)[[3, 1, 3, 7]])
+    assert np.array_equal(host(A[:, idx].to_dense()), mat.astype(np.float32)[:, [3, 1, 3, 7]])
+    m = dev(rng.random(50) < 0.5)
+    assert np.array_equal(host(A[m].to_dense()), mat.astype(np.float32)[host(m)])
+    assert A == A.clone() and not (A == A.t())
+    assert A.nnz() == int((mat != 0).sum()) and A.sizes() == [50, 40] and A.dtype() == torch.float32
+
+
+# ----------------------------------------------------------------------------- sample.py
+def test_sample_adj_api(ps):
+    g = G.SAMPLE_ADJ
+    A = ps.SparseTensor(row=ten(g["row"]), col=ten(g["col"]), value=torch.arange(14, device="cuda"),
+                        sparse_sizes=g["sizes"])
+    out, n_id = A.sample_adj(ten(g["subset"]), num_neighbors=-1)
+    assert n_id.tolist() == g["all_n_id"]
+    r, c, v = out.coo()
+    assert r.tolist() == g["all_row"] and c.tolist() == g["all_col"] and v.tolist() == g["all_val"]
+    out, n_id = A.sample_adj(ten(g["subset"]), num_neighbors=2, replace=True)
+    assert out.nnz() == g["nnz_replace_k2"]
+    out, n_id = A.sample_adj(ten(g["subset"]), num_neighbors=2, replace=False)
+    assert out.nnz() == g["nnz_noreplace_k2"]
+    s = A.sample(3)
+    assert s.shape == (6, 3) and int(s.min()) >= 0 and int(s.max()) < 6  # test_sample.py:8-14
+
+
+# ----------------------------------------------------------------------------- the headline pipeline
+def _pipeline(ps, row, col, val, M, N):
+    A = ps.SparseTensor(row=row, col=col, value=val, sparse_sizes=(M, N)).coalesce("add").fill_cache_()
+    return A, A.t()
+
+
+def test_pipeline_config1_full_compare(ps):
+    """BASELINE.json configs[0]: N=10k, nnz=100k (20 % duplicates) fp32: coalesce + rowptr/colptr + t() + sum(1)."""
+    rng = np.random.default_rng(1)
+    M = N = 10000
+    row, col = _random_coo(rng, M, N, 100000, 0.2)
+    val = rng.random(100000).astype(np.float32)
+    want = np_ref.build_pipeline(row, col, val, M, N)
+    A, At = _pipeline(ps, dev(row), dev(col), dev(val), M, N)
+    st = A.storage
+    for k, t_ in dict(row=st.row(), col=st.col(), rowptr=st.rowptr(), csr2csc=st.csr2csc(), colptr=st.colptr(),
+                      csc2csr=st.csc2csr(), t_row=At.storage.row(), t_col=At.storage.col()).items():
+        assert np.array_equal(host(t_), want[k]), k
+    np.testing.assert_allclose(host(st.value()), want["value"], rtol=1e-6)
+    np.testing.assert_allclose(host(At.storage.value()), want["t_value"], rtol=1e-6)
+    O = np_ref.SparseTensor(row=want["row"], col=want["col"], value=want["value"].astype(np.float64), sparse_sizes=(M, N))
+    np.testing.assert_allclose(host(A.sum(1)), np_ref.reduction(O, 1, "sum"), rtol=2e-6)
+
+
+def test_pipeline_config2_full_size_properties(ps, ops):
+    """BASELINE.json configs[1] at full size (2,449,029 nodes, 61,859,140 nnz): size-independent
+    properties — sortedness, strictness, checksum conservation, permutation validity, t(t(A)) == A."""
+    M = N = 2449029
+    nnz = 61859140
+    row, col, val = ops.synth_coo(0x5EED0002, 0, nnz, M, N, "cuda")
+    A, At = _pipeline(ps, row, col, val, M, N)
+    st = A.storage
+    assert ops.coo_order(st.row(), st.col()) == (True, True)
+    assert ops.coo_order(At.storage.row(), At.storage.col()) == (True, True)
+    nz = A.nnz()
+    assert 0 < nz <= nnz and int(st.rowptr()[-1]) == nz and int(st.colptr()[-1]) == nz
+    # duplicates only merge: total mass and key checksums are conserved
+    np.testing.assert_allclose(float(val.double().sum()), float(st.value().double().sum()), rtol=1e-9)
+    assert int(st.rowcount().sum()) == nz and int(st.colcount().sum()) == nz
+    iota = torch.arange(nz, device="cuda")
+    assert torch.equal(st.csr2csc()[st.csc2csr()], iota)
+    assert torch.equal(st.col()[st.csr2csc()], At.storage.row()) and torch.equal(st.row()[st.csr2csc()], At.storage.col())
+    assert torch.equal(st.value()[st.csr2csc()], At.storage.value())
+    assert torch.equal(ops.ptr2ind(st.rowptr(), nz), st.row())
+    Att = At.t()
+    assert torch.equal(Att.storage.row(), st.row()) and torch.equal(Att.storage.col(), st.col())
+    assert torch.equal(Att.storage.value(), st.value())
+    # distinct-key count agrees with an independent computation on the packed keys
+    keys = torch.unique(row * N + col)
+    assert keys.numel() == nz
+    assert torch.equal(keys, st.row() * N + st.col())
