@@ -1,0 +1,338 @@
+#!/usr/bin/env python
+"""bench.py — coalesce + CSR/CSC build throughput (nnz/s), the metric of BASELINE.json.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+One "step" = one pass of the hot path over one batch of synthetic COO input, through the public
+API:   SparseTensor(row, col, value, sparse_sizes)   (sort-on-construct)
+       .coalesce("add")  .fill_cache_()              (rowptr, rowcount, csr2csc, colptr, colcount, csc2csr)
+       .t()                                           (fused transpose gather)
+N = 1 : BASELINE.json configs[1] — ogbn-products shape, 2,449,029 nodes, 61,859,140 nnz, fp32.
+N > 1 : the row-range-partitioned build (configs[4] shape, papers100M: 111,059,956 nodes,
+        201,960,734 nnz per GPU = 1.6157 B nnz at N = 8), weak scaling, one NCCL all-to-all.
+Prints ONE JSON line (rank 0).  `--impl reference` times the reference's CPU path (NumPy
+restatement of its Python op chain + its own csrc/cpu compiled unmodified where available).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+PRODUCTS = dict(name="ogbn-products-shape", M=2449029, N=2449029, nnz=61859140, seed=0x5EED0002)
+PAPERS = dict(name="ogbn-papers100M-shape", M=111059956, N=111059956, nnz_per_gpu=201960734, seed=0x5EED0005)
+# SURVEY.md 8d figure A: compulsory bytes of the whole pipeline per input nnz at configs[1] (no duplicates)
+PIPELINE_BYTES_PER_NNZ = 128.6
+CPU_SAMPLE_NNZ = 8_000_000
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """Samples SM clocks and throttle reasons with NVML while the timed region runs."""
+
+    def __init__(self, index: int):
+        self.index, self.samples, self.reasons, self.max_mhz = index, [], set(), None
+        self._stop = threading.Event()
+        self._thr = None
+
+    def __enter__(self):
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self._nv = pynvml
+            self._h = pynvml.nvmlDeviceGetHandleByIndex(self.index)
+            self.max_mhz = int(pynvml.nvmlDeviceGetMaxClockInfo(self._h, pynvml.NVML_CLOCK_SM))
+            self._thr = threading.Thread(target=self._run, daemon=True)
+            self._thr.start()
+        except Exception:  # NVML missing: fall back to one nvidia-smi sample at exit
+            self._nv = None
+        return self
+
+    def _run(self):
+        nv = self._nv
+        names = {
+            nv.nvmlClocksThrottleReasonHwSlowdown: "hw_slowdown",
+            nv.nvmlClocksThrottleReasonHwThermalSlowdown: "hw_thermal_slowdown",
+            nv.nvmlClocksThrottleReasonSwThermalSlowdown: "sw_thermal_slowdown",
+            nv.nvmlClocksThrottleReasonSwPowerCap: "sw_power_cap",
+            nv.nvmlClocksThrottleReasonHwPowerBrakeSlowdown: "hw_power_brake",
+        }
+        while not self._stop.is_set():
+            try:
+                self.samples.append(int(nv.nvmlDeviceGetClockInfo(self._h, nv.NVML_CLOCK_SM)))
+                mask = int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(self._h))
+                for bit, name in names.items():
+                    if mask & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(0.01)
+
+    def __exit__(self, *exc):
+        self._stop.set()
+        if self._thr is not None:
+            self._thr.join()
+        if not self.samples:
+            try:
+                out = subprocess.check_output(
+                    ["nvidia-smi", f"--id={self.index}", "--query-gpu=clocks.sm,clocks.max.sm",
+                     "--format=csv,noheader,nounits"], text=True).strip().split(",")
+                self.samples, self.max_mhz = [int(out[0])], int(out[1])
+            except Exception:
+                pass
+
+    def summary(self):
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(s)}
+
+
+# =============================================================================== the CPU reference arm
+def cpu_pipeline_sample(sample_nnz: int, cfg=PRODUCTS):
+    """The reference's CPU path on a bounded sample of the workload: the first `sample_nnz` entries of
+    the same synthetic stream, same sparse sizes.  Returns (seconds, kind)."""
+    from oracle import native, np_ref, synth
+    row, col, val = synth.synth_coo(cfg["seed"], 0, sample_nnz, cfg["M"], cfg["N"])
+    t0 = time.perf_counter()
+    np_ref.build_pipeline(row, col, val, cfg["M"], cfg["N"])
+    dt = time.perf_counter() - t0
+    return dt, ("reference" if native.have_ref() else "port")
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from oracle import native
+    native.port_lib()
+    for _ in range(max(args.warmup, 0) and 1):
+        cpu_pipeline_sample(CPU_SAMPLE_NNZ // 8)
+    times = []
+    for _ in range(args.steps):
+        dt, kind = cpu_pipeline_sample(CPU_SAMPLE_NNZ)
+        times.append(dt)
+    ms = 1e3 * sum(times) / len(times)
+    value = CPU_SAMPLE_NNZ / (ms * 1e-3)
+    sample = (f"first {CPU_SAMPLE_NNZ} entries of the configs[1] stream at full sparse sizes per step; NumPy restatement "
+              f"of storage.py/transpose.py op chain + reference csrc/cpu ind2ptr ({kind}); single-threaded like the reference")
+    line = {
+        "impl": "reference", "metric": "coalesce+CSR/CSC build nnz/s", "value": value, "unit": "nnz/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int64 keys + f32 values",
+        "data": "synthetic", "config": workload_config(args.gpus),
+        "cpu_baseline": {"value": value, "unit": "nnz/s", "cores": 1, "kind": kind, "sample": sample,
+                         "host_cores_available": os.cpu_count()},
+        "e2e": {"value": value, "unit": "nnz/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+def workload_config(n_gpus: int):
+    if n_gpus <= 1:
+        c = PRODUCTS
+        return {"workload": f"{c['name']}: {c['M']} nodes, {c['nnz']} nnz, fp32; SparseTensor(...) sort-on-construct + "
+                            "coalesce(add) + fill_cache_ (rowptr, csr2csc, colptr, csc2csr, counts) + t()",
+                "l2": "inputs (1.24 GB) and every intermediate exceed the 126 MB L2; no explicit flush"}
+    c = PAPERS
+    return {"workload": f"{c['name']} row-partitioned over {n_gpus} GPUs: {c['M']} nodes, {c['nnz_per_gpu']} nnz per GPU "
+                        f"({c['nnz_per_gpu'] * n_gpus} total), fp32; splitter histogram + NCCL all-to-all + local "
+                        "coalesce + CSR/CSC build per row shard",
+            "l2": "per-GPU inputs (4.0 GB) exceed the 126 MB L2; no explicit flush", "parallelism": f"row-range x{n_gpus}"}
+
+
+# =============================================================================== our arm
+def pipeline_step(ps, row, col, val, M, N):
+    A = ps.SparseTensor(row=row, col=col, value=val, sparse_sizes=(M, N)).coalesce("add").fill_cache_()
+    return A, A.t()
+
+
+def sort_passes(bits: int) -> int:
+    return max((bits + 7) // 8, 1)
+
+
+def bits_for(n: int) -> int:
+    b = 0
+    while (1 << b) < n:
+        b += 1
+    return b
+
+
+def rs_pass_bytes(nnz_in: int, nnz_out: int, M: int, N: int) -> int:
+    """Algorithmic bytes moved by every rs_pass_kernel launch of one step ('kernels'):
+    sort-on-construct = P1 passes over nnz_in 8-byte keys + 4-byte payload (the first reads int64 row, col +
+    fp32 value = 20 B, the last writes them back unpacked = 20 B); csr2csc = P2 passes over nnz_out 4-byte keys
+    + 4-byte payload (first reads the int64 col, last writes the int64 permutation + the sorted 4-byte keys)."""
+    p1 = sort_passes(bits_for(M) + bits_for(N))
+    p2 = sort_passes(bits_for(N))
+    sort1 = nnz_in * ((20 + 12) + max(p1 - 2, 0) * 24 + (12 + 20)) if p1 > 1 else nnz_in * 40
+    sort2 = nnz_out * ((8 + 8) + max(p2 - 2, 0) * 16 + (8 + 12)) if p2 > 1 else nnz_out * 20
+    return sort1 + sort2
+
+
+def read_profile(lib):
+    import ctypes
+    out = {}
+    for i in range(lib.ps_prof_kinds()):
+        ms, n = ctypes.c_double(), ctypes.c_int64()
+        lib.ps_prof_read(i, ctypes.byref(ms), ctypes.byref(n))
+        if n.value:
+            out[lib.ps_prof_name(i).decode()] = (ms.value, n.value)
+    return out
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != max(args.gpus, 1):
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torch.distributed.run")
+    torch.cuda.set_device(local_rank)
+    device = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=device)
+
+    import paddle_sparse_b200 as ps  # raises when the CUDA library is missing: no fallback
+    lib = ps._lib.lib()
+    hbm_peak, peak_src = peaks()
+
+    if world == 1:
+        cfg = PRODUCTS
+        M, N, nnz = cfg["M"], cfg["N"], cfg["nnz"]
+        row, col, val = ps.ops.synth_coo(cfg["seed"], 0, nnz, M, N, device)
+
+        def step():
+            return pipeline_step(ps, row, col, val, M, N)
+        units_per_step = nnz
+    else:
+        from paddle_sparse_b200 import dist as psd
+        cfg = PAPERS
+        M, N, npg = cfg["M"], cfg["N"], cfg["nnz_per_gpu"]
+        row, col, val = ps.ops.synth_coo(cfg["seed"], rank * npg, npg, M, N, device)
+
+        def step():
+            return psd.build_partitioned(row, col, val, (M, N), fill_cache=True, transpose=False)
+        units_per_step = npg * world
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        out = None
+        for _ in range(steps):
+            out = fn()
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1) / steps], device=device, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms), out
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    read_profile(lib)
+    lib.ps_prof_enable(1)
+    launches0 = int(lib.ps_launch_count())
+    with ClockSampler(local_rank) as clocks:
+        ms, out = timed(step, args.steps)
+    launches = int(lib.ps_launch_count()) - launches0
+    lib.ps_prof_enable(0)
+    prof = read_profile(lib)
+    value = units_per_step / (ms * 1e-3)
+
+    # ---- end to end: host (pinned) inputs, H2D + hot path + D2H of the result pointer array, every step
+    if world == 1:
+        h_row, h_col, h_val = (t.cpu().pin_memory() for t in (row, col, val))
+        h_out = torch.empty(M + 1, dtype=torch.int64).pin_memory()
+
+        def e2e_step():
+            r, c, v = (t.to(device, non_blocking=True) for t in (h_row, h_col, h_val))
+            A, At = pipeline_step(ps, r, c, v, M, N)
+            h_out.copy_(A.storage.rowptr(), non_blocking=True)
+            return A
+        h2d = sum(t.numel() * t.element_size() for t in (h_row, h_col, h_val))
+        d2h = h_out.numel() * h_out.element_size()
+        for _ in range(2):
+            e2e_step()
+        e2e_ms, _ = timed(e2e_step, max(args.steps // 2, 2))
+        e2e = {"value": units_per_step / (e2e_ms * 1e-3), "unit": "nnz/s", "h2d_bytes_per_step": h2d,
+               "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms}
+        nnz_out = out[0].nnz()
+    else:
+        e2e = psd.bench_e2e(ps, cfg, rank, world, device, args, timed, units_per_step)
+        nnz_out = None
+
+    line = {
+        "metric": "coalesce+CSR/CSC build nnz/s", "value": value, "unit": "nnz/s", "n_gpus": world,
+        "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "int64 keys + f32 values", "data": "synthetic",
+        "config": workload_config(world), "clocks": clocks.summary(), "e2e": e2e,
+        "gpu_launches": launches,
+        "kernels_ms_per_step": {k: round(v[0] / args.steps, 4) for k, v in sorted(prof.items(), key=lambda kv: -kv[1][0])},
+    }
+    if world == 1:
+        fam_ms, fam_n = prof.get("rs_pass_kernel", (0.0, 0))
+        alg = rs_pass_bytes(nnz, nnz_out, M, N)  # per step
+        achieved = alg * args.steps / (fam_ms * 1e-3) / 1e9 if fam_ms else None
+        line["roofline"] = {
+            "bound": "hbm", "kernel": "rs_pass_kernel (one-sweep radix pass)", "achieved": achieved, "peak": hbm_peak,
+            "unit": "GB/s", "frac": (achieved / hbm_peak) if achieved else None, "traffic": None,
+            "peak_source": peak_src, "launches_per_step": fam_n / args.steps,
+            "avg_launch_ms": fam_ms / fam_n if fam_n else None,
+            "algorithmic_bytes_per_launch": alg / (fam_n / args.steps) if fam_n else None,
+            "share_of_step": (fam_ms / args.steps) / ms if ms else None,
+        }
+        line["pipeline_roofline"] = {
+            "algorithmic_bytes_per_nnz": PIPELINE_BYTES_PER_NNZ,
+            "achieved_GBps": PIPELINE_BYTES_PER_NNZ * value / 1e9,
+            "frac_of_measured_hbm": PIPELINE_BYTES_PER_NNZ * value / 1e9 / hbm_peak,
+            "frac_of_nominal_8TBps": PIPELINE_BYTES_PER_NNZ * value / 1e9 / 8000.0,
+        }
+        if rank == 0 and not args.no_cpu:
+            dt, kind = cpu_pipeline_sample(CPU_SAMPLE_NNZ)
+            line["cpu_baseline"] = {
+                "value": CPU_SAMPLE_NNZ / dt, "unit": "nnz/s", "cores": 1, "kind": kind,
+                "sample": f"first {CPU_SAMPLE_NNZ} entries of the same stream at full sparse sizes, one pass ({dt:.1f} s)",
+                "host_cores_available": os.cpu_count()}
+    if rank == 0:
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -43,6 +43,15 @@ enum { PS_SUM = 0, PS_MEAN = 1, PS_MIN = 2, PS_MAX = 3 };
 /* csrc/version.cpp:8-33 `sparse_cuda_version` -> CUDA_VERSION the library was built with */
 int64_t ps_cuda_version(void);
 const char *ps_last_error(void);
+/* number of CUDA kernels this library has launched so far in the process (bench.py: gpu_launches) */
+int64_t ps_launch_count(void);
+/* Live per-kernel timing for bench.py's roofline: when enabled, CUDA events are recorded on the
+ * launching stream around every launch of the main kernel families; ps_prof_read returns the
+ * summed duration and launch count of family `id` since the last read. */
+void ps_prof_enable(int on);
+int ps_prof_kinds(void);
+const char *ps_prof_name(int id);
+int ps_prof_read(int id, double *total_ms, int64_t *launches);
 
 /* ------------------------------------------------------------------ convert */
 /* csrc/convert.cpp:13-23 `ind2ptr(ind, M)`; kernels csrc/cuda/convert_cuda.cu:6-40,

@@ -23,6 +23,11 @@ c_ptr = ctypes.c_void_p
 SIGNATURES = {
     "ps_cuda_version": [],
     "ps_last_error": [],
+    "ps_launch_count": [],
+    "ps_prof_enable": [c_int],
+    "ps_prof_kinds": [],
+    "ps_prof_name": [c_int],
+    "ps_prof_read": [c_int, c_ptr, c_ptr],
     "ps_ind2ptr": [c_ptr, c_i64, c_i64, c_ptr, c_ptr],
     "ps_ptr2ind": [c_ptr, c_i64, c_i64, c_ptr, c_ptr],
     "ps_ptr2count": [c_ptr, c_i64, c_ptr, c_ptr],
@@ -57,7 +62,8 @@ SIGNATURES = {
     "ps_add_scalar": [c_ptr, c_i64, c_i64, c_ptr, c_ptr],
     "ps_synth_coo": [c_u64, c_i64, c_i64, c_i64, c_i64, c_ptr, c_ptr, c_ptr, c_ptr],
 }
-_RESTYPES = {"ps_cuda_version": c_i64, "ps_last_error": ctypes.c_char_p}
+_RESTYPES = {"ps_cuda_version": c_i64, "ps_last_error": ctypes.c_char_p, "ps_launch_count": c_i64,
+             "ps_prof_enable": None, "ps_prof_name": ctypes.c_char_p}
 
 _lib = None
 

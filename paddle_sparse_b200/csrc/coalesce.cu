@@ -113,8 +113,11 @@ int dedup_launch(KeySrc ksrc, PaySrc psrc, int64_t n, int cbits, int64_t *out_ro
   const int64_t tiles = ceil_div(n, THREADS * ITEMS);
   PS_SCRATCH(state, scratch, uint64_t, tiles + 1);
   PS_CUDA(cudaMemsetAsync(state, 0, sizeof(uint64_t) * (size_t)(tiles + 1), s));
-  dedup_kernel<KeyT, T, RED, MODE, THREADS, ITEMS><<<(unsigned)tiles, THREADS, 0, s>>>(
-      ksrc, psrc, n, cbits, out_row, out_col, reinterpret_cast<T *>(out_value), run_start, state, d_nnz);
+  {
+    ProfScope prof(PROF_DEDUP, s);
+    dedup_kernel<KeyT, T, RED, MODE, THREADS, ITEMS><<<(unsigned)tiles, THREADS, 0, s>>>(
+        ksrc, psrc, n, cbits, out_row, out_col, reinterpret_cast<T *>(out_value), run_start, state, d_nnz);
+  }
   PS_LAUNCH_OK();
   return PS_OK;
 }

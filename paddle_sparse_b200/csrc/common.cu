@@ -4,6 +4,7 @@
 #include <stdio.h>
 #include <string.h>
 
+#include <atomic>
 #include <mutex>
 
 #include "common.cuh"
@@ -17,6 +18,40 @@ void set_error(const char *fmt, ...) {
   va_start(ap, fmt);
   vsnprintf(g_err, sizeof(g_err), fmt, ap);
   va_end(ap);
+}
+
+static std::atomic<long long> g_launches{0};
+void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+
+// ---- live kernel timing (see common.cuh)
+struct ProfPair {
+  cudaEvent_t a, b;
+};
+static std::atomic<bool> g_prof_on{false};
+static std::mutex g_prof_mu;
+static std::vector<ProfPair> g_prof[PROF_COUNT];
+static const char *const g_prof_names[PROF_COUNT] = {"rs_hist_kernel",  "rs_pass_kernel",   "dedup_kernel",
+                                                     "ind2ptr_kernel",  "ptr2ind_kernel",   "invert_perm_kernel",
+                                                     "transpose_gather_kernel", "segment_reduce_kernel",
+                                                     "gather_rows_kernel"};
+
+ProfScope::ProfScope(int id, cudaStream_t s) : id_(id), s_(s), slot_(nullptr) {
+  if (!g_prof_on.load(std::memory_order_relaxed)) return;
+  ProfPair *p = new ProfPair;
+  if (cudaEventCreate(&p->a) != cudaSuccess || cudaEventCreate(&p->b) != cudaSuccess) {
+    delete p;
+    return;
+  }
+  cudaEventRecord(p->a, s_);
+  slot_ = p;
+}
+ProfScope::~ProfScope() {
+  if (!slot_) return;
+  ProfPair *p = static_cast<ProfPair *>(slot_);
+  cudaEventRecord(p->b, s_);
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  g_prof[id_].push_back(*p);
+  delete p;
 }
 
 int sm_count() {
@@ -73,5 +108,37 @@ extern "C" {
 int64_t ps_cuda_version(void) { return (int64_t)CUDA_VERSION; }
 
 const char *ps_last_error(void) { return ps::g_err; }
+
+int64_t ps_launch_count(void) { return (int64_t)ps::g_launches.load(); }
+
+void ps_prof_enable(int on) { ps::g_prof_on.store(on != 0); }
+
+int ps_prof_kinds(void) { return (int)ps::PROF_COUNT; }
+
+const char *ps_prof_name(int id) { return (id >= 0 && id < ps::PROF_COUNT) ? ps::g_prof_names[id] : ""; }
+
+// Sum of the recorded durations of kernel family `id` since the last read (synchronises on the
+// recorded events, then forgets them).
+int ps_prof_read(int id, double *total_ms, int64_t *launches) {
+  using namespace ps;
+  PS_CHECK(id >= 0 && id < PROF_COUNT && total_ms && launches, "prof_read: bad arguments");
+  std::vector<ProfPair> v;
+  {
+    std::lock_guard<std::mutex> lk(g_prof_mu);
+    v.swap(g_prof[id]);
+  }
+  double tot = 0;
+  for (auto &p : v) {
+    float ms = 0;
+    PS_CUDA(cudaEventSynchronize(p.b));
+    PS_CUDA(cudaEventElapsedTime(&ms, p.a, p.b));
+    tot += ms;
+    cudaEventDestroy(p.a);
+    cudaEventDestroy(p.b);
+  }
+  *total_ms = tot;
+  *launches = (int64_t)v.size();
+  return PS_OK;
+}
 
 }  // extern "C"

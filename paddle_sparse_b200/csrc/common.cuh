@@ -44,7 +44,28 @@ int sm_count();  // SMs of the current device (148 on B200), cached
     if (rc_ != PS_OK) return rc_; \
   } while (0)
 
-#define PS_LAUNCH_OK() PS_CUDA(cudaGetLastError())
+// every kernel launch is followed by PS_LAUNCH_OK(): it checks the launch and counts it
+// (ps_launch_count(), reported by bench.py as gpu_launches)
+void count_launch();
+#define PS_LAUNCH_OK()            \
+  do {                            \
+    ps::count_launch();           \
+    PS_CUDA(cudaGetLastError());  \
+  } while (0)
+
+// ----------------------------------------------------------------------------- live kernel timing
+// Optional (ps_prof_enable): CUDA events recorded on the launching stream around the launches of
+// one kernel family, so bench.py can report the dominant kernel's average duration measured
+// inside the timed region.  Off by default: no events, no overhead.
+enum ProfId { PROF_RS_HIST = 0, PROF_RS_PASS, PROF_DEDUP, PROF_IND2PTR, PROF_PTR2IND, PROF_INVERT_PERM,
+              PROF_TRANSPOSE_GATHER, PROF_SEGMENT_REDUCE, PROF_GATHER, PROF_COUNT };
+struct ProfScope {
+  ProfScope(int id, cudaStream_t s);
+  ~ProfScope();
+  int id_;
+  cudaStream_t s_;
+  void *slot_;
+};
 
 // ----------------------------------------------------------------------------- scratch
 // Stream-ordered scratch: cudaMallocAsync from the device's default pool (release

@@ -86,8 +86,11 @@ int ind2ptr_launch(const IndT *ind, int64_t numel, int64_t M, int64_t *out, cuda
   if (fill_blocks > cap) fill_blocks = cap;
   if (fill_blocks < 1) fill_blocks = 1;
   if (elem_blocks + fill_blocks > 2147483647LL) { set_error("ind2ptr: input too large"); return PS_ERR_ARG; }
-  ind2ptr_kernel<IndT, THREADS><<<(unsigned)(elem_blocks + fill_blocks), THREADS, 0, s>>>(
-      ind, numel, M, out, (int)elem_blocks, (int)fill_blocks, (reinterpret_cast<uintptr_t>(ind) & 15) == 0);
+  {
+    ProfScope prof(PROF_IND2PTR, s);
+    ind2ptr_kernel<IndT, THREADS><<<(unsigned)(elem_blocks + fill_blocks), THREADS, 0, s>>>(
+        ind, numel, M, out, (int)elem_blocks, (int)fill_blocks, (reinterpret_cast<uintptr_t>(ind) & 15) == 0);
+  }
   PS_LAUNCH_OK();
   return PS_OK;
 }
@@ -238,7 +241,10 @@ int ps_ptr2ind(const int64_t *ptr, int64_t M, int64_t E, int64_t *out_ind, void 
   PS_CHECK(M > 0, "ptr2ind: E > 0 with no rows");
   constexpr int THREADS = 256, ITEMS = 8;
   const int64_t tiles = ceil_div(E, THREADS * ITEMS);
-  ptr2ind_kernel<THREADS, ITEMS><<<(unsigned)tiles, THREADS, 0, (cudaStream_t)stream>>>(ptr, M, E, out_ind);
+  {
+    ProfScope prof(PROF_PTR2IND, (cudaStream_t)stream);
+    ptr2ind_kernel<THREADS, ITEMS><<<(unsigned)tiles, THREADS, 0, (cudaStream_t)stream>>>(ptr, M, E, out_ind);
+  }
   PS_LAUNCH_OK();
   return PS_OK;
 }

@@ -294,7 +294,10 @@ int radix_sort_pairs(KeySrc ksrc, PaySrc psrc, int64_t n, int total_bits, KeyT *
   int64_t hb = ceil_div(n, 512 * 16);
   const int64_t cap = 8 * (int64_t)sm_count();
   if (hb > cap) hb = cap;
-  rs_hist_kernel<KeyT><<<(unsigned)hb, 512, 0, s>>>(ksrc, n, plan, ghist);
+  {
+    ProfScope prof(PROF_RS_HIST, s);
+    rs_hist_kernel<KeyT><<<(unsigned)hb, 512, 0, s>>>(ksrc, n, plan, ghist);
+  }
   PS_LAUNCH_OK();
   rs_scan_kernel<<<plan.passes, RS_RADIX, 0, s>>>(ghist);
   PS_LAUNCH_OK();
@@ -316,8 +319,11 @@ int radix_sort_pairs(KeySrc ksrc, PaySrc psrc, int64_t n, int total_bits, KeyT *
       ko = keys_final;
       pd = pay_final;
     }
-    rs_pass_kernel<KeyT, ITEMS><<<(unsigned)tiles, RS_THREADS, smem, s>>>(
-        ks, ps_, ko, pd, n, plan.begin[p], plan.bits[p], p + 1, ghist + (size_t)p * RS_RADIX, state, tickets + p);
+    {
+      ProfScope prof(PROF_RS_PASS, s);
+      rs_pass_kernel<KeyT, ITEMS><<<(unsigned)tiles, RS_THREADS, smem, s>>>(
+          ks, ps_, ko, pd, n, plan.begin[p], plan.bits[p], p + 1, ghist + (size_t)p * RS_RADIX, state, tickets + p);
+    }
     PS_LAUNCH_OK();
   }
   return PS_OK;

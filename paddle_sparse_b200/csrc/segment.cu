@@ -51,6 +51,7 @@ static int segment_reduce_typed(const T *src, int64_t width, const int64_t *ptr,
   else if (avg <= 48.0) G = 8;
   const int64_t threads = outputs * G;
   const unsigned blocks = (unsigned)ceil_div(threads, 256);
+  ProfScope prof(PROF_SEGMENT_REDUCE, s);
   switch (G) {
     case 1: segment_reduce_kernel<T, RED, 1><<<blocks, 256, 0, s>>>(src, width, ptr, S, out, perm); break;
     case 4: segment_reduce_kernel<T, RED, 4><<<blocks, 256, 0, s>>>(src, width, ptr, S, out, perm); break;
@@ -89,6 +90,7 @@ int gather_rows_launch(const void *src, int64_t row_bytes, const IndexT *index, 
   const int unit = copy_unit(row_bytes, src, out);
   const int64_t upr = row_bytes / unit, n_units = n_out * upr;
   const unsigned blocks = (unsigned)ceil_div(n_units, 256);
+  ProfScope prof(PROF_GATHER, s);
 #define PS_G(U) gather_rows_kernel<U, IndexT><<<blocks, 256, 0, s>>>((const U *)src, upr, index, n_units, (U *)out)
   switch (unit) {
     case 16: PS_G(uint4); break;

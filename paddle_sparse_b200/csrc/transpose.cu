@@ -79,7 +79,10 @@ int ps_csr2csc(const int64_t *col, int64_t nnz, int64_t N, int64_t *out_csr2csc,
 int ps_invert_perm(const int64_t *perm, int64_t n, int64_t *out, void *stream) {
   PS_CHECK(n >= 0, "invert_perm: negative size");
   if (n == 0) return PS_OK;
-  invert_perm_kernel<<<(unsigned)ceil_div(n, 256), 256, 0, (cudaStream_t)stream>>>(perm, n, out);
+  {
+    ProfScope prof(PROF_INVERT_PERM, (cudaStream_t)stream);
+    invert_perm_kernel<<<(unsigned)ceil_div(n, 256), 256, 0, (cudaStream_t)stream>>>(perm, n, out);
+  }
   PS_LAUNCH_OK();
   return PS_OK;
 }
@@ -103,6 +106,7 @@ int ps_transpose_gather(const int64_t *csr2csc, const int64_t *row, const int64_
     if (with_row) PS_T(U, true, true); \
     else PS_T(U, false, true);       \
   } while (0)
+  ProfScope *prof = new ProfScope(PROF_TRANSPOSE_GATHER, s);
   if (fused_value) {
     switch (unit) {
       case 16: PS_TV(uint4); break;
@@ -117,6 +121,7 @@ int ps_transpose_gather(const int64_t *csr2csc, const int64_t *row, const int64_
   }
 #undef PS_TV
 #undef PS_T
+  delete prof;
   PS_LAUNCH_OK();
   if (value && !fused_value) PS_TRY(gather_rows_launch<int64_t>(value, row_bytes, csr2csc, nnz, out_value, s));
   return PS_OK;
