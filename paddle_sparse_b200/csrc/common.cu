@@ -2,6 +2,7 @@
 #include <cuda.h>
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <atomic>
@@ -52,6 +53,15 @@ ProfScope::~ProfScope() {
   std::lock_guard<std::mutex> lk(g_prof_mu);
   g_prof[id_].push_back(*p);
   delete p;
+}
+
+int rs_variant() {
+  static int v = -1;
+  if (v < 0) {
+    const char *e = getenv("PS_RS_VARIANT");
+    v = e ? atoi(e) : 0;
+  }
+  return v;
 }
 
 int sm_count() {

@@ -21,8 +21,6 @@ namespace ps {
 
 constexpr int RS_RADIX = 256;
 constexpr int RS_MAX_PASSES = 8;
-constexpr int RS_THREADS = 512;
-constexpr int RS_WARPS = RS_THREADS / 32;
 
 struct SortPlan {
   int passes;
@@ -145,94 +143,195 @@ struct RsState {
   __device__ static uint64_t value(uint64_t w) { return w & ((uint64_t(1) << 56) - 1); }
 };
 
-template <typename KeyT, int ITEMS>
+template <typename KeyT, int THREADS, int ITEMS>
 struct RsSmem {
-  static constexpr int TILE = RS_THREADS * ITEMS;
+  static constexpr int TILE = THREADS * ITEMS;
+  static constexpr int WARPS = THREADS / 32;
   KeyT keys[TILE];
   uint32_t pay[TILE];
-  uint32_t warp_cnt[RS_WARPS][RS_RADIX];
+  uint32_t warp_cnt[WARPS][RS_RADIX];
   uint64_t gbase[RS_RADIX];
   uint32_t dig_excl[RS_RADIX];
   uint32_t scan_tmp[34];
   long long tile;
 };
 
+// Tile loads / stores with the (uniform) mode switch hoisted out of the unrolled loops.
 template <typename KeyT, int ITEMS>
-__global__ void __launch_bounds__(RS_THREADS, 2)
-rs_pass_kernel(KeySrc ksrc, PaySrc psrc, KeyDst kdst, PayDst pdst, int64_t n, int begin_bit,
-               int num_bits, int epoch, const unsigned long long *__restrict__ bin_base /*[256]*/,
+__device__ __forceinline__ void load_tile_keys(const KeySrc &s, int64_t tile_base, int warp_base, unsigned lane,
+                                               int tile_n, KeyT (&key)[ITEMS]) {
+  if (s.mode == KSRC_KEYS) {
+    const KeyT *p = reinterpret_cast<const KeyT *>(s.a) + tile_base;
+#pragma unroll
+    for (int i = 0; i < ITEMS; ++i) {
+      const int j = warp_base + i * 32 + lane;
+      key[i] = j < tile_n ? ld_stream(p + j) : ~KeyT(0);
+    }
+  } else if (s.mode == KSRC_PACK_COO) {
+    const int64_t *r = reinterpret_cast<const int64_t *>(s.a) + tile_base;
+    const int64_t *c = reinterpret_cast<const int64_t *>(s.b) + tile_base;
+    int64_t rv[ITEMS], cv[ITEMS];
+#pragma unroll
+    for (int i = 0; i < ITEMS; ++i) {
+      const int j = warp_base + i * 32 + lane;
+      rv[i] = j < tile_n ? ld_stream(r + j) : -1;
+    }
+#pragma unroll
+    for (int i = 0; i < ITEMS; ++i) {
+      const int j = warp_base + i * 32 + lane;
+      cv[i] = j < tile_n ? ld_stream(c + j) : -1;
+    }
+#pragma unroll
+    for (int i = 0; i < ITEMS; ++i) {
+      const int j = warp_base + i * 32 + lane;
+      key[i] = j < tile_n ? (KeyT)(((uint64_t)rv[i] << s.cbits) | (uint64_t)cv[i]) : ~KeyT(0);
+    }
+  } else {
+    const int64_t *p = reinterpret_cast<const int64_t *>(s.a) + tile_base;
+#pragma unroll
+    for (int i = 0; i < ITEMS; ++i) {
+      const int j = warp_base + i * 32 + lane;
+      key[i] = j < tile_n ? (KeyT)ld_stream(p + j) : ~KeyT(0);
+    }
+  }
+}
+
+template <int ITEMS>
+__device__ __forceinline__ void load_tile_pay(const PaySrc &s, int64_t tile_base, int warp_base, unsigned lane,
+                                              int tile_n, uint32_t (&pay)[ITEMS]) {
+  if (s.mode == PSRC_U32) {
+    const uint32_t *p = reinterpret_cast<const uint32_t *>(s.p) + tile_base;
+#pragma unroll
+    for (int i = 0; i < ITEMS; ++i) {
+      const int j = warp_base + i * 32 + lane;
+      pay[i] = j < tile_n ? ld_stream(p + j) : 0u;
+    }
+  } else if (s.mode == PSRC_IOTA) {
+#pragma unroll
+    for (int i = 0; i < ITEMS; ++i) pay[i] = (uint32_t)(tile_base + warp_base + i * 32 + lane);
+  } else if (s.mode == PSRC_U16) {
+    const uint16_t *p = reinterpret_cast<const uint16_t *>(s.p) + tile_base;
+#pragma unroll
+    for (int i = 0; i < ITEMS; ++i) {
+      const int j = warp_base + i * 32 + lane;
+      pay[i] = j < tile_n ? (uint32_t)p[j] : 0u;
+    }
+  } else {
+    const uint8_t *p = reinterpret_cast<const uint8_t *>(s.p) + tile_base;
+#pragma unroll
+    for (int i = 0; i < ITEMS; ++i) {
+      const int j = warp_base + i * 32 + lane;
+      pay[i] = j < tile_n ? (uint32_t)p[j] : 0u;
+    }
+  }
+}
+
+// One tile: THREADS * ITEMS pairs.  Phases:
+//   1 load keys (all loads in flight)
+//   2 per item round: match lanes with equal digits, rank inside the warp, warp-private digit counts
+//   3 digit totals -> the tile's aggregate is PUBLISHED EARLY (successors rarely wait on it), block scan
+//   4 position of every item inside the sorted tile
+//   5 stage pairs in tile-sorted order; digit threads finish the decoupled look-back meanwhile
+//   6 coalesced scatter of contiguous per-digit runs
+template <typename KeyT, int THREADS, int ITEMS, int MIN_BLOCKS>
+__global__ void __launch_bounds__(THREADS, MIN_BLOCKS)
+rs_pass_kernel(KeySrc ksrc, PaySrc psrc, KeyDst kdst, PayDst pdst, int64_t n, int begin_bit, int num_bits, int epoch,
+               const unsigned long long *__restrict__ bin_base /*[256]*/,
                uint64_t *__restrict__ tile_state /*[tiles][256]*/, unsigned long long *ticket) {
-  constexpr int TILE = RS_THREADS * ITEMS;
+  constexpr int TILE = THREADS * ITEMS;
+  constexpr int WARPS = THREADS / 32;
+  static_assert(THREADS >= RS_RADIX, "one thread per digit is required");
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  RsSmem<KeyT, ITEMS> &sm = *reinterpret_cast<RsSmem<KeyT, ITEMS> *>(smem_raw);
+  RsSmem<KeyT, THREADS, ITEMS> &sm = *reinterpret_cast<RsSmem<KeyT, THREADS, ITEMS> *>(smem_raw);
 
   const unsigned tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
   if (tid == 0) sm.tile = (long long)atomicAdd(ticket, 1ull);
-  for (int j = tid; j < RS_WARPS * RS_RADIX; j += RS_THREADS) (&sm.warp_cnt[0][0])[j] = 0;
+  for (int j = tid; j < WARPS * RS_RADIX; j += THREADS) (&sm.warp_cnt[0][0])[j] = 0;
   __syncthreads();
   const int64_t tile = sm.tile;
   const int64_t tile_base = tile * TILE;
   const int tile_n = (int)((n - tile_base) < TILE ? (n - tile_base) : TILE);
   const unsigned mask = (1u << num_bits) - 1u;
-
-  // ---- load (warp-striped: item i of lane l sits at warp_base + i*32 + l)
-  KeyT key[ITEMS];
-  uint32_t pay[ITEMS];
   const int warp_base = warp * (32 * ITEMS);
-#pragma unroll
-  for (int i = 0; i < ITEMS; ++i) {
-    const int j = warp_base + i * 32 + lane;
-    key[i] = j < tile_n ? load_key<KeyT>(ksrc, tile_base + j) : ~KeyT(0);
-  }
-#pragma unroll
-  for (int i = 0; i < ITEMS; ++i) {
-    const int j = warp_base + i * 32 + lane;
-    pay[i] = j < tile_n ? load_pay(psrc, tile_base + j) : 0u;
-  }
 
-  // ---- rank inside the warp, item by item (stable): match lanes with the same digit
-  uint32_t rank[ITEMS];
+  // ---- 1: keys, digits, match masks (padding keys are all-ones: the largest digit, ranked last)
+  KeyT key[ITEMS];
+  load_tile_keys<KeyT, ITEMS>(ksrc, tile_base, warp_base, lane, tile_n, key);
+  // ---- 2: rank inside the warp, item round by item round (stable), with warp-private digit counters:
+  // plain LDS / STS (shared-memory atomics cost 2 cycles per lane on this part) ordered by __syncwarp
+  unsigned peers[ITEMS];  // becomes the rank of the item inside its (warp, digit) group
   uint32_t *my_cnt = sm.warp_cnt[warp];
   const unsigned lt = lanemask_lt();
 #pragma unroll
   for (int i = 0; i < ITEMS; ++i) {
     const unsigned d = (unsigned)(key[i] >> begin_bit) & mask;
-    const unsigned peers = __match_any_sync(0xffffffffu, d);
+    const unsigned m = __match_any_sync(0xffffffffu, d);
     const uint32_t before = my_cnt[d];
     __syncwarp();
-    if ((peers & lt) == 0) my_cnt[d] = before + __popc(peers);  // lowest peer lane updates
+    if ((m & lt) == 0) my_cnt[d] = before + __popc(m);  // lowest peer lane updates
     __syncwarp();
-    rank[i] = before + __popc(peers & lt);
+    peers[i] = before + __popc(m & lt);
   }
   __syncthreads();
 
-  // ---- per digit: exclusive prefix over warps, tile total, look-back
+  // ---- 3: per digit: exclusive prefix over warps, tile total; publish the aggregate right away
   uint32_t total = 0;
+  uint64_t *st = tile_state + tid;  // word of (tile t, digit tid) at st[t * 256]
   if (tid < RS_RADIX) {
 #pragma unroll
-    for (int w = 0; w < RS_WARPS; ++w) {
+    for (int w = 0; w < WARPS; ++w) {
       const uint32_t c = sm.warp_cnt[w][tid];
       sm.warp_cnt[w][tid] = total;
       total += c;
     }
+    TileState::store(st + tile * RS_RADIX, RsState::pack(epoch, tile == 0 ? RsState::PREFIX : RsState::AGG, total));
   }
   uint32_t tile_total;
-  const uint32_t dexcl = block_exclusive_scan<uint32_t, RS_THREADS>(total, sm.scan_tmp, &tile_total);
+  const uint32_t dexcl = block_exclusive_scan<uint32_t, THREADS>(total, sm.scan_tmp, &tile_total);
+  if (tid < RS_RADIX) sm.dig_excl[tid] = dexcl;
+  __syncthreads();
+
+  // ---- 4: position inside the sorted tile
+#pragma unroll
+  for (int i = 0; i < ITEMS; ++i) {
+    const unsigned d = (unsigned)(key[i] >> begin_bit) & mask;
+    peers[i] += sm.dig_excl[d] + my_cnt[d];
+  }
+
+  // ---- 5: stage in tile-sorted order (payloads are loaded late: registers, see -Xptxas -v)
+  {
+    uint32_t pay[ITEMS];
+    load_tile_pay<ITEMS>(psrc, tile_base, warp_base, lane, tile_n, pay);
+#pragma unroll
+    for (int i = 0; i < ITEMS; ++i) sm.keys[peers[i]] = key[i];
+#pragma unroll
+    for (int i = 0; i < ITEMS; ++i) sm.pay[peers[i]] = pay[i];
+  }
+  // look-back: by now the predecessors have usually published their inclusive prefix
   if (tid < RS_RADIX) {
-    sm.dig_excl[tid] = dexcl;
-    uint64_t *st = tile_state + tid;  // word of (tile t, digit tid) at st[t * 256]
     uint64_t excl = 0;
-    if (tile == 0) {
-      TileState::store(st, RsState::pack(epoch, RsState::PREFIX, total));
-    } else {
-      TileState::store(st + tile * RS_RADIX, RsState::pack(epoch, RsState::AGG, total));
+    if (tile > 0) {
+      // walk back LB tiles per step with all LB loads in flight (the walk is latency-bound: a serial
+      // walk costs one L2 round trip per predecessor that has only published its aggregate)
+      constexpr int LB = 8;
       int64_t t = tile - 1;
-      while (true) {
-        const uint64_t w = TileState::load(st + t * RS_RADIX);
-        if (RsState::epoch(w) != (uint64_t)epoch) continue;  // not published in this pass yet
-        excl += RsState::value(w);
-        if (RsState::status(w) == RsState::PREFIX) break;
-        --t;
+      bool done = false;
+      while (!done) {
+        uint64_t w[LB];
+#pragma unroll
+        for (int q = 0; q < LB; ++q) w[q] = (t - q >= 0) ? TileState::load(st + (t - q) * RS_RADIX) : 0;
+#pragma unroll
+        for (int q = 0; q < LB; ++q) {
+          if (done) break;
+          if (RsState::epoch(w[q]) != (uint64_t)epoch) {  // not published in this pass yet: resume here
+            t -= q;
+            goto next_round;
+          }
+          excl += RsState::value(w[q]);
+          if (RsState::status(w[q]) == RsState::PREFIX) done = true;
+        }
+        t -= LB;
+      next_round:;
       }
       TileState::store(st + tile * RS_RADIX, RsState::pack(epoch, RsState::PREFIX, excl + total));
     }
@@ -240,33 +339,87 @@ rs_pass_kernel(KeySrc ksrc, PaySrc psrc, KeyDst kdst, PayDst pdst, int64_t n, in
   }
   __syncthreads();
 
-  // ---- stage in tile-sorted order
+  // ---- 6: coalesced scatter: consecutive staged slots of one digit go to consecutive addresses
+  const bool full = tile_n == TILE;
+  if (kdst.mode == KDST_KEYS && pdst.mode == PDST_U32) {
+    KeyT *ko = reinterpret_cast<KeyT *>(kdst.a);
+    uint32_t *po = reinterpret_cast<uint32_t *>(pdst.p);
 #pragma unroll
-  for (int i = 0; i < ITEMS; ++i) {
-    const unsigned d = (unsigned)(key[i] >> begin_bit) & mask;
-    const uint32_t pos = sm.dig_excl[d] + my_cnt[d] + rank[i];
-    sm.keys[pos] = key[i];
-    sm.pay[pos] = pay[i];
-  }
-  __syncthreads();
-
-  // ---- coalesced scatter: consecutive staged slots of one digit go to consecutive addresses
+    for (int k = 0; k < ITEMS; ++k) {
+      const int j = k * THREADS + tid;
+      if (full || j < tile_n) {
+        const KeyT kk = sm.keys[j];
+        const unsigned d = (unsigned)(kk >> begin_bit) & mask;
+        const int64_t dst = (int64_t)(sm.gbase[d] + (uint64_t)j);
+        ko[dst] = kk;
+        po[dst] = sm.pay[j];
+      }
+    }
+  } else {
 #pragma unroll
-  for (int k = 0; k < ITEMS; ++k) {
-    const int j = k * RS_THREADS + tid;
-    if (j < tile_n) {
-      const KeyT kk = sm.keys[j];
-      const unsigned d = (unsigned)(kk >> begin_bit) & mask;
-      const int64_t dst = (int64_t)(sm.gbase[d] + (uint64_t)j);
-      store_key<KeyT>(kdst, dst, kk);
-      store_pay(pdst, dst, sm.pay[j]);
+    for (int k = 0; k < ITEMS; ++k) {
+      const int j = k * THREADS + tid;
+      if (full || j < tile_n) {
+        const KeyT kk = sm.keys[j];
+        const unsigned d = (unsigned)(kk >> begin_bit) & mask;
+        const int64_t dst = (int64_t)(sm.gbase[d] + (uint64_t)j);
+        store_key<KeyT>(kdst, dst, kk);
+        store_pay(pdst, dst, sm.pay[j]);
+      }
     }
   }
 }
 
 // ----------------------------------------------------------------------------- host driver
-template <typename KeyT> struct RsItems { static constexpr int value = 12; };
-template <> struct RsItems<uint32_t> { static constexpr int value = 16; };
+// Tile geometry per key type (measured on B200, profiles/): 8-byte keys 256 x 12 with 4 CTAs per SM,
+// 4-byte keys 256 x 16.  PS_RS_VARIANT (bench knob, read once) overrides: 0 = default.
+int rs_variant();
+
+template <typename KeyT, int THREADS, int ITEMS, int MIN_BLOCKS>
+int rs_launch_pass(KeySrc ks, PaySrc ps_, KeyDst ko, PayDst pd, int64_t n, int begin, int bits, int epoch,
+                   const unsigned long long *bin_base, uint64_t *state, unsigned long long *ticket, cudaStream_t s) {
+  constexpr int TILE = THREADS * ITEMS;
+  const size_t smem = sizeof(RsSmem<KeyT, THREADS, ITEMS>);
+  PS_CUDA(cudaFuncSetAttribute(rs_pass_kernel<KeyT, THREADS, ITEMS, MIN_BLOCKS>,
+                               cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const int64_t tiles = ceil_div(n, TILE);
+  {
+    ProfScope prof(PROF_RS_PASS, s);
+    rs_pass_kernel<KeyT, THREADS, ITEMS, MIN_BLOCKS><<<(unsigned)tiles, THREADS, smem, s>>>(
+        ks, ps_, ko, pd, n, begin, bits, epoch, bin_base, state, ticket);
+  }
+  PS_LAUNCH_OK();
+  return PS_OK;
+}
+
+template <typename KeyT> struct RsGeom;
+template <> struct RsGeom<uint64_t> { static constexpr int T0 = 256, I0 = 12, B0 = 4; };
+template <> struct RsGeom<uint32_t> { static constexpr int T0 = 256, I0 = 16, B0 = 4; };
+
+template <typename KeyT>
+int rs_tile_size() {
+  switch (rs_variant()) {
+    case 1: return 512 * 12;
+    case 2: return 256 * 16;
+    case 3: return 384 * 16;
+    case 4: return 256 * 8;
+    default: return RsGeom<KeyT>::T0 * RsGeom<KeyT>::I0;
+  }
+}
+
+template <typename KeyT>
+int rs_dispatch_pass(KeySrc ks, PaySrc ps_, KeyDst ko, PayDst pd, int64_t n, int begin, int bits, int epoch,
+                     const unsigned long long *bin_base, uint64_t *state, unsigned long long *ticket, cudaStream_t s) {
+  switch (rs_variant()) {
+    case 1: return rs_launch_pass<KeyT, 512, 12, 2>(ks, ps_, ko, pd, n, begin, bits, epoch, bin_base, state, ticket, s);
+    case 2: return rs_launch_pass<KeyT, 256, 16, 3>(ks, ps_, ko, pd, n, begin, bits, epoch, bin_base, state, ticket, s);
+    case 3: return rs_launch_pass<KeyT, 384, 16, 2>(ks, ps_, ko, pd, n, begin, bits, epoch, bin_base, state, ticket, s);
+    case 4: return rs_launch_pass<KeyT, 256, 8, 6>(ks, ps_, ko, pd, n, begin, bits, epoch, bin_base, state, ticket, s);
+    default:
+      return rs_launch_pass<KeyT, RsGeom<KeyT>::T0, RsGeom<KeyT>::I0, RsGeom<KeyT>::B0>(ks, ps_, ko, pd, n, begin, bits,
+                                                                                        epoch, bin_base, state, ticket, s);
+  }
+}
 
 // Sorts n pairs on key bits [0, total_bits).  First-pass sources are ksrc/psrc.  The last
 // pass writes keys to keys_final (KDST_NONE: keys dropped) and payloads to pay_final.
@@ -276,11 +429,9 @@ int radix_sort_pairs(KeySrc ksrc, PaySrc psrc, int64_t n, int total_bits, KeyT *
                      uint32_t *pay_tmp0, uint32_t *pay_tmp1, KeyDst keys_final, PayDst pay_final,
                      Scratch &scratch, cudaStream_t s) {
   if (n <= 0) return PS_OK;
-  constexpr int ITEMS = RsItems<KeyT>::value;
-  constexpr int TILE = RS_THREADS * ITEMS;
   const SortPlan plan = make_sort_plan(total_bits);
   if (plan.passes > RS_MAX_PASSES) { set_error("radix sort: %d key bits unsupported", total_bits); return PS_ERR_ARG; }
-  const int64_t tiles = ceil_div(n, TILE);
+  const int64_t tiles = ceil_div(n, rs_tile_size<KeyT>());
 
   // one allocation: [passes*256 hist | passes tickets (padded to 32) | tiles*256 state words]
   const size_t hist_words = (size_t)plan.passes * RS_RADIX;
@@ -302,8 +453,6 @@ int radix_sort_pairs(KeySrc ksrc, PaySrc psrc, int64_t n, int total_bits, KeyT *
   rs_scan_kernel<<<plan.passes, RS_RADIX, 0, s>>>(ghist);
   PS_LAUNCH_OK();
 
-  const size_t smem = sizeof(RsSmem<KeyT, ITEMS>);
-  PS_CUDA(cudaFuncSetAttribute(rs_pass_kernel<KeyT, ITEMS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   KeyT *kt[2] = {keys_tmp0, keys_tmp1};
   uint32_t *pt[2] = {pay_tmp0, pay_tmp1};
   for (int p = 0; p < plan.passes; ++p) {
@@ -319,12 +468,8 @@ int radix_sort_pairs(KeySrc ksrc, PaySrc psrc, int64_t n, int total_bits, KeyT *
       ko = keys_final;
       pd = pay_final;
     }
-    {
-      ProfScope prof(PROF_RS_PASS, s);
-      rs_pass_kernel<KeyT, ITEMS><<<(unsigned)tiles, RS_THREADS, smem, s>>>(
-          ks, ps_, ko, pd, n, plan.begin[p], plan.bits[p], p + 1, ghist + (size_t)p * RS_RADIX, state, tickets + p);
-    }
-    PS_LAUNCH_OK();
+    PS_TRY(rs_dispatch_pass<KeyT>(ks, ps_, ko, pd, n, plan.begin[p], plan.bits[p], p + 1,
+                                  ghist + (size_t)p * RS_RADIX, state, tickets + p, s));
   }
   return PS_OK;
 }

@@ -1,0 +1,63 @@
+"""Micro-benchmark of the building blocks on the configs[1] shape (run on the GPU box):
+   python tools/sortbench.py [what ...]     what in {sort, coalesce, csc, all}
+Prints the live per-kernel timings of include/ps_abi.h: ps_prof_read."""
+import ctypes
+import os
+import sys
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import paddle_sparse_b200 as ps  # noqa: E402
+from paddle_sparse_b200 import ops  # noqa: E402
+
+lib = ps._lib.lib()
+M = N = 2449029
+NNZ = 61859140
+
+
+def prof():
+    out = {}
+    for i in range(lib.ps_prof_kinds()):
+        ms, n = ctypes.c_double(), ctypes.c_int64()
+        lib.ps_prof_read(i, ctypes.byref(ms), ctypes.byref(n))
+        if n.value:
+            out[lib.ps_prof_name(i).decode()] = (round(ms.value / n.value, 4), n.value)
+    return out
+
+
+def timeit(name, fn, reps=5):
+    for _ in range(2):
+        fn()
+    torch.cuda.synchronize()
+    prof()
+    lib.ps_prof_enable(1)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    lib.ps_prof_enable(0)
+    print(f"{name}: {e0.elapsed_time(e1) / reps:.3f} ms  per-launch avg ms (launches): {prof()}", flush=True)
+
+
+def main():
+    what = set(sys.argv[1:]) or {"all"}
+    row, col, val = ops.synth_coo(0x5EED0002, 0, NNZ, M, N, "cuda")
+    print("variant", os.environ.get("PS_RS_VARIANT", "0"))
+    if what & {"sort", "all"}:
+        timeit("sort_coo", lambda: ops.sort_coo(row, col, val, M, N))
+    if what & {"coalesce", "all"}:
+        timeit("coalesce", lambda: ops.coalesce(row, col, val, M, N))
+    if what & {"csc", "all"}:
+        r, c, v = ops.coalesce(row, col, val, M, N)
+        timeit("csr2csc", lambda: ops.csr2csc(c, N, True, False))
+        perm, colptr, _ = ops.csr2csc(c, N, True, False)
+        timeit("invert_perm", lambda: ops.invert_perm(perm))
+        timeit("transpose_gather", lambda: ops.transpose_gather(perm, r, c, v, colptr, N))
+        timeit("ind2ptr", lambda: ops.ind2ptr(r, M))
+
+
+if __name__ == "__main__":
+    main()
