@@ -28,6 +28,8 @@ PRODUCTS = dict(name="ogbn-products-shape", M=2449029, N=2449029, nnz=61859140, 
 PAPERS = dict(name="ogbn-papers100M-shape", M=111059956, N=111059956, nnz_per_gpu=201960734, seed=0x5EED0005)
 # SURVEY.md 8d figure A: compulsory bytes of the whole pipeline per input nnz at configs[1] (no duplicates)
 PIPELINE_BYTES_PER_NNZ = 128.6
+# without t() (the sharded step builds CSR + CSC structures per shard, no transposed copy): 128.6 - 48
+PIPELINE_LOCAL_BYTES_PER_NNZ = 80.6
 CPU_SAMPLE_NNZ = 8_000_000
 
 
@@ -279,8 +281,21 @@ def run_ours(args):
                "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms}
         nnz_out = out[0].nnz()
     else:
-        e2e = psd.bench_e2e(ps, cfg, rank, world, device, args, timed, units_per_step)
+        h_row, h_col, h_val = (t.cpu().pin_memory() for t in (row, col, val))
+
+        def e2e_step():
+            r, c, v = (t.to(device, non_blocking=True) for t in (h_row, h_col, h_val))
+            shard = psd.build_partitioned(r, c, v, (M, N), fill_cache=True, transpose=False)
+            return shard.tensor.storage.rowptr()[-1:].cpu()
+        h2d = sum(t.numel() * t.element_size() for t in (h_row, h_col, h_val))
+        e2e_step()
+        e2e_ms, _ = timed(e2e_step, max(args.steps // 2, 2))
+        e2e = {"value": units_per_step / (e2e_ms * 1e-3), "unit": "nnz/s", "h2d_bytes_per_step": h2d * world,
+               "d2h_bytes_per_step": 8 * world, "ms_per_step": e2e_ms}
         nnz_out = None
+        shard = out
+        sent = torch.tensor([shard.sent, shard.received], device=device, dtype=torch.float64)
+        dist.all_reduce(sent, op=dist.ReduceOp.MAX)
 
     line = {
         "metric": "coalesce+CSR/CSC build nnz/s", "value": value, "unit": "nnz/s", "n_gpus": world,
@@ -314,6 +329,19 @@ def run_ours(args):
                 "value": CPU_SAMPLE_NNZ / dt, "unit": "nnz/s", "cores": 1, "kind": kind,
                 "sample": f"first {CPU_SAMPLE_NNZ} entries of the same stream at full sparse sizes, one pass ({dt:.1f} s)",
                 "host_cores_available": os.cpu_count()}
+    if world > 1:
+        # SURVEY.md 8e combined roofline: local figure-A bytes / HBM peak + bytes sent per GPU / NVLink (770 GB/s
+        # measured peer copy per direction, B200_PROFILING.md; 900 nominal)
+        local_bytes = PIPELINE_LOCAL_BYTES_PER_NNZ * float(sent[1])
+        sent_bytes = 20.0 * float(sent[0])
+        t_roof_ms = (local_bytes / (hbm_peak * 1e9) + sent_bytes / 770e9) * 1e3
+        line["roofline"] = {
+            "bound": "hbm", "kernel": "partitioned build (exchange + local pipeline)", "achieved": None, "peak": hbm_peak,
+            "unit": "GB/s", "frac": t_roof_ms / ms, "traffic": None, "peak_source": peak_src,
+            "t_roof_ms": t_roof_ms, "max_tuples_sent_per_gpu": int(sent[0]), "max_tuples_received_per_gpu": int(sent[1]),
+            "nvlink_GBps_per_direction": 770.0,
+            "note": "frac = (local figure-A bytes / HBM peak + bytes sent / NVLink peak) / measured step time",
+        }
     if rank == 0:
         print(json.dumps(line))
     if world > 1:

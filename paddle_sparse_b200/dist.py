@@ -1,0 +1,125 @@
+"""Row-range-partitioned build for matrices that span several GPUs of one NVSwitch box.
+
+The reference has no distributed code; this is the sample sort named by the north star:
+
+  1. every rank histograms its local tuples over coarse row buckets            (ps_dist_row_histogram)
+  2. all-reduce of the histogram; identical, nnz-balanced, ROW-ALIGNED splitters on every rank
+  3. stable partition of the local tuples by destination rank                  (ps_dist_partition)
+  4. ONE all-to-all-v over NCCL / NVLink (counts first, then row, col, value)
+  5. shard-local coalesce + CSR/CSC build on local row ids                     (ps_coalesce, SparseStorage)
+
+Duplicates of a key always meet on the rank that owns the row, so dedup, rowptr, row reductions and
+row/col-broadcast mul need no further communication.  One process per GPU (torch.distributed).
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Optional, Tuple
+
+import torch
+import torch.distributed as dist
+
+MAX_BUCKETS = 32768  # histogram counters live in shared memory (128 KB) up to this many buckets
+
+
+def bucket_shift(M: int, max_buckets: int = MAX_BUCKETS) -> Tuple[int, int]:
+    """Smallest shift s such that ceil(M / 2^s) <= max_buckets.  Returns (shift, buckets)."""
+    shift = 0
+    while ((M + (1 << shift) - 1) >> shift) > max_buckets:
+        shift += 1
+    return shift, max((M + (1 << shift) - 1) >> shift, 1)
+
+
+def choose_splitters(hist: torch.Tensor, G: int, shift: int, M: int) -> torch.Tensor:
+    """Row-aligned splitters r_0 = 0 <= r_1 <= ... <= r_G = M balancing nnz: r_g is the first bucket
+    boundary at which the running count reaches g * total / G.  Deterministic given the (all-reduced)
+    histogram, so every rank computes the same answer without another exchange."""
+    h = hist.to("cpu", torch.int64)
+    cum = torch.cumsum(h, 0)
+    total = int(cum[-1]) if cum.numel() else 0
+    targets = torch.tensor([(total * g + G - 1) // G for g in range(1, G)], dtype=torch.int64)
+    # first bucket b with cum[b] >= target  ->  boundary after bucket b
+    idx = torch.searchsorted(cum, targets, right=False) + 1 if G > 1 else targets
+    rows = torch.clamp(idx << shift, max=M)
+    out = torch.empty(G + 1, dtype=torch.int64)
+    out[0], out[G] = 0, M
+    if G > 1:
+        out[1:G] = rows
+    return torch.cummax(out, 0)[0]
+
+
+@dataclass
+class RowShard:
+    """The rows [row_start, row_end) of the global matrix as a local SparseTensor with LOCAL row ids."""
+    tensor: "object"
+    row_start: int
+    row_end: int
+    sparse_sizes: Tuple[int, int]
+    splitters: torch.Tensor
+    sent: int = 0      # tuples this rank sent to other ranks
+    received: int = 0  # tuples this rank received (including its own)
+    transposed: "object" = None  # local N x rows transpose (column ids global) when requested
+
+    def global_row(self) -> torch.Tensor:
+        from . import ops
+        return ops.add_scalar(self.tensor.storage.row(), self.row_start)
+
+
+def exchange(row, col, value, counts: torch.Tensor, group=None):
+    """all-to-all-v of the destination-grouped tuples: counts first, then one collective per array."""
+    G = dist.get_world_size(group)
+    send_counts = counts.to(torch.int64)
+    recv_counts = torch.empty_like(send_counts)
+    dist.all_to_all_single(recv_counts, send_counts, group=group)
+    s = send_counts.tolist() if send_counts.device.type == "cpu" else send_counts.cpu().tolist()
+    r = recv_counts.tolist() if recv_counts.device.type == "cpu" else recv_counts.cpu().tolist()
+    n_recv = int(sum(r))
+
+    def a2a(x):
+        if x is None:
+            return None
+        out = torch.empty((n_recv,) + tuple(x.shape[1:]), dtype=x.dtype, device=x.device)
+        dist.all_to_all_single(out, x.contiguous(), output_split_sizes=r, input_split_sizes=s, group=group)
+        return out
+
+    rank = dist.get_rank(group)
+    sent = int(sum(s)) - int(s[rank])
+    return a2a(row), a2a(col), a2a(value), sent, n_recv, G
+
+
+def route_tuples(row, col, value, sparse_sizes, group=None, _ops=None):
+    """Steps 1-4: returns (row, col, value) of the tuples this rank owns (GLOBAL row ids, arrival order:
+    grouped by source rank, source order kept) plus (splitters, sent, received).  `_ops` lets the CPU
+    (gloo) tests drive this host logic with stand-in kernels; the product path uses the CUDA operators."""
+    if _ops is None:
+        from . import ops as _ops
+    M = int(sparse_sizes[0])
+    G = dist.get_world_size(group)
+    shift, buckets = bucket_shift(M)
+    hist = _ops.dist_row_histogram(row, shift, buckets)
+    dist.all_reduce(hist, op=dist.ReduceOp.SUM, group=group)
+    splitters = choose_splitters(hist, G, shift, M)
+    p_row, p_col, p_val, counts = _ops.dist_partition(row, col, value, splitters.to(row.device))
+    r_row, r_col, r_val, sent, n_recv, _ = exchange(p_row, p_col, p_val, counts, group)
+    return r_row, r_col, r_val, splitters, sent, n_recv
+
+
+def build_partitioned(row, col, value, sparse_sizes, group=None, reduce: str = "add", fill_cache: bool = True,
+                      transpose: bool = False) -> RowShard:
+    """Build this rank's row shard of the coalesced matrix from its local, unsorted tuples."""
+    from . import ops
+    from .tensor import SparseTensor
+    M, N = int(sparse_sizes[0]), int(sparse_sizes[1])
+    rank = dist.get_rank(group)
+    r_row, r_col, r_val, splitters, sent, n_recv = route_tuples(row, col, value, (M, N), group)
+    r0, r1 = int(splitters[rank]), int(splitters[rank + 1])
+    local_row = ops.add_scalar(r_row, -r0) if r0 else r_row
+    c_row, c_col, c_val = ops.coalesce(local_row, r_col, r_val, max(r1 - r0, 0), N, reduce)
+    A = SparseTensor(row=c_row, col=c_col, value=c_val, sparse_sizes=(max(r1 - r0, 0), N), is_sorted=True,
+                     trust_data=True)
+    if fill_cache:
+        A.fill_cache_()
+    At = A.t() if transpose else None
+    shard = RowShard(A, r0, r1, (M, N), splitters, sent, n_recv)
+    shard.transposed = At
+    return shard
