@@ -16,6 +16,7 @@ from .reduce import sum, mean, min, max, reduction  # noqa: E402,A004
 from .mul import mul, mul_, mul_nnz, mul_nnz_  # noqa: E402
 from .index_select import index_select, index_select_nnz  # noqa: E402
 from .masked_select import masked_select, masked_select_nnz  # noqa: E402
+from .narrow import narrow, select  # noqa: E402
 from .sample import sample, sample_adj, manual_seed  # noqa: E402
 
 __version__ = "0.1.0"
@@ -24,5 +25,5 @@ cuda_version = int(ops.sparse_cuda_version()[0])  # paddle_sparse/__init__.py:17
 __all__ = [
     "SparseStorage", "SparseTensor", "coalesce", "t", "transpose", "sum", "mean", "min", "max", "reduction",
     "mul", "mul_", "mul_nnz", "mul_nnz_", "index_select", "index_select_nnz", "masked_select",
-    "masked_select_nnz", "sample", "sample_adj", "manual_seed", "ops", "__version__",
+    "masked_select_nnz", "narrow", "select", "sample", "sample_adj", "manual_seed", "ops", "__version__",
 ]

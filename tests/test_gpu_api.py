@@ -274,6 +274,8 @@ def test_getitem_and_to_dense(ps):
     idx = dev(np.array([3, 1, 3, 7], I64))
     assert np.array_equal(host(A[idx].to_dense()), mat.astype(np.float32)[[3, 1, 3, 7]])
     assert np.array_equal(host(A[:, idx].to_dense()), mat.astype(np.float32)[:, [3, 1, 3, 7]])
+    assert np.array_equal(host(A[5:17, -9:].to_dense()), mat.astype(np.float32)[5:17, -9:])
+    assert np.array_equal(host(A[3].to_dense()), mat.astype(np.float32)[3:4])
     m = dev(rng.random(50) < 0.5)
     assert np.array_equal(host(A[m].to_dense()), mat.astype(np.float32)[host(m)])
     assert A == A.clone() and not (A == A.t())
