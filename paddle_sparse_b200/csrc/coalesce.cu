@@ -191,7 +191,7 @@ int sort_impl(const int64_t *row, const int64_t *col, int64_t nnz, KeyGeom g, co
   PS_SCRATCH(k1, scratch, KeyT, nnz);
   PS_SCRATCH(p0, scratch, uint32_t, nnz);
   PS_SCRATCH(p1, scratch, uint32_t, nnz);
-  const int passes = make_sort_plan(g.bits).passes;
+  const int passes = rs_num_passes<KeyT>(g.bits);
   KeySrc ksrc{row, col, KSRC_PACK_COO, g.cbits};
   PaySrc psrc = fast ? PaySrc{value, pay_src_mode(dtype)} : PaySrc{nullptr, PSRC_IOTA};
 
@@ -247,6 +247,19 @@ int sort_impl(const int64_t *row, const int64_t *col, int64_t nnz, KeyGeom g, co
 using namespace ps;
 
 extern "C" {
+
+// debug builds (make TIMELINE=1): cycles thread 0 of every radix-pass CTA of the COO sort spent per phase; resets
+int ps_debug_timeline(unsigned long long *out16) {
+#ifdef PS_RS_TIMELINE
+  unsigned long long z[16] = {0};
+  if (cudaMemcpyFromSymbol(out16, ps::g_rs_timeline, sizeof(z)) != cudaSuccess) return PS_ERR_CUDA;
+  if (cudaMemcpyToSymbol(ps::g_rs_timeline, z, sizeof(z)) != cudaSuccess) return PS_ERR_CUDA;
+  return PS_OK;
+#else
+  (void)out16;
+  return PS_ERR_ARG;
+#endif
+}
 
 int ps_sort_coo(const int64_t *row, const int64_t *col, int64_t nnz, int64_t M, int64_t N, const void *value,
                 int dtype, int64_t width, int64_t *out_row, int64_t *out_col, void *out_value, int64_t *out_perm,

@@ -66,7 +66,7 @@ int ps_csr2csc(const int64_t *col, int64_t nnz, int64_t N, int64_t *out_csr2csc,
   PS_SCRATCH(k1, scratch, uint32_t, nnz);
   PS_SCRATCH(p0, scratch, uint32_t, nnz);
   PS_SCRATCH(p1, scratch, uint32_t, nnz);
-  const int passes = make_sort_plan(cbits).passes;
+  const int passes = rs_num_passes<uint32_t>(cbits);
   uint32_t *sorted_col = (passes & 1) ? k0 : k1;
   KeyDst kd = want_ptr ? KeyDst{sorted_col, nullptr, KDST_KEYS, 0} : KeyDst{nullptr, nullptr, KDST_NONE, 0};
   PS_TRY(radix_sort_pairs<uint32_t>(KeySrc{col, nullptr, KSRC_I64, 0}, PaySrc{nullptr, PSRC_IOTA}, nnz, cbits, k0, k1,

@@ -47,7 +47,9 @@ def main():
     row, col, val = ops.synth_coo(0x5EED0002, 0, NNZ, M, N, "cuda")
     print("variant", os.environ.get("PS_RS_VARIANT", "0"))
     if what & {"sort", "all"}:
+        timeline("(reset)")
         timeit("sort_coo", lambda: ops.sort_coo(row, col, val, M, N))
+        timeline("sort_coo")
     if what & {"coalesce", "all"}:
         timeit("coalesce", lambda: ops.coalesce(row, col, val, M, N))
     if what & {"csc", "all"}:
@@ -57,6 +59,18 @@ def main():
         timeit("invert_perm", lambda: ops.invert_perm(perm))
         timeit("transpose_gather", lambda: ops.transpose_gather(perm, r, c, v, colptr, N))
         timeit("ind2ptr", lambda: ops.ind2ptr(r, M))
+
+
+def timeline(label):
+    """debug builds (make TIMELINE=1): share of CTA time per phase of the radix pass"""
+    buf = (ctypes.c_ulonglong * 16)()
+    if lib.ps_debug_timeline(buf) != 0:
+        return
+    names = ["loop top", "B0 wait (ticket, prev scatter)", "keys+rank", "B1 wait", "digit phase+scan", "B3 wait",
+             "positions+staging", "look-back", "B5 wait", "scatter"]
+    tot = float(sum(buf[:10])) or 1.0
+    print(label, "timeline:", ", ".join(f"{n} {100 * buf[i] / tot:.1f}%" for i, n in enumerate(names)),
+          f"| total {tot / 1e6:.1f} Mcycles", flush=True)
 
 
 if __name__ == "__main__":
