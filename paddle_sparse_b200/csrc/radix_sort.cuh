@@ -151,18 +151,21 @@ struct RsState {
 template <int NPAY> struct PaySrcN { PaySrc s[NPAY > 0 ? NPAY : 1]; };
 template <int NPAY> struct PayDstN { PayDst d[NPAY > 0 ? NPAY : 1]; };
 
-template <typename KeyT, int NPAY, int RBITS, int THREADS, int ITEMS>
+// Shared memory of one CTA.  The register file holds the tile in ARRIVAL order (ITEMS keys per thread), shared
+// memory holds it in SORTED order; u32 payload words of the NEXT tile land in pay_in (cp.async) meanwhile.
+template <typename KeyT, int NPAY, int RBITS, int THREADS, int ITEMS, bool PREFETCH>
 struct RsSmem {
   static constexpr int TILE = THREADS * ITEMS;
   static constexpr int WARPS = THREADS / 32;
   static constexpr int RADIX = 1 << RBITS;
-  KeyT keys[TILE];                         // tile in sorted order
-  uint32_t pay[NPAY > 0 ? NPAY : 1][TILE];  // arrival order (cp.async prefetch), then sorted order
-  uint32_t cnt[WARPS][RADIX];              // items of the (warp, digit) group
-  uint16_t base[WARPS][RADIX];             // start of the (warp, digit) group inside the sorted tile
-  uint32_t gbase[RADIX];                   // global position of the digit's run minus its tile offset
+  static constexpr int ROW = RADIX / 2 + 1;  // counter row in 32-bit words: odd stride, so a column read is conflict-free
+  KeyT keys[TILE];
+  uint32_t pay[NPAY > 0 ? NPAY : 1][TILE];
+  uint32_t pay_in[(PREFETCH && NPAY > 0) ? NPAY : 1][(PREFETCH && NPAY > 0) ? TILE : 1];
+  uint32_t cnt[WARPS][ROW];  // two 16-bit counters per word: items of (warp, digit); later the group's start in the tile
+  uint32_t gbase[RADIX];     // global position of the digit's run minus its offset inside the tile
   uint32_t scan_tmp[32];
-  long long tile;
+  long long tile_next;
 };
 
 __device__ __forceinline__ void cp_async4(void *smem_dst, const void *gsrc) {
@@ -237,56 +240,45 @@ __device__ __forceinline__ void load_tile_pay_sync(const PaySrc &s, int64_t tile
   }
 }
 
-// ---- decoupled look-back for one digit: w[] holds the words of tiles t0, t0-1, ... (loaded early so
-// the round trip overlaps the staging phase); tiles before 0 read as "prefix 0"
-template <int LB>
-__device__ __forceinline__ void rs_lb_load(const uint64_t *stw, int radix, int64_t t0, int epoch, uint64_t (&w)[LB]) {
-#pragma unroll
-  for (int q = 0; q < LB; ++q)
-    w[q] = (t0 - q >= 0) ? TileState::load(stw + (t0 - q) * radix) : RsState::pack(epoch, RsState::PREFIX, 0);
+// ---- decoupled look-back, warp-cooperative: the 32 / DPW lanes {k, k + DPW, ...} of a warp serve digit k of the
+// warp together.  Lane (k, r) loads the word of tile t - r (one register pair per lane instead of a window per
+// digit thread); the words are exchanged by shuffles and every lane of the group tracks the same walk state.
+// The first words are loaded EARLY (phase 3) so their round trip overlaps the staging phase; later rounds read
+// two words per lane.  Tiles before 0 read as "prefix 0".
+__device__ __forceinline__ uint64_t rs_lb_word(const uint64_t *stw, int radix, int64_t t, int epoch) {
+  return t >= 0 ? TileState::load(stw + t * radix) : RsState::pack(epoch, RsState::PREFIX, 0);
 }
-// The walk continues LB2 tiles per round trip: the prefix frontier trails the newest aggregate by roughly
-// (L2 round trip / tile period) tiles, so later rounds must cover many tiles at once to keep up.
-template <int LB, int LB2>
-__device__ __forceinline__ uint32_t rs_lb_finish(const uint64_t *stw, int radix, int64_t tile, int epoch,
-                                                 uint64_t (&w)[LB]) {
+template <int DPW>
+__device__ __forceinline__ uint32_t rs_lb_finish(const uint64_t *stw, int radix, int64_t tile, int epoch, uint64_t w0,
+                                                 unsigned lane) {
+  constexpr int GS = 32 / DPW;
+  const unsigned lk = lane % DPW, lr = lane / DPW;
   uint64_t excl = 0;
-  int64_t t = tile - 1;
-  {
-    int q = 0;
+  int64_t t = tile - 1;  // next tile to consume
+  bool done = false, stuck = false;
+  auto consume = [&](uint64_t w) {
+    if (done || stuck) return;
+    if (RsState::epoch(w) != (uint64_t)epoch) { stuck = true; return; }  // not published in this pass yet
+    excl += RsState::value(w);
+    --t;
+    if (RsState::status(w) == RsState::PREFIX) done = true;
+  };
 #pragma unroll
-    for (; q < LB; ++q) {
-      if (RsState::epoch(w[q]) != (uint64_t)epoch) break;  // not published in this pass yet: resume here
-      excl += RsState::value(w[q]);
-      if (RsState::status(w[q]) == RsState::PREFIX) return (uint32_t)excl;
-    }
-    t -= q;
-  }
-  uint64_t v[LB2];
-  while (true) {
-    rs_lb_load<LB2>(stw, radix, t, epoch, v);
-    int q = 0;
+  for (int r = 0; r < GS; ++r) consume(__shfl_sync(0xffffffffu, w0, lk + r * DPW));
+  while (!__all_sync(0xffffffffu, done)) {
+    const uint64_t u0 = done ? 0 : rs_lb_word(stw, radix, t - (int64_t)lr, epoch);
+    const uint64_t u1 = done ? 0 : rs_lb_word(stw, radix, t - (int64_t)lr - GS, epoch);
+    stuck = false;
 #pragma unroll
-    for (; q < LB2; ++q) {
-      if (RsState::epoch(v[q]) != (uint64_t)epoch) break;
-      excl += RsState::value(v[q]);
-      if (RsState::status(v[q]) == RsState::PREFIX) return (uint32_t)excl;
-    }
-    t -= q;
+    for (int r = 0; r < GS; ++r) consume(__shfl_sync(0xffffffffu, u0, lk + r * DPW));
+#pragma unroll
+    for (int r = 0; r < GS; ++r) consume(__shfl_sync(0xffffffffu, u1, lk + r * DPW));
   }
+  return (uint32_t)excl;
 }
 
-// One tile = THREADS * ITEMS pairs; CTAs are persistent and draw tiles from an atomic ticket (the next
-// ticket is requested while the current tile is processed).  Phases per tile:
-//   1 keys -> registers (all loads in flight); u32 payload words start moving to shared memory (cp.async)
-//   2 rank inside the warp: one shared-memory atomicAdd per item on warp-private digit counters
-//   3 digit totals -> the tile's aggregate is PUBLISHED EARLY and the first look-back words are requested;
-//     block scan of the totals gives every (warp, digit) group its start inside the sorted tile
-//   4 position of every item inside the sorted tile
-//   5 stage pairs in tile-sorted order; finish the decoupled look-back
-//   6 coalesced scatter of contiguous per-digit runs
-// PS_RS_TIMELINE (debug builds only): thread 0 of every CTA accumulates the SM cycles it spends between
-// phase markers; ps_debug_timeline() reads the totals.
+// PS_RS_TIMELINE (debug builds, make TIMELINE=1): thread 0 of every CTA accumulates the SM cycles it spends
+// between phase markers; ps_debug_timeline() reads the totals.
 #ifdef PS_RS_TIMELINE
 static __device__ unsigned long long g_rs_timeline[16];  // one copy per translation unit
 #define PS_TL_DECL long long tl_prev = clock64(); unsigned long long tl_acc[12] = {0}
@@ -298,148 +290,165 @@ static __device__ unsigned long long g_rs_timeline[16];  // one copy per transla
 #define PS_TL_FLUSH
 #endif
 
-template <typename KeyT, int NPAY, int RBITS, int THREADS, int ITEMS, int MIN_BLOCKS>
-__global__ void __launch_bounds__(THREADS, MIN_BLOCKS)
+// One tile = THREADS * ITEMS tuples, ONE persistent CTA per SM.  Why so large: the scatter of a pass writes
+// RADIX interleaved streams in runs of TILE / RADIX elements, and the HBM/L2 path of a B200 only approaches
+// streaming speed when those runs are >= ~48 elements (tools/microbench/scatter_bw.cu: runs of 12 -> 2.0 TB/s,
+// 24 -> 3.0, 48 -> 4.1, 96 -> 4.5, streaming copy 5.5).  The register file holds the tile in arrival order, shared
+// memory holds it in sorted order.  Tiles come from an atomic ticket; the loop is software-pipelined: the
+// NEXT tile's key loads (and cp.async payload) are issued as soon as the current tile is staged, so their
+// latency overlaps the look-back and the scatter.  Phases per tile:
+//   2 rank: ONE shared-memory atomicAdd per item on warp-private 16-bit digit counters returns the item's rank
+//     inside its (warp, digit) group
+//   3 every warp scans RADIX / WARPS digit columns across the warps (lane = warp index); lanes < RADIX / WARPS
+//     own one digit each: they PUBLISH the tile's aggregate early and request the first look-back words; a block
+//     scan of the digit totals turns the counters into group starts inside the sorted tile
+//   4 position of every item; stage tuples in tile-sorted order; request the next tile
+//   5 finish the decoupled look-back
+//   6 coalesced scatter of contiguous per-digit runs
+template <typename KeyT, int NPAY, int RBITS, int THREADS, int ITEMS, bool PREFETCH>
+__global__ void __launch_bounds__(THREADS, 1024 / THREADS)
 rs_pass_kernel(KeySrc ksrc, PaySrcN<NPAY> psrc, KeyDst kdst, PayDstN<NPAY> pdst, int64_t n, int64_t tiles,
                int begin_bit, int num_bits, int epoch, const unsigned long long *__restrict__ bin_base,
                uint64_t *__restrict__ tile_state /*[tiles][RADIX]*/, unsigned long long *ticket) {
-  using Smem = RsSmem<KeyT, NPAY, RBITS, THREADS, ITEMS>;
+  using Smem = RsSmem<KeyT, NPAY, RBITS, THREADS, ITEMS, PREFETCH>;
   constexpr int TILE = Smem::TILE, WARPS = Smem::WARPS, RADIX = Smem::RADIX;
-  constexpr int DPT = RADIX > THREADS ? RADIX / THREADS : 1;  // consecutive digits owned by a digit thread
-  constexpr int LB = DPT == 1 ? 4 : 2, LB2 = 16 / DPT;
-  static_assert(RADIX % (THREADS < RADIX ? THREADS : RADIX) == 0, "THREADS must divide the radix (or exceed it)");
-  static_assert(TILE < 65536, "group starts are kept in 16 bits");
+  constexpr int DPW = RADIX / WARPS;  // digit columns scanned by one warp; lane k < DPW owns digit warp*DPW + k
+  static_assert(RADIX % WARPS == 0 && DPW <= 32, "one warp scans RADIX / WARPS digit columns");
+  static_assert(32 * ITEMS < 65536 && TILE < 65536, "counters and group starts are kept in 16 bits");
   extern __shared__ __align__(16) unsigned char smem_raw[];
   Smem &sm = *reinterpret_cast<Smem *>(smem_raw);
 
   const unsigned tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
   const unsigned mask = (1u << num_bits) - 1u;
-  const unsigned lt = lanemask_lt();
   const int warp_base = warp * (32 * ITEMS);
   uint32_t *my_cnt = sm.cnt[warp];
-  const uint16_t *my_base = sm.base[warp];
-  const bool digit_thread = (int)tid * DPT < RADIX;
-  const int d0 = digit_thread ? tid * DPT : 0;  // first digit this thread owns
-  uint64_t *stw = tile_state + d0;               // word of (tile t, digit d0 + q) at stw[t * RADIX + q]
-  uint32_t bin0[DPT];
-#pragma unroll
-  for (int q = 0; q < DPT; ++q) bin0[q] = (uint32_t)bin_base[d0 + q];
+  const bool digit_thread = lane < (unsigned)DPW;  // lane k < DPW owns digit warp*DPW + k; lanes k + r*DPW assist
+  const int my_digit = warp * DPW + lane % DPW;
+  uint64_t *stw = tile_state + my_digit;  // word of (tile t, my digit) at stw[t * RADIX]
+  const uint32_t bin0 = (uint32_t)bin_base[my_digit];
 
-  long long next_tile = 0;
-  if (tid == 0) next_tile = (long long)atomicAdd(ticket, 1ull);
-  PS_TL_DECL;
-  while (true) {
-    if (tid == 0) sm.tile = next_tile;
-    PS_TL(0);
-    __syncthreads();  // also: every read of the previous tile's staged pairs is done
-    PS_TL(1);
-    const int64_t tile = sm.tile;
-    if (tile >= tiles) break;
-    if (tid == 0) next_tile = (long long)atomicAdd(ticket, 1ull);  // consumed at the top of the next round
-    const int64_t tile_base = tile * TILE;
-    const int tile_n = (int)((n - tile_base) < TILE ? (n - tile_base) : TILE);
-
-    // ---- 1: keys (padding keys are all-ones: the largest digit, ranked last); payload prefetch
-    KeyT key[ITEMS];
-    load_tile_keys<KeyT, ITEMS>(ksrc, tile_base, warp_base, lane, tile_n, key);
-    if (NPAY > 0) {
+  // request one tile: keys into registers, u32 payload words towards pay_in
+  KeyT key[ITEMS];
+  auto request = [&](int64_t t) {
+    const int64_t tb = t * TILE;
+    const int tn = (int)((n - tb) < TILE ? (n - tb) : TILE);
+    load_tile_keys<KeyT, ITEMS>(ksrc, tb, warp_base, lane, tn, key);
+    if (PREFETCH && NPAY > 0) {
 #pragma unroll
       for (int p = 0; p < NPAY; ++p) {
         if (psrc.s[p].mode == PSRC_U32) {
-          const uint32_t *src = reinterpret_cast<const uint32_t *>(psrc.s[p].p) + tile_base;
+          const uint32_t *src = reinterpret_cast<const uint32_t *>(psrc.s[p].p) + tb;
 #pragma unroll
           for (int i = 0; i < ITEMS; ++i) {
             const int j = warp_base + i * 32 + lane;
-            if (j < tile_n) cp_async4(&sm.pay[p][j], src + j);
+            if (j < tn) cp_async4(&sm.pay_in[p][j], src + j);
           }
         }
       }
       cp_async_commit();
     }
+  };
+
+  long long ticket_ahead = 0;  // thread 0: the ticket drawn one tile ahead
+  if (tid == 0) sm.tile_next = (long long)atomicAdd(ticket, 1ull);
+  __syncthreads();
+  int64_t tile = sm.tile_next;
+  if (tile < tiles) request(tile);
+  if (tid == 0) ticket_ahead = (long long)atomicAdd(ticket, 1ull);
+  PS_TL_DECL;
+
+  while (tile < tiles) {
+    const int64_t tile_base = tile * TILE;
+    const int tile_n = (int)((n - tile_base) < TILE ? (n - tile_base) : TILE);
+    PS_TL(0);
 #pragma unroll
-    for (int q = lane; q < RADIX; q += 32) my_cnt[q] = 0;
+    for (int q = lane; q < Smem::ROW; q += 32) my_cnt[q] = 0;
     __syncwarp();
 
-    // ---- 2: rank inside the warp (stable): set s covers rounds [s*SI, (s+1)*SI) and owns byte s
-    // One shared-memory atomic per item returns the item's rank inside its (warp, digit) group.  Stability
-    // needs the lanes of ONE instruction that hit the same counter to be served in ascending lane order:
-    // that is how ATOMS behaves on sm_100a (tools/microbench/atom_order.cu: 6e10 lane-instances under every
-    // collision / bank-conflict pattern, none out of order; rank_bench.cu: 2 SM-cycles per warp instruction
-    // against 40 for MATCH.ANY and 17 for eight ballots) and ps_selftest() re-checks it on the device in use.
+    // ---- 2: rank.  Stability needs the lanes of ONE atomic instruction that hit the same counter to be served
+    // in ascending lane order: that is how ATOMS behaves on sm_100a (tools/microbench/atom_order.cu: 6e10
+    // lane-instances under every collision / bank-conflict pattern, none out of order; rank_bench.cu: ~2 SM
+    // cycles per warp instruction against 40 for MATCH.ANY and 17 for eight ballots).  Padding keys of a partial
+    // tile are all-ones: the largest digit, and ranked last inside it.
     unsigned rank[ITEMS];
 #pragma unroll
-    for (int i = 0; i < ITEMS; ++i) rank[i] = atomicAdd(&my_cnt[(unsigned)(key[i] >> begin_bit) & mask], 1u);
-    PS_TL(2);
-    __syncthreads();
-    PS_TL(3);
-
-    // ---- 3: per digit: exclusive prefix over warps, tile total; publish the aggregate right away
-    uint32_t tot[DPT];
-    uint64_t lbw[DPT][LB];
-#pragma unroll
-    for (int q = 0; q < DPT; ++q) tot[q] = 0;
-    if (digit_thread) {
-#pragma unroll
-      for (int q = 0; q < DPT; ++q) {
-        uint32_t t = 0;
-#pragma unroll
-        for (int w = 0; w < WARPS; ++w) t += sm.cnt[w][d0 + q];
-        tot[q] = t;
-        TileState::store(stw + tile * RADIX + q, RsState::pack(epoch, tile == 0 ? RsState::PREFIX : RsState::AGG, t));
-      }
-#pragma unroll
-      for (int q = 0; q < DPT; ++q) rs_lb_load<LB>(stw + q, RADIX, tile - 1, epoch, lbw[q]);
+    for (int i = 0; i < ITEMS; ++i) {
+      const unsigned d = (unsigned)(key[i] >> begin_bit) & mask;
+      const unsigned sh = (d & 1u) * 16u;
+      rank[i] = (atomicAdd(&my_cnt[d >> 1], 1u << sh) >> sh) & 0xffffu;
     }
-    uint32_t dexcl;  // tile-exclusive start of digit d0
+    PS_TL(1);
+    __syncthreads();
+    PS_TL(2);
+
+    // ---- 3: column scans.  Lane l reads the counter of warp l for each of this warp's DPW digits.
+    uint32_t tot = 0;       // digit threads: total of my digit in this tile
+    uint32_t wsum = 0;      // all lanes: total of this warp's DPW digits
+    uint32_t below = 0;     // digit threads: total of this warp's digits below mine
+    uint16_t *col = reinterpret_cast<uint16_t *>(&sm.cnt[lane < (unsigned)WARPS ? lane : 0][0]) + warp * DPW;
     {
-      uint32_t tsum = 0;
 #pragma unroll
-      for (int q = 0; q < DPT; ++q) tsum += tot[q];
-      uint32_t inc = tsum;
+      for (int k = 0; k < DPW; ++k) {
+        const uint32_t c = lane < (unsigned)WARPS ? (uint32_t)col[k] : 0u;
+        uint32_t inc = c;
 #pragma unroll
-      for (int d = 1; d < 32; d <<= 1) {
-        const uint32_t o = __shfl_up_sync(0xffffffffu, inc, d);
-        if (lane >= (unsigned)d) inc += o;
+        for (int d = 1; d < 32; d <<= 1) {
+          const uint32_t o = __shfl_up_sync(0xffffffffu, inc, d);
+          if (lane >= (unsigned)d) inc += o;
+        }
+        if (lane < (unsigned)WARPS) col[k] = (uint16_t)(inc - c);  // items of digit k in warps < l
+        const uint32_t t = __shfl_sync(0xffffffffu, inc, 31);
+        if (lane == (unsigned)k) { tot = t; below = wsum; }
+        wsum += t;
       }
-      if (lane == 31) sm.scan_tmp[warp] = inc;
-      __syncthreads();
+    }
+    if (digit_thread)
+      TileState::store(stw + tile * RADIX, RsState::pack(epoch, tile == 0 ? RsState::PREFIX : RsState::AGG, tot));
+    const uint64_t lbw = rs_lb_word(stw, RADIX, tile - 1 - (int64_t)(lane / DPW), epoch);
+    if (lane == 0) sm.scan_tmp[warp] = wsum;
+    __syncthreads();
+    uint32_t dexcl;  // digit threads: offset of my digit inside the sorted tile
+    {
       uint32_t wb = 0;
 #pragma unroll
       for (int w = 0; w < WARPS; ++w) wb += (w < (int)warp) ? sm.scan_tmp[w] : 0u;
-      dexcl = wb + inc - tsum;
-    }
-    if (digit_thread) {
-      uint32_t dx = dexcl;  // second sweep over the warp counters (cheaper than holding the prefixes in registers)
+      dexcl = wb + below;
+      // group start of (warp l, digit k) = start of digit k + items of digit k in warps < l
 #pragma unroll
-      for (int q = 0; q < DPT; ++q) {
-#pragma unroll
-        for (int w = 0; w < WARPS; ++w) {
-          sm.base[w][d0 + q] = (uint16_t)dx;
-          dx += sm.cnt[w][d0 + q];
-        }
+      for (int k = 0; k < DPW; ++k) {
+        const uint32_t dk = __shfl_sync(0xffffffffu, dexcl, k);
+        if (lane < (unsigned)WARPS) col[k] = (uint16_t)(dk + col[k]);
       }
     }
-    PS_TL(4);
+    if (tid == 0) sm.tile_next = ticket_ahead;
+    PS_TL(3);
     __syncthreads();
-    PS_TL(5);
+    PS_TL(4);
 
-    // ---- 4: position inside the sorted tile = group start + rank inside the group
+    // ---- 4: position inside the sorted tile = group start + rank inside the group; stage
+    {
+      const uint16_t *my_start = reinterpret_cast<const uint16_t *>(my_cnt);
 #pragma unroll
-    for (int i = 0; i < ITEMS; ++i) rank[i] += (unsigned)my_base[(unsigned)(key[i] >> begin_bit) & mask];
-
-    // ---- 5: stage in tile-sorted order
+      for (int i = 0; i < ITEMS; ++i) rank[i] += (unsigned)my_start[(unsigned)(key[i] >> begin_bit) & mask];
+    }
 #pragma unroll
     for (int i = 0; i < ITEMS; ++i) sm.keys[rank[i]] = key[i];
+    PS_TL(10);
     if (NPAY > 0) {
-      cp_async_wait_all();
+      if (PREFETCH) cp_async_wait_all();
 #pragma unroll
       for (int p = 0; p < NPAY; ++p) {
         uint32_t pv[ITEMS];
-        const bool prefetched = psrc.s[p].mode == PSRC_U32;
-        if (prefetched) {
+        if (PREFETCH && psrc.s[p].mode == PSRC_U32) {
 #pragma unroll
-          for (int i = 0; i < ITEMS; ++i) pv[i] = sm.pay[p][warp_base + i * 32 + lane];
-          __syncthreads();  // every arrival-order slot is read before sorted order overwrites it
+          for (int i = 0; i < ITEMS; ++i) pv[i] = sm.pay_in[p][warp_base + i * 32 + lane];
+        } else if (psrc.s[p].mode == PSRC_U32) {
+          const uint32_t *src = reinterpret_cast<const uint32_t *>(psrc.s[p].p) + tile_base;
+#pragma unroll
+          for (int i = 0; i < ITEMS; ++i) {
+            const int j = warp_base + i * 32 + lane;
+            pv[i] = j < tile_n ? ld_stream(src + j) : 0u;
+          }
         } else {
           load_tile_pay_sync<ITEMS>(psrc.s[p], tile_base, warp_base, lane, tile_n, pv);
         }
@@ -447,23 +456,24 @@ rs_pass_kernel(KeySrc ksrc, PaySrcN<NPAY> psrc, KeyDst kdst, PayDstN<NPAY> pdst,
         for (int i = 0; i < ITEMS; ++i) sm.pay[p][rank[i]] = pv[i];
       }
     }
-    PS_TL(6);
-    // look-back: the first words were requested in phase 3 and have usually arrived by now
-    if (digit_thread) {
-#pragma unroll
-      for (int q = 0; q < DPT; ++q) {
-        uint32_t excl = 0;
-        if (tile > 0) {
-          excl = rs_lb_finish<LB, LB2>(stw + q, RADIX, tile, epoch, lbw[q]);
-          TileState::store(stw + tile * RADIX + q, RsState::pack(epoch, RsState::PREFIX, (uint64_t)excl + tot[q]));
-        }
-        sm.gbase[d0 + q] = bin0[q] + excl - dexcl;
-        dexcl += tot[q];
+    PS_TL(5);
+    // ---- 5: look-back (the first words were requested in phase 3 and have usually arrived by now)
+    {
+      const uint32_t excl = rs_lb_finish<DPW>(stw, RADIX, tile, epoch, lbw, lane);  // tile 0: "prefix 0" at once
+      if (digit_thread) {
+        if (tile > 0) TileState::store(stw + tile * RADIX, RsState::pack(epoch, RsState::PREFIX, (uint64_t)excl + tot));
+        sm.gbase[my_digit] = bin0 + excl - dexcl;
       }
     }
-    PS_TL(7);
+    PS_TL(9);
+    // the registers are free again: request the next tile now, its latency hides behind look-back and scatter
+    const int64_t next = sm.tile_next;
+    if (next < tiles) request(next);
+    if (tid == 0) ticket_ahead = (long long)atomicAdd(ticket, 1ull);
+
+    PS_TL(6);
     __syncthreads();
-    PS_TL(8);
+    PS_TL(7);
 
     // ---- 6: coalesced scatter: consecutive staged slots of one digit go to consecutive addresses
     const bool full = tile_n == TILE;
@@ -472,7 +482,7 @@ rs_pass_kernel(KeySrc ksrc, PaySrcN<NPAY> psrc, KeyDst kdst, PayDstN<NPAY> pdst,
     for (int p = 0; p < NPAY; ++p) plain = plain && pdst.d[p].mode == PDST_U32;
     if (plain) {
       KeyT *ko = reinterpret_cast<KeyT *>(kdst.a);
-#pragma unroll
+#pragma unroll 4
       for (int k = 0; k < ITEMS; ++k) {
         const int j = k * THREADS + tid;
         if (full || j < tile_n) {
@@ -485,7 +495,7 @@ rs_pass_kernel(KeySrc ksrc, PaySrcN<NPAY> psrc, KeyDst kdst, PayDstN<NPAY> pdst,
         }
       }
     } else {
-#pragma unroll
+#pragma unroll 2
       for (int k = 0; k < ITEMS; ++k) {
         const int j = k * THREADS + tid;
         if (full || j < tile_n) {
@@ -498,35 +508,49 @@ rs_pass_kernel(KeySrc ksrc, PaySrcN<NPAY> psrc, KeyDst kdst, PayDstN<NPAY> pdst,
         }
       }
     }
-    PS_TL(9);
+    PS_TL(8);
+    tile = next;
   }
   PS_TL_FLUSH;
 }
 
 // ----------------------------------------------------------------------------- host driver
-// Geometry per key type (measured on B200, profiles/).  PS_RS_VARIANT (bench knob, read once) overrides.
+// Geometry: 1024 threads, one CTA per SM; ITEMS per (key type, payload words) chosen so the sorted tile, the
+// payload prefetch buffer and the counters fit the 227 KB of shared memory.  PS_RS_VARIANT (bench knob, read
+// once): 1 = 9-bit digits.
 int rs_variant();
+
+template <typename KeyT, int NPAY> struct RsGeom;
+template <> struct RsGeom<uint64_t, 1> { static constexpr int ITEMS = 12; static constexpr bool PREFETCH = true; };
+template <> struct RsGeom<uint32_t, 1> { static constexpr int ITEMS = 16; static constexpr bool PREFETCH = true; };
+template <> struct RsGeom<uint32_t, 3> { static constexpr int ITEMS = 12; static constexpr bool PREFETCH = false; };
+template <> struct RsGeom<uint64_t, 3> { static constexpr int ITEMS = 8; static constexpr bool PREFETCH = false; };
 
 struct RsGeomRt {
   int rbits, tile;
 };
+// variants (PS_RS_VARIANT): 0 = 1024 threads, one CTA per SM; 1 = 512 threads, two CTAs per SM; 2 = 0 with 9-bit digits
+template <typename KeyT, int NPAY>
+RsGeomRt rs_geometry() {
+  const int v = rs_variant();
+  return RsGeomRt{v == 2 ? 9 : 8, (v == 1 ? 512 : 1024) * RsGeom<KeyT, NPAY>::ITEMS};
+}
 
-template <typename KeyT, int NPAY, int RBITS, int THREADS, int ITEMS, int MIN_BLOCKS>
+template <typename KeyT, int NPAY, int RBITS, int THREADS>
 int rs_launch_pass(KeySrc ks, PaySrcN<NPAY> ps_, KeyDst ko, PayDstN<NPAY> pd, int64_t n, int begin, int bits,
                    int epoch, const unsigned long long *bin_base, uint64_t *state, unsigned long long *ticket,
                    cudaStream_t s) {
-  using Smem = RsSmem<KeyT, NPAY, RBITS, THREADS, ITEMS>;
-  auto kern = rs_pass_kernel<KeyT, NPAY, RBITS, THREADS, ITEMS, MIN_BLOCKS>;
+  using G = RsGeom<KeyT, NPAY>;
+  using Smem = RsSmem<KeyT, NPAY, RBITS, THREADS, G::ITEMS, G::PREFETCH>;
+  auto kern = rs_pass_kernel<KeyT, NPAY, RBITS, THREADS, G::ITEMS, G::PREFETCH>;
   const size_t smem = sizeof(Smem);
-  static int resident = 0;  // CTAs per SM of this instantiation (same on every B200 of the box)
-  if (resident == 0) {
+  static bool configured = false;
+  if (!configured) {
     PS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    int r = 0;
-    PS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&r, kern, THREADS, smem));
-    resident = r > 0 ? r : 1;
+    configured = true;
   }
   const int64_t tiles = ceil_div(n, Smem::TILE);
-  int64_t grid = (int64_t)sm_count() * resident;
+  int64_t grid = (int64_t)sm_count() * (1024 / THREADS);
   if (grid > tiles) grid = tiles;
   {
     ProfScope prof(PROF_RS_PASS, s);
@@ -536,39 +560,15 @@ int rs_launch_pass(KeySrc ks, PaySrcN<NPAY> ps_, KeyDst ko, PayDstN<NPAY> pd, in
   return PS_OK;
 }
 
-// variant table: {rbits, threads, items, min blocks}; 0 is the default of the key type
-#define PS_RS_VARIANTS(KeyT, X)                                  \
-  switch (rs_variant()) {                                        \
-    case 1:                                                      \
-      if constexpr (sizeof(KeyT) == 8) { X(8, 512, 12, 2); }     \
-      else { X(8, 512, 16, 2); }                                 \
-      break;                                                     \
-    case 2: X(9, 512, 12, 1); break;                             \
-    case 3: X(8, 1024, 12, 1); break;                            \
-    default:                                                     \
-      if constexpr (sizeof(KeyT) == 8) { X(8, 256, 12, 4); }     \
-      else { X(8, 256, 16, 4); }                                 \
-      break;                                                     \
-  }
-
-template <typename KeyT>
-RsGeomRt rs_geometry() {
-  RsGeomRt g{8, 256 * 12};
-#define PS_X(RB, T, I, B) g = RsGeomRt{RB, (T) * (I)}
-  PS_RS_VARIANTS(KeyT, PS_X)
-#undef PS_X
-  return g;
-}
-
 template <typename KeyT, int NPAY>
 int rs_dispatch_pass(KeySrc ks, PaySrcN<NPAY> ps_, KeyDst ko, PayDstN<NPAY> pd, int64_t n, int begin, int bits,
                      int epoch, const unsigned long long *bin_base, uint64_t *state, unsigned long long *ticket,
                      cudaStream_t s) {
-#define PS_X(RB, T, I, B) \
-  return rs_launch_pass<KeyT, NPAY, RB, T, I, B>(ks, ps_, ko, pd, n, begin, bits, epoch, bin_base, state, ticket, s)
-  PS_RS_VARIANTS(KeyT, PS_X)
-#undef PS_X
-  return PS_ERR_ARG;
+  switch (rs_variant()) {
+    case 1: return rs_launch_pass<KeyT, NPAY, 8, 512>(ks, ps_, ko, pd, n, begin, bits, epoch, bin_base, state, ticket, s);
+    case 2: return rs_launch_pass<KeyT, NPAY, 9, 1024>(ks, ps_, ko, pd, n, begin, bits, epoch, bin_base, state, ticket, s);
+    default: return rs_launch_pass<KeyT, NPAY, 8, 1024>(ks, ps_, ko, pd, n, begin, bits, epoch, bin_base, state, ticket, s);
+  }
 }
 
 // Sorts n (key, NPAY payload words) tuples on key bits [0, total_bits).  First-pass sources are
@@ -580,7 +580,7 @@ int radix_sort_tuples(KeySrc ksrc, PaySrcN<NPAY> psrc, int64_t n, int total_bits
                       uint32_t *const *pay_tmp0, uint32_t *const *pay_tmp1, KeyDst keys_final,
                       PayDstN<NPAY> pay_final, Scratch &scratch, cudaStream_t s) {
   if (n <= 0) return PS_OK;
-  const RsGeomRt geom = rs_geometry<KeyT>();
+  const RsGeomRt geom = rs_geometry<KeyT, NPAY>();
   const SortPlan plan = make_sort_plan(total_bits, geom.rbits);
   if (plan.passes > RS_MAX_PASSES) { set_error("radix sort: %d key bits unsupported", total_bits); return PS_ERR_ARG; }
   const int radix = 1 << geom.rbits;
@@ -629,7 +629,7 @@ int radix_sort_tuples(KeySrc ksrc, PaySrcN<NPAY> psrc, int64_t n, int total_bits
 
 // number of passes radix_sort_* will run for this key type (callers pick the ping-pong buffer with it)
 template <typename KeyT>
-int rs_num_passes(int total_bits) { return make_sort_plan(total_bits, rs_geometry<KeyT>().rbits).passes; }
+int rs_num_passes(int total_bits) { return make_sort_plan(total_bits, rs_geometry<KeyT, 1>().rbits).passes; }
 
 // the common single-payload form
 template <typename KeyT>

@@ -66,9 +66,9 @@ def timeline(label):
     buf = (ctypes.c_ulonglong * 16)()
     if lib.ps_debug_timeline(buf) != 0:
         return
-    names = ["loop top", "B0 wait (ticket, prev scatter)", "keys+rank", "B1 wait", "digit phase+scan", "B3 wait",
-             "positions+staging", "look-back", "B5 wait", "scatter"]
-    tot = float(sum(buf[:10])) or 1.0
+    names = ["zero counters", "rank (waits for keys)", "B1", "column scans+publish", "B3", "positions+staging+request",
+             "look-back", "B5", "scatter", "(payload staging)", "(positions + key staging)"]
+    tot = float(sum(buf[:11])) or 1.0
     print(label, "timeline:", ", ".join(f"{n} {100 * buf[i] / tot:.1f}%" for i, n in enumerate(names)),
           f"| total {tot / 1e6:.1f} Mcycles", flush=True)
 
