@@ -103,6 +103,15 @@ int ps_coalesce(const int64_t *row, const int64_t *col, int64_t nnz, int64_t M, 
  * storage.py:386-400; out_colcount (nullable) [N] = storage.py:405-420. */
 int ps_csr2csc(const int64_t *col, int64_t nnz, int64_t N, int64_t *out_csr2csc,
                int64_t *out_colptr, int64_t *out_colcount, void *stream);
+/* The whole CSC side in one call (storage.py:386-447 + transpose.py:9-33): the stable sort by col carries
+ * (entry index, row, value bits) as payload, so its last pass writes csr2csc AND the transposed arrays
+ * out_t_row = col[csr2csc] (the sorted col), out_t_col = row[csr2csc], out_t_value = value[csr2csc] directly:
+ * no random gathers.  value (nullable) must be one 4-byte element per entry (value_bytes == 4); out_colptr,
+ * out_colcount, out_csc2csr (inverse permutation, bucketed scatter) are nullable. */
+int ps_csc_build(const int64_t *row, const int64_t *col, const void *value, int64_t value_bytes,
+                 int64_t nnz, int64_t N, int64_t *out_csr2csc, int64_t *out_colptr,
+                 int64_t *out_colcount, int64_t *out_csc2csr, int64_t *out_t_row, int64_t *out_t_col,
+                 void *out_t_value, void *stream);
 /* storage.py:439-447 `csc2csr` = argsort(csr2csc) = inverse permutation. */
 int ps_invert_perm(const int64_t *perm, int64_t n, int64_t *out, void *stream);
 /* x[perm] for [n_src, row_bytes]-byte rows: storage.py:166-169,238-241, transpose.py:15,

@@ -41,6 +41,7 @@ SIGNATURES = {
                     c_ptr],
     "ps_csr2csc": [c_ptr, c_i64, c_i64, c_ptr, c_ptr, c_ptr, c_ptr],
     "ps_invert_perm": [c_ptr, c_i64, c_ptr, c_ptr],
+    "ps_csc_build": [c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_i64, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr],
     "ps_gather_rows": [c_ptr, c_i64, c_ptr, c_i64, c_ptr, c_ptr],
     "ps_transpose_gather": [c_ptr, c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_ptr, c_i64, c_ptr, c_ptr, c_ptr, c_ptr],
     "ps_segment_reduce": [c_ptr, c_int, c_i64, c_i64, c_ptr, c_i64, c_int, c_ptr, c_ptr],

@@ -46,7 +46,7 @@ inline SortPlan make_sort_plan(int total_bits, int rbits) {
 
 // ---- where the first pass finds its keys / payload, and where the last one puts them
 enum { KSRC_KEYS = 0, KSRC_PACK_COO = 1, KSRC_I64 = 2 };
-enum { PSRC_U32 = 0, PSRC_IOTA = 1, PSRC_U16 = 2, PSRC_U8 = 3, PSRC_I64 = 4 };
+enum { PSRC_U32 = 0, PSRC_IOTA = 1, PSRC_U16 = 2, PSRC_U8 = 3, PSRC_I64 = 4, PSRC_NONE = 5 /* word unused */ };
 enum { PDST_U32 = 0, PDST_I64 = 1, PDST_U16 = 2, PDST_U8 = 3, PDST_NONE = 4 };
 enum { KDST_NONE = 0, KDST_KEYS = 1, KDST_UNPACK_COO = 2, KDST_I64 = 3 };
 
@@ -216,6 +216,9 @@ __device__ __forceinline__ void load_tile_pay_sync(const PaySrc &s, int64_t tile
   if (s.mode == PSRC_IOTA) {
 #pragma unroll
     for (int i = 0; i < ITEMS; ++i) pay[i] = (uint32_t)(tile_base + warp_base + i * 32 + lane);
+  } else if (s.mode == PSRC_NONE) {
+#pragma unroll
+    for (int i = 0; i < ITEMS; ++i) pay[i] = 0u;
   } else if (s.mode == PSRC_I64) {
     const int64_t *p = reinterpret_cast<const int64_t *>(s.p) + tile_base;
 #pragma unroll
@@ -479,7 +482,7 @@ rs_pass_kernel(KeySrc ksrc, PaySrcN<NPAY> psrc, KeyDst kdst, PayDstN<NPAY> pdst,
     const bool full = tile_n == TILE;
     bool plain = kdst.mode == KDST_KEYS;
 #pragma unroll
-    for (int p = 0; p < NPAY; ++p) plain = plain && pdst.d[p].mode == PDST_U32;
+    for (int p = 0; p < NPAY; ++p) plain = plain && (pdst.d[p].mode == PDST_U32 || pdst.d[p].mode == PDST_NONE);
     if (plain) {
       KeyT *ko = reinterpret_cast<KeyT *>(kdst.a);
 #pragma unroll 4
@@ -491,7 +494,8 @@ rs_pass_kernel(KeySrc ksrc, PaySrcN<NPAY> psrc, KeyDst kdst, PayDstN<NPAY> pdst,
           const size_t dst = (size_t)(uint32_t)(sm.gbase[d] + (uint32_t)j);
           ko[dst] = kk;
 #pragma unroll
-          for (int p = 0; p < NPAY; ++p) reinterpret_cast<uint32_t *>(pdst.d[p].p)[dst] = sm.pay[p][j];
+          for (int p = 0; p < NPAY; ++p)
+            if (pdst.d[p].mode == PDST_U32) reinterpret_cast<uint32_t *>(pdst.d[p].p)[dst] = sm.pay[p][j];
         }
       }
     } else {
@@ -571,17 +575,18 @@ int rs_dispatch_pass(KeySrc ks, PaySrcN<NPAY> ps_, KeyDst ko, PayDstN<NPAY> pd, 
   }
 }
 
-// Sorts n (key, NPAY payload words) tuples on key bits [0, total_bits).  First-pass sources are
+// Sorts n (key, NPAY payload words) tuples on key bits [first_bit, first_bit + total_bits).  First-pass sources are
 // ksrc/psrc.  The last pass writes keys to keys_final (KDST_NONE: keys dropped) and payloads to
 // pay_final.  keys_tmp*/pay_tmp* are scratch buffers of n elements each (pay_tmp*[p] for word p;
 // unused when one pass suffices).
 template <typename KeyT, int NPAY>
 int radix_sort_tuples(KeySrc ksrc, PaySrcN<NPAY> psrc, int64_t n, int total_bits, KeyT *keys_tmp0, KeyT *keys_tmp1,
                       uint32_t *const *pay_tmp0, uint32_t *const *pay_tmp1, KeyDst keys_final,
-                      PayDstN<NPAY> pay_final, Scratch &scratch, cudaStream_t s) {
+                      PayDstN<NPAY> pay_final, Scratch &scratch, cudaStream_t s, int first_bit = 0) {
   if (n <= 0) return PS_OK;
   const RsGeomRt geom = rs_geometry<KeyT, NPAY>();
-  const SortPlan plan = make_sort_plan(total_bits, geom.rbits);
+  SortPlan plan = make_sort_plan(total_bits, geom.rbits);
+  for (int i = 0; i < plan.passes; ++i) plan.begin[i] += first_bit;  // sort on key bits [first_bit, first_bit + total_bits)
   if (plan.passes > RS_MAX_PASSES) { set_error("radix sort: %d key bits unsupported", total_bits); return PS_ERR_ARG; }
   const int radix = 1 << geom.rbits;
   const int64_t tiles = ceil_div(n, geom.tile);
@@ -612,11 +617,13 @@ int radix_sort_tuples(KeySrc ksrc, PaySrcN<NPAY> psrc, int64_t n, int total_bits
     PaySrcN<NPAY> ps_ = psrc;
     if (p > 0) {
       ks = KeySrc{kt[(p - 1) & 1], nullptr, KSRC_KEYS, 0};
-      for (int w = 0; w < NPAY; ++w) ps_.s[w] = PaySrc{((p - 1) & 1) ? pay_tmp1[w] : pay_tmp0[w], PSRC_U32};
+      for (int w = 0; w < NPAY; ++w)
+        ps_.s[w] = psrc.s[w].mode == PSRC_NONE ? psrc.s[w] : PaySrc{((p - 1) & 1) ? pay_tmp1[w] : pay_tmp0[w], PSRC_U32};
     }
     KeyDst ko{kt[p & 1], nullptr, KDST_KEYS, 0};
     PayDstN<NPAY> pd;
-    for (int w = 0; w < NPAY; ++w) pd.d[w] = PayDst{(p & 1) ? pay_tmp1[w] : pay_tmp0[w], PDST_U32};
+    for (int w = 0; w < NPAY; ++w)
+      pd.d[w] = psrc.s[w].mode == PSRC_NONE ? PayDst{nullptr, PDST_NONE} : PayDst{(p & 1) ? pay_tmp1[w] : pay_tmp0[w], PDST_U32};
     if (p == plan.passes - 1) {
       ko = keys_final;
       pd = pay_final;
@@ -635,13 +642,14 @@ int rs_num_passes(int total_bits) { return make_sort_plan(total_bits, rs_geometr
 template <typename KeyT>
 int radix_sort_pairs(KeySrc ksrc, PaySrc psrc, int64_t n, int total_bits, KeyT *keys_tmp0, KeyT *keys_tmp1,
                      uint32_t *pay_tmp0, uint32_t *pay_tmp1, KeyDst keys_final, PayDst pay_final, Scratch &scratch,
-                     cudaStream_t s) {
+                     cudaStream_t s, int first_bit = 0) {
   PaySrcN<1> ps_;
   ps_.s[0] = psrc;
   PayDstN<1> pd;
   pd.d[0] = pay_final;
   uint32_t *t0[1] = {pay_tmp0}, *t1[1] = {pay_tmp1};
-  return radix_sort_tuples<KeyT, 1>(ksrc, ps_, n, total_bits, keys_tmp0, keys_tmp1, t0, t1, keys_final, pd, scratch, s);
+  return radix_sort_tuples<KeyT, 1>(ksrc, ps_, n, total_bits, keys_tmp0, keys_tmp1, t0, t1, keys_final, pd, scratch, s,
+                                    first_bit);
 }
 
 }  // namespace ps

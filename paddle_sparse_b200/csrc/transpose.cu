@@ -22,6 +22,52 @@ invert_perm_kernel(const int64_t *__restrict__ perm, int64_t n, int64_t *__restr
   if (i < n) out[ld_stream(perm + i)] = i;
 }
 
+// Second half of the bucketed inverse: the (target, source) pairs arrive grouped by target >> INV_WINDOW_BITS, so
+// the CTAs working at any moment write into a few windows of 2^INV_WINDOW_BITS entries (2 MB each) that stay in L2
+// until they are complete: the random 8-byte stores merge into full lines before they reach HBM.
+constexpr int INV_WINDOW_BITS = 18;
+__global__ void __launch_bounds__(256)
+invert_scatter_kernel(const uint32_t *__restrict__ target, const uint32_t *__restrict__ source, int64_t n,
+                      int64_t *__restrict__ out) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x * 4;
+  for (int64_t base = ((int64_t)blockIdx.x * blockDim.x) * 4; base < n; base += stride) {
+    const int64_t i0 = base + threadIdx.x;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int64_t i = i0 + k * 256;
+      if (i < n) out[ld_stream(target + i)] = (int64_t)ld_stream(source + i);
+    }
+  }
+}
+
+// out[perm[i]] = i.  Large inputs: one stable radix partition of (perm[i], i) on the high bits of perm[i], then
+// the windowed scatter above; small inputs (the whole output fits L2 comfortably): the direct scatter.
+static int invert_perm_impl(const int64_t *perm, int64_t n, int64_t *out, cudaStream_t s) {
+  const int nbits = bits_for(n);
+  if (nbits <= INV_WINDOW_BITS + 2 || n >= (int64_t(1) << 32)) {
+    ProfScope prof(PROF_INVERT_PERM, s);
+    invert_perm_kernel<<<(unsigned)ceil_div(n, 256), 256, 0, s>>>(perm, n, out);
+    PS_LAUNCH_OK();
+    return PS_OK;
+  }
+  Scratch scratch(s);
+  PS_SCRATCH(k0, scratch, uint32_t, n);
+  PS_SCRATCH(k1, scratch, uint32_t, n);
+  PS_SCRATCH(p0, scratch, uint32_t, n);
+  PS_SCRATCH(p1, scratch, uint32_t, n);
+  const int top = nbits - INV_WINDOW_BITS;
+  const int passes = rs_num_passes<uint32_t>(top);
+  uint32_t *tk = (passes & 1) ? k0 : k1, *tp = (passes & 1) ? p0 : p1;
+  PS_TRY(radix_sort_pairs<uint32_t>(KeySrc{perm, nullptr, KSRC_I64, 0}, PaySrc{nullptr, PSRC_IOTA}, n, top, k0, k1, p0, p1,
+                                    KeyDst{tk, nullptr, KDST_KEYS, 0}, PayDst{tp, PDST_U32}, scratch, s, INV_WINDOW_BITS));
+  {
+    ProfScope prof(PROF_INVERT_PERM, s);
+    invert_scatter_kernel<<<(unsigned)(sm_count() * 8), 256, 0, s>>>(tk, tp, n, out);
+  }
+  PS_LAUNCH_OK();
+  return PS_OK;
+}
+
 // out_col[j] = row[p], out_row[j] = col[p] (unless streamed from colptr), out_value[j] = value[p]
 template <typename U, bool WITH_ROW, bool WITH_VALUE>
 __global__ void __launch_bounds__(256)
@@ -79,11 +125,56 @@ int ps_csr2csc(const int64_t *col, int64_t nnz, int64_t N, int64_t *out_csr2csc,
 int ps_invert_perm(const int64_t *perm, int64_t n, int64_t *out, void *stream) {
   PS_CHECK(n >= 0, "invert_perm: negative size");
   if (n == 0) return PS_OK;
-  {
-    ProfScope prof(PROF_INVERT_PERM, (cudaStream_t)stream);
-    invert_perm_kernel<<<(unsigned)ceil_div(n, 256), 256, 0, (cudaStream_t)stream>>>(perm, n, out);
+  return invert_perm_impl(perm, n, out, (cudaStream_t)stream);
+}
+
+int ps_csc_build(const int64_t *row, const int64_t *col, const void *value, int64_t value_bytes, int64_t nnz, int64_t N,
+                 int64_t *out_csr2csc, int64_t *out_colptr, int64_t *out_colcount, int64_t *out_csc2csr,
+                 int64_t *out_t_row, int64_t *out_t_col, void *out_t_value, void *stream) {
+  PS_CHECK(nnz >= 0 && N >= 0, "csc_build: negative size");
+  PS_CHECK(nnz < (int64_t(1) << 32), "csc_build: nnz=%lld exceeds the 2^32-1 entries per call this build supports",
+           (long long)nnz);
+  PS_CHECK(N <= (int64_t(1) << 32), "csc_build: N=%lld exceeds the 2^32 columns this build supports", (long long)N);
+  PS_CHECK(row && col && out_csr2csc && out_t_row && out_t_col, "csc_build: NULL argument");
+  PS_CHECK(!value || (value_bytes == 4 && out_t_value), "csc_build: carried values are one 4-byte element per entry");
+  cudaStream_t s = (cudaStream_t)stream;
+  Scratch scratch(s);
+  const bool want_ptr = out_colptr || out_colcount;
+  int64_t *colptr = out_colptr;
+  if (want_ptr && !colptr) {
+    PS_SCRATCH(tmp, scratch, int64_t, N + 1);
+    colptr = tmp;
   }
-  PS_LAUNCH_OK();
+  if (nnz == 0) {
+    if (want_ptr) PS_CUDA(cudaMemsetAsync(colptr, 0, sizeof(int64_t) * (size_t)(N + 1), s));
+    if (out_colcount && N > 0) PS_CUDA(cudaMemsetAsync(out_colcount, 0, sizeof(int64_t) * (size_t)N, s));
+    return PS_OK;
+  }
+  // stable sort by col of (col | entry index, row, value bits): the last pass writes the transposed arrays directly
+  const int cbits = bits_for(N);
+  PS_SCRATCH(k0, scratch, uint32_t, nnz);
+  PS_SCRATCH(k1, scratch, uint32_t, nnz);
+  uint32_t *t0[3], *t1[3];
+  for (int w = 0; w < 3; ++w) {
+    if (w == 2 && !value) { t0[w] = t1[w] = nullptr; continue; }
+    PS_SCRATCH(a, scratch, uint32_t, nnz);
+    PS_SCRATCH(b, scratch, uint32_t, nnz);
+    t0[w] = a;
+    t1[w] = b;
+  }
+  PaySrcN<3> ps_;
+  ps_.s[0] = PaySrc{nullptr, PSRC_IOTA};
+  ps_.s[1] = PaySrc{row, PSRC_I64};
+  ps_.s[2] = value ? PaySrc{value, PSRC_U32} : PaySrc{nullptr, PSRC_NONE};
+  PayDstN<3> pd;
+  pd.d[0] = PayDst{out_csr2csc, PDST_I64};
+  pd.d[1] = PayDst{out_t_col, PDST_I64};
+  pd.d[2] = value ? PayDst{out_t_value, PDST_U32} : PayDst{nullptr, PDST_NONE};
+  PS_TRY((radix_sort_tuples<uint32_t, 3>(KeySrc{col, nullptr, KSRC_I64, 0}, ps_, nnz, cbits, k0, k1, t0, t1,
+                                         KeyDst{out_t_row, nullptr, KDST_I64, 0}, pd, scratch, s)));
+  if (want_ptr) PS_TRY(ind2ptr_launch<int64_t>(out_t_row, nnz, N, colptr, s));
+  if (out_colcount) PS_TRY(ps_ptr2count(colptr, N, out_colcount, stream));
+  if (out_csc2csr) PS_TRY(invert_perm_impl(out_csr2csc, nnz, out_csc2csr, s));
   return PS_OK;
 }
 

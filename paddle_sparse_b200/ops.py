@@ -247,6 +247,29 @@ def csr2csc(col: torch.Tensor, N: int, want_colptr: bool = True, want_colcount: 
     return perm, colptr, colcount
 
 
+def csc_build(row: torch.Tensor, col: torch.Tensor, value: Optional[torch.Tensor], N: int,
+              want_colcount: bool = True, want_csc2csr: bool = True):
+    """storage.py:386-447 + transpose.py:9-33 in one call: csr2csc, colptr, colcount, csc2csr and the transposed
+    arrays (col[csr2csc], row[csr2csc], value[csr2csc]); the values ride through the sort when they are one 4-byte
+    element per entry, else they are gathered once at the end.
+    Returns dict(csr2csc, colptr, colcount, csc2csr, t_row, t_col, t_value)."""
+    row, col = _idx(row, "row"), _idx(col, "col")
+    value = None if value is None else _dev(value, "value")
+    nnz = col.numel()
+    carry = value is not None and nnz > 0 and _row_bytes(value) == 4
+    perm, t_row, t_col = _new(col, nnz), _new(col, nnz), _new(col, nnz)
+    colptr = _new(col, N + 1)
+    colcount = _new(col, N) if want_colcount else None
+    inv = _new(col, nnz) if want_csc2csr else None
+    t_value = torch.empty_like(value) if carry else None
+    with torch.cuda.device(col.device):
+        _lib.call("ps_csc_build", _p(row), _p(col), _p(value) if carry else None, 4 if carry else 0, nnz, N, _p(perm),
+                  _p(colptr), _p(colcount), _p(inv), _p(t_row), _p(t_col), _p(t_value), _stream(col))
+    if value is not None and not carry:
+        t_value = gather_rows(value, perm)
+    return dict(csr2csc=perm, colptr=colptr, colcount=colcount, csc2csr=inv, t_row=t_row, t_col=t_col, t_value=t_value)
+
+
 def invert_perm(perm: torch.Tensor) -> torch.Tensor:
     """storage.py:439-447: argsort of a permutation == its inverse."""
     perm = _idx(perm, "perm")

@@ -255,6 +255,37 @@ class SparseStorage(object):
         if need_ptr:
             self._colptr_spare = colptr
 
+    def _build_csc_carry(self, everything: bool) -> None:
+        """The CSC side in ONE call (ops.csc_build): the stable sort by col carries (entry index, row, value) so
+        its last pass also writes the transposed arrays, which are parked in `_t_parts` for `t()` (not a cache
+        key; dropped by clear_cache_ and ignored once the value tensor has been replaced).  `everything` also
+        builds colcount and csc2csr and promotes all CSC caches (fill_cache_, storage.py:488-496)."""
+        r = ops.csc_build(self.row(), self._col, self._value, self._sparse_sizes[1], everything, everything)
+        self._csr2csc = r["csr2csc"]
+        self._t_parts = (r["t_row"], r["t_col"], r["t_value"], self._value)
+        if everything:
+            if self._colptr is None:
+                self._colptr = r["colptr"]
+            if self._colcount is None:
+                self._colcount = r["colcount"]
+            self._csc2csr = r["csc2csr"]
+        elif self._colptr is None:
+            self._colptr_spare = r["colptr"]
+
+    def take_transposed_parts(self):
+        """(col[csr2csc], row[csr2csc], value[csr2csc]) for transpose.py:9-33, building csr2csc if needed.
+        Uses the by-products of the carrying sort when they are there, else one fused gather."""
+        if self._csr2csc is None:
+            self._build_csc_carry(False)
+        parts, self._t_parts = getattr(self, "_t_parts", None), None
+        if parts is not None:
+            t_row, t_col, t_value, value_then = parts
+            if value_then is not self._value:  # set_value_ since: re-gather the values only
+                t_value = None if self._value is None else ops.gather_rows(self._value, self._csr2csc)
+            return t_row, t_col, t_value
+        return ops.transpose_gather(self._csr2csc, self.row(), self._col, self._value, self._colptr,
+                                    self._sparse_sizes[1])
+
     def colptr(self) -> torch.Tensor:
         if self._colptr is None:
             spare = getattr(self, "_colptr_spare", None)
@@ -316,6 +347,8 @@ class SparseStorage(object):
         self.row()
         self.rowptr()
         self.rowcount()
+        if self._csr2csc is None and self._col.numel() > 0:
+            self._build_csc_carry(True)
         self.csr2csc()
         self.colptr()
         self.colcount()
@@ -324,6 +357,7 @@ class SparseStorage(object):
 
     def clear_cache_(self):
         self._colptr_spare = None
+        self._t_parts = None
         self._rowcount = None
         self._colptr = None
         self._colcount = None

@@ -9,14 +9,13 @@ from .tensor import SparseTensor
 
 
 def t(src: SparseTensor) -> SparseTensor:
-    """transpose.py:9-33: gather (row, col, value) through the cached csr2csc and swap the caches.
-    One fused gather kernel instead of three; when colptr is cached the new row array is streamed
-    from it instead of being gathered."""
+    """transpose.py:9-33: (row, col, value) in CSC order, caches swapped.  The transposed arrays are by-products
+    of the sort that builds csr2csc (SparseStorage.take_transposed_parts); when csr2csc was cached without them
+    they come from one fused gather."""
     st = src.storage
-    csr2csc = st.csr2csc()
-    row, col, value = src.coo()
     M, N = st.sparse_sizes()
-    new_row, new_col, new_value = ops.transpose_gather(csr2csc, row, col, value, st._colptr, N)
+    new_row, new_col, new_value = st.take_transposed_parts()
+    csr2csc = st.csr2csc()
     storage = SparseStorage(row=new_row, rowptr=st._colptr, col=new_col, value=new_value, sparse_sizes=(N, M),
                             rowcount=st._colcount, colptr=st._rowptr, colcount=st._rowcount, csr2csc=st._csc2csr,
                             csc2csr=csr2csc, is_sorted=True, trust_data=True)

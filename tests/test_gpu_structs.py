@@ -55,6 +55,43 @@ def test_csc_structures_match_oracle(ops, M, N, nnz):
     assert tv is None and np.array_equal(host(tr), At.storage.row())
 
 
+@pytest.mark.parametrize("M,N,nnz", [(1, 1, 1), (5, 300, 400), (1000, 1000, 30000), (200, 70000, 90000),
+                                     (2500000, 2500000, 300000), (3000, 3000, 1500000)])
+@pytest.mark.parametrize("vdt", ["float32", "int32", "bfloat16", "float64", None])
+def test_csc_build_matches_oracle(ops, M, N, nnz, vdt):
+    """ps_csc_build: csr2csc, colptr, colcount, csc2csr and the transposed arrays in one call (values carried
+    through the sort when 4 bytes wide, gathered otherwise) == storage.py:386-447 + transpose.py:9-33."""
+    rng = np.random.default_rng(N + nnz)
+    row, col = _coalesced(rng, M, N, nnz)
+    val = None if vdt is None else rng.integers(-50, 50, row.size).astype(np.float64)
+    A = np_ref.SparseTensor(row=row, col=col, value=val, sparse_sizes=(M, N), is_sorted=True, trust_data=True)
+    st = A.storage
+    tval = None if vdt is None else dev(val).to(getattr(torch, vdt))
+    r = ops.csc_build(dev(row), dev(col), tval, N, True, True)
+    perm = st.csr2csc()
+    assert np.array_equal(host(r["csr2csc"]), perm)
+    assert np.array_equal(host(r["colptr"]), st.colptr())
+    assert np.array_equal(host(r["colcount"]), st.colcount())
+    assert np.array_equal(host(r["csc2csr"]), st.csc2csr())
+    assert np.array_equal(host(r["t_row"]), col[perm])
+    assert np.array_equal(host(r["t_col"]), row[perm])
+    if vdt is None:
+        assert r["t_value"] is None
+    else:
+        assert np.array_equal(host(r["t_value"].to(torch.float64)), val[perm])
+    light = ops.csc_build(dev(row), dev(col), tval, N, False, False)
+    assert light["csc2csr"] is None and light["colcount"] is None
+    assert np.array_equal(host(light["csr2csc"]), perm) and np.array_equal(host(light["colptr"]), st.colptr())
+
+
+def test_invert_perm_large(ops):
+    """the bucketed inverse (radix partition on the high bits + windowed scatter) on a permutation beyond 2^20"""
+    n = (1 << 21) + 12345
+    perm = torch.randperm(n, device="cuda", generator=torch.Generator(device="cuda").manual_seed(5))
+    inv = ops.invert_perm(perm)
+    assert torch.equal(inv[perm], torch.arange(n, device="cuda"))
+
+
 def test_csr2csc_on_uncoalesced_is_stable(ops):
     rng = np.random.default_rng(0)
     M = N = 50

@@ -59,6 +59,8 @@ def main():
         timeit("invert_perm", lambda: ops.invert_perm(perm))
         timeit("transpose_gather", lambda: ops.transpose_gather(perm, r, c, v, colptr, N))
         timeit("ind2ptr", lambda: ops.ind2ptr(r, M))
+        timeit("csc_build(all)", lambda: ops.csc_build(r, c, v, N, True, True))
+        timeit("csc_build(light)", lambda: ops.csc_build(r, c, v, N, False, False))
 
 
 def timeline(label):
