@@ -92,10 +92,13 @@ int ps_coalesce_sorted(const int64_t *row, const int64_t *col, int64_t nnz, cons
                        int dtype, int64_t width, int reduce, int64_t *out_row, int64_t *out_col,
                        void *out_value, int64_t *host_nnz_out, void *stream);
 /* coalesce.py:8-29 free function = sort-on-construct + coalesce, fused: one radix sort
- * of the packed keys followed by run detection + segmented reduce.  Synchronises once. */
+ * of the packed keys followed by run detection + segmented reduce.  out_rowptr (nullable, [M+1]): the
+ * rowptr of the coalesced result (storage.py:211-222 = ind2ptr(row, M)), written by the same pass.
+ * Synchronises once. */
 int ps_coalesce(const int64_t *row, const int64_t *col, int64_t nnz, int64_t M, int64_t N,
                 const void *value, int dtype, int64_t width, int reduce, int64_t *out_row,
-                int64_t *out_col, void *out_value, int64_t *host_nnz_out, void *stream);
+                int64_t *out_col, void *out_value, int64_t *out_rowptr, int64_t *host_nnz_out,
+                void *stream);
 
 /* ------------------------------------------------------------------ CSC structures */
 /* storage.py:425-434 `csr2csc` = argsort(M*col + row); on CSR-ordered input this is a

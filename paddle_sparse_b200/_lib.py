@@ -38,7 +38,7 @@ SIGNATURES = {
     "ps_sort_coo": [c_ptr, c_ptr, c_i64, c_i64, c_i64, c_ptr, c_int, c_i64, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr],
     "ps_coalesce_sorted": [c_ptr, c_ptr, c_i64, c_ptr, c_int, c_i64, c_int, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr],
     "ps_coalesce": [c_ptr, c_ptr, c_i64, c_i64, c_i64, c_ptr, c_int, c_i64, c_int, c_ptr, c_ptr, c_ptr, c_ptr,
-                    c_ptr],
+                    c_ptr, c_ptr],
     "ps_csr2csc": [c_ptr, c_i64, c_i64, c_ptr, c_ptr, c_ptr, c_ptr],
     "ps_invert_perm": [c_ptr, c_i64, c_ptr, c_ptr],
     "ps_csc_build": [c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_i64, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr],

@@ -27,63 +27,103 @@ template <> __device__ __forceinline__ __nv_bfloat16 pay_as<__nv_bfloat16>(uint3
 }
 template <> __device__ __forceinline__ __half pay_as<__half>(uint32_t p) { return __ushort_as_half((unsigned short)p); }
 
-// One tile = THREADS*ITEMS consecutive sorted entries; thread t owns ITEMS consecutive ones.
+// One tile = THREADS*ITEMS consecutive sorted entries, held in shared memory; thread t looks at entries
+// t, t + THREADS, ... (conflict-free).  Run heads are ranked with ballots + one small scan, the tile's offset comes
+// from a decoupled look-back, every head folds its run in sorted (= stable) order, the compacted (key, value)
+// pairs are staged in shared memory and written out coalesced as int64 row / col + value.  With out_rowptr the
+// kernel also emits rowptr (csrc/convert.cpp:13-43 semantics) of the coalesced result: the head that opens row r
+// fills rowptr[prev_row + 1 .. r], the CTA of the last tile fills the tail.
 template <typename KeyT, typename T, int RED, int MODE, int THREADS, int ITEMS>
 __global__ void __launch_bounds__(THREADS)
-dedup_kernel(KeySrc ksrc, PaySrc psrc, int64_t n, int cbits, int64_t *__restrict__ out_row,
+dedup_kernel(KeySrc ksrc, PaySrc psrc, int64_t n, int cbits, int64_t M, int64_t *__restrict__ out_row,
              int64_t *__restrict__ out_col, T *__restrict__ out_value, int64_t *__restrict__ run_start,
-             uint64_t *state /*[0]=ticket,[1..]=tiles*/, long long *d_nnz_out) {
-  constexpr int TILE = THREADS * ITEMS;
+             int64_t *__restrict__ out_rowptr, uint64_t *state /*[0]=ticket,[1..]=tiles*/, long long *d_nnz_out) {
+  constexpr int TILE = THREADS * ITEMS, WARPS = THREADS / 32;
   using A = typename Acc<T>::type;
-  __shared__ KeyT s_key[TILE + 1];  // s_key[0] = key preceding the tile
+  __shared__ KeyT s_key[TILE + 1];  // s_key[0] = key preceding the tile; later the compacted keys
   __shared__ uint32_t s_pay[MODE == DD_FAST ? TILE : 1];
-  __shared__ int64_t warp_sums[33];
+  __shared__ uint32_t s_wcnt[ITEMS * WARPS];
   __shared__ int64_t s_tile, s_excl;
-  if (threadIdx.x == 0) s_tile = (int64_t)atomicAdd((unsigned long long *)state, 1ull);
+  __shared__ int s_heads;
+  const unsigned tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+  if (tid == 0) s_tile = (int64_t)atomicAdd((unsigned long long *)state, 1ull);
   __syncthreads();
   const int64_t tile = s_tile;
   const int64_t tile_base = tile * TILE;
   const int tile_n = (int)((n - tile_base) < TILE ? (n - tile_base) : TILE);
 
-  for (int j = threadIdx.x; j < tile_n; j += THREADS) {
-    s_key[j + 1] = load_key<KeyT>(ksrc, tile_base + j);
-    if (MODE == DD_FAST) s_pay[j] = load_pay(psrc, tile_base + j);
-  }
-  if (threadIdx.x == 0) s_key[0] = tile_base > 0 ? load_key<KeyT>(ksrc, tile_base - 1) : KeyT(0);
-  __syncthreads();
-
-  const int j0 = threadIdx.x * ITEMS;
-  unsigned heads = 0;
-  int cnt = 0;
 #pragma unroll
   for (int k = 0; k < ITEMS; ++k) {
-    const int j = j0 + k;
+    const int j = k * THREADS + tid;
+    if (j < tile_n) {
+      s_key[j + 1] = load_key<KeyT>(ksrc, tile_base + j);
+      if (MODE == DD_FAST) s_pay[j] = load_pay(psrc, tile_base + j);
+    }
+  }
+  if (tid == 0) s_key[0] = tile_base > 0 ? load_key<KeyT>(ksrc, tile_base - 1) : KeyT(0);
+  __syncthreads();
+
+  // ---- run heads, ranked in entry order (k, warp, lane)
+  unsigned heads = 0, below[ITEMS];
+  const unsigned lt = lanemask_lt();
+#pragma unroll
+  for (int k = 0; k < ITEMS; ++k) {
+    const int j = k * THREADS + tid;
     const bool h = j < tile_n && ((tile_base + j == 0) || s_key[j + 1] != s_key[j]);
+    const unsigned bal = __ballot_sync(0xffffffffu, h);
     heads |= (unsigned)h << k;
-    cnt += h;
-  }
-  int64_t total;
-  int64_t excl = block_exclusive_scan<int64_t, THREADS>((int64_t)cnt, warp_sums, &total);
-  if (threadIdx.x < 32) {
-    const uint64_t p = warp_lookback(state + 1, tile, (uint64_t)total);
-    if (threadIdx.x == 0) s_excl = (int64_t)p;
+    below[k] = __popc(bal & lt);
+    if (lane == 0) s_wcnt[k * WARPS + warp] = __popc(bal);
   }
   __syncthreads();
-  excl += s_excl;
-  if (tile_base + tile_n == n && threadIdx.x == 0) {
-    *d_nnz_out = (long long)(s_excl + total);
-    if (MODE == DD_PTR) run_start[s_excl + total] = n;
+  if (warp == 0) {  // exclusive scan of the ITEMS*WARPS counts, then the look-back for the tile's offset
+    constexpr int PER = (ITEMS * WARPS + 31) / 32;
+    uint32_t v[PER], sum = 0;
+#pragma unroll
+    for (int q = 0; q < PER; ++q) {
+      const int idx = lane * PER + q;
+      v[q] = idx < ITEMS * WARPS ? s_wcnt[idx] : 0u;
+      sum += v[q];
+    }
+    uint32_t inc = sum;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t o = __shfl_up_sync(0xffffffffu, inc, d);
+      if (lane >= (unsigned)d) inc += o;
+    }
+    uint32_t run = inc - sum;
+#pragma unroll
+    for (int q = 0; q < PER; ++q) {
+      const int idx = lane * PER + q;
+      if (idx < ITEMS * WARPS) s_wcnt[idx] = run;
+      run += v[q];
+    }
+    const uint32_t total = __shfl_sync(0xffffffffu, inc, 31);
+    const uint64_t p = warp_lookback(state + 1, tile, (uint64_t)total);
+    if (lane == 0) {
+      s_excl = (int64_t)p;
+      s_heads = (int)total;
+    }
   }
-
+  __syncthreads();
+  const int64_t tile_excl = s_excl;
+  const int tile_heads = s_heads;
+  const bool last_tile = tile_base + tile_n == n;
   const KeyT cmask = (KeyT)((uint64_t(1) << cbits) - 1);
+
+  // ---- every head folds its run and opens its row
+  KeyT hkey[ITEMS];
+  A hacc[ITEMS];
 #pragma unroll
   for (int k = 0; k < ITEMS; ++k) {
+    hkey[k] = KeyT(0);
+    hacc[k] = A(0);
     if (!((heads >> k) & 1u)) continue;
-    const int j = j0 + k;
+    const int j = k * THREADS + tid;
     const KeyT key = s_key[j + 1];
-    const int64_t o = excl++;
-    out_row[o] = (int64_t)((uint64_t)key >> cbits);
-    out_col[o] = (int64_t)(key & cmask);
+    hkey[k] = key;
+    below[k] += s_wcnt[k * WARPS + warp];  // rank of this head among the tile's heads
+    const int64_t o = tile_excl + below[k];
     if (MODE == DD_PTR) run_start[o] = tile_base + j;
     if (MODE == DD_FAST) {
       A acc = to_acc<T>(pay_as<T>(s_pay[j]));
@@ -101,22 +141,58 @@ dedup_kernel(KeySrc ksrc, PaySrc psrc, int64_t n, int cbits, int64_t *__restrict
           ++len;
         }
       }
-      out_value[o] = from_acc<T>(Red<RED, A>::finish(acc, len));
+      hacc[k] = Red<RED, A>::finish(acc, len);
     }
+    if (out_rowptr) {
+      const int64_t r = (int64_t)((uint64_t)key >> cbits);
+      const int64_t pr = (tile_base + j == 0) ? -1 : (int64_t)((uint64_t)s_key[j] >> cbits);
+      for (int64_t q = pr + 1; q <= r; ++q) out_rowptr[q] = o;
+    }
+  }
+  int64_t last_row = -1;
+  if (last_tile && tid == 0) last_row = (int64_t)((uint64_t)s_key[tile_n] >> cbits);
+  __syncthreads();  // every read of the tile is done: compact in place
+#pragma unroll
+  for (int k = 0; k < ITEMS; ++k) {
+    if (!((heads >> k) & 1u)) continue;
+    s_key[below[k]] = hkey[k];
+    if (MODE == DD_FAST) {
+      const T v = from_acc<T>(hacc[k]);
+      uint32_t bits = 0;
+      memcpy(&bits, &v, sizeof(T));
+      s_pay[below[k]] = bits;
+    }
+  }
+  if (last_tile && tid == 0) {
+    *d_nnz_out = (long long)(tile_excl + tile_heads);
+    if (MODE == DD_PTR) run_start[tile_excl + tile_heads] = n;
+    s_tile = last_row;
+  }
+  __syncthreads();
+  for (int i = tid; i < tile_heads; i += THREADS) {
+    const KeyT key = s_key[i];
+    out_row[tile_excl + i] = (int64_t)((uint64_t)key >> cbits);
+    out_col[tile_excl + i] = (int64_t)(key & cmask);
+    if (MODE == DD_FAST) out_value[tile_excl + i] = pay_as<T>(s_pay[i]);
+  }
+  if (last_tile && out_rowptr) {  // rows after the last entry point at nnz'
+    const int64_t total = tile_excl + tile_heads;
+    for (int64_t q = s_tile + 1 + tid; q <= M; q += THREADS) out_rowptr[q] = total;
   }
 }
 
 template <typename KeyT, typename T, int RED, int MODE>
-int dedup_launch(KeySrc ksrc, PaySrc psrc, int64_t n, int cbits, int64_t *out_row, int64_t *out_col, void *out_value,
-                 int64_t *run_start, long long *d_nnz, Scratch &scratch, cudaStream_t s) {
-  constexpr int THREADS = 256, ITEMS = 8;
+int dedup_launch(KeySrc ksrc, PaySrc psrc, int64_t n, int cbits, int64_t M, int64_t *out_row, int64_t *out_col,
+                 void *out_value, int64_t *run_start, int64_t *out_rowptr, long long *d_nnz, Scratch &scratch,
+                 cudaStream_t s) {
+  constexpr int THREADS = 512, ITEMS = 6;  // 3072 entries: 36 KB of static shared memory with 8-byte keys
   const int64_t tiles = ceil_div(n, THREADS * ITEMS);
   PS_SCRATCH(state, scratch, uint64_t, tiles + 1);
   PS_CUDA(cudaMemsetAsync(state, 0, sizeof(uint64_t) * (size_t)(tiles + 1), s));
   {
     ProfScope prof(PROF_DEDUP, s);
     dedup_kernel<KeyT, T, RED, MODE, THREADS, ITEMS><<<(unsigned)tiles, THREADS, 0, s>>>(
-        ksrc, psrc, n, cbits, out_row, out_col, reinterpret_cast<T *>(out_value), run_start, state, d_nnz);
+        ksrc, psrc, n, cbits, M, out_row, out_col, reinterpret_cast<T *>(out_value), run_start, out_rowptr, state, d_nnz);
   }
   PS_LAUNCH_OK();
   return PS_OK;
@@ -130,19 +206,19 @@ static int pay_src_mode(int dtype) { return dtype_size(dtype) == 4 ? PSRC_U32 : 
 static int pay_dst_mode(int dtype) { return dtype_size(dtype) == 4 ? PDST_U32 : PDST_U16; }
 
 template <typename KeyT>
-int dedup_dispatch(KeySrc ksrc, PaySrc psrc, int64_t n, int cbits, int mode, int dtype, int reduce, int64_t *out_row,
-                   int64_t *out_col, void *out_value, int64_t *run_start, long long *d_nnz, Scratch &scratch,
-                   cudaStream_t s) {
+int dedup_dispatch(KeySrc ksrc, PaySrc psrc, int64_t n, int cbits, int64_t M, int mode, int dtype, int reduce,
+                   int64_t *out_row, int64_t *out_col, void *out_value, int64_t *run_start, int64_t *out_rowptr,
+                   long long *d_nnz, Scratch &scratch, cudaStream_t s) {
   if (mode == DD_INDEX_ONLY)
-    return dedup_launch<KeyT, float, PS_SUM, DD_INDEX_ONLY>(ksrc, psrc, n, cbits, out_row, out_col, nullptr, nullptr,
-                                                            d_nnz, scratch, s);
+    return dedup_launch<KeyT, float, PS_SUM, DD_INDEX_ONLY>(ksrc, psrc, n, cbits, M, out_row, out_col, nullptr, nullptr,
+                                                            out_rowptr, d_nnz, scratch, s);
   if (mode == DD_PTR)
-    return dedup_launch<KeyT, float, PS_SUM, DD_PTR>(ksrc, psrc, n, cbits, out_row, out_col, nullptr, run_start, d_nnz,
-                                                     scratch, s);
-#define PS_DD(T)                                                                                              \
-  PS_DISPATCH_REDUCE(reduce, RED, return (dedup_launch<KeyT, T, RED, DD_FAST>(ksrc, psrc, n, cbits, out_row,   \
-                                                                             out_col, out_value, nullptr, d_nnz, \
-                                                                             scratch, s)))
+    return dedup_launch<KeyT, float, PS_SUM, DD_PTR>(ksrc, psrc, n, cbits, M, out_row, out_col, nullptr, run_start,
+                                                     out_rowptr, d_nnz, scratch, s);
+#define PS_DD(T)                                                                                               \
+  PS_DISPATCH_REDUCE(reduce, RED, return (dedup_launch<KeyT, T, RED, DD_FAST>(ksrc, psrc, n, cbits, M, out_row, \
+                                                                             out_col, out_value, nullptr,      \
+                                                                             out_rowptr, d_nnz, scratch, s)))
   switch (dtype) {
     case PS_F32: PS_DD(float); break;
     case PS_I32: PS_DD(int32_t); break;
@@ -183,7 +259,7 @@ static int check_value_args(const void *value, const void *out_value, int dtype,
 template <typename KeyT>
 int sort_impl(const int64_t *row, const int64_t *col, int64_t nnz, KeyGeom g, const void *value, int dtype,
               int64_t width, bool dedup, int reduce, int64_t *out_row, int64_t *out_col, void *out_value,
-              int64_t *out_perm, int64_t *host_nnz_out, cudaStream_t s) {
+              int64_t *out_perm, int64_t *host_nnz_out, int64_t M, int64_t *out_rowptr, cudaStream_t s) {
   Scratch scratch(s);
   const bool fast = value && fast_value(dtype, width) && !out_perm;
   const bool need_perm = (value && !fast) || out_perm;
@@ -224,17 +300,17 @@ int sort_impl(const int64_t *row, const int64_t *col, int64_t nnz, KeyGeom g, co
   PaySrc sp{psorted, PSRC_U32};
   long long h_nnz = 0;
   if (!value) {
-    PS_TRY(dedup_dispatch<KeyT>(sk, sp, nnz, g.cbits, DD_INDEX_ONLY, dtype, reduce, out_row, out_col, nullptr, nullptr,
-                                d_nnz, scratch, s));
+    PS_TRY(dedup_dispatch<KeyT>(sk, sp, nnz, g.cbits, M, DD_INDEX_ONLY, dtype, reduce, out_row, out_col, nullptr, nullptr,
+                                out_rowptr, d_nnz, scratch, s));
     PS_TRY(read_back(&h_nnz, d_nnz, sizeof(h_nnz), s));
   } else if (fast) {
-    PS_TRY(dedup_dispatch<KeyT>(sk, sp, nnz, g.cbits, DD_FAST, dtype, reduce, out_row, out_col, out_value, nullptr,
-                                d_nnz, scratch, s));
+    PS_TRY(dedup_dispatch<KeyT>(sk, sp, nnz, g.cbits, M, DD_FAST, dtype, reduce, out_row, out_col, out_value, nullptr,
+                                out_rowptr, d_nnz, scratch, s));
     PS_TRY(read_back(&h_nnz, d_nnz, sizeof(h_nnz), s));
   } else {
     PS_SCRATCH(run_start, scratch, int64_t, nnz + 1);
-    PS_TRY(dedup_dispatch<KeyT>(sk, sp, nnz, g.cbits, DD_PTR, dtype, reduce, out_row, out_col, nullptr, run_start,
-                                d_nnz, scratch, s));
+    PS_TRY(dedup_dispatch<KeyT>(sk, sp, nnz, g.cbits, M, DD_PTR, dtype, reduce, out_row, out_col, nullptr, run_start,
+                                out_rowptr, d_nnz, scratch, s));
     PS_TRY(read_back(&h_nnz, d_nnz, sizeof(h_nnz), s));
     PS_TRY(segment_reduce_launch(value, dtype, width, run_start, h_nnz, reduce, out_value, psorted, nnz, s));
   }
@@ -274,14 +350,14 @@ int ps_sort_coo(const int64_t *row, const int64_t *col, int64_t nnz, int64_t M, 
   cudaStream_t s = (cudaStream_t)stream;
   if (g.bits <= 32)
     return sort_impl<uint32_t>(row, col, nnz, g, value, dtype, width, false, PS_SUM, out_row, out_col, out_value,
-                               out_perm, nullptr, s);
+                               out_perm, nullptr, M, nullptr, s);
   return sort_impl<uint64_t>(row, col, nnz, g, value, dtype, width, false, PS_SUM, out_row, out_col, out_value, out_perm,
-                             nullptr, s);
+                             nullptr, M, nullptr, s);
 }
 
 int ps_coalesce(const int64_t *row, const int64_t *col, int64_t nnz, int64_t M, int64_t N, const void *value, int dtype,
-                int64_t width, int reduce, int64_t *out_row, int64_t *out_col, void *out_value, int64_t *host_nnz_out,
-                void *stream) {
+                int64_t width, int reduce, int64_t *out_row, int64_t *out_col, void *out_value, int64_t *out_rowptr,
+                int64_t *host_nnz_out, void *stream) {
   PS_CHECK(nnz >= 0 && M >= 0 && N >= 0, "coalesce: negative size");
   PS_CHECK(nnz < (int64_t(1) << 32), "coalesce: nnz=%lld exceeds the 2^32-1 entries per call this build supports",
            (long long)nnz);
@@ -289,15 +365,18 @@ int ps_coalesce(const int64_t *row, const int64_t *col, int64_t nnz, int64_t M, 
   PS_CHECK(reduce >= PS_SUM && reduce <= PS_MAX, "coalesce: bad reduce %d", reduce);
   PS_TRY(check_value_args(value, out_value, dtype, width));
   *host_nnz_out = 0;
-  if (nnz == 0) return PS_OK;
+  cudaStream_t s = (cudaStream_t)stream;
+  if (nnz == 0) {
+    if (out_rowptr) PS_CUDA(cudaMemsetAsync(out_rowptr, 0, sizeof(int64_t) * (size_t)(M + 1), s));
+    return PS_OK;
+  }
   KeyGeom g;
   PS_TRY(key_geometry(M, N, &g));
-  cudaStream_t s = (cudaStream_t)stream;
   if (g.bits <= 32)
     return sort_impl<uint32_t>(row, col, nnz, g, value, dtype, width, true, reduce, out_row, out_col, out_value, nullptr,
-                               host_nnz_out, s);
+                               host_nnz_out, M, out_rowptr, s);
   return sort_impl<uint64_t>(row, col, nnz, g, value, dtype, width, true, reduce, out_row, out_col, out_value, nullptr,
-                             host_nnz_out, s);
+                             host_nnz_out, M, out_rowptr, s);
 }
 
 int ps_coalesce_sorted(const int64_t *row, const int64_t *col, int64_t nnz, const void *value, int dtype, int64_t width,
@@ -318,17 +397,17 @@ int ps_coalesce_sorted(const int64_t *row, const int64_t *col, int64_t nnz, cons
   PS_SCRATCH(d_nnz, scratch, long long, 1);
   long long h_nnz = 0;
   if (!value) {
-    PS_TRY(dedup_dispatch<uint64_t>(sk, PaySrc{nullptr, PSRC_IOTA}, nnz, cbits, DD_INDEX_ONLY, dtype, reduce, out_row,
-                                    out_col, nullptr, nullptr, d_nnz, scratch, s));
+    PS_TRY(dedup_dispatch<uint64_t>(sk, PaySrc{nullptr, PSRC_IOTA}, nnz, cbits, 0, DD_INDEX_ONLY, dtype, reduce, out_row,
+                                    out_col, nullptr, nullptr, nullptr, d_nnz, scratch, s));
     PS_TRY(read_back(&h_nnz, d_nnz, sizeof(h_nnz), s));
   } else if (fast_value(dtype, width)) {
-    PS_TRY(dedup_dispatch<uint64_t>(sk, PaySrc{value, pay_src_mode(dtype)}, nnz, cbits, DD_FAST, dtype, reduce, out_row,
-                                    out_col, out_value, nullptr, d_nnz, scratch, s));
+    PS_TRY(dedup_dispatch<uint64_t>(sk, PaySrc{value, pay_src_mode(dtype)}, nnz, cbits, 0, DD_FAST, dtype, reduce, out_row,
+                                    out_col, out_value, nullptr, nullptr, d_nnz, scratch, s));
     PS_TRY(read_back(&h_nnz, d_nnz, sizeof(h_nnz), s));
   } else {
     PS_SCRATCH(run_start, scratch, int64_t, nnz + 1);
-    PS_TRY(dedup_dispatch<uint64_t>(sk, PaySrc{nullptr, PSRC_IOTA}, nnz, cbits, DD_PTR, dtype, reduce, out_row, out_col,
-                                    nullptr, run_start, d_nnz, scratch, s));
+    PS_TRY(dedup_dispatch<uint64_t>(sk, PaySrc{nullptr, PSRC_IOTA}, nnz, cbits, 0, DD_PTR, dtype, reduce, out_row, out_col,
+                                    nullptr, run_start, nullptr, d_nnz, scratch, s));
     PS_TRY(read_back(&h_nnz, d_nnz, sizeof(h_nnz), s));
     PS_TRY(segment_reduce_launch(value, dtype, width, run_start, h_nnz, reduce, out_value, nullptr, nnz, s));
   }

@@ -200,21 +200,23 @@ def sort_coo(row, col, value, M: int, N: int, want_perm: bool = False):
     return out_row, out_col, out_value, out_perm
 
 
-def coalesce(row, col, value, M: int, N: int, reduce: str = "add"):
+def coalesce(row, col, value, M: int, N: int, reduce: str = "add", want_rowptr: bool = False):
     """coalesce.py:8-29 fused: packed-key radix sort + run detection + segmented reduce.
-    Returns (row', col', value')."""
+    Returns (row', col', value'), plus rowptr' (= ind2ptr(row', M), written by the same pass) when asked."""
     row, col = _idx(row, "row"), _idx(col, "col")
     value = None if value is None else _dev(value, "value")
     v, dt, w = _value_args(value)
     nnz = row.numel()
     out_row, out_col = _new(row, nnz), _new(row, nnz)
     out_value = None if value is None else torch.empty_like(value)
+    rowptr = _new(row, M + 1) if want_rowptr else None
     h = _host_i64()
     with torch.cuda.device(row.device):
         _lib.call("ps_coalesce", _p(row), _p(col), nnz, M, N, _p(v), dt, w, reduce_code(reduce), _p(out_row),
-                  _p(out_col), _p(out_value), h, _stream(row))
+                  _p(out_col), _p(out_value), _p(rowptr), h, _stream(row))
     k = int(h[0])
-    return out_row[:k], out_col[:k], (None if out_value is None else out_value[:k])
+    res = (out_row[:k], out_col[:k], (None if out_value is None else out_value[:k]))
+    return res + (rowptr,) if want_rowptr else res
 
 
 def coalesce_sorted(row, col, value, reduce: str = "add"):

@@ -122,13 +122,42 @@ class SparseStorage(object):
         self._csr2csc = csr2csc
         self._csc2csr = csc2csr
 
-        # ---- sort-on-construct (storage.py:158-171)
-        if not is_sorted and nnz > 0:
-            in_order, _ = ops.coo_order(self.row(), col)
-            if not in_order:
-                self._row, self._col, self._value, _ = ops.sort_coo(self.row(), col, value, M, N)
-                self._csr2csc = None
-                self._csc2csr = None
+        # ---- sort-on-construct (storage.py:158-171), DEFERRED to the first access of row / col / value: a
+        # `coalesce()` that follows the constructor then runs sort + dedup + rowptr as one fused pipeline
+        # (ops.coalesce) instead of sort -> write -> re-read -> dedup.  Every accessor sees sorted data.
+        self._pending_sort = (not is_sorted) and nnz > 0
+
+    def _ensure_sorted(self) -> None:
+        if not self.__dict__.get("_pending_sort", False):
+            return
+        self._pending_sort = False
+        d = self.__dict__
+        if d["_row_raw"] is None:
+            d["_row_raw"] = ops.ptr2ind(self._rowptr, d["_col_raw"].numel())  # storage.py:202
+        in_order, _ = ops.coo_order(d["_row_raw"], d["_col_raw"])
+        if not in_order:
+            M, N = self._sparse_sizes
+            d["_row_raw"], d["_col_raw"], d["_value_raw"], _ = ops.sort_coo(d["_row_raw"], d["_col_raw"],
+                                                                           d["_value_raw"], M, N)
+            self._csr2csc = None
+            self._csc2csr = None
+
+    def _sorted_field(name):  # noqa: N805  (property factory, evaluated in the class body)
+        raw = name + "_raw"
+
+        def get(self):
+            self._ensure_sorted()
+            return self.__dict__[raw]
+
+        def set_(self, v):
+            self.__dict__[raw] = v
+
+        return property(get, set_)
+
+    _row = _sorted_field("_row")
+    _col = _sorted_field("_col")
+    _value = _sorted_field("_value")
+    del _sorted_field
 
     @classmethod
     def empty(cls, device="cuda"):
@@ -334,6 +363,19 @@ class SparseStorage(object):
 
     def coalesce(self, reduce: str = "add"):
         """storage.py:454-486; returns `self` when nothing has to be merged (:459-460)."""
+        d = self.__dict__
+        if (d.get("_pending_sort", False) and d["_row_raw"] is not None and self._rowptr is None
+                and self._csr2csc is None and self._csc2csr is None and self._colptr is None):
+            # constructor immediately followed by coalesce(): one fused sort + dedup + rowptr pipeline
+            M, N = self._sparse_sizes
+            row, col, value, rowptr = ops.coalesce(d["_row_raw"], d["_col_raw"], d["_value_raw"], M, N, reduce, True)
+            if row.numel() == d["_col_raw"].numel():  # nothing merged: this object simply becomes sorted
+                d["_row_raw"], d["_col_raw"], d["_value_raw"] = row, col, value
+                self._rowptr = rowptr
+                self._pending_sort = False
+                return self
+            return SparseStorage(row=row, rowptr=rowptr, col=col, value=value, sparse_sizes=self._sparse_sizes,
+                                 is_sorted=True, trust_data=True)
         if self._col.numel() <= 1:
             return self
         row, col, value = ops.coalesce_sorted(self.row(), self._col, self._value, reduce)

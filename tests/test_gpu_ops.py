@@ -152,3 +152,56 @@ def test_coalesce_empty_and_single(ops):
     one = dev(np.array([3], I64))
     r, c, v = ops.coalesce(one, one, dev(np.array([2.5], np.float32)), 5, 5)
     assert host(r).tolist() == [3] and host(v).tolist() == [2.5]
+
+
+@pytest.mark.parametrize("M,N,nnz", [(1, 1, 1), (7, 5, 3), (10000, 10000, 100000), (3, 3, 50000),
+                                     (2500000, 1000, 40000), (300, 2500000, 200000)])
+@pytest.mark.parametrize("with_value", [True, False])
+def test_coalesce_emits_rowptr(ops, M, N, nnz, with_value):
+    """ps_coalesce's out_rowptr == ind2ptr(row', M) (storage.py:211-222), including empty leading / trailing /
+    interior rows (M far larger than the number of occupied rows) and rows spanning many tiles."""
+    rng = np.random.default_rng(M + nnz)
+    row, col = _random_coo(rng, M, N, nnz, 0.2)
+    val = rng.random(nnz).astype(np.float32) if with_value else None
+    r, c, v, rowptr = ops.coalesce(dev(row), dev(col), None if val is None else dev(val), M, N, "add", True)
+    idx, want = np_ref.coalesce(np.stack([row, col]), val, M, N, "add")
+    assert np.array_equal(host(r), idx[0]) and np.array_equal(host(c), idx[1])
+    assert np.array_equal(host(rowptr), np.searchsorted(idx[0], np.arange(M + 1), side="left"))
+    if with_value:
+        np.testing.assert_allclose(host(v), want, rtol=2e-5)
+    e = dev(np.array([], I64))
+    assert host(ops.coalesce(e, e, None, 4, 4, "add", True)[3]).tolist() == [0] * 5
+
+
+def test_lazy_sort_then_coalesce_is_fused_and_equivalent():
+    """SparseStorage defers sort-on-construct (storage.py:158-171) to the first accessor; coalesce() right after the
+    constructor takes the fused path.  Both orders of use must give the reference's results, and coalesce() must
+    return the SAME object when nothing is merged (storage.py:459-460)."""
+    import paddle_sparse_b200 as ps
+    rng = np.random.default_rng(21)
+    M = N = 500
+    row, col = _random_coo(rng, M, N, 4000, 0.3)
+    val = rng.random(4000).astype(np.float32)
+    want = np_ref.SparseStorage(row=row, col=col, value=val, sparse_sizes=(M, N))
+    wc = want.coalesce("add")
+    a = ps.SparseStorage(row=dev(row), col=dev(col), value=dev(val), sparse_sizes=(M, N))
+    ca = a.coalesce("add")  # fused: the constructor has not sorted yet
+    assert ca is not a
+    assert np.array_equal(host(ca.row()), wc.row()) and np.array_equal(host(ca.col()), wc.col())
+    np.testing.assert_allclose(host(ca.value()), wc.value(), rtol=2e-6)
+    assert np.array_equal(host(ca.rowptr()), wc.rowptr()) and ca.cached_keys() == []
+    # the original object still behaves like the reference's sorted, uncoalesced storage
+    assert np.array_equal(host(a.row()), want.row()) and np.array_equal(host(a.col()), want.col())
+    assert np.array_equal(host(a.value()), want.value())
+    b = ps.SparseStorage(row=dev(row), col=dev(col), value=dev(val), sparse_sizes=(M, N))
+    assert np.array_equal(host(b.col()), want.col())  # accessor first: sorts, then the sorted-input path
+    cb = b.coalesce("add")
+    assert np.array_equal(host(cb.col()), wc.col())
+    # nothing to merge: same object comes back, now sorted
+    key = np.unique(row * N + col)
+    perm = rng.permutation(key.size)
+    r2, c2 = (key // N)[perm].astype(I64), (key % N)[perm].astype(I64)
+    d = ps.SparseStorage(row=dev(r2), col=dev(c2), sparse_sizes=(M, N))
+    assert d.coalesce() is d
+    assert np.array_equal(host(d.row()), key // N) and np.array_equal(host(d.col()), key % N)
+    assert np.array_equal(host(d.rowptr()), np.searchsorted(key // N, np.arange(M + 1)))
