@@ -27,6 +27,10 @@ template <> __device__ __forceinline__ __nv_bfloat16 pay_as<__nv_bfloat16>(uint3
 }
 template <> __device__ __forceinline__ __half pay_as<__half>(uint32_t p) { return __ushort_as_half((unsigned short)p); }
 
+}  // namespace ps
+#include "local_sort.cuh"
+namespace ps {
+
 // One tile = THREADS*ITEMS consecutive sorted entries, held in shared memory; thread t looks at entries
 // t, t + THREADS, ... (conflict-free).  Run heads are ranked with ballots + one small scan, the tile's offset comes
 // from a decoupled look-back, every head folds its run in sorted (= stable) order, the compacted (key, value)
@@ -40,7 +44,8 @@ dedup_kernel(KeySrc ksrc, PaySrc psrc, int64_t n, int cbits, int64_t M, int64_t 
              int64_t *__restrict__ out_rowptr, uint64_t *state /*[0]=ticket,[1..]=tiles*/, long long *d_nnz_out) {
   constexpr int TILE = THREADS * ITEMS, WARPS = THREADS / 32;
   using A = typename Acc<T>::type;
-  __shared__ KeyT s_key[TILE + 1];  // s_key[0] = key preceding the tile; later the compacted keys
+  __shared__ KeyT s_key[TILE + 2];  // s_key[0] = key preceding the tile, s_key[tile_n + 1] = key following it;
+                                    // later the compacted keys
   __shared__ uint32_t s_pay[MODE == DD_FAST ? TILE : 1];
   __shared__ uint32_t s_wcnt[ITEMS * WARPS];
   __shared__ int64_t s_tile, s_excl;
@@ -61,6 +66,7 @@ dedup_kernel(KeySrc ksrc, PaySrc psrc, int64_t n, int cbits, int64_t M, int64_t 
     }
   }
   if (tid == 0) s_key[0] = tile_base > 0 ? load_key<KeyT>(ksrc, tile_base - 1) : KeyT(0);
+  if (tid == 32 && tile_base + tile_n < n) s_key[tile_n + 1] = load_key<KeyT>(ksrc, tile_base + tile_n);
   __syncthreads();
 
   // ---- run heads, ranked in entry order (k, warp, lane)
@@ -133,7 +139,7 @@ dedup_kernel(KeySrc ksrc, PaySrc psrc, int64_t n, int cbits, int64_t M, int64_t 
         ++jj;
       }
       int64_t len = jj - j;
-      if (jj == tile_n) {  // the run may continue past the tile: finish it from global memory
+      if (jj == tile_n && tile_base + tile_n < n && s_key[tile_n + 1] == key) {  // the run continues past the tile
         int64_t g = tile_base + tile_n;
         while (g < n && load_key<KeyT>(ksrc, g) == key) {
           acc = Red<RED, A>::op(acc, to_acc<T>(pay_as<T>(load_pay(psrc, g))));
@@ -255,13 +261,132 @@ static int check_value_args(const void *value, const void *out_value, int dtype,
 }
 
 // ------------------------------------------------------------------------------------------------
+// Hybrid coalesce (local_sort.cuh): top-T-bit buckets by one or two one-sweep passes, then one CTA per bucket sorts,
+// merges and writes the final arrays.  *used = false (nothing written) when the shape or the bucket sizes rule it
+// out; the caller then runs the plain LSD pipeline.  One extra host read (the largest bucket) decides.
+int hybrid_variant();  // PS_HYBRID=0 disables (bench knob)
+
+template <typename T, int RED, bool HAS_VALUE>
+static int ls_launch(const uint32_t *lowkeys, const uint32_t *lowvals, const unsigned int *bucket_off, int nb, int R,
+                     int cbits, int64_t M, int64_t *out_row, int64_t *out_col, void *out_value, int64_t *out_rowptr,
+                     uint64_t *state, long long *d_nnz, cudaStream_t s) {
+  auto kern = ls_sort_dedup_kernel<T, RED, HAS_VALUE>;
+  const size_t smem = sizeof(LsSmem<HAS_VALUE>);
+  static bool configured = false;
+  if (!configured) {
+    PS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured = true;
+  }
+  int grid = sm_count() * 2;
+  if (grid > nb) grid = nb;
+  {
+    ProfScope prof(PROF_DEDUP, s);
+    kern<<<grid, LS_SORT_THREADS, smem, s>>>(lowkeys, lowvals, bucket_off, nb, R, cbits, M, out_row, out_col,
+                                            reinterpret_cast<T *>(out_value), out_rowptr, state, d_nnz);
+  }
+  PS_LAUNCH_OK();
+  return PS_OK;
+}
+
+static int hybrid_coalesce(const int64_t *row, const int64_t *col, int64_t nnz, int rbits, int cbits, int64_t M,
+                           const void *value, int dtype, int reduce, int64_t *out_row, int64_t *out_col,
+                           void *out_value, int64_t *out_rowptr, int64_t *host_nnz_out, bool *used, cudaStream_t s) {
+  *used = false;
+  const int K = rbits + cbits;
+  if (!hybrid_variant() || nnz < (int64_t(1) << 16) || K <= 32) return PS_OK;
+  // T: buckets of about LS_CAP / 2 entries on average; a bucket must be a whole range of rows (T <= rbits)
+  int T = bits_for(ceil_div(nnz, LS_CAP / 2));
+  if (T < K - 32) T = K - 32;  // the bucket-local key must fit 32 bits
+  if (T > LS_MAX_T) T = LS_MAX_T;
+  if (T > rbits) T = rbits;
+  const int R = K - T;
+  if (T < 1 || R > 32 || nnz / (int64_t(1) << T) > LS_CAP * 3 / 4) return PS_OK;
+  const int nb = 1 << T;
+  Scratch scratch(s);
+
+  // bucket sizes -> offsets, largest bucket, bin bases of the global passes
+  const SortPlan gp = make_sort_plan(T, rs_geometry<uint64_t, 1>().rbits);  // the plan radix_sort_pairs will use
+  if (gp.passes > 2) return PS_OK;
+  LsPlan lp;
+  lp.passes = gp.passes;
+  for (int p = 0; p < gp.passes; ++p) { lp.pbegin[p] = gp.begin[p]; lp.pbits[p] = gp.bits[p]; }
+  PS_SCRATCH(gcount, scratch, unsigned int, (size_t)nb);
+  PS_SCRATCH(bucket_off, scratch, unsigned int, (size_t)nb + 1);
+  PS_SCRATCH(ghist, scratch, unsigned long long, (size_t)2 * RS_MAX_RADIX);
+  PS_SCRATCH(d_max, scratch, unsigned int, 2);
+  PS_CUDA(cudaMemsetAsync(gcount, 0, sizeof(unsigned int) * (size_t)nb, s));
+  {
+    static bool configured = false;
+    if (!configured) {
+      PS_CUDA(cudaFuncSetAttribute(ls_bucket_hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   (int)(sizeof(unsigned int) << LS_MAX_T)));
+      configured = true;
+    }
+    ProfScope prof(PROF_RS_HIST, s);
+    ls_bucket_hist_kernel<<<sm_count() * 2, 1024, sizeof(unsigned int) * (size_t)nb, s>>>(row, col, nnz, cbits, R, T,
+                                                                                        gcount);
+  }
+  PS_LAUNCH_OK();
+  ls_derive_kernel<<<1, 1024, 0, s>>>(gcount, T, lp, bucket_off, ghist, d_max);
+  PS_LAUNCH_OK();
+  unsigned int h_max = 0;
+  PS_TRY(read_back(&h_max, d_max, sizeof(h_max), s));
+  if (h_max > (unsigned)LS_CAP) return PS_OK;  // skewed rows: the plain LSD sort handles any distribution
+
+  // global passes on key bits [R, K): the last one keeps only the low R bits of the key
+  PS_SCRATCH(k0, scratch, uint64_t, nnz);
+  PS_SCRATCH(p0, scratch, uint32_t, nnz);
+  PS_SCRATCH(lowkeys, scratch, uint32_t, nnz);
+  PS_SCRATCH(lowvals, scratch, uint32_t, nnz);
+  KeySrc ksrc{row, col, KSRC_PACK_COO, cbits};
+  PaySrc psrc = value ? PaySrc{value, pay_src_mode(dtype)} : PaySrc{nullptr, PSRC_NONE};
+  PayDst pdst = value ? PayDst{lowvals, PDST_U32} : PayDst{nullptr, PDST_NONE};
+  PS_TRY(radix_sort_pairs<uint64_t>(ksrc, psrc, nnz, T, k0, nullptr, p0, nullptr, KeyDst{lowkeys, nullptr, KDST_LOW32, R},
+                                    pdst, scratch, s, R, ghist));
+
+  PS_SCRATCH(state, scratch, uint64_t, (size_t)nb + 1);
+  PS_CUDA(cudaMemsetAsync(state, 0, sizeof(uint64_t) * ((size_t)nb + 1), s));
+  PS_SCRATCH(d_nnz, scratch, long long, 1);
+  int rc = PS_ERR_ARG;
+#define PS_LS(T_)                                                                                              \
+  PS_DISPATCH_REDUCE(reduce, RED, rc = (ls_launch<T_, RED, true>(lowkeys, lowvals, bucket_off, nb, R, cbits, M, \
+                                                                 out_row, out_col, out_value, out_rowptr, state, \
+                                                                 d_nnz, s)))
+  if (!value) {
+    rc = ls_launch<float, PS_SUM, false>(lowkeys, nullptr, bucket_off, nb, R, cbits, M, out_row, out_col, nullptr,
+                                         out_rowptr, state, d_nnz, s);
+  } else {
+    switch (dtype) {
+      case PS_F32: PS_LS(float); break;
+      case PS_I32: PS_LS(int32_t); break;
+      case PS_BF16: PS_LS(__nv_bfloat16); break;
+      case PS_F16: PS_LS(__half); break;
+      default: break;
+    }
+  }
+#undef PS_LS
+  PS_TRY(rc);
+  long long h_nnz = 0;
+  PS_TRY(read_back(&h_nnz, d_nnz, sizeof(h_nnz), s));
+  *host_nnz_out = (int64_t)h_nnz;
+  *used = true;
+  return PS_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
 // sort + (optionally) dedup, shared by ps_sort_coo and ps_coalesce
 template <typename KeyT>
 int sort_impl(const int64_t *row, const int64_t *col, int64_t nnz, KeyGeom g, const void *value, int dtype,
               int64_t width, bool dedup, int reduce, int64_t *out_row, int64_t *out_col, void *out_value,
               int64_t *out_perm, int64_t *host_nnz_out, int64_t M, int64_t *out_rowptr, cudaStream_t s) {
-  Scratch scratch(s);
   const bool fast = value && fast_value(dtype, width) && !out_perm;
+  if (dedup && sizeof(KeyT) == 8 && (fast || !value)) {
+    bool used = false;
+    PS_TRY(hybrid_coalesce(row, col, nnz, g.rbits, g.cbits, M, value, dtype, reduce, out_row, out_col, out_value,
+                           out_rowptr, host_nnz_out, &used, s));
+    if (used) return PS_OK;
+  }
+  Scratch scratch(s);
   const bool need_perm = (value && !fast) || out_perm;
   PS_SCRATCH(k0, scratch, KeyT, nnz);
   PS_SCRATCH(k1, scratch, KeyT, nnz);

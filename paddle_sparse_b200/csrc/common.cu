@@ -64,6 +64,15 @@ int rs_variant() {
   return v;
 }
 
+int hybrid_variant() {
+  static int v = -1;
+  if (v < 0) {
+    const char *e = getenv("PS_HYBRID");
+    v = e ? atoi(e) : 1;
+  }
+  return v;
+}
+
 int sm_count() {
   static int cached[64] = {0};
   int dev = 0;

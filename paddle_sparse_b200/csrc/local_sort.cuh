@@ -1,0 +1,328 @@
+// Hybrid coalesce: bucket by the TOP bits with one-sweep passes, then sort every bucket INSIDE shared memory.
+//
+// An LSD sort of the 44-bit (row, col) key of an ogbn-products-shaped graph needs six passes over HBM.  Here the
+// top T <= 14 key bits are sorted globally (one or two passes of the one-sweep kernel, radix_sort.cuh), which
+// leaves 2^T buckets of a few thousand entries that are already in bucket order; one CTA then loads a bucket
+// (32-bit low key + 32-bit value), sorts it with LSD passes that never leave the SM (ranking by shared-memory
+// atomics, the same column scans as the global pass), merges duplicates, and writes the final int64 row / col,
+// the reduced values and the rowptr of its own row range - coalesced, straight to their final place.
+//   reference behaviour: storage.py:158-171 (sort-on-construct) + :454-486 (coalesce) + :211-222 (rowptr)
+// Needs: key bits - T <= 32, T <= row bits (a bucket is a whole range of rows), every bucket <= LS_CAP entries
+// (checked on the histogram, otherwise the caller falls back to the plain LSD sort).
+#pragma once
+#include "common.cuh"
+#include "radix_sort.cuh"
+
+namespace ps {
+
+constexpr int LS_THREADS = 1024;
+constexpr int LS_ITEMS = 8;
+constexpr int LS_CAP = LS_THREADS * LS_ITEMS;  // entries one CTA sorts in shared memory
+constexpr int LS_MAX_T = 14;                    // 2^14 bucket counters = 64 KB of shared memory in the histogram
+
+// ---- histogram of the top T key bits (bucket sizes); keys are packed on the fly from the int64 arrays
+__global__ void __launch_bounds__(1024)
+ls_bucket_hist_kernel(const int64_t *__restrict__ row, const int64_t *__restrict__ col, int64_t n, int cbits, int R,
+                      int T, unsigned int *__restrict__ gcount /*[2^T]*/) {
+  extern __shared__ unsigned int ls_sh[];
+  const int nb = 1 << T;
+  for (int j = threadIdx.x; j < nb; j += blockDim.x) ls_sh[j] = 0;
+  __syncthreads();
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  for (; i + 3 * stride < n; i += 4 * stride) {
+    uint64_t r[4], c[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) r[q] = (uint64_t)ld_stream(row + i + q * stride);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) c[q] = (uint64_t)ld_stream(col + i + q * stride);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) atomicAdd(&ls_sh[(unsigned)(((r[q] << cbits) | c[q]) >> R)], 1u);
+  }
+  for (; i < n; i += stride) {
+    const uint64_t k = ((uint64_t)ld_stream(row + i) << cbits) | (uint64_t)ld_stream(col + i);
+    atomicAdd(&ls_sh[(unsigned)(k >> R)], 1u);
+  }
+  __syncthreads();
+  for (int j = threadIdx.x; j < nb; j += blockDim.x)
+    if (ls_sh[j]) atomicAdd(&gcount[j], ls_sh[j]);
+}
+
+// ---- one CTA: bucket offsets (exclusive scan), the largest bucket, and the scanned digit histograms of the
+// global passes (pass p sorts bucket-id bits [pbegin[p], pbegin[p] + pbits[p]))
+struct LsPlan {
+  int passes, pbegin[2], pbits[2];
+};
+__global__ void __launch_bounds__(1024)
+ls_derive_kernel(const unsigned int *__restrict__ gcount, int T, LsPlan plan, unsigned int *__restrict__ bucket_off,
+                 unsigned long long *__restrict__ ghist /*[passes][512]*/, unsigned int *__restrict__ max_bucket) {
+  __shared__ unsigned long long dig[2][RS_MAX_RADIX];
+  __shared__ unsigned int wsum[33];
+  __shared__ unsigned int smax;
+  const unsigned tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+  for (int j = tid; j < 2 * RS_MAX_RADIX; j += 1024) (&dig[0][0])[j] = 0;
+  if (tid == 0) smax = 0;
+  __syncthreads();
+  const int nb = 1 << T;
+  const int per = (nb + 1023) / 1024;  // consecutive buckets per thread
+  unsigned int local = 0, mx = 0;
+  for (int q = 0; q < per; ++q) {
+    const int b = tid * per + q;
+    if (b < nb) {
+      const unsigned int c = gcount[b];
+      local += c;
+      mx = c > mx ? c : mx;
+      if (c) {
+        for (int p = 0; p < plan.passes; ++p)
+          atomicAdd(&dig[p][(b >> plan.pbegin[p]) & ((1 << plan.pbits[p]) - 1)], (unsigned long long)c);
+      }
+    }
+  }
+  atomicMax(&smax, mx);
+  unsigned int total;
+  const unsigned int excl = block_exclusive_scan<unsigned int, 1024>(local, wsum, &total);
+  unsigned int run = excl;
+  for (int q = 0; q < per; ++q) {
+    const int b = tid * per + q;
+    if (b < nb) {
+      bucket_off[b] = run;
+      run += gcount[b];
+    }
+  }
+  if (tid == 1023) bucket_off[nb] = total;
+  __syncthreads();
+  if (tid == 0) *max_bucket = smax;
+  // exclusive scans of the digit histograms: warp p scans pass p (16 digits per lane)
+  if (warp < (unsigned)plan.passes) {
+    unsigned long long v[16], sum = 0;
+    for (int q = 0; q < 16; ++q) {
+      v[q] = dig[warp][lane * 16 + q];
+      sum += v[q];
+    }
+    unsigned long long inc = sum;
+    for (int d = 1; d < 32; d <<= 1) {
+      const unsigned long long o = __shfl_up_sync(0xffffffffu, inc, d);
+      if (lane >= (unsigned)d) inc += o;
+    }
+    unsigned long long r = inc - sum;
+    for (int q = 0; q < 16; ++q) {
+      ghist[warp * RS_MAX_RADIX + lane * 16 + q] = r;
+      r += v[q];
+    }
+  }
+}
+
+// ---- the in-shared-memory sort + dedup of one bucket per CTA round
+constexpr int LS_SORT_THREADS = 512;   // two CTAs per SM
+constexpr int LS_SORT_ITEMS = 16;      // LS_CAP = 512 * 16
+constexpr int LS_WARPS = LS_SORT_THREADS / 32;
+constexpr int LS_ROW = 256 / 2 + 1;    // counter row in words (odd: conflict-free column reads)
+static_assert(LS_SORT_THREADS * LS_SORT_ITEMS == LS_CAP, "bucket capacity");
+
+template <bool HAS_VALUE>
+struct LsSmem {
+  uint32_t keys[LS_CAP];
+  uint32_t vals[HAS_VALUE ? LS_CAP : 1];
+  uint32_t cnt[LS_WARPS][LS_ROW];  // two 16-bit counters per word, later group starts
+  uint32_t scan_tmp[32];
+  uint32_t wcnt[LS_SORT_ITEMS * LS_WARPS];
+  long long bucket, excl;
+  int heads;
+};
+
+template <typename T, int RED, bool HAS_VALUE>
+__global__ void __launch_bounds__(LS_SORT_THREADS, 2)
+ls_sort_dedup_kernel(const uint32_t *__restrict__ lowkeys, const uint32_t *__restrict__ lowvals,
+                     const unsigned int *__restrict__ bucket_off, int nb, int R, int cbits, int64_t M,
+                     int64_t *__restrict__ out_row, int64_t *__restrict__ out_col, T *__restrict__ out_value,
+                     int64_t *__restrict__ out_rowptr, uint64_t *state /*[0]=ticket,[1..]=buckets*/,
+                     long long *d_nnz_out) {
+  using A = typename Acc<T>::type;
+  constexpr int THREADS = LS_SORT_THREADS, ITEMS = LS_SORT_ITEMS, WARPS = LS_WARPS, DPW = 256 / WARPS;
+  extern __shared__ __align__(16) unsigned char ls_raw[];
+  LsSmem<HAS_VALUE> &sm = *reinterpret_cast<LsSmem<HAS_VALUE> *>(ls_raw);
+  const unsigned tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+  const unsigned lt = lanemask_lt();
+  uint32_t *my_cnt = sm.cnt[warp];
+  const int passes = (R + 7) / 8;
+  const uint64_t cmask = (uint64_t(1) << cbits) - 1;
+
+  while (true) {
+    __syncthreads();  // the previous bucket is completely written out
+    if (tid == 0) sm.bucket = (long long)atomicAdd((unsigned long long *)state, 1ull);
+    __syncthreads();
+    const int64_t bucket = sm.bucket;
+    if (bucket >= nb) break;
+    const uint32_t start = bucket_off[bucket];
+    const int cnt = (int)(bucket_off[bucket + 1] - start);
+    // balanced warp-blocked layout: warp w holds entries [w*32*ie, (w+1)*32*ie), item i of lane l is entry
+    // w*32*ie + i*32 + l: ranking order (warp, item, lane) == entry order, which keeps every pass stable
+    const int ie = (cnt + THREADS - 1) / THREADS;
+    const int wb0 = warp * 32 * ie;
+    uint32_t key[ITEMS], val[ITEMS];
+#pragma unroll
+    for (int i = 0; i < ITEMS; ++i) {
+      const int j = wb0 + i * 32 + lane;
+      key[i] = 0;
+      val[i] = 0;
+      if (i < ie && j < cnt) {
+        key[i] = ld_stream(lowkeys + start + j);
+        if (HAS_VALUE) val[i] = ld_stream(lowvals + start + j);
+      }
+    }
+    // ---- LSD passes inside shared memory
+    for (int p = 0; p < passes; ++p) {
+      const int shift = p * 8;
+      const unsigned mask = (R - shift) >= 8 ? 255u : ((1u << (R - shift)) - 1u);
+#pragma unroll
+      for (int q = lane; q < LS_ROW; q += 32) my_cnt[q] = 0;
+      __syncwarp();
+      unsigned rank[ITEMS];
+#pragma unroll
+      for (int i = 0; i < ITEMS; ++i) {
+        rank[i] = 0;
+        if (i < ie && wb0 + i * 32 + (int)lane < cnt) {
+          const unsigned d = (key[i] >> shift) & mask;
+          const unsigned sh = (d & 1u) * 16u;
+          rank[i] = (atomicAdd(&my_cnt[d >> 1], 1u << sh) >> sh) & 0xffffu;  // lanes served in order: rs_pass_kernel
+        }
+      }
+      __syncthreads();
+      // column scans: lane l reads the counter of warp l for this warp's DPW digits (see rs_pass_kernel phase 3)
+      uint16_t *col = reinterpret_cast<uint16_t *>(&sm.cnt[lane < (unsigned)WARPS ? lane : 0][0]) + warp * DPW;
+      uint32_t wsum = 0, below = 0;
+#pragma unroll
+      for (int k = 0; k < DPW; ++k) {
+        const uint32_t c = lane < (unsigned)WARPS ? (uint32_t)col[k] : 0u;
+        uint32_t inc = c;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+          const uint32_t o = __shfl_up_sync(0xffffffffu, inc, d);
+          if (lane >= (unsigned)d) inc += o;
+        }
+        if (lane < (unsigned)WARPS) col[k] = (uint16_t)(inc - c);
+        const uint32_t t = __shfl_sync(0xffffffffu, inc, 31);
+        if (lane == (unsigned)k) below = wsum;
+        wsum += t;
+      }
+      if (lane == 0) sm.scan_tmp[warp] = wsum;
+      __syncthreads();
+      {
+        uint32_t wb = 0;
+#pragma unroll
+        for (int w = 0; w < WARPS; ++w) wb += (w < (int)warp) ? sm.scan_tmp[w] : 0u;
+        const uint32_t dexcl = wb + below;
+#pragma unroll
+        for (int k = 0; k < DPW; ++k) {
+          const uint32_t dk = __shfl_sync(0xffffffffu, dexcl, k);
+          if (lane < (unsigned)WARPS) col[k] = (uint16_t)(dk + col[k]);
+        }
+      }
+      __syncthreads();
+      const uint16_t *my_start = reinterpret_cast<const uint16_t *>(my_cnt);
+#pragma unroll
+      for (int i = 0; i < ITEMS; ++i) {
+        if (i < ie && wb0 + i * 32 + (int)lane < cnt) {
+          const unsigned pos = rank[i] + (unsigned)my_start[(key[i] >> shift) & mask];
+          sm.keys[pos] = key[i];
+          if (HAS_VALUE) sm.vals[pos] = val[i];
+        }
+      }
+      __syncthreads();
+      if (p + 1 < passes) {
+#pragma unroll
+        for (int i = 0; i < ITEMS; ++i) {
+          const int j = wb0 + i * 32 + lane;
+          if (i < ie && j < cnt) {
+            key[i] = sm.keys[j];
+            if (HAS_VALUE) val[i] = sm.vals[j];
+          }
+        }
+      }
+    }
+    // ---- the bucket is sorted in shared memory: run heads (entry order = (item, warp, lane) with the striped
+    // layout j = i*THREADS + tid), their ranks, the bucket's offset in the output by look-back over the buckets
+    unsigned heads = 0, below[ITEMS];
+#pragma unroll
+    for (int i = 0; i < ITEMS; ++i) {
+      below[i] = 0;
+      if (i < ie) {  // uniform
+        const int j = i * THREADS + tid;
+        const bool h = j < cnt && (j == 0 || sm.keys[j] != sm.keys[j - 1]);
+        const unsigned bal = __ballot_sync(0xffffffffu, h);
+        heads |= (unsigned)h << i;
+        below[i] = __popc(bal & lt);
+        if (lane == 0) sm.wcnt[i * WARPS + warp] = __popc(bal);
+      } else if (lane == 0) {
+        sm.wcnt[i * WARPS + warp] = 0;
+      }
+    }
+    __syncthreads();
+    if (warp == 0) {
+      constexpr int PER = ITEMS * WARPS / 32;
+      uint32_t v[PER], sum = 0;
+#pragma unroll
+      for (int q = 0; q < PER; ++q) {
+        v[q] = sm.wcnt[lane * PER + q];
+        sum += v[q];
+      }
+      uint32_t inc = sum;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t o = __shfl_up_sync(0xffffffffu, inc, d);
+        if (lane >= (unsigned)d) inc += o;
+      }
+      uint32_t run = inc - sum;
+#pragma unroll
+      for (int q = 0; q < PER; ++q) {
+        sm.wcnt[lane * PER + q] = run;
+        run += v[q];
+      }
+      const uint32_t total = __shfl_sync(0xffffffffu, inc, 31);
+      const uint64_t pfx = warp_lookback(state + 1, bucket, (uint64_t)total);
+      if (lane == 0) {
+        sm.excl = (long long)pfx;
+        sm.heads = (int)total;
+      }
+    }
+    __syncthreads();
+    const int64_t excl = sm.excl;
+    const int nheads = sm.heads;
+    const uint64_t hi_bits = (uint64_t)bucket << R;
+    // rows owned by this bucket: [rlo, rhi) (the last bucket also owns everything up to M)
+    const int64_t rlo = (int64_t)(hi_bits >> cbits);
+    int64_t rhi = (int64_t)((((uint64_t)bucket + 1) << R) >> cbits);
+    if (bucket == nb - 1 || rhi > M + 1) rhi = M + 1;
+#pragma unroll
+    for (int i = 0; i < ITEMS; ++i) {
+      if (!((heads >> i) & 1u)) continue;
+      const int j = i * THREADS + tid;
+      const uint32_t lk = sm.keys[j];
+      const int64_t o = excl + below[i] + sm.wcnt[i * WARPS + warp];
+      const uint64_t full = hi_bits | lk;
+      const int64_t r = (int64_t)(full >> cbits);
+      out_row[o] = r;  // consecutive lanes hold consecutive heads: coalesced wherever nothing was merged
+      out_col[o] = (int64_t)(full & cmask);
+      if (HAS_VALUE) {
+        A acc = to_acc<T>(pay_as<T>(sm.vals[j]));
+        int jj = j + 1;
+        while (jj < cnt && sm.keys[jj] == lk) {
+          acc = Red<RED, A>::op(acc, to_acc<T>(pay_as<T>(sm.vals[jj])));
+          ++jj;
+        }
+        out_value[o] = from_acc<T>(Red<RED, A>::finish(acc, (int64_t)(jj - j)));
+      }
+      if (out_rowptr) {
+        const int64_t pr = j == 0 ? rlo - 1 : (int64_t)((hi_bits | sm.keys[j - 1]) >> cbits);
+        for (int64_t q = pr + 1; q <= r && q <= M; ++q) out_rowptr[q] = o;
+      }
+    }
+    if (out_rowptr) {  // rows of this bucket after its last entry (all of them when the bucket is empty)
+      const int64_t first = cnt > 0 ? (int64_t)((hi_bits | sm.keys[cnt - 1]) >> cbits) + 1 : rlo;
+      for (int64_t q = first + tid; q < rhi; q += THREADS) out_rowptr[q] = excl + nheads;
+    }
+    if (bucket == nb - 1 && tid == 0) *d_nnz_out = (long long)(excl + nheads);
+  }
+}
+
+}  // namespace ps

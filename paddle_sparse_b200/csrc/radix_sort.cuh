@@ -48,7 +48,7 @@ inline SortPlan make_sort_plan(int total_bits, int rbits) {
 enum { KSRC_KEYS = 0, KSRC_PACK_COO = 1, KSRC_I64 = 2 };
 enum { PSRC_U32 = 0, PSRC_IOTA = 1, PSRC_U16 = 2, PSRC_U8 = 3, PSRC_I64 = 4, PSRC_NONE = 5 /* word unused */ };
 enum { PDST_U32 = 0, PDST_I64 = 1, PDST_U16 = 2, PDST_U8 = 3, PDST_NONE = 4 };
-enum { KDST_NONE = 0, KDST_KEYS = 1, KDST_UNPACK_COO = 2, KDST_I64 = 3 };
+enum { KDST_NONE = 0, KDST_KEYS = 1, KDST_UNPACK_COO = 2, KDST_I64 = 3, KDST_LOW32 = 4 /* low cbits bits as u32 */ };
 
 struct KeySrc {
   const void *a;  // keys (KSRC_KEYS), row (KSRC_PACK_COO), the int64 array (KSRC_I64)
@@ -98,6 +98,8 @@ template <typename KeyT>
 __device__ __forceinline__ void store_key(const KeyDst &d, int64_t i, KeyT k) {
   if (d.mode == KDST_KEYS) reinterpret_cast<KeyT *>(d.a)[i] = k;
   else if (d.mode == KDST_I64) reinterpret_cast<int64_t *>(d.a)[i] = (int64_t)k;
+  else if (d.mode == KDST_LOW32)
+    reinterpret_cast<uint32_t *>(d.a)[i] = (uint32_t)((uint64_t)k & ((uint64_t(1) << d.cbits) - 1));
   else if (d.mode == KDST_UNPACK_COO) {
     reinterpret_cast<int64_t *>(d.a)[i] = (int64_t)((uint64_t)k >> d.cbits);
     reinterpret_cast<int64_t *>(d.b)[i] = (int64_t)((uint64_t)k & ((uint64_t(1) << d.cbits) - 1));
@@ -582,7 +584,8 @@ int rs_dispatch_pass(KeySrc ks, PaySrcN<NPAY> ps_, KeyDst ko, PayDstN<NPAY> pd, 
 template <typename KeyT, int NPAY>
 int radix_sort_tuples(KeySrc ksrc, PaySrcN<NPAY> psrc, int64_t n, int total_bits, KeyT *keys_tmp0, KeyT *keys_tmp1,
                       uint32_t *const *pay_tmp0, uint32_t *const *pay_tmp1, KeyDst keys_final,
-                      PayDstN<NPAY> pay_final, Scratch &scratch, cudaStream_t s, int first_bit = 0) {
+                      PayDstN<NPAY> pay_final, Scratch &scratch, cudaStream_t s, int first_bit = 0,
+                      const unsigned long long *scanned_hist = nullptr /* [passes][512] bin bases, if known */) {
   if (n <= 0) return PS_OK;
   const RsGeomRt geom = rs_geometry<KeyT, NPAY>();
   SortPlan plan = make_sort_plan(total_bits, geom.rbits);
@@ -600,16 +603,20 @@ int radix_sort_tuples(KeySrc ksrc, PaySrcN<NPAY> psrc, int64_t n, int total_bits
   unsigned long long *tickets = ghist + hist_words;
   uint64_t *state = words + hist_words + 32;
 
-  int64_t hb = ceil_div(n, 512 * 16);
-  const int64_t cap = 8 * (int64_t)sm_count();
-  if (hb > cap) hb = cap;
-  {
-    ProfScope prof(PROF_RS_HIST, s);
-    rs_hist_kernel<KeyT><<<(unsigned)hb, 512, 0, s>>>(ksrc, n, plan, ghist);
+  if (scanned_hist) {
+    ghist = const_cast<unsigned long long *>(scanned_hist);
+  } else {
+    int64_t hb = ceil_div(n, 512 * 16);
+    const int64_t cap = 8 * (int64_t)sm_count();
+    if (hb > cap) hb = cap;
+    {
+      ProfScope prof(PROF_RS_HIST, s);
+      rs_hist_kernel<KeyT><<<(unsigned)hb, 512, 0, s>>>(ksrc, n, plan, ghist);
+    }
+    PS_LAUNCH_OK();
+    rs_scan_kernel<<<plan.passes, RS_MAX_RADIX, 0, s>>>(ghist);
+    PS_LAUNCH_OK();
   }
-  PS_LAUNCH_OK();
-  rs_scan_kernel<<<plan.passes, RS_MAX_RADIX, 0, s>>>(ghist);
-  PS_LAUNCH_OK();
 
   KeyT *kt[2] = {keys_tmp0, keys_tmp1};
   for (int p = 0; p < plan.passes; ++p) {
@@ -642,14 +649,14 @@ int rs_num_passes(int total_bits) { return make_sort_plan(total_bits, rs_geometr
 template <typename KeyT>
 int radix_sort_pairs(KeySrc ksrc, PaySrc psrc, int64_t n, int total_bits, KeyT *keys_tmp0, KeyT *keys_tmp1,
                      uint32_t *pay_tmp0, uint32_t *pay_tmp1, KeyDst keys_final, PayDst pay_final, Scratch &scratch,
-                     cudaStream_t s, int first_bit = 0) {
+                     cudaStream_t s, int first_bit = 0, const unsigned long long *scanned_hist = nullptr) {
   PaySrcN<1> ps_;
   ps_.s[0] = psrc;
   PayDstN<1> pd;
   pd.d[0] = pay_final;
   uint32_t *t0[1] = {pay_tmp0}, *t1[1] = {pay_tmp1};
   return radix_sort_tuples<KeyT, 1>(ksrc, ps_, n, total_bits, keys_tmp0, keys_tmp1, t0, t1, keys_final, pd, scratch, s,
-                                    first_bit);
+                                    first_bit, scanned_hist);
 }
 
 }  // namespace ps

@@ -205,3 +205,45 @@ def test_lazy_sort_then_coalesce_is_fused_and_equivalent():
     assert d.coalesce() is d
     assert np.array_equal(host(d.row()), key // N) and np.array_equal(host(d.col()), key % N)
     assert np.array_equal(host(d.rowptr()), np.searchsorted(key // N, np.arange(M + 1)))
+
+
+@pytest.mark.parametrize("M,N,nnz,dup", [(2449029, 2449029, 70000, 0.2), (2449029, 2449029, 1500000, 0.3),
+                                         (3000000, 1 << 22, 400000, 0.0), (1 << 23, 1 << 23, 3000000, 0.05),
+                                         (70000, 2000000, 250000, 0.5)])
+@pytest.mark.parametrize("dtype,reduce", [(torch.float32, "add"), (torch.float32, "max"), (torch.int32, "mean"),
+                                          (torch.bfloat16, "add"), (None, "add")])
+def test_hybrid_coalesce_matches_oracle(ops, M, N, nnz, dup, dtype, reduce):
+    """keys wider than 32 bits and >= 2^16 entries take the hybrid path (local_sort.cuh: top-bit buckets by
+    one-sweep passes, bucket-local sort + dedup + rowptr in shared memory); same results as the oracle."""
+    rng = np.random.default_rng(nnz)
+    row, col = _random_coo(rng, M, N, nnz, dup)
+    val = None if dtype is None else rng.integers(-40, 40, nnz)
+    tv = None if dtype is None else dev(val, dtype)
+    r, c, v, rowptr = ops.coalesce(dev(row), dev(col), tv, M, N, reduce, True)
+    idx, want = np_ref.coalesce(np.stack([row, col]), None if val is None else val.astype(np.float64), M, N, reduce)
+    assert np.array_equal(host(r), idx[0]) and np.array_equal(host(c), idx[1])
+    assert np.array_equal(host(rowptr), np.searchsorted(idx[0], np.arange(M + 1), side="left"))
+    if dtype is not None:
+        if dtype == torch.int32 and reduce == "mean":
+            cnt = np_ref.coalesce(np.stack([row, col]), np.ones(nnz), M, N, "sum")[1]
+            tot = np_ref.coalesce(np.stack([row, col]), val.astype(np.float64), M, N, "sum")[1]
+            want = np.trunc(tot / cnt)
+        got = host(v.to(torch.float64))
+        if dtype == torch.bfloat16:
+            np.testing.assert_allclose(got, want, rtol=8e-3, atol=1e-6)
+        else:
+            assert np.array_equal(got, want)
+
+
+def test_hybrid_coalesce_hub_rows_fall_back(ops):
+    """one bucket beyond the shared-memory capacity (a hub row range): the plain LSD pipeline takes over"""
+    rng = np.random.default_rng(9)
+    M = N = 2449029
+    row = np.concatenate([rng.integers(0, M, 100000), rng.integers(5, 9, 60000)]).astype(I64)
+    col = rng.integers(0, N, row.size).astype(I64)
+    val = rng.random(row.size).astype(np.float32)
+    r, c, v, rowptr = ops.coalesce(dev(row), dev(col), dev(val), M, N, "add", True)
+    idx, want = np_ref.coalesce(np.stack([row, col]), val, M, N, "add")
+    assert np.array_equal(host(r), idx[0]) and np.array_equal(host(c), idx[1])
+    np.testing.assert_allclose(host(v), want, rtol=2e-6)
+    assert np.array_equal(host(rowptr), np.searchsorted(idx[0], np.arange(M + 1), side="left"))
