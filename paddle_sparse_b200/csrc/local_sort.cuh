@@ -116,14 +116,16 @@ ls_derive_kernel(const unsigned int *__restrict__ gcount, int T, LsPlan plan, un
 constexpr int LS_SORT_THREADS = 512;   // two CTAs per SM
 constexpr int LS_SORT_ITEMS = 16;      // LS_CAP = 512 * 16
 constexpr int LS_WARPS = LS_SORT_THREADS / 32;
-constexpr int LS_ROW = 256 / 2 + 1;    // counter row in words (odd: conflict-free column reads)
+constexpr int LS_ROW = 256 / 2;        // counter row in words (two 16-bit counters per word)
 static_assert(LS_SORT_THREADS * LS_SORT_ITEMS == LS_CAP, "bucket capacity");
 
 template <bool HAS_VALUE>
 struct LsSmem {
   uint32_t keys[LS_CAP];
   uint32_t vals[HAS_VALUE ? LS_CAP : 1];
-  uint32_t cnt[LS_WARPS][LS_ROW];  // two 16-bit counters per word, later group starts
+  uint32_t cnt[LS_WARPS][LS_ROW];  // two 16-bit counters per word, later the group's offset inside its half
+  uint16_t half_tot[2][256];       // items of digit d in warps [0, 8) / [8, 16)
+  uint16_t dbase[2][256];          // start of digit d's groups of that half inside the sorted bucket
   uint32_t scan_tmp[32];
   uint32_t wcnt[LS_SORT_ITEMS * LS_WARPS];
   long long bucket, excl;
@@ -138,7 +140,8 @@ ls_sort_dedup_kernel(const uint32_t *__restrict__ lowkeys, const uint32_t *__res
                      int64_t *__restrict__ out_rowptr, uint64_t *state /*[0]=ticket,[1..]=buckets*/,
                      long long *d_nnz_out) {
   using A = typename Acc<T>::type;
-  constexpr int THREADS = LS_SORT_THREADS, ITEMS = LS_SORT_ITEMS, WARPS = LS_WARPS, DPW = 256 / WARPS;
+  constexpr int THREADS = LS_SORT_THREADS, ITEMS = LS_SORT_ITEMS, WARPS = LS_WARPS;
+  static_assert(THREADS == 512 && WARPS == 16, "the digit prefix below is written for two halves of 8 warps");
   extern __shared__ __align__(16) unsigned char ls_raw[];
   LsSmem<HAS_VALUE> &sm = *reinterpret_cast<LsSmem<HAS_VALUE> *>(ls_raw);
   const unsigned tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
@@ -188,42 +191,45 @@ ls_sort_dedup_kernel(const uint32_t *__restrict__ lowkeys, const uint32_t *__res
         }
       }
       __syncthreads();
-      // column scans: lane l reads the counter of warp l for this warp's DPW digits (see rs_pass_kernel phase 3)
-      uint16_t *col = reinterpret_cast<uint16_t *>(&sm.cnt[lane < (unsigned)WARPS ? lane : 0][0]) + warp * DPW;
-      uint32_t wsum = 0, below = 0;
+      // prefix over the warps, per digit: thread (d, h) walks the 8 warps of half h (row-wise, conflict-free);
+      // then a block scan over the 256 digit totals, done redundantly by both halves
+      const unsigned dg = tid & 255u, hf = tid >> 8;
+      {
+        uint16_t *c16 = reinterpret_cast<uint16_t *>(&sm.cnt[hf * 8][0]) + dg;
+        uint32_t run = 0;
 #pragma unroll
-      for (int k = 0; k < DPW; ++k) {
-        const uint32_t c = lane < (unsigned)WARPS ? (uint32_t)col[k] : 0u;
-        uint32_t inc = c;
+        for (int w = 0; w < 8; ++w) {
+          const uint32_t c = c16[w * (LS_ROW * 2)];
+          c16[w * (LS_ROW * 2)] = (uint16_t)run;
+          run += c;
+        }
+        sm.half_tot[hf][dg] = (uint16_t)run;
+      }
+      __syncthreads();
+      {
+        const uint32_t h0 = sm.half_tot[0][dg], h1 = sm.half_tot[1][dg];
+        const uint32_t tot = h0 + h1;
+        uint32_t inc = tot;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
           const uint32_t o = __shfl_up_sync(0xffffffffu, inc, d);
           if (lane >= (unsigned)d) inc += o;
         }
-        if (lane < (unsigned)WARPS) col[k] = (uint16_t)(inc - c);
-        const uint32_t t = __shfl_sync(0xffffffffu, inc, 31);
-        if (lane == (unsigned)k) below = wsum;
-        wsum += t;
-      }
-      if (lane == 0) sm.scan_tmp[warp] = wsum;
-      __syncthreads();
-      {
+        if (lane == 31) sm.scan_tmp[warp] = inc;
+        __syncthreads();
         uint32_t wb = 0;
 #pragma unroll
-        for (int w = 0; w < WARPS; ++w) wb += (w < (int)warp) ? sm.scan_tmp[w] : 0u;
-        const uint32_t dexcl = wb + below;
-#pragma unroll
-        for (int k = 0; k < DPW; ++k) {
-          const uint32_t dk = __shfl_sync(0xffffffffu, dexcl, k);
-          if (lane < (unsigned)WARPS) col[k] = (uint16_t)(dk + col[k]);
-        }
+        for (int w = 0; w < 8; ++w) wb += (w < (int)(warp & 7u)) ? sm.scan_tmp[hf * 8 + w] : 0u;
+        sm.dbase[hf][dg] = (uint16_t)(wb + inc - tot + (hf ? h0 : 0u));
       }
       __syncthreads();
       const uint16_t *my_start = reinterpret_cast<const uint16_t *>(my_cnt);
+      const uint16_t *my_dbase = sm.dbase[warp >> 3];
 #pragma unroll
       for (int i = 0; i < ITEMS; ++i) {
         if (i < ie && wb0 + i * 32 + (int)lane < cnt) {
-          const unsigned pos = rank[i] + (unsigned)my_start[(key[i] >> shift) & mask];
+          const unsigned d = (key[i] >> shift) & mask;
+          const unsigned pos = rank[i] + (unsigned)my_start[d] + (unsigned)my_dbase[d];
           sm.keys[pos] = key[i];
           if (HAS_VALUE) sm.vals[pos] = val[i];
         }
