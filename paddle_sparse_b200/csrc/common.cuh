@@ -341,4 +341,52 @@ __device__ __forceinline__ uint64_t warp_lookback(uint64_t *state, int64_t tile,
   return excl;
 }
 
+// Same protocol, W x 32 predecessors per round trip (all W loads of a lane in flight together).  For chains whose
+// tiles publish their aggregates almost simultaneously (equal work per tile, e.g. one sorted bucket per CTA round):
+// the walk back to the nearest published prefix is then up to #resident-CTAs long, and its cost is round trips.
+template <int W>
+__device__ __forceinline__ uint64_t warp_lookback_wide(uint64_t *state, int64_t tile, uint64_t aggregate) {
+  const unsigned lane = lane_id();
+  if (tile == 0) {
+    if (lane == 0) TileState::store(state, TileState::pack(TileState::PREFIX, aggregate));
+    return 0;
+  }
+  if (lane == 0) TileState::store(state + tile, TileState::pack(TileState::AGG, aggregate));
+  uint64_t excl = 0;
+  int64_t base = tile - 1;
+  bool done = false;
+  while (!done) {
+    uint64_t w[W];
+#pragma unroll
+    for (int q = 0; q < W; ++q) {
+      const int64_t t = base - (int64_t)lane - 32 * q;
+      w[q] = t >= 0 ? TileState::load(state + t) : TileState::pack(TileState::PREFIX, 0);
+    }
+    int used = 0;
+#pragma unroll
+    for (int q = 0; q < W; ++q) {
+      if (done || used != q) continue;  // uniform: stop at the first window with an unpublished needed word
+      const uint64_t st = TileState::status(w[q]);
+      const unsigned pmask = __ballot_sync(0xffffffffu, st == TileState::PREFIX);
+      const unsigned emask = __ballot_sync(0xffffffffu, st == TileState::EMPTY);
+      unsigned need = 0xffffffffu;
+      if (pmask) {
+        const int fp = __ffs(pmask) - 1;
+        need = fp == 31 ? 0xffffffffu : ((2u << fp) - 1u);
+      }
+      if (emask & need) continue;  // poll this window again in the next round
+      uint64_t c = ((need >> lane) & 1u) ? TileState::value(w[q]) : 0;
+#pragma unroll
+      for (int d = 16; d > 0; d >>= 1) c += __shfl_xor_sync(0xffffffffu, c, d);
+      excl += c;
+      used = q + 1;
+      if (pmask) done = true;
+    }
+    base -= 32 * used;
+  }
+  if (lane == 0)
+    TileState::store(state + tile, TileState::pack(TileState::PREFIX, excl + aggregate));
+  return excl;
+}
+
 }  // namespace ps

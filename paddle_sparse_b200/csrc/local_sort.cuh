@@ -56,7 +56,7 @@ struct LsPlan {
 __global__ void __launch_bounds__(1024)
 ls_derive_kernel(const unsigned int *__restrict__ gcount, int T, LsPlan plan, unsigned int *__restrict__ bucket_off,
                  unsigned long long *__restrict__ ghist /*[passes][512]*/, unsigned int *__restrict__ max_bucket) {
-  __shared__ unsigned long long dig[2][RS_MAX_RADIX];
+  __shared__ unsigned int dig[2][RS_MAX_RADIX];  // 32-bit shared atomics are native, 64-bit ones are CAS loops
   __shared__ unsigned int wsum[33];
   __shared__ unsigned int smax;
   const unsigned tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
@@ -74,7 +74,7 @@ ls_derive_kernel(const unsigned int *__restrict__ gcount, int T, LsPlan plan, un
       mx = c > mx ? c : mx;
       if (c) {
         for (int p = 0; p < plan.passes; ++p)
-          atomicAdd(&dig[p][(b >> plan.pbegin[p]) & ((1 << plan.pbits[p]) - 1)], (unsigned long long)c);
+          atomicAdd(&dig[p][(b >> plan.pbegin[p]) & ((1 << plan.pbits[p]) - 1)], c);
       }
     }
   }
@@ -285,7 +285,7 @@ ls_sort_dedup_kernel(const uint32_t *__restrict__ lowkeys, const uint32_t *__res
         run += v[q];
       }
       const uint32_t total = __shfl_sync(0xffffffffu, inc, 31);
-      const uint64_t pfx = warp_lookback(state + 1, bucket, (uint64_t)total);
+      const uint64_t pfx = warp_lookback_wide<4>(state + 1, bucket, (uint64_t)total);
       if (lane == 0) {
         sm.excl = (long long)pfx;
         sm.heads = (int)total;

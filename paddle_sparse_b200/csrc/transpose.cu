@@ -22,29 +22,43 @@ invert_perm_kernel(const int64_t *__restrict__ perm, int64_t n, int64_t *__restr
   if (i < n) out[ld_stream(perm + i)] = i;
 }
 
-// Second half of the bucketed inverse: the (target, source) pairs arrive grouped by target >> INV_WINDOW_BITS, so
-// the CTAs working at any moment write into a few windows of 2^INV_WINDOW_BITS entries (2 MB each) that stay in L2
-// until they are complete: the random 8-byte stores merge into full lines before they reach HBM.
-constexpr int INV_WINDOW_BITS = 18;
-__global__ void __launch_bounds__(256)
-invert_scatter_kernel(const uint32_t *__restrict__ target, const uint32_t *__restrict__ source, int64_t n,
-                      int64_t *__restrict__ out) {
-  const int64_t stride = (int64_t)gridDim.x * blockDim.x * 4;
-  for (int64_t base = ((int64_t)blockIdx.x * blockDim.x) * 4; base < n; base += stride) {
-    const int64_t i0 = base + threadIdx.x;
+// Second half of the bucketed inverse.  `perm` is a permutation, so after the (target, source) pairs have been
+// partitioned on target >> INV_WINDOW_BITS the pairs of window w sit exactly at [w << BITS, (w + 1) << BITS): one CTA
+// drops the sources into a shared-memory table indexed by the low target bits and writes the window out coalesced.
+constexpr int INV_WINDOW_BITS = 12;
+__global__ void __launch_bounds__(512)
+invert_window_kernel(const uint32_t *__restrict__ target, const uint32_t *__restrict__ source, int64_t n,
+                     int64_t *__restrict__ out) {
+  constexpr int WIN = 1 << INV_WINDOW_BITS;
+  __shared__ uint32_t table[WIN];
+  for (int64_t w = blockIdx.x; (w << INV_WINDOW_BITS) < n; w += gridDim.x) {
+    const int64_t base = w << INV_WINDOW_BITS;
+    const int len = (int)((n - base) < WIN ? (n - base) : WIN);
+    uint32_t t[WIN / 512], v[WIN / 512];
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      const int64_t i = i0 + k * 256;
-      if (i < n) out[ld_stream(target + i)] = (int64_t)ld_stream(source + i);
+    for (int k = 0; k < WIN / 512; ++k) {
+      const int i = k * 512 + threadIdx.x;
+      t[k] = i < len ? ld_stream(target + base + i) : 0u;
+      v[k] = i < len ? ld_stream(source + base + i) : 0u;
     }
+#pragma unroll
+    for (int k = 0; k < WIN / 512; ++k)
+      if (k * 512 + (int)threadIdx.x < len) table[t[k] & (WIN - 1)] = v[k];
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < WIN / 512; ++k) {
+      const int i = k * 512 + threadIdx.x;
+      if (i < len) out[base + i] = (int64_t)table[i];
+    }
+    __syncthreads();
   }
 }
 
-// out[perm[i]] = i.  Large inputs: one stable radix partition of (perm[i], i) on the high bits of perm[i], then
-// the windowed scatter above; small inputs (the whole output fits L2 comfortably): the direct scatter.
+// out[perm[i]] = i.  Large inputs: a stable radix partition of (perm[i], i) on the high bits of perm[i] (two
+// one-sweep passes), then the window kernel above; small inputs (the output fits L2 comfortably): direct scatter.
 static int invert_perm_impl(const int64_t *perm, int64_t n, int64_t *out, cudaStream_t s) {
   const int nbits = bits_for(n);
-  if (nbits <= INV_WINDOW_BITS + 2 || n >= (int64_t(1) << 32)) {
+  if (nbits <= 20 || n >= (int64_t(1) << 32)) {
     ProfScope prof(PROF_INVERT_PERM, s);
     invert_perm_kernel<<<(unsigned)ceil_div(n, 256), 256, 0, s>>>(perm, n, out);
     PS_LAUNCH_OK();
@@ -62,7 +76,7 @@ static int invert_perm_impl(const int64_t *perm, int64_t n, int64_t *out, cudaSt
                                     KeyDst{tk, nullptr, KDST_KEYS, 0}, PayDst{tp, PDST_U32}, scratch, s, INV_WINDOW_BITS));
   {
     ProfScope prof(PROF_INVERT_PERM, s);
-    invert_scatter_kernel<<<(unsigned)(sm_count() * 8), 256, 0, s>>>(tk, tp, n, out);
+    invert_window_kernel<<<(unsigned)(sm_count() * 4), 512, 0, s>>>(tk, tp, n, out);
   }
   PS_LAUNCH_OK();
   return PS_OK;
