@@ -31,6 +31,9 @@ PIPELINE_BYTES_PER_NNZ = 128.6
 # without t() (the sharded step builds CSR + CSC structures per shard, no transposed copy): 128.6 - 48
 PIPELINE_LOCAL_BYTES_PER_NNZ = 80.6
 CPU_SAMPLE_NNZ = 8_000_000
+# dram__bytes_read.sum + dram__bytes_write.sum of rs_pass_kernel, average per launch over the 7 launches of one
+# step, from the committed `ncu --set full` capture (profiles/r01c_*): updated whenever the capture is
+NCU_TRAFFIC_PER_LAUNCH = 1.711e9
 
 
 def peaks():
@@ -161,10 +164,6 @@ def pipeline_step(ps, row, col, val, M, N):
     return A, A.t()
 
 
-def sort_passes(bits: int) -> int:
-    return max((bits + 7) // 8, 1)
-
-
 def bits_for(n: int) -> int:
     b = 0
     while (1 << b) < n:
@@ -172,16 +171,31 @@ def bits_for(n: int) -> int:
     return b
 
 
-def rs_pass_bytes(nnz_in: int, nnz_out: int, M: int, N: int) -> int:
-    """Algorithmic bytes moved by every rs_pass_kernel launch of one step ('kernels'):
-    sort-on-construct = P1 passes over nnz_in 8-byte keys + 4-byte payload (the first reads int64 row, col +
-    fp32 value = 20 B, the last writes them back unpacked = 20 B); csr2csc = P2 passes over nnz_out 4-byte keys
-    + 4-byte payload (first reads the int64 col, last writes the int64 permutation + the sorted 4-byte keys)."""
-    p1 = sort_passes(bits_for(M) + bits_for(N))
-    p2 = sort_passes(bits_for(N))
-    sort1 = nnz_in * ((20 + 12) + max(p1 - 2, 0) * 24 + (12 + 20)) if p1 > 1 else nnz_in * 40
-    sort2 = nnz_out * ((8 + 8) + max(p2 - 2, 0) * 16 + (8 + 12)) if p2 > 1 else nnz_out * 20
-    return sort1 + sort2
+def rs_pass_launches(nnz_in: int, nnz_out: int, M: int, N: int):
+    """Algorithmic bytes of every rs_pass_kernel launch of one step, in launch order:
+    each pass reads and writes every tuple once, at the width it has in that pass.
+      hybrid coalesce (44-bit key, top 14 bits sorted globally):
+        pass A  reads int64 row + int64 col + f32 value (20 B), writes u64 key + u32 value (12 B)
+        pass B  reads 12 B, writes the u32 bucket-local key + u32 value (8 B)
+      CSC side, stable sort by col carrying (index, row, value), ceil(22 / 8) = 3 passes:
+        first   reads int64 col + int64 row + f32 value (20 B), writes 4 x u32 (16 B)
+        middle  16 B + 16 B
+        last    reads 16 B, writes int64 t_row, t_col, csr2csc + f32 value (28 B)
+      csc2csr, partition of (target, source) on the top 14 bits of the target, 2 passes:
+        first   reads the int64 permutation (8 B), writes 2 x u32 (8 B);  second 8 B + 8 B"""
+    out = []
+    kbits = bits_for(M) + bits_for(N)
+    if kbits > 32 and nnz_in >= (1 << 16) and kbits - 14 <= 32:  # the hybrid path (coalesce.cu: hybrid_coalesce)
+        out += [nnz_in * (20 + 12), nnz_in * (12 + 8)]
+    else:
+        p = max((kbits + 7) // 8, 1)
+        out += [nnz_in * (20 + 12)] + [nnz_in * 24] * max(p - 2, 0) + ([nnz_in * 24] if p > 1 else [])
+    pc = max((bits_for(N) + 7) // 8, 1)
+    out += [nnz_out * (20 + 16)] + [nnz_out * 32] * max(pc - 2, 0) + [nnz_out * (16 + 28)]
+    if bits_for(nnz_out) > 20:
+        pi = max((bits_for(nnz_out) - 12 + 7) // 8, 1)
+        out += [nnz_out * 16] * pi
+    return out
 
 
 def read_profile(lib):
@@ -252,15 +266,19 @@ def run_ours(args):
 
     for _ in range(max(args.warmup, 3)):
         step()
-    read_profile(lib)
-    lib.ps_prof_enable(1)
+    # timed region 1: the headline (no per-kernel events)
     launches0 = int(lib.ps_launch_count())
     with ClockSampler(local_rank) as clocks:
         ms, out = timed(step, args.steps)
     launches = int(lib.ps_launch_count()) - launches0
+    value = units_per_step / (ms * 1e-3)
+    # timed region 2: the same K steps with CUDA events around every launch of the main kernel families, recorded
+    # on the launching stream (ps_prof_enable): per-kernel durations for the roofline of the dominant kernel
+    read_profile(lib)
+    lib.ps_prof_enable(1)
+    ms_prof, out = timed(step, args.steps)
     lib.ps_prof_enable(0)
     prof = read_profile(lib)
-    value = units_per_step / (ms * 1e-3)
 
     # ---- end to end: host (pinned) inputs, H2D + hot path + D2H of the result pointer array, every step
     if world == 1:
@@ -304,10 +322,12 @@ def run_ours(args):
         "config": workload_config(world), "clocks": clocks.summary(), "e2e": e2e,
         "gpu_launches": launches,
         "kernels_ms_per_step": {k: round(v[0] / args.steps, 4) for k, v in sorted(prof.items(), key=lambda kv: -kv[1][0])},
+        "ms_per_step_with_kernel_events": ms_prof,
     }
     if world == 1:
         fam_ms, fam_n = prof.get("rs_pass_kernel", (0.0, 0))
-        alg = rs_pass_bytes(nnz, nnz_out, M, N)  # per step
+        per_launch = rs_pass_launches(nnz, nnz_out, M, N)
+        alg = sum(per_launch)  # per step
         achieved = alg * args.steps / (fam_ms * 1e-3) / 1e9 if fam_ms else None
         line["roofline"] = {
             "bound": "hbm", "kernel": "rs_pass_kernel (one-sweep radix pass)", "achieved": achieved, "peak": hbm_peak,
@@ -315,8 +335,11 @@ def run_ours(args):
             "peak_source": peak_src, "launches_per_step": fam_n / args.steps,
             "avg_launch_ms": fam_ms / fam_n if fam_n else None,
             "algorithmic_bytes_per_launch": alg / (fam_n / args.steps) if fam_n else None,
-            "share_of_step": (fam_ms / args.steps) / ms if ms else None,
+            "share_of_step": (fam_ms / args.steps) / ms_prof if ms_prof else None,
+            "launches_modelled_per_step": len(per_launch),
+            "traffic_source": "profiles/ (ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum per launch)",
         }
+        line["roofline"]["traffic"] = NCU_TRAFFIC_PER_LAUNCH
         line["pipeline_roofline"] = {
             "algorithmic_bytes_per_nnz": PIPELINE_BYTES_PER_NNZ,
             "achieved_GBps": PIPELINE_BYTES_PER_NNZ * value / 1e9,

@@ -280,7 +280,7 @@ static int ls_launch(const uint32_t *lowkeys, const uint32_t *lowvals, const uns
   int grid = sm_count() * 2;
   if (grid > nb) grid = nb;
   {
-    ProfScope prof(PROF_DEDUP, s);
+    ProfScope prof(PROF_LOCAL_SORT, s);
     kern<<<grid, LS_SORT_THREADS, smem, s>>>(lowkeys, lowvals, bucket_off, nb, R, cbits, M, out_row, out_col,
                                             reinterpret_cast<T *>(out_value), out_rowptr, state, d_nnz);
   }
@@ -322,7 +322,7 @@ static int hybrid_coalesce(const int64_t *row, const int64_t *col, int64_t nnz, 
                                    (int)(sizeof(unsigned int) << LS_MAX_T)));
       configured = true;
     }
-    ProfScope prof(PROF_RS_HIST, s);
+    ProfScope prof(PROF_BUCKET_HIST, s);
     ls_bucket_hist_kernel<<<sm_count() * 2, 1024, sizeof(unsigned int) * (size_t)nb, s>>>(row, col, nnz, cbits, R, T,
                                                                                         gcount);
   }

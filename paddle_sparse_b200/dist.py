@@ -114,9 +114,9 @@ def build_partitioned(row, col, value, sparse_sizes, group=None, reduce: str = "
     r_row, r_col, r_val, splitters, sent, n_recv = route_tuples(row, col, value, (M, N), group)
     r0, r1 = int(splitters[rank]), int(splitters[rank + 1])
     local_row = ops.add_scalar(r_row, -r0) if r0 else r_row
-    c_row, c_col, c_val = ops.coalesce(local_row, r_col, r_val, max(r1 - r0, 0), N, reduce)
-    A = SparseTensor(row=c_row, col=c_col, value=c_val, sparse_sizes=(max(r1 - r0, 0), N), is_sorted=True,
-                     trust_data=True)
+    c_row, c_col, c_val, c_rowptr = ops.coalesce(local_row, r_col, r_val, max(r1 - r0, 0), N, reduce, True)
+    A = SparseTensor(row=c_row, rowptr=c_rowptr, col=c_col, value=c_val, sparse_sizes=(max(r1 - r0, 0), N),
+                     is_sorted=True, trust_data=True)
     if fill_cache:
         A.fill_cache_()
     At = A.t() if transpose else None
