@@ -320,7 +320,10 @@ ls_sort_dedup_kernel(const uint32_t *__restrict__ lowkeys, const uint32_t *__res
       }
       if (out_rowptr) {
         const int64_t pr = j == 0 ? rlo - 1 : (int64_t)((hi_bits | sm.keys[j - 1]) >> cbits);
-        for (int64_t q = pr + 1; q <= r && q <= M; ++q) out_rowptr[q] = o;
+        if (r != pr && r <= M) {  // this head opens row r (and the empty rows before it)
+          out_rowptr[r] = o;
+          for (int64_t q = pr + 1; q < r; ++q) out_rowptr[q] = o;
+        }
       }
     }
     if (out_rowptr) {  // rows of this bucket after its last entry (all of them when the bucket is empty)

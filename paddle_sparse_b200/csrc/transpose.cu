@@ -54,6 +54,24 @@ invert_window_kernel(const uint32_t *__restrict__ target, const uint32_t *__rest
   }
 }
 
+// Bin bases of the partition passes without reading anything: the keys are the integers 0 .. n-1, each exactly once,
+// so digit d of bits [lo, lo + bits) occurs count(d) = #{x < n : (x >> lo) & (2^bits - 1) == d} times.
+__global__ void __launch_bounds__(RS_MAX_RADIX)
+dense_key_hist_kernel(long long n, SortPlan plan, unsigned long long *__restrict__ ghist /*[passes][512] scanned*/) {
+  __shared__ unsigned long long warp_sums[33];
+  const int p = blockIdx.x, d = threadIdx.x;
+  const int lo = plan.begin[p], bits = plan.bits[p];
+  unsigned long long c = 0;
+  if (d < (1 << bits)) {
+    const unsigned long long period = 1ull << (lo + bits), block = 1ull << lo;
+    const unsigned long long full = (unsigned long long)n / period, rem = (unsigned long long)n % period;
+    const unsigned long long start = (unsigned long long)d * block;
+    c = full * block + (rem > start ? (rem - start < block ? rem - start : block) : 0ull);
+  }
+  unsigned long long total;
+  ghist[(size_t)p * RS_MAX_RADIX + d] = block_exclusive_scan<unsigned long long, RS_MAX_RADIX>(c, warp_sums, &total);
+}
+
 // out[perm[i]] = i.  Large inputs: a stable radix partition of (perm[i], i) on the high bits of perm[i] (two
 // one-sweep passes), then the window kernel above; small inputs (the output fits L2 comfortably): direct scatter.
 static int invert_perm_impl(const int64_t *perm, int64_t n, int64_t *out, cudaStream_t s) {
@@ -72,8 +90,14 @@ static int invert_perm_impl(const int64_t *perm, int64_t n, int64_t *out, cudaSt
   const int top = nbits - INV_WINDOW_BITS;
   const int passes = rs_num_passes<uint32_t>(top);
   uint32_t *tk = (passes & 1) ? k0 : k1, *tp = (passes & 1) ? p0 : p1;
+  SortPlan plan = make_sort_plan(top, rs_geometry<uint32_t, 1>().rbits);
+  for (int i = 0; i < plan.passes; ++i) plan.begin[i] += INV_WINDOW_BITS;
+  PS_SCRATCH(ghist, scratch, unsigned long long, (size_t)plan.passes * RS_MAX_RADIX);
+  dense_key_hist_kernel<<<plan.passes, RS_MAX_RADIX, 0, s>>>((long long)n, plan, ghist);
+  PS_LAUNCH_OK();
   PS_TRY(radix_sort_pairs<uint32_t>(KeySrc{perm, nullptr, KSRC_I64, 0}, PaySrc{nullptr, PSRC_IOTA}, n, top, k0, k1, p0, p1,
-                                    KeyDst{tk, nullptr, KDST_KEYS, 0}, PayDst{tp, PDST_U32}, scratch, s, INV_WINDOW_BITS));
+                                    KeyDst{tk, nullptr, KDST_KEYS, 0}, PayDst{tp, PDST_U32}, scratch, s, INV_WINDOW_BITS,
+                                    ghist));
   {
     ProfScope prof(PROF_INVERT_PERM, s);
     invert_window_kernel<<<(unsigned)(sm_count() * 4), 512, 0, s>>>(tk, tp, n, out);
