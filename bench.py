@@ -4,9 +4,10 @@
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
 
 One "step" = one pass of the hot path over one batch of synthetic COO input, through the public
-API:   SparseTensor(row, col, value, sparse_sizes)   (sort-on-construct)
-       .coalesce("add")  .fill_cache_()              (rowptr, rowcount, csr2csc, colptr, colcount, csc2csr)
-       .t()                                           (fused transpose gather)
+API:   SparseTensor(row, col, value, sparse_sizes)   (validation; sort-on-construct is deferred)
+       .coalesce("add")                               (sort + dedup + rowptr: hybrid coalesce)
+       .fill_cache_()                                 (rowcount, csr2csc, colptr, colcount, csc2csr: ps_csc_build)
+       .t()                                           (takes the transposed arrays the CSC sort carried)
 N = 1 : BASELINE.json configs[1] — ogbn-products shape, 2,449,029 nodes, 61,859,140 nnz, fp32.
 N > 1 : the row-range-partitioned build (configs[4] shape, papers100M: 111,059,956 nodes,
         201,960,734 nnz per GPU = 1.6157 B nnz at N = 8), weak scaling, one NCCL all-to-all.
@@ -148,8 +149,8 @@ def run_reference(args):
 def workload_config(n_gpus: int):
     if n_gpus <= 1:
         c = PRODUCTS
-        return {"workload": f"{c['name']}: {c['M']} nodes, {c['nnz']} nnz, fp32; SparseTensor(...) sort-on-construct + "
-                            "coalesce(add) + fill_cache_ (rowptr, csr2csc, colptr, csc2csr, counts) + t()",
+        return {"workload": f"{c['name']}: {c['M']} nodes, {c['nnz']} nnz, fp32; SparseTensor(...) + coalesce(add) + "
+                            "fill_cache_ (rowptr, csr2csc, colptr, csc2csr, counts) + t() through the public API",
                 "l2": "inputs (1.24 GB) and every intermediate exceed the 126 MB L2; no explicit flush"}
     c = PAPERS
     return {"workload": f"{c['name']} row-partitioned over {n_gpus} GPUs: {c['M']} nodes, {c['nnz_per_gpu']} nnz per GPU "

@@ -2,18 +2,18 @@
 // sort-on-construct / coalesce (storage.py:158-171, 454-486: the reference calls
 // Tensor.argsort on 64-bit keys, utils.py:21-23) and csr2csc (storage.py:425-434).
 //
-// Design (one-sweep: every pass reads and writes each pair exactly once):
-//   1. hist kernel   — one read of the keys builds the digit histograms of ALL passes in
-//                      shared memory; a 256-thread scan turns them into bin bases.
-//   2. pass kernel   — per tile: keys loaded warp-striped (coalesced), ranked with
-//                      __match_any_sync + per-warp digit counters (no atomics), tile digit
-//                      totals chained to earlier tiles by decoupled look-back (one 64-bit
-//                      status word per tile x digit, epoch-tagged so a single memset serves
-//                      every pass), pairs staged in shared memory in tile-sorted order and
-//                      written out as contiguous per-digit runs (coalesced).
-// The first pass can read its keys straight from the int64 (row, col) arrays (packing
-// row << cbits | col on the fly) and the last pass can widen the payload to int64, so no
-// separate pack / unpack passes touch HBM.
+// Design (one-sweep: every pass reads and writes each tuple exactly once):
+//   1. hist kernel   - one read of the keys builds the digit histograms of ALL passes in shared memory; a scan
+//                      turns them into bin bases (callers that know them pass them in: hybrid coalesce, inverse).
+//   2. pass kernel   - one persistent 1024-thread CTA per SM, 12-16 K-tuple tiles from an atomic ticket: keys in
+//                      registers, ranked by ONE shared-memory atomicAdd per item on warp-private 16-bit counters
+//                      (ATOMS serves lanes in order on sm_100a: stable), tile digit totals published early and
+//                      chained to earlier tiles by a warp-cooperative decoupled look-back (one 64-bit status word
+//                      per tile x digit, epoch-tagged so a single memset serves every pass), tuples staged in
+//                      shared memory in tile-sorted order and written out as contiguous per-digit runs.
+// The first pass can read its keys straight from the int64 (row, col) arrays (packing row << cbits | col on the
+// fly), the last pass can widen keys / payload to int64 or keep only the low key bits, so no separate pack /
+// unpack passes touch HBM.  Up to three u32 payload words travel with a key.
 #pragma once
 #include "common.cuh"
 

@@ -20,7 +20,7 @@ def declared_symbols():
 def test_header_declares_the_hot_path():
     names = declared_symbols()
     for must in ("ps_ind2ptr", "ps_ptr2ind", "ps_sample_adj", "ps_cuda_version", "ps_coalesce", "ps_sort_coo",
-                 "ps_csr2csc", "ps_invert_perm", "ps_transpose_gather", "ps_segment_reduce", "ps_scatter_reduce",
+                 "ps_csr2csc", "ps_csc_build", "ps_invert_perm", "ps_transpose_gather", "ps_segment_reduce", "ps_scatter_reduce",
                  "ps_gather_csr", "ps_mul_row", "ps_mul_col", "ps_index_select_fill", "ps_mask_to_index",
                  "ps_dist_partition", "ps_dist_row_histogram"):
         assert must in names, must
@@ -39,7 +39,7 @@ def test_library_exports_every_declared_symbol():
 def test_header_cites_the_reference_interface():
     text = open(HEADER).read()
     for cite in ("csrc/convert.cpp:13-23", "csrc/convert.cpp:46-56", "csrc/sample.cpp:8-24", "csrc/version.cpp",
-                 "storage.py:454-486", "storage.py:425-434", "transpose.py:9-33", "reduce.py:42", "mul.py:76-93"):
+                 "storage.py:454-486", "storage.py:425-434", "storage.py:211-222", "transpose.py:9-33", "reduce.py:42", "mul.py:76-93"):
         assert cite in text, cite
 
 
