@@ -266,11 +266,11 @@ static int check_value_args(const void *value, const void *out_value, int dtype,
 // out; the caller then runs the plain LSD pipeline.  One extra host read (the largest bucket) decides.
 int hybrid_variant();  // PS_HYBRID=0 disables (bench knob)
 
-template <typename T, int RED, bool HAS_VALUE>
+template <typename T, int RED, bool HAS_VALUE, bool DEDUP>
 static int ls_launch(const uint32_t *lowkeys, const uint32_t *lowvals, const unsigned int *bucket_off, int nb, int R,
                      int cbits, int64_t M, int64_t *out_row, int64_t *out_col, void *out_value, int64_t *out_rowptr,
                      uint64_t *state, long long *d_nnz, cudaStream_t s) {
-  auto kern = ls_sort_dedup_kernel<T, RED, HAS_VALUE>;
+  auto kern = ls_sort_dedup_kernel<T, RED, HAS_VALUE, DEDUP>;
   const size_t smem = sizeof(LsSmem<HAS_VALUE>);
   static bool configured = false;
   if (!configured) {
@@ -289,7 +289,7 @@ static int ls_launch(const uint32_t *lowkeys, const uint32_t *lowvals, const uns
 }
 
 static int hybrid_coalesce(const int64_t *row, const int64_t *col, int64_t nnz, int rbits, int cbits, int64_t M,
-                           const void *value, int dtype, int reduce, int64_t *out_row, int64_t *out_col,
+                           const void *value, int dtype, bool dedup, int reduce, int64_t *out_row, int64_t *out_col,
                            void *out_value, int64_t *out_rowptr, int64_t *host_nnz_out, bool *used, cudaStream_t s) {
   *used = false;
   const int K = rbits + cbits;
@@ -348,13 +348,17 @@ static int hybrid_coalesce(const int64_t *row, const int64_t *col, int64_t nnz, 
   PS_CUDA(cudaMemsetAsync(state, 0, sizeof(uint64_t) * ((size_t)nb + 1), s));
   PS_SCRATCH(d_nnz, scratch, long long, 1);
   int rc = PS_ERR_ARG;
-#define PS_LS(T_)                                                                                              \
-  PS_DISPATCH_REDUCE(reduce, RED, rc = (ls_launch<T_, RED, true>(lowkeys, lowvals, bucket_off, nb, R, cbits, M, \
-                                                                 out_row, out_col, out_value, out_rowptr, state, \
-                                                                 d_nnz, s)))
+#define PS_LS_ARGS lowkeys, lowvals, bucket_off, nb, R, cbits, M, out_row, out_col, out_value, out_rowptr, state, d_nnz, s
+#define PS_LS(T_)                                                                          \
+  do {                                                                                     \
+    if (dedup) { PS_DISPATCH_REDUCE(reduce, RED, rc = (ls_launch<T_, RED, true, true>(PS_LS_ARGS))); } \
+    else rc = ls_launch<T_, PS_SUM, true, false>(PS_LS_ARGS);                              \
+  } while (0)
   if (!value) {
-    rc = ls_launch<float, PS_SUM, false>(lowkeys, nullptr, bucket_off, nb, R, cbits, M, out_row, out_col, nullptr,
-                                         out_rowptr, state, d_nnz, s);
+    rc = dedup ? ls_launch<float, PS_SUM, false, true>(lowkeys, nullptr, bucket_off, nb, R, cbits, M, out_row, out_col,
+                                                       nullptr, out_rowptr, state, d_nnz, s)
+               : ls_launch<float, PS_SUM, false, false>(lowkeys, nullptr, bucket_off, nb, R, cbits, M, out_row, out_col,
+                                                        nullptr, out_rowptr, state, d_nnz, s);
   } else {
     switch (dtype) {
       case PS_F32: PS_LS(float); break;
@@ -365,10 +369,13 @@ static int hybrid_coalesce(const int64_t *row, const int64_t *col, int64_t nnz, 
     }
   }
 #undef PS_LS
+#undef PS_LS_ARGS
   PS_TRY(rc);
-  long long h_nnz = 0;
-  PS_TRY(read_back(&h_nnz, d_nnz, sizeof(h_nnz), s));
-  *host_nnz_out = (int64_t)h_nnz;
+  if (dedup) {
+    long long h_nnz = 0;
+    PS_TRY(read_back(&h_nnz, d_nnz, sizeof(h_nnz), s));
+    *host_nnz_out = (int64_t)h_nnz;
+  }
   *used = true;
   return PS_OK;
 }
@@ -380,10 +387,11 @@ int sort_impl(const int64_t *row, const int64_t *col, int64_t nnz, KeyGeom g, co
               int64_t width, bool dedup, int reduce, int64_t *out_row, int64_t *out_col, void *out_value,
               int64_t *out_perm, int64_t *host_nnz_out, int64_t M, int64_t *out_rowptr, cudaStream_t s) {
   const bool fast = value && fast_value(dtype, width) && !out_perm;
-  if (dedup && sizeof(KeyT) == 8 && (fast || !value)) {
+  if (sizeof(KeyT) == 8 && (fast || !value) && !out_perm) {  // hybrid path (sort only, or sort + dedup)
     bool used = false;
-    PS_TRY(hybrid_coalesce(row, col, nnz, g.rbits, g.cbits, M, value, dtype, reduce, out_row, out_col, out_value,
-                           out_rowptr, host_nnz_out, &used, s));
+    int64_t ignored = 0;
+    PS_TRY(hybrid_coalesce(row, col, nnz, g.rbits, g.cbits, M, value, dtype, dedup, reduce, out_row, out_col, out_value,
+                           out_rowptr, dedup ? host_nnz_out : &ignored, &used, s));
     if (used) return PS_OK;
   }
   Scratch scratch(s);

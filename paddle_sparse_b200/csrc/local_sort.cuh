@@ -132,7 +132,9 @@ struct LsSmem {
   int heads;
 };
 
-template <typename T, int RED, bool HAS_VALUE>
+// DEDUP = false: sort only (sort-on-construct, storage.py:158-171): every entry is kept, so the bucket's output
+// offset is its input offset and no chaining over the buckets is needed.
+template <typename T, int RED, bool HAS_VALUE, bool DEDUP>
 __global__ void __launch_bounds__(LS_SORT_THREADS, 2)
 ls_sort_dedup_kernel(const uint32_t *__restrict__ lowkeys, const uint32_t *__restrict__ lowvals,
                      const unsigned int *__restrict__ bucket_off, int nb, int R, int cbits, int64_t M,
@@ -249,51 +251,62 @@ ls_sort_dedup_kernel(const uint32_t *__restrict__ lowkeys, const uint32_t *__res
     // ---- the bucket is sorted in shared memory: run heads (entry order = (item, warp, lane) with the striped
     // layout j = i*THREADS + tid), their ranks, the bucket's offset in the output by look-back over the buckets
     unsigned heads = 0, below[ITEMS];
+    int64_t excl = (int64_t)start;
+    int nheads = cnt;
+    if (DEDUP) {
 #pragma unroll
-    for (int i = 0; i < ITEMS; ++i) {
-      below[i] = 0;
-      if (i < ie) {  // uniform
+      for (int i = 0; i < ITEMS; ++i) {
+        below[i] = 0;
+        if (i < ie) {  // uniform
+          const int j = i * THREADS + tid;
+          const bool h = j < cnt && (j == 0 || sm.keys[j] != sm.keys[j - 1]);
+          const unsigned bal = __ballot_sync(0xffffffffu, h);
+          heads |= (unsigned)h << i;
+          below[i] = __popc(bal & lt);
+          if (lane == 0) sm.wcnt[i * WARPS + warp] = __popc(bal);
+        } else if (lane == 0) {
+          sm.wcnt[i * WARPS + warp] = 0;
+        }
+      }
+      __syncthreads();
+      if (warp == 0) {
+        constexpr int PER = ITEMS * WARPS / 32;
+        uint32_t v[PER], sum = 0;
+#pragma unroll
+        for (int q = 0; q < PER; ++q) {
+          v[q] = sm.wcnt[lane * PER + q];
+          sum += v[q];
+        }
+        uint32_t inc = sum;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+          const uint32_t o = __shfl_up_sync(0xffffffffu, inc, d);
+          if (lane >= (unsigned)d) inc += o;
+        }
+        uint32_t run = inc - sum;
+#pragma unroll
+        for (int q = 0; q < PER; ++q) {
+          sm.wcnt[lane * PER + q] = run;
+          run += v[q];
+        }
+        const uint32_t total = __shfl_sync(0xffffffffu, inc, 31);
+        const uint64_t pfx = warp_lookback_wide<4>(state + 1, bucket, (uint64_t)total);
+        if (lane == 0) {
+          sm.excl = (long long)pfx;
+          sm.heads = (int)total;
+        }
+      }
+      __syncthreads();
+      excl = sm.excl;
+      nheads = sm.heads;
+    } else {
+#pragma unroll
+      for (int i = 0; i < ITEMS; ++i) {
         const int j = i * THREADS + tid;
-        const bool h = j < cnt && (j == 0 || sm.keys[j] != sm.keys[j - 1]);
-        const unsigned bal = __ballot_sync(0xffffffffu, h);
-        heads |= (unsigned)h << i;
-        below[i] = __popc(bal & lt);
-        if (lane == 0) sm.wcnt[i * WARPS + warp] = __popc(bal);
-      } else if (lane == 0) {
-        sm.wcnt[i * WARPS + warp] = 0;
+        below[i] = (unsigned)j;  // every entry is kept: its output slot is its sorted slot
+        if (i < ie && j < cnt) heads |= 1u << i;
       }
     }
-    __syncthreads();
-    if (warp == 0) {
-      constexpr int PER = ITEMS * WARPS / 32;
-      uint32_t v[PER], sum = 0;
-#pragma unroll
-      for (int q = 0; q < PER; ++q) {
-        v[q] = sm.wcnt[lane * PER + q];
-        sum += v[q];
-      }
-      uint32_t inc = sum;
-#pragma unroll
-      for (int d = 1; d < 32; d <<= 1) {
-        const uint32_t o = __shfl_up_sync(0xffffffffu, inc, d);
-        if (lane >= (unsigned)d) inc += o;
-      }
-      uint32_t run = inc - sum;
-#pragma unroll
-      for (int q = 0; q < PER; ++q) {
-        sm.wcnt[lane * PER + q] = run;
-        run += v[q];
-      }
-      const uint32_t total = __shfl_sync(0xffffffffu, inc, 31);
-      const uint64_t pfx = warp_lookback_wide<4>(state + 1, bucket, (uint64_t)total);
-      if (lane == 0) {
-        sm.excl = (long long)pfx;
-        sm.heads = (int)total;
-      }
-    }
-    __syncthreads();
-    const int64_t excl = sm.excl;
-    const int nheads = sm.heads;
     const uint64_t hi_bits = (uint64_t)bucket << R;
     // rows owned by this bucket: [rlo, rhi) (the last bucket also owns everything up to M)
     const int64_t rlo = (int64_t)(hi_bits >> cbits);
@@ -304,12 +317,13 @@ ls_sort_dedup_kernel(const uint32_t *__restrict__ lowkeys, const uint32_t *__res
       if (!((heads >> i) & 1u)) continue;
       const int j = i * THREADS + tid;
       const uint32_t lk = sm.keys[j];
-      const int64_t o = excl + below[i] + sm.wcnt[i * WARPS + warp];
+      const int64_t o = excl + below[i] + (DEDUP ? sm.wcnt[i * WARPS + warp] : 0u);
       const uint64_t full = hi_bits | lk;
       const int64_t r = (int64_t)(full >> cbits);
       out_row[o] = r;  // consecutive lanes hold consecutive heads: coalesced wherever nothing was merged
       out_col[o] = (int64_t)(full & cmask);
-      if (HAS_VALUE) {
+      if (HAS_VALUE && !DEDUP) out_value[o] = pay_as<T>(sm.vals[j]);
+      if (HAS_VALUE && DEDUP) {
         A acc = to_acc<T>(pay_as<T>(sm.vals[j]));
         int jj = j + 1;
         while (jj < cnt && sm.keys[jj] == lk) {
@@ -320,7 +334,7 @@ ls_sort_dedup_kernel(const uint32_t *__restrict__ lowkeys, const uint32_t *__res
       }
       if (out_rowptr) {
         const int64_t pr = j == 0 ? rlo - 1 : (int64_t)((hi_bits | sm.keys[j - 1]) >> cbits);
-        if (r != pr && r <= M) {  // this head opens row r (and the empty rows before it)
+        if (r != pr && r <= M) {  // (with DEDUP = false duplicates of a key share the row: only a row change writes)  // this head opens row r (and the empty rows before it)
           out_rowptr[r] = o;
           for (int64_t q = pr + 1; q < r; ++q) out_rowptr[q] = o;
         }
@@ -330,7 +344,7 @@ ls_sort_dedup_kernel(const uint32_t *__restrict__ lowkeys, const uint32_t *__res
       const int64_t first = cnt > 0 ? (int64_t)((hi_bits | sm.keys[cnt - 1]) >> cbits) + 1 : rlo;
       for (int64_t q = first + tid; q < rhi; q += THREADS) out_rowptr[q] = excl + nheads;
     }
-    if (bucket == nb - 1 && tid == 0) *d_nnz_out = (long long)(excl + nheads);
+    if (DEDUP && bucket == nb - 1 && tid == 0) *d_nnz_out = (long long)(excl + nheads);
   }
 }
 

@@ -247,3 +247,19 @@ def test_hybrid_coalesce_hub_rows_fall_back(ops):
     assert np.array_equal(host(r), idx[0]) and np.array_equal(host(c), idx[1])
     np.testing.assert_allclose(host(v), want, rtol=2e-6)
     assert np.array_equal(host(rowptr), np.searchsorted(idx[0], np.arange(M + 1), side="left"))
+
+
+@pytest.mark.parametrize("M,N,nnz,dup", [(2449029, 2449029, 500000, 0.3), (1 << 23, 1 << 22, 2000000, 0.1)])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16, None])
+def test_hybrid_sort_coo_is_stable(ops, M, N, nnz, dup, dtype):
+    """sort-on-construct (storage.py:158-171) on the hybrid path: duplicate keys carry distinct values, so any
+    instability of the bucket-local passes or of the atomic ranking shows up as a value mismatch."""
+    rng = np.random.default_rng(nnz + 1)
+    row, col = _random_coo(rng, M, N, nnz, dup)
+    order = np.argsort(row * N + col, kind="stable")
+    val = None if dtype is None else np.arange(nnz) % 251
+    tv = None if dtype is None else dev(val, dtype)
+    r, c, v, _ = ops.sort_coo(dev(row), dev(col), tv, M, N)
+    assert np.array_equal(host(r), row[order]) and np.array_equal(host(c), col[order])
+    if dtype is not None:
+        assert np.array_equal(host(v.to(torch.float64)), val[order].astype(np.float64))
