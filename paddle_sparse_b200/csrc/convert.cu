@@ -20,10 +20,13 @@ namespace ps {
 template <typename IndT>
 __device__ __forceinline__ int64_t ind_load(const IndT *p) { return (int64_t)*p; }
 
+constexpr int I2P_ITEMS = 4;  // consecutive elements per thread: 16 B of uint32 keys / 32 B of int64 indices
+
 template <typename IndT, int THREADS>
 __global__ void __launch_bounds__(THREADS)
 ind2ptr_kernel(const IndT *__restrict__ ind, int64_t numel, int64_t M, int64_t *__restrict__ out,
                int elem_blocks, int fill_blocks, bool aligned16) {
+  constexpr int ITEMS = I2P_ITEMS;
   if ((int)blockIdx.x >= elem_blocks) {
     // ---- head / tail fill blocks
     const int64_t first = (int64_t)ind[0], last = (int64_t)ind[numel - 1];
@@ -33,42 +36,61 @@ ind2ptr_kernel(const IndT *__restrict__ ind, int64_t numel, int64_t M, int64_t *
     for (int64_t r = last + 1 + fb * THREADS + threadIdx.x; r <= M; r += stride) out[r] = numel;
     return;
   }
-  // ---- boundary detection: each thread owns 2 consecutive elements (one 128-bit load for int64)
-  const int64_t e0 = ((int64_t)blockIdx.x * THREADS + threadIdx.x) * 2;
-  int64_t v0 = 0, v1 = 0, prev = 0;
-  const bool has0 = e0 < numel, has1 = e0 + 1 < numel;
-  if (has0) {
-    if (sizeof(IndT) == 8 && has1 && aligned16) {
-      const longlong2 t = ld_stream2(reinterpret_cast<const int64_t *>(ind) + e0);
-      v0 = t.x;
-      v1 = t.y;
-    } else {
-      v0 = (int64_t)ind[e0];
-      v1 = has1 ? (int64_t)ind[e0 + 1] : v0;
-    }
-  }
-  // previous element: neighbour lane's v1, lane 0 reads it from memory
-  int64_t up = __shfl_up_sync(0xffffffffu, v1, 1);
-  if (has0) prev = (lane_id() == 0) ? (e0 == 0 ? v0 : (int64_t)ind[e0 - 1]) : up;
-  // rows r in (prev, v0] get e0 ; rows in (v0, v1] get e0+1   (head handled by fill blocks)
-  int64_t lo[2] = {prev + 1, v0 + 1}, hi[2] = {v0, v1};
-  if (!has0) { lo[0] = 1; hi[0] = 0; }
-  if (!has1) { lo[1] = 1; hi[1] = 0; }
+  // ---- boundary detection: each thread owns ITEMS consecutive elements (128-bit loads)
+  const int64_t e0 = ((int64_t)blockIdx.x * THREADS + threadIdx.x) * ITEMS;
+  const int64_t left = numel - e0;
+  const int have = left >= ITEMS ? ITEMS : (left > 0 ? (int)left : 0);
+  int64_t v[ITEMS];
+  if (have == ITEMS && aligned16) {
+    if (sizeof(IndT) == 8) {
 #pragma unroll
-  for (int k = 0; k < 2; ++k) {
-    const int64_t gap = hi[k] - lo[k] + 1;
-    const bool is_long = gap > 32;
-    if (!is_long)
-      for (int64_t r = lo[k]; r <= hi[k]; ++r) out[r] = e0 + k;
-    unsigned m = __ballot_sync(0xffffffffu, is_long);
-    while (m) {  // warp-cooperative fill of every long gap in this warp
+      for (int k = 0; k < ITEMS; k += 2) {
+        const longlong2 t = ld_stream2(reinterpret_cast<const int64_t *>(ind) + e0 + k);
+        v[k] = t.x;
+        v[k + 1] = t.y;
+      }
+    } else {
+      uint32_t w[4];
+      asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];"
+                   : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3])
+                   : "l"(reinterpret_cast<const uint32_t *>(ind) + e0));
+#pragma unroll
+      for (int k = 0; k < ITEMS; ++k) v[k] = (int64_t)w[k];
+    }
+  } else {
+#pragma unroll
+    for (int k = 0; k < ITEMS; ++k) v[k] = k < have ? (int64_t)ind[e0 + k] : (k > 0 ? v[k - 1] : 0);
+  }
+  // previous element: neighbour lane's last one, lane 0 reads it from memory
+  const int64_t up = __shfl_up_sync(0xffffffffu, v[ITEMS - 1], 1);
+  int64_t prev = v[0];
+  if (have > 0 && e0 > 0) prev = lane_id() == 0 ? (int64_t)ind[e0 - 1] : up;
+  // rows r in (p_k, v_k] get e0 + k, p_0 = prev, p_k = v_{k-1}   (head handled by the fill blocks);
+  // absent elements repeat their predecessor, so their interval is empty
+  bool any_long = false;
+  int64_t p = prev;
+#pragma unroll
+  for (int k = 0; k < ITEMS; ++k) {
+    const int64_t gap = v[k] - p;
+    if (gap > 32) any_long = true;
+    else
+      for (int64_t r = p + 1; r <= v[k]; ++r) out[r] = e0 + k;
+    p = v[k];
+  }
+  if (!__any_sync(0xffffffffu, any_long)) return;
+  p = prev;
+#pragma unroll
+  for (int k = 0; k < ITEMS; ++k) {  // warp-cooperative fill of every gap longer than a warp
+    unsigned m = __ballot_sync(0xffffffffu, v[k] - p > 32);
+    while (m) {
       const int src = __ffs(m) - 1;
       m &= m - 1;
-      const int64_t l = __shfl_sync(0xffffffffu, lo[k], src);
-      const int64_t h = __shfl_sync(0xffffffffu, hi[k], src);
+      const int64_t l = __shfl_sync(0xffffffffu, p + 1, src);
+      const int64_t h = __shfl_sync(0xffffffffu, v[k], src);
       const int64_t val = __shfl_sync(0xffffffffu, e0 + k, src);
       for (int64_t r = l + lane_id(); r <= h; r += 32) out[r] = val;
     }
+    p = v[k];
   }
 }
 
@@ -80,7 +102,7 @@ int ind2ptr_launch(const IndT *ind, int64_t numel, int64_t M, int64_t *out, cuda
     return PS_OK;
   }
   constexpr int THREADS = 256;
-  const int64_t elem_blocks = ceil_div(numel, THREADS * 2);
+  const int64_t elem_blocks = ceil_div(numel, THREADS * I2P_ITEMS);
   int64_t fill_blocks = ceil_div(M + 1, THREADS * 8);
   const int64_t cap = 2 * (int64_t)sm_count();
   if (fill_blocks > cap) fill_blocks = cap;

@@ -13,26 +13,42 @@ namespace ps {
 
 // ============================================================================= segment reduce
 // G lanes cooperate on one output (segment s, feature f); o = s*width + f.
-template <typename T, int RED, int G>
+// W1: width == 1 known at compile time (the [nnz] value vector of reduce.py:51) - no 64-bit divide per output,
+// and the segment walk is unrolled so that each lane keeps several loads in flight.
+template <typename T, int RED, int G, bool W1>
 __global__ void __launch_bounds__(256)
 segment_reduce_kernel(const T *__restrict__ src, int64_t width, const int64_t *__restrict__ ptr, int64_t S,
                       T *__restrict__ out, const uint32_t *__restrict__ perm) {
   using A = typename Acc<T>::type;
   const int64_t gid = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / G;
   const int sub = threadIdx.x % G;
-  const int64_t total = S * width;
+  const int64_t total = W1 ? S : S * width;
   const bool live = gid < total;
-  const int64_t sgm = live ? gid / width : 0;
-  const int64_t f = live ? gid - sgm * width : 0;
+  const int64_t sgm = live ? (W1 ? gid : gid / width) : 0;
+  const int64_t f = (live && !W1) ? gid - sgm * width : 0;
   int64_t lo = 0, hi = 0;
   if (live) {
     lo = ptr[sgm];
     hi = ptr[sgm + 1];
   }
   A acc = Red<RED, A>::init();
-  for (int64_t e = lo + sub; e < hi; e += G) {
-    const int64_t r = perm ? (int64_t)perm[e] : e;
-    acc = Red<RED, A>::op(acc, to_acc<T>(src[r * width + f]));
+  if (W1) {
+    int64_t e = lo + sub;
+    if (!perm) {
+      for (; e + 3 * G < hi; e += 4 * G) {
+        const T v0 = src[e], v1 = src[e + G], v2 = src[e + 2 * G], v3 = src[e + 3 * G];
+        acc = Red<RED, A>::op(acc, to_acc<T>(v0));
+        acc = Red<RED, A>::op(acc, to_acc<T>(v1));
+        acc = Red<RED, A>::op(acc, to_acc<T>(v2));
+        acc = Red<RED, A>::op(acc, to_acc<T>(v3));
+      }
+    }
+    for (; e < hi; e += G) acc = Red<RED, A>::op(acc, to_acc<T>(src[perm ? (int64_t)perm[e] : e]));
+  } else {
+    for (int64_t e = lo + sub; e < hi; e += G) {
+      const int64_t r = perm ? (int64_t)perm[e] : e;
+      acc = Red<RED, A>::op(acc, to_acc<T>(src[r * width + f]));
+    }
   }
 #pragma unroll
   for (int d = G / 2; d > 0; d >>= 1) acc = Red<RED, A>::op(acc, __shfl_xor_sync(0xffffffffu, acc, d));
@@ -52,12 +68,23 @@ static int segment_reduce_typed(const T *src, int64_t width, const int64_t *ptr,
   const int64_t threads = outputs * G;
   const unsigned blocks = (unsigned)ceil_div(threads, 256);
   ProfScope prof(PROF_SEGMENT_REDUCE, s);
-  switch (G) {
-    case 1: segment_reduce_kernel<T, RED, 1><<<blocks, 256, 0, s>>>(src, width, ptr, S, out, perm); break;
-    case 4: segment_reduce_kernel<T, RED, 4><<<blocks, 256, 0, s>>>(src, width, ptr, S, out, perm); break;
-    case 8: segment_reduce_kernel<T, RED, 8><<<blocks, 256, 0, s>>>(src, width, ptr, S, out, perm); break;
-    default: segment_reduce_kernel<T, RED, 32><<<blocks, 256, 0, s>>>(src, width, ptr, S, out, perm); break;
+#define PS_SR(G_, W1_) segment_reduce_kernel<T, RED, G_, W1_><<<blocks, 256, 0, s>>>(src, width, ptr, S, out, perm)
+  if (width == 1) {
+    switch (G) {
+      case 1: PS_SR(1, true); break;
+      case 4: PS_SR(4, true); break;
+      case 8: PS_SR(8, true); break;
+      default: PS_SR(32, true); break;
+    }
+  } else {
+    switch (G) {
+      case 1: PS_SR(1, false); break;
+      case 4: PS_SR(4, false); break;
+      case 8: PS_SR(8, false); break;
+      default: PS_SR(32, false); break;
+    }
   }
+#undef PS_SR
   PS_LAUNCH_OK();
   return PS_OK;
 }
@@ -149,6 +176,51 @@ mul_row_kernel(const T *value, int64_t width, const int64_t *__restrict__ rowptr
   }
 }
 
+// width == 1: the [nnz] value vector times an [M,1] operand; no divide, ITEMS independent loads per thread
+template <typename T, int THREADS, int ITEMS>
+__global__ void __launch_bounds__(THREADS)
+mul_row_w1_kernel(const T *value, const int64_t *__restrict__ rowptr, int64_t M, int64_t nnz,
+                  const T *__restrict__ other, T *out) {
+  constexpr int TILE = THREADS * ITEMS;
+  __shared__ int32_t seg[TILE];
+  __shared__ int32_t aux[40];
+  const int64_t e0 = (int64_t)blockIdx.x * TILE;
+  const int tile_n = (int)((nnz - e0) < TILE ? (nnz - e0) : TILE);
+  T v[ITEMS];
+#pragma unroll
+  for (int k = 0; k < ITEMS; ++k) {
+    const int j = k * THREADS + threadIdx.x;
+    if (j < tile_n) v[k] = value[e0 + j];
+  }
+  expand_tile<THREADS, ITEMS>(rowptr, M, e0, tile_n, seg, aux);
+#pragma unroll
+  for (int k = 0; k < ITEMS; ++k) {
+    const int j = k * THREADS + threadIdx.x;
+    if (j < tile_n) out[e0 + j] = mul_values<T>(v[k], other[seg[j]]);
+  }
+}
+
+template <typename T, int THREADS, int ITEMS>
+__global__ void __launch_bounds__(THREADS)
+mul_col_w1_kernel(const T *value, const int64_t *__restrict__ col, int64_t nnz, const T *__restrict__ other, T *out) {
+  const int64_t e0 = (int64_t)blockIdx.x * (THREADS * ITEMS) + threadIdx.x;
+  int64_t c[ITEMS];
+  T v[ITEMS];
+#pragma unroll
+  for (int k = 0; k < ITEMS; ++k) {
+    const int64_t e = e0 + k * THREADS;
+    if (e < nnz) {
+      c[k] = ld_stream(col + e);
+      v[k] = value[e];
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < ITEMS; ++k) {
+    const int64_t e = e0 + k * THREADS;
+    if (e < nnz) out[e] = mul_values<T>(v[k], other[c[k]]);
+  }
+}
+
 template <typename T>
 __global__ void __launch_bounds__(256)
 mul_col_kernel(const T *value, int64_t width, const int64_t *__restrict__ col, int64_t n_units,
@@ -199,14 +271,15 @@ __global__ void fill_init_kernel(A *p, int64_t n) {
   if (i < n) p[i] = Red<RED, A>::init();
 }
 
-template <typename T, int RED>
+template <typename T, int RED, bool W1>
 __global__ void __launch_bounds__(256)
 scatter_reduce_kernel(const T *__restrict__ src, int64_t width, const int64_t *__restrict__ index, int64_t n_units,
                       typename Acc<T>::type *__restrict__ acc, int *__restrict__ cnt) {
   using A = typename Acc<T>::type;
   const int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (q >= n_units) return;
-  const int64_t e = q / width, f = q - e * width;
+  if (W1) width = 1;
+  const int64_t e = W1 ? q : q / width, f = W1 ? 0 : q - e * width;
   const int64_t r = index[e];
   const A v = to_acc<T>(src[q]);
   if (RED == PS_SUM || RED == PS_MEAN) atomic_red_add<A>(&acc[r * width + f], v);
@@ -249,7 +322,9 @@ static int scatter_reduce_typed(const T *src, int64_t width, const int64_t *inde
   PS_LAUNCH_OK();
   const int64_t n_units = n * width;
   if (n_units > 0) {
-    scatter_reduce_kernel<T, RED><<<(unsigned)ceil_div(n_units, 256), 256, 0, s>>>(src, width, index, n_units, acc, cnt);
+    const unsigned blocks = (unsigned)ceil_div(n_units, 256);
+    if (width == 1) scatter_reduce_kernel<T, RED, true><<<blocks, 256, 0, s>>>(src, width, index, n_units, acc, cnt);
+    else scatter_reduce_kernel<T, RED, false><<<blocks, 256, 0, s>>>(src, width, index, n_units, acc, cnt);
     PS_LAUNCH_OK();
   }
   if (RED != PS_SUM || !same) {
@@ -389,6 +464,14 @@ int ps_mul_row(const void *value, int dtype, int64_t width, const int64_t *rowpt
   constexpr int THREADS = 256, ITEMS = 8;
   const unsigned blocks = (unsigned)ceil_div(nnz, THREADS * ITEMS);
   cudaStream_t s = (cudaStream_t)stream;
+  if (width == 1) {
+    PS_DISPATCH_DTYPE(dtype, T,
+                      (mul_row_w1_kernel<T, THREADS, ITEMS><<<blocks, THREADS, 0, s>>>(
+                          reinterpret_cast<const T *>(value), rowptr, M, nnz, reinterpret_cast<const T *>(other),
+                          reinterpret_cast<T *>(out))));
+    PS_LAUNCH_OK();
+    return PS_OK;
+  }
   PS_DISPATCH_DTYPE(dtype, T,
                     (mul_row_kernel<T, THREADS, ITEMS><<<blocks, THREADS, 0, s>>>(
                         reinterpret_cast<const T *>(value), width, rowptr, M, nnz, reinterpret_cast<const T *>(other),
@@ -404,6 +487,16 @@ int ps_mul_col(const void *value, int dtype, int64_t width, const int64_t *col, 
   if (n_units == 0) return PS_OK;
   const unsigned blocks = (unsigned)ceil_div(n_units, 256);
   cudaStream_t s = (cudaStream_t)stream;
+  if (width == 1) {
+    constexpr int THREADS = 256, ITEMS = 4;
+    const unsigned wblocks = (unsigned)ceil_div(nnz, THREADS * ITEMS);
+    PS_DISPATCH_DTYPE(dtype, T,
+                      (mul_col_w1_kernel<T, THREADS, ITEMS><<<wblocks, THREADS, 0, s>>>(
+                          reinterpret_cast<const T *>(value), col, nnz, reinterpret_cast<const T *>(other),
+                          reinterpret_cast<T *>(out))));
+    PS_LAUNCH_OK();
+    return PS_OK;
+  }
   PS_DISPATCH_DTYPE(dtype, T,
                     (mul_col_kernel<T><<<blocks, 256, 0, s>>>(reinterpret_cast<const T *>(value), width, col, n_units,
                                                               reinterpret_cast<const T *>(other),
