@@ -154,6 +154,22 @@ int ps_mul_col(const void *value, int dtype, int64_t width, const int64_t *col, 
                const void *other, void *out, void *stream);
 /* mul.py:96-119 `mul_nnz`: out = value * other, both [n]. */
 int ps_mul_nnz(const void *value, int dtype, int64_t n, const void *other, void *out, void *stream);
+/* add.py:12-28, 53-69 (dense [M,1] / [1,N] operand) and add.py:72-81 `add_nnz`: the three
+ * multiplies above with + in place of *; same arguments. */
+int ps_add_row(const void *value, int dtype, int64_t width, const int64_t *rowptr, int64_t M,
+               int64_t nnz, const void *other, void *out, void *stream);
+int ps_add_col(const void *value, int dtype, int64_t width, const int64_t *col, int64_t nnz,
+               const void *other, void *out, void *stream);
+int ps_add_nnz(const void *value, int dtype, int64_t n, const void *other, void *out, void *stream);
+
+/* ------------------------------------------------------------------ set operations */
+/* mul.py:35-73 sparse (.) sparse, the matching step: for every entry e of A (row[e], col[e];
+ * n of them) the position of the equal entry in the coalesced CSR (rowptr_b[M_b+1], col_b) of B,
+ * or -1; out_mask[e] = 1 when matched.  Replaces the reference's concat + argsort + adjacent-equal
+ * scan; both operands are coalesced there (mul.py:38-41). */
+int ps_coo_match(const int64_t *row, const int64_t *col, int64_t n, const int64_t *rowptr_b,
+                 const int64_t *col_b, int64_t M_b, int64_t *out_pos, uint8_t *out_mask,
+                 void *stream);
 
 /* ------------------------------------------------------------------ select */
 /* masked_select.py:18-24: indices of the set entries of a byte mask, ascending.

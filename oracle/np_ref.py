@@ -478,6 +478,112 @@ def mul(src: SparseTensor, other: np.ndarray) -> SparseTensor:
     return mul_(out, other)
 
 
+def mul_sparse(src: SparseTensor, other: SparseTensor) -> SparseTensor:
+    """mul.py:35-73, sparse (.) sparse: both operands coalesced; concatenate, sort the keys
+    row*N+col behind a -1 sentinel, keep the second entry of every adjacent equal pair and
+    multiply it with its predecessor."""
+    if not src.is_coalesced():
+        raise ValueError("The `src` tensor is not coalesced")
+    if not other.is_coalesced():
+        raise ValueError("The `other` tensor is not coalesced")
+    rowA, colA, valueA = src.coo()
+    rowB, colB, valueB = other.coo()
+    row = np.concatenate([rowA, rowB])
+    col = np.concatenate([colA, colB])
+    if valueA is None or valueB is None:
+        raise ValueError("Both sparse tensors must contain values")
+    value = np.concatenate([valueA, valueB])
+    M = max(src.size(0), other.size(0))
+    N = max(src.size(1), other.size(1))
+    idx = np.full(col.size + 1, -1, dtype=np.int64)
+    idx[1:] = row * N + col
+    perm = np.argsort(idx[1:], kind="stable")
+    idx[1:] = idx[1:][perm]
+    row, col, value = row[perm], col[perm], value[perm]
+    valid_mask = idx[1:] == idx[:-1]
+    valid_idx = np.nonzero(valid_mask)[0]
+    return SparseTensor(row=row[valid_mask], col=col[valid_mask],
+                        value=value[valid_idx - 1] * value[valid_idx], sparse_sizes=(M, N))
+
+
+# =========================================================================== add.py
+def add_(src: SparseTensor, other: np.ndarray) -> SparseTensor:
+    """add.py:53-69 (dense [M,1] / [1,N] operand; the out-of-place `add` :12-28 computes the same)."""
+    rowptr, col, value = src.csr()
+    if other.shape[0] == src.size(0) and other.shape[1] == 1:
+        other = gather_csr(other.squeeze(1), rowptr)
+    elif other.shape[0] == 1 and other.shape[1] == src.size(1):
+        other = other.squeeze(0)[col]
+    else:
+        raise ValueError("Size mismatch")
+    if value is not None:
+        value = value + other.astype(value.dtype)
+    else:
+        value = other + np.ones((), dtype=other.dtype)
+    return src.set_value_(value, layout="coo")
+
+
+def add(src: SparseTensor, other) -> SparseTensor:
+    """add.py:12-50.  Sparse + sparse (:30-47): concatenate the COO triples, construct on the
+    element-wise maximum of the sizes, coalesce with "sum"; the value is dropped unless both have one."""
+    if isinstance(other, SparseTensor):
+        rowA, colA, valueA = src.coo()
+        rowB, colB, valueB = other.coo()
+        row = np.concatenate([rowA, rowB])
+        col = np.concatenate([colA, colB])
+        value = None
+        if valueA is not None and valueB is not None:
+            value = np.concatenate([valueA, valueB])
+        M = max(src.size(0), other.size(0))
+        N = max(src.size(1), other.size(1))
+        return SparseTensor(row=row, col=col, value=value, sparse_sizes=(M, N)).coalesce(reduce="sum")
+    out = SparseTensor.from_storage(src.storage)
+    if out.storage._value is not None:
+        out.storage._value = out.storage._value.copy()
+    return add_(out, other)
+
+
+# =========================================================================== tensor.py (symmetry)
+def is_symmetric(src: SparseTensor) -> bool:
+    """tensor.py:400-413."""
+    if src.sparse_size(0) != src.sparse_size(1):
+        return False
+    rowptr, col, value1 = src.csr()
+    colptr, row, value2 = src.csc()
+    if (rowptr != colptr).any() or (col != row).any():
+        return False
+    if value1 is None or value2 is None:
+        return True
+    return bool((value1 == value2).all())
+
+
+def to_symmetric(src: SparseTensor, reduce: str = "sum") -> SparseTensor:
+    """tensor.py:415-451: keys of [row;col]*N + [col;row] behind a -1 sentinel, sorted; a run starts
+    where the sorted key grows; values of a run are reduced with segment_csr; the index of a run is taken
+    from its first element.  Result is (N, N) with N = max(M, N)."""
+    N = max(src.size(0), src.size(1))
+    row, col, value = src.coo()
+    n = row.size
+    idx = np.full(2 * n + 1, -1, dtype=np.int64)
+    idx[1:n + 1] = row
+    idx[n + 1:] = col
+    idx[1:] *= N
+    idx[1:n + 1] += col
+    idx[n + 1:] += row
+    perm = np.argsort(idx, kind="stable")
+    idx = idx[perm]
+    mask = idx[1:] > idx[:-1]
+    perm = perm[1:] - 1
+    sel = perm[mask]
+    if value is not None:
+        ptr = np.concatenate([np.nonzero(mask)[0], np.array([perm.size], dtype=np.int64)])
+        value = segment_csr(np.concatenate([value, value])[perm], ptr, reduce)
+    new_row = np.concatenate([row, col])[sel]
+    new_col = np.concatenate([col, row])[sel]
+    return SparseTensor(row=new_row, col=new_col, value=value, sparse_sizes=(N, N),
+                        is_sorted=True, trust_data=True)
+
+
 # =========================================================================== index_select.py
 def index_select(src: SparseTensor, dim: int, idx: np.ndarray) -> SparseTensor:
     """index_select.py:13-96."""

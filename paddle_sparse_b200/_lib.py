@@ -51,6 +51,10 @@ SIGNATURES = {
     "ps_mul_row": [c_ptr, c_int, c_i64, c_ptr, c_i64, c_i64, c_ptr, c_ptr, c_ptr],
     "ps_mul_col": [c_ptr, c_int, c_i64, c_ptr, c_i64, c_ptr, c_ptr, c_ptr],
     "ps_mul_nnz": [c_ptr, c_int, c_i64, c_ptr, c_ptr, c_ptr],
+    "ps_add_row": [c_ptr, c_int, c_i64, c_ptr, c_i64, c_i64, c_ptr, c_ptr, c_ptr],
+    "ps_add_col": [c_ptr, c_int, c_i64, c_ptr, c_i64, c_ptr, c_ptr, c_ptr],
+    "ps_add_nnz": [c_ptr, c_int, c_i64, c_ptr, c_ptr, c_ptr],
+    "ps_coo_match": [c_ptr, c_ptr, c_i64, c_ptr, c_ptr, c_i64, c_ptr, c_ptr, c_ptr],
     "ps_mask_to_index": [c_ptr, c_i64, c_ptr, c_ptr, c_ptr],
     "ps_mask_entries": [c_ptr, c_ptr, c_i64, c_ptr, c_ptr, c_ptr],
     "ps_index_select_fill": [c_ptr, c_ptr, c_ptr, c_i64, c_ptr, c_i64, c_ptr, c_i64, c_ptr, c_ptr, c_ptr, c_ptr,

@@ -151,14 +151,15 @@ gather_csr_kernel(const U *__restrict__ src, int64_t upr, const int64_t *__restr
   }
 }
 
-// ============================================================================= broadcast multiply
-template <typename T>
-__device__ __forceinline__ T mul_values(T a, T b) {
-  using A = typename Acc<T>::type;
-  return from_acc<T>(to_acc<T>(a) * to_acc<T>(b));
+// ============================================================================= broadcast multiply / add
+// OP: 0 = multiply (mul.py), 1 = add (add.py) - same traversal, one arithmetic instruction apart
+enum { BC_MUL = 0, BC_ADD = 1 };
+template <typename T, int OP>
+__device__ __forceinline__ T bc_values(T a, T b) {
+  return OP == BC_MUL ? from_acc<T>(to_acc<T>(a) * to_acc<T>(b)) : from_acc<T>(to_acc<T>(a) + to_acc<T>(b));
 }
 
-template <typename T, int THREADS, int ITEMS>
+template <typename T, int OP, int THREADS, int ITEMS>
 __global__ void __launch_bounds__(THREADS)
 mul_row_kernel(const T *value, int64_t width, const int64_t *__restrict__ rowptr, int64_t M, int64_t nnz,
                const T *__restrict__ other, T *out) {
@@ -172,12 +173,12 @@ mul_row_kernel(const T *value, int64_t width, const int64_t *__restrict__ rowptr
   for (int64_t q = threadIdx.x; q < units; q += THREADS) {
     const int64_t j = q / width, f = q - j * width;
     const int64_t o = (e0 + j) * width + f;
-    out[o] = mul_values<T>(value[o], other[(int64_t)seg[j] * width + f]);
+    out[o] = bc_values<T, OP>(value[o], other[(int64_t)seg[j] * width + f]);
   }
 }
 
 // width == 1: the [nnz] value vector times an [M,1] operand; no divide, ITEMS independent loads per thread
-template <typename T, int THREADS, int ITEMS>
+template <typename T, int OP, int THREADS, int ITEMS>
 __global__ void __launch_bounds__(THREADS)
 mul_row_w1_kernel(const T *value, const int64_t *__restrict__ rowptr, int64_t M, int64_t nnz,
                   const T *__restrict__ other, T *out) {
@@ -196,11 +197,11 @@ mul_row_w1_kernel(const T *value, const int64_t *__restrict__ rowptr, int64_t M,
 #pragma unroll
   for (int k = 0; k < ITEMS; ++k) {
     const int j = k * THREADS + threadIdx.x;
-    if (j < tile_n) out[e0 + j] = mul_values<T>(v[k], other[seg[j]]);
+    if (j < tile_n) out[e0 + j] = bc_values<T, OP>(v[k], other[seg[j]]);
   }
 }
 
-template <typename T, int THREADS, int ITEMS>
+template <typename T, int OP, int THREADS, int ITEMS>
 __global__ void __launch_bounds__(THREADS)
 mul_col_w1_kernel(const T *value, const int64_t *__restrict__ col, int64_t nnz, const T *__restrict__ other, T *out) {
   const int64_t e0 = (int64_t)blockIdx.x * (THREADS * ITEMS) + threadIdx.x;
@@ -217,25 +218,25 @@ mul_col_w1_kernel(const T *value, const int64_t *__restrict__ col, int64_t nnz, 
 #pragma unroll
   for (int k = 0; k < ITEMS; ++k) {
     const int64_t e = e0 + k * THREADS;
-    if (e < nnz) out[e] = mul_values<T>(v[k], other[c[k]]);
+    if (e < nnz) out[e] = bc_values<T, OP>(v[k], other[c[k]]);
   }
 }
 
-template <typename T>
+template <typename T, int OP>
 __global__ void __launch_bounds__(256)
 mul_col_kernel(const T *value, int64_t width, const int64_t *__restrict__ col, int64_t n_units,
                const T *__restrict__ other, T *out) {
   const int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (q >= n_units) return;
   const int64_t e = q / width, f = q - e * width;
-  out[q] = mul_values<T>(value[q], other[col[e] * width + f]);
+  out[q] = bc_values<T, OP>(value[q], other[col[e] * width + f]);
 }
 
-template <typename T>
+template <typename T, int OP>
 __global__ void __launch_bounds__(256)
 mul_nnz_kernel(const T *value, int64_t n, const T *__restrict__ other, T *out) {
   const int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (q < n) out[q] = mul_values<T>(value[q], other[q]);
+  if (q < n) out[q] = bc_values<T, OP>(value[q], other[q]);
 }
 
 // ============================================================================= scatter reduce (by col)
@@ -393,6 +394,70 @@ static int reduce_all_typed(const T *src, int64_t n, T *out, cudaStream_t s) {
 
 }  // namespace ps
 
+namespace ps {
+
+template <int OP>
+static int bc_row(const void *value, int dtype, int64_t width, const int64_t *rowptr, int64_t M, int64_t nnz,
+                  const void *other, void *out, cudaStream_t s) {
+  PS_CHECK(width >= 1 && M >= 0 && nnz >= 0, "mul/add_row: bad sizes");
+  PS_CHECK(M < 2147483647LL, "mul/add_row: too many rows");
+  if (nnz == 0) return PS_OK;
+  constexpr int THREADS = 256, ITEMS = 8;
+  const unsigned blocks = (unsigned)ceil_div(nnz, THREADS * ITEMS);
+  if (width == 1) {
+    PS_DISPATCH_DTYPE(dtype, T,
+                      (mul_row_w1_kernel<T, OP, THREADS, ITEMS><<<blocks, THREADS, 0, s>>>(
+                          reinterpret_cast<const T *>(value), rowptr, M, nnz, reinterpret_cast<const T *>(other),
+                          reinterpret_cast<T *>(out))));
+  } else {
+    PS_DISPATCH_DTYPE(dtype, T,
+                      (mul_row_kernel<T, OP, THREADS, ITEMS><<<blocks, THREADS, 0, s>>>(
+                          reinterpret_cast<const T *>(value), width, rowptr, M, nnz,
+                          reinterpret_cast<const T *>(other), reinterpret_cast<T *>(out))));
+  }
+  PS_LAUNCH_OK();
+  return PS_OK;
+}
+
+template <int OP>
+static int bc_col(const void *value, int dtype, int64_t width, const int64_t *col, int64_t nnz, const void *other,
+                  void *out, cudaStream_t s) {
+  PS_CHECK(width >= 1 && nnz >= 0, "mul/add_col: bad sizes");
+  const int64_t n_units = nnz * width;
+  if (n_units == 0) return PS_OK;
+  if (width == 1) {
+    constexpr int THREADS = 256, ITEMS = 4;
+    const unsigned wblocks = (unsigned)ceil_div(nnz, THREADS * ITEMS);
+    PS_DISPATCH_DTYPE(dtype, T,
+                      (mul_col_w1_kernel<T, OP, THREADS, ITEMS><<<wblocks, THREADS, 0, s>>>(
+                          reinterpret_cast<const T *>(value), col, nnz, reinterpret_cast<const T *>(other),
+                          reinterpret_cast<T *>(out))));
+  } else {
+    const unsigned blocks = (unsigned)ceil_div(n_units, 256);
+    PS_DISPATCH_DTYPE(dtype, T,
+                      (mul_col_kernel<T, OP><<<blocks, 256, 0, s>>>(reinterpret_cast<const T *>(value), width, col,
+                                                                    n_units, reinterpret_cast<const T *>(other),
+                                                                    reinterpret_cast<T *>(out))));
+  }
+  PS_LAUNCH_OK();
+  return PS_OK;
+}
+
+template <int OP>
+static int bc_nnz(const void *value, int dtype, int64_t n, const void *other, void *out, cudaStream_t s) {
+  PS_CHECK(n >= 0, "mul/add_nnz: negative size");
+  if (n == 0) return PS_OK;
+  const unsigned blocks = (unsigned)ceil_div(n, 256);
+  PS_DISPATCH_DTYPE(dtype, T,
+                    (mul_nnz_kernel<T, OP><<<blocks, 256, 0, s>>>(reinterpret_cast<const T *>(value), n,
+                                                                  reinterpret_cast<const T *>(other),
+                                                                  reinterpret_cast<T *>(out))));
+  PS_LAUNCH_OK();
+  return PS_OK;
+}
+
+}  // namespace ps
+
 using namespace ps;
 
 extern "C" {
@@ -458,64 +523,25 @@ int ps_reduce_all(const void *src, int dtype, int64_t n, int reduce, void *out, 
 
 int ps_mul_row(const void *value, int dtype, int64_t width, const int64_t *rowptr, int64_t M, int64_t nnz,
                const void *other, void *out, void *stream) {
-  PS_CHECK(width >= 1 && M >= 0 && nnz >= 0, "mul_row: bad sizes");
-  PS_CHECK(M < 2147483647LL, "mul_row: too many rows");
-  if (nnz == 0) return PS_OK;
-  constexpr int THREADS = 256, ITEMS = 8;
-  const unsigned blocks = (unsigned)ceil_div(nnz, THREADS * ITEMS);
-  cudaStream_t s = (cudaStream_t)stream;
-  if (width == 1) {
-    PS_DISPATCH_DTYPE(dtype, T,
-                      (mul_row_w1_kernel<T, THREADS, ITEMS><<<blocks, THREADS, 0, s>>>(
-                          reinterpret_cast<const T *>(value), rowptr, M, nnz, reinterpret_cast<const T *>(other),
-                          reinterpret_cast<T *>(out))));
-    PS_LAUNCH_OK();
-    return PS_OK;
-  }
-  PS_DISPATCH_DTYPE(dtype, T,
-                    (mul_row_kernel<T, THREADS, ITEMS><<<blocks, THREADS, 0, s>>>(
-                        reinterpret_cast<const T *>(value), width, rowptr, M, nnz, reinterpret_cast<const T *>(other),
-                        reinterpret_cast<T *>(out))));
-  PS_LAUNCH_OK();
-  return PS_OK;
+  return bc_row<BC_MUL>(value, dtype, width, rowptr, M, nnz, other, out, (cudaStream_t)stream);
 }
-
+int ps_add_row(const void *value, int dtype, int64_t width, const int64_t *rowptr, int64_t M, int64_t nnz,
+               const void *other, void *out, void *stream) {
+  return bc_row<BC_ADD>(value, dtype, width, rowptr, M, nnz, other, out, (cudaStream_t)stream);
+}
 int ps_mul_col(const void *value, int dtype, int64_t width, const int64_t *col, int64_t nnz, const void *other,
                void *out, void *stream) {
-  PS_CHECK(width >= 1 && nnz >= 0, "mul_col: bad sizes");
-  const int64_t n_units = nnz * width;
-  if (n_units == 0) return PS_OK;
-  const unsigned blocks = (unsigned)ceil_div(n_units, 256);
-  cudaStream_t s = (cudaStream_t)stream;
-  if (width == 1) {
-    constexpr int THREADS = 256, ITEMS = 4;
-    const unsigned wblocks = (unsigned)ceil_div(nnz, THREADS * ITEMS);
-    PS_DISPATCH_DTYPE(dtype, T,
-                      (mul_col_w1_kernel<T, THREADS, ITEMS><<<wblocks, THREADS, 0, s>>>(
-                          reinterpret_cast<const T *>(value), col, nnz, reinterpret_cast<const T *>(other),
-                          reinterpret_cast<T *>(out))));
-    PS_LAUNCH_OK();
-    return PS_OK;
-  }
-  PS_DISPATCH_DTYPE(dtype, T,
-                    (mul_col_kernel<T><<<blocks, 256, 0, s>>>(reinterpret_cast<const T *>(value), width, col, n_units,
-                                                              reinterpret_cast<const T *>(other),
-                                                              reinterpret_cast<T *>(out))));
-  PS_LAUNCH_OK();
-  return PS_OK;
+  return bc_col<BC_MUL>(value, dtype, width, col, nnz, other, out, (cudaStream_t)stream);
 }
-
+int ps_add_col(const void *value, int dtype, int64_t width, const int64_t *col, int64_t nnz, const void *other,
+               void *out, void *stream) {
+  return bc_col<BC_ADD>(value, dtype, width, col, nnz, other, out, (cudaStream_t)stream);
+}
 int ps_mul_nnz(const void *value, int dtype, int64_t n, const void *other, void *out, void *stream) {
-  PS_CHECK(n >= 0, "mul_nnz: negative size");
-  if (n == 0) return PS_OK;
-  const unsigned blocks = (unsigned)ceil_div(n, 256);
-  cudaStream_t s = (cudaStream_t)stream;
-  PS_DISPATCH_DTYPE(dtype, T,
-                    (mul_nnz_kernel<T><<<blocks, 256, 0, s>>>(reinterpret_cast<const T *>(value), n,
-                                                              reinterpret_cast<const T *>(other),
-                                                              reinterpret_cast<T *>(out))));
-  PS_LAUNCH_OK();
-  return PS_OK;
+  return bc_nnz<BC_MUL>(value, dtype, n, other, out, (cudaStream_t)stream);
+}
+int ps_add_nnz(const void *value, int dtype, int64_t n, const void *other, void *out, void *stream) {
+  return bc_nnz<BC_ADD>(value, dtype, n, other, out, (cudaStream_t)stream);
 }
 
 }  // extern "C"

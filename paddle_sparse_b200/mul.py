@@ -1,5 +1,6 @@
-"""Dense-broadcast multiply (reference: paddle_sparse/mul.py:12-33, 76-128).  The sparse (.) sparse
-branch (mul.py:35-73) is a "next" row of SURVEY.md 8f."""
+"""Multiply (reference: paddle_sparse/mul.py:12-128): a dense [M,1] / [1,N] operand broadcast over the stored
+entries, an [nnz] operand, or another coalesced SparseTensor (intersection of the entry sets, values of
+equal entries multiplied; mul.py:35-73)."""
 from __future__ import annotations
 
 from typing import Optional
@@ -30,10 +31,34 @@ def _broadcast_mul(src: SparseTensor, other: torch.Tensor, inplace: bool):
     return ops.mul_row(value, rowptr, vec, out) if row_wise else ops.mul_col(value, col, vec, out)
 
 
+def _sparse_mul(src: SparseTensor, other: SparseTensor) -> SparseTensor:
+    """mul.py:35-73.  Both operands are coalesced, so the reference's concat + argsort + adjacent-equal scan
+    is an intersection of two sorted sets: each entry of A looks its column up in B's row (ps_coo_match), the
+    matches are compacted in order (they stay sorted by (row, col)) and the two values multiplied."""
+    if not src.is_coalesced():
+        raise ValueError("The `src` tensor is not coalesced")
+    if not other.is_coalesced():
+        raise ValueError("The `other` tensor is not coalesced")
+    rowA, colA, valueA = src.coo()
+    rowptrB, colB, valueB = other.csr()
+    if valueA is None or valueB is None:
+        raise ValueError("Both sparse tensors must contain values")
+    if valueA.dtype != valueB.dtype or valueA.shape[1:] != valueB.shape[1:]:
+        raise ValueError("sparse * sparse: value dtypes / trailing shapes differ")
+    M = max(src.size(0), other.size(0))
+    N = max(src.size(1), other.size(1))
+    pos, mask = ops.coo_match(rowA, colA, rowptrB, colB)
+    sel = ops.mask_to_index(mask)
+    value = ops.mul_nnz(ops.gather_rows(valueA, sel), ops.gather_rows(valueB, ops.gather_rows(pos, sel)))
+    return SparseTensor(row=ops.gather_rows(rowA, sel), col=ops.gather_rows(colA, sel), value=value,
+                        sparse_sizes=(M, N), is_sorted=True, trust_data=True)
+
+
 def mul(src: SparseTensor, other):
     if isinstance(other, torch.Tensor):
         return src.set_value(_broadcast_mul(src, other, inplace=False), layout="coo")
-    raise NotImplementedError("sparse (.) sparse mul is outside the SparseStorage hot path (SURVEY.md 8f)")
+    assert isinstance(other, SparseTensor)
+    return _sparse_mul(src, other)
 
 
 def mul_(src: SparseTensor, other: torch.Tensor) -> SparseTensor:

@@ -354,31 +354,68 @@ def reduce_all(src: torch.Tensor, reduce: str = "sum") -> torch.Tensor:
     return res[0]
 
 
-# ------------------------------------------------------------------ broadcast multiply (mul.py:76-119)
-def mul_row(value, rowptr, other, out=None):
+# ------------------------------------------------------------------ broadcast multiply / add (mul.py:76-119, add.py:12-81)
+def _bc_row(sym, value, rowptr, other, out=None):
     value, rowptr, other = _dev(value, "value"), _idx(rowptr, "rowptr"), _dev(other, "other")
     out = torch.empty_like(value) if out is None else out
     with torch.cuda.device(value.device):
-        _lib.call("ps_mul_row", _p(value), dtype_code(value), max(_width(value), 1), _p(rowptr), rowptr.numel() - 1,
+        _lib.call(sym, _p(value), dtype_code(value), max(_width(value), 1), _p(rowptr), rowptr.numel() - 1,
                   value.shape[0], _p(other), _p(out), _stream(value))
     return out
 
 
-def mul_col(value, col, other, out=None):
+def _bc_col(sym, value, col, other, out=None):
     value, col, other = _dev(value, "value"), _idx(col, "col"), _dev(other, "other")
     out = torch.empty_like(value) if out is None else out
     with torch.cuda.device(value.device):
-        _lib.call("ps_mul_col", _p(value), dtype_code(value), max(_width(value), 1), _p(col), value.shape[0],
+        _lib.call(sym, _p(value), dtype_code(value), max(_width(value), 1), _p(col), value.shape[0],
                   _p(other), _p(out), _stream(value))
     return out
 
 
-def mul_nnz(value, other, out=None):
+def _bc_nnz(sym, value, other, out=None):
     value, other = _dev(value, "value"), _dev(other, "other")
     out = torch.empty_like(value) if out is None else out
     with torch.cuda.device(value.device):
-        _lib.call("ps_mul_nnz", _p(value), dtype_code(value), value.numel(), _p(other), _p(out), _stream(value))
+        _lib.call(sym, _p(value), dtype_code(value), value.numel(), _p(other), _p(out), _stream(value))
     return out
+
+
+def mul_row(value, rowptr, other, out=None):
+    return _bc_row("ps_mul_row", value, rowptr, other, out)
+
+
+def mul_col(value, col, other, out=None):
+    return _bc_col("ps_mul_col", value, col, other, out)
+
+
+def mul_nnz(value, other, out=None):
+    return _bc_nnz("ps_mul_nnz", value, other, out)
+
+
+def add_row(value, rowptr, other, out=None):
+    return _bc_row("ps_add_row", value, rowptr, other, out)
+
+
+def add_col(value, col, other, out=None):
+    return _bc_col("ps_add_col", value, col, other, out)
+
+
+def add_nnz(value, other, out=None):
+    return _bc_nnz("ps_add_nnz", value, other, out)
+
+
+# ------------------------------------------------------------------ set operations (mul.py:35-73)
+def coo_match(row, col, rowptr_b, col_b):
+    """Position in the coalesced CSR (rowptr_b, col_b) of every entry (row[e], col[e]), -1 when absent,
+    and the byte mask of the matched entries."""
+    row, col, rowptr_b, col_b = _idx(row, "row"), _idx(col, "col"), _idx(rowptr_b, "rowptr"), _idx(col_b, "col")
+    pos = _new(row, row.numel())
+    mask = _new(row, row.numel(), torch.uint8)
+    with torch.cuda.device(row.device):
+        _lib.call("ps_coo_match", _p(row), _p(col), row.numel(), _p(rowptr_b), _p(col_b), rowptr_b.numel() - 1,
+                  _p(pos), _p(mask), _stream(row))
+    return pos, mask
 
 
 # ------------------------------------------------------------------ select building blocks

@@ -228,6 +228,19 @@ class SparseTensor(object):
             return True
         return bool(torch.equal(value1, value2))
 
+    def to_symmetric(self, reduce: str = "sum"):
+        """tensor.py:415-451: the entries plus their mirror images on an (N, N) grid, N = max(M, N), equal
+        positions reduced.  The reference sorts 2*nnz keys and runs segment_csr over the runs; here the doubled
+        triple goes through the constructor unsorted and coalesce(reduce) - one fused sort + dedup-reduce."""
+        N = max(self.size(0), self.size(1))
+        row, col, value = self.coo()
+        new_row = torch.cat([row, col], dim=0)
+        new_col = torch.cat([col, row], dim=0)
+        if value is not None:
+            value = torch.cat([value, value], dim=0)
+        out = self.__class__(row=new_row, col=new_col, value=value, sparse_sizes=(N, N), trust_data=True)
+        return out.coalesce(reduce)
+
     # ------------------------------------------------------------------ autograd / device / dtype
     def detach_(self):
         value = self.storage.value()

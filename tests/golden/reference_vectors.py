@@ -51,3 +51,18 @@ PERMUTE = dict(row=[0, 0, 1, 2, 2], col=[0, 1, 0, 1, 2], value=[1, 2, 3, 4, 5],
                out_value=[3, 2, 1, 4, 5])
 
 # test/test_tensor.py:71-88 exercises to_symmetric (a "next" row) — not pinned here.
+
+# test/test_add.py:15-39 (sparse + sparse)
+SPARSE_ADD = dict(rowA=[0, 0, 1, 2, 2], colA=[0, 2, 1, 0, 1], valueA=[1, 2, 4, 1, 3],
+                  rowB=[0, 0, 1, 2, 2], colB=[1, 2, 2, 1, 2], valueB=[2, 3, 1, 2, 4],
+                  row=[0, 0, 0, 1, 1, 2, 2, 2], col=[0, 1, 2, 1, 2, 0, 1, 2], value=[1, 2, 5, 4, 1, 1, 5, 4])
+
+# test/test_mul.py:15-39 and :42-61 (sparse (.) sparse; second case has an empty result)
+SPARSE_MUL = dict(rowA=[0, 0, 1, 2, 2], colA=[0, 2, 1, 0, 1], valueA=[1, 2, 4, 1, 3],
+                  rowB=[0, 0, 1, 2, 2], colB=[1, 2, 2, 1, 2], valueB=[2, 3, 1, 2, 4],
+                  row=[0, 2], col=[2, 1], value=[6, 6])
+SPARSE_MUL_EMPTY = dict(rowA=[0], colA=[1], valueA=[1], rowB=[1], colB=[0], valueB=[2], row=[], col=[], value=[])
+
+# test/test_tensor.py:71-88
+TO_SYMMETRIC = dict(row=[0, 0, 0, 1, 1], col=[0, 1, 2, 0, 2], value=[1, 2, 3, 4, 5],
+                    dense=[[2, 6, 3], [6, 0, 5], [3, 5, 0]])

@@ -223,6 +223,143 @@ def test_mul_broadcast(ps, dtype):
     assert torch.equal(A.mul_nnz(w, layout="coo").storage.value(), tv * w)
 
 
+# ----------------------------------------------------------------------------- add / sparse mul / to_symmetric
+@pytest.mark.parametrize("dtype", [torch.float32, torch.float64, torch.int64, torch.bfloat16, torch.float16])
+def test_sparse_add_mul_golden(ps, dtype):
+    """test/test_add.py:15-39, test/test_mul.py:15-61."""
+    def T(r, c, v):
+        return ps.SparseTensor(row=dev(np.array(r, I64)), col=dev(np.array(c, I64)),
+                               value=dev(np.array(v, np.float32), dtype))
+    g = G.SPARSE_ADD
+    C = T(g["rowA"], g["colA"], g["valueA"]) + T(g["rowB"], g["colB"], g["valueB"])
+    row, col, val = C.coo()
+    assert row.tolist() == g["row"] and col.tolist() == g["col"] and host(val).tolist() == g["value"]
+    assert val.dtype == dtype
+    for g in (G.SPARSE_MUL, G.SPARSE_MUL_EMPTY):
+        C = T(g["rowA"], g["colA"], g["valueA"]) * T(g["rowB"], g["colB"], g["valueB"])
+        row, col, val = C.coo()
+        assert row.tolist() == g["row"] and col.tolist() == g["col"] and host(val).tolist() == g["value"]
+    dup = T([0, 0], [1, 1], [1, 2])
+    with pytest.raises(ValueError):  # mul.py:38-41
+        dup * dup
+
+
+def test_to_symmetric_golden(ps):
+    """test/test_tensor.py:71-88."""
+    g = G.TO_SYMMETRIC
+    A = ps.SparseTensor(row=dev(np.array(g["row"], I64)), col=dev(np.array(g["col"], I64)),
+                        value=dev(np.array(g["value"], I64)))
+    assert not A.is_symmetric()
+    S = A.to_symmetric()
+    assert S.is_symmetric()
+    assert S.to_dense().tolist() == g["dense"]
+
+
+@pytest.mark.parametrize("with_value", [True, False])
+@pytest.mark.parametrize("sizes", [((400, 300), (350, 420)), ((5000, 5000), (5000, 5000))])
+def test_sparse_add_matches_oracle(ps, sizes, with_value):
+    rng = np.random.default_rng(31)
+    (MA, NA), (MB, NB) = sizes
+    rowA, colA = _random_coo(rng, MA, NA, 30000)
+    rowB, colB = _random_coo(rng, MB, NB, 40000)
+    vA = rng.integers(0, 1 << 20, rowA.size).astype(np.float64) if with_value else None
+    vB = rng.integers(0, 1 << 20, rowB.size).astype(np.float64) if with_value else None
+    A = ps.SparseTensor(row=dev(rowA), col=dev(colA), value=dev(vA) if with_value else None, sparse_sizes=(MA, NA))
+    B = ps.SparseTensor(row=dev(rowB), col=dev(colB), value=dev(vB) if with_value else None, sparse_sizes=(MB, NB))
+    OA = np_ref.SparseTensor(row=rowA, col=colA, value=vA, sparse_sizes=(MA, NA))
+    OB = np_ref.SparseTensor(row=rowB, col=colB, value=vB, sparse_sizes=(MB, NB))
+    C, OC = A + B, np_ref.add(OA, OB)
+    assert tuple(C.sparse_sizes()) == tuple(OC.sparse_sizes())
+    for got, want in zip(C.coo(), OC.coo()):
+        assert (got is None) == (want is None)
+        if got is not None:
+            assert np.array_equal(host(got), want)  # integer-valued doubles: sums exact in any order
+    assert np.array_equal(host(C.storage.rowptr()), OC.storage.rowptr())
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.float64, torch.bfloat16])
+@pytest.mark.parametrize("width", [0, 3])
+def test_sparse_mul_matches_oracle(ps, dtype, width):
+    rng = np.random.default_rng(37)
+    MA, NA, MB, NB = 600, 700, 650, 500
+    rowA, colA = _random_coo(rng, MA, NA, 60000)
+    rowB, colB = _random_coo(rng, MB, NB, 50000)
+    shape = lambda n: (n,) if width == 0 else (n, width)  # noqa: E731
+    vA = rng.integers(1, 16, shape(rowA.size)).astype(np.float64)  # products < 256: exact in bf16
+    vB = rng.integers(1, 16, shape(rowB.size)).astype(np.float64)
+    A = ps.SparseTensor(row=dev(rowA), col=dev(colA), value=dev(vA, dtype), sparse_sizes=(MA, NA)).coalesce("max")
+    B = ps.SparseTensor(row=dev(rowB), col=dev(colB), value=dev(vB, dtype), sparse_sizes=(MB, NB)).coalesce("max")
+    OA = np_ref.SparseTensor(row=rowA, col=colA, value=vA, sparse_sizes=(MA, NA)).coalesce("max")
+    OB = np_ref.SparseTensor(row=rowB, col=colB, value=vB, sparse_sizes=(MB, NB)).coalesce("max")
+    C, OC = A * B, np_ref.mul_sparse(OA, OB)
+    assert C.nnz() == OC.nnz() > 0
+    assert tuple(C.sparse_sizes()) == tuple(OC.sparse_sizes()) == (650, 700)
+    for got, want in zip(C.coo(), OC.coo()):
+        assert np.array_equal(host(got), want)
+    assert C.is_coalesced()
+    E = A * ps.SparseTensor(row=dev(np.array([MB - 1], I64)), col=dev(np.array([NB - 1], I64)),
+                            value=dev(np.ones(shape(1)), dtype), sparse_sizes=(MB, NB))
+    assert E.nnz() in (0, 1)
+
+
+@pytest.mark.parametrize("reduce", ["sum", "mean", "min", "max"])
+@pytest.mark.parametrize("with_value", [True, False])
+def test_to_symmetric_matches_oracle(ps, reduce, with_value):
+    rng = np.random.default_rng(41)
+    M, N = 900, 1100
+    row, col = _random_coo(rng, M, N, 50000)
+    val = rng.integers(0, 1 << 16, row.size).astype(np.float64) if with_value else None
+    A = ps.SparseTensor(row=dev(row), col=dev(col), value=dev(val) if with_value else None, sparse_sizes=(M, N))
+    O = np_ref.SparseTensor(row=row, col=col, value=val, sparse_sizes=(M, N))
+    S, OS = A.to_symmetric(reduce), np_ref.to_symmetric(O, reduce)
+    assert tuple(S.sparse_sizes()) == tuple(OS.sparse_sizes()) == (1100, 1100)
+    assert np.array_equal(host(S.storage.row()), OS.storage.row())
+    assert np.array_equal(host(S.storage.col()), OS.storage.col())
+    if with_value:
+        np.testing.assert_allclose(host(S.storage.value()), OS.storage.value(), rtol=1e-12)
+    else:
+        assert S.storage.value() is None
+    assert S.is_symmetric()
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16, torch.float64])
+def test_add_broadcast(ps, dtype):
+    """add.py:12-28, 53-100 against the oracle's restatement."""
+    rng = np.random.default_rng(29)
+    M, N = 300, 500
+    row, col, val = _pair(rng, M, N, 20000)
+    tv = dev(val, dtype)
+    seen = tv.float().cpu().numpy().astype(np.float64) if dtype != torch.float64 else host(tv)
+    orow = dev(rng.random((M, 1)).astype(np.float32), dtype)
+    ocol = dev(rng.random((1, N)).astype(np.float32), dtype)
+    for other in (orow, ocol):
+        A = ps.SparseTensor(row=dev(row), col=dev(col), value=tv.clone(), sparse_sizes=(M, N))
+        O = np_ref.SparseTensor(row=row, col=col, value=seen.copy(), sparse_sizes=(M, N))
+        want = np_ref.add(O, other.float().cpu().numpy().astype(np.float64)).storage.value()
+        rtol = {torch.float32: 1e-6, torch.bfloat16: 8e-3, torch.float64: 1e-12}[dtype]
+        out = A.add(other)
+        np.testing.assert_allclose(host(out.storage.value()), want, rtol=rtol)
+        assert torch.equal(A.storage.value(), tv)  # out of place
+        assert torch.equal((A + other).storage.value(), out.storage.value())
+        B = A.add_(other)
+        assert B is A and torch.equal(A.storage.value(), out.storage.value())
+    V = ps.SparseTensor(row=dev(row), col=dev(col), sparse_sizes=(M, N))  # value-less: entries count as 1
+    srow, scol = host(V.storage.row()), host(V.storage.col())
+    np.testing.assert_allclose(host((V + orow).storage.value()), host(orow)[:, 0][srow] + 1, rtol=8e-3)
+    np.testing.assert_allclose(host((V + ocol).storage.value()), host(ocol)[0][scol] + 1, rtol=8e-3)
+    with pytest.raises(ValueError):
+        V.add(dev(np.ones((3, 3), np.float32)))
+    A = ps.SparseTensor(row=dev(row), col=dev(col), value=tv.clone(), sparse_sizes=(M, N))
+    w = dev(rng.random(row.size).astype(np.float32), dtype)
+    assert torch.equal(A.add_nnz(w, layout="coo").storage.value(), tv + w)
+    wide = dev(rng.random((row.size, 3)).astype(np.float32), dtype)
+    Aw = ps.SparseTensor(row=dev(row), col=dev(col), value=wide.clone(), sparse_sizes=(M, N))
+    o3 = dev(rng.random((M, 1, 3)).astype(np.float32), dtype)
+    got = Aw.add(o3).storage.value()
+    want = Aw.storage.value().double() + o3[:, 0][Aw.storage.row()].double()
+    np.testing.assert_allclose(got.double().cpu().numpy(), want.cpu().numpy(), rtol=8e-3)
+
+
 # ----------------------------------------------------------------------------- index_select / masked_select
 def test_permute_golden(ps):
     g = G.PERMUTE

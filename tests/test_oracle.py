@@ -178,6 +178,50 @@ def test_permute_golden():
     assert val.tolist() == g["out_value"]
 
 
+@pytest.mark.parametrize("dtype", DTYPES)
+def test_sparse_add_mul_golden(dtype):
+    """test/test_add.py:15-39, test/test_mul.py:15-61."""
+    def T(r, c, v):
+        return np_ref.SparseTensor(row=a(r), col=a(c), value=a(v, dtype))
+    g = G.SPARSE_ADD
+    row, col, val = np_ref.add(T(g["rowA"], g["colA"], g["valueA"]), T(g["rowB"], g["colB"], g["valueB"])).coo()
+    assert row.tolist() == g["row"] and col.tolist() == g["col"] and val.tolist() == g["value"]
+    assert val.dtype == dtype
+    for g in (G.SPARSE_MUL, G.SPARSE_MUL_EMPTY):
+        C = np_ref.mul_sparse(T(g["rowA"], g["colA"], g["valueA"]), T(g["rowB"], g["colB"], g["valueB"]))
+        row, col, val = C.coo()
+        assert row.tolist() == g["row"] and col.tolist() == g["col"] and val.tolist() == g["value"]
+    dup = np_ref.SparseTensor(row=a([0, 0]), col=a([1, 1]), value=a([1, 2], dtype))
+    with pytest.raises(ValueError):  # mul.py:38-41
+        np_ref.mul_sparse(dup, dup)
+
+
+def test_to_symmetric_golden():
+    """test/test_tensor.py:71-88."""
+    g = G.TO_SYMMETRIC
+    A = np_ref.SparseTensor(row=a(g["row"]), col=a(g["col"]), value=a(g["value"]))
+    assert not np_ref.is_symmetric(A)
+    S = np_ref.to_symmetric(A)
+    assert np_ref.is_symmetric(S)
+    assert S.to_dense().tolist() == g["dense"]
+    assert S.sparse_sizes() == (3, 3)
+
+
+def test_dense_add_matches_dense_arithmetic():
+    """add.py:53-69 against the dense matrix it describes."""
+    rng = np.random.default_rng(5)
+    M, N = 7, 9
+    key = rng.choice(M * N, 30, replace=False)
+    row, col = (key // N).astype(I64), (key % N).astype(I64)
+    val = rng.random(30)
+    A = np_ref.SparseTensor(row=row, col=col, value=val, sparse_sizes=(M, N))
+    orow, ocol = rng.random((M, 1)), rng.random((1, N))
+    r, c, v = np_ref.add(A, orow).coo()
+    assert np.allclose(v, A.to_dense()[r, c] + orow[r, 0])
+    r, c, v = np_ref.add(A, ocol).coo()
+    assert np.allclose(v, A.to_dense()[r, c] + ocol[0, c])
+
+
 def test_paddle_scatter_restatement():
     src = a([1, 2, 3, 4, 5, 6], np.float32)
     ptr = a([0, 2, 2, 5, 6])
