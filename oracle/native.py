@@ -23,6 +23,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _REF_PATH = os.path.join(_HERE, "_ref", "libps_ref_cpu.so")
 _PORT_PATH = os.path.join(_HERE, "_build", "libps_oracle_port.so")
+_REF_CUDA_PATH = os.path.join(_HERE, "_ref", "libps_ref_cuda.so")
 
 _i64p = ctypes.POINTER(ctypes.c_int64)
 _ref = None
@@ -39,10 +40,36 @@ def build(ref: bool = True) -> None:
     subprocess.check_call(["make", "-s", "-C", _HERE, "port"])
     if ref and os.path.isdir("/root/reference/csrc"):
         subprocess.check_call(["make", "-s", "-C", _HERE, "ref"])
+        subprocess.check_call(["make", "-s", "-C", _HERE, "refcuda"])
 
 
 def have_ref() -> bool:
     return os.path.exists(_REF_PATH)
+
+
+def have_ref_cuda() -> bool:
+    return os.path.exists(_REF_CUDA_PATH)
+
+
+_ref_cuda = None
+
+
+def ref_cuda_lib():
+    """The reference's own CUDA ind2ptr / ptr2ind (csrc/cuda/convert_cuda.cu, unmodified, sm_100a) behind
+    oracle/ref_cuda_shim.cu.  Arguments are raw device pointers (ints) and a stream handle."""
+    global _ref_cuda
+    if _ref_cuda is None:
+        if not have_ref_cuda():
+            raise FileNotFoundError(
+                f"{_REF_CUDA_PATH} not built (run `make -C oracle refcuda` where /root/reference exists)"
+            )
+        lib = ctypes.CDLL(_REF_CUDA_PATH)
+        lib.refcuda_last_error.restype = ctypes.c_char_p
+        for f in (lib.refcuda_ind2ptr, lib.refcuda_ptr2ind):
+            f.argtypes = [ctypes.c_void_p, ctypes.c_int64, ctypes.c_int64, ctypes.c_void_p, ctypes.c_void_p]
+            f.restype = ctypes.c_int
+        _ref_cuda = lib
+    return _ref_cuda
 
 
 def port_lib():
