@@ -123,3 +123,54 @@ def build_partitioned(row, col, value, sparse_sizes, group=None, reduce: str = "
     shard = RowShard(A, r0, r1, (M, N), splitters, sent, n_recv)
     shard.transposed = At
     return shard
+
+
+# ------------------------------------------------------------------ second exchange
+def combine_column_partials(partial: torch.Tensor, count: torch.Tensor, reduce: str, group=None) -> torch.Tensor:
+    """Global `reduction(dim=0)` (reduce.py:40-42) from per-shard results.  `partial[c]` is this shard's
+    reduction over its own entries of column c - the SUM for sum / mean, the min / max otherwise, 0 where the
+    shard has no entry (as scatter leaves it) - and `count[c]` how many entries that was.
+    sum: all-reduce(SUM).  mean: all-reduce(SUM) of sums and counts, one division (floor for integers, as
+    scatter's mean).  min / max: columns a shard does not touch are neutralised before all-reduce(MIN / MAX) and
+    columns nobody touches come back as 0, the value scatter gives an empty segment."""
+    reduce = "sum" if reduce == "add" else reduce
+    if reduce not in ("sum", "mean", "min", "max"):
+        raise ValueError(reduce)
+    wide = (slice(None),) + (None,) * (partial.dim() - 1)
+    if reduce == "sum":
+        acc = partial.clone()
+        dist.all_reduce(acc, op=dist.ReduceOp.SUM, group=group)
+        return acc
+    total = count.clone()
+    dist.all_reduce(total, op=dist.ReduceOp.SUM, group=group)
+    if reduce == "mean":
+        acc = partial.clone()
+        dist.all_reduce(acc, op=dist.ReduceOp.SUM, group=group)
+        den = total.clamp(min=1)[wide]
+        if acc.dtype.is_floating_point:
+            return acc / den.to(acc.dtype)
+        return torch.div(acc, den, rounding_mode="floor")
+    info = torch.finfo(partial.dtype) if partial.dtype.is_floating_point else torch.iinfo(partial.dtype)
+    neutral = info.max if reduce == "min" else info.min
+    acc = torch.where((count > 0)[wide], partial, torch.full_like(partial, neutral))
+    dist.all_reduce(acc, op=dist.ReduceOp.MIN if reduce == "min" else dist.ReduceOp.MAX, group=group)
+    return torch.where((total > 0)[wide], acc, torch.zeros_like(acc))
+
+
+def reduce_columns(shard: RowShard, reduce: str = "sum", group=None) -> torch.Tensor:
+    """`A.sum(dim=0)` / mean / min / max of the GLOBAL matrix, identical on every rank: the shard-local scatter
+    reduction over `col` ([N] partials, ps_scatter_reduce) followed by one all-reduce over NVLink."""
+    from .reduce import reduction
+    reduce = "sum" if reduce == "add" else reduce
+    A = shard.tensor
+    partial = reduction(A, dim=0, reduce="sum" if reduce == "mean" else reduce)
+    return combine_column_partials(partial, A.storage.colcount(), reduce, group)
+
+
+def transpose_partitioned(shard: RowShard, group=None, fill_cache: bool = True) -> RowShard:
+    """Global `A.t()` (transpose.py:9-33) under row partitioning: the rows of the transpose are the columns of
+    A, which every shard holds a slice of, so this is the second all-to-all - keyed on col - through the same
+    route / coalesce / CSR build.  Returns this rank's row shard of the N x M transpose."""
+    st = shard.tensor.storage
+    M, N = shard.sparse_sizes
+    return build_partitioned(st.col(), shard.global_row(), st.value(), (N, M), group, "add", fill_cache, False)

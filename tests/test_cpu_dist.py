@@ -10,6 +10,7 @@ import torch
 import torch.distributed as dist
 import torch.multiprocessing as mp
 
+from oracle import np_ref
 from paddle_sparse_b200 import dist as psd
 
 
@@ -97,3 +98,48 @@ def test_route_tuples_gloo_world2():
         assert np.array_equal(r["val"], all_src[2][own])
     assert sum(r["recv"] for r in res) == world * per_rank
     assert abs(res[0]["recv"] - res[1]["recv"]) < 0.2 * per_rank  # nnz-balanced despite the skew
+
+
+def _col_worker(rank, world, port, N, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        rng = np.random.default_rng(2000 + rank)
+        res = {}
+        for dt in (np.float64, np.int64):
+            col = rng.integers(0, N, 400)
+            col = col[col % 5 != rank]           # columns only one rank touches, and (c % 5 in {0,1} on both missing) none
+            col = col[col % 7 != 3]              # columns nobody touches
+            val = (rng.integers(-50, 50, (col.size, 2))).astype(dt)
+            res[dt.__name__] = dict(col=col, val=val)
+            for red in ("sum", "mean", "min", "max"):
+                local = "sum" if red == "mean" else red
+                partial = torch.from_numpy(np_ref.scatter(val, col, N, local))
+                count = torch.from_numpy(np.bincount(col, minlength=N).astype(np.int64))
+                res[dt.__name__][red] = psd.combine_column_partials(partial, count, red).numpy()
+        out[rank] = res
+    finally:
+        dist.destroy_process_group()
+
+
+def test_combine_column_partials_gloo_world2():
+    """dim=0 reductions across row shards == the reduction over the union (reduce.py:40-42 semantics)."""
+    world, N = 2, 64
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    out = mp.Manager().dict()
+    mp.spawn(_col_worker, args=(world, port, N, out), nprocs=world, join=True)
+    for dt in ("float64", "int64"):
+        col = np.concatenate([out[r][dt]["col"] for r in range(world)])
+        val = np.concatenate([out[r][dt]["val"] for r in range(world)])
+        assert np.setdiff1d(np.arange(N), col).size > 0  # some columns are empty everywhere
+        for red in ("sum", "mean", "min", "max"):
+            want = np_ref.scatter(val, col, N, red)
+            for r in range(world):
+                got = out[r][dt][red]
+                assert got.dtype == want.dtype
+                if dt == "int64":
+                    assert np.array_equal(got, want), (dt, red)
+                else:
+                    np.testing.assert_allclose(got, want, rtol=1e-12, err_msg=f"{dt} {red}")
