@@ -171,6 +171,15 @@ int ps_coo_match(const int64_t *row, const int64_t *col, int64_t n, const int64_
                  const int64_t *col_b, int64_t M_b, int64_t *out_pos, uint8_t *out_mask,
                  void *stream);
 
+/* ------------------------------------------------------------------ cat */
+/* cat.py:49-276: out = concat_k(src_k[0:lens[k]] + deltas[k]) in one launch per 32 pieces
+ * (rows / cols shifted by the running sizes, pointers and permutations by the running nnz).
+ * srcs / lens / deltas are HOST arrays of K entries; srcs[k] and out are device pointers. */
+int ps_concat_add_i64(const int64_t *const *srcs, const int64_t *lens, const int64_t *deltas,
+                      int64_t K, int64_t *out, void *stream);
+/* the value concat of cat.py (any dtype / trailing shape): K device-to-device copies on `stream`. */
+int ps_concat_bytes(const void *const *srcs, const int64_t *nbytes, int64_t K, void *out, void *stream);
+
 /* ------------------------------------------------------------------ select */
 /* masked_select.py:18-24: indices of the set entries of a byte mask, ascending.
  * out_idx sized n; *host_count = number selected.  Synchronises. */

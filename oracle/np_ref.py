@@ -584,6 +584,63 @@ def to_symmetric(src: SparseTensor, reduce: str = "sum") -> SparseTensor:
                         is_sorted=True, trust_data=True)
 
 
+# =========================================================================== cat.py
+def _cat_pieces(parts, shifts, pointer=False):
+    """`concat([x_k + shift_k])`, None unless every operand has the piece; pointers drop their leading entry
+    after the first operand (cat.py:63, :137, :201, :216)."""
+    if any(p is None for p in parts):
+        return None
+    out = []
+    for k, (p, sh) in enumerate(zip(parts, shifts)):
+        out.append((p[1:] if pointer and k > 0 else p) + sh)
+    return np.concatenate(out)
+
+
+def cat(tensors, dim):
+    """cat.py:12-276: dim 0 (cat_first :49-112), dim 1 (cat_second :115-172), dim (0, 1) (cat_diag :175-276),
+    or a dense value dimension (:25-32)."""
+    assert len(tensors) > 0
+    st = [t.storage for t in tensors]
+    rows_off = np.concatenate([[0], np.cumsum([t.sparse_size(0) for t in tensors])]).tolist()
+    cols_off = np.concatenate([[0], np.cumsum([t.sparse_size(1) for t in tensors])]).tolist()
+    nnz_off = np.concatenate([[0], np.cumsum([t.nnz() for t in tensors])]).tolist()
+    zeros = [0] * len(tensors)
+    vals = [s._value for s in st]
+    value = None if any(v is None for v in vals) else np.concatenate(vals)
+    if isinstance(dim, int):
+        dim = tensors[0].dim() + dim if dim < 0 else dim
+        if dim == 0:
+            storage = SparseStorage(
+                row=_cat_pieces([s._row for s in st], rows_off), rowptr=_cat_pieces([s._rowptr for s in st], nnz_off, True),
+                col=np.concatenate([s._col for s in st]), value=value,
+                sparse_sizes=(rows_off[-1], max(t.sparse_size(1) for t in tensors)),
+                rowcount=_cat_pieces([s._rowcount for s in st], zeros), is_sorted=True)
+            return SparseTensor.from_storage(storage)
+        if dim == 1:
+            storage = SparseStorage(
+                row=np.concatenate([t.coo()[0] for t in tensors]), rowptr=None,
+                col=_cat_pieces([s._col for s in st], cols_off), value=value,
+                sparse_sizes=(max(t.sparse_size(0) for t in tensors), cols_off[-1]),
+                colptr=_cat_pieces([s._colptr for s in st], nnz_off, True),
+                colcount=_cat_pieces([s._colcount for s in st], zeros), is_sorted=False)
+            return SparseTensor.from_storage(storage)
+        if 1 < dim < tensors[0].dim():
+            values = [t.storage.value() for t in tensors]
+            assert all(v is not None for v in values)
+            return tensors[0].set_value(np.concatenate(values, axis=dim - 1), layout="coo")
+        raise IndexError("Dimension out of range")
+    assert isinstance(dim, (tuple, list)) and len(dim) == 2 and sorted(dim) == [0, 1]
+    storage = SparseStorage(
+        row=_cat_pieces([s._row for s in st], rows_off), rowptr=_cat_pieces([s._rowptr for s in st], nnz_off, True),
+        col=_cat_pieces([s._col for s in st], cols_off), value=value, sparse_sizes=(rows_off[-1], cols_off[-1]),
+        rowcount=_cat_pieces([s._rowcount for s in st], zeros),
+        colptr=_cat_pieces([s._colptr for s in st], nnz_off, True),
+        colcount=_cat_pieces([s._colcount for s in st], zeros),
+        csr2csc=_cat_pieces([s._csr2csc for s in st], nnz_off), csc2csr=_cat_pieces([s._csc2csr for s in st], nnz_off),
+        is_sorted=True)
+    return SparseTensor.from_storage(storage)
+
+
 # =========================================================================== index_select.py
 def index_select(src: SparseTensor, dim: int, idx: np.ndarray) -> SparseTensor:
     """index_select.py:13-96."""

@@ -30,6 +30,31 @@ coo_match_kernel(const int64_t *__restrict__ row, const int64_t *__restrict__ co
   out_mask[e] = found >= 0 ? 1 : 0;
 }
 
+// cat.py:49-276 stitches row / rowptr / col / colptr / csr2csc / csc2csr of several matrices by
+// `concat([x_k + delta_k])` (one elementwise add per piece, then a concat).  Here one launch writes the whole
+// output: out[start_k + i] = src_k[i] + delta_k for up to CAT_MAX pieces passed by value.
+constexpr int CAT_MAX = 32;
+struct CatPieces {
+  const int64_t *src[CAT_MAX];
+  int64_t start[CAT_MAX + 1];  // start[k] = first output position of piece k, start[n] = total
+  int64_t delta[CAT_MAX];
+  int n;
+};
+
+__global__ void __launch_bounds__(256) concat_add_kernel(CatPieces p, int64_t *__restrict__ out) {
+  const int64_t total = p.start[p.n];
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+    int lo = 0, hi = p.n - 1;  // last piece with start <= i (empty pieces share a start: the last one wins)
+    while (lo < hi) {
+      const int mid = (lo + hi + 1) >> 1;
+      if (p.start[mid] <= i) lo = mid;
+      else hi = mid - 1;
+    }
+    out[i] = ld_stream(p.src[lo] + (i - p.start[lo])) + p.delta[lo];
+  }
+}
+
 }  // namespace ps
 
 using namespace ps;
@@ -43,6 +68,47 @@ int ps_coo_match(const int64_t *row, const int64_t *col, int64_t n, const int64_
   coo_match_kernel<<<(unsigned)ceil_div(n, 256), 256, 0, (cudaStream_t)stream>>>(row, col, n, rowptr_b, col_b, M_b,
                                                                                   out_pos, out_mask);
   PS_LAUNCH_OK();
+  return PS_OK;
+}
+
+int ps_concat_add_i64(const int64_t *const *srcs, const int64_t *lens, const int64_t *deltas, int64_t K,
+                      int64_t *out, void *stream) {
+  PS_CHECK(K >= 0, "concat_add: negative piece count");
+  cudaStream_t s = (cudaStream_t)stream;
+  int64_t done = 0;
+  for (int64_t k0 = 0; k0 < K; k0 += CAT_MAX) {
+    CatPieces p;
+    p.n = (int)((K - k0) < CAT_MAX ? (K - k0) : CAT_MAX);
+    int64_t at = 0;
+    for (int j = 0; j < p.n; ++j) {
+      PS_CHECK(lens[k0 + j] >= 0, "concat_add: negative length");
+      p.src[j] = srcs[k0 + j];
+      p.start[j] = at;
+      p.delta[j] = deltas[k0 + j];
+      at += lens[k0 + j];
+    }
+    p.start[p.n] = at;
+    if (at > 0) {
+      int64_t blocks = ceil_div(at, 256 * 4);
+      const int64_t cap = 16 * (int64_t)sm_count();
+      if (blocks > cap) blocks = cap;
+      concat_add_kernel<<<(unsigned)blocks, 256, 0, s>>>(p, out + done);
+      PS_LAUNCH_OK();
+    }
+    done += at;
+  }
+  return PS_OK;
+}
+
+int ps_concat_bytes(const void *const *srcs, const int64_t *nbytes, int64_t K, void *out, void *stream) {
+  PS_CHECK(K >= 0, "concat_bytes: negative piece count");
+  cudaStream_t s = (cudaStream_t)stream;
+  char *dst = reinterpret_cast<char *>(out);
+  for (int64_t k = 0; k < K; ++k) {
+    PS_CHECK(nbytes[k] >= 0, "concat_bytes: negative length");
+    if (nbytes[k] > 0) PS_CUDA(cudaMemcpyAsync(dst, srcs[k], (size_t)nbytes[k], cudaMemcpyDeviceToDevice, s));
+    dst += nbytes[k];
+  }
   return PS_OK;
 }
 

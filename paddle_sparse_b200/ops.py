@@ -418,6 +418,39 @@ def coo_match(row, col, rowptr_b, col_b):
     return pos, mask
 
 
+# ------------------------------------------------------------------ cat (cat.py:49-276)
+def concat_add(pieces, deltas, skip_first=None) -> torch.Tensor:
+    """concat_k(pieces[k][skip_k:] + deltas[k]) in one launch (per 32 pieces); int64, 1-D."""
+    pieces = [_idx(t, "piece") for t in pieces]
+    K = len(pieces)
+    skip = [0] * K if skip_first is None else [int(bool(x)) for x in skip_first]
+    lens = [max(t.numel() - sk, 0) for t, sk in zip(pieces, skip)]
+    out = _new(pieces[0], sum(lens))
+    srcs = (ctypes.c_void_p * K)(*[t.data_ptr() + 8 * sk for t, sk in zip(pieces, skip)])
+    c_lens = (ctypes.c_int64 * K)(*lens)
+    c_deltas = (ctypes.c_int64 * K)(*[int(d) for d in deltas])
+    with torch.cuda.device(out.device):
+        _lib.call("ps_concat_add_i64", srcs, c_lens, c_deltas, K, _p(out), _stream(out))
+    return out
+
+
+def concat_rows(pieces) -> torch.Tensor:
+    """Concatenation along dim 0 of same-dtype tensors with equal trailing shape (the value concat of cat.py)."""
+    pieces = [_dev(t, "piece") for t in pieces]
+    first = pieces[0]
+    for t in pieces:
+        if t.dtype != first.dtype or t.shape[1:] != first.shape[1:]:
+            raise ValueError("concat_rows: dtypes / trailing shapes differ")
+    K = len(pieces)
+    out = torch.empty((sum(t.shape[0] for t in pieces),) + tuple(first.shape[1:]), dtype=first.dtype,
+                      device=first.device)
+    srcs = (ctypes.c_void_p * K)(*[t.data_ptr() for t in pieces])
+    nbytes = (ctypes.c_int64 * K)(*[t.numel() * t.element_size() for t in pieces])
+    with torch.cuda.device(out.device):
+        _lib.call("ps_concat_bytes", srcs, nbytes, K, _p(out), _stream(out))
+    return out
+
+
 # ------------------------------------------------------------------ select building blocks
 def _mask_u8(mask: torch.Tensor) -> torch.Tensor:
     mask = _dev(mask, "mask")

@@ -66,3 +66,10 @@ SPARSE_MUL_EMPTY = dict(rowA=[0], colA=[1], valueA=[1], rowB=[1], colB=[0], valu
 # test/test_tensor.py:71-88
 TO_SYMMETRIC = dict(row=[0, 0, 0, 1, 1], col=[0, 1, 2, 0, 2], value=[1, 2, 3, 4, 5],
                     dense=[[2, 6, 3], [6, 0, 5], [3, 5, 0]])
+
+# test/test_cat.py:11-66 (value-less operands with filled caches; dense view and which structures survive)
+CAT = dict(row1=[0, 0, 1], col1=[0, 1, 2], row2=[0, 0, 1, 2], col2=[0, 1, 1, 0],
+           dim0=[[1, 1, 0], [0, 0, 1], [1, 1, 0], [0, 1, 0], [1, 0, 0]], dim0_cached=1,
+           dim1=[[1, 1, 0, 1, 1], [0, 0, 1, 0, 1], [0, 0, 0, 1, 0]], dim1_cached=2,
+           diag=[[1, 1, 0, 0, 0], [0, 0, 1, 0, 0], [0, 0, 0, 1, 1], [0, 0, 0, 0, 1], [0, 0, 0, 1, 0]],
+           diag_cached=5, value_width=4, value_cat_width=8, value_cat_cached=5)

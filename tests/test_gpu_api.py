@@ -360,6 +360,77 @@ def test_add_broadcast(ps, dtype):
     np.testing.assert_allclose(got.double().cpu().numpy(), want.cpu().numpy(), rtol=8e-3)
 
 
+# ----------------------------------------------------------------------------- cat
+def test_cat_golden(ps):
+    """test/test_cat.py:11-66."""
+    g = G.CAT
+    m1 = ps.SparseTensor(row=dev(np.array(g["row1"], I64)), col=dev(np.array(g["col1"], I64))).fill_cache_()
+    m2 = ps.SparseTensor(row=dev(np.array(g["row2"], I64)), col=dev(np.array(g["col2"], I64))).fill_cache_()
+    out = ps.cat([m1, m2], dim=0)
+    assert out.to_dense().tolist() == g["dim0"]
+    assert out.storage.has_row() and out.storage.has_rowptr() and out.storage.has_rowcount()
+    assert out.storage.num_cached_keys() == g["dim0_cached"]
+    out = ps.cat([m1, m2], dim=1)
+    assert out.to_dense().tolist() == g["dim1"]
+    assert out.storage.has_row() and not out.storage.has_rowptr()
+    assert out.storage.num_cached_keys() == g["dim1_cached"]
+    out = ps.cat([m1, m2], dim=(0, 1))
+    assert out.to_dense().tolist() == g["diag"]
+    assert out.storage.has_row() and out.storage.has_rowptr()
+    assert out.storage.num_cached_keys() == g["diag_cached"]
+    m1 = m1.set_value_(torch.randn((m1.nnz(), g["value_width"]), device="cuda"), layout="coo")
+    out = ps.cat([m1, m1], dim=-1)
+    assert list(out.storage.value().shape) == [m1.nnz(), g["value_cat_width"]]
+    assert out.storage.has_row() and out.storage.has_rowptr()
+    assert out.storage.num_cached_keys() == g["value_cat_cached"]
+    with pytest.raises(IndexError):
+        ps.cat([m1, m1], dim=3)
+
+
+@pytest.mark.parametrize("dim", [0, 1, (0, 1)])
+@pytest.mark.parametrize("cached", ["all", "first-only", "none"])
+@pytest.mark.parametrize("with_value", [True, False])
+def test_cat_matches_oracle(ps, dim, cached, with_value):
+    """Indices, values and every stitched structure against the oracle, for 3 operands (40 when dim=0: more than one
+    launch of the concat kernel), one of them empty; a structure survives only if every operand carries it."""
+    rng = np.random.default_rng(43)
+    shapes = [(300, 200, 5000), (50, 400, 0), (700, 100, 9000)]
+    if dim == 0 and cached == "all":
+        shapes = shapes + [(int(rng.integers(1, 40)), int(rng.integers(1, 90)), int(rng.integers(0, 300)))
+                           for _ in range(37)]
+    gs, os_ = [], []
+    for k, (M, N, nnz) in enumerate(shapes):
+        row, col, val = _pair(rng, M, N, max(nnz, 1), width=2)
+        if nnz == 0:
+            row, col, val = row[:0], col[:0], val[:0]
+        A = ps.SparseTensor(row=dev(row), col=dev(col), value=dev(val) if with_value else None, sparse_sizes=(M, N))
+        O = np_ref.SparseTensor(row=row, col=col, value=val if with_value else None, sparse_sizes=(M, N))
+        if cached == "all" or (cached == "first-only" and k == 0):
+            A.fill_cache_()
+            O.fill_cache_()
+        gs.append(A)
+        os_.append(O)
+    got, want = ps.cat(gs, dim), np_ref.cat(os_, dim)
+    assert tuple(got.sparse_sizes()) == tuple(want.sparse_sizes())
+    assert sorted(got.storage.cached_keys()) == sorted(want.storage.cached_keys())
+    assert got.storage.has_rowptr() == (want.storage._rowptr is not None)
+    for g_, w_ in zip(got.coo(), want.coo()):
+        assert (g_ is None) == (w_ is None)
+        if g_ is not None:
+            assert np.array_equal(host(g_), w_)
+    for key in ("_rowptr", "_rowcount", "_colptr", "_colcount", "_csr2csc", "_csc2csr"):
+        w_ = getattr(want.storage, key)
+        g_ = getattr(got.storage, key)
+        assert (g_ is None) == (w_ is None), key
+        if w_ is not None:
+            assert np.array_equal(host(g_), w_), key
+    # the stitched structures are the ones a fresh build would compute
+    fresh = np_ref.SparseTensor(row=want.coo()[0], col=want.coo()[1], sparse_sizes=want.sparse_sizes()).fill_cache_()
+    assert np.array_equal(host(got.storage.rowptr()), fresh.storage.rowptr())
+    assert np.array_equal(host(got.storage.colptr()), fresh.storage.colptr())
+    assert np.array_equal(host(got.storage.csr2csc()), fresh.storage.csr2csc())
+
+
 # ----------------------------------------------------------------------------- index_select / masked_select
 def test_permute_golden(ps):
     g = G.PERMUTE

@@ -222,6 +222,30 @@ def test_dense_add_matches_dense_arithmetic():
     assert np.allclose(v, A.to_dense()[r, c] + ocol[0, c])
 
 
+def test_cat_golden():
+    """test/test_cat.py:11-66: dense views and which structures survive each kind of concatenation."""
+    g = G.CAT
+    m1 = np_ref.SparseTensor(row=a(g["row1"]), col=a(g["col1"])).fill_cache_()
+    m2 = np_ref.SparseTensor(row=a(g["row2"]), col=a(g["col2"])).fill_cache_()
+    out = np_ref.cat([m1, m2], 0)
+    assert out.to_dense().tolist() == g["dim0"]
+    assert out.storage._row is not None and out.storage._rowptr is not None and out.storage._rowcount is not None
+    assert out.storage.num_cached_keys() == g["dim0_cached"]
+    out = np_ref.cat([m1, m2], 1)
+    assert out.to_dense().tolist() == g["dim1"]
+    assert out.storage._row is not None and out.storage._rowptr is None
+    assert out.storage.num_cached_keys() == g["dim1_cached"]
+    out = np_ref.cat([m1, m2], (0, 1))
+    assert out.to_dense().tolist() == g["diag"]
+    assert out.storage._row is not None and out.storage._rowptr is not None
+    assert out.storage.num_cached_keys() == g["diag_cached"]
+    m1 = m1.set_value_(np.random.default_rng(0).random((3, g["value_width"])), layout="coo")
+    out = np_ref.cat([m1, m1], -1)
+    assert out.storage.value().shape == (3, g["value_cat_width"])
+    assert out.storage._row is not None and out.storage._rowptr is not None
+    assert out.storage.num_cached_keys() == g["value_cat_cached"]
+
+
 def test_paddle_scatter_restatement():
     src = a([1, 2, 3, 4, 5, 6], np.float32)
     ptr = a([0, 2, 2, 5, 6])
