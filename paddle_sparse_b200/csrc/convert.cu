@@ -122,14 +122,32 @@ template int ind2ptr_launch<uint32_t>(const uint32_t *, int64_t, int64_t, int64_
 // ============================================================================= ptr2ind
 template <int THREADS, int ITEMS>
 __global__ void __launch_bounds__(THREADS)
-ptr2ind_kernel(const int64_t *__restrict__ ptr, int64_t M, int64_t E, int64_t *__restrict__ out) {
+ptr2ind_kernel(const int64_t *__restrict__ ptr, int64_t M, int64_t E, int64_t *__restrict__ out,
+               const int32_t *__restrict__ bounds) {
   constexpr int TILE = THREADS * ITEMS;
   __shared__ int32_t seg[TILE];
   __shared__ int32_t aux[40];
   const int64_t e0 = (int64_t)blockIdx.x * TILE;
   const int tile_n = (int)((E - e0) < TILE ? (E - e0) : TILE);
-  expand_tile<THREADS, ITEMS>(ptr, M, e0, tile_n, seg, aux);
+  expand_tile<THREADS, ITEMS>(ptr, M, e0, tile_n, seg, aux, bounds);
   for (int j = threadIdx.x; j < tile_n; j += THREADS) out[e0 + j] = (int64_t)seg[j];
+}
+
+__global__ void __launch_bounds__(256)
+tile_bounds_kernel(const int64_t *__restrict__ ptr, int64_t S, int64_t tile, int64_t tiles,
+                   int32_t *__restrict__ bounds) {
+  const int64_t t = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (t > tiles) return;  // warp-uniform
+  int64_t c = S;
+  if (t < tiles) c = warp_upper_bound(ptr, S, t * tile);
+  if (lane_id() == 0) bounds[t] = (int32_t)(c > 0 ? c - 1 : 0);
+}
+
+int tile_bounds_launch(const int64_t *ptr, int64_t S, int64_t E, int tile, int32_t *bounds, cudaStream_t s) {
+  const int64_t tiles = ceil_div(E, tile);
+  tile_bounds_kernel<<<(unsigned)ceil_div((tiles + 1) * 32, 256), 256, 0, s>>>(ptr, S, tile, tiles, bounds);
+  PS_LAUNCH_OK();
+  return PS_OK;
 }
 
 // ============================================================================= small utilities
@@ -263,9 +281,12 @@ int ps_ptr2ind(const int64_t *ptr, int64_t M, int64_t E, int64_t *out_ind, void 
   PS_CHECK(M > 0, "ptr2ind: E > 0 with no rows");
   constexpr int THREADS = 256, ITEMS = 8;
   const int64_t tiles = ceil_div(E, THREADS * ITEMS);
+  Scratch scratch((cudaStream_t)stream);
+  PS_SCRATCH(bounds, scratch, int32_t, tiles + 1);
   {
     ProfScope prof(PROF_PTR2IND, (cudaStream_t)stream);
-    ptr2ind_kernel<THREADS, ITEMS><<<(unsigned)tiles, THREADS, 0, (cudaStream_t)stream>>>(ptr, M, E, out_ind);
+    if (int rc = tile_bounds_launch(ptr, M, E, THREADS * ITEMS, bounds, (cudaStream_t)stream)) return rc;
+    ptr2ind_kernel<THREADS, ITEMS><<<(unsigned)tiles, THREADS, 0, (cudaStream_t)stream>>>(ptr, M, E, out_ind, bounds);
   }
   PS_LAUNCH_OK();
   return PS_OK;

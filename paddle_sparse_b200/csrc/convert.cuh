@@ -32,13 +32,19 @@ __device__ __forceinline__ int64_t warp_upper_bound(const int64_t *__restrict__ 
 // Tile geometry shared by ptr2ind and the CSR-expanding kernels (gather_csr, mul_row,
 // index_select_fill): a block resolves, for a tile of TILE consecutive output entries,
 // the segment id of every entry into shared memory (int32).
+// `bounds` (optional, from tile_bounds_launch): bounds[t] = first segment touching tile t, bounds[tiles] = S - 1.
+// With it a tile starts from two loads instead of two 32-ary searches of ~5 dependent loads each, which is what
+// bounds these kernels when the whole grid is resident in a few waves (the searches serialise per tile).
 template <int THREADS, int ITEMS>
 __device__ __forceinline__ void expand_tile(const int64_t *__restrict__ ptr, int64_t S, int64_t e0,
-                                            int tile_n, int32_t *seg /*[TILE]*/, int32_t *aux /*[40]*/) {
+                                            int tile_n, int32_t *seg /*[TILE]*/, int32_t *aux /*[40]*/,
+                                            const int32_t *__restrict__ bounds = nullptr) {
   constexpr int TILE = THREADS * ITEMS;
   const unsigned lane = lane_id(), warp = threadIdx.x >> 5;
   // first / last segment touching the tile: largest s in [0,S-1] with ptr[s] <= e
-  if (warp == 0) {
+  if (bounds) {
+    if (threadIdx.x < 2) aux[32 + threadIdx.x] = bounds[e0 / TILE + threadIdx.x];  // s_hi may overshoot: filtered below
+  } else if (warp == 0) {
     const int64_t c = warp_upper_bound(ptr, S, e0);
     if (lane == 0) aux[32] = (int32_t)(c > 0 ? c - 1 : 0);
   } else if (warp == 1) {
@@ -82,6 +88,9 @@ __device__ __forceinline__ void expand_tile(const int64_t *__restrict__ ptr, int
   for (int k = 0; k < ITEMS; ++k) seg[threadIdx.x * ITEMS + k] = loc[k] > carry ? loc[k] : carry;
   __syncthreads();
 }
+
+// bounds[t] = largest s in [0, S-1] with ptr[s] <= t * tile (t < tiles), bounds[tiles] = S - 1; one warp per tile
+int tile_bounds_launch(const int64_t *ptr, int64_t S, int64_t E, int tile, int32_t *bounds, cudaStream_t s);
 
 // ind2ptr on int64 or packed uint32 keys (the latter is used on the sorted col keys of csr2csc)
 template <typename IndT>

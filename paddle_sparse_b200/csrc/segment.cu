@@ -137,13 +137,13 @@ template int gather_rows_launch<uint32_t>(const void *, int64_t, const uint32_t 
 template <typename U, int THREADS, int ITEMS>
 __global__ void __launch_bounds__(THREADS)
 gather_csr_kernel(const U *__restrict__ src, int64_t upr, const int64_t *__restrict__ ptr, int64_t S, int64_t E,
-                  U *__restrict__ out) {
+                  U *__restrict__ out, const int32_t *__restrict__ bounds) {
   constexpr int TILE = THREADS * ITEMS;
   __shared__ int32_t seg[TILE];
   __shared__ int32_t aux[40];
   const int64_t e0 = (int64_t)blockIdx.x * TILE;
   const int tile_n = (int)((E - e0) < TILE ? (E - e0) : TILE);
-  expand_tile<THREADS, ITEMS>(ptr, S, e0, tile_n, seg, aux);
+  expand_tile<THREADS, ITEMS>(ptr, S, e0, tile_n, seg, aux, bounds);
   const int64_t units = (int64_t)tile_n * upr;
   for (int64_t q = threadIdx.x; q < units; q += THREADS) {
     const int64_t j = q / upr, u = q - j * upr;
@@ -162,13 +162,13 @@ __device__ __forceinline__ T bc_values(T a, T b) {
 template <typename T, int OP, int THREADS, int ITEMS>
 __global__ void __launch_bounds__(THREADS)
 mul_row_kernel(const T *value, int64_t width, const int64_t *__restrict__ rowptr, int64_t M, int64_t nnz,
-               const T *__restrict__ other, T *out) {
+               const T *__restrict__ other, T *out, const int32_t *__restrict__ bounds) {
   constexpr int TILE = THREADS * ITEMS;
   __shared__ int32_t seg[TILE];
   __shared__ int32_t aux[40];
   const int64_t e0 = (int64_t)blockIdx.x * TILE;
   const int tile_n = (int)((nnz - e0) < TILE ? (nnz - e0) : TILE);
-  expand_tile<THREADS, ITEMS>(rowptr, M, e0, tile_n, seg, aux);
+  expand_tile<THREADS, ITEMS>(rowptr, M, e0, tile_n, seg, aux, bounds);
   const int64_t units = (int64_t)tile_n * width;
   for (int64_t q = threadIdx.x; q < units; q += THREADS) {
     const int64_t j = q / width, f = q - j * width;
@@ -181,7 +181,7 @@ mul_row_kernel(const T *value, int64_t width, const int64_t *__restrict__ rowptr
 template <typename T, int OP, int THREADS, int ITEMS>
 __global__ void __launch_bounds__(THREADS)
 mul_row_w1_kernel(const T *value, const int64_t *__restrict__ rowptr, int64_t M, int64_t nnz,
-                  const T *__restrict__ other, T *out) {
+                  const T *__restrict__ other, T *out, const int32_t *__restrict__ bounds) {
   constexpr int TILE = THREADS * ITEMS;
   __shared__ int32_t seg[TILE];
   __shared__ int32_t aux[40];
@@ -193,7 +193,7 @@ mul_row_w1_kernel(const T *value, const int64_t *__restrict__ rowptr, int64_t M,
     const int j = k * THREADS + threadIdx.x;
     if (j < tile_n) v[k] = value[e0 + j];
   }
-  expand_tile<THREADS, ITEMS>(rowptr, M, e0, tile_n, seg, aux);
+  expand_tile<THREADS, ITEMS>(rowptr, M, e0, tile_n, seg, aux, bounds);
 #pragma unroll
   for (int k = 0; k < ITEMS; ++k) {
     const int j = k * THREADS + threadIdx.x;
@@ -404,16 +404,19 @@ static int bc_row(const void *value, int dtype, int64_t width, const int64_t *ro
   if (nnz == 0) return PS_OK;
   constexpr int THREADS = 256, ITEMS = 8;
   const unsigned blocks = (unsigned)ceil_div(nnz, THREADS * ITEMS);
+  Scratch scratch(s);
+  PS_SCRATCH(bounds, scratch, int32_t, (int64_t)blocks + 1);
+  if (int rc = tile_bounds_launch(rowptr, M, nnz, THREADS * ITEMS, bounds, s)) return rc;
   if (width == 1) {
     PS_DISPATCH_DTYPE(dtype, T,
                       (mul_row_w1_kernel<T, OP, THREADS, ITEMS><<<blocks, THREADS, 0, s>>>(
                           reinterpret_cast<const T *>(value), rowptr, M, nnz, reinterpret_cast<const T *>(other),
-                          reinterpret_cast<T *>(out))));
+                          reinterpret_cast<T *>(out), bounds)));
   } else {
     PS_DISPATCH_DTYPE(dtype, T,
                       (mul_row_kernel<T, OP, THREADS, ITEMS><<<blocks, THREADS, 0, s>>>(
                           reinterpret_cast<const T *>(value), width, rowptr, M, nnz,
-                          reinterpret_cast<const T *>(other), reinterpret_cast<T *>(out))));
+                          reinterpret_cast<const T *>(other), reinterpret_cast<T *>(out), bounds)));
   }
   PS_LAUNCH_OK();
   return PS_OK;
@@ -486,7 +489,11 @@ int ps_gather_csr(const void *src, int64_t row_bytes, const int64_t *ptr, int64_
   const int unit = copy_unit(row_bytes, src, out);
   const int64_t upr = row_bytes / unit;
   cudaStream_t s = (cudaStream_t)stream;
-#define PS_G(U) gather_csr_kernel<U, THREADS, ITEMS><<<blocks, THREADS, 0, s>>>((const U *)src, upr, ptr, S, E, (U *)out)
+  Scratch scratch(s);
+  PS_SCRATCH(bounds, scratch, int32_t, (int64_t)blocks + 1);
+  if (int rc = tile_bounds_launch(ptr, S, E, THREADS * ITEMS, bounds, s)) return rc;
+#define PS_G(U) \
+  gather_csr_kernel<U, THREADS, ITEMS><<<blocks, THREADS, 0, s>>>((const U *)src, upr, ptr, S, E, (U *)out, bounds)
   switch (unit) {
     case 16: PS_G(uint4); break;
     case 8: PS_G(uint64_t); break;
