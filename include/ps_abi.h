@@ -138,9 +138,11 @@ int ps_segment_reduce(const void *src, int dtype, int64_t width, int64_t E, cons
 int ps_gather_csr(const void *src, int64_t row_bytes, const int64_t *ptr, int64_t S, int64_t E,
                   void *out, void *stream);
 /* paddle_scatter.scatter(src, index, 0, None, dim_size, reduce): reduce.py:42.
- * src [n, width], out [dim_size, width]; untouched rows -> 0. */
+ * src [n, width], out [dim_size, width]; untouched rows -> 0.
+ * count (nullable): count[i] = number of entries with index == i when the caller already holds it
+ * (the cached colcount of storage.py:405-420); mean / min / max then skip their counting atomics. */
 int ps_scatter_reduce(const void *src, int dtype, int64_t width, const int64_t *index, int64_t n,
-                      int64_t dim_size, int reduce, void *out, void *stream);
+                      int64_t dim_size, int reduce, void *out, const int64_t *count, void *stream);
 /* reduce.py:17-27 dim=None: out[1] = reduce over all n elements of src. */
 int ps_reduce_all(const void *src, int dtype, int64_t n, int reduce, void *out, void *stream);
 

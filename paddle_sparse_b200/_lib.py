@@ -46,7 +46,7 @@ SIGNATURES = {
     "ps_transpose_gather": [c_ptr, c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_ptr, c_i64, c_ptr, c_ptr, c_ptr, c_ptr],
     "ps_segment_reduce": [c_ptr, c_int, c_i64, c_i64, c_ptr, c_i64, c_int, c_ptr, c_ptr],
     "ps_gather_csr": [c_ptr, c_i64, c_ptr, c_i64, c_i64, c_ptr, c_ptr],
-    "ps_scatter_reduce": [c_ptr, c_int, c_i64, c_ptr, c_i64, c_i64, c_int, c_ptr, c_ptr],
+    "ps_scatter_reduce": [c_ptr, c_int, c_i64, c_ptr, c_i64, c_i64, c_int, c_ptr, c_ptr, c_ptr],
     "ps_reduce_all": [c_ptr, c_int, c_i64, c_int, c_ptr, c_ptr],
     "ps_mul_row": [c_ptr, c_int, c_i64, c_ptr, c_i64, c_i64, c_ptr, c_ptr, c_ptr],
     "ps_mul_col": [c_ptr, c_int, c_i64, c_ptr, c_i64, c_ptr, c_ptr, c_ptr],

@@ -286,23 +286,23 @@ scatter_reduce_kernel(const T *__restrict__ src, int64_t width, const int64_t *_
   if (RED == PS_SUM || RED == PS_MEAN) atomic_red_add<A>(&acc[r * width + f], v);
   else if (RED == PS_MIN) atomic_red_min(&acc[r * width + f], v);
   else atomic_red_max(&acc[r * width + f], v);
-  if (RED != PS_SUM && f == 0) atomicAdd(&cnt[r], 1);
+  if (RED != PS_SUM && cnt != nullptr && f == 0) atomicAdd(&cnt[r], 1);
 }
 
 template <typename T, int RED>
 __global__ void __launch_bounds__(256)
-scatter_finish_kernel(const typename Acc<T>::type *__restrict__ acc, const int *__restrict__ cnt, int64_t width,
-                      int64_t n_units, T *__restrict__ out) {
+scatter_finish_kernel(const typename Acc<T>::type *__restrict__ acc, const int *__restrict__ cnt,
+                      const int64_t *__restrict__ count64, int64_t width, int64_t n_units, T *__restrict__ out) {
   using A = typename Acc<T>::type;
   const int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (q >= n_units) return;
-  const int64_t c = RED == PS_SUM ? 1 : (int64_t)cnt[q / width];
+  const int64_t c = RED == PS_SUM ? 1 : (count64 ? count64[q / width] : (int64_t)cnt[q / width]);
   out[q] = from_acc<T>(Red<RED, A>::finish_floor(acc[q], c));
 }
 
 template <typename T, int RED>
 static int scatter_reduce_typed(const T *src, int64_t width, const int64_t *index, int64_t n, int64_t dim_size, T *out,
-                                cudaStream_t s) {
+                                const int64_t *count64, cudaStream_t s) {
   using A = typename Acc<T>::type;
   const int64_t out_units = dim_size * width;
   if (out_units == 0) return PS_OK;
@@ -314,7 +314,7 @@ static int scatter_reduce_typed(const T *src, int64_t width, const int64_t *inde
     acc = tmp;
   }
   int *cnt = nullptr;
-  if (RED != PS_SUM) {
+  if (RED != PS_SUM && count64 == nullptr) {  // a caller that knows the per-output counts saves one atomic per entry
     PS_SCRATCH(c, scratch, int, dim_size);
     PS_CUDA(cudaMemsetAsync(c, 0, sizeof(int) * (size_t)dim_size, s));
     cnt = c;
@@ -329,7 +329,8 @@ static int scatter_reduce_typed(const T *src, int64_t width, const int64_t *inde
     PS_LAUNCH_OK();
   }
   if (RED != PS_SUM || !same) {
-    scatter_finish_kernel<T, RED><<<(unsigned)ceil_div(out_units, 256), 256, 0, s>>>(acc, cnt, width, out_units, out);
+    scatter_finish_kernel<T, RED><<<(unsigned)ceil_div(out_units, 256), 256, 0, s>>>(acc, cnt, count64, width, out_units,
+                                                                                      out);
     PS_LAUNCH_OK();
   }
   return PS_OK;
@@ -507,14 +508,14 @@ int ps_gather_csr(const void *src, int64_t row_bytes, const int64_t *ptr, int64_
 }
 
 int ps_scatter_reduce(const void *src, int dtype, int64_t width, const int64_t *index, int64_t n, int64_t dim_size,
-                      int reduce, void *out, void *stream) {
+                      int reduce, void *out, const int64_t *count, void *stream) {
   PS_CHECK(n >= 0 && dim_size >= 0 && width >= 1, "scatter_reduce: bad sizes");
   cudaStream_t s = (cudaStream_t)stream;
   PS_DISPATCH_DTYPE(dtype, T,
                     PS_DISPATCH_REDUCE(reduce, RED,
                                        return (scatter_reduce_typed<T, RED>(reinterpret_cast<const T *>(src), width,
                                                                             index, n, dim_size,
-                                                                            reinterpret_cast<T *>(out), s))));
+                                                                            reinterpret_cast<T *>(out), count, s))));
   return PS_OK;
 }
 

@@ -334,14 +334,17 @@ def gather_csr(src: torch.Tensor, indptr: torch.Tensor, E: Optional[int] = None)
 
 
 def scatter(src: torch.Tensor, index: torch.Tensor, dim: int = 0, out=None, dim_size: Optional[int] = None,
-            reduce: str = "sum") -> torch.Tensor:
-    """paddle_scatter.scatter(src, index, 0, None, dim_size, reduce) (reduce.py:42)."""
+            reduce: str = "sum", count: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """paddle_scatter.scatter(src, index, 0, None, dim_size, reduce) (reduce.py:42).  `count` (optional): the
+    histogram of `index` when the caller holds it (a cached colcount) - saves one atomic per entry."""
     assert dim == 0 and out is None and dim_size is not None
     src, index = _dev(src, "src"), _idx(index, "index")
+    count = None if count is None else _idx(count, "count")
+    assert count is None or count.numel() == dim_size
     res = torch.empty((dim_size,) + tuple(src.shape[1:]), dtype=src.dtype, device=src.device)
     with torch.cuda.device(src.device):
         _lib.call("ps_scatter_reduce", _p(src), dtype_code(src), max(_width(src), 1), _p(index), index.numel(),
-                  dim_size, reduce_code(reduce), _p(res), _stream(src))
+                  dim_size, reduce_code(reduce), _p(res), _p(count), _stream(src))
     return res
 
 

@@ -30,7 +30,12 @@ def reduction(src: SparseTensor, dim: Optional[int] = None, reduce: str = "sum")
 
     if dim == 0:  # reduce.py:40-47
         if value is not None:
-            return ops.scatter(value, src.storage.col(), 0, None, src.size(1), reduce)
+            parked = src.storage.csc_ordered_value()
+            if parked is not None and src.storage.has_colptr():
+                # fill_cache_ left value[csr2csc] behind: columns are contiguous runs there, no atomics needed
+                return ops.segment_csr(parked, src.storage.colptr(), None, reduce)
+            count = src.storage._colcount if reduce != "sum" else None  # cached histogram of col, if any
+            return ops.scatter(value, src.storage.col(), 0, None, src.size(1), reduce, count)
         if reduce == "sum":
             return src.storage.colcount().to(src.dtype())
         return torch.ones(src.size(1), dtype=src.dtype(), device=src.device())

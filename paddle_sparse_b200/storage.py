@@ -205,6 +205,9 @@ class SparseStorage(object):
 
     def set_value_(self, value, layout: Optional[str] = None):
         self._value = self._prepare_value(value, layout)
+        parts = getattr(self, "_t_parts", None)
+        if parts is not None:  # the parked value[csr2csc] is stale, also when `value` is the same tensor rewritten in place
+            self._t_parts = parts[:3] + (None, -1)
         return self
 
     def set_value(self, value, layout: Optional[str] = None):
@@ -291,7 +294,8 @@ class SparseStorage(object):
         builds colcount and csc2csr and promotes all CSC caches (fill_cache_, storage.py:488-496)."""
         r = ops.csc_build(self.row(), self._col, self._value, self._sparse_sizes[1], everything, everything)
         self._csr2csc = r["csr2csc"]
-        self._t_parts = (r["t_row"], r["t_col"], r["t_value"], self._value)
+        self._t_parts = (r["t_row"], r["t_col"], r["t_value"], self._value,
+                         -1 if self._value is None else self._value._version)
         if everything:
             if self._colptr is None:
                 self._colptr = r["colptr"]
@@ -301,6 +305,22 @@ class SparseStorage(object):
         elif self._colptr is None:
             self._colptr_spare = r["colptr"]
 
+    def _parked_value_valid(self, parts) -> bool:
+        """The parked value[csr2csc] still describes `_value`: same tensor object and no in-place edit since
+        (torch's version counter; edits through this package's kernels go through set_value_, which unparks)."""
+        value_then, version_then = parts[3], parts[4]
+        if self._value is None:
+            return value_then is None and parts[2] is None
+        return value_then is self._value and version_then == self._value._version
+
+    def csc_ordered_value(self) -> Optional[torch.Tensor]:
+        """value[csr2csc] when the carrying CSC sort left it behind and it is still current, else None (never
+        computes anything): lets a column reduction run as a segment reduction over colptr."""
+        parts = getattr(self, "_t_parts", None)
+        if parts is None or parts[2] is None or self._value is None or not self._parked_value_valid(parts):
+            return None
+        return parts[2]
+
     def take_transposed_parts(self):
         """(col[csr2csc], row[csr2csc], value[csr2csc]) for transpose.py:9-33, building csr2csc if needed.
         Uses the by-products of the carrying sort when they are there, else one fused gather."""
@@ -308,8 +328,8 @@ class SparseStorage(object):
             self._build_csc_carry(False)
         parts, self._t_parts = getattr(self, "_t_parts", None), None
         if parts is not None:
-            t_row, t_col, t_value, value_then = parts
-            if value_then is not self._value:  # set_value_ since: re-gather the values only
+            t_row, t_col, t_value = parts[:3]
+            if not self._parked_value_valid(parts):  # set_value_ / in-place edit since: re-gather the values only
                 t_value = None if self._value is None else ops.gather_rows(self._value, self._csr2csc)
             return t_row, t_col, t_value
         return ops.transpose_gather(self._csr2csc, self.row(), self._col, self._value, self._colptr,

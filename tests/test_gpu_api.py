@@ -184,6 +184,15 @@ def test_reductions_all_dims(ps, reduce, width):
         np.testing.assert_allclose(host(got), want, rtol=0 if reduce in ("min", "max") else 2e-6)
     # the test_reduce.py:13-62 identity
     np.testing.assert_allclose(float(getattr(A, reduce)()), float(getattr(val.astype(np.float64), reduce)()), rtol=1e-6)
+    # with the CSC caches filled, dim=0 runs over the parked value[csr2csc] (segment reduction over colptr), and
+    # after t() took that away, with the per-column counts from the cached colcount: same answer each time
+    A.fill_cache_()
+    assert A.storage.has_colcount()
+    for parked in (True, False):
+        assert (A.storage.csc_ordered_value() is not None) == parked
+        np.testing.assert_allclose(host(getattr(A, reduce)(0)), np_ref.reduction(O, 0, reduce),
+                                   rtol=0 if reduce in ("min", "max") else 2e-6)
+        A.t()
     V = ps.SparseTensor(row=dev(row), col=dev(col), sparse_sizes=(M, N))  # value-less
     OV = np_ref.SparseTensor(row=row, col=col, sparse_sizes=(M, N))
     for dim in (None, 0, 1):
@@ -221,6 +230,34 @@ def test_mul_broadcast(ps, dtype):
     A = ps.SparseTensor(row=dev(row), col=dev(col), value=tv.clone(), sparse_sizes=(M, N))
     w = dev(rng.random(row.size).astype(np.float32), dtype)
     assert torch.equal(A.mul_nnz(w, layout="coo").storage.value(), tv * w)
+
+
+def test_value_edits_after_fill_cache_reach_t_and_column_sums(ps):
+    """fill_cache_ parks value[csr2csc] for t(); an in-place multiply (same tensor object), an in-place torch edit of
+    storage.value() and set_value_ must each invalidate it."""
+    rng = np.random.default_rng(53)
+    M, N = 200, 300
+    row, col, val = _pair(rng, M, N, 8000)
+    other = rng.random((M, 1)).astype(np.float32)
+
+    def fresh():
+        A = ps.SparseTensor(row=dev(row), col=dev(col), value=dev(val), sparse_sizes=(M, N)).fill_cache_()
+        assert A.storage.csc_ordered_value() is not None
+        return A
+    edits = {
+        "mul_": (lambda A: A.mul_(dev(other)), val * other[row, 0]),
+        "torch in-place": (lambda A: A.storage.value().mul_(3.0), val * np.float32(3.0)),
+        "set_value_": (lambda A: A.set_value_(dev(val + 1), layout="coo"), val + 1),
+    }
+    for name, (edit, new_val) in edits.items():
+        O = np_ref.SparseTensor(row=row, col=col, value=new_val.astype(np.float32), sparse_sizes=(M, N))
+        A = fresh()
+        edit(A)
+        np.testing.assert_allclose(host(A.sum(0)), np_ref.reduction(O, 0, "sum"), rtol=2e-6, err_msg=name)
+        A = fresh()
+        edit(A)
+        _, _, tv = A.t().coo()
+        assert np.array_equal(host(tv), np_ref.t(O).coo()[2]), name
 
 
 # ----------------------------------------------------------------------------- add / sparse mul / to_symmetric

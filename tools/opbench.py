@@ -50,6 +50,7 @@ def main():
     st = A.storage
     n = st.col().numel()
     rowptr, colv = st.rowptr(), st.col()
+    colcount = ops.scatter_add_ones(colv, N)
     del row, col, val
     for dt, bv in ((torch.float32, 4), (torch.bfloat16, 2)):
         v = st.value().to(dt)
@@ -65,6 +66,14 @@ def main():
                    8 * (M + 1) + bv * n + bv * M)
             report(f"reduce dim=0 {red}[{tag}] (reduce.py:42 scatter)",
                    timeit(lambda: ops.scatter(v, colv, 0, None, N, red)), (8 + bv) * n + bv * N)
+            if red != "sum":
+                report(f"reduce dim=0 {red}[{tag}] with the cached colcount",
+                       timeit(lambda: ops.scatter(v, colv, 0, None, N, red, colcount)), (8 + bv) * n + (8 + bv) * N)
+    A.fill_cache_()  # parks value[csr2csc]: reduction(dim=0) becomes a segment reduction over colptr
+    for red in ("sum", "mean", "max"):
+        report(f"reduce dim=0 {red}[f32] through the public API after fill_cache_ (parked CSC-ordered values)",
+               timeit(lambda: ps.reduction(A, 0, red)), 8 * (N + 1) + 4 * n + 4 * N)
+    A.clear_cache_()
     report("ptr2ind / row() (csrc/convert.cpp:46-76)", timeit(lambda: ops.ptr2ind(rowptr, n)), 8 * (M + 1) + 8 * n)
     report("ind2ptr / rowptr() (csrc/convert.cpp:13-43)", timeit(lambda: ops.ind2ptr(st.row(), M)), 8 * n + 8 * (M + 1))
     del A, st, rowptr, colv
