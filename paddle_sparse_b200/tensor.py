@@ -5,7 +5,7 @@ paddle_sparse/tensor.py:20-592 for everything that reaches the SparseStorage hot
 (`t`, reductions, `mul`, `index_select`, `masked_select`, `sample_adj` …) are bound onto the
 class by those modules, as the reference does (e.g. reduce.py:90-93, mul.py:122-128).
 Interop converters (paddle.sparse / scipy, tensor.py:110-155, 564-591, 796-856) are host-side
-glue outside the hot path.
+glue bound onto the class by convert.py.
 """
 from __future__ import annotations
 

@@ -73,3 +73,6 @@ CAT = dict(row1=[0, 0, 1], col1=[0, 1, 2], row2=[0, 0, 1, 2], col2=[0, 1, 1, 0],
            dim1=[[1, 1, 0, 1, 1], [0, 0, 1, 0, 1], [0, 0, 0, 1, 0]], dim1_cached=2,
            diag=[[1, 1, 0, 0, 0], [0, 0, 1, 0, 0], [0, 0, 0, 1, 1], [0, 0, 0, 0, 1], [0, 0, 0, 1, 0]],
            diag_cached=5, value_width=4, value_cat_width=8, value_cat_cached=5)
+
+# test/test_convert.py:9-30 (round trips through scipy and the framework's own sparse COO type)
+CONVERT = dict(index=[[0, 0, 1, 2, 2], [0, 2, 1, 0, 1]], value=[1, 2, 4, 1, 3], N=3)

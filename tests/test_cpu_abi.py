@@ -70,3 +70,17 @@ def test_product_never_imports_the_oracle():
                 src = open(os.path.join(dirpath, f)).read()
                 assert not re.search(r"^\s*(from|import)\s+oracle\b", src, flags=re.M), f
                 assert '#include "../../oracle' not in src and "oracle/" not in src.replace("oracle/oracle_port.c", ""), f
+
+
+def test_convert_round_trips_golden():
+    """test/test_convert.py:9-30: the free converters are host-side glue and run without a GPU."""
+    import torch
+    import paddle_sparse_b200 as ps
+    from tests.golden import reference_vectors as G
+    g = G.CONVERT
+    index, value, N = torch.tensor(g["index"]), torch.tensor(g["value"]), g["N"]
+    out = ps.from_scipy(ps.to_scipy(index, value, N, N))
+    assert out[0].tolist() == index.tolist() and out[1].tolist() == value.tolist()
+    out = ps.from_torch_sparse(ps.to_torch_sparse(index, value, N, N).coalesce())
+    assert out[0].tolist() == index.tolist() and out[1].tolist() == value.tolist()
+    assert ps.to_paddle_sparse is ps.to_torch_sparse and ps.from_paddle_sparse is ps.from_torch_sparse

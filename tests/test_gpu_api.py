@@ -397,6 +397,52 @@ def test_add_broadcast(ps, dtype):
     np.testing.assert_allclose(got.double().cpu().numpy(), want.cpu().numpy(), rtol=8e-3)
 
 
+# ----------------------------------------------------------------------------- converters
+@pytest.mark.parametrize("fmt", ["coo", "csr", "csc"])
+@pytest.mark.parametrize("has_value", [True, False])
+def test_scipy_round_trip(ps, fmt, has_value):
+    """tensor.py:796-856: from_scipy keeps rowptr (and colptr for CSC input) and skips the sort; to_scipy in every
+    layout gives back the same matrix."""
+    import scipy.sparse as sp
+    rng = np.random.default_rng(47)
+    M, N = 120, 90
+    row, col, val = _pair(rng, M, N, 2000)
+    mat = getattr(sp.coo_matrix((val, (row, col)), (M, N)), "to" + fmt)()
+    A = ps.SparseTensor.from_scipy(mat, has_value=has_value)
+    assert A.storage.has_rowptr() and A.storage.has_colptr() == (fmt == "csc")
+    assert tuple(A.sparse_sizes()) == (M, N) and A.has_value() == has_value
+    O = np_ref.SparseTensor(row=row, col=col, value=val if has_value else None, sparse_sizes=(M, N))
+    for got, want in zip(A.coo(), O.coo()):
+        assert (got is None) == (want is None)
+        if got is not None:
+            assert np.array_equal(host(got), want)
+    assert np.array_equal(host(A.storage.rowptr()), O.storage.rowptr())
+    assert np.array_equal(host(A.storage.colptr()), O.storage.colptr())
+    ref = mat if has_value else (mat != 0).astype(np.float32)
+    for layout in ("coo", "csr", "csc"):
+        back = A.to_scipy(layout=layout, dtype=torch.float32)
+        assert back.format == layout and back.shape == (M, N)
+        assert (abs(back - ref)).nnz == 0
+
+
+def test_torch_sparse_round_trip(ps):
+    """tensor.py:110-155, 564-591 with torch.sparse standing in for paddle.sparse; test/test_convert.py:22-30."""
+    g = G.CONVERT
+    index, value, N = dev(np.array(g["index"], I64)), dev(np.array(g["value"], np.float32)), g["N"]
+    A = ps.SparseTensor.from_torch_sparse_coo_tensor(torch.sparse_coo_tensor(index, value, (N, N)))
+    assert torch.equal(torch.stack(A.coo()[:2]), index) and torch.equal(A.coo()[2], value)
+    coo = A.to_torch_sparse_coo_tensor()
+    assert torch.equal(coo.to_dense(), A.to_dense())
+    csr = A.to_paddle_sparse_csr_tensor()
+    assert torch.equal(csr.to_dense(), A.to_dense())
+    B = ps.SparseTensor.from_torch_sparse_csr_tensor(csr)
+    assert B.storage.has_rowptr() and torch.equal(B.to_dense(), A.to_dense())
+    V = ps.SparseTensor(row=index[0], col=index[1], sparse_sizes=(N, N))
+    assert torch.equal(V.to_torch_sparse_coo_tensor(torch.float32).to_dense(), (A.to_dense() != 0).float())
+    with pytest.raises(NotImplementedError):
+        A.to_paddle_sparse_csc_tensor()
+
+
 # ----------------------------------------------------------------------------- cat
 def test_cat_golden(ps):
     """test/test_cat.py:11-66."""
