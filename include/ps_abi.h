@@ -91,6 +91,15 @@ int ps_sort_coo(const int64_t *row, const int64_t *col, int64_t nnz, int64_t M, 
 int ps_coalesce_sorted(const int64_t *row, const int64_t *col, int64_t nnz, const void *value,
                        int dtype, int64_t width, int reduce, int64_t *out_row, int64_t *out_col,
                        void *out_value, int64_t *host_nnz_out, void *stream);
+/* storage.py:65-89 (validation maxima) fused with the first read the coalesce needs: ONE pass over
+ * (row, col) yields max(row), max(col) and - when the hybrid plan applies to (nnz, M, N) - the bucket
+ * histogram, offsets and pass bases, left in `state` (device, ps_coo_inspect_bytes() bytes, caller-owned).
+ * host_out[3] = {max row, max col, largest bucket or -1 when nothing was left in `state`}.  Synchronises
+ * once.  Hand `state` and host_out[2] to ps_coalesce on the SAME, unmodified arrays: it then skips its
+ * own histogram read and one synchronisation.  state may be NULL (validation only). */
+int64_t ps_coo_inspect_bytes(void);
+int ps_coo_inspect(const int64_t *row, const int64_t *col, int64_t nnz, int64_t M, int64_t N,
+                   void *state, int64_t *host_out, void *stream);
 /* coalesce.py:8-29 free function = sort-on-construct + coalesce, fused: one radix sort
  * of the packed keys followed by run detection + segmented reduce.  out_rowptr (nullable, [M+1]): the
  * rowptr of the coalesced result (storage.py:211-222 = ind2ptr(row, M)), written by the same pass.
@@ -98,6 +107,7 @@ int ps_coalesce_sorted(const int64_t *row, const int64_t *col, int64_t nnz, cons
 int ps_coalesce(const int64_t *row, const int64_t *col, int64_t nnz, int64_t M, int64_t N,
                 const void *value, int dtype, int64_t width, int reduce, int64_t *out_row,
                 int64_t *out_col, void *out_value, int64_t *out_rowptr, int64_t *host_nnz_out,
+                const void *inspect /* nullable, see ps_coo_inspect */, int64_t inspect_max_bucket,
                 void *stream);
 
 /* ------------------------------------------------------------------ CSC structures */
@@ -233,6 +243,10 @@ int ps_add_scalar(const int64_t *in, int64_t n, int64_t delta, int64_t *out, voi
 /* SURVEY.md 8d generator: h = splitmix64(seed + i); row = (h >> 32) % M; col = (h & 0xffffffff) % N;
  * value = fp32((splitmix64((seed ^ 0x9e3779b97f4a7c15) + i) >> 40) * 2^-24).  i in [first, first+n). */
 int ps_synth_coo(uint64_t seed, int64_t first, int64_t n, int64_t M, int64_t N, int64_t *out_row,
+                 int64_t *out_col, float *out_value, void *stream);
+/* The skewed variant of the same generator: R-MAT (0.57, 0.19, 0.19, 0.05) descents on the
+ * counter stream, reduced mod M / mod N; values as ps_synth_coo.  Same arguments. */
+int ps_synth_rmat(uint64_t seed, int64_t first, int64_t n, int64_t M, int64_t N, int64_t *out_row,
                  int64_t *out_col, float *out_value, void *stream);
 
 #ifdef __cplusplus

@@ -33,3 +33,33 @@ def synth_coo(seed: int, first: int, n: int, M: int, N: int, with_value: bool = 
             g = splitmix64((_U64(seed) ^ _GOLD) + c)
             value = ((g >> _U64(40)).astype(np.float32) * np.float32(2.0 ** -24)).astype(np.float32)
     return row, col, value
+
+
+_RMAT_A, _RMAT_AB, _RMAT_ABC = 2448131358, 3264175144, 4080218931  # floor(0.57 / 0.76 / 0.95 * 2**32)
+
+
+def synth_rmat(seed: int, first: int, n: int, M: int, N: int, with_value: bool = True):
+    """The skewed variant of SURVEY.md 8d: R-MAT (a, b, c, d) = (0.57, 0.19, 0.19, 0.05) on the same counter
+    stream (paddle_sparse_b200/csrc/synth.cu: synth_rmat_kernel).  Level l of entry c reads the high (l even) or
+    low (l odd) 32 bits of splitmix64(seed + 16 c + l // 2); values as in synth_coo."""
+    levels = max(int(max(M, N) - 1).bit_length(), 0)
+    with np.errstate(over="ignore"):
+        c = np.arange(first, first + n, dtype=_U64)
+        r = np.zeros(n, dtype=_U64)
+        q = np.zeros(n, dtype=_U64)
+        h = None
+        for lvl in range(levels):
+            if lvl % 2 == 0:
+                h = splitmix64(_U64(seed) + _U64(16) * c + _U64(lvl // 2))
+            u = (h & _U64(0xFFFFFFFF)) if lvl % 2 else (h >> _U64(32))
+            rb = (u >= _U64(_RMAT_AB)).astype(_U64)
+            cb = (((u >= _U64(_RMAT_A)) & (u < _U64(_RMAT_AB))) | (u >= _U64(_RMAT_ABC))).astype(_U64)
+            r = (r << _U64(1)) | rb
+            q = (q << _U64(1)) | cb
+        row = (r % _U64(M)).astype(np.int64)
+        col = (q % _U64(N)).astype(np.int64)
+        value = None
+        if with_value:
+            g = splitmix64((_U64(seed) ^ _GOLD) + c)
+            value = ((g >> _U64(40)).astype(np.float32) * np.float32(2.0 ** -24)).astype(np.float32)
+    return row, col, value

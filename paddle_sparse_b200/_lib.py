@@ -37,8 +37,10 @@ SIGNATURES = {
     "ps_coo_order": [c_ptr, c_ptr, c_i64, c_ptr, c_ptr],
     "ps_sort_coo": [c_ptr, c_ptr, c_i64, c_i64, c_i64, c_ptr, c_int, c_i64, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr],
     "ps_coalesce_sorted": [c_ptr, c_ptr, c_i64, c_ptr, c_int, c_i64, c_int, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr],
+    "ps_coo_inspect_bytes": [],
+    "ps_coo_inspect": [c_ptr, c_ptr, c_i64, c_i64, c_i64, c_ptr, c_ptr, c_ptr],
     "ps_coalesce": [c_ptr, c_ptr, c_i64, c_i64, c_i64, c_ptr, c_int, c_i64, c_int, c_ptr, c_ptr, c_ptr, c_ptr,
-                    c_ptr, c_ptr],
+                    c_ptr, c_ptr, c_i64, c_ptr],
     "ps_csr2csc": [c_ptr, c_i64, c_i64, c_ptr, c_ptr, c_ptr, c_ptr],
     "ps_invert_perm": [c_ptr, c_i64, c_ptr, c_ptr],
     "ps_csc_build": [c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_i64, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr],
@@ -68,8 +70,9 @@ SIGNATURES = {
     "ps_dist_partition": [c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_ptr, c_int, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr],
     "ps_add_scalar": [c_ptr, c_i64, c_i64, c_ptr, c_ptr],
     "ps_synth_coo": [c_u64, c_i64, c_i64, c_i64, c_i64, c_ptr, c_ptr, c_ptr, c_ptr],
+    "ps_synth_rmat": [c_u64, c_i64, c_i64, c_i64, c_i64, c_ptr, c_ptr, c_ptr, c_ptr],
 }
-_RESTYPES = {"ps_cuda_version": c_i64, "ps_last_error": ctypes.c_char_p, "ps_launch_count": c_i64,
+_RESTYPES = {"ps_cuda_version": c_i64, "ps_last_error": ctypes.c_char_p, "ps_launch_count": c_i64, "ps_coo_inspect_bytes": c_i64,
              "ps_prof_enable": None, "ps_prof_name": ctypes.c_char_p}
 
 _lib = None

@@ -8,7 +8,6 @@ from __future__ import annotations
 from typing import Optional
 
 import numpy as np
-import scipy.sparse
 import torch
 
 from .storage import SparseStorage, get_layout
@@ -25,6 +24,7 @@ def from_torch_sparse(A: torch.Tensor):
 
 
 def to_scipy(index: torch.Tensor, value: torch.Tensor, m: int, n: int):
+    import scipy.sparse  # imported where it is used: scipy is not needed by, and not loaded for, the GPU path
     assert not index.is_cuda and not value.is_cuda  # convert.py:18
     (row, col), data = index.detach().numpy(), value.detach().numpy()
     return scipy.sparse.coo_matrix((data, (row, col)), (m, n))
@@ -44,6 +44,7 @@ to_paddle_sparse, from_paddle_sparse = to_torch_sparse, from_torch_sparse
 def tensor_from_scipy(mat, has_value: bool = True, device="cuda") -> SparseTensor:
     """tensor.py:796-825: rowptr from the CSR view, (row, col, data) from the COO view of it, and the colptr kept
     when the input already was CSC.  The arrays are uploaded once; nothing is sorted again (is_sorted=True)."""
+    import scipy.sparse
     dev = torch.device(device)
     colptr = None
     if isinstance(mat, scipy.sparse.csc_matrix):
@@ -61,6 +62,7 @@ def tensor_from_scipy(mat, has_value: bool = True, device="cuda") -> SparseTenso
 
 def tensor_to_scipy(self: SparseTensor, layout: Optional[str] = None, dtype=None):
     """tensor.py:828-856."""
+    import scipy.sparse
     assert self.dim() == 2
     layout = get_layout(layout)
 

@@ -288,33 +288,38 @@ static int ls_launch(const uint32_t *lowkeys, const uint32_t *lowvals, const uns
   return PS_OK;
 }
 
-static int hybrid_coalesce(const int64_t *row, const int64_t *col, int64_t nnz, int rbits, int cbits, int64_t M,
-                           const void *value, int dtype, bool dedup, int reduce, int64_t *out_row, int64_t *out_col,
-                           void *out_value, int64_t *out_rowptr, int64_t *host_nnz_out, bool *used, cudaStream_t s) {
-  *used = false;
+// The hybrid plan for (nnz, rbits, cbits): T top key bits select a bucket, the low R = K - T bits are sorted inside
+// it.  Returns false when the hybrid path does not apply (narrow keys, tiny inputs, R > 32, > 2 global passes).
+struct HybridPlan {
+  int T, R, K, nb;
+  LsPlan lp;
+};
+static bool hybrid_plan(int64_t nnz, int rbits, int cbits, HybridPlan *hp) {
   const int K = rbits + cbits;
-  if (!hybrid_variant() || nnz < (int64_t(1) << 16) || K <= 32) return PS_OK;
+  if (!hybrid_variant() || nnz < (int64_t(1) << 16) || K <= 32) return false;
   // T: buckets of about LS_CAP / 2 entries on average; a bucket must be a whole range of rows (T <= rbits)
   int T = bits_for(ceil_div(nnz, LS_CAP / 2));
   if (T < K - 32) T = K - 32;  // the bucket-local key must fit 32 bits
   if (T > LS_MAX_T) T = LS_MAX_T;
   if (T > rbits) T = rbits;
   const int R = K - T;
-  if (T < 1 || R > 32 || nnz / (int64_t(1) << T) > LS_CAP * 3 / 4) return PS_OK;
-  const int nb = 1 << T;
-  Scratch scratch(s);
-
-  // bucket sizes -> offsets, largest bucket, bin bases of the global passes
+  if (T < 1 || R > 32 || nnz / (int64_t(1) << T) > LS_CAP * 3 / 4) return false;
   const SortPlan gp = make_sort_plan(T, rs_geometry<uint64_t, 1>().rbits);  // the plan radix_sort_pairs will use
-  if (gp.passes > 2) return PS_OK;
-  LsPlan lp;
-  lp.passes = gp.passes;
-  for (int p = 0; p < gp.passes; ++p) { lp.pbegin[p] = gp.begin[p]; lp.pbits[p] = gp.bits[p]; }
-  PS_SCRATCH(gcount, scratch, unsigned int, (size_t)nb);
-  PS_SCRATCH(bucket_off, scratch, unsigned int, (size_t)nb + 1);
-  PS_SCRATCH(ghist, scratch, unsigned long long, (size_t)2 * RS_MAX_RADIX);
-  PS_SCRATCH(d_max, scratch, unsigned int, 2);
-  PS_CUDA(cudaMemsetAsync(gcount, 0, sizeof(unsigned int) * (size_t)nb, s));
+  if (gp.passes > 2) return false;
+  hp->T = T;
+  hp->R = R;
+  hp->K = K;
+  hp->nb = 1 << T;
+  hp->lp.passes = gp.passes;
+  for (int p = 0; p < gp.passes; ++p) { hp->lp.pbegin[p] = gp.begin[p]; hp->lp.pbits[p] = gp.bits[p]; }
+  return true;
+}
+
+// bucket sizes -> offsets, largest bucket, bin bases of the global passes (and, with_max, max(row) / max(col))
+static int hybrid_inspect(const int64_t *row, const int64_t *col, int64_t nnz, int cbits, const HybridPlan &hp,
+                          LsInspect *st, bool with_max, cudaStream_t s) {
+  PS_CUDA(cudaMemsetAsync(st->max_rc, 0xff, sizeof(st->max_rc), s));  // -1: empty
+  PS_CUDA(cudaMemsetAsync(st->gcount, 0, sizeof(unsigned int) * (size_t)hp.nb, s));
   {
     static bool configured = false;
     if (!configured) {
@@ -323,15 +328,39 @@ static int hybrid_coalesce(const int64_t *row, const int64_t *col, int64_t nnz, 
       configured = true;
     }
     ProfScope prof(PROF_BUCKET_HIST, s);
-    ls_bucket_hist_kernel<<<sm_count() * 2, 1024, sizeof(unsigned int) * (size_t)nb, s>>>(row, col, nnz, cbits, R, T,
-                                                                                        gcount);
+    ls_bucket_hist_kernel<<<sm_count() * 2, 1024, sizeof(unsigned int) * (size_t)hp.nb, s>>>(
+        row, col, nnz, cbits, hp.R, hp.T, st->gcount, with_max ? st->max_rc : nullptr);
   }
   PS_LAUNCH_OK();
-  ls_derive_kernel<<<1, 1024, 0, s>>>(gcount, T, lp, bucket_off, ghist, d_max);
+  ls_derive_kernel<<<1, 1024, 0, s>>>(st->gcount, hp.T, hp.lp, st->bucket_off, st->ghist, st->max_bucket);
   PS_LAUNCH_OK();
+  return PS_OK;
+}
+
+// `pre` / `pre_max_bucket`: the inspection ps_coo_inspect ran on these very arrays (nullable / -1): saves the
+// histogram read and one host synchronisation.
+static int hybrid_coalesce(const int64_t *row, const int64_t *col, int64_t nnz, int rbits, int cbits, int64_t M,
+                           const void *value, int dtype, bool dedup, int reduce, int64_t *out_row, int64_t *out_col,
+                           void *out_value, int64_t *out_rowptr, int64_t *host_nnz_out, bool *used,
+                           const LsInspect *pre, int64_t pre_max_bucket, cudaStream_t s) {
+  *used = false;
+  HybridPlan hp;
+  if (!hybrid_plan(nnz, rbits, cbits, &hp)) return PS_OK;
+  const int T = hp.T, R = hp.R, nb = hp.nb;
+  Scratch scratch(s);
+  const LsInspect *st = pre;
   unsigned int h_max = 0;
-  PS_TRY(read_back(&h_max, d_max, sizeof(h_max), s));
+  if (pre && pre_max_bucket >= 0) {
+    h_max = (unsigned int)pre_max_bucket;
+  } else {
+    PS_SCRATCH(own, scratch, LsInspect, 1);
+    PS_TRY(hybrid_inspect(row, col, nnz, cbits, hp, own, false, s));
+    PS_TRY(read_back(&h_max, own->max_bucket, sizeof(h_max), s));
+    st = own;
+  }
   if (h_max > (unsigned)LS_CAP) return PS_OK;  // skewed rows: the plain LSD sort handles any distribution
+  const unsigned int *bucket_off = st->bucket_off;
+  const unsigned long long *ghist = st->ghist;
 
   // global passes on key bits [R, K): the last one keeps only the low R bits of the key
   PS_SCRATCH(k0, scratch, uint64_t, nnz);
@@ -385,13 +414,14 @@ static int hybrid_coalesce(const int64_t *row, const int64_t *col, int64_t nnz, 
 template <typename KeyT>
 int sort_impl(const int64_t *row, const int64_t *col, int64_t nnz, KeyGeom g, const void *value, int dtype,
               int64_t width, bool dedup, int reduce, int64_t *out_row, int64_t *out_col, void *out_value,
-              int64_t *out_perm, int64_t *host_nnz_out, int64_t M, int64_t *out_rowptr, cudaStream_t s) {
+              int64_t *out_perm, int64_t *host_nnz_out, int64_t M, int64_t *out_rowptr, cudaStream_t s,
+              const LsInspect *pre = nullptr, int64_t pre_max_bucket = -1) {
   const bool fast = value && fast_value(dtype, width) && !out_perm;
   if (sizeof(KeyT) == 8 && (fast || !value) && !out_perm) {  // hybrid path (sort only, or sort + dedup)
     bool used = false;
     int64_t ignored = 0;
     PS_TRY(hybrid_coalesce(row, col, nnz, g.rbits, g.cbits, M, value, dtype, dedup, reduce, out_row, out_col, out_value,
-                           out_rowptr, dedup ? host_nnz_out : &ignored, &used, s));
+                           out_rowptr, dedup ? host_nnz_out : &ignored, &used, pre, pre_max_bucket, s));
     if (used) return PS_OK;
   }
   Scratch scratch(s);
@@ -488,9 +518,33 @@ int ps_sort_coo(const int64_t *row, const int64_t *col, int64_t nnz, int64_t M, 
                              nullptr, M, nullptr, s);
 }
 
+int64_t ps_coo_inspect_bytes(void) { return (int64_t)sizeof(LsInspect); }
+
+int ps_coo_inspect(const int64_t *row, const int64_t *col, int64_t nnz, int64_t M, int64_t N, void *state,
+                   int64_t *host_out, void *stream) {
+  PS_CHECK(nnz >= 0 && M >= 0 && N >= 0, "coo_inspect: negative size");
+  PS_CHECK(host_out != nullptr, "coo_inspect: host_out is NULL");
+  host_out[0] = host_out[1] = host_out[2] = -1;
+  if (nnz == 0) return PS_OK;
+  cudaStream_t s = (cudaStream_t)stream;
+  KeyGeom g;
+  HybridPlan hp;
+  if (state == nullptr || nnz >= (int64_t(1) << 32) || key_geometry(M, N, &g) != PS_OK || g.bits <= 32 ||
+      !hybrid_plan(nnz, g.rbits, g.cbits, &hp))
+    return ps_index_max(row, nnz, col, nnz, host_out, stream);  // the plain validation pass; host_out[2] stays -1
+  LsInspect *st = reinterpret_cast<LsInspect *>(state);
+  PS_TRY(hybrid_inspect(row, col, nnz, g.cbits, hp, st, true, s));
+  struct { long long max_rc[2]; unsigned int max_bucket[2]; } h;
+  PS_TRY(read_back(&h, st, sizeof(h), s));
+  host_out[0] = (int64_t)h.max_rc[0];
+  host_out[1] = (int64_t)h.max_rc[1];
+  host_out[2] = (int64_t)h.max_bucket[0];
+  return PS_OK;
+}
+
 int ps_coalesce(const int64_t *row, const int64_t *col, int64_t nnz, int64_t M, int64_t N, const void *value, int dtype,
                 int64_t width, int reduce, int64_t *out_row, int64_t *out_col, void *out_value, int64_t *out_rowptr,
-                int64_t *host_nnz_out, void *stream) {
+                int64_t *host_nnz_out, const void *inspect, int64_t inspect_max_bucket, void *stream) {
   PS_CHECK(nnz >= 0 && M >= 0 && N >= 0, "coalesce: negative size");
   PS_CHECK(nnz < (int64_t(1) << 32), "coalesce: nnz=%lld exceeds the 2^32-1 entries per call this build supports",
            (long long)nnz);
@@ -509,7 +563,8 @@ int ps_coalesce(const int64_t *row, const int64_t *col, int64_t nnz, int64_t M, 
     return sort_impl<uint32_t>(row, col, nnz, g, value, dtype, width, true, reduce, out_row, out_col, out_value, nullptr,
                                host_nnz_out, M, out_rowptr, s);
   return sort_impl<uint64_t>(row, col, nnz, g, value, dtype, width, true, reduce, out_row, out_col, out_value, nullptr,
-                             host_nnz_out, M, out_rowptr, s);
+                             host_nnz_out, M, out_rowptr, s, reinterpret_cast<const LsInspect *>(inspect),
+                             inspect ? inspect_max_bucket : -1);
 }
 
 int ps_coalesce_sorted(const int64_t *row, const int64_t *col, int64_t nnz, const void *value, int dtype, int64_t width,

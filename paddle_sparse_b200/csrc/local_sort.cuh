@@ -20,16 +20,20 @@ constexpr int LS_ITEMS = 8;
 constexpr int LS_CAP = LS_THREADS * LS_ITEMS;  // entries one CTA sorts in shared memory
 constexpr int LS_MAX_T = 14;                    // 2^14 bucket counters = 64 KB of shared memory in the histogram
 
-// ---- histogram of the top T key bits (bucket sizes); keys are packed on the fly from the int64 arrays
+// ---- histogram of the top T key bits (bucket sizes); keys are packed on the fly from the int64 arrays.
+// With `max_rc` it is also the constructor's validation pass (storage.py:65-89: max(row), max(col)) - the same
+// 16 bytes per entry are read once for both; entries whose bucket id falls outside [0, 2^T) (out-of-range
+// indices the caller is about to reject) are not counted.
 __global__ void __launch_bounds__(1024)
 ls_bucket_hist_kernel(const int64_t *__restrict__ row, const int64_t *__restrict__ col, int64_t n, int cbits, int R,
-                      int T, unsigned int *__restrict__ gcount /*[2^T]*/) {
+                      int T, unsigned int *__restrict__ gcount /*[2^T]*/, long long *__restrict__ max_rc /*[2] | null*/) {
   extern __shared__ unsigned int ls_sh[];
-  const int nb = 1 << T;
-  for (int j = threadIdx.x; j < nb; j += blockDim.x) ls_sh[j] = 0;
+  const unsigned nb = 1u << T;
+  for (unsigned j = threadIdx.x; j < nb; j += blockDim.x) ls_sh[j] = 0;
   __syncthreads();
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  long long mr = -1, mc = -1;
   for (; i + 3 * stride < n; i += 4 * stride) {
     uint64_t r[4], c[4];
 #pragma unroll
@@ -37,16 +41,47 @@ ls_bucket_hist_kernel(const int64_t *__restrict__ row, const int64_t *__restrict
 #pragma unroll
     for (int q = 0; q < 4; ++q) c[q] = (uint64_t)ld_stream(col + i + q * stride);
 #pragma unroll
-    for (int q = 0; q < 4; ++q) atomicAdd(&ls_sh[(unsigned)(((r[q] << cbits) | c[q]) >> R)], 1u);
+    for (int q = 0; q < 4; ++q) {
+      const uint64_t b = ((r[q] << cbits) | c[q]) >> R;
+      if (b < nb && (c[q] >> cbits) == 0) atomicAdd(&ls_sh[(unsigned)b], 1u);
+      mr = (long long)r[q] > mr ? (long long)r[q] : mr;
+      mc = (long long)c[q] > mc ? (long long)c[q] : mc;
+    }
   }
   for (; i < n; i += stride) {
-    const uint64_t k = ((uint64_t)ld_stream(row + i) << cbits) | (uint64_t)ld_stream(col + i);
-    atomicAdd(&ls_sh[(unsigned)(k >> R)], 1u);
+    const uint64_t r = (uint64_t)ld_stream(row + i), c = (uint64_t)ld_stream(col + i);
+    const uint64_t b = ((r << cbits) | c) >> R;
+    if (b < nb && (c >> cbits) == 0) atomicAdd(&ls_sh[(unsigned)b], 1u);
+    mr = (long long)r > mr ? (long long)r : mr;
+    mc = (long long)c > mc ? (long long)c : mc;
+  }
+  if (max_rc) {
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+      const long long a = __shfl_xor_sync(0xffffffffu, mr, d), b = __shfl_xor_sync(0xffffffffu, mc, d);
+      mr = a > mr ? a : mr;
+      mc = b > mc ? b : mc;
+    }
+    if ((threadIdx.x & 31u) == 0) {
+      if (mr >= 0) atomicMax(&max_rc[0], mr);
+      if (mc >= 0) atomicMax(&max_rc[1], mc);
+    }
   }
   __syncthreads();
-  for (int j = threadIdx.x; j < nb; j += blockDim.x)
+  for (unsigned j = threadIdx.x; j < nb; j += blockDim.x)
     if (ls_sh[j]) atomicAdd(&gcount[j], ls_sh[j]);
 }
+
+// What one read of (row, col) leaves behind for the hybrid coalesce (ps_coo_inspect fills it at construction time,
+// ps_coalesce consumes it): the validation maxima, the largest bucket, the bin bases of the global passes, the
+// bucket offsets.  The first 24 bytes are what the host reads back.
+struct LsInspect {
+  long long max_rc[2];
+  unsigned int max_bucket[2];
+  unsigned long long ghist[2 * RS_MAX_RADIX];
+  unsigned int bucket_off[(1 << LS_MAX_T) + 1];
+  unsigned int gcount[1 << LS_MAX_T];
+};
 
 // ---- one CTA: bucket offsets (exclusive scan), the largest bucket, and the scanned digit histograms of the
 // global passes (pass p sorts bucket-id bits [pbegin[p], pbegin[p] + pbits[p]))

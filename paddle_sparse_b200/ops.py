@@ -200,9 +200,22 @@ def sort_coo(row, col, value, M: int, N: int, want_perm: bool = False):
     return out_row, out_col, out_value, out_perm
 
 
-def coalesce(row, col, value, M: int, N: int, reduce: str = "add", want_rowptr: bool = False):
+def coo_inspect(row: torch.Tensor, col: torch.Tensor, M: int, N: int):
+    """The constructor's validation pass (storage.py:65-89) fused with the first read `coalesce` needs: one pass
+    over (row, col) gives (max row, max col) and, where the hybrid plan applies, the bucket histogram left on the
+    device.  Returns (max_row, max_col, inspection | None); hand the inspection to `coalesce` on the same arrays."""
+    row, col = _idx(row, "row"), _idx(col, "col")
+    state = torch.empty(int(_lib.lib().ps_coo_inspect_bytes()), dtype=torch.uint8, device=row.device)
+    h = _host_i64(3)
+    with torch.cuda.device(row.device):
+        _lib.call("ps_coo_inspect", _p(row), _p(col), row.numel(), M, N, _p(state), h, _stream(row))
+    return int(h[0]), int(h[1]), ((state, int(h[2])) if h[2] >= 0 else None)
+
+
+def coalesce(row, col, value, M: int, N: int, reduce: str = "add", want_rowptr: bool = False, inspection=None):
     """coalesce.py:8-29 fused: packed-key radix sort + run detection + segmented reduce.
-    Returns (row', col', value'), plus rowptr' (= ind2ptr(row', M), written by the same pass) when asked."""
+    Returns (row', col', value'), plus rowptr' (= ind2ptr(row', M), written by the same pass) when asked.
+    `inspection`: what coo_inspect left behind for these very arrays (saves a read and a host sync)."""
     row, col = _idx(row, "row"), _idx(col, "col")
     value = None if value is None else _dev(value, "value")
     v, dt, w = _value_args(value)
@@ -213,7 +226,8 @@ def coalesce(row, col, value, M: int, N: int, reduce: str = "add", want_rowptr: 
     h = _host_i64()
     with torch.cuda.device(row.device):
         _lib.call("ps_coalesce", _p(row), _p(col), nnz, M, N, _p(v), dt, w, reduce_code(reduce), _p(out_row),
-                  _p(out_col), _p(out_value), _p(rowptr), h, _stream(row))
+                  _p(out_col), _p(out_value), _p(rowptr), h, _p(inspection[0]) if inspection else None,
+                  inspection[1] if inspection else -1, _stream(row))
     k = int(h[0])
     res = (out_row[:k], out_col[:k], (None if out_value is None else out_value[:k]))
     return res + (rowptr,) if want_rowptr else res
@@ -535,13 +549,14 @@ def add_scalar(x: torch.Tensor, delta: int) -> torch.Tensor:
 
 
 # ------------------------------------------------------------------ synthetic inputs (bench / tests)
-def synth_coo(seed: int, first: int, n: int, M: int, N: int, device, with_value: bool = True):
-    """SURVEY.md 8d counter-hash generator, on the device.  Returns (row, col, value|None)."""
+def synth_coo(seed: int, first: int, n: int, M: int, N: int, device, with_value: bool = True, rmat: bool = False):
+    """SURVEY.md 8d counter-hash generator, on the device (uniform, or the R-MAT skewed variant).
+    Returns (row, col, value|None)."""
     device = torch.device(device)
     row = torch.empty(n, dtype=torch.int64, device=device)
     col = torch.empty(n, dtype=torch.int64, device=device)
     value = torch.empty(n, dtype=torch.float32, device=device) if with_value else None
     with torch.cuda.device(device):
-        _lib.call("ps_synth_coo", ctypes.c_uint64(seed & (2**64 - 1)), first, n, M, N, _p(row), _p(col), _p(value),
-                  _stream(row))
+        _lib.call("ps_synth_rmat" if rmat else "ps_synth_coo", ctypes.c_uint64(seed & (2**64 - 1)), first, n, M, N,
+                  _p(row), _p(col), _p(value), _stream(row))
     return row, col, value

@@ -62,8 +62,13 @@ class SparseStorage(object):
             sparse_sizes is None or sparse_sizes[0] is None or not trust_data)
         need_n = nnz > 0 and (sparse_sizes is None or sparse_sizes[1] is None or not trust_data)
         row_max = col_max = -1
+        inspection = None
         if need_m or need_n:
-            if need_m and need_n:
+            if (need_m and need_n and not is_sorted and sparse_sizes is not None and sparse_sizes[0] is not None
+                    and sparse_sizes[1] is not None and nnz >= (1 << 16)):
+                # the validation read doubles as the first read of the coalesce / sort that an unsorted input owes
+                row_max, col_max, inspection = ops.coo_inspect(row, col, int(sparse_sizes[0]), int(sparse_sizes[1]))
+            elif need_m and need_n:
                 row_max, col_max = ops.index_max(row, col)
             elif need_m:
                 row_max, _ = ops.index_max(row)
@@ -126,10 +131,46 @@ class SparseStorage(object):
         # `coalesce()` that follows the constructor then runs sort + dedup + rowptr as one fused pipeline
         # (ops.coalesce) instead of sort -> write -> re-read -> dedup.  Every accessor sees sorted data.
         self._pending_sort = (not is_sorted) and nnz > 0
+        # the sort is deferred, so `row` / `col` are still the caller's tensors: remember their version counters and
+        # validate again at materialisation time if they were edited in place in between
+        d0 = self.__dict__
+        self._seen = (None if d0["_row_raw"] is None else d0["_row_raw"]._version, d0["_col_raw"]._version,
+                      not trust_data)
+        # what ops.coo_inspect left on the device, valid while row / col are the tensors it read, unedited
+        self._inspection = None
+        if inspection is not None and self._pending_sort:
+            d = self.__dict__
+            self._inspection = inspection + (d["_row_raw"], d["_row_raw"]._version, d["_col_raw"], d["_col_raw"]._version)
+
+    def _take_inspection(self):
+        """The constructor's inspection if row / col are still the tensors it read, with no in-place edit since."""
+        ins, self._inspection = self.__dict__.get("_inspection"), None
+        if ins is None:
+            return None
+        state, max_bucket, row_t, row_v, col_t, col_v = ins
+        d = self.__dict__
+        if d["_row_raw"] is row_t and d["_col_raw"] is col_t and row_t._version == row_v and col_t._version == col_v:
+            return state, max_bucket
+        return None
+
+    def _revalidate_if_edited(self) -> None:
+        """Deferred sort only: an in-place edit of the caller's row / col between construction and first use is
+        checked against the sparse sizes again (the reference had copied them by then; here they are read late)."""
+        d = self.__dict__
+        row_v, col_v, checked = d.get("_seen", (None, None, False))
+        row, col = d["_row_raw"], d["_col_raw"]
+        if not checked or ((row is None or row._version == row_v) and col._version == col_v):
+            return
+        self._inspection = None
+        row_max, col_max = ops.index_max(row, col) if row is not None else (-1, ops.index_max(col)[0])
+        M, N = self._sparse_sizes
+        if row_max >= M or col_max >= N:
+            raise AssertionError("row / col were edited in place after construction and no longer fit sparse_sizes")
 
     def _ensure_sorted(self) -> None:
         if not self.__dict__.get("_pending_sort", False):
             return
+        self._revalidate_if_edited()
         self._pending_sort = False
         d = self.__dict__
         if d["_row_raw"] is None:
@@ -387,8 +428,10 @@ class SparseStorage(object):
         if (d.get("_pending_sort", False) and d["_row_raw"] is not None and self._rowptr is None
                 and self._csr2csc is None and self._csc2csr is None and self._colptr is None):
             # constructor immediately followed by coalesce(): one fused sort + dedup + rowptr pipeline
+            self._revalidate_if_edited()
             M, N = self._sparse_sizes
-            row, col, value, rowptr = ops.coalesce(d["_row_raw"], d["_col_raw"], d["_value_raw"], M, N, reduce, True)
+            row, col, value, rowptr = ops.coalesce(d["_row_raw"], d["_col_raw"], d["_value_raw"], M, N, reduce, True,
+                                                   self._take_inspection())
             if row.numel() == d["_col_raw"].numel():  # nothing merged: this object simply becomes sorted
                 d["_row_raw"], d["_col_raw"], d["_value_raw"] = row, col, value
                 self._rowptr = rowptr

@@ -129,6 +129,45 @@ def test_storage_validation(ps):
     assert e.sparse_sizes() == (0, 0) and e.rowptr().tolist() == [0]
 
 
+def test_construction_inspect_validates_and_feeds_coalesce(ps, ops):
+    """Large unsorted inputs: the constructor's validation pass is the bucket histogram of the coalesce that
+    follows (ps_coo_inspect).  Out-of-range indices are still rejected at construction; the coalesce that reuses
+    the inspection equals the one that does not; an in-place edit of row / col in between is noticed."""
+    rng = np.random.default_rng(59)
+    M, N, nnz = 3_000_000, 2_500_000, 400_000
+    row, col = _random_coo(rng, M, N, nnz, 0.3)
+    val = rng.random(nnz).astype(np.float32)
+    for bad_row, bad_col in ((M, 0), (0, N), (M + (1 << 40), 0), (0, N + (1 << 45))):
+        r, c = row.copy(), col.copy()
+        r[1234], c[4321] = max(r[1234], bad_row), max(c[4321], bad_col)
+        with pytest.raises(AssertionError):
+            ps.SparseStorage(row=dev(r), col=dev(c), value=dev(val), sparse_sizes=(M, N))
+    mx = ops.coo_inspect(dev(row), dev(col), M, N)
+    assert mx[0] == row.max() and mx[1] == col.max() and mx[2] is not None
+    assert ops.coo_inspect(dev(row[:1000]), dev(col[:1000]), M, N)[2] is None  # too small for the hybrid plan
+    want = np_ref.SparseStorage(row=row, col=col, value=val.astype(np.float64), sparse_sizes=(M, N)).coalesce("add")
+    st = ps.SparseStorage(row=dev(row), col=dev(col), value=dev(val), sparse_sizes=(M, N))
+    assert st._inspection is not None
+    fused = st.coalesce("add")
+    plain = ops.coalesce(dev(row), dev(col), dev(val), M, N, "add", True)
+    for got, ref_, w in zip((fused.row(), fused.col(), fused.rowptr()), (plain[0], plain[1], plain[3]),
+                            (want.row(), want.col(), want.rowptr())):
+        assert torch.equal(got, ref_) and np.array_equal(host(got), w)
+    assert torch.equal(fused.value(), plain[2])
+    np.testing.assert_allclose(host(fused.value()), want.value(), rtol=1e-6)
+    # in-place edits between construction and first use
+    d_row, d_col = dev(row), dev(col)
+    st = ps.SparseStorage(row=d_row, col=d_col, value=dev(val), sparse_sizes=(M, N))
+    d_col.add_(1).sub_(1)                      # same content, new version: the inspection is dropped, result unchanged
+    assert torch.equal(st.coalesce("add").col(), fused.col())
+    st = ps.SparseStorage(row=d_row, col=d_col, value=dev(val), sparse_sizes=(M, N))
+    d_row[7] = M + 5
+    with pytest.raises(AssertionError):
+        st.coalesce("add")
+    st = ps.SparseStorage(row=d_row, col=d_col, value=dev(val), sparse_sizes=(M, N), trust_data=True)
+    assert st._inspection is None              # trust_data: nothing is read at construction
+
+
 # ----------------------------------------------------------------------------- test_coalesce.py / test_transpose.py
 def test_free_coalesce_golden(ps):
     g = G.COALESCE
@@ -641,3 +680,55 @@ def test_pipeline_config2_full_size_properties(ps, ops):
     keys = torch.unique(row * N + col)
     assert keys.numel() == nz
     assert torch.equal(keys, st.row() * N + st.col())
+
+
+@pytest.mark.parametrize("rmat", [False, True])
+def test_synthetic_generators_match_the_oracle_restatement(ops, rmat):
+    """host (oracle/synth.py) and device (csrc/synth.cu) produce the same stream, bit for bit, for
+    the uniform and the R-MAT variant, at an offset and with non-power-of-two sizes."""
+    from oracle import synth
+    M, N, first, n = 2449029, 1234567, 987654321, 200000
+    row, col, val = ops.synth_coo(0x5EED0002, first, n, M, N, "cuda", rmat=rmat)
+    h_row, h_col, h_val = (synth.synth_rmat if rmat else synth.synth_coo)(0x5EED0002, first, n, M, N)
+    assert np.array_equal(host(row), h_row) and np.array_equal(host(col), h_col) and np.array_equal(host(val), h_val)
+    if rmat:  # skew: the heaviest row holds far more than its uniform share
+        assert np.bincount(h_row).max() > 50 * n / M
+
+
+def test_pipeline_rmat_small_full_compare(ps, ops):
+    """The skewed variant through the whole pipeline against the oracle: hub rows overflow the shared-memory buckets
+    of the hybrid coalesce, so this covers its fall-back on realistic skew."""
+    from oracle import synth
+    M = N = 200000
+    nnz = 1500000
+    row, col, val = synth.synth_rmat(0x5EED0007, 0, nnz, M, N)
+    want = np_ref.build_pipeline(row, col, val, M, N)
+    d_row, d_col, d_val = ops.synth_coo(0x5EED0007, 0, nnz, M, N, "cuda", rmat=True)
+    A, At = _pipeline(ps, d_row, d_col, d_val, M, N)
+    st = A.storage
+    for k, t_ in dict(row=st.row(), col=st.col(), rowptr=st.rowptr(), csr2csc=st.csr2csc(), colptr=st.colptr(),
+                      csc2csr=st.csc2csr(), t_row=At.storage.row(), t_col=At.storage.col()).items():
+        assert np.array_equal(host(t_), want[k]), k
+    np.testing.assert_allclose(host(st.value()), want["value"], rtol=2e-6)
+    np.testing.assert_allclose(host(At.storage.value()), want["t_value"], rtol=2e-6)
+
+
+def test_pipeline_config2_rmat_full_size_properties(ps, ops):
+    """configs[1] sizes with the R-MAT stream (SURVEY.md 8d's skewed variant): the same size-independent
+    properties as the uniform case."""
+    M = N = 2449029
+    nnz = 61859140
+    row, col, val = ops.synth_coo(0x5EED0002, 0, nnz, M, N, "cuda", rmat=True)
+    A, At = _pipeline(ps, row, col, val, M, N)
+    st = A.storage
+    assert ops.coo_order(st.row(), st.col()) == (True, True)
+    assert ops.coo_order(At.storage.row(), At.storage.col()) == (True, True)
+    nz = A.nnz()
+    assert 0 < nz < nnz and int(st.rowptr()[-1]) == nz and int(st.colptr()[-1]) == nz
+    np.testing.assert_allclose(float(val.double().sum()), float(st.value().double().sum()), rtol=1e-9)
+    iota = torch.arange(nz, device="cuda")
+    assert torch.equal(st.csr2csc()[st.csc2csr()], iota)
+    assert torch.equal(st.col()[st.csr2csc()], At.storage.row()) and torch.equal(st.row()[st.csr2csc()], At.storage.col())
+    assert torch.equal(ops.ptr2ind(st.rowptr(), nz), st.row())
+    keys = torch.unique(row * N + col)
+    assert keys.numel() == nz and torch.equal(keys, st.row() * N + st.col())
