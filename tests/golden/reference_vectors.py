@@ -76,3 +76,13 @@ CAT = dict(row1=[0, 0, 1], col1=[0, 1, 2], row2=[0, 0, 1, 2], col2=[0, 1, 1, 0],
 
 # test/test_convert.py:9-30 (round trips through scipy and the framework's own sparse COO type)
 CONVERT = dict(index=[[0, 0, 1, 2, 2], [0, 2, 1, 0, 1]], value=[1, 2, 4, 1, 3], N=3)
+
+# test/test_eye.py:14-66
+EYE = dict(square=dict(M=3, N=3, row=[0, 1, 2], rowptr=[0, 1, 2, 3], col=[0, 1, 2], value=[1, 1, 1]),
+           wide=dict(M=3, N=4, row=[0, 1, 2], rowptr=[0, 1, 2, 3], col=[0, 1, 2], rowcount=[1, 1, 1],
+                     colptr=[0, 1, 2, 3, 3], colcount=[1, 1, 1, 0], csr2csc=[0, 1, 2], csc2csr=[0, 1, 2]),
+           tall=dict(M=4, N=3, row=[0, 1, 2], rowptr=[0, 1, 2, 3, 3], col=[0, 1, 2], rowcount=[1, 1, 1, 0],
+                     colptr=[0, 1, 2, 3], colcount=[1, 1, 1], csr2csc=[0, 1, 2], csc2csr=[0, 1, 2]))
+
+# test/test_overload.py:6-22 (value-less matrix, dense operand on either side of + and *)
+OVERLOAD = dict(row=[0, 1, 1, 2, 2], col=[1, 0, 2, 1, 2], other=[1, 2, 3])

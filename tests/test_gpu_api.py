@@ -436,6 +436,44 @@ def test_add_broadcast(ps, dtype):
     np.testing.assert_allclose(got.double().cpu().numpy(), want.cpu().numpy(), rtol=8e-3)
 
 
+# ----------------------------------------------------------------------------- test_eye.py / test_overload.py
+@pytest.mark.parametrize("dtype", [torch.float32, torch.float64, torch.int64, torch.bfloat16, torch.float16])
+def test_eye_golden(ps, dtype):
+    """test/test_eye.py:14-66."""
+    g = G.EYE["square"]
+    mat = ps.SparseTensor.eye(3, dtype=dtype, device="cuda")
+    st = mat.storage
+    assert mat.device().type == "cuda" and st.sparse_sizes() == (3, 3)
+    assert st.row().tolist() == g["row"] and st.rowptr().tolist() == g["rowptr"] and st.col().tolist() == g["col"]
+    assert host(st.value()).tolist() == g["value"] and st.value().dtype == dtype
+    assert st.num_cached_keys() == 0
+    st = ps.SparseTensor.eye(3, has_value=False, device="cuda").storage
+    assert st.row().tolist() == g["row"] and st.rowptr().tolist() == g["rowptr"] and st.col().tolist() == g["col"]
+    assert st.value() is None and st.num_cached_keys() == 0
+    for key in ("wide", "tall"):
+        g = G.EYE[key]
+        st = ps.SparseTensor.eye(g["M"], g["N"], fill_cache=True, device="cuda").storage
+        assert st.sparse_sizes() == (g["M"], g["N"]) and st.num_cached_keys() == 5
+        for name in ("row", "rowptr", "col", "rowcount", "colptr", "colcount", "csr2csc", "csc2csr"):
+            assert getattr(st, name)().tolist() == g[name], (key, name)
+
+
+def test_overload_golden(ps):
+    """test/test_overload.py:6-22: a dense [M,1] / [1,N] operand on either side of + and * of a value-less matrix;
+    the stored entries count as 1 for + and take the operand's value for *."""
+    g = G.OVERLOAD
+    row, col = np.array(g["row"], I64), np.array(g["col"], I64)
+    mat = ps.SparseTensor(row=dev(row), col=dev(col))
+    for shape, picked in (((3, 1), row), ((1, 3), col)):
+        other = dev(np.array(g["other"], I64)).view(shape)
+        want = np.array(g["other"])[picked]
+        for out in (other + mat, mat + other):
+            assert out.storage.value().tolist() == (want + 1).tolist()
+        for out in (other * mat, mat * other):
+            assert out.storage.value().tolist() == want.tolist()
+            assert out.storage.row().tolist() == g["row"] and out.storage.col().tolist() == g["col"]
+
+
 # ----------------------------------------------------------------------------- converters
 @pytest.mark.parametrize("fmt", ["coo", "csr", "csc"])
 @pytest.mark.parametrize("has_value", [True, False])
