@@ -265,6 +265,43 @@ class SparseTensor(object):
     def cuda(self):
         return self  # GPU-only package: a SparseTensor always lives on a CUDA device
 
+    def to(self, *args, **kwargs):
+        """tensor.py:606-700: `to(device, dtype, non_blocking)`, `to(dtype, non_blocking)` or `to(other, non_blocking)`.
+        The dtype applies to the values; a CUDA device moves every stored array; a CPU device is refused - this
+        package has no CPU representation (the reference moves the arrays to the host here)."""
+        if not 0 < len(args) + len(kwargs) <= 3:
+            raise TypeError("to() expects (device, dtype, non_blocking), (dtype, non_blocking) or (other, non_blocking)")
+        if not set(kwargs) <= {"device", "dtype", "blocking", "non_blocking", "other"}:
+            raise TypeError(f"to() got unexpected keyword arguments {sorted(set(kwargs))}")
+        device, dtype = kwargs.get("device"), kwargs.get("dtype")
+        other = kwargs.get("other")
+        for a in args:
+            if isinstance(a, torch.Tensor):
+                other = a
+            elif isinstance(a, torch.dtype):
+                dtype = a
+            elif isinstance(a, (str, torch.device, int)) and not isinstance(a, bool):
+                device = a
+        if other is not None:
+            device, dtype = other.device, other.dtype
+        out = self
+        if device is not None:
+            device = torch.device("cuda", device) if isinstance(device, int) else torch.device(device)
+            if device.type != "cuda":
+                raise RuntimeError("paddle_sparse_b200.SparseTensor is GPU-only (no CPU representation): "
+                                   f"cannot move to {device}")
+            if device.index is not None and device != self.device():
+                st = self.storage
+
+                def mv(t):
+                    return None if t is None else t.to(device)
+                out = self.from_storage(SparseStorage(
+                    row=mv(st._row), rowptr=mv(st._rowptr), col=mv(st._col), value=mv(st._value),
+                    sparse_sizes=st._sparse_sizes, rowcount=mv(st._rowcount), colptr=mv(st._colptr),
+                    colcount=mv(st._colcount), csr2csc=mv(st._csr2csc), csc2csr=mv(st._csc2csr), is_sorted=True,
+                    trust_data=True))
+        return out.type(dtype) if dtype is not None else out
+
     def dtype(self):
         value = self.storage.value()
         return torch.float32 if value is None else value.dtype  # tensor.py:503-505

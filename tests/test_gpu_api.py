@@ -474,6 +474,28 @@ def test_overload_golden(ps):
             assert out.storage.row().tolist() == g["row"] and out.storage.col().tolist() == g["col"]
 
 
+def test_equal_and_to(ps):
+    """test/test_tensor.py:91-124: `==` compares sizes, indices and values; `to(dtype)` converts the values.  The
+    reference's `to(CPUPlace)` has no counterpart here (GPU-only) and says so."""
+    row, col = dev(np.array([0, 0, 0, 1, 1], I64)), dev(np.array([0, 1, 2, 0, 2], I64))
+    value = torch.arange(1, 6, device="cuda")
+    matA = ps.SparseTensor(row=row, col=col, value=value)
+    matB = ps.SparseTensor(row=row, col=col, value=value)
+    matC = ps.SparseTensor(row=row, col=dev(np.array([0, 1, 2, 0, 1], I64)), value=value)
+    assert matA is not matB and matA == matB
+    assert matA is not matC and matA != matC
+    assert value.dtype == torch.int64
+    mat = matA.to(torch.float32)
+    assert mat.storage.value().dtype == torch.float32 and matA.storage.value().dtype == torch.int64
+    assert matA.to("cuda", torch.float64).storage.value().dtype == torch.float64
+    assert matA.to(torch.zeros(1, dtype=torch.float16, device="cuda")).storage.value().dtype == torch.float16
+    assert matA.to("cuda:0").storage.row().device == row.device
+    with pytest.raises(RuntimeError):
+        matA.to("cpu", torch.float32)
+    with pytest.raises(TypeError):
+        matA.to()
+
+
 # ----------------------------------------------------------------------------- converters
 @pytest.mark.parametrize("fmt", ["coo", "csr", "csc"])
 @pytest.mark.parametrize("has_value", [True, False])
