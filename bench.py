@@ -271,7 +271,7 @@ def run_ours(args):
     # warm-up: W untimed steps through the SAME loop as the timed region (the previous step's result stays alive
     # while the next one is built), so that the caching allocators already hold the blocks that loop needs; a
     # warm-up that drops each result at once leaves ~12 cudaMalloc calls to the first timed steps
-    # (tools/gcprobe.py: 7.0 vs 6.2 ms/step over the first five).
+    # (tools/allocprobe.py: 7.0 vs 6.2 ms/step over the first five).
     _, out = timed(step, max(args.warmup, 3))
     del out
     # timed region 1: the headline (no per-kernel events)
