@@ -310,8 +310,8 @@ static __device__ unsigned long long g_rs_timeline[16];  // one copy per transla
 //   4 position of every item; stage tuples in tile-sorted order; request the next tile
 //   5 finish the decoupled look-back
 //   6 coalesced scatter of contiguous per-digit runs
-template <typename KeyT, int NPAY, int RBITS, int THREADS, int ITEMS, bool PREFETCH>
-__global__ void __launch_bounds__(THREADS, 1024 / THREADS)
+template <typename KeyT, int NPAY, int RBITS, int THREADS, int ITEMS, bool PREFETCH, int MINB = 1024 / THREADS>
+__global__ void __launch_bounds__(THREADS, MINB)
 rs_pass_kernel(KeySrc ksrc, PaySrcN<NPAY> psrc, KeyDst kdst, PayDstN<NPAY> pdst, int64_t n, int64_t tiles,
                int begin_bit, int num_bits, int epoch, const unsigned long long *__restrict__ bin_base,
                uint64_t *__restrict__ tile_state /*[tiles][RADIX]*/, unsigned long long *ticket) {
@@ -535,20 +535,23 @@ template <> struct RsGeom<uint64_t, 3> { static constexpr int ITEMS = 8; static 
 struct RsGeomRt {
   int rbits, tile;
 };
-// variants (PS_RS_VARIANT): 0 = 1024 threads, one CTA per SM; 1 = 512 threads, two CTAs per SM; 2 = 0 with 9-bit digits
+// Launch shape (PS_RS_VARIANT): 0 (default) = 512 threads holding 2 x ITEMS tuples each, 1 = 1024 threads holding
+// ITEMS each; one CTA per SM and the same tile either way.  With 1024 threads the register file caps a thread at 64
+// registers and the key / rank / payload arrays spill (56-72 B per thread); 512 threads get 128 registers and no
+// spills: 7 % faster passes (0.606 -> 0.561 ms on the 61.9 M-tuple u64 passes).  9-bit digits and two
+// 512-thread CTAs per SM on half tiles were measured too and brought nothing.
 template <typename KeyT, int NPAY>
 RsGeomRt rs_geometry() {
-  const int v = rs_variant();
-  return RsGeomRt{v == 2 ? 9 : 8, (v == 1 ? 512 : 1024) * RsGeom<KeyT, NPAY>::ITEMS};
+  return RsGeomRt{8, 1024 * RsGeom<KeyT, NPAY>::ITEMS};
 }
 
-template <typename KeyT, int NPAY, int RBITS, int THREADS>
+template <typename KeyT, int NPAY, int RBITS, int THREADS, int IMUL = 1>
 int rs_launch_pass(KeySrc ks, PaySrcN<NPAY> ps_, KeyDst ko, PayDstN<NPAY> pd, int64_t n, int begin, int bits,
                    int epoch, const unsigned long long *bin_base, uint64_t *state, unsigned long long *ticket,
                    cudaStream_t s) {
   using G = RsGeom<KeyT, NPAY>;
-  using Smem = RsSmem<KeyT, NPAY, RBITS, THREADS, G::ITEMS, G::PREFETCH>;
-  auto kern = rs_pass_kernel<KeyT, NPAY, RBITS, THREADS, G::ITEMS, G::PREFETCH>;
+  using Smem = RsSmem<KeyT, NPAY, RBITS, THREADS, G::ITEMS * IMUL, G::PREFETCH>;
+  auto kern = rs_pass_kernel<KeyT, NPAY, RBITS, THREADS, G::ITEMS * IMUL, G::PREFETCH, 1024 / (THREADS * IMUL)>;
   const size_t smem = sizeof(Smem);
   static bool configured = false;
   if (!configured) {
@@ -556,7 +559,7 @@ int rs_launch_pass(KeySrc ks, PaySrcN<NPAY> ps_, KeyDst ko, PayDstN<NPAY> pd, in
     configured = true;
   }
   const int64_t tiles = ceil_div(n, Smem::TILE);
-  int64_t grid = (int64_t)sm_count() * (1024 / THREADS);
+  int64_t grid = (int64_t)sm_count() * (1024 / (THREADS * IMUL));
   if (grid > tiles) grid = tiles;
   {
     ProfScope prof(PROF_RS_PASS, s);
@@ -570,11 +573,9 @@ template <typename KeyT, int NPAY>
 int rs_dispatch_pass(KeySrc ks, PaySrcN<NPAY> ps_, KeyDst ko, PayDstN<NPAY> pd, int64_t n, int begin, int bits,
                      int epoch, const unsigned long long *bin_base, uint64_t *state, unsigned long long *ticket,
                      cudaStream_t s) {
-  switch (rs_variant()) {
-    case 1: return rs_launch_pass<KeyT, NPAY, 8, 512>(ks, ps_, ko, pd, n, begin, bits, epoch, bin_base, state, ticket, s);
-    case 2: return rs_launch_pass<KeyT, NPAY, 9, 1024>(ks, ps_, ko, pd, n, begin, bits, epoch, bin_base, state, ticket, s);
-    default: return rs_launch_pass<KeyT, NPAY, 8, 1024>(ks, ps_, ko, pd, n, begin, bits, epoch, bin_base, state, ticket, s);
-  }
+  if (rs_variant() == 1)
+    return rs_launch_pass<KeyT, NPAY, 8, 1024, 1>(ks, ps_, ko, pd, n, begin, bits, epoch, bin_base, state, ticket, s);
+  return rs_launch_pass<KeyT, NPAY, 8, 512, 2>(ks, ps_, ko, pd, n, begin, bits, epoch, bin_base, state, ticket, s);
 }
 
 // Sorts n (key, NPAY payload words) tuples on key bits [first_bit, first_bit + total_bits).  First-pass sources are
