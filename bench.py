@@ -36,8 +36,9 @@ PIPELINE_BYTES_PER_NNZ = 128.6
 PIPELINE_LOCAL_BYTES_PER_NNZ = 80.6
 CPU_SAMPLE_NNZ = 8_000_000
 # dram__bytes_read.sum + dram__bytes_write.sum of rs_pass_kernel, average per launch over the 7 launches of one
-# step, from the committed `ncu --set full` capture (profiles/r01c_*): updated whenever the capture is
-NCU_TRAFFIC_PER_LAUNCH = 1.711e9
+# step, from the committed `ncu --set full` capture (profiles/r01d_bench_step_kernels_summary.txt: 11.83 GB over the
+# 7 launches): updated whenever the capture is
+NCU_TRAFFIC_PER_LAUNCH = 1.690e9
 
 
 def peaks():
