@@ -172,6 +172,7 @@ class SparseStorage(object):
             return
         self._revalidate_if_edited()
         self._pending_sort = False
+        self._inspection = None  # only the fused constructor + coalesce pipeline consumes it
         d = self.__dict__
         if d["_row_raw"] is None:
             d["_row_raw"] = ops.ptr2ind(self._rowptr, d["_col_raw"].numel())  # storage.py:202
