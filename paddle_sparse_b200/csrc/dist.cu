@@ -106,17 +106,36 @@ int ps_dist_partition(const int64_t *row, const int64_t *col, const void *value,
   if (nnz == 0) return PS_OK;
   Scratch scratch(s);
   PS_SCRATCH(dest, scratch, uint32_t, nnz);
-  PS_SCRATCH(perm, scratch, uint32_t, nnz);
   int64_t blocks = ceil_div(nnz, 256 * 8);
   const int64_t cap = 8 * (int64_t)sm_count();
   if (blocks > cap) blocks = cap;
   dest_kernel<<<(unsigned)blocks, 256, 0, s>>>(row, nnz, splitters, G, dest,
                                               reinterpret_cast<unsigned long long *>(out_counts));
   PS_LAUNCH_OK();
-  // one stable counting pass on the destination id; the payload is the entry index
-  PS_TRY(radix_sort_pairs<uint32_t>(KeySrc{dest, nullptr, KSRC_KEYS, 0}, PaySrc{nullptr, PSRC_IOTA}, nnz,
-                                    G > 1 ? bits_for(G) : 1, nullptr, nullptr, nullptr, nullptr,
-                                    KeyDst{nullptr, nullptr, KDST_NONE, 0}, PayDst{perm, PDST_U32}, scratch, s));
+  const int dbits = G > 1 ? bits_for(G) : 1;
+  if (row_bytes == 0 || row_bytes == 4) {
+    // ONE stable counting pass on the destination id that carries the tuple itself (row, col and the 4-byte value as
+    // three 32-bit payload words; indices are < 2^32 on this path) and writes the int64 outputs directly: 24 B read +
+    // 20 B written per tuple, where a pass on (destination, entry index) followed by three gathers moved 68 B
+    const bool has_v = value && row_bytes > 0;
+    uint32_t *none[3] = {nullptr, nullptr, nullptr};
+    PaySrcN<3> ps_;
+    ps_.s[0] = PaySrc{row, PSRC_I64};
+    ps_.s[1] = PaySrc{col, PSRC_I64};
+    ps_.s[2] = has_v ? PaySrc{value, PSRC_U32} : PaySrc{nullptr, PSRC_NONE};
+    PayDstN<3> pd;
+    pd.d[0] = PayDst{out_row, PDST_I64};
+    pd.d[1] = PayDst{out_col, PDST_I64};
+    pd.d[2] = has_v ? PayDst{out_value, PDST_U32} : PayDst{nullptr, PDST_NONE};
+    PS_TRY((radix_sort_tuples<uint32_t, 3>(KeySrc{dest, nullptr, KSRC_KEYS, 0}, ps_, nnz, dbits, nullptr, nullptr, none,
+                                           none, KeyDst{nullptr, nullptr, KDST_NONE, 0}, pd, scratch, s)));
+    return PS_OK;
+  }
+  // wide values: one stable counting pass on the destination id with the entry index as payload, then gathers
+  PS_SCRATCH(perm, scratch, uint32_t, nnz);
+  PS_TRY(radix_sort_pairs<uint32_t>(KeySrc{dest, nullptr, KSRC_KEYS, 0}, PaySrc{nullptr, PSRC_IOTA}, nnz, dbits, nullptr,
+                                    nullptr, nullptr, nullptr, KeyDst{nullptr, nullptr, KDST_NONE, 0},
+                                    PayDst{perm, PDST_U32}, scratch, s));
   PS_TRY(gather_rows_launch<uint32_t>(row, 8, perm, nnz, out_row, s));
   PS_TRY(gather_rows_launch<uint32_t>(col, 8, perm, nnz, out_col, s));
   if (value && row_bytes > 0) PS_TRY(gather_rows_launch<uint32_t>(value, row_bytes, perm, nnz, out_value, s));

@@ -258,3 +258,12 @@ def test_dist_histogram_and_partition(ops, G_):
     assert np.array_equal(host(counts), np.bincount(dest, minlength=G_))
     assert np.array_equal(host(r), row[order]) and np.array_equal(host(c), col[order])
     assert np.array_equal(host(v), val[order])
+    # value-less tuples ride the same single pass; wide values take the permutation + gather route
+    r, c, v, _ = ops.dist_partition(dev(row), dev(col), None, dev(splitters))
+    assert v is None and np.array_equal(host(r), row[order]) and np.array_equal(host(c), col[order])
+    wide = rng.random((nnz, 3))
+    r, c, v, _ = ops.dist_partition(dev(row), dev(col), dev(wide), dev(splitters))
+    assert np.array_equal(host(r), row[order]) and np.array_equal(host(v), wide[order])
+    big = row + (1 << 31)  # indices above 2^31 survive the 32-bit payload words
+    r, c, _, _ = ops.dist_partition(dev(big), dev(col), None, dev(splitters + (1 << 31)))
+    assert np.array_equal(host(r), big[order])
