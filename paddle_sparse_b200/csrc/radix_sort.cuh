@@ -545,6 +545,15 @@ RsGeomRt rs_geometry() {
   return RsGeomRt{8, 1024 * RsGeom<KeyT, NPAY>::ITEMS};
 }
 
+// Digit width of a sort that computes its own histograms: 9 bits where that saves a whole pass over HBM (64-bit keys
+// of 41-45 or 49-54 bits: 5 or 6 passes instead of 6 or 7; a 9-bit pass costs what an 8-bit one does), else 8.
+// Callers that bring their own bin bases (hybrid coalesce, inverse permutation) planned with 8 and stay there.
+template <typename KeyT, int NPAY>
+inline int rs_auto_rbits(int total_bits) {
+  if (sizeof(KeyT) == 8 && NPAY == 1 && (total_bits + 8) / 9 < (total_bits + 7) / 8) return 9;
+  return 8;
+}
+
 template <typename KeyT, int NPAY, int RBITS, int THREADS, int IMUL = 1>
 int rs_launch_pass(KeySrc ks, PaySrcN<NPAY> ps_, KeyDst ko, PayDstN<NPAY> pd, int64_t n, int begin, int bits,
                    int epoch, const unsigned long long *bin_base, uint64_t *state, unsigned long long *ticket,
@@ -570,9 +579,13 @@ int rs_launch_pass(KeySrc ks, PaySrcN<NPAY> ps_, KeyDst ko, PayDstN<NPAY> pd, in
 }
 
 template <typename KeyT, int NPAY>
-int rs_dispatch_pass(KeySrc ks, PaySrcN<NPAY> ps_, KeyDst ko, PayDstN<NPAY> pd, int64_t n, int begin, int bits,
-                     int epoch, const unsigned long long *bin_base, uint64_t *state, unsigned long long *ticket,
-                     cudaStream_t s) {
+int rs_dispatch_pass(int rbits, KeySrc ks, PaySrcN<NPAY> ps_, KeyDst ko, PayDstN<NPAY> pd, int64_t n, int begin,
+                     int bits, int epoch, const unsigned long long *bin_base, uint64_t *state,
+                     unsigned long long *ticket, cudaStream_t s) {
+  if constexpr (sizeof(KeyT) == 8 && NPAY == 1) {
+    if (rbits == 9)
+      return rs_launch_pass<KeyT, NPAY, 9, 512, 2>(ks, ps_, ko, pd, n, begin, bits, epoch, bin_base, state, ticket, s);
+  }
   if (rs_variant() == 1)
     return rs_launch_pass<KeyT, NPAY, 8, 1024, 1>(ks, ps_, ko, pd, n, begin, bits, epoch, bin_base, state, ticket, s);
   return rs_launch_pass<KeyT, NPAY, 8, 512, 2>(ks, ps_, ko, pd, n, begin, bits, epoch, bin_base, state, ticket, s);
@@ -589,10 +602,11 @@ int radix_sort_tuples(KeySrc ksrc, PaySrcN<NPAY> psrc, int64_t n, int total_bits
                       const unsigned long long *scanned_hist = nullptr /* [passes][512] bin bases, if known */) {
   if (n <= 0) return PS_OK;
   const RsGeomRt geom = rs_geometry<KeyT, NPAY>();
-  SortPlan plan = make_sort_plan(total_bits, geom.rbits);
+  const int rbits = scanned_hist ? geom.rbits : rs_auto_rbits<KeyT, NPAY>(total_bits);
+  SortPlan plan = make_sort_plan(total_bits, rbits);
   for (int i = 0; i < plan.passes; ++i) plan.begin[i] += first_bit;  // sort on key bits [first_bit, first_bit + total_bits)
   if (plan.passes > RS_MAX_PASSES) { set_error("radix sort: %d key bits unsupported", total_bits); return PS_ERR_ARG; }
-  const int radix = 1 << geom.rbits;
+  const int radix = 1 << rbits;
   const int64_t tiles = ceil_div(n, geom.tile);
 
   // one allocation: [passes*512 hist | passes tickets (padded to 32) | tiles*radix state words]
@@ -636,7 +650,7 @@ int radix_sort_tuples(KeySrc ksrc, PaySrcN<NPAY> psrc, int64_t n, int total_bits
       ko = keys_final;
       pd = pay_final;
     }
-    PS_TRY((rs_dispatch_pass<KeyT, NPAY>(ks, ps_, ko, pd, n, plan.begin[p], plan.bits[p], p + 1,
+    PS_TRY((rs_dispatch_pass<KeyT, NPAY>(rbits, ks, ps_, ko, pd, n, plan.begin[p], plan.bits[p], p + 1,
                                          ghist + (size_t)p * RS_MAX_RADIX, state, tickets + p, s)));
   }
   return PS_OK;
@@ -644,7 +658,7 @@ int radix_sort_tuples(KeySrc ksrc, PaySrcN<NPAY> psrc, int64_t n, int total_bits
 
 // number of passes radix_sort_* will run for this key type (callers pick the ping-pong buffer with it)
 template <typename KeyT>
-int rs_num_passes(int total_bits) { return make_sort_plan(total_bits, rs_geometry<KeyT, 1>().rbits).passes; }
+int rs_num_passes(int total_bits) { return make_sort_plan(total_bits, rs_auto_rbits<KeyT, 1>(total_bits)).passes; }
 
 // the common single-payload form
 template <typename KeyT>
