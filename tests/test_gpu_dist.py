@@ -13,8 +13,8 @@ import torch.multiprocessing as mp
 pytestmark = pytest.mark.gpu
 
 
-def _worker(rank, world, port, M, N, per_rank, out):
-    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+def _worker(rank, world, port, M, N, per_rank, out, exchange="peer"):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), PS_DIST_EXCHANGE=exchange)
     torch.cuda.set_device(rank)
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
     try:
@@ -24,7 +24,8 @@ def _worker(rank, world, port, M, N, per_rank, out):
         row = (row * row) % M  # skew the rows so that the splitters matter
         shard = psd.build_partitioned(row, col, val, (M, N), fill_cache=True, transpose=True)
         st = shard.tensor.storage
-        out[rank] = dict(r0=shard.row_start, r1=shard.row_end, row=shard.global_row().cpu().numpy(),
+        out[rank] = dict(peer=bool(psd._peer_buffers) and not psd._peer_unavailable,
+                         r0=shard.row_start, r1=shard.row_end, row=shard.global_row().cpu().numpy(),
                          col=st.col().cpu().numpy(), val=st.value().cpu().numpy(), rowptr=st.rowptr().cpu().numpy(),
                          colptr=st.colptr().cpu().numpy(), sizes=shard.tensor.sparse_sizes(),
                          t_sizes=shard.transposed.sparse_sizes(), src=(row.cpu().numpy(), col.cpu().numpy(),
@@ -33,8 +34,9 @@ def _worker(rank, world, port, M, N, per_rank, out):
         dist.destroy_process_group()
 
 
+@pytest.mark.parametrize("exchange", ["peer", "nccl"])  # peer-memory copies (default) / all_to_all_single (fall-back)
 @pytest.mark.parametrize("world", [2])
-def test_partitioned_build_matches_single_gpu(cuda, world):
+def test_partitioned_build_matches_single_gpu(cuda, world, exchange):
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs")
     from oracle import np_ref
@@ -43,8 +45,9 @@ def test_partitioned_build_matches_single_gpu(cuda, world):
         s.bind(("127.0.0.1", 0))
         port = s.getsockname()[1]
     out = mp.Manager().dict()
-    mp.spawn(_worker, args=(world, port, M, N, per_rank, out), nprocs=world, join=True)
+    mp.spawn(_worker, args=(world, port, M, N, per_rank, out, exchange), nprocs=world, join=True)
     res = [out[r] for r in range(world)]
+    assert all(r["peer"] == (exchange == "peer") for r in res)  # the path that was asked for is the one that ran
     src = [np.concatenate([res[r]["src"][k] for r in range(world)]) for k in range(3)]
     idx, val = np_ref.coalesce(np.stack([src[0], src[1]]), src[2].astype(np.float64), M, N, "add")
     assert res[0]["r0"] == 0 and res[-1]["r1"] == M
