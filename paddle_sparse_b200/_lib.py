@@ -68,6 +68,8 @@ SIGNATURES = {
                       c_ptr, c_ptr],
     "ps_dist_row_histogram": [c_ptr, c_i64, c_int, c_i64, c_ptr, c_ptr],
     "ps_dist_partition": [c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_ptr, c_int, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr],
+    "ps_dist_dest": [c_ptr, c_i64, c_ptr, c_int, c_ptr, c_ptr, c_ptr],
+    "ps_dist_scatter_peer": [c_ptr, c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_int, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr],
     "ps_add_scalar": [c_ptr, c_i64, c_i64, c_ptr, c_ptr],
     "ps_synth_coo": [c_u64, c_i64, c_i64, c_i64, c_i64, c_ptr, c_ptr, c_ptr, c_ptr],
     "ps_synth_rmat": [c_u64, c_i64, c_i64, c_i64, c_i64, c_ptr, c_ptr, c_ptr, c_ptr],

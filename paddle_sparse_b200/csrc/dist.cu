@@ -142,4 +142,48 @@ int ps_dist_partition(const int64_t *row, const int64_t *col, const void *value,
   return PS_OK;
 }
 
+int ps_dist_dest(const int64_t *row, int64_t nnz, const int64_t *splitters, int G, uint32_t *out_dest,
+                 int64_t *out_counts, void *stream) {
+  PS_CHECK(nnz >= 0 && G >= 1 && G <= 64, "dist_dest: bad arguments (G must be in [1, 64])");
+  cudaStream_t s = (cudaStream_t)stream;
+  PS_CUDA(cudaMemsetAsync(out_counts, 0, sizeof(int64_t) * (size_t)G, s));
+  if (nnz == 0) return PS_OK;
+  int64_t blocks = ceil_div(nnz, 256 * 8);
+  const int64_t cap = 8 * (int64_t)sm_count();
+  if (blocks > cap) blocks = cap;
+  dest_kernel<<<(unsigned)blocks, 256, 0, s>>>(row, nnz, splitters, G, out_dest,
+                                              reinterpret_cast<unsigned long long *>(out_counts));
+  PS_LAUNCH_OK();
+  return PS_OK;
+}
+
+int ps_dist_scatter_peer(const uint32_t *dest, const int64_t *row, const int64_t *col, const void *value,
+                         int64_t row_bytes, int64_t nnz, int G, const int64_t *bases, void *const *peer_row,
+                         void *const *peer_col, void *const *peer_value, void *stream) {
+  PS_CHECK(nnz >= 0 && G >= 1 && G <= 64, "dist_scatter_peer: bad arguments (G must be in [1, 64])");
+  PS_CHECK(row_bytes == 0 || row_bytes == 4, "dist_scatter_peer: values must be absent or 4 bytes per entry");
+  PS_CHECK(nnz < (int64_t(1) << 32), "dist_scatter_peer: nnz=%lld exceeds 2^32-1 entries per call", (long long)nnz);
+  if (nnz == 0) return PS_OK;
+  cudaStream_t s = (cudaStream_t)stream;
+  Scratch scratch(s);
+  // the "histogram" of this single pass is given: bin d starts at bases[d] inside destination d's buffer
+  PS_SCRATCH(gh, scratch, unsigned long long, RS_MAX_RADIX);
+  PS_CUDA(cudaMemsetAsync(gh, 0, sizeof(unsigned long long) * RS_MAX_RADIX, s));
+  PS_CUDA(cudaMemcpyAsync(gh, bases, sizeof(int64_t) * (size_t)G, cudaMemcpyDeviceToDevice, s));
+  const bool has_v = value && row_bytes > 0;
+  uint32_t *none[3] = {nullptr, nullptr, nullptr};
+  PaySrcN<3> ps_;
+  ps_.s[0] = PaySrc{row, PSRC_I64};
+  ps_.s[1] = PaySrc{col, PSRC_I64};
+  ps_.s[2] = has_v ? PaySrc{value, PSRC_U32} : PaySrc{nullptr, PSRC_NONE};
+  PayDstN<3> pd;
+  pd.d[0] = PayDst{const_cast<void **>(peer_row), PDST_I64_BY_DIGIT};
+  pd.d[1] = PayDst{const_cast<void **>(peer_col), PDST_I64_BY_DIGIT};
+  pd.d[2] = has_v ? PayDst{const_cast<void **>(peer_value), PDST_U32_BY_DIGIT} : PayDst{nullptr, PDST_NONE};
+  PS_TRY((radix_sort_tuples<uint32_t, 3>(KeySrc{dest, nullptr, KSRC_KEYS, 0}, ps_, nnz, G > 1 ? bits_for(G) : 1, nullptr,
+                                         nullptr, none, none, KeyDst{nullptr, nullptr, KDST_NONE, 0}, pd, scratch, s, 0,
+                                         gh)));
+  return PS_OK;
+}
+
 }  // extern "C"

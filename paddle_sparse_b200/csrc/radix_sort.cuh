@@ -47,7 +47,10 @@ inline SortPlan make_sort_plan(int total_bits, int rbits) {
 // ---- where the first pass finds its keys / payload, and where the last one puts them
 enum { KSRC_KEYS = 0, KSRC_PACK_COO = 1, KSRC_I64 = 2 };
 enum { PSRC_U32 = 0, PSRC_IOTA = 1, PSRC_U16 = 2, PSRC_U8 = 3, PSRC_I64 = 4, PSRC_NONE = 5 /* word unused */ };
-enum { PDST_U32 = 0, PDST_I64 = 1, PDST_U16 = 2, PDST_U8 = 3, PDST_NONE = 4 };
+enum { PDST_U32 = 0, PDST_I64 = 1, PDST_U16 = 2, PDST_U8 = 3, PDST_NONE = 4,
+       // p = device array of one base pointer PER DIGIT (single-pass partitions whose bins live in different
+       // buffers, e.g. the receive buffers of peer GPUs): the word goes to p[digit][bin_base[digit] + rank in bin]
+       PDST_I64_BY_DIGIT = 5, PDST_U32_BY_DIGIT = 6 };
 enum { KDST_NONE = 0, KDST_KEYS = 1, KDST_UNPACK_COO = 2, KDST_I64 = 3, KDST_LOW32 = 4 /* low cbits bits as u32 */ };
 
 struct KeySrc {
@@ -93,6 +96,11 @@ __device__ __forceinline__ void store_pay(const PayDst &d, int64_t i, uint32_t v
   else if (d.mode == PDST_I64) reinterpret_cast<int64_t *>(d.p)[i] = (int64_t)v;
   else if (d.mode == PDST_U16) reinterpret_cast<uint16_t *>(d.p)[i] = (uint16_t)v;
   else if (d.mode == PDST_U8) reinterpret_cast<uint8_t *>(d.p)[i] = (uint8_t)v;
+}
+__device__ __forceinline__ void store_pay(const PayDst &d, int64_t i, uint32_t v, unsigned digit) {
+  if (d.mode == PDST_I64_BY_DIGIT) reinterpret_cast<int64_t *const *>(d.p)[digit][i] = (int64_t)v;
+  else if (d.mode == PDST_U32_BY_DIGIT) reinterpret_cast<uint32_t *const *>(d.p)[digit][i] = v;
+  else store_pay(d, i, v);
 }
 template <typename KeyT>
 __device__ __forceinline__ void store_key(const KeyDst &d, int64_t i, KeyT k) {
@@ -510,7 +518,7 @@ rs_pass_kernel(KeySrc ksrc, PaySrcN<NPAY> psrc, KeyDst kdst, PayDstN<NPAY> pdst,
           const int64_t dst = (int64_t)(uint32_t)(sm.gbase[d] + (uint32_t)j);
           store_key<KeyT>(kdst, dst, kk);
 #pragma unroll
-          for (int p = 0; p < NPAY; ++p) store_pay(pdst.d[p], dst, sm.pay[p][j]);
+          for (int p = 0; p < NPAY; ++p) store_pay(pdst.d[p], dst, sm.pay[p][j], d);
         }
       }
     }

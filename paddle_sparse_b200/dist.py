@@ -110,10 +110,54 @@ class _PeerBuffers:
         self.peer_row = [self.h_row.get_buffer(g, (capacity,), torch.int64) for g in range(G)]
         self.peer_col = [self.h_col.get_buffer(g, (capacity,), torch.int64) for g in range(G)]
         self.peer_val = [self.h_val.get_buffer(g, (max(capacity * value_row_bytes, 1),), torch.uint8) for g in range(G)]
+        # the same base addresses as device tables, for the kernel that scatters straight into the peers' buffers
+
+        def table(bufs):
+            return torch.tensor([b.data_ptr() for b in bufs], dtype=torch.int64, device=device)
+        self.tab_row, self.tab_col, self.tab_val = table(self.peer_row), table(self.peer_col), table(self.peer_val)
 
 
 _peer_buffers = {}       # group -> _PeerBuffers
 _peer_unavailable = []   # non-empty once symmetric memory failed to come up: the reason, and NCCL from then on
+
+
+def _peer_plan(counts: torch.Tensor, value, device, group):
+    """Counts of every (source, destination) pair on the host (one all-gather, one sync) and receive buffers large
+    enough for this step.  Returns (c[src][dst], buffers, value bytes per entry)."""
+    G = dist.get_world_size(group)
+    mine = counts.to(torch.int64)
+    table = torch.empty(G * G, dtype=torch.int64, device=mine.device)
+    dist.all_gather_into_tensor(table, mine, group=group)
+    c = table.view(G, G).cpu()
+    need = int(c.sum(0).max())
+    vb = 0 if value is None else value.element_size() * int(torch.Size(value.shape[1:]).numel())
+    buf = _peer_buffers.get(group)
+    if buf is None or buf.capacity < need or buf.value_row_bytes < vb:
+        cap = max(int(need * 1.125) + 1024, 0 if buf is None else buf.capacity)
+        buf = _peer_buffers[group] = _PeerBuffers(group, cap, max(vb, 0 if buf is None else buf.value_row_bytes), device)
+    return c, buf, vb
+
+
+def partition_exchange_fused(row, col, value, splitters: torch.Tensor, group=None):
+    """Steps 3 + 4 as ONE kernel over peer memory: the stable counting pass on the destination id stores each
+    destination's run directly into that rank's symmetric receive buffer, so the tuples cross NVLink tile by tile
+    while the pass is still ranking the next tile - nothing is staged locally and nothing is copied afterwards.
+    Values: absent or 4 bytes per entry.  Same result and validity rule as exchange_peer."""
+    from . import ops
+    G, me = dist.get_world_size(group), dist.get_rank(group)
+    dest, counts = ops.dist_dest(row, splitters)
+    c, buf, vb = _peer_plan(counts, value, row.device, group)
+    recv_base = torch.cumsum(c, 0) - c  # recv_base[src][dst]: where src's tuples start in dst's buffer
+    bases = recv_base[me].to(row.device)
+    n_recv = int(c[:, me].sum())
+    buf.h_row.barrier()  # every rank has consumed what the previous exchange left in its buffers
+    ops.dist_scatter_peer(dest, row, col, value, bases, buf.tab_row, buf.tab_col, None if value is None else buf.tab_val)
+    buf.h_row.barrier()  # every rank's pass has finished writing into my buffers
+    r_val = None
+    if value is not None:
+        r_val = buf.val[:n_recv * vb].view(value.dtype).reshape((n_recv,) + tuple(value.shape[1:]))
+    sent = int(c[me].sum()) - int(c[me][me])
+    return buf.row[:n_recv], buf.col[:n_recv], r_val, sent, n_recv
 
 
 def exchange_peer(row, col, value, counts: torch.Tensor, group=None):
@@ -121,20 +165,10 @@ def exchange_peer(row, col, value, counts: torch.Tensor, group=None):
     kept).  The returned row / col / value are views of this rank's symmetric receive buffers: they stay valid until
     the next exchange on the same group (build_partitioned consumes them at once)."""
     G, me = dist.get_world_size(group), dist.get_rank(group)
-    mine = counts.to(torch.int64)
-    table = torch.empty(G * G, dtype=torch.int64, device=mine.device)
-    dist.all_gather_into_tensor(table, mine, group=group)
-    c = table.view(G, G).cpu()                      # c[src][dst]; the one host sync of the exchange
+    c, buf, vb = _peer_plan(counts, value, row.device, group)  # c[src][dst]; the one host sync of the exchange
     send_off = torch.cumsum(c[me], 0) - c[me]       # where each destination's tuples start in my partitioned arrays
     recv_base = torch.cumsum(c, 0) - c              # recv_base[src][dst]: where src's tuples start in dst's buffer
     n_recv = int(c[:, me].sum())
-    need = int(c.sum(0).max())
-    vb = 0 if value is None else value.element_size() * int(torch.Size(value.shape[1:]).numel())
-    buf = _peer_buffers.get(group)
-    if buf is None or buf.capacity < need or buf.value_row_bytes < vb:
-        cap = max(int(need * 1.125) + 1024, 0 if buf is None else buf.capacity)
-        buf = _peer_buffers[group] = _PeerBuffers(group, cap, max(vb, 0 if buf is None else buf.value_row_bytes),
-                                                  row.device)
     vbytes = None if value is None else value.contiguous().view(torch.uint8).reshape(-1)
     buf.h_row.barrier()  # every rank has consumed what the previous exchange left in its buffers
     for k in range(G):
@@ -158,7 +192,7 @@ def _exchange_auto(row, col, value, counts, group):
     """Peer-memory exchange on CUDA tensors across several ranks; NCCL / gloo all_to_all_single otherwise, and from
     then on if symmetric memory cannot be set up on this machine."""
     if row.is_cuda and dist.get_world_size(group) > 1 and not _peer_unavailable and \
-            os.environ.get("PS_DIST_EXCHANGE", "peer") == "peer":
+            os.environ.get("PS_DIST_EXCHANGE", "fused") in ("peer", "fused"):
         try:
             return exchange_peer(row, col, value, counts, group)
         except (RuntimeError, ImportError, AttributeError) as e:  # no P2P / no symmetric memory on this box
@@ -180,6 +214,14 @@ def route_tuples(row, col, value, sparse_sizes, group=None, _ops=None):
     hist = _ops.dist_row_histogram(row, shift, buckets)
     dist.all_reduce(hist, op=dist.ReduceOp.SUM, group=group)
     splitters = choose_splitters(hist, G, shift, M)
+    mode = os.environ.get("PS_DIST_EXCHANGE", "fused")
+    narrow = value is None or value.element_size() * int(torch.Size(value.shape[1:]).numel()) == 4
+    if row.is_cuda and G > 1 and narrow and mode == "fused" and not _peer_unavailable:
+        try:
+            r_row, r_col, r_val, sent, n_recv = partition_exchange_fused(row, col, value, splitters.to(row.device), group)
+            return r_row, r_col, r_val, splitters, sent, n_recv
+        except (ImportError, AttributeError) as e:  # no symmetric memory in this torch build
+            _peer_unavailable.append(repr(e))
     p_row, p_col, p_val, counts = _ops.dist_partition(row, col, value, splitters.to(row.device))
     r_row, r_col, r_val, sent, n_recv, _ = _exchange_auto(p_row, p_col, p_val, counts, group)
     return r_row, r_col, r_val, splitters, sent, n_recv

@@ -540,6 +540,31 @@ def dist_partition(row, col, value, splitters: torch.Tensor):
     return out_row, out_col, out_value, counts
 
 
+def dist_dest(row: torch.Tensor, splitters: torch.Tensor):
+    """Destination rank of every tuple (uint32 stored as int32 bits) and the per-destination counts (device)."""
+    row, splitters = _idx(row, "row"), _idx(splitters, "splitters")
+    G = splitters.numel() - 1
+    dest = torch.empty(row.numel(), dtype=torch.int32, device=row.device)
+    counts = _new(row, G)
+    with torch.cuda.device(row.device):
+        _lib.call("ps_dist_dest", _p(row), row.numel(), _p(splitters), G, _p(dest), _p(counts), _stream(row))
+    return dest, counts
+
+
+def dist_scatter_peer(dest, row, col, value, bases: torch.Tensor, peer_row: torch.Tensor, peer_col: torch.Tensor,
+                      peer_value: Optional[torch.Tensor]) -> None:
+    """The stable partition pass writing destination d's run at element bases[d] of the d-th buffer whose base
+    address peer_row / peer_col / peer_value (int64 device tensors of addresses) hold: partition and exchange in
+    one kernel over peer memory."""
+    row, col = _idx(row, "row"), _idx(col, "col")
+    value = None if value is None else _dev(value, "value")
+    G = bases.numel()
+    with torch.cuda.device(row.device):
+        _lib.call("ps_dist_scatter_peer", _p(dest), _p(row), _p(col), _p(value),
+                  0 if value is None else value.element_size() * max(_width(value), 1), row.numel(), G, _p(bases),
+                  _p(peer_row), _p(peer_col), _p(peer_value), _stream(row))
+
+
 def add_scalar(x: torch.Tensor, delta: int) -> torch.Tensor:
     x = _idx(x, "x")
     out = torch.empty_like(x)

@@ -34,7 +34,9 @@ def _worker(rank, world, port, M, N, per_rank, out, exchange="peer"):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("exchange", ["peer", "nccl"])  # peer-memory copies (default) / all_to_all_single (fall-back)
+# fused = the partition pass stores into the peers' buffers (default); peer = partition, then device-to-device copies
+# into them; nccl = partition, then all_to_all_single (the fall-back)
+@pytest.mark.parametrize("exchange", ["fused", "peer", "nccl"])
 @pytest.mark.parametrize("world", [2])
 def test_partitioned_build_matches_single_gpu(cuda, world, exchange):
     if torch.cuda.device_count() < world:
@@ -47,7 +49,7 @@ def test_partitioned_build_matches_single_gpu(cuda, world, exchange):
     out = mp.Manager().dict()
     mp.spawn(_worker, args=(world, port, M, N, per_rank, out, exchange), nprocs=world, join=True)
     res = [out[r] for r in range(world)]
-    assert all(r["peer"] == (exchange == "peer") for r in res)  # the path that was asked for is the one that ran
+    assert all(r["peer"] == (exchange != "nccl") for r in res)  # the path that was asked for is the one that ran
     src = [np.concatenate([res[r]["src"][k] for r in range(world)]) for k in range(3)]
     idx, val = np_ref.coalesce(np.stack([src[0], src[1]]), src[2].astype(np.float64), M, N, "add")
     assert res[0]["r0"] == 0 and res[-1]["r1"] == M
@@ -67,6 +69,7 @@ def test_partitioned_build_matches_single_gpu(cuda, world, exchange):
 
 def _second_exchange_worker(rank, world, port, M, N, per_rank, out):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    os.environ.pop("PS_DIST_EXCHANGE", None)
     torch.cuda.set_device(rank)
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
     try:
