@@ -201,6 +201,14 @@ int ps_mask_to_index(const uint8_t *mask, int64_t n, int64_t *out_idx, int64_t *
  * (mask[index[e]]) compacted to entry ids.  index nullable (then mask[e]).  Synchronises. */
 int ps_mask_entries(const uint8_t *mask, const int64_t *index, int64_t nnz, int64_t *out_idx,
                     int64_t *host_count, void *stream);
+/* narrow.py:53-62 `narrow(dim=1)`: keep the entries with lo <= col[e] < hi, in order, as
+ * (row[e], col[e] - lo, value[e]) -- the reference builds a boolean mask, selects three
+ * times and subtracts; here one compaction writes row / col and the value rows follow by one
+ * gather.  Outputs sized nnz; value / out_value nullable (row_bytes = bytes per value row).
+ * *host_count = entries kept.  Synchronises. */
+int ps_narrow_cols(const int64_t *row, const int64_t *col, const void *value, int64_t row_bytes,
+                   int64_t nnz, int64_t lo, int64_t hi, int64_t *out_row, int64_t *out_col,
+                   void *out_value, int64_t *host_count, void *stream);
 /* index_select.py:17-33 (dim 0) and :53-67 (dim 1, on the CSC arrays): given the new
  * pointer out_ptr[K+1] (ps_count2ptr of the old counts at idx) write, for every output
  * entry e of new row r: out_major[e] = r, out_perm[e] = old_ptr[idx[r]] + e - out_ptr[r],

@@ -641,6 +641,100 @@ def cat(tensors, dim):
     return SparseTensor.from_storage(storage)
 
 
+# =========================================================================== narrow.py / select.py
+def narrow(src: SparseTensor, dim: int, start: int, length: int) -> SparseTensor:
+    """narrow.py:11-100.  No reference test exercises it (parity unpinned): this restatement follows the source
+    line by line and is cross-checked against index_select over an arange, which the golden vectors do pin."""
+    if dim < 0:
+        dim = src.dim() + dim
+    if start < 0:
+        start = src.size(dim) + start
+    st = src.storage
+    if dim == 0:  # narrow.py:18-51
+        rowptr, col, value = src.csr()
+        rowptr = rowptr[start:start + length + 1]
+        row_start = int(rowptr[0])
+        rowptr = rowptr - row_start
+        row_length = int(rowptr[-1])
+        row = st._row
+        if row is not None:
+            row = row[row_start:row_start + row_length] - start
+        col = col[row_start:row_start + row_length].copy()
+        if value is not None:
+            value = value[row_start:row_start + row_length].copy()
+        rowcount = st._rowcount
+        if rowcount is not None:
+            rowcount = rowcount[start:start + length].copy()
+        storage = SparseStorage(row=row, rowptr=rowptr, col=col, value=value,
+                                sparse_sizes=(length, src.sparse_size(1)), rowcount=rowcount, is_sorted=True)
+        return SparseTensor.from_storage(storage)
+    if dim == 1:  # narrow.py:53-92
+        row, col, value = src.coo()
+        mask = (col >= start) & (col < start + length)
+        row = row[mask]
+        col = col[mask] - start
+        if value is not None:
+            value = value[mask]
+        colptr = st._colptr
+        if colptr is not None:
+            colptr = colptr[start:start + length + 1]
+            colptr = colptr - colptr[0]
+        colcount = st._colcount
+        if colcount is not None:
+            colcount = colcount[start:start + length].copy()
+        storage = SparseStorage(row=row, rowptr=None, col=col, value=value,
+                                sparse_sizes=(src.sparse_size(0), length), colptr=colptr, colcount=colcount,
+                                is_sorted=True)
+        return SparseTensor.from_storage(storage)
+    value = st.value()  # narrow.py:94-100
+    if value is None:
+        raise ValueError
+    index = [slice(None)] * value.ndim
+    index[dim - 1] = slice(start, start + length)
+    return src.set_value(value[tuple(index)].copy(), layout="coo")
+
+
+def narrow_diag(src: SparseTensor, start, length) -> SparseTensor:
+    """`__narrow_diag__`, narrow.py:103-168: the inverse of cat_diag."""
+    st = src.storage
+    rowptr, col, value = src.csr()
+    rowptr = rowptr[start[0]:start[0] + length[0] + 1]
+    row_start = int(rowptr[0])
+    rowptr = rowptr - row_start
+    row_length = int(rowptr[-1])
+    sl = slice(row_start, row_start + row_length)
+    row = st._row
+    if row is not None:
+        row = row[sl] - start[0]
+    col = col[sl] - start[1]
+    if value is not None:
+        value = value[sl].copy()
+    rowcount = st._rowcount
+    if rowcount is not None:
+        rowcount = rowcount[start[0]:start[0] + length[0]].copy()
+    colptr = st._colptr
+    if colptr is not None:
+        colptr = colptr[start[1]:start[1] + length[1] + 1]
+        colptr = colptr - int(colptr[0])
+    colcount = st._colcount
+    if colcount is not None:
+        colcount = colcount[start[1]:start[1] + length[1]].copy()
+    csr2csc = st._csr2csc
+    if csr2csc is not None:
+        csr2csc = csr2csc[sl] - row_start
+    csc2csr = st._csc2csr
+    if csc2csr is not None:
+        csc2csr = csc2csr[sl] - row_start
+    storage = SparseStorage(row=row, rowptr=rowptr, col=col, value=value, sparse_sizes=tuple(length),
+                            rowcount=rowcount, colptr=colptr, colcount=colcount, csr2csc=csr2csc, csc2csr=csc2csr,
+                            is_sorted=True)
+    return SparseTensor.from_storage(storage)
+
+
+def select(src: SparseTensor, dim: int, idx: int) -> SparseTensor:  # select.py:7-8
+    return narrow(src, dim, start=idx, length=1)
+
+
 # =========================================================================== index_select.py
 def index_select(src: SparseTensor, dim: int, idx: np.ndarray) -> SparseTensor:
     """index_select.py:13-96."""

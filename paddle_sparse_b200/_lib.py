@@ -61,6 +61,7 @@ SIGNATURES = {
     "ps_coo_match": [c_ptr, c_ptr, c_i64, c_ptr, c_ptr, c_i64, c_ptr, c_ptr, c_ptr],
     "ps_mask_to_index": [c_ptr, c_i64, c_ptr, c_ptr, c_ptr],
     "ps_mask_entries": [c_ptr, c_ptr, c_i64, c_ptr, c_ptr, c_ptr],
+    "ps_narrow_cols": [c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_i64, c_i64, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr],
     "ps_index_select_fill": [c_ptr, c_ptr, c_ptr, c_i64, c_ptr, c_i64, c_ptr, c_i64, c_ptr, c_ptr, c_ptr, c_ptr,
                              c_ptr],
     "ps_sample_adj_bound": [c_ptr, c_ptr, c_i64, c_i64, c_int, c_ptr, c_ptr],

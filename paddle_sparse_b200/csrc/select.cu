@@ -13,10 +13,18 @@
 
 namespace ps {
 
+// Column-range selection of `narrow(dim=1)` rides on the compaction kernel: mask == nullptr switches the
+// predicate to lo <= index[i] < hi and the kept (row, col - lo) pairs are written next to the entry ids.
+struct RangeSelect {
+  int64_t lo, hi;
+  const int64_t *row;
+  int64_t *out_row, *out_col;
+};
+
 template <int THREADS, int ITEMS>
 __global__ void __launch_bounds__(THREADS)
 compact_kernel(const uint8_t *__restrict__ mask, const int64_t *__restrict__ index, int64_t n,
-               int64_t *__restrict__ out_idx, uint64_t *state, long long *d_count) {
+               int64_t *__restrict__ out_idx, uint64_t *state, long long *d_count, RangeSelect range) {
   constexpr int TILE = THREADS * ITEMS;
   __shared__ int64_t warp_sums[33];
   __shared__ int64_t s_tile, s_excl;
@@ -30,7 +38,14 @@ compact_kernel(const uint8_t *__restrict__ mask, const int64_t *__restrict__ ind
   for (int k = 0; k < ITEMS; ++k) {
     const int64_t i = base + k;
     bool f = false;
-    if (i < n) f = mask[index ? index[i] : i] != 0;
+    if (i < n) {
+      if (mask) {
+        f = mask[index ? index[i] : i] != 0;
+      } else {  // narrow.py:56-57: lo <= col < hi
+        const int64_t c = index[i];
+        f = c >= range.lo && c < range.hi;
+      }
+    }
     flags |= (unsigned)f << k;
     cnt += f;
   }
@@ -43,13 +58,25 @@ compact_kernel(const uint8_t *__restrict__ mask, const int64_t *__restrict__ ind
   __syncthreads();
   excl += s_excl;
   if ((tile + 1) * (int64_t)TILE >= n && threadIdx.x == 0) *d_count = (long long)(s_excl + total);
+  if (mask) {
 #pragma unroll
-  for (int k = 0; k < ITEMS; ++k)
-    if ((flags >> k) & 1u) out_idx[excl++] = base + k;
+    for (int k = 0; k < ITEMS; ++k)
+      if ((flags >> k) & 1u) out_idx[excl++] = base + k;
+  } else {  // the kept entries' (row, col - lo) go out with their ids (narrow.py:59-60)
+#pragma unroll
+    for (int k = 0; k < ITEMS; ++k)
+      if ((flags >> k) & 1u) {
+        const int64_t i = base + k;
+        if (out_idx) out_idx[excl] = i;
+        range.out_row[excl] = range.row[i];
+        range.out_col[excl] = index[i] - range.lo;
+        ++excl;
+      }
+  }
 }
 
 static int compact_launch(const uint8_t *mask, const int64_t *index, int64_t n, int64_t *out_idx, int64_t *host_count,
-                          cudaStream_t s) {
+                          cudaStream_t s, RangeSelect range = RangeSelect{0, 0, nullptr, nullptr, nullptr}) {
   *host_count = 0;
   if (n == 0) return PS_OK;
   constexpr int THREADS = 256, ITEMS = 8;
@@ -58,7 +85,7 @@ static int compact_launch(const uint8_t *mask, const int64_t *index, int64_t n, 
   PS_SCRATCH(state, scratch, uint64_t, tiles + 2);
   PS_CUDA(cudaMemsetAsync(state, 0, sizeof(uint64_t) * (size_t)(tiles + 2), s));
   long long *d_count = reinterpret_cast<long long *>(state + tiles + 1);
-  compact_kernel<THREADS, ITEMS><<<(unsigned)tiles, THREADS, 0, s>>>(mask, index, n, out_idx, state, d_count);
+  compact_kernel<THREADS, ITEMS><<<(unsigned)tiles, THREADS, 0, s>>>(mask, index, n, out_idx, state, d_count, range);
   PS_LAUNCH_OK();
   long long h = 0;
   PS_TRY(read_back(&h, d_count, sizeof(h), s));
@@ -103,6 +130,21 @@ int ps_mask_entries(const uint8_t *mask, const int64_t *index, int64_t nnz, int6
                     void *stream) {
   PS_CHECK(nnz >= 0 && host_count, "mask_entries: bad arguments");
   return compact_launch(mask, index, nnz, out_idx, host_count, (cudaStream_t)stream);
+}
+
+int ps_narrow_cols(const int64_t *row, const int64_t *col, const void *value, int64_t row_bytes, int64_t nnz,
+                   int64_t lo, int64_t hi, int64_t *out_row, int64_t *out_col, void *out_value, int64_t *host_count,
+                   void *stream) {
+  PS_CHECK(nnz >= 0 && row_bytes >= 0 && host_count && lo <= hi, "narrow_cols: bad arguments");
+  *host_count = 0;
+  if (nnz == 0) return PS_OK;
+  cudaStream_t s = (cudaStream_t)stream;
+  Scratch scratch(s);
+  PS_SCRATCH(ids_buf, scratch, int64_t, value ? nnz : 1);
+  int64_t *ids = value ? ids_buf : nullptr;
+  PS_TRY(compact_launch(nullptr, col, nnz, ids, host_count, s, RangeSelect{lo, hi, row, out_row, out_col}));
+  if (value && *host_count > 0) PS_TRY(gather_rows_launch<int64_t>(value, row_bytes, ids, *host_count, out_value, s));
+  return PS_OK;
 }
 
 int ps_index_select_fill(const int64_t *old_ptr, const int64_t *minor, const void *value, int64_t row_bytes,

@@ -499,6 +499,27 @@ def mask_entries(mask: torch.Tensor, index: Optional[torch.Tensor], nnz: int) ->
     return out[: int(h[0])]
 
 
+def slice_add(x: torch.Tensor, start: int, length: int, delta: int = 0) -> torch.Tensor:
+    """x[start:start+length] + delta as a fresh tensor (the `paddle.slice(...) - offset` pairs of narrow.py)."""
+    return concat_add([_idx(x, "x")[start:start + length]], [delta])
+
+
+def narrow_cols(row: torch.Tensor, col: torch.Tensor, value: Optional[torch.Tensor], start: int, length: int):
+    """narrow.py:53-62: the entries with start <= col < start+length as (row, col - start, value), order kept."""
+    row, col = _idx(row, "row"), _idx(col, "col")
+    value = None if value is None else _dev(value, "value")
+    nnz = col.numel()
+    out_row, out_col = _new(col, nnz), _new(col, nnz)
+    out_value = None if value is None else torch.empty_like(value)
+    h = _host_i64()
+    with torch.cuda.device(col.device):
+        _lib.call("ps_narrow_cols", _p(row), _p(col), _p(value),
+                  0 if value is None else value.element_size() * max(_width(value), 1), nnz, int(start),
+                  int(start) + int(length), _p(out_row), _p(out_col), _p(out_value), h, _stream(col))
+    k = int(h[0])
+    return out_row[:k], out_col[:k], None if out_value is None else out_value[:k]
+
+
 def index_select_fill(old_ptr, minor, value, idx, out_ptr, E: int, want_perm: bool = False):
     """index_select.py:17-33 / 53-67 in one launch.  Returns (major, minor', value', perm|None)."""
     old_ptr, minor, idx, out_ptr = _idx(old_ptr), _idx(minor), _idx(idx), _idx(out_ptr)

@@ -613,6 +613,139 @@ def test_cat_matches_oracle(ps, dim, cached, with_value):
     assert np.array_equal(host(got.storage.csr2csc()), fresh.storage.csr2csc())
 
 
+# ----------------------------------------------------------------------------- narrow / __narrow_diag__ / select
+_STRUCTS = ("_row", "_rowptr", "_rowcount", "_colptr", "_colcount", "_csr2csc", "_csc2csr")
+
+
+def _same_structs(got, want):
+    assert tuple(got.sparse_sizes()) == tuple(want.sparse_sizes())
+    assert sorted(got.storage.cached_keys()) == sorted(want.storage.cached_keys())
+    for g_, w_ in zip(got.coo(), want.coo()):
+        assert (g_ is None) == (w_ is None)
+        if g_ is not None:
+            assert np.array_equal(host(g_), w_)
+    for key in _STRUCTS:
+        w_, g_ = getattr(want.storage, key), getattr(got.storage, key)
+        if key in ("_row", "_rowptr"):  # either may be derived lazily on our side; when held it must agree
+            if g_ is not None and w_ is not None:
+                assert np.array_equal(host(g_), w_), key
+            continue
+        assert (g_ is None) == (w_ is None), key
+        if w_ is not None:
+            assert np.array_equal(host(g_), w_), key
+
+
+@pytest.mark.parametrize("cached", [True, False])
+@pytest.mark.parametrize("with_value", [True, False])
+def test_narrow_matches_oracle(ps, cached, with_value):
+    """narrow.py:11-100 against its restatement: indices, values, sizes and which caches survive, for interior,
+    full, single, empty and negative-start ranges on both sparse dimensions, and a value dimension."""
+    rng = np.random.default_rng(77)
+    M, N = 4000, 3100
+    row, col, val = _pair(rng, M, N, 90000, width=3)
+    A = ps.SparseTensor(row=dev(row), col=dev(col), value=dev(val) if with_value else None, sparse_sizes=(M, N))
+    O = np_ref.SparseTensor(row=row, col=col, value=val if with_value else None, sparse_sizes=(M, N))
+    if cached:
+        A.fill_cache_()
+        O.fill_cache_()
+    for dim, start, length in ((0, 700, 2100), (0, 0, M), (0, M - 1, 1), (0, 1234, 0), (0, -50, 20),
+                               (1, 500, 1700), (1, 0, N), (1, N - 1, 1), (1, 77, 0), (-2 if not with_value else -3, 5, 9)):
+        got, want = A.narrow(dim, start, length), np_ref.narrow(O, dim, start, length)
+        _same_structs(got, want)
+        # what was carried over is what a fresh build computes
+        fresh = np_ref.SparseTensor(row=want.coo()[0], col=want.coo()[1], sparse_sizes=want.sparse_sizes()).fill_cache_()
+        assert np.array_equal(host(got.storage.rowptr()), fresh.storage.rowptr())
+        assert np.array_equal(host(got.storage.colptr()), fresh.storage.colptr())
+        assert np.array_equal(host(got.storage.csr2csc()), fresh.storage.csr2csc())
+    if with_value:
+        got, want = A.narrow(2, 1, 2), np_ref.narrow(O, 2, 1, 2)
+        assert np.array_equal(host(got.storage.value()), want.storage.value())
+        got = ps.select(A, 0, 17)
+        _same_structs(got, np_ref.select(O, 0, 17))
+        # slicing through __getitem__ goes the same way (tensor.py:704-786)
+        _same_structs(A[100:300, 40:900], np_ref.narrow(np_ref.narrow(O, 0, 100, 200), 1, 40, 860))
+    else:
+        with pytest.raises(ValueError):
+            A.narrow(2, 0, 1)
+    with pytest.raises(ValueError):
+        A.narrow(0, M - 3, 10)
+
+
+def test_narrow_owns_its_memory(ps):
+    """The reference's `paddle.slice` results are copies: an in-place multiply on a slice must not reach the source."""
+    rng = np.random.default_rng(3)
+    row, col, val = _pair(rng, 500, 400, 6000)
+    A = ps.SparseTensor(row=dev(row), col=dev(col), value=dev(val), sparse_sizes=(500, 400)).fill_cache_()
+    before = host(A.storage.value()).copy()
+    for B in (A.narrow(0, 100, 200), A.narrow(1, 30, 300), A.__narrow_diag__((0, 0), (500, 400))):
+        B.storage.value().mul_(0)
+        B.storage.col().add_(1)
+        B.storage.rowptr().add_(1)
+    assert np.array_equal(host(A.storage.value()), before)
+    assert np.array_equal(host(A.storage.col()), col)
+    assert int(A.storage.rowptr()[0]) == 0
+
+
+@pytest.mark.parametrize("cached", ["all", "first-only", "none"])
+def test_narrow_diag_inverts_cat_diag(ps, cached):
+    """narrow.py:103-168: blocks of a diagonal stack come back with every structure the stack carried, equal to the
+    operands' own (golden operands of test/test_cat.py first, then four random blocks, one of them empty)."""
+    g = G.CAT
+    m1 = ps.SparseTensor(row=dev(np.array(g["row1"], I64)), col=dev(np.array(g["col1"], I64))).fill_cache_()
+    m2 = ps.SparseTensor(row=dev(np.array(g["row2"], I64)), col=dev(np.array(g["col2"], I64))).fill_cache_()
+    both = ps.cat([m1, m2], dim=(0, 1))
+    for m, start in ((m1, (0, 0)), (m2, tuple(m1.sparse_sizes()))):
+        back = both.__narrow_diag__(start, tuple(m.sparse_sizes()))
+        assert back.to_dense().tolist() == m.to_dense().tolist()
+        assert back.storage.num_cached_keys() == 5
+        for key in _STRUCTS:
+            assert torch.equal(getattr(back.storage, key), getattr(m.storage, key)), key
+
+    rng = np.random.default_rng(91)
+    shapes = [(900, 700, 20000), (40, 60, 0), (1500, 1100, 50000), (3, 5, 7)]
+    gs, os_ = [], []
+    for k, (M, N, nnz) in enumerate(shapes):
+        row, col, val = _pair(rng, M, N, max(nnz, 1), width=2)
+        if nnz == 0:
+            row, col, val = row[:0], col[:0], val[:0]
+        A = ps.SparseTensor(row=dev(row), col=dev(col), value=dev(val), sparse_sizes=(M, N))
+        O = np_ref.SparseTensor(row=row, col=col, value=val, sparse_sizes=(M, N))
+        if cached == "all" or (cached == "first-only" and k == 0):
+            A.fill_cache_()
+            O.fill_cache_()
+        gs.append(A)
+        os_.append(O)
+    stack, ostack = ps.cat(gs, (0, 1)), np_ref.cat(os_, (0, 1))
+    r0 = c0 = 0
+    for A, O in zip(gs, os_):
+        size = tuple(O.sparse_sizes())
+        got, want = stack.__narrow_diag__((r0, c0), size), np_ref.narrow_diag(ostack, (r0, c0), size)
+        _same_structs(got, want)
+        assert np.array_equal(host(got.storage.value()), O.storage.value())
+        assert np.array_equal(host(got.storage.row()), O.storage.row())
+        assert np.array_equal(host(got.storage.col()), O.storage.col())
+        r0, c0 = r0 + size[0], c0 + size[1]
+
+
+def test_narrow_cols_full_shape(ps):
+    """configs[1]-sized column range: entries kept in order, shifted, counts add up across a partition of the
+    columns (size-independent properties; the oracle would take minutes here)."""
+    M = N = 2449029
+    row, col, val = ps.ops.synth_coo(0x5eed0001, 0, 20_000_000, M, N, "cuda")
+    A = ps.SparseTensor(row=row, col=col, value=val, sparse_sizes=(M, N)).coalesce()
+    total, mass = 0, 0.0
+    for start, length in ((0, 1_000_000), (1_000_000, 449_029), (1_449_029, 1_000_000)):
+        B = A.narrow(1, start, length)
+        r, c, v = B.coo()
+        total += B.nnz()
+        mass += float(v.double().sum())
+        assert int(c.min()) >= 0 and int(c.max()) < length
+        key = r * length + c
+        assert bool((key[1:] > key[:-1]).all())
+    assert total == A.nnz()
+    assert abs(mass - float(A.storage.value().double().sum())) <= 1e-9 * mass
+
+
 # ----------------------------------------------------------------------------- index_select / masked_select
 def test_permute_golden(ps):
     g = G.PERMUTE

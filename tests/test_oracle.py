@@ -246,6 +246,46 @@ def test_cat_golden():
     assert out.storage.num_cached_keys() == g["value_cat_cached"]
 
 
+def test_narrow_restatement():
+    """narrow.py has no reference test.  The restatement is anchored two ways: `__narrow_diag__` undoes the
+    diagonal concatenation of test/test_cat.py:11-66 (operands and every cached structure come back), and a
+    row / column range equals index_select over an arange, which test/test_permute.py pins."""
+    g = G.CAT
+    m1 = np_ref.SparseTensor(row=a(g["row1"]), col=a(g["col1"])).fill_cache_()
+    m2 = np_ref.SparseTensor(row=a(g["row2"]), col=a(g["col2"])).fill_cache_()
+    both = np_ref.cat([m1, m2], (0, 1))
+    assert both.to_dense().tolist() == g["diag"]
+    starts = [(0, 0), tuple(m1.sparse_sizes())]
+    for m, start in zip((m1, m2), starts):
+        back = np_ref.narrow_diag(both, start, tuple(m.sparse_sizes()))
+        assert back.to_dense().tolist() == m.to_dense().tolist()
+        assert back.storage.num_cached_keys() == 5
+        for key in ("_row", "_rowptr", "_col", "_rowcount", "_colptr", "_colcount", "_csr2csc", "_csc2csr"):
+            assert np.array_equal(getattr(back.storage, key), getattr(m.storage, key)), key
+    rng = np.random.default_rng(5)
+    M, N = 60, 45
+    key = np.unique(rng.integers(0, M * N, 700))
+    row, col = (key // N).astype(np.int64), (key % N).astype(np.int64)
+    val = rng.random((key.size, 2)).astype(np.float32)
+    A = np_ref.SparseTensor(row=row, col=col, value=val, sparse_sizes=(M, N)).fill_cache_()
+    dense = A.to_dense()
+    for dim, start, length in ((0, 7, 20), (0, 0, M), (0, 59, 1), (0, 13, 0), (1, 5, 30), (1, 44, 1), (1, 9, 0),
+                               (0, -10, 4), (1, -45, 45)):
+        out = np_ref.narrow(A, dim, start, length)
+        s0 = start + (M, N)[dim] if start < 0 else start
+        via = np_ref.index_select(A, dim, np.arange(s0, s0 + length, dtype=np.int64))
+        for x, y in zip(out.coo(), via.coo()):
+            assert np.array_equal(x, y)
+        assert out.to_dense().tolist() == (dense[s0:s0 + length] if dim == 0 else dense[:, s0:s0 + length]).tolist()
+        kept = {"rowcount"} if dim == 0 else {"colptr", "colcount"}
+        assert set(out.storage.cached_keys()) == kept
+        fresh = np_ref.SparseTensor(row=out.coo()[0], col=out.coo()[1], sparse_sizes=out.sparse_sizes()).fill_cache_()
+        for k in kept:
+            assert np.array_equal(getattr(out.storage, "_" + k), getattr(fresh.storage, "_" + k)), k
+    assert np.array_equal(np_ref.narrow(A, 2, 1, 1).storage.value(), val[:, 1:2])
+    assert np_ref.select(A, 0, 3).to_dense().tolist() == dense[3:4].tolist()
+
+
 def test_paddle_scatter_restatement():
     src = a([1, 2, 3, 4, 5, 6], np.float32)
     ptr = a([0, 2, 2, 5, 6])
