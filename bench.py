@@ -10,7 +10,8 @@ API:   SparseTensor(row, col, value, sparse_sizes)   (validation; sort-on-constr
        .t()                                           (takes the transposed arrays the CSC sort carried)
 N = 1 : BASELINE.json configs[1] — ogbn-products shape, 2,449,029 nodes, 61,859,140 nnz, fp32.
 N > 1 : the row-range-partitioned build (configs[4] shape, papers100M: 111,059,956 nodes,
-        201,960,734 nnz per GPU = 1.6157 B nnz at N = 8), weak scaling, one NCCL all-to-all.
+        201,960,734 nnz per GPU = 1.6157 B nnz at N = 8), weak scaling, one all-to-all-v (over peer memory, fused
+        with the partition pass; NCCL all_to_all_single is the fall-back).
 `value` = inputs resident in HBM.  `e2e` = the same step from pinned HOST buffers (H2D of row / col / value and D2H
 of the resulting rowptr inside the timed region, every step), run as a double-buffered loader would: the upload of
 step i+1 on a copy stream overlaps the build of step i; the strictly serial figure is reported beside it.
@@ -158,8 +159,9 @@ def workload_config(n_gpus: int):
                 "l2": "inputs (1.24 GB) and every intermediate exceed the 126 MB L2; no explicit flush"}
     c = PAPERS
     return {"workload": f"{c['name']} row-partitioned over {n_gpus} GPUs: {c['M']} nodes, {c['nnz_per_gpu']} nnz per GPU "
-                        f"({c['nnz_per_gpu'] * n_gpus} total), fp32; splitter histogram + NCCL all-to-all + local "
-                        "coalesce + CSR/CSC build per row shard",
+                        f"({c['nnz_per_gpu'] * n_gpus} total), fp32; splitter histogram + all-to-all-v of the tuples (the "
+                        "partition pass writes straight into the peers' symmetric receive buffers over NVLink; NCCL for the "
+                        "histogram all-reduce and the counts) + local coalesce + CSR/CSC build per row shard",
             "l2": "per-GPU inputs (4.0 GB) exceed the 126 MB L2; no explicit flush", "parallelism": f"row-range x{n_gpus}"}
 
 

@@ -18,6 +18,7 @@ from .add import add, add_, add_nnz, add_nnz_  # noqa: E402
 from .index_select import index_select, index_select_nnz  # noqa: E402
 from .masked_select import masked_select, masked_select_nnz  # noqa: E402
 from .narrow import narrow, select, __narrow_diag__  # noqa: E402
+from .permute import permute  # noqa: E402
 from .cat import cat  # noqa: E402
 from .convert import (to_scipy, from_scipy, to_torch_sparse, from_torch_sparse, to_paddle_sparse,  # noqa: E402
                       from_paddle_sparse)
@@ -29,6 +30,6 @@ cuda_version = int(ops.sparse_cuda_version()[0])  # paddle_sparse/__init__.py:17
 __all__ = [
     "SparseStorage", "SparseTensor", "coalesce", "t", "transpose", "sum", "mean", "min", "max", "reduction",
     "mul", "mul_", "mul_nnz", "mul_nnz_", "add", "add_", "add_nnz", "add_nnz_", "index_select", "index_select_nnz", "masked_select",
-    "masked_select_nnz", "narrow", "__narrow_diag__", "select", "cat", "to_scipy", "from_scipy", "to_torch_sparse", "from_torch_sparse",
+    "masked_select_nnz", "narrow", "__narrow_diag__", "select", "permute", "cat", "to_scipy", "from_scipy", "to_torch_sparse", "from_torch_sparse",
     "to_paddle_sparse", "from_paddle_sparse", "sample", "sample_adj", "manual_seed", "ops", "__version__",
 ]

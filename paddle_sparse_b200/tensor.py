@@ -256,6 +256,41 @@ class SparseTensor(object):
         value = self.storage.value()
         return False if value is None else value.requires_grad
 
+    def requires_grad_(self, requires_grad: bool = True, dtype=None):
+        """tensor.py:472-483."""
+        if requires_grad and not self.has_value():
+            self.fill_value_(1.0, dtype)
+        value = self.storage.value()
+        if value is not None:
+            value.requires_grad_(requires_grad)
+        return self
+
+    def to_device(self, device, non_blocking: bool = False):
+        """tensor.py:232-239 (a CPU target is refused, see `to`)."""
+        return self.to(device=device, non_blocking=non_blocking)
+
+    def device_as(self, tensor: torch.Tensor, non_blocking: bool = False):
+        """tensor.py:241-242."""
+        return self.to_device(tensor.device, non_blocking=non_blocking)
+
+    def cpu(self):
+        """tensor.py:692-693 — refused: this package holds no CPU representation (no CPU fallback)."""
+        return self.to_device(torch.device("cpu"))
+
+    def pin_memory(self):
+        """tensor.py:485-486 pins host arrays; device arrays have nothing to pin."""
+        raise RuntimeError("paddle_sparse_b200.SparseTensor is GPU-only: pin_memory() applies to host tensors")
+
+    def is_pinned(self) -> bool:
+        return False  # tensor.py:488-489 on device-resident arrays
+
+    def share_memory_(self):
+        """tensor.py:597-599 moves host arrays to shared memory; a no-op for device arrays, as in the framework."""
+        return self
+
+    def is_shared(self) -> bool:
+        return False  # tensor.py:602-603 on device-resident arrays
+
     def device(self):
         return self.storage.col().device
 
@@ -309,6 +344,18 @@ class SparseTensor(object):
     def is_floating_point(self) -> bool:
         value = self.storage.value()
         return True if value is None else value.is_floating_point()
+
+    def bool(self):
+        return self.type(torch.bool)
+
+    def byte(self):
+        return self.type(torch.uint8)
+
+    def char(self):
+        return self.type(torch.int8)
+
+    def short(self):
+        return self.type(torch.int16)
 
     def bfloat16(self):
         return self.type(torch.bfloat16)

@@ -754,6 +754,28 @@ def test_permute_golden(ps):
     out = A.index_select(0, perm).index_select(1, perm)  # permute.py:8-13
     r, c, v = out.coo()
     assert r.tolist() == g["out_row"] and c.tolist() == g["out_col"] and v.tolist() == g["out_value"]
+    r, c, v = A.permute(perm).coo()
+    assert r.tolist() == g["out_row"] and c.tolist() == g["out_col"] and v.tolist() == g["out_value"]
+    r, c, v = ps.permute(A, perm).coo()
+    assert r.tolist() == g["out_row"] and c.tolist() == g["out_col"] and v.tolist() == g["out_value"]
+
+
+def test_device_dtype_and_grad_helpers(ps):
+    """tensor.py:232-242, 472-489, 597-603, 692-693 and the dtype shorthands: same names and meaning; every CPU
+    target is refused (no CPU representation)."""
+    A = ps.SparseTensor(row=ten([0, 1, 1]), col=ten([1, 0, 2]), sparse_sizes=(2, 3))
+    assert not A.requires_grad() and not A.has_value()
+    A.requires_grad_()  # fills ones first, like the reference
+    assert A.has_value() and A.requires_grad() and A.storage.value().tolist() == [1.0, 1.0, 1.0]
+    A.requires_grad_(False)
+    assert not A.requires_grad()
+    assert A.device_as(A.storage.col()) is A and A.to_device("cuda") is A
+    for name, dtype in (("bool", torch.bool), ("byte", torch.uint8), ("char", torch.int8), ("short", torch.int16)):
+        assert getattr(A, name)().dtype() == dtype
+    assert not A.is_pinned() and not A.is_shared() and A.share_memory_() is A
+    for refuse in (A.cpu, A.pin_memory, lambda: A.to_device("cpu")):
+        with pytest.raises(RuntimeError):
+            refuse()
 
 
 @pytest.mark.parametrize("with_value", [True, False])
