@@ -246,6 +246,14 @@ __device__ __forceinline__ longlong2 ld_stream2(const int64_t *p) {  // 128-bit,
   return v;
 }
 
+// 128-bit evict-first load through the coherent path: safe on a buffer the same thread overwrites afterwards
+// (the in-place mul_ / add_), unlike the .nc forms above
+__device__ __forceinline__ uint4 ld_once(const uint4 *p) {
+  uint4 v;
+  asm volatile("ld.global.cs.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+  return v;
+}
+
 inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
 inline int bits_for(int64_t n) {  // bits needed to represent values in [0, n)
   int b = 0;

@@ -35,10 +35,13 @@ __device__ __forceinline__ int64_t warp_upper_bound(const int64_t *__restrict__ 
 // `bounds` (optional, from tile_bounds_launch): bounds[t] = first segment touching tile t, bounds[tiles] = S - 1.
 // With it a tile starts from two loads instead of two 32-ary searches of ~5 dependent loads each, which is what
 // bounds these kernels when the whole grid is resident in a few waves (the searches serialise per tile).
+// expand_tile_owned: the same resolution, but each thread keeps the segments of ITS ITEMS consecutive entries
+// (tile entries threadIdx.x * ITEMS + k) in registers and nothing is written back: kernels whose threads consume
+// exactly those entries (mul_row on 16-byte vectors) save the shared-memory round trip and one barrier.
 template <int THREADS, int ITEMS>
-__device__ __forceinline__ void expand_tile(const int64_t *__restrict__ ptr, int64_t S, int64_t e0,
-                                            int tile_n, int32_t *seg /*[TILE]*/, int32_t *aux /*[40]*/,
-                                            const int32_t *__restrict__ bounds = nullptr) {
+__device__ __forceinline__ void expand_tile_owned(const int64_t *__restrict__ ptr, int64_t S, int64_t e0,
+                                                  int tile_n, int32_t *seg /*[TILE]*/, int32_t *aux /*[40]*/,
+                                                  const int32_t *__restrict__ bounds, int32_t (&own)[ITEMS]) {
   constexpr int TILE = THREADS * ITEMS;
   const unsigned lane = lane_id(), warp = threadIdx.x >> 5;
   // first / last segment touching the tile: largest s in [0,S-1] with ptr[s] <= e
@@ -51,9 +54,36 @@ __device__ __forceinline__ void expand_tile(const int64_t *__restrict__ ptr, int
     const int64_t c = warp_upper_bound(ptr, S, e0 + tile_n - 1);
     if (lane == 0) aux[33] = (int32_t)(c > 0 ? c - 1 : 0);
   }
-  for (int j = threadIdx.x; j < TILE; j += THREADS) seg[j] = -1;
   __syncthreads();
   const int32_t s_lo = aux[32], s_hi = aux[33];
+  // Few segments start inside the tile (the usual case; always when rows are long): their clamped starts go into
+  // `seg` as a sorted table and every thread finds its first entry's segment by a binary search of that table,
+  // then walks it for the other ITEMS - 1 entries.  One barrier, no tile-wide initialisation, atomics or scan.
+  // segment of entry p = s_lo + #{s in (s_lo, s_hi] : ptr[s] - e0 <= p} (ptr is monotone; empty segments share a
+  // start and the last one wins, as below).
+  const int nseg = s_hi - s_lo;
+  if (nseg <= TILE) {  // uniform over the CTA
+    for (int i = threadIdx.x; i < nseg; i += THREADS) {
+      const int64_t p = ptr[(int64_t)s_lo + 1 + i] - e0;
+      seg[i] = p < 0 ? 0 : (p > TILE ? TILE : (int32_t)p);
+    }
+    __syncthreads();
+    const int p0 = (int)threadIdx.x * ITEMS;
+    int lo = 0, hi = nseg;
+    while (lo < hi) {
+      const int mid = (lo + hi) >> 1;
+      if (seg[mid] <= p0) lo = mid + 1;
+      else hi = mid;
+    }
+#pragma unroll
+    for (int k = 0; k < ITEMS; ++k) {
+      while (lo < nseg && seg[lo] <= p0 + k) ++lo;
+      own[k] = s_lo + lo;
+    }
+    return;
+  }
+  for (int j = threadIdx.x; j < TILE; j += THREADS) seg[j] = -1;
+  __syncthreads();
   if (threadIdx.x == 0) seg[0] = s_lo;
   __syncthreads();
   // segments starting strictly inside the tile: empty segments share a start, the last wins
@@ -85,7 +115,19 @@ __device__ __forceinline__ void expand_tile(const int64_t *__restrict__ ptr, int
   const int32_t lane_excl = __shfl_up_sync(0xffffffffu, inc, 1);
   if (lane > 0) carry = lane_excl > carry ? lane_excl : carry;
 #pragma unroll
-  for (int k = 0; k < ITEMS; ++k) seg[threadIdx.x * ITEMS + k] = loc[k] > carry ? loc[k] : carry;
+  for (int k = 0; k < ITEMS; ++k) own[k] = loc[k] > carry ? loc[k] : carry;
+}
+
+// seg[j] = segment of tile entry j for every j, visible to the whole CTA on return
+template <int THREADS, int ITEMS>
+__device__ __forceinline__ void expand_tile(const int64_t *__restrict__ ptr, int64_t S, int64_t e0,
+                                            int tile_n, int32_t *seg /*[TILE]*/, int32_t *aux /*[40]*/,
+                                            const int32_t *__restrict__ bounds = nullptr) {
+  int32_t own[ITEMS];
+  expand_tile_owned<THREADS, ITEMS>(ptr, S, e0, tile_n, seg, aux, bounds, own);
+  __syncthreads();  // `seg` may still be read as the table of segment starts
+#pragma unroll
+  for (int k = 0; k < ITEMS; ++k) seg[threadIdx.x * ITEMS + k] = own[k];
   __syncthreads();
 }
 

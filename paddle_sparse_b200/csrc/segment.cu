@@ -201,6 +201,61 @@ mul_row_w1_kernel(const T *value, const int64_t *__restrict__ rowptr, int64_t M,
   }
 }
 
+// the element-wise body for one given tile (the partial last tile after the vector kernel)
+template <typename T, int OP, int THREADS, int ITEMS>
+__global__ void __launch_bounds__(THREADS)
+mul_row_w1_tail_kernel(const T *value, const int64_t *__restrict__ rowptr, int64_t M, int64_t nnz, int64_t tile,
+                       const T *__restrict__ other, T *out, const int32_t *__restrict__ bounds) {
+  constexpr int TILE = THREADS * ITEMS;
+  __shared__ int32_t seg[TILE];
+  __shared__ int32_t aux[40];
+  const int64_t e0 = tile * TILE;
+  const int tile_n = (int)((nnz - e0) < TILE ? (nnz - e0) : TILE);
+  T v[ITEMS];
+#pragma unroll
+  for (int k = 0; k < ITEMS; ++k) {
+    const int j = k * THREADS + threadIdx.x;
+    if (j < tile_n) v[k] = value[e0 + j];
+  }
+  expand_tile<THREADS, ITEMS>(rowptr, M, e0, tile_n, seg, aux, bounds);
+#pragma unroll
+  for (int k = 0; k < ITEMS; ++k) {
+    const int j = k * THREADS + threadIdx.x;
+    if (j < tile_n) out[e0 + j] = bc_values<T, OP>(v[k], other[seg[j]]);
+  }
+}
+
+// width == 1 on 16-byte-aligned vectors: a thread owns ITEMS consecutive entries, moved as 128-bit loads / stores
+// (ITEMS * sizeof(T) is 16, 32 or 64 bytes), and reads their rows out of expand_tile_owned's registers; the partial
+// last tile takes the element-wise kernel above.
+template <typename T, int OP, int THREADS, int ITEMS>
+__global__ void __launch_bounds__(THREADS)
+mul_row_w1_vec_kernel(const T *value, const int64_t *__restrict__ rowptr, int64_t M, int64_t full_tiles,
+                      const T *__restrict__ other, T *out, const int32_t *__restrict__ bounds) {
+  constexpr int TILE = THREADS * ITEMS;
+  constexpr int VECS = ITEMS * (int)sizeof(T) / 16;
+  static_assert(ITEMS * sizeof(T) % 16 == 0, "a thread's entries are whole 16-byte vectors");
+  __shared__ int32_t seg[TILE];
+  __shared__ int32_t aux[40];
+  const int64_t e0 = (int64_t)blockIdx.x * TILE;
+  const int64_t mine = e0 + (int64_t)threadIdx.x * ITEMS;
+  union alignas(16) Pack {
+    uint4 q[VECS];
+    T v[ITEMS];
+    __device__ Pack() {}
+  } in, res;
+  const uint4 *src = reinterpret_cast<const uint4 *>(value + mine);
+#pragma unroll
+  for (int k = 0; k < VECS; ++k) in.q[k] = ld_once(src + k);
+  int32_t own[ITEMS];
+  expand_tile_owned<THREADS, ITEMS>(rowptr, M, e0, TILE, seg, aux, bounds, own);
+#pragma unroll
+  for (int k = 0; k < ITEMS; ++k) res.v[k] = bc_values<T, OP>(in.v[k], other[own[k]]);
+  uint4 *dst = reinterpret_cast<uint4 *>(out + mine);
+#pragma unroll
+  for (int k = 0; k < VECS; ++k) dst[k] = res.q[k];
+}
+
 template <typename T, int OP, int THREADS, int ITEMS>
 __global__ void __launch_bounds__(THREADS)
 mul_col_w1_kernel(const T *value, const int64_t *__restrict__ col, int64_t nnz, const T *__restrict__ other, T *out) {
@@ -408,7 +463,22 @@ static int bc_row(const void *value, int dtype, int64_t width, const int64_t *ro
   Scratch scratch(s);
   PS_SCRATCH(bounds, scratch, int32_t, (int64_t)blocks + 1);
   if (int rc = tile_bounds_launch(rowptr, M, nnz, THREADS * ITEMS, bounds, s)) return rc;
-  if (width == 1) {
+  const bool aligned = (reinterpret_cast<uintptr_t>(value) | reinterpret_cast<uintptr_t>(out)) % 16 == 0;
+  const int64_t full_tiles = nnz / (THREADS * ITEMS);
+  if (width == 1 && aligned && full_tiles > 0) {
+    PS_DISPATCH_DTYPE(dtype, T,
+                      (mul_row_w1_vec_kernel<T, OP, THREADS, ITEMS><<<(unsigned)full_tiles, THREADS, 0, s>>>(
+                          reinterpret_cast<const T *>(value), rowptr, M, full_tiles, reinterpret_cast<const T *>(other),
+                          reinterpret_cast<T *>(out), bounds)));
+    PS_LAUNCH_OK();
+    const int64_t done = full_tiles * THREADS * ITEMS;
+    if (done < nnz) {  // the partial last tile: same tile index, element-wise
+      PS_DISPATCH_DTYPE(dtype, T,
+                        (mul_row_w1_tail_kernel<T, OP, THREADS, ITEMS><<<1, THREADS, 0, s>>>(
+                            reinterpret_cast<const T *>(value), rowptr, M, nnz, full_tiles,
+                            reinterpret_cast<const T *>(other), reinterpret_cast<T *>(out), bounds)));
+    }
+  } else if (width == 1) {
     PS_DISPATCH_DTYPE(dtype, T,
                       (mul_row_w1_kernel<T, OP, THREADS, ITEMS><<<blocks, THREADS, 0, s>>>(
                           reinterpret_cast<const T *>(value), rowptr, M, nnz, reinterpret_cast<const T *>(other),
