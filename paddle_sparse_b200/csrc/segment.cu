@@ -459,24 +459,30 @@ static int bc_row(const void *value, int dtype, int64_t width, const int64_t *ro
   PS_CHECK(M < 2147483647LL, "mul/add_row: too many rows");
   if (nnz == 0) return PS_OK;
   constexpr int THREADS = 256, ITEMS = 8;
-  const unsigned blocks = (unsigned)ceil_div(nnz, THREADS * ITEMS);
+  const bool aligned = (reinterpret_cast<uintptr_t>(value) | reinterpret_cast<uintptr_t>(out)) % 16 == 0;
+  // the vector kernel moves 32 bytes per thread at least: 16 entries of a 2-byte type, 8 otherwise
+  const bool vec = width == 1 && aligned;
+  const int tile = THREADS * (vec && dtype_size(dtype) == 2 ? 2 * ITEMS : ITEMS);
+  const unsigned blocks = (unsigned)ceil_div(nnz, tile);
   Scratch scratch(s);
   PS_SCRATCH(bounds, scratch, int32_t, (int64_t)blocks + 1);
-  if (int rc = tile_bounds_launch(rowptr, M, nnz, THREADS * ITEMS, bounds, s)) return rc;
-  const bool aligned = (reinterpret_cast<uintptr_t>(value) | reinterpret_cast<uintptr_t>(out)) % 16 == 0;
-  const int64_t full_tiles = nnz / (THREADS * ITEMS);
-  if (width == 1 && aligned && full_tiles > 0) {
-    PS_DISPATCH_DTYPE(dtype, T,
-                      (mul_row_w1_vec_kernel<T, OP, THREADS, ITEMS><<<(unsigned)full_tiles, THREADS, 0, s>>>(
-                          reinterpret_cast<const T *>(value), rowptr, M, full_tiles, reinterpret_cast<const T *>(other),
-                          reinterpret_cast<T *>(out), bounds)));
-    PS_LAUNCH_OK();
-    const int64_t done = full_tiles * THREADS * ITEMS;
-    if (done < nnz) {  // the partial last tile: same tile index, element-wise
+  if (int rc = tile_bounds_launch(rowptr, M, nnz, tile, bounds, s)) return rc;
+  const int64_t full_tiles = nnz / tile;
+  if (vec) {
+    if (full_tiles > 0) {
       PS_DISPATCH_DTYPE(dtype, T,
-                        (mul_row_w1_tail_kernel<T, OP, THREADS, ITEMS><<<1, THREADS, 0, s>>>(
-                            reinterpret_cast<const T *>(value), rowptr, M, nnz, full_tiles,
-                            reinterpret_cast<const T *>(other), reinterpret_cast<T *>(out), bounds)));
+                        (mul_row_w1_vec_kernel<T, OP, THREADS, (sizeof(T) == 2 ? 2 * ITEMS : ITEMS)>
+                         <<<(unsigned)full_tiles, THREADS, 0, s>>>(
+                             reinterpret_cast<const T *>(value), rowptr, M, full_tiles,
+                             reinterpret_cast<const T *>(other), reinterpret_cast<T *>(out), bounds)));
+      PS_LAUNCH_OK();
+    }
+    if (full_tiles * tile < nnz) {  // the partial last tile: same tile index, element-wise
+      PS_DISPATCH_DTYPE(dtype, T,
+                        (mul_row_w1_tail_kernel<T, OP, THREADS, (sizeof(T) == 2 ? 2 * ITEMS : ITEMS)>
+                         <<<1, THREADS, 0, s>>>(
+                             reinterpret_cast<const T *>(value), rowptr, M, nnz, full_tiles,
+                             reinterpret_cast<const T *>(other), reinterpret_cast<T *>(out), bounds)));
     }
   } else if (width == 1) {
     PS_DISPATCH_DTYPE(dtype, T,

@@ -263,3 +263,45 @@ def test_hybrid_sort_coo_is_stable(ops, M, N, nnz, dup, dtype):
     assert np.array_equal(host(r), row[order]) and np.array_equal(host(c), col[order])
     if dtype is not None:
         assert np.array_equal(host(v.to(torch.float64)), val[order].astype(np.float64))
+
+
+# ----------------------------------------------------------------------------- broadcast mul / add on [nnz] values
+@pytest.mark.parametrize("dtype", DT)
+@pytest.mark.parametrize("shape", ["long rows", "short rows", "many empty rows"])
+def test_broadcast_row_col_vector_paths(ops, dtype, shape):
+    """mul.py:76-93 / add.py:50-70 on width-1 values: the 128-bit kernels (aligned), the element-wise ones (a view
+    at an odd element offset), the partial last tile, in place and out of place.  Small integers keep every dtype
+    exact, so the comparison with NumPy (gather_csr / other[col] then * or +) is bit for bit."""
+    rng = np.random.default_rng(len(shape) + 7)
+    M, N = {"long rows": (90, 4000), "short rows": (30000, 700), "many empty rows": (400000, 50)}[shape]
+    nnz = 100003
+    row = np.sort(rng.integers(0, M, nnz)).astype(I64)
+    if shape == "many empty rows":
+        row = np.sort(rng.choice(np.arange(0, M, 97), nnz)).astype(I64)
+    col = rng.integers(0, N, nnz).astype(I64)
+    rowptr = native.ind2ptr(row, M)
+    val = rng.integers(1, 12, nnz + 1).astype(np.float64)
+    orow = rng.integers(1, 12, M).astype(np.float64)
+    ocol = rng.integers(1, 12, N).astype(np.float64)
+    d_ptr, d_col, d_orow, d_ocol = dev(rowptr), dev(col), dev(orow, dtype), dev(ocol, dtype)
+    for off in (0, 1):  # off = 1: base pointers that are not 16-byte aligned
+        n = nnz - off
+        buf = dev(val, dtype)
+        v = buf[off:off + n]
+        r, c = row[off:off + n], col[off:off + n]
+        ptr_np = native.ind2ptr(r, M)
+        p = dev(ptr_np)
+        cc = dev(np.concatenate([[0], c]).astype(I64))[1:] if off else dev(c)
+        x = val[off:off + n]
+        assert np.array_equal(host(ops.mul_row(v, p, d_orow)).astype(np.float64), x * orow[r])
+        assert np.array_equal(host(ops.add_row(v, p, d_orow)).astype(np.float64), x + orow[r])
+        assert np.array_equal(host(ops.mul_col(v, cc, d_ocol)).astype(np.float64), x * ocol[c])
+        assert np.array_equal(host(ops.add_col(v, cc, d_ocol)).astype(np.float64), x + ocol[c])
+        assert np.array_equal(host(v).astype(np.float64), x)  # inputs untouched
+        w = v.clone() if off == 0 else dev(val, dtype)[off:off + n]
+        ops.mul_row(w, p, d_orow, out=w)
+        assert np.array_equal(host(w).astype(np.float64), x * orow[r])
+        w = v.clone() if off == 0 else dev(val, dtype)[off:off + n]
+        ops.mul_col(w, cc, d_ocol, out=w)
+        assert np.array_equal(host(w).astype(np.float64), x * ocol[c])
+    del d_ptr, d_col
