@@ -69,16 +69,28 @@ __device__ __forceinline__ void expand_tile_owned(const int64_t *__restrict__ pt
     }
     __syncthreads();
     const int p0 = (int)threadIdx.x * ITEMS;
-    int lo = 0, hi = nseg;
-    while (lo < hi) {
-      const int mid = (lo + hi) >> 1;
-      if (seg[mid] <= p0) lo = mid + 1;
-      else hi = mid;
-    }
+    auto count_le = [&](int lo, int hi, int p) {  // first index in [lo, hi] whose start exceeds p
+      while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (seg[mid] <= p) lo = mid + 1;
+        else hi = mid;
+      }
+      return lo;
+    };
+    int lo = count_le(0, nseg, p0);
+    const int last = count_le(lo, nseg, p0 + ITEMS - 1);
+    if (last - lo <= 2 * ITEMS) {
 #pragma unroll
-    for (int k = 0; k < ITEMS; ++k) {
-      while (lo < nseg && seg[lo] <= p0 + k) ++lo;
-      own[k] = s_lo + lo;
+      for (int k = 0; k < ITEMS; ++k) {
+        while (lo < last && seg[lo] <= p0 + k) ++lo;
+        own[k] = s_lo + lo;
+      }
+    } else {  // a run of empty segments lands inside this thread's entries: search per entry instead of walking it
+#pragma unroll
+      for (int k = 0; k < ITEMS; ++k) {
+        lo = count_le(lo, last, p0 + k);
+        own[k] = s_lo + lo;
+      }
     }
     return;
   }

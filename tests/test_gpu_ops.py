@@ -41,6 +41,24 @@ def test_ind2ptr_ptr2ind_random(ops, M, nnz):
     assert np.array_equal(host(ops.ind2ptr(buf[1:], M)), want)
 
 
+@pytest.mark.parametrize("gap", [3, 40, 1500, 2040, 2047, 2048, 5000])
+def test_ptr2ind_runs_of_empty_rows(ops, gap):
+    """A run of `gap` empty rows inside a tile: up to a tile's worth of segment starts the expansion searches a
+    sorted table (walking it, or searching per entry when the run lands inside one thread's entries); beyond that it
+    falls back to scatter-of-starts + max-scan.  Same answers as the reference's ptr2ind_cpu either way."""
+    rng = np.random.default_rng(gap)
+    for lead in (0, 1000, 2047, 4100):
+        row = np.concatenate([np.zeros(lead, I64), np.full(3000, gap + 1, I64),
+                              np.sort(rng.integers(gap + 1, gap + 60, 7000)).astype(I64)])
+        M = gap + 70
+        ptr = native.ind2ptr(row, M)
+        assert np.array_equal(host(ops.ptr2ind(dev(ptr), row.size)), row)
+        v = dev(rng.integers(1, 9, row.size).astype(np.float32))
+        o = dev(rng.integers(1, 9, M).astype(np.float32))
+        assert np.array_equal(host(ops.mul_row(v, dev(ptr), o)), host(v) * host(o)[row])
+        assert np.array_equal(host(ops.gather_csr(o, dev(ptr), row.size)), host(o)[row])
+
+
 def test_ptr_count_helpers(ops):
     rng = np.random.default_rng(5)
     cnt = rng.integers(0, 9, 100001).astype(I64)
