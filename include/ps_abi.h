@@ -53,6 +53,29 @@ int ps_prof_kinds(void);
 const char *ps_prof_name(int id);
 int ps_prof_read(int id, double *total_ms, int64_t *launches);
 
+/* The shim-owned device allocator of the DLPack boundary (paddle_sparse_b200/paddle_sparse_ops.py): the reference's
+ * ops allocate their outputs inside the op with paddle::empty / paddle::zeros (csrc/cpu/convert_cpu.cpp:10,13,
+ * csrc/cuda/convert_cuda.cu:27,30, csrc/cpu/sample_cpu.cpp:25-26,123-130); a caller that brings no allocator of its
+ * own gets stream-ordered blocks (cudaMallocAsync / cudaFreeAsync) owned by the DLPack capsule that wraps them.
+ * ps_memcpy: kind 1 = host->device, 2 = device->host (both synchronise), 3 = device->device (asynchronous). */
+int ps_alloc(int64_t bytes, void **out_ptr, void *stream);
+int ps_free(void *ptr, void *stream);
+int ps_memcpy(void *dst, const void *src, int64_t bytes, int kind, void *stream);
+/* cudaStreamSynchronize(stream): a DLPack consumer on another stream is ordered behind the producing stream */
+int ps_stream_sync(void *stream);
+/* current CUDA device of the calling thread (-1 on error) / make `dev` current: the boundary launches on the device
+ * its input tensors live on (CHECK_CUDA + the tensor's place, csrc/cuda/convert_cuda.cu:24,34) */
+int ps_current_device(void);
+int ps_set_device(int dev);
+
+/* Self-test of the hardware behaviour the stable ranking rests on (shared-memory atomics of one warp instruction that
+ * hit the same word are served in ascending lane order; csrc/selftest.cu): host_out[0] = lane-instances checked,
+ * [1] = of which in collisions, [2] = served OUT of lane order (must be 0).  Synchronises.  ps_rank_mode(): 0 = the
+ * sorts rank with one atomic per item, 1 = match-based ranking (environment PS_RANK_MODE=match), which does not
+ * depend on that order. */
+int ps_selftest_atom_order(int64_t *host_out, void *stream);
+int ps_rank_mode(void);
+
 /* ------------------------------------------------------------------ convert */
 /* csrc/convert.cpp:13-23 `ind2ptr(ind, M)`; kernels csrc/cuda/convert_cuda.cu:6-40,
  * csrc/cpu/convert_cpu.cpp:6-30.  ind sorted ascending, out_ptr[M+1]. */

@@ -8,6 +8,7 @@ from . import _lib
 _lib.lib()  # fail at import time, not at first use, when libpaddle_sparse_b200.so is missing
 
 from . import ops  # noqa: E402
+from . import paddle_sparse_ops  # noqa: E402  (the module object of paddle_sparse/__init__.py:8-17, over DLPack)
 from .storage import SparseStorage  # noqa: E402
 from .tensor import SparseTensor  # noqa: E402
 from .coalesce import coalesce  # noqa: E402
@@ -25,11 +26,11 @@ from .convert import (to_scipy, from_scipy, to_torch_sparse, from_torch_sparse, 
 from .sample import sample, sample_adj, manual_seed  # noqa: E402
 
 __version__ = "0.1.0"
-cuda_version = int(ops.sparse_cuda_version()[0])  # paddle_sparse/__init__.py:17-32 reads the same probe
+cuda_version = paddle_sparse_ops.sparse_cuda_version().item()  # paddle_sparse/__init__.py:17, verbatim
 
 __all__ = [
     "SparseStorage", "SparseTensor", "coalesce", "t", "transpose", "sum", "mean", "min", "max", "reduction",
     "mul", "mul_", "mul_nnz", "mul_nnz_", "add", "add_", "add_nnz", "add_nnz_", "index_select", "index_select_nnz", "masked_select",
     "masked_select_nnz", "narrow", "__narrow_diag__", "select", "permute", "cat", "to_scipy", "from_scipy", "to_torch_sparse", "from_torch_sparse",
-    "to_paddle_sparse", "from_paddle_sparse", "sample", "sample_adj", "manual_seed", "ops", "__version__",
+    "to_paddle_sparse", "from_paddle_sparse", "sample", "sample_adj", "manual_seed", "ops", "paddle_sparse_ops", "__version__",
 ]

@@ -12,7 +12,8 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libpaddle_sparse_b200.so")
+# PS_B200_LIB: a differently built copy of the same library (debug / timeline builds of the tools); never a fallback
+LIB_PATH = os.environ.get("PS_B200_LIB") or os.path.join(_HERE, "libpaddle_sparse_b200.so")
 
 c_int = ctypes.c_int
 c_i64 = ctypes.c_int64
@@ -28,6 +29,14 @@ SIGNATURES = {
     "ps_prof_kinds": [],
     "ps_prof_name": [c_int],
     "ps_prof_read": [c_int, c_ptr, c_ptr],
+    "ps_alloc": [c_i64, c_ptr, c_ptr],
+    "ps_free": [c_ptr, c_ptr],
+    "ps_memcpy": [c_ptr, c_ptr, c_i64, c_int, c_ptr],
+    "ps_stream_sync": [c_ptr],
+    "ps_current_device": [],
+    "ps_set_device": [c_int],
+    "ps_selftest_atom_order": [c_ptr, c_ptr],
+    "ps_rank_mode": [],
     "ps_ind2ptr": [c_ptr, c_i64, c_i64, c_ptr, c_ptr],
     "ps_ptr2ind": [c_ptr, c_i64, c_i64, c_ptr, c_ptr],
     "ps_ptr2count": [c_ptr, c_i64, c_ptr, c_ptr],

@@ -272,11 +272,7 @@ static int ls_launch(const uint32_t *lowkeys, const uint32_t *lowvals, const uns
                      uint64_t *state, long long *d_nnz, cudaStream_t s) {
   auto kern = ls_sort_dedup_kernel<T, RED, HAS_VALUE, DEDUP>;
   const size_t smem = sizeof(LsSmem<HAS_VALUE>);
-  static bool configured = false;
-  if (!configured) {
-    PS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = true;
-  }
+  PS_FUNC_SMEM(kern, smem);
   int grid = sm_count() * 2;
   if (grid > nb) grid = nb;
   {
@@ -321,12 +317,7 @@ static int hybrid_inspect(const int64_t *row, const int64_t *col, int64_t nnz, i
   PS_CUDA(cudaMemsetAsync(st->max_rc, 0xff, sizeof(st->max_rc), s));  // -1: empty
   PS_CUDA(cudaMemsetAsync(st->gcount, 0, sizeof(unsigned int) * (size_t)hp.nb, s));
   {
-    static bool configured = false;
-    if (!configured) {
-      PS_CUDA(cudaFuncSetAttribute(ls_bucket_hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                   (int)(sizeof(unsigned int) << LS_MAX_T)));
-      configured = true;
-    }
+    PS_FUNC_SMEM(ls_bucket_hist_kernel, sizeof(unsigned int) << LS_MAX_T);
     ProfScope prof(PROF_BUCKET_HIST, s);
     ls_bucket_hist_kernel<<<sm_count() * 2, 1024, sizeof(unsigned int) * (size_t)hp.nb, s>>>(
         row, col, nnz, cbits, hp.R, hp.T, st->gcount, with_max ? st->max_rc : nullptr);

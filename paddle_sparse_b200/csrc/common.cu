@@ -7,6 +7,8 @@
 
 #include <atomic>
 #include <mutex>
+#include <set>
+#include <utility>
 
 #include "common.cuh"
 
@@ -86,22 +88,33 @@ int sm_count() {
   return cached[dev];
 }
 
-cudaError_t Scratch::alloc_(void **p, size_t bytes) {
+bool func_needs_config(const void *kernel) {
+  static std::mutex mu;
+  static std::set<std::pair<int, const void *>> seen;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return true;
+  std::lock_guard<std::mutex> lk(mu);
+  return seen.insert(std::make_pair(dev, kernel)).second;
+}
+
+static void retain_pool_blocks() {
   static std::once_flag once[64];
   int dev = 0;
-  cudaError_t e = cudaGetDevice(&dev);
-  if (e != cudaSuccess) return e;
-  if (dev >= 0 && dev < 64) {
-    std::call_once(once[dev], [dev]() {
-      cudaMemPool_t pool;
-      if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
-        uint64_t keep = UINT64_MAX;  // retain freed blocks: no OS round trip per call
-        cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
-      }
-    });
-  }
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return;
+  std::call_once(once[dev], [dev]() {
+    cudaMemPool_t pool;
+    if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
+      uint64_t keep = UINT64_MAX;  // retain freed blocks: no OS round trip per call
+      cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+    }
+  });
+}
+
+cudaError_t Scratch::alloc_(void **p, size_t bytes) {
+  retain_pool_blocks();
   return cudaMallocAsync(p, bytes, s_);
 }
+
 
 int read_back(void *host_dst, const void *dev_src, size_t bytes, cudaStream_t s) {
   static thread_local void *pinned = nullptr;
@@ -130,6 +143,44 @@ int64_t ps_cuda_version(void) { return (int64_t)CUDA_VERSION; }
 const char *ps_last_error(void) { return ps::g_err; }
 
 int64_t ps_launch_count(void) { return (int64_t)ps::g_launches.load(); }
+
+// ---- the shim-owned device allocator: stream-ordered blocks for outputs the DLPack boundary
+// (paddle_sparse_ops.py) hands to a caller that brought no allocator of its own
+int ps_alloc(int64_t bytes, void **out_ptr, void *stream) {
+  using namespace ps;
+  PS_CHECK(bytes >= 0 && out_ptr, "alloc: bad arguments");
+  retain_pool_blocks();
+  PS_CUDA(cudaMallocAsync(out_ptr, (size_t)(bytes > 0 ? bytes : 1), (cudaStream_t)stream));
+  return PS_OK;
+}
+int ps_free(void *ptr, void *stream) {
+  using namespace ps;
+  if (ptr) PS_CUDA(cudaFreeAsync(ptr, (cudaStream_t)stream));
+  return PS_OK;
+}
+int ps_memcpy(void *dst, const void *src, int64_t bytes, int kind, void *stream) {
+  using namespace ps;
+  PS_CHECK(bytes >= 0 && kind >= 1 && kind <= 3, "memcpy: bad arguments");
+  if (bytes == 0) return PS_OK;
+  const cudaMemcpyKind k = kind == 1 ? cudaMemcpyHostToDevice : kind == 2 ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice;
+  PS_CUDA(cudaMemcpyAsync(dst, src, (size_t)bytes, k, (cudaStream_t)stream));
+  if (kind != 3) PS_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+  return PS_OK;
+}
+int ps_stream_sync(void *stream) {
+  using namespace ps;
+  PS_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+  return PS_OK;
+}
+int ps_current_device(void) {
+  int dev = -1;
+  return cudaGetDevice(&dev) == cudaSuccess ? dev : -1;
+}
+int ps_set_device(int dev) {
+  using namespace ps;
+  PS_CUDA(cudaSetDevice(dev));
+  return PS_OK;
+}
 
 void ps_prof_enable(int on) { ps::g_prof_on.store(on != 0); }
 

@@ -20,6 +20,13 @@ namespace ps {
 // ----------------------------------------------------------------------------- errors
 void set_error(const char *fmt, ...);
 int sm_count();  // SMs of the current device (148 on B200), cached
+// cudaFuncSetAttribute is per DEVICE: true the first time (kernel, current device) is asked about
+bool func_needs_config(const void *kernel);
+#define PS_FUNC_SMEM(kern, bytes)                                                                        \
+  do {                                                                                                   \
+    if (ps::func_needs_config((const void *)(kern)))                                                      \
+      PS_CUDA(cudaFuncSetAttribute((kern), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(bytes)));    \
+  } while (0)
 
 #define PS_CUDA(expr)                                                                  \
   do {                                                                                 \

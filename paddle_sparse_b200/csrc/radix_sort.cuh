@@ -570,11 +570,7 @@ int rs_launch_pass(KeySrc ks, PaySrcN<NPAY> ps_, KeyDst ko, PayDstN<NPAY> pd, in
   using Smem = RsSmem<KeyT, NPAY, RBITS, THREADS, G::ITEMS * IMUL, G::PREFETCH>;
   auto kern = rs_pass_kernel<KeyT, NPAY, RBITS, THREADS, G::ITEMS * IMUL, G::PREFETCH, 1024 / (THREADS * IMUL)>;
   const size_t smem = sizeof(Smem);
-  static bool configured = false;
-  if (!configured) {
-    PS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = true;
-  }
+  PS_FUNC_SMEM(kern, smem);
   const int64_t tiles = ceil_div(n, Smem::TILE);
   int64_t grid = (int64_t)sm_count() * (1024 / (THREADS * IMUL));
   if (grid > tiles) grid = tiles;

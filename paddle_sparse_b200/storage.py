@@ -52,7 +52,10 @@ class SparseStorage(object):
         assert col is not None
         assert col.dtype == torch.int64
         assert col.dim() == 1
-        if not col.is_cuda:
+        if not col.is_cuda and not (is_sorted and trust_data):
+            # Host tensors are accepted only as an inert holder (`pin_memory()` staging copies of an already built
+            # storage, storage.py:693-733): nothing is validated, sorted or computed for them, and every operator
+            # raises on a CPU tensor.  There is no CPU compute path.
             raise RuntimeError("paddle_sparse_b200.SparseStorage is GPU-only (no CPU fallback): `col` is on the CPU")
         col = col.contiguous()
         nnz = col.numel()
@@ -487,3 +490,69 @@ class SparseStorage(object):
 
     def num_cached_keys(self) -> int:
         return len(self.cached_keys())
+
+    # ------------------------------------------------------------------ copies, dtype and placement (storage.py:523-776)
+    def _fields(self):
+        return dict(row=self._row, rowptr=self._rowptr, col=self._col, value=self._value, rowcount=self._rowcount,
+                    colptr=self._colptr, colcount=self._colcount, csr2csc=self._csr2csc, csc2csr=self._csc2csr)
+
+    def _rebuilt(self, fn):
+        """A new storage whose every present tensor is fn(tensor); sizes kept, nothing re-validated or re-sorted."""
+        kw = {k: (None if t is None else fn(t)) for k, t in self._fields().items()}
+        return SparseStorage(sparse_sizes=self._sparse_sizes, is_sorted=True, trust_data=True, **kw)
+
+    def copy(self):
+        """storage.py:523-537: a new storage object SHARING every tensor (test_storage.py:148-150)."""
+        return self._rebuilt(lambda t: t)
+
+    def clone(self):
+        """storage.py:539-580: a new storage owning copies of every tensor (test_storage.py:152-154)."""
+        return self._rebuilt(lambda t: t.clone())
+
+    def type(self, dtype: torch.dtype, non_blocking: bool = False):
+        """storage.py:582-594: value cast; `self` when there is no value or the dtype already matches."""
+        value = self._value
+        if value is None or dtype == value.dtype:
+            return self
+        return self.set_value(value.to(dtype=dtype, non_blocking=non_blocking), layout="coo")
+
+    def type_as(self, tensor: torch.Tensor, non_blocking: bool = False):
+        return self.type(dtype=tensor.dtype, non_blocking=non_blocking)
+
+    def to_device(self, device, non_blocking: bool = False):
+        """storage.py:599-641: every tensor moved, caches kept; `self` when already there.  A CUDA target gives a
+        working storage; a CPU target gives an inert host copy (see the constructor), as pin_memory() does."""
+        device = torch.device(device)
+        here = self._col.device
+        if device == here or (device.type == "cuda" and device.index is None and here.type == "cuda"):
+            return self
+        return self._rebuilt(lambda t: t.to(device, non_blocking=non_blocking))
+
+    def device_as(self, tensor: torch.Tensor, non_blocking: bool = False):
+        return self.to_device(device=tensor.device, non_blocking=non_blocking)
+
+    def cuda(self):
+        """storage.py:646-691: `self` when the tensors already live on a CUDA device."""
+        if self._col.is_cuda:
+            return self
+        return self._rebuilt(lambda t: t.cuda())
+
+    def pin_memory(self):
+        """storage.py:693-733: page-locked host copies of every tensor (a staging copy for asynchronous uploads:
+        `st.pin_memory().to_device("cuda", non_blocking=True)`); the result holds data only."""
+        return self._rebuilt(lambda t: t.cpu().pin_memory() if t.is_cuda else t.pin_memory())
+
+    def is_pinned(self) -> bool:
+        """storage.py:735-762 as intended (the reference body shadows its own accumulator): true when
+        every present tensor is page-locked host memory."""
+        return all(t.is_pinned() for t in self._fields().values() if t is not None)
+
+    def share_memory_(self):
+        """storage.py:765-766: unsupported in the reference too (warns, returns None)."""
+        warnings.warn("`share_memory_` is not supported (device tensors are not shared between processes this way). "
+                      "Please avoid calling this api.")
+
+    def is_shared(self) -> bool:
+        """storage.py:769-772: always False, with the reference's warning."""
+        warnings.warn("`is_shared` is not supported. The return value is always `False`.")
+        return False

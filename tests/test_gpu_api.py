@@ -101,6 +101,65 @@ def test_storage_set_value_and_copy(ps, dtype):
     assert out.col().data_ptr() == st.col().data_ptr()
     with pytest.warns(UserWarning):
         st.set_value_(ten(g["value"], dtype))
+    # test/test_storage.py:145-154
+    st = st.sparse_resize((3, 3))
+    assert st.sparse_sizes() == (3, 3)
+    new = st.copy()
+    assert new != st and new is not st
+    assert new.col().data_ptr() == st.col().data_ptr()
+    new = st.clone()
+    assert new != st
+    assert new.col().data_ptr() != st.col().data_ptr()
+    assert new.col().tolist() == st.col().tolist() and new.value().float().tolist() == st.value().float().tolist()
+
+
+def test_storage_dtype_and_placement(ps):
+    """storage.py:582-776: type / type_as / to_device / device_as / cuda / pin_memory / is_pinned / share_memory_ /
+    is_shared.  Caches travel with the data; a host copy is an inert staging holder."""
+    g = G.CACHING
+    st = ps.SparseStorage(row=ten(g["row"]), col=ten(g["col"]), value=ten([1, 2, 3, 4], torch.float32)).fill_cache_()
+    assert st.type(torch.float32) is st and st.type_as(torch.zeros(1)) is st
+    h = st.type(torch.float16)
+    assert h is not st and h.value().dtype == torch.float16 and h.col().data_ptr() == st.col().data_ptr()
+    assert h.cached_keys() == st.cached_keys() and st.type_as(torch.zeros(1, dtype=torch.float64)).value().dtype == torch.float64
+    novalue = ps.SparseStorage(row=ten(g["row"]), col=ten(g["col"]))
+    assert novalue.type(torch.float16) is novalue
+    assert st.cuda() is st and st.to_device("cuda") is st and st.to_device(st.col().device) is st
+    assert st.device_as(st.col()) is st and not st.is_pinned()
+    pinned = st.pin_memory()
+    assert pinned.is_pinned() and not pinned.col().is_cuda and pinned.cached_keys() == st.cached_keys()
+    assert pinned.col().tolist() == st.col().tolist() and pinned._csr2csc.tolist() == g["csr2csc"]
+    with pytest.raises(RuntimeError, match="GPU-only"):  # a host copy holds data only: no operator runs on it
+        pinned.clear_cache_().csr2csc()
+    back = st.pin_memory().to_device("cuda", non_blocking=True)
+    assert back.col().is_cuda and back.csc2csr().tolist() == g["csc2csr"] and back.num_cached_keys() == 5
+    assert back.value().tolist() == [1, 2, 3, 4] and pinned.cuda().col().is_cuda
+    assert back.device_as(torch.zeros(1)).col().device.type == "cpu"
+    with pytest.warns(UserWarning):
+        assert st.share_memory_() is None
+    with pytest.warns(UserWarning):
+        assert st.is_shared() is False
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two CUDA devices in one process")
+def test_second_device_in_one_process(ps):
+    """cudaFuncSetAttribute is per device: the > 48 KB shared-memory kernels must be configured on each device a
+    process uses."""
+    rng = np.random.default_rng(2)
+    M, N, nnz = 3_000_000, 2_500_000, 300_000
+    row, col = _random_coo(rng, M, N, nnz, 0.3)
+    val = rng.random(nnz).astype(np.float32)
+    want = np_ref.build_pipeline(row, col, val, M, N)
+    A0 = ps.SparseTensor(row=dev(row), col=dev(col), value=dev(val), sparse_sizes=(M, N)).coalesce("add").fill_cache_()
+    raw = ps.SparseTensor(row=dev(row).to("cuda:1"), col=dev(col).to("cuda:1"), value=dev(val).to("cuda:1"),
+                          sparse_sizes=(M, N))
+    A1 = raw.coalesce("add").fill_cache_()
+    for A in (A0, A1, A0.to("cuda:1").clear_cache_().fill_cache_()):
+        st = A.storage
+        for k, t in dict(row=st.row(), col=st.col(), rowptr=st.rowptr(), colptr=st.colptr(), csr2csc=st.csr2csc(),
+                         csc2csr=st.csc2csr()).items():
+            assert np.array_equal(t.cpu().numpy(), want[k]), k
+    assert A1.device() == torch.device("cuda:1")
 
 
 @pytest.mark.parametrize("dtype", DTYPES)

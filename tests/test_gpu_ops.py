@@ -323,3 +323,15 @@ def test_broadcast_row_col_vector_paths(ops, dtype, shape):
         ops.mul_col(w, cc, d_ocol, out=w)
         assert np.array_equal(host(w).astype(np.float64), x * ocol[c])
     del d_ptr, d_col
+
+
+def test_atomic_rank_order_selftest(ops):
+    """Stability of every sort here rests on ATOMS serving the colliding lanes of one warp instruction in lane order
+    (radix_sort.cuh phase 2): re-checked on THIS device, for both counter layouts, under every collision pattern."""
+    import ctypes
+    h = (ctypes.c_int64 * 3)()
+    ops._lib.call("ps_selftest_atom_order", h, None)
+    checked, collided, bad = int(h[0]), int(h[1]), int(h[2])
+    assert checked >= 10 ** 9 and collided > checked // 10
+    if ops._lib.lib().ps_rank_mode() == 0:
+        assert bad == 0, f"{bad} of {collided} colliding lane-instances were served out of lane order: set PS_RANK_MODE=match"
