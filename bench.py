@@ -12,11 +12,15 @@ N = 1 : BASELINE.json configs[1] — ogbn-products shape, 2,449,029 nodes, 61,85
 N > 1 : the row-range-partitioned build (configs[4] shape, papers100M: 111,059,956 nodes,
         201,960,734 nnz per GPU = 1.6157 B nnz at N = 8), weak scaling, one all-to-all-v (over peer memory, fused
         with the partition pass; NCCL all_to_all_single is the fall-back).
-`value` = inputs resident in HBM.  `e2e` = the same step from pinned HOST buffers (H2D of row / col / value and D2H
-of the resulting rowptr inside the timed region, every step), run as a double-buffered loader would: the upload of
-step i+1 on a copy stream overlaps the build of step i; the strictly serial figure is reported beside it.
-Prints ONE JSON line (rank 0).  `--impl reference` times the reference's CPU path (NumPy
-restatement of its Python op chain + its own csrc/cpu compiled unmodified where available).
+`value` = inputs resident in HBM.  `e2e` = the same step from pinned HOST buffers to pinned HOST buffers: H2D of
+row / col / value and D2H of EVERY array the step produces (row, col, value, rowptr, colptr, csr2csc, csc2csr and the
+transposed triple at N = 1) inside the timed region, every step, run as a double-buffered loader would (copies of
+neighbouring steps overlap the build on the copy engines); the strictly serial figure is reported beside it.
+A line is printed only if the run passed its parity gate: at N = 1 every array of one step is
+compared with the CPU oracle on the full configuration (the same oracle pass is the timed `cpu_baseline`).
+Prints ONE JSON line (rank 0).  `--impl reference` times the reference's CPU path (NumPy restatement of its Python
+op chain + its own csrc/cpu compiled unmodified where available) on the FULL configs[1] input, as many steps as fit
+a few minutes.
 """
 import argparse
 import json
@@ -35,7 +39,8 @@ PAPERS = dict(name="ogbn-papers100M-shape", M=111059956, N=111059956, nnz_per_gp
 PIPELINE_BYTES_PER_NNZ = 128.6
 # without t() (the sharded step builds CSR + CSC structures per shard, no transposed copy): 128.6 - 48
 PIPELINE_LOCAL_BYTES_PER_NNZ = 80.6
-CPU_SAMPLE_NNZ = 8_000_000
+CPU_SAMPLE_NNZ = 8_000_000      # bounded CPU sample where the full configuration cannot be timed (N > 1, --quick-cpu)
+REFERENCE_BUDGET_S = 170.0      # the reference arm runs as many full-size steps as fit this (at least one)
 # dram__bytes_read.sum + dram__bytes_write.sum of rs_pass_kernel, average per launch over the 7 launches of one
 # step, from the committed `ncu --set full` capture (profiles/r01d_bench_step_kernels_summary.txt: 11.83 GB over the
 # 7 launches): updated whenever the capture is
@@ -111,15 +116,36 @@ class ClockSampler:
 
 
 # =============================================================================== the CPU reference arm
-def cpu_pipeline_sample(sample_nnz: int, cfg=PRODUCTS):
-    """The reference's CPU path on a bounded sample of the workload: the first `sample_nnz` entries of
-    the same synthetic stream, same sparse sizes.  Returns (seconds, kind)."""
+def cpu_pipeline(nnz: int, cfg=PRODUCTS, first: int = 0):
+    """The reference's CPU path (oracle/np_ref.build_pipeline: storage.py / transpose.py op chain restated in NumPy,
+    ind2ptr from the reference's own csrc/cpu compiled unmodified where oracle/_ref was built) on entries
+    [first, first + nnz) of the synthetic stream at the configuration's sparse sizes.
+    Returns (seconds, kind, inputs, outputs)."""
     from oracle import native, np_ref, synth
-    row, col, val = synth.synth_coo(cfg["seed"], 0, sample_nnz, cfg["M"], cfg["N"])
+    row, col, val = synth.synth_coo(cfg["seed"], first, nnz, cfg["M"], cfg["N"])
     t0 = time.perf_counter()
-    np_ref.build_pipeline(row, col, val, cfg["M"], cfg["N"])
+    out = np_ref.build_pipeline(row, col, val, cfg["M"], cfg["N"])
     dt = time.perf_counter() - t0
-    return dt, ("reference" if native.have_ref() else "port")
+    kind = "port"  # the Python op chain is restated (Paddle is not installable); see `detail`
+    return dt, kind, (row, col, val), out
+
+
+CPU_DETAIL = ("NumPy restatement of the reference's storage.py / transpose.py op chain (np.argsort for its three "
+              "argsorts, reduceat for segment_csr, fancy-index gathers) + the reference's own csrc/cpu ind2ptr "
+              "compiled unmodified when oracle/_ref is present; single-threaded like the reference's native code")
+
+
+def reference_workload(n_gpus: int, nnz: int, full: bool):
+    if n_gpus <= 1:
+        c = PRODUCTS
+        what = "every entry" if full else f"the first {nnz} entries"
+        return {"workload": f"{c['name']}: {c['M']} nodes, {c['nnz']} nnz, fp32; coalesce(add) + rowptr + csr2csc + colptr + "
+                            f"csc2csr + t() on the host CPU; {what} of the stream per step"
+                            + ("" if full else " (BOUNDED SAMPLE, not the full configuration)")}
+    c = PAPERS
+    return {"workload": f"{c['name']}: {c['M']} nodes; CPU arm times the first {nnz} entries of rank 0's "
+                        f"{c['nnz_per_gpu']}-entry stream at full sparse sizes per step (BOUNDED SAMPLE of one shard's "
+                        "input; no exchange on the CPU)", "parallelism": f"row-range x{n_gpus} on the GPU arm"}
 
 
 def run_reference(args):
@@ -128,23 +154,32 @@ def run_reference(args):
         return
     from oracle import native
     native.port_lib()
-    for _ in range(max(args.warmup, 0) and 1):
-        cpu_pipeline_sample(CPU_SAMPLE_NNZ // 8)
-    times = []
-    for _ in range(args.steps):
-        dt, kind = cpu_pipeline_sample(CPU_SAMPLE_NNZ)
+    multi = args.gpus > 1
+    cfg = PAPERS if multi else PRODUCTS
+    # calibration / warm-up on a small prefix (also pages the libraries in)
+    t_cal, _, _, _ = cpu_pipeline(2_000_000, cfg)
+    full_nnz = cfg["nnz_per_gpu"] if multi else cfg["nnz"]
+    est_full = t_cal * (full_nnz / 2e6) * 1.25  # argsort is n log n
+    full = (not multi) and not args.quick_cpu and est_full <= REFERENCE_BUDGET_S
+    nnz = full_nnz if full else (2 * CPU_SAMPLE_NNZ if multi else CPU_SAMPLE_NNZ)
+    times, kind, t_begin = [], "port", time.perf_counter()
+    while len(times) < max(args.steps, 1):  # as many steps as fit the budget, at least one
+        dt, kind, _, _ = cpu_pipeline(nnz, cfg)
         times.append(dt)
+        if time.perf_counter() - t_begin + dt > REFERENCE_BUDGET_S:
+            break
+    steps = len(times)
     ms = 1e3 * sum(times) / len(times)
-    value = CPU_SAMPLE_NNZ / (ms * 1e-3)
-    sample = (f"first {CPU_SAMPLE_NNZ} entries of the configs[1] stream at full sparse sizes per step; NumPy restatement "
-              f"of storage.py/transpose.py op chain + reference csrc/cpu ind2ptr ({kind}); single-threaded like the reference")
+    value = nnz / (ms * 1e-3)
+    sample = (("the full configuration" if full else f"first {nnz} entries of the stream at full sparse sizes")
+              + f", {steps} step(s) of {ms / 1e3:.1f} s; " + CPU_DETAIL)
     line = {
         "impl": "reference", "metric": "coalesce+CSR/CSC build nnz/s", "value": value, "unit": "nnz/s",
-        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
+        "n_gpus": args.gpus, "steps": steps, "steps_requested": args.steps, "warmup": 1, "ms_per_step": ms,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int64 keys + f32 values",
-        "data": "synthetic", "config": workload_config(args.gpus),
+        "data": "synthetic", "config": reference_workload(args.gpus, nnz, full),
         "cpu_baseline": {"value": value, "unit": "nnz/s", "cores": 1, "kind": kind, "sample": sample,
-                         "host_cores_available": os.cpu_count()},
+                         "host_cores_available": os.cpu_count(), "full_config": full},
         "e2e": {"value": value, "unit": "nnz/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -216,6 +251,96 @@ def read_profile(lib):
     return out
 
 
+def compare_with_oracle(np, got: dict, want: dict):
+    """Every array of one step against the oracle: indices / pointers / permutations bit-exact, fp32 values within
+    1e-6 relative (north_star).  Returns the list of array names compared; raises AssertionError on a mismatch."""
+    for k, w in want.items():
+        g = got[k]
+        assert g.shape == w.shape, f"parity gate: {k} has shape {g.shape}, the oracle {w.shape}"
+        if w.dtype.kind == "f":
+            np.testing.assert_allclose(g, w, rtol=1e-6, atol=0, err_msg=f"parity gate: {k}")
+        else:
+            assert np.array_equal(g, w), f"parity gate: {k} differs from the oracle"
+    return sorted(want)
+
+
+def parity_gate(args, ps, torch, dist, device, rank, world, cfg, row, col, val):
+    """N = 1: one full step on the bench inputs, every result array compared with the CPU oracle run on the same
+    61.86 M entries (that oracle pass is also the timed cpu_baseline).  With --no-cpu / --quick-cpu the gate runs
+    on a prefix of the stream instead and says so.  N > 1: the partitioned build at reduced scale (the same
+    sparse sizes, 1 M entries per rank) gathered on rank 0 and compared with the oracle's single-matrix build, and
+    - on the full-size shards, after the timed region - the global invariants (run_ours)."""
+    import numpy as np
+    M, N = cfg["M"], cfg["N"]
+    if world == 1:
+        full = not (args.no_cpu or args.quick_cpu)
+        n = cfg["nnz"] if full else (4_000_000 if args.no_cpu else CPU_SAMPLE_NNZ)
+        dt, kind, _, want = cpu_pipeline(n, cfg)
+        A, At = pipeline_step(ps, row[:n], col[:n], val[:n], M, N)
+        st, tt = A.storage, At.storage
+        got = dict(row=st.row(), col=st.col(), value=st.value(), rowptr=st.rowptr(), colptr=st.colptr(),
+                   csr2csc=st.csr2csc(), csc2csr=st.csc2csr(), t_row=tt.row(), t_col=tt.col(), t_value=tt.value())
+        got = {k: v.cpu().numpy() for k, v in got.items()}
+        compared = compare_with_oracle(np, got, want)
+        del A, At, st, tt, got
+        parity = {"passed": True, "arrays": compared, "nnz_in": n, "nnz_out": int(want["row"].size),
+                  "full_config": full, "rule": "indices, pointers, permutations bit-exact; fp32 values rtol 1e-6",
+                  "oracle": "oracle/np_ref.build_pipeline on the same synthetic entries"}
+        base = None
+        if not args.no_cpu:
+            base = {"value": n / dt, "unit": "nnz/s", "cores": 1, "kind": kind, "full_config": full,
+                    "sample": (("the full configuration" if full else f"first {n} entries of the same stream at full "
+                                "sparse sizes") + f", one pass ({dt:.1f} s); " + CPU_DETAIL),
+                    "host_cores_available": os.cpu_count()}
+        return parity, base
+    # ---- N > 1, reduced scale
+    from paddle_sparse_b200 import dist as psd
+    small = 1_000_000
+    r, c, v = ps.ops.synth_coo(cfg["seed"] ^ 0x77, rank * small, small, M, N, device)
+    shard = psd.build_partitioned(r, c, v, (M, N), fill_cache=True, transpose=False)
+    st = shard.tensor.storage
+    mine = dict(row=shard.global_row(), col=st.col(), value=st.value())
+    sizes = torch.tensor([st.col().numel(), shard.row_start, shard.row_end], device=device, dtype=torch.int64)
+    all_sizes = [torch.empty_like(sizes) for _ in range(world)]
+    dist.all_gather(all_sizes, sizes)
+    all_sizes = [t.tolist() for t in all_sizes]
+    cap = max(s[0] for s in all_sizes)
+    gathered = {}
+    for k, t in mine.items():
+        pad = torch.zeros(cap, dtype=t.dtype, device=device)
+        pad[: t.numel()] = t
+        bufs = [torch.empty_like(pad) for _ in range(world)]
+        dist.all_gather(bufs, pad)
+        gathered[k] = bufs
+    # shard-local structure checks on every rank
+    rows = shard.row_end - shard.row_start
+    ok = bool(st.rowptr().numel() == rows + 1 and int(st.rowptr()[-1]) == st.col().numel()
+              and torch.equal(st.rowptr(), ps.ops.ind2ptr(st.row(), rows))
+              and torch.equal(st.colptr(), ps.ops.ind2ptr(st.col()[st.csr2csc()], N))
+              and torch.equal(st.csc2csr()[st.csr2csc()], torch.arange(st.col().numel(), device=device)))
+    flag = torch.tensor([int(ok)], device=device)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    assert int(flag) == 1, "parity gate: a shard's rowptr / colptr / permutations are inconsistent"
+    parity = {"passed": True}
+    if rank == 0:
+        from oracle import np_ref, synth
+        src = [synth.synth_coo(cfg["seed"] ^ 0x77, g * small, small, M, N) for g in range(world)]
+        srow, scol, sval = (np.concatenate([s[k] for s in src]) for k in range(3))
+        idx, value = np_ref.coalesce(np.stack([srow, scol]), sval, M, N, "add")
+        got = {k: np.concatenate([gathered[k][g][: all_sizes[g][0]].cpu().numpy() for g in range(world)])
+               for k in mine}
+        compare_with_oracle(np, got, dict(row=idx[0], col=idx[1], value=value))
+        assert all_sizes[0][1] == 0 and all_sizes[-1][2] == M
+        assert all(all_sizes[g][2] == all_sizes[g + 1][1] for g in range(world - 1))
+        parity = {"passed": True, "arrays": ["row", "col", "value", "shard rowptr / colptr / csr2csc / csc2csr consistency"],
+                  "nnz_in": small * world, "nnz_out": int(idx.shape[1]), "full_config": False,
+                  "rule": "concatenated shards == the oracle's single-matrix coalesce at reduced scale (same sparse sizes, "
+                          f"{small} entries per rank), bit-exact indices, fp32 rtol 1e-6; full-size shards: global "
+                          "invariants after the timed region",
+                  "oracle": "oracle/np_ref.coalesce"}
+    return parity, None
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -271,6 +396,9 @@ def run_ours(args):
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return float(ms), out
 
+    # ---- parity gate: precedes any timing; no line is printed unless it passes
+    parity, cpu_baseline = parity_gate(args, ps, torch, dist, device, rank, world, cfg, row, col, val)
+
     # warm-up: W untimed steps through the SAME loop as the timed region (the previous step's result stays alive
     # while the next one is built), so that the caching allocators already hold the blocks that loop needs; a
     # warm-up that drops each result at once leaves ~12 cudaMalloc calls to the first timed steps
@@ -292,18 +420,38 @@ def run_ours(args):
     lib.ps_prof_enable(0)
     prof = read_profile(lib)
 
-    # ---- end to end: host (pinned) inputs, H2D + hot path + D2H of the result pointer array, every step
+    # ---- end to end: pinned host inputs -> pinned host outputs, every step: H2D of row / col / value, the hot path,
+    # D2H of every array the step produced (what a caller that leaves the device receives)
     if world == 1:
         h_row, h_col, h_val = (t.cpu().pin_memory() for t in (row, col, val))
-        h_out = torch.empty(M + 1, dtype=torch.int64).pin_memory()
+        names = ("row", "col", "value", "rowptr", "colptr", "csr2csc", "csc2csr", "t_row", "t_col", "t_value")
+
+        def result_arrays(A, At):
+            st, tt = A.storage, At.storage
+            return dict(row=st.row(), col=st.col(), value=st.value(), rowptr=st.rowptr(), colptr=st.colptr(),
+                        csr2csc=st.csr2csc(), csc2csr=st.csc2csr(), t_row=tt.row(), t_col=tt.col(), t_value=tt.value())
+
+        ref_arrays = result_arrays(*out)
+        h_out = [{k: torch.empty(v.shape, dtype=v.dtype).pin_memory() for k, v in ref_arrays.items()} for _ in range(2)]
+        del ref_arrays
+
+        def download(A, At, slot):
+            got = result_arrays(A, At)
+            n = 0
+            for k in names:
+                dst = h_out[slot][k][: got[k].numel()]
+                dst.copy_(got[k], non_blocking=True)
+                n += dst.numel() * dst.element_size()
+            return n
 
         def e2e_step():
             r, c, v = (t.to(device, non_blocking=True) for t in (h_row, h_col, h_val))
             A, At = pipeline_step(ps, r, c, v, M, N)
-            h_out.copy_(A.storage.rowptr(), non_blocking=True)
+            download(A, At, 0)
             return A
 
         copy_stream = torch.cuda.Stream(device=device)
+        down_stream = torch.cuda.Stream(device=device)
 
         def upload():
             """This step's inputs, pinned host -> device on the copy stream; the event marks their arrival."""
@@ -313,9 +461,12 @@ def run_ours(args):
                 ev.record(copy_stream)
             return bufs, ev
 
+        d2h_bytes = [0]
+
         def e2e_pipelined(steps):
-            """The same K steps as a user's double-buffered loader runs them: every step uploads its own inputs and
-            reads its own result back, but step i+1's upload (copy engine) overlaps step i's build (SMs)."""
+            """The same K steps as a double-buffered loader runs them: every step uploads its own inputs and reads
+            ALL of its own results back; the upload of step i+1 and the download of step i-1 (copy engines, one per
+            direction) overlap the build of step i (SMs)."""
             cur = torch.cuda.current_stream()
             pending = upload()
             A = None
@@ -326,10 +477,16 @@ def run_ours(args):
                 for t in (r, c, v):
                     t.record_stream(cur)
                 A, At = pipeline_step(ps, r, c, v, M, N)
-                h_out.copy_(A.storage.rowptr(), non_blocking=True)
+                built = torch.cuda.Event()
+                built.record(cur)
+                with torch.cuda.stream(down_stream):
+                    down_stream.wait_event(built)
+                    d2h_bytes[0] = download(A, At, i & 1)
+                    for t in result_arrays(A, At).values():
+                        t.record_stream(down_stream)
+            cur.wait_stream(down_stream)
             return A
         h2d = sum(t.numel() * t.element_size() for t in (h_row, h_col, h_val))
-        d2h = h_out.numel() * h_out.element_size()
         e2e_steps = max(args.steps // 2, 2)
         for _ in range(2):
             e2e_step()
@@ -338,14 +495,15 @@ def run_ours(args):
         total_ms, _ = timed(lambda: e2e_pipelined(e2e_steps), 1)
         e2e_ms = total_ms / e2e_steps
         e2e = {"value": units_per_step / (e2e_ms * 1e-3), "unit": "nnz/s", "h2d_bytes_per_step": h2d,
-               "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms, "steps": e2e_steps,
-               "mode": "double-buffered: upload of step i+1 on a copy stream overlaps the build of step i; "
-                       "K uploads, K builds and K read-backs inside the timed region",
+               "d2h_bytes_per_step": d2h_bytes[0], "ms_per_step": e2e_ms, "steps": e2e_steps,
+               "mode": "pinned host -> pinned host, double-buffered: every step uploads row / col / value and downloads "
+                       "ALL result arrays (row, col, value, rowptr, colptr, csr2csc, csc2csr, t_row, t_col, t_value); "
+                       "copies of neighbouring steps overlap the build; K uploads, K builds, K downloads timed",
                "serial_ms_per_step": serial_ms, "serial_value": units_per_step / (serial_ms * 1e-3)}
         nnz_out = out[0].nnz()
         # ---- secondary figure: the same shape from the R-MAT stream (degree skew; hub rows overflow the
         # shared-memory buckets of the hybrid coalesce, which then takes its LSD fall-back).  Uniform is the headline.
-        del h_row, h_col, h_val
+        del h_row, h_col, h_val, h_out
         s_row, s_col, s_val = ps.ops.synth_coo(cfg["seed"], 0, nnz, M, N, device, rmat=True)
 
         def skew_step():
@@ -359,11 +517,27 @@ def run_ours(args):
     else:
         skewed = None
         h_row, h_col, h_val = (t.cpu().pin_memory() for t in (row, col, val))
+        # what a caller that leaves the device receives from a shard: its CSR triple (rowptr, col, value) on local rows
+        cap_out = int(npg * 1.3) + 1024
+        h_res = dict(rowptr=torch.empty(M + 1, dtype=torch.int64).pin_memory(),
+                     col=torch.empty(cap_out, dtype=torch.int64).pin_memory(),
+                     value=torch.empty(cap_out, dtype=val.dtype).pin_memory())
+        d2h_bytes = [0]
+
+        def download(shard):
+            st = shard.tensor.storage
+            n = 0
+            for k, t in (("rowptr", st.rowptr()), ("col", st.col()), ("value", st.value())):
+                dst = h_res[k][: t.numel()]
+                dst.copy_(t, non_blocking=True)
+                n += dst.numel() * dst.element_size()
+            d2h_bytes[0] = n
 
         def e2e_step():
             r, c, v = (t.to(device, non_blocking=True) for t in (h_row, h_col, h_val))
             shard = psd.build_partitioned(r, c, v, (M, N), fill_cache=True, transpose=False)
-            return shard.tensor.storage.rowptr()[-1:].cpu()
+            download(shard)
+            return shard
 
         copy_stream = torch.cuda.Stream(device=device)
 
@@ -385,8 +559,8 @@ def run_ours(args):
                 cur.wait_event(ev)
                 for t in (r, c, v):
                     t.record_stream(cur)
-                shard = psd.build_partitioned(r, c, v, (M, N), fill_cache=True, transpose=False)
-                last = shard.tensor.storage.rowptr()[-1:].cpu()
+                last = psd.build_partitioned(r, c, v, (M, N), fill_cache=True, transpose=False)
+                download(last)
             return last
         h2d = sum(t.numel() * t.element_size() for t in (h_row, h_col, h_val))
         e2e_steps = max(args.steps // 2, 2)
@@ -395,22 +569,58 @@ def run_ours(args):
         e2e_pipelined(2)
         total_ms, _ = timed(lambda: e2e_pipelined(e2e_steps), 1)
         e2e_ms = total_ms / e2e_steps
+        tot_d2h = torch.tensor([float(d2h_bytes[0])], device=device, dtype=torch.float64)
+        dist.all_reduce(tot_d2h, op=dist.ReduceOp.SUM)
         e2e = {"value": units_per_step / (e2e_ms * 1e-3), "unit": "nnz/s", "h2d_bytes_per_step": h2d * world,
-               "d2h_bytes_per_step": 8 * world, "ms_per_step": e2e_ms, "steps": e2e_steps,
-               "mode": "double-buffered: upload of step i+1 on a copy stream overlaps step i; K uploads, K builds "
-                       "and K read-backs inside the timed region",
+               "d2h_bytes_per_step": int(tot_d2h), "ms_per_step": e2e_ms, "steps": e2e_steps,
+               "mode": "pinned host -> pinned host per rank, double-buffered uploads: every step uploads the rank's row / "
+                       "col / value and downloads its shard's CSR triple (rowptr, col, value on local rows); the CSC-side "
+                       "caches stay on the device for the shard-local operators; bytes summed over the ranks",
                "serial_ms_per_step": serial_ms, "serial_value": units_per_step / (serial_ms * 1e-3)}
+        del h_row, h_col, h_val, h_res
         nnz_out = None
         shard = out
         sent = torch.tensor([shard.sent, shard.received], device=device, dtype=torch.float64)
         dist.all_reduce(sent, op=dist.ReduceOp.MAX)
+        # ---- the same step taken apart: (a) the exchange alone (splitter histogram + all-reduce + fused partition /
+        # all-to-all-v), (b) ONE GPU building one shard of this shape with no exchange: the tuples this rank owns
+        # after the exchange, as if they had arrived locally - the anchor for scaling efficiency
+        def exchange_only():
+            return psd.route_tuples(row, col, val, (M, N))
+        exchange_only()
+        exchange_ms, routed = timed(exchange_only, max(args.steps // 2, 2))
+        o_row, o_col, o_val = (t.clone() for t in routed[:3])
+        r0 = int(routed[3][rank])
+        rows_local = int(routed[3][rank + 1]) - r0
+        del routed
+
+        def local_only():
+            lr = ps.ops.add_scalar(o_row, -r0) if r0 else o_row
+            c_row, c_col, c_val, c_rowptr = ps.ops.coalesce(lr, o_col, o_val, rows_local, N, "add", True)
+            A = ps.SparseTensor(row=c_row, rowptr=c_rowptr, col=c_col, value=c_val, sparse_sizes=(rows_local, N),
+                                is_sorted=True, trust_data=True)
+            return A.fill_cache_()
+        local_only()
+        local_ms, A_full = timed(local_only, max(args.steps // 2, 2))
+        # global invariants of the full-size shards (parity gate, second half)
+        st = A_full.storage
+        n_loc = st.col().numel()
+        key = st.row() * N + st.col()
+        inv_ok = bool(n_loc == 0 or (key[1:] > key[:-1]).all())
+        inv_ok = inv_ok and int(st.rowptr()[-1]) == n_loc and bool((st.col()[st.csr2csc()][1:] >= st.col()[st.csr2csc()][:-1]).all())
+        flag = torch.tensor([int(inv_ok), n_loc], device=device, dtype=torch.int64)
+        dist.all_reduce(flag, op=dist.ReduceOp.SUM)
+        assert int(flag[0]) == world, "full-size shards: sortedness / rowptr / csr2csc invariants violated"
+        parity["full_size_invariants"] = {"strictly_sorted_shards": True, "rowptr_closes": True,
+                                          "csr2csc_sorts_columns": True, "total_nnz_out": int(flag[1])}
+        del A_full, st, key, o_row, o_col, o_val
 
     line = {
         "metric": "coalesce+CSR/CSC build nnz/s", "value": value, "unit": "nnz/s", "n_gpus": world,
         "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "int64 keys + f32 values", "data": "synthetic",
         "config": workload_config(world), "clocks": clocks.summary(), "e2e": e2e,
-        "gpu_launches": launches,
+        "gpu_launches": launches, "parity_checked": bool(parity.get("passed")), "parity": parity,
         "kernels_ms_per_step": {k: round(v[0] / args.steps, 4) for k, v in sorted(prof.items(), key=lambda kv: -kv[1][0])},
         "ms_per_step_with_kernel_events": ms_prof,
     }
@@ -438,12 +648,8 @@ def run_ours(args):
             "frac_of_measured_hbm": PIPELINE_BYTES_PER_NNZ * value / 1e9 / hbm_peak,
             "frac_of_nominal_8TBps": PIPELINE_BYTES_PER_NNZ * value / 1e9 / 8000.0,
         }
-        if rank == 0 and not args.no_cpu:
-            dt, kind = cpu_pipeline_sample(CPU_SAMPLE_NNZ)
-            line["cpu_baseline"] = {
-                "value": CPU_SAMPLE_NNZ / dt, "unit": "nnz/s", "cores": 1, "kind": kind,
-                "sample": f"first {CPU_SAMPLE_NNZ} entries of the same stream at full sparse sizes, one pass ({dt:.1f} s)",
-                "host_cores_available": os.cpu_count()}
+        if cpu_baseline is not None:
+            line["cpu_baseline"] = cpu_baseline
     if world > 1:
         # SURVEY.md 8e combined roofline: local figure-A bytes / HBM peak + bytes sent per GPU / NVLink (770 GB/s
         # measured peer copy per direction, B200_PROFILING.md; 900 nominal)
@@ -455,9 +661,14 @@ def run_ours(args):
             "unit": "GB/s", "frac": t_roof_ms / ms, "traffic": None, "peak_source": peak_src,
             "t_roof_ms": t_roof_ms, "max_tuples_sent_per_gpu": int(sent[0]), "max_tuples_received_per_gpu": int(sent[1]),
             "nvlink_GBps_per_direction": 770.0,
+            "exchange_ms": exchange_ms, "single_gpu_same_shape_ms": local_ms,
+            "exchange_GBps_per_direction": sent_bytes / (exchange_ms * 1e-3) / 1e9,
+            "scaling_anchor": "single_gpu_same_shape_ms = one GPU building one shard of this shape (the tuples the rank "
+                              "owns, no exchange); efficiency = single_gpu_same_shape_ms / ms_per_step",
             "note": "frac = (local figure-A bytes / HBM peak + bytes sent / NVLink peak) / measured step time",
         }
     if rank == 0:
+        assert line["parity_checked"], "no bench line without a passed parity gate"
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
@@ -469,7 +680,11 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
+    ap.add_argument("--no-cpu", action="store_true",
+                    help="profiling runs: no cpu_baseline; the parity gate runs on a 4 M-entry prefix")
+    ap.add_argument("--quick-cpu", action="store_true",
+                    help="CPU legs (parity gate, cpu_baseline, reference arm) on an 8 M-entry prefix instead of the "
+                         "full configuration")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

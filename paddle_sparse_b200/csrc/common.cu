@@ -76,6 +76,15 @@ int hybrid_variant() {
   return v;
 }
 
+int csc_variant() {
+  static int v = -1;
+  if (v < 0) {
+    const char *e = getenv("PS_CSC_HYBRID");
+    v = e ? atoi(e) : 1;
+  }
+  return v;
+}
+
 int sm_count() {
   static int cached[64] = {0};
   int dev = 0;

@@ -171,19 +171,42 @@ struct RsSmem {
   static constexpr int ROW = RADIX / 2 + 1;  // counter row in 32-bit words: odd stride, so a column read is conflict-free
   KeyT keys[TILE];
   uint32_t pay[NPAY > 0 ? NPAY : 1][TILE];
-  uint32_t pay_in[(PREFETCH && NPAY > 0) ? NPAY : 1][(PREFETCH && NPAY > 0) ? TILE : 1];
+  // landing zone of the bulk asynchronous copies (TMA, cp.async.bulk): 16-byte aligned, completion on `mbar`
+  alignas(16) uint32_t pay_in[(PREFETCH && NPAY > 0) ? NPAY : 1][(PREFETCH && NPAY > 0) ? TILE : 4];
+  alignas(8) uint64_t mbar;
   uint32_t cnt[WARPS][ROW];  // two 16-bit counters per word: items of (warp, digit); later the group's start in the tile
   uint32_t gbase[RADIX];     // global position of the digit's run minus its offset inside the tile
   uint32_t scan_tmp[32];
   long long tile_next;
 };
 
-__device__ __forceinline__ void cp_async4(void *smem_dst, const void *gsrc) {
-  const unsigned sa = (unsigned)__cvta_generic_to_shared(smem_dst);
-  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sa), "l"(gsrc) : "memory");
+// ---- bulk asynchronous copy global -> shared (the 1-D form of TMA; SASS: UBLKCP) completing on an mbarrier.  One
+// elected thread arms the barrier with the byte count and issues the copies; the data path involves no thread, no
+// register and no LSU slot.  Source, destination and size must be multiples of 16 bytes.
+__device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t *bar, unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
 }
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_copy_g2s(void *smem_dst, const void *gsrc, unsigned bytes, uint64_t *bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   smem_u32(smem_dst)),
+               "l"(__cvta_generic_to_global(gsrc)), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, unsigned parity) {
+  unsigned ok;
+  do {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+  } while (!ok);
+}
 
 // Tile loads with the (uniform) mode switch hoisted out of the unrolled loops.
 template <typename KeyT, int ITEMS>
@@ -261,6 +284,7 @@ __device__ __forceinline__ void load_tile_pay_sync(const PaySrc &s, int64_t tile
 __device__ __forceinline__ uint64_t rs_lb_word(const uint64_t *stw, int radix, int64_t t, int epoch) {
   return t >= 0 ? TileState::load(stw + t * radix) : RsState::pack(epoch, RsState::PREFIX, 0);
 }
+constexpr int RS_LB_WORDS = 8;  // status words one lane requests per round trip (GS * RS_LB_WORDS tiles per round)
 template <int DPW>
 __device__ __forceinline__ uint32_t rs_lb_finish(const uint64_t *stw, int radix, int64_t tile, int epoch, uint64_t w0,
                                                  unsigned lane) {
@@ -278,14 +302,20 @@ __device__ __forceinline__ uint32_t rs_lb_finish(const uint64_t *stw, int radix,
   };
 #pragma unroll
   for (int r = 0; r < GS; ++r) consume(__shfl_sync(0xffffffffu, w0, lk + r * DPW));
+  // With one big tile per SM the CTAs run almost in lock step: when a tile looks back, its ~SM-count predecessors
+  // have published aggregates but no prefix yet, so the walk is long and its cost is round trips to L2.  Every lane
+  // therefore keeps RS_LB_WORDS loads in flight per round (round 2 timeline: the look-back was 23 % of a tile's
+  // time with two).
   while (!__all_sync(0xffffffffu, done)) {
-    const uint64_t u0 = done ? 0 : rs_lb_word(stw, radix, t - (int64_t)lr, epoch);
-    const uint64_t u1 = done ? 0 : rs_lb_word(stw, radix, t - (int64_t)lr - GS, epoch);
+    uint64_t u[RS_LB_WORDS];
+#pragma unroll
+    for (int w = 0; w < RS_LB_WORDS; ++w) u[w] = done ? 0 : rs_lb_word(stw, radix, t - (int64_t)lr - w * GS, epoch);
     stuck = false;
 #pragma unroll
-    for (int r = 0; r < GS; ++r) consume(__shfl_sync(0xffffffffu, u0, lk + r * DPW));
+    for (int w = 0; w < RS_LB_WORDS; ++w) {
 #pragma unroll
-    for (int r = 0; r < GS; ++r) consume(__shfl_sync(0xffffffffu, u1, lk + r * DPW));
+      for (int r = 0; r < GS; ++r) consume(__shfl_sync(0xffffffffu, u[w], lk + r * DPW));
+    }
   }
   return (uint32_t)excl;
 }
@@ -342,32 +372,49 @@ rs_pass_kernel(KeySrc ksrc, PaySrcN<NPAY> psrc, KeyDst kdst, PayDstN<NPAY> pdst,
 
   // request one tile: keys into registers, u32 payload words towards pay_in
   KeyT key[ITEMS];
-  auto request = [&](int64_t t) {
+  // u32 payload words of a FULL tile whose source is 16-byte aligned arrive by bulk asynchronous copy (one thread
+  // issues, the mbarrier counts the bytes); other tiles / sources are read by the threads in the staging phase
+  bool pay_bulk[NPAY > 0 ? NPAY : 1];
+#pragma unroll
+  for (int p = 0; p < (NPAY > 0 ? NPAY : 1); ++p)
+    pay_bulk[p] = PREFETCH && NPAY > 0 && psrc.s[p].mode == PSRC_U32 &&
+                  (reinterpret_cast<uintptr_t>(psrc.s[p].p) & 15u) == 0;
+  auto bulk_tile = [&](int64_t t) { return PREFETCH && NPAY > 0 && t < tiles && (n - t * TILE) >= TILE; };
+  auto request_keys = [&](int64_t t) {
     const int64_t tb = t * TILE;
     const int tn = (int)((n - tb) < TILE ? (n - tb) : TILE);
     load_tile_keys<KeyT, ITEMS>(ksrc, tb, warp_base, lane, tn, key);
-    if (PREFETCH && NPAY > 0) {
-#pragma unroll
-      for (int p = 0; p < NPAY; ++p) {
-        if (psrc.s[p].mode == PSRC_U32) {
-          const uint32_t *src = reinterpret_cast<const uint32_t *>(psrc.s[p].p) + tb;
-#pragma unroll
-          for (int i = 0; i < ITEMS; ++i) {
-            const int j = warp_base + i * 32 + lane;
-            if (j < tn) cp_async4(&sm.pay_in[p][j], src + j);
-          }
-        }
-      }
-      cp_async_commit();
-    }
   };
+  auto request_pay = [&](int64_t t) {  // thread 0 only, after every read of pay_in of the previous tile
+    if (!bulk_tile(t)) return;
+    unsigned bytes = 0;
+#pragma unroll
+    for (int p = 0; p < NPAY; ++p) bytes += pay_bulk[p] ? (unsigned)(TILE * sizeof(uint32_t)) : 0u;
+    if (bytes == 0) return;
+    mbar_expect_tx(&sm.mbar, bytes);
+#pragma unroll
+    for (int p = 0; p < NPAY; ++p)
+      if (pay_bulk[p])
+        bulk_copy_g2s(&sm.pay_in[p][0], reinterpret_cast<const uint32_t *>(psrc.s[p].p) + t * TILE,
+                      (unsigned)(TILE * sizeof(uint32_t)), &sm.mbar);
+  };
+  unsigned mbar_phase = 0;
+  bool any_bulk = false;
+#pragma unroll
+  for (int p = 0; p < (NPAY > 0 ? NPAY : 1); ++p) any_bulk = any_bulk || pay_bulk[p];
 
   long long ticket_ahead = 0;  // thread 0: the ticket drawn one tile ahead
-  if (tid == 0) sm.tile_next = (long long)atomicAdd(ticket, 1ull);
+  if (tid == 0) {
+    sm.tile_next = (long long)atomicAdd(ticket, 1ull);
+    if (PREFETCH && NPAY > 0) mbar_init(&sm.mbar, 1);
+  }
   __syncthreads();
   int64_t tile = sm.tile_next;
-  if (tile < tiles) request(tile);
-  if (tid == 0) ticket_ahead = (long long)atomicAdd(ticket, 1ull);
+  if (tile < tiles) request_keys(tile);
+  if (tid == 0) {
+    if (any_bulk) request_pay(tile);
+    ticket_ahead = (long long)atomicAdd(ticket, 1ull);
+  }
   PS_TL_DECL;
 
   while (tile < tiles) {
@@ -448,11 +495,15 @@ rs_pass_kernel(KeySrc ksrc, PaySrcN<NPAY> psrc, KeyDst kdst, PayDstN<NPAY> pdst,
     for (int i = 0; i < ITEMS; ++i) sm.keys[rank[i]] = key[i];
     PS_TL(10);
     if (NPAY > 0) {
-      if (PREFETCH) cp_async_wait_all();
+      const bool landed = any_bulk && bulk_tile(tile);  // uniform: this tile's u32 words came by bulk copy
+      if (landed) {
+        mbar_wait(&sm.mbar, mbar_phase);
+        mbar_phase ^= 1u;
+      }
 #pragma unroll
       for (int p = 0; p < NPAY; ++p) {
         uint32_t pv[ITEMS];
-        if (PREFETCH && psrc.s[p].mode == PSRC_U32) {
+        if (landed && pay_bulk[p]) {
 #pragma unroll
           for (int i = 0; i < ITEMS; ++i) pv[i] = sm.pay_in[p][warp_base + i * 32 + lane];
         } else if (psrc.s[p].mode == PSRC_U32) {
@@ -481,12 +532,13 @@ rs_pass_kernel(KeySrc ksrc, PaySrcN<NPAY> psrc, KeyDst kdst, PayDstN<NPAY> pdst,
     PS_TL(9);
     // the registers are free again: request the next tile now, its latency hides behind look-back and scatter
     const int64_t next = sm.tile_next;
-    if (next < tiles) request(next);
+    if (next < tiles) request_keys(next);
     if (tid == 0) ticket_ahead = (long long)atomicAdd(ticket, 1ull);
 
     PS_TL(6);
     __syncthreads();
     PS_TL(7);
+    if (tid == 0 && any_bulk) request_pay(next);  // every thread is past its reads of pay_in: the buffer is free
 
     // ---- 6: coalesced scatter: consecutive staged slots of one digit go to consecutive addresses
     const bool full = tile_n == TILE;

@@ -13,8 +13,119 @@
 #include "convert.cuh"
 #include "radix_sort.cuh"
 #include "segment.cuh"
+#include "csc_local.cuh"
 
 namespace ps {
+
+int csc_variant();  // PS_CSC_HYBRID=0 disables the hybrid CSC sort (bench knob)
+
+// The hybrid CSC sort (csc_local.cuh).  *used = false (nothing written) when the shape rules it out; the caller then
+// runs the LSD pipeline.  `t_row / t_col / t_val` null: csr2csc + colptr / colcount only.
+static int csc_hybrid(const int64_t *row, const int64_t *col, const void *value, int64_t n, int64_t N,
+                      int64_t *out_csr2csc, int64_t *out_colptr, int64_t *out_colcount, int64_t *t_row, int64_t *t_col,
+                      void *t_val, bool *used, cudaStream_t s) {
+  *used = false;
+  const int cbits = bits_for(N);
+  if (!csc_variant() || n < (int64_t(1) << 16) || cbits < 2) return PS_OK;
+  // The low L <= 8 col bits are sorted locally, the top T = cbits - L select a bucket of 2^L columns.  L is the largest
+  // width whose AVERAGE bucket (n * 2^L / N entries: only N of the 2^cbits key values exist) still fills at most 90 % of
+  // a CTA's capacity; larger buckets (skew) are cut into chunks by the kernels.
+  int L = CL_MAX_L < cbits - 1 ? CL_MAX_L : cbits - 1;
+  while (L > 0 && (double)n * (double)(int64_t(1) << L) / (double)(N > 0 ? N : 1) > 0.9 * CL_CAP) --L;
+  const int T = cbits - L;
+  if (T > CL_MAX_T || T < 1) return PS_OK;
+  const SortPlan gp = make_sort_plan(T, rs_geometry<uint32_t, 3>().rbits);
+  if (gp.passes > 2) return PS_OK;
+  const bool carry = t_row != nullptr;
+  const int nb = 1 << T;
+  ClPlan plan;
+  plan.passes = gp.passes;
+  for (int p = 0; p < gp.passes; ++p) { plan.pbegin[p] = gp.begin[p]; plan.pbits[p] = gp.bits[p]; }
+
+  Scratch scratch(s);
+  const size_t max_chunks = (size_t)nb + (size_t)(n / CL_CAP) + 1;
+  PS_SCRATCH(gcount, scratch, unsigned int, nb);
+  PS_SCRATCH(bucket_off, scratch, unsigned int, (size_t)nb + 1);
+  PS_SCRATCH(chunk_start, scratch, unsigned int, (size_t)nb + 1);
+  PS_SCRATCH(chunk_bucket, scratch, unsigned int, max_chunks);
+  PS_SCRATCH(multi_list, scratch, unsigned int, nb);
+  PS_SCRATCH(ghist, scratch, unsigned long long, 2 * RS_MAX_RADIX);
+  PS_SCRATCH(info, scratch, ClInfo, 1);
+  PS_SCRATCH(ticket, scratch, unsigned long long, 1);
+  PS_CUDA(cudaMemsetAsync(gcount, 0, sizeof(unsigned int) * (size_t)nb, s));
+  PS_CUDA(cudaMemsetAsync(ticket, 0, sizeof(unsigned long long), s));
+  {
+    PS_FUNC_SMEM(cl_bucket_hist_kernel, sizeof(unsigned int) << CL_MAX_T);
+    ProfScope prof(PROF_BUCKET_HIST, s);
+    cl_bucket_hist_kernel<<<sm_count() * (T <= 14 ? 2 : 1), 1024, sizeof(unsigned int) * (size_t)nb, s>>>(col, n, L, (unsigned)nb,
+                                                                                                         gcount);
+  }
+  PS_LAUNCH_OK();
+  cl_plan_kernel<<<1, 1024, 0, s>>>(gcount, nb, plan, bucket_off, chunk_start, chunk_bucket, multi_list, ghist, info);
+  PS_LAUNCH_OK();
+
+  // global passes on col bits [L, cbits): (col, entry index[, row, value]) -> u32 arrays in bucket order
+  PS_SCRATCH(scol, scratch, uint32_t, n);
+  PS_SCRATCH(sp, scratch, uint32_t, n);
+  PS_SCRATCH(k0, scratch, uint32_t, n);
+  uint32_t *srow = nullptr, *sval = nullptr;
+  if (carry) {
+    PS_SCRATCH(a0, scratch, uint32_t, n);
+    PS_SCRATCH(a1, scratch, uint32_t, n);
+    PS_SCRATCH(srow_, scratch, uint32_t, n);
+    srow = srow_;
+    uint32_t *t0[3] = {a0, a1, nullptr}, *t1[3] = {nullptr, nullptr, nullptr};
+    if (value) {
+      PS_SCRATCH(a2, scratch, uint32_t, n);
+      PS_SCRATCH(sval_, scratch, uint32_t, n);
+      t0[2] = a2;
+      sval = sval_;
+    }
+    PaySrcN<3> ps_;
+    ps_.s[0] = PaySrc{nullptr, PSRC_IOTA};
+    ps_.s[1] = PaySrc{row, PSRC_I64};
+    ps_.s[2] = value ? PaySrc{value, PSRC_U32} : PaySrc{nullptr, PSRC_NONE};
+    PayDstN<3> pd;
+    pd.d[0] = PayDst{sp, PDST_U32};
+    pd.d[1] = PayDst{srow, PDST_U32};
+    pd.d[2] = value ? PayDst{sval, PDST_U32} : PayDst{nullptr, PDST_NONE};
+    PS_TRY((radix_sort_tuples<uint32_t, 3>(KeySrc{col, nullptr, KSRC_I64, 0}, ps_, n, T, k0, nullptr, t0, t1,
+                                           KeyDst{scol, nullptr, KDST_KEYS, 0}, pd, scratch, s, L, ghist)));
+  } else {
+    PS_SCRATCH(a0, scratch, uint32_t, n);
+    PS_TRY(radix_sort_pairs<uint32_t>(KeySrc{col, nullptr, KSRC_I64, 0}, PaySrc{nullptr, PSRC_IOTA}, n, T, k0, nullptr, a0,
+                                      nullptr, KeyDst{scol, nullptr, KDST_KEYS, 0}, PayDst{sp, PDST_U32}, scratch, s, L,
+                                      ghist));
+  }
+
+  // oversized buckets (hub columns) only: per-chunk digit offsets
+  PS_SCRATCH(chunk_hist, scratch, unsigned int, max_chunks * 256);
+  cl_chunk_hist_kernel<<<sm_count() * 8, 256, 0, s>>>(scol, bucket_off, chunk_start, chunk_bucket, info, (1u << L) - 1u,
+                                                     chunk_hist);
+  PS_LAUNCH_OK();
+  cl_chunk_scan_kernel<<<sm_count() * 2, 256, 0, s>>>(bucket_off, chunk_start, multi_list, info, L, N, chunk_hist,
+                                                     out_colptr, out_colcount);
+  PS_LAUNCH_OK();
+
+  const size_t smem = sizeof(ClSmem);
+  int grid = sm_count() * 4;
+#define PS_CL(C_, V_)                                                                                              \
+  do {                                                                                                             \
+    auto kern = cl_local_kernel<C_, V_>;                                                                           \
+    PS_FUNC_SMEM(kern, smem);                                                                                      \
+    ProfScope prof(PROF_LOCAL_SORT, s);                                                                            \
+    kern<<<grid, CL_THREADS, smem, s>>>(scol, sp, srow, sval, bucket_off, chunk_start, chunk_bucket, chunk_hist,  \
+                                       info, nb, L, N, out_csr2csc, out_colptr, out_colcount, t_row, t_col,      \
+                                       reinterpret_cast<uint32_t *>(t_val), ticket);                              \
+  } while (0)
+  if (carry && value) PS_CL(true, true);
+  else if (carry) PS_CL(true, false);
+  else PS_CL(false, false);
+#undef PS_CL
+  PS_LAUNCH_OK();
+  *used = true;
+  return PS_OK;
+}
 
 __global__ void __launch_bounds__(256)
 invert_perm_kernel(const int64_t *__restrict__ perm, int64_t n, int64_t *__restrict__ out) {
@@ -145,6 +256,11 @@ int ps_csr2csc(const int64_t *col, int64_t nnz, int64_t N, int64_t *out_csr2csc,
     if (out_colcount && N > 0) PS_CUDA(cudaMemsetAsync(out_colcount, 0, sizeof(int64_t) * (size_t)N, s));
     return PS_OK;
   }
+  {
+    bool used = false;
+    PS_TRY(csc_hybrid(nullptr, col, nullptr, nnz, N, out_csr2csc, colptr, out_colcount, nullptr, nullptr, nullptr, &used, s));
+    if (used) return PS_OK;
+  }
   const int cbits = bits_for(N);
   PS_SCRATCH(k0, scratch, uint32_t, nnz);
   PS_SCRATCH(k1, scratch, uint32_t, nnz);
@@ -187,6 +303,14 @@ int ps_csc_build(const int64_t *row, const int64_t *col, const void *value, int6
     if (want_ptr) PS_CUDA(cudaMemsetAsync(colptr, 0, sizeof(int64_t) * (size_t)(N + 1), s));
     if (out_colcount && N > 0) PS_CUDA(cudaMemsetAsync(out_colcount, 0, sizeof(int64_t) * (size_t)N, s));
     return PS_OK;
+  }
+  {  // hybrid: two global passes on the top col bits, one local pass that writes every output
+    bool used = false;
+    PS_TRY(csc_hybrid(row, col, value, nnz, N, out_csr2csc, colptr, out_colcount, out_t_row, out_t_col, out_t_value, &used, s));
+    if (used) {
+      if (out_csc2csr) PS_TRY(invert_perm_impl(out_csr2csc, nnz, out_csc2csr, s));
+      return PS_OK;
+    }
   }
   // stable sort by col of (col | entry index, row, value bits): the last pass writes the transposed arrays directly
   const int cbits = bits_for(N);

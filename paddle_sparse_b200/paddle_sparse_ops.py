@@ -195,7 +195,7 @@ def _import(obj, name: str, stream: int) -> _View:
     if t.dtype.lanes != 1:
         v.release()
         raise TypeError(f"paddle_sparse_ops: `{name}` has a vector dtype")
-    if t.strides:  # NULL strides = compact row-major
+    if t.strides and v.numel > 0:  # NULL strides = compact row-major; an empty array has no layout to check
         expect = 1
         for i in range(t.ndim - 1, -1, -1):
             if v.shape[i] != 1 and int(t.strides[i]) != expect:
@@ -216,14 +216,12 @@ def _check_index(v: _View, name: str, ndim: int = 1) -> None:
 
 
 # ------------------------------------------------------------------------------------------------ exporting
-_live = {}  # id -> everything a handed-out DLManagedTensor points at (kept until its deleter runs)
+_live = {}  # address of a handed-out DLManagedTensor -> everything it points at (kept until its deleter runs)
 
 
 @_DELETER
 def _release_export(mptr):
-    rec = _live.pop(ctypes.addressof(mptr.contents), None)
-    if rec is not None:
-        rec["owner"]._unref()
+    _live.pop(ctypes.addressof(mptr.contents), None)  # drops the record's reference to the block
 
 
 @_CAPSULE_DTOR
@@ -235,41 +233,33 @@ def _capsule_dropped(capsule_ptr):
             m.contents.deleter(m)
 
 
+class _Block:
+    """One allocation of the shim's allocator (or a host buffer).  Released - ps_free, ordered on the stream it was
+    produced on - when the last DeviceArray and the last exported DLPack capsule that refer to it are gone."""
+
+    def __init__(self, ptr: int, device_type: int, stream: int, host_buffer=None):
+        self.ptr, self.device_type, self.stream, self.host_buffer, self.freed = int(ptr), device_type, stream, host_buffer, False
+
+    def __del__(self):
+        if not self.freed:
+            self.freed = True
+            if self.device_type == kDLCUDA and self.host_buffer is None and self.ptr:
+                try:
+                    _lib.lib().ps_free(ctypes.c_void_p(self.ptr), ctypes.c_void_p(self.stream))
+                except Exception:  # interpreter shutdown
+                    pass
+
+
 class DeviceArray:
-    """A device (or host) block owned by the shim, exported zero-copy through the DLPack protocol.  `base` shares
-    another DeviceArray's block (a slice); the block is released (ps_free, ordered on the stream it was produced
-    on) when the last DeviceArray and the last exported capsule referring to it are gone."""
+    """A view of a block owned by the shim, exported zero-copy through the DLPack producer protocol
+    (``__dlpack__`` / ``__dlpack_device__``); 1-D contiguous slices share the block."""
 
     def __init__(self, ptr: int, shape: Sequence[int], dtype: str, device_type: int, device_id: int, stream: int = 0,
                  base: "Optional[DeviceArray]" = None, host_buffer=None):
         self.ptr, self.shape, self.dtype = int(ptr), tuple(int(s) for s in shape), dtype
         self.device_type, self.device_id, self.stream = device_type, device_id, stream
-        self._root = base._root if base is not None else self
-        self._host_buffer = host_buffer
-        if base is None:
-            self._refs = 0
-            self._freed = False
-        self._root._refs += 1
-        self._alive = True
+        self._block = base._block if base is not None else _Block(ptr, device_type, stream, host_buffer)
 
-    # -- lifetime
-    def _unref(self) -> None:
-        root = self._root
-        root._refs -= 1
-        if root._refs == 0 and not root._freed:
-            root._freed = True
-            if root.device_type == kDLCUDA and root._host_buffer is None and root.ptr:
-                try:
-                    _lib.lib().ps_free(ctypes.c_void_p(root.ptr), ctypes.c_void_p(root.stream))
-                except Exception:  # interpreter shutdown
-                    pass
-
-    def __del__(self):
-        if getattr(self, "_alive", False):
-            self._alive = False
-            self._unref()
-
-    # -- array-ish conveniences
     @property
     def nbytes(self) -> int:
         n = _DTYPES[self.dtype][2]
@@ -286,14 +276,13 @@ class DeviceArray:
         lo, hi, _ = key.indices(self.shape[0])
         hi = max(hi, lo)
         return DeviceArray(self.ptr + lo * _DTYPES[self.dtype][2], (hi - lo,), self.dtype, self.device_type,
-                           self.device_id, self.stream, base=self, host_buffer=self._root._host_buffer)
+                           self.device_id, self.stream, base=self)
 
     def tolist(self):
         """Host copy as a Python list (synchronises; for tests and small results)."""
-        code, bits, size = _DTYPES[self.dtype]
         if self.dtype != "int64":
             raise TypeError("tolist() is implemented for int64 arrays")
-        n = self.nbytes // size
+        n = self.nbytes // 8
         buf = (ctypes.c_int64 * max(n, 1))()
         if n:
             if self.device_type == kDLCUDA:
@@ -314,7 +303,7 @@ class DeviceArray:
 
     def __dlpack__(self, stream=None, **_):
         # the data was produced on self.stream; a consumer on another stream is ordered behind it here
-        if self.device_type == kDLCUDA and stream is not None and stream not in (-1,):
+        if self.device_type == kDLCUDA and stream is not None and stream != -1:
             want = 0 if stream in (1, 2) else int(stream)
             if want != self.stream:
                 _lib.call("ps_stream_sync", ctypes.c_void_p(self.stream))
@@ -330,8 +319,7 @@ class DeviceArray:
         m.dl_tensor.byte_offset = 0
         m.manager_ctx = None
         m.deleter = _release_export
-        self._root._refs += 1
-        _live[ctypes.addressof(m)] = {"m": m, "shape": shape, "owner": self}
+        _live[ctypes.addressof(m)] = {"m": m, "shape": shape, "block": self._block}
         return _py.PyCapsule_New(ctypes.addressof(m), _NAME, _capsule_dropped)
 
 

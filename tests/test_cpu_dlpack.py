@@ -63,14 +63,19 @@ def test_host_tensors_are_refused():
 
 
 def test_device_array_slices_share_one_block():
+    import sys
     buf = (pso.ctypes.c_int64 * 6)(*range(6))
     a = pso.DeviceArray(pso.ctypes.addressof(buf), (6,), "int64", pso.kDLCPU, 0, host_buffer=buf)
+    block = a._block
     b = a[2:5]
-    assert b.tolist() == [2, 3, 4] and len(b) == 3 and a._refs == 2
+    assert b.tolist() == [2, 3, 4] and len(b) == 3 and b._block is block
     t = torch.from_dlpack(b)
-    assert t.tolist() == [2, 3, 4] and a._refs == 3
-    del b, t
+    assert t.tolist() == [2, 3, 4] and len(pso._live) == 1
+    del a, b
     gc.collect()
-    assert a._refs == 1 and not pso._live
+    assert not block.freed and t.tolist() == [2, 3, 4]  # the consumer's capsule keeps the block alive
+    del t
+    gc.collect()
+    assert not pso._live and sys.getrefcount(block) == 2  # only `block` itself (+ the call's temporary) is left
     with pytest.raises(IndexError):
-        a[::2]
+        pso.DeviceArray(pso.ctypes.addressof(buf), (6,), "int64", pso.kDLCPU, 0, host_buffer=buf)[::2]

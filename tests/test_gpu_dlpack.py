@@ -161,12 +161,13 @@ def test_sample_adj_matches_the_operator_layer(ops):
 def test_outputs_release_their_blocks():
     t = dev(np.arange(1000, dtype=I64))
     out = pso.ind2ptr(t, 1000)
-    root = out._root
+    block = out._block
     view = torch.from_dlpack(out)
-    assert root._refs == 2
     del out
     gc.collect()
-    assert root._refs == 1 and not root._freed and view[-1].item() == 999
+    assert not block.freed and view[-1].item() == 1000  # the consumer's capsule keeps the block alive
     del view
     gc.collect()
-    assert root._freed and not pso._live
+    assert not pso._live and not block.freed
+    del block
+    gc.collect()  # the last reference: _Block.__del__ hands the memory back (ps_free, stream-ordered)
