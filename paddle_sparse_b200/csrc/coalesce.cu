@@ -29,6 +29,7 @@ template <> __device__ __forceinline__ __half pay_as<__half>(uint32_t p) { retur
 
 }  // namespace ps
 #include "local_sort.cuh"
+#include "local_sort2.cuh"
 namespace ps {
 
 // One tile = THREADS*ITEMS consecutive sorted entries, held in shared memory; thread t looks at entries
@@ -266,10 +267,28 @@ static int check_value_args(const void *value, const void *out_value, int dtype,
 // out; the caller then runs the plain LSD pipeline.  One extra host read (the largest bucket) decides.
 int hybrid_variant();  // PS_HYBRID=0 disables (bench knob)
 
+int ls_variant();  // PS_LS_VARIANT: 2 (default) = counting pass + in-bin compare (local_sort2.cuh), 1 = four LSD passes
+
+static int ls_cap() { return ls_variant() == 1 ? LS_CAP : L2_CAP; }
+
 template <typename T, int RED, bool HAS_VALUE, bool DEDUP>
 static int ls_launch(const uint32_t *lowkeys, const uint32_t *lowvals, const unsigned int *bucket_off, int nb, int R,
                      int cbits, int64_t M, int64_t *out_row, int64_t *out_col, void *out_value, int64_t *out_rowptr,
                      uint64_t *state, long long *d_nnz, cudaStream_t s) {
+  if (ls_variant() != 1) {
+    auto kern = ls2_sort_dedup_kernel<T, RED, HAS_VALUE, DEDUP>;
+    const size_t smem = sizeof(L2Smem<HAS_VALUE>);
+    PS_FUNC_SMEM(kern, smem);
+    int grid = sm_count() * 2;
+    if (grid > nb) grid = nb;
+    {
+      ProfScope prof(PROF_LOCAL_SORT, s);
+      kern<<<grid, L2_THREADS, smem, s>>>(lowkeys, lowvals, bucket_off, nb, R, cbits, M, out_row, out_col,
+                                         reinterpret_cast<T *>(out_value), out_rowptr, state, d_nnz);
+    }
+    PS_LAUNCH_OK();
+    return PS_OK;
+  }
   auto kern = ls_sort_dedup_kernel<T, RED, HAS_VALUE, DEDUP>;
   const size_t smem = sizeof(LsSmem<HAS_VALUE>);
   PS_FUNC_SMEM(kern, smem);
@@ -284,22 +303,23 @@ static int ls_launch(const uint32_t *lowkeys, const uint32_t *lowvals, const uns
   return PS_OK;
 }
 
-// The hybrid plan for (nnz, rbits, cbits): T top key bits select a bucket, the low R = K - T bits are sorted inside
-// it.  Returns false when the hybrid path does not apply (narrow keys, tiny inputs, R > 32, > 2 global passes).
+// The hybrid plan for (nnz, M, rbits, cbits): T top key bits select a bucket (a whole range of 2^(rbits - T) rows), the
+// low R = K - T bits are sorted inside it.  T is the smallest width whose AVERAGE bucket - nnz * 2^(rbits - T) / M
+// entries: only M of the 2^rbits row values exist - fills at most 90 % of a CTA's capacity.  Returns false when the
+// hybrid path does not apply (narrow keys, tiny inputs, R > 32, T > 15, more than two global passes).
 struct HybridPlan {
   int T, R, K, nb;
   LsPlan lp;
 };
-static bool hybrid_plan(int64_t nnz, int rbits, int cbits, HybridPlan *hp) {
+static bool hybrid_plan(int64_t nnz, int64_t M, int rbits, int cbits, HybridPlan *hp) {
   const int K = rbits + cbits;
   if (!hybrid_variant() || nnz < (int64_t(1) << 16) || K <= 32) return false;
-  // T: buckets of about LS_CAP / 2 entries on average; a bucket must be a whole range of rows (T <= rbits)
-  int T = bits_for(ceil_div(nnz, LS_CAP / 2));
-  if (T < K - 32) T = K - 32;  // the bucket-local key must fit 32 bits
-  if (T > LS_MAX_T) T = LS_MAX_T;
-  if (T > rbits) T = rbits;
+  const int cap = ls_cap();
+  int T = K - 32 > 1 ? K - 32 : 1;  // the bucket-local key must fit 32 bits
+  const int tmax = LS_MAX_T < rbits ? LS_MAX_T : rbits;
+  while (T <= tmax && (double)nnz * (double)(int64_t(1) << (rbits - T)) / (double)(M > 0 ? M : 1) > 0.9 * cap) ++T;
+  if (T > tmax) return false;
   const int R = K - T;
-  if (T < 1 || R > 32 || nnz / (int64_t(1) << T) > LS_CAP * 3 / 4) return false;
   const SortPlan gp = make_sort_plan(T, rs_geometry<uint64_t, 1>().rbits);  // the plan radix_sort_pairs will use
   if (gp.passes > 2) return false;
   hp->T = T;
@@ -336,8 +356,9 @@ static int hybrid_coalesce(const int64_t *row, const int64_t *col, int64_t nnz, 
                            const LsInspect *pre, int64_t pre_max_bucket, cudaStream_t s) {
   *used = false;
   HybridPlan hp;
-  if (!hybrid_plan(nnz, rbits, cbits, &hp)) return PS_OK;
-  const int T = hp.T, R = hp.R, nb = hp.nb;
+  if (!hybrid_plan(nnz, M, rbits, cbits, &hp)) return PS_OK;
+  const int T = hp.T, R = hp.R;
+  int nb = hp.nb;
   Scratch scratch(s);
   const LsInspect *st = pre;
   unsigned int h_max = 0;
@@ -349,7 +370,7 @@ static int hybrid_coalesce(const int64_t *row, const int64_t *col, int64_t nnz, 
     PS_TRY(read_back(&h_max, own->max_bucket, sizeof(h_max), s));
     st = own;
   }
-  if (h_max > (unsigned)LS_CAP) return PS_OK;  // skewed rows: the plain LSD sort handles any distribution
+  if (h_max > (unsigned)ls_cap()) return PS_OK;  // skewed rows: the plain LSD sort handles any distribution
   const unsigned int *bucket_off = st->bucket_off;
   const unsigned long long *ghist = st->ghist;
 
@@ -364,6 +385,12 @@ static int hybrid_coalesce(const int64_t *row, const int64_t *col, int64_t nnz, 
   PS_TRY(radix_sort_pairs<uint64_t>(ksrc, psrc, nnz, T, k0, nullptr, p0, nullptr, KeyDst{lowkeys, nullptr, KDST_LOW32, R},
                                     pdst, scratch, s, R, ghist));
 
+  // buckets past the one holding the largest possible key are empty: only the used ones are processed (the last of
+  // them owns the rows up to M)
+  {
+    const uint64_t top = M > 0 ? ((((uint64_t)(M - 1)) << cbits) | ((uint64_t(1) << cbits) - 1)) >> R : 0;
+    if ((int64_t)top + 1 < nb) nb = (int)top + 1;
+  }
   PS_SCRATCH(state, scratch, uint64_t, (size_t)nb + 1);
   PS_CUDA(cudaMemsetAsync(state, 0, sizeof(uint64_t) * ((size_t)nb + 1), s));
   PS_SCRATCH(d_nnz, scratch, long long, 1);
@@ -521,7 +548,7 @@ int ps_coo_inspect(const int64_t *row, const int64_t *col, int64_t nnz, int64_t 
   KeyGeom g;
   HybridPlan hp;
   if (state == nullptr || nnz >= (int64_t(1) << 32) || key_geometry(M, N, &g) != PS_OK || g.bits <= 32 ||
-      !hybrid_plan(nnz, g.rbits, g.cbits, &hp))
+      !hybrid_plan(nnz, M, g.rbits, g.cbits, &hp))
     return ps_index_max(row, nnz, col, nnz, host_out, stream);  // the plain validation pass; host_out[2] stays -1
   LsInspect *st = reinterpret_cast<LsInspect *>(state);
   PS_TRY(hybrid_inspect(row, col, nnz, g.cbits, hp, st, true, s));

@@ -76,6 +76,15 @@ int hybrid_variant() {
   return v;
 }
 
+int ls_variant() {
+  static int v = -1;
+  if (v < 0) {
+    const char *e = getenv("PS_LS_VARIANT");
+    v = e ? atoi(e) : 2;
+  }
+  return v;
+}
+
 int csc_variant() {
   static int v = -1;
   if (v < 0) {

@@ -18,7 +18,7 @@ namespace ps {
 constexpr int LS_THREADS = 1024;
 constexpr int LS_ITEMS = 8;
 constexpr int LS_CAP = LS_THREADS * LS_ITEMS;  // entries one CTA sorts in shared memory
-constexpr int LS_MAX_T = 14;                    // 2^14 bucket counters = 64 KB of shared memory in the histogram
+constexpr int LS_MAX_T = 15;                    // 2^15 bucket counters = 128 KB of shared memory in the histogram
 
 // ---- histogram of the top T key bits (bucket sizes); keys are packed on the fly from the int64 arrays.
 // With `max_rc` it is also the constructor's validation pass (storage.py:65-89: max(row), max(col)) - the same

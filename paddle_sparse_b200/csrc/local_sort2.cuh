@@ -1,0 +1,363 @@
+// Hybrid coalesce, second-generation bucket kernel (round 2).
+//
+// local_sort.cuh sorts a bucket with four stable LSD passes inside shared memory: ~120 warp instructions per 32
+// entries and pass (ncu, round 1: 923 M instructions, 1.44 ms, issue-bound).  A bucket's low keys are ~3,200 random
+// 29-bit values, so ONE counting pass on their top 12 bits already separates them into 4,096 bins of ~0.8 entries;
+// what is left is to order the few entries that share a bin, which each entry does by COMPARING itself with its
+// bin mates: final slot = bin start + #{mates with a smaller (key, arrival index)}.  The arrival index breaks ties,
+// so equal keys keep their input order (the stable order the oracle's sort gives, and the order duplicates are
+// summed in).  One counting pass + one short compare loop replace four ranked passes; 256 threads and ~50 KB per
+// CTA keep four CTAs in different phases on an SM.  Then, as before: run heads, duplicates folded in sorted order,
+// the bucket's output offset chained over the buckets (aggregate published EARLY, prefix consumed LATE), int64
+// row / col / value and the rowptr entries of the bucket's own rows written coalesced.
+//   reference behaviour: storage.py:158-171 (sort-on-construct) + :454-486 (coalesce) + :211-222 (rowptr)
+#pragma once
+#include "common.cuh"
+#include "radix_sort.cuh"
+
+namespace ps {
+
+constexpr int L2_THREADS = 512;
+constexpr int L2_ITEMS = 8;
+constexpr int L2_CAP = L2_THREADS * L2_ITEMS;  // 4,096 entries per bucket
+constexpr int L2_WARPS = L2_THREADS / 32;
+constexpr int L2_BINBITS = 12;
+constexpr int L2_BINS = 1 << L2_BINBITS;
+static_assert(L2_BINS == L2_THREADS * 8, "the bin scan gives every thread eight bins (four counter words)");
+
+struct L2Meta {
+  long long bucket;
+  unsigned int start, end;
+  int heads;
+};
+template <bool HAS_VALUE>
+struct L2Smem {
+  uint32_t skeys[2][L2_CAP];                   // sorted low keys: [slot] = bucket being sorted / awaiting its offset
+  uint32_t svals[2][HAS_VALUE ? L2_CAP : 4];   // their values
+  uint32_t wkeys[L2_CAP];                      // by bin (arrival order inside a bin)
+  uint16_t widx[L2_CAP];                       // arrival index of the entry in that slot
+  uint32_t bins[L2_BINS / 2 + 2];              // two 16-bit counters per word; after the scan: bin starts (+ sentinel)
+  uint32_t wcnt[L2_ITEMS * L2_WARPS];
+  uint32_t scan_tmp[33];
+  unsigned int maxbin, nheads;
+  long long excl;
+  L2Meta meta[2];
+};
+
+// DEDUP = false: sort only (sort-on-construct): every entry is kept, the bucket's output offset is its input offset.
+// The loop is software-pipelined over the buckets a CTA draws: bucket k is sorted and its number of distinct keys
+// PUBLISHED, then bucket k-1 - whose sorted form waits in the other half of the double buffer - reads its output
+// offset from the chain and is written out.  The chain (a decoupled look-back over the buckets) is thereby consumed
+// one whole bucket-sort after it was fed: in round 2's first version, which consumed it at once, 38 % of all warp
+// samples sat at the barrier behind the look-back warp.
+template <typename T, int RED, bool HAS_VALUE, bool DEDUP>
+__global__ void __launch_bounds__(L2_THREADS, 2)
+ls2_sort_dedup_kernel(const uint32_t *__restrict__ lowkeys, const uint32_t *__restrict__ lowvals,
+                      const unsigned int *__restrict__ bucket_off, int nb, int R, int cbits, int64_t M,
+                      int64_t *__restrict__ out_row, int64_t *__restrict__ out_col, T *__restrict__ out_value,
+                      int64_t *__restrict__ out_rowptr, uint64_t *state /*[0]=ticket,[1..]=buckets*/,
+                      long long *d_nnz_out) {
+  using A = typename Acc<T>::type;
+  constexpr int THREADS = L2_THREADS, ITEMS = L2_ITEMS, WARPS = L2_WARPS;
+  extern __shared__ __align__(16) unsigned char l2_raw[];
+  L2Smem<HAS_VALUE> &sm = *reinterpret_cast<L2Smem<HAS_VALUE> *>(l2_raw);
+  const unsigned tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+  const unsigned lt = lanemask_lt();
+  const int binshift = R > L2_BINBITS ? R - L2_BINBITS : 0;
+  const uint64_t cmask = (uint64_t(1) << cbits) - 1;
+  const uint16_t *bstart16 = reinterpret_cast<const uint16_t *>(sm.bins);
+
+  if (tid == 0) {  // the first bucket and its range
+    const long long b = (long long)atomicAdd((unsigned long long *)state, 1ull);
+    L2Meta m{b, 0u, 0u, 0};
+    if (b < nb) {
+      m.start = bucket_off[b];
+      m.end = bucket_off[b + 1];
+    }
+    sm.meta[0] = m;
+  }
+  int slot = 0;
+  bool pending = false;
+  while (true) {
+    __syncthreads();  // the previous round is completely written out; meta[slot] is filled
+    const int64_t bucket = sm.meta[slot].bucket;
+    const bool valid = bucket < nb;
+    long long nxt_bucket = 0;  // thread 0: the bucket after this one, kept in registers until the round ends
+    unsigned nxt_start = 0, nxt_end = 0;
+    if (valid) {
+      const uint32_t start = sm.meta[slot].start;
+      const int cnt = (int)(sm.meta[slot].end - start);
+      const int ie = (cnt + THREADS - 1) / THREADS;  // item rows in use (uniform)
+      uint32_t *skeys = sm.skeys[slot], *svals = sm.svals[slot];
+      // ---- A: keys and values into registers (entry j = i * THREADS + tid: its arrival index)
+      uint32_t key[ITEMS], val[HAS_VALUE ? ITEMS : 1];
+#pragma unroll
+      for (int i = 0; i < ITEMS; ++i) {
+        const int j = i * THREADS + (int)tid;
+        key[i] = (i < ie && j < cnt) ? ld_stream(lowkeys + start + j) : 0xffffffffu;
+      }
+      if (HAS_VALUE) {
+#pragma unroll
+        for (int i = 0; i < ITEMS; ++i) {
+          const int j = i * THREADS + (int)tid;
+          val[i] = (i < ie && j < cnt) ? ld_stream(lowvals + start + j) : 0u;
+        }
+      }
+      for (int q = tid; q < L2_BINS / 2 + 2; q += THREADS) sm.bins[q] = 0;
+      if (tid == 0) {
+        sm.maxbin = 0;
+        sm.nheads = 0;
+        nxt_bucket = (long long)atomicAdd((unsigned long long *)state, 1ull);
+      }
+      __syncthreads();
+      // ---- B: counting pass on the top bits of the low key; the atomic's return value is the arrival rank in the bin
+      uint32_t br[ITEMS];  // bin | rank << 16, later the entry's slot
+#pragma unroll
+      for (int i = 0; i < ITEMS; ++i) {
+        br[i] = 0;
+        if (i < ie && i * THREADS + (int)tid < cnt) {
+          const unsigned b = key[i] >> binshift;
+          const unsigned sh = (b & 1u) * 16u;
+          const unsigned r = (atomicAdd(&sm.bins[b >> 1], 1u << sh) >> sh) & 0xffffu;
+          br[i] = b | (r << 16);
+        }
+      }
+      __syncthreads();
+      // ---- C: exclusive scan of the 4,096 bin counts (8 per thread), largest bin
+      {
+        uint32_t w[4], c[8], sum = 0, mx = 0;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) w[q] = sm.bins[tid * 4 + q];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          const uint32_t t = (w[q >> 1] >> ((q & 1) * 16)) & 0xffffu;
+          mx = t > mx ? t : mx;
+          c[q] = sum;
+          sum += t;
+        }
+        uint32_t total;
+        const uint32_t base = block_exclusive_scan<uint32_t, THREADS>(sum, sm.scan_tmp, &total);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) sm.bins[tid * 4 + q] = ((c[2 * q] + base) & 0xffffu) | ((c[2 * q + 1] + base) << 16);
+        if (tid == THREADS - 1) sm.bins[L2_BINS / 2] = total & 0xffffu;  // sentinel: start of "bin 4096" = cnt
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) {
+          const uint32_t o = __shfl_xor_sync(0xffffffffu, mx, d);
+          mx = o > mx ? o : mx;
+        }
+        if (lane == 0 && mx > 1) atomicMax(&sm.maxbin, mx);
+      }
+      if (tid == 0 && nxt_bucket < nb) {
+        nxt_start = bucket_off[nxt_bucket];
+        nxt_end = bucket_off[nxt_bucket + 1];
+      }
+      __syncthreads();
+      // ---- D / E: no bin holds two entries -> the bin start IS the sorted slot.  Otherwise entries go into their bins
+      // in arrival order first, and every entry finds its slot = bin start + number of bin mates that sort before it
+      // ((key, arrival index) lexicographic: equal keys keep their input order).
+      if (sm.maxbin > 1) {
+#pragma unroll
+        for (int i = 0; i < ITEMS; ++i) {
+          if (i < ie && i * THREADS + (int)tid < cnt) {
+            const unsigned pos = (unsigned)bstart16[br[i] & 0xffffu] + (br[i] >> 16);
+            sm.wkeys[pos] = key[i];
+            sm.widx[pos] = (uint16_t)(i * THREADS + tid);
+          }
+        }
+        __syncthreads();
+#pragma unroll
+        for (int i = 0; i < ITEMS; ++i) {
+          if (i < ie && i * THREADS + (int)tid < cnt) {
+            const unsigned b = br[i] & 0xffffu;
+            const unsigned s_ = bstart16[b], e_ = bstart16[b + 1];
+            const unsigned me = (unsigned)(i * THREADS) + tid;
+            unsigned less = 0;
+            if (e_ - s_ > 1) {
+              for (unsigned t = s_; t < e_; ++t) {
+                const uint32_t k2 = sm.wkeys[t];
+                const unsigned j2 = sm.widx[t];
+                less += (k2 < key[i] || (k2 == key[i] && j2 < me)) ? 1u : 0u;
+              }
+            }
+            skeys[s_ + less] = key[i];
+            if (HAS_VALUE) svals[s_ + less] = val[i];
+          }
+        }
+      } else {
+#pragma unroll
+        for (int i = 0; i < ITEMS; ++i) {
+          if (i < ie && i * THREADS + (int)tid < cnt) {
+            const unsigned pos = (unsigned)bstart16[br[i] & 0xffffu];
+            skeys[pos] = key[i];
+            if (HAS_VALUE) svals[pos] = val[i];
+          }
+        }
+      }
+      __syncthreads();
+      // ---- F: number of distinct keys, published at once (the chain is fed as early as it can be)
+      if (DEDUP) {
+        unsigned mine = 0;
+#pragma unroll
+        for (int i = 0; i < ITEMS; ++i) {
+          if (i < ie) {
+            const int j = i * THREADS + (int)tid;
+            const bool h = j < cnt && (j == 0 || skeys[j] != skeys[j - 1]);
+            mine += __popc(__ballot_sync(0xffffffffu, h));
+          }
+        }
+        if (lane == 0 && mine) atomicAdd(&sm.nheads, mine);
+        __syncthreads();
+        if (tid == 0) {
+          const unsigned total = sm.nheads;
+          sm.meta[slot].heads = (int)total;
+          TileState::store(state + 1 + bucket,
+                           TileState::pack(bucket == 0 ? TileState::PREFIX : TileState::AGG, (uint64_t)total));
+        }
+      }
+    }
+    // ---- the bucket sorted one round ago: offset from the chain, heads ranked, output
+    if (pending) {
+      const int ps_ = slot ^ 1;
+      const int64_t pbucket = sm.meta[ps_].bucket;
+      const uint32_t start = sm.meta[ps_].start;
+      const int cnt = (int)(sm.meta[ps_].end - start);
+      const int ie = (cnt + THREADS - 1) / THREADS;
+      const uint32_t *skeys = sm.skeys[ps_], *svals = sm.svals[ps_];
+      unsigned heads = 0, below[ITEMS];
+      if (DEDUP) {
+#pragma unroll
+        for (int i = 0; i < ITEMS; ++i) {
+          below[i] = 0;
+          if (i < ie) {  // uniform
+            const int j = i * THREADS + (int)tid;
+            const bool h = j < cnt && (j == 0 || skeys[j] != skeys[j - 1]);
+            const unsigned bal = __ballot_sync(0xffffffffu, h);
+            heads |= (unsigned)h << i;
+            below[i] = __popc(bal & lt);
+            if (lane == 0) sm.wcnt[i * WARPS + warp] = __popc(bal);
+          } else if (lane == 0) {
+            sm.wcnt[i * WARPS + warp] = 0;
+          }
+        }
+        __syncthreads();
+        if (warp == 0) {
+          constexpr int PER = ITEMS * WARPS / 32;
+          uint32_t v[PER], sum = 0;
+#pragma unroll
+          for (int q = 0; q < PER; ++q) {
+            v[q] = sm.wcnt[lane * PER + q];
+            sum += v[q];
+          }
+          uint32_t inc = sum;
+#pragma unroll
+          for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t o = __shfl_up_sync(0xffffffffu, inc, d);
+            if (lane >= (unsigned)d) inc += o;
+          }
+          uint32_t run = inc - sum;
+#pragma unroll
+          for (int q = 0; q < PER; ++q) {
+            sm.wcnt[lane * PER + q] = run;
+            run += v[q];
+          }
+          // the chain: walk back over the published counts to the nearest prefix (wide: 128 buckets per round trip)
+          uint64_t pfx = 0;
+          if (pbucket > 0) {
+            uint64_t *st = state + 1;
+            int64_t base = pbucket - 1;
+            bool done = false;
+            while (!done) {
+              constexpr int W = 4;
+              uint64_t w[W];
+#pragma unroll
+              for (int q = 0; q < W; ++q) {
+                const int64_t t = base - (int64_t)lane - 32 * q;
+                w[q] = t >= 0 ? TileState::load(st + t) : TileState::pack(TileState::PREFIX, 0);
+              }
+              int used = 0;
+#pragma unroll
+              for (int q = 0; q < W; ++q) {
+                if (done || used != q) continue;
+                const uint64_t s_ = TileState::status(w[q]);
+                const unsigned pmask = __ballot_sync(0xffffffffu, s_ == TileState::PREFIX);
+                const unsigned emask = __ballot_sync(0xffffffffu, s_ == TileState::EMPTY);
+                unsigned need = 0xffffffffu;
+                if (pmask) {
+                  const int fp = __ffs(pmask) - 1;
+                  need = fp == 31 ? 0xffffffffu : ((2u << fp) - 1u);
+                }
+                if (emask & need) continue;
+                uint64_t c = ((need >> lane) & 1u) ? TileState::value(w[q]) : 0;
+#pragma unroll
+                for (int d = 16; d > 0; d >>= 1) c += __shfl_xor_sync(0xffffffffu, c, d);
+                pfx += c;
+                used = q + 1;
+                if (pmask) done = true;
+              }
+              base -= 32 * used;
+            }
+            if (lane == 0)
+              TileState::store(st + pbucket, TileState::pack(TileState::PREFIX, pfx + (uint64_t)sm.meta[ps_].heads));
+          }
+          if (lane == 0) sm.excl = (long long)pfx;
+        }
+        __syncthreads();
+      } else {
+#pragma unroll
+        for (int i = 0; i < ITEMS; ++i) {
+          const int j = i * THREADS + (int)tid;
+          below[i] = (unsigned)j;  // every entry is kept: its output slot is its sorted slot
+          if (i < ie && j < cnt) heads |= 1u << i;
+        }
+      }
+      const int64_t excl = DEDUP ? (int64_t)sm.excl : (int64_t)start;
+      const int nheads = DEDUP ? sm.meta[ps_].heads : cnt;
+      // output: consecutive lanes hold consecutive heads, coalesced wherever nothing was merged
+      const uint64_t hi_bits = (uint64_t)pbucket << R;
+      const int64_t rlo = (int64_t)(hi_bits >> cbits);  // rows owned by this bucket: [rlo, rhi)
+      int64_t rhi = (int64_t)((((uint64_t)pbucket + 1) << R) >> cbits);
+      if (pbucket == nb - 1 || rhi > M + 1) rhi = M + 1;
+#pragma unroll
+      for (int i = 0; i < ITEMS; ++i) {
+        if (!((heads >> i) & 1u)) continue;
+        const int j = i * THREADS + (int)tid;
+        const uint32_t lk = skeys[j];
+        const int64_t o = excl + below[i] + (DEDUP ? sm.wcnt[i * WARPS + warp] : 0u);
+        const uint64_t full = hi_bits | lk;
+        const int64_t r = (int64_t)(full >> cbits);
+        out_row[o] = r;
+        out_col[o] = (int64_t)(full & cmask);
+        if (HAS_VALUE && !DEDUP) out_value[o] = pay_as<T>(svals[j]);
+        if (HAS_VALUE && DEDUP) {
+          A acc = to_acc<T>(pay_as<T>(svals[j]));
+          int jj = j + 1;
+          while (jj < cnt && skeys[jj] == lk) {
+            acc = Red<RED, A>::op(acc, to_acc<T>(pay_as<T>(svals[jj])));
+            ++jj;
+          }
+          out_value[o] = from_acc<T>(Red<RED, A>::finish(acc, (int64_t)(jj - j)));
+        }
+        if (out_rowptr) {
+          const int64_t pr = j == 0 ? rlo - 1 : (int64_t)((hi_bits | skeys[j - 1]) >> cbits);
+          if (r != pr && r <= M) {  // this head opens row r ...
+            out_rowptr[r] = o;
+            if (r - pr > 1)  // ... and the empty rows before it (rare)
+              for (int64_t q = pr + 1; q < r; ++q) out_rowptr[q] = o;
+          }
+        }
+      }
+      if (out_rowptr) {  // rows of this bucket after its last entry (all of them when the bucket is empty)
+        const int64_t first = cnt > 0 ? (int64_t)((hi_bits | skeys[cnt - 1]) >> cbits) + 1 : rlo;
+        for (int64_t q = first + tid; q < rhi; q += THREADS) out_rowptr[q] = excl + nheads;
+      }
+      if (DEDUP && pbucket == nb - 1 && tid == 0) *d_nnz_out = (long long)(excl + nheads);
+    }
+    if (!valid) break;
+    pending = true;
+    __syncthreads();  // every reader of meta[slot ^ 1] (the bucket just written out) is done
+    if (tid == 0) sm.meta[slot ^ 1] = L2Meta{nxt_bucket, nxt_start, nxt_end, 0};
+    slot ^= 1;
+  }
+}
+
+}  // namespace ps
