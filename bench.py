@@ -216,27 +216,31 @@ def bits_for(n: int) -> int:
 def rs_pass_launches(nnz_in: int, nnz_out: int, M: int, N: int):
     """Algorithmic bytes of every rs_pass_kernel launch of one step, in launch order:
     each pass reads and writes every tuple once, at the width it has in that pass.
-      hybrid coalesce (44-bit key, top 14 bits sorted globally):
+      hybrid coalesce (44-bit key, top 15 bits sorted globally, 8 + 7):
         pass A  reads int64 row + int64 col + f32 value (20 B), writes u64 key + u32 value (12 B)
         pass B  reads 12 B, writes the u32 bucket-local key + u32 value (8 B)
-      CSC side, stable sort by col carrying (index, row, value), ceil(22 / 8) = 3 passes:
-        first   reads int64 col + int64 row + f32 value (20 B), writes 4 x u32 (16 B)
-        middle  16 B + 16 B
-        last    reads 16 B, writes int64 t_row, t_col, csr2csc + f32 value (28 B)
-      csc2csr, partition of (target, source) on the top 14 bits of the target, 2 passes:
-        first   reads the int64 permutation (8 B), writes 2 x u32 (8 B);  second 8 B + 8 B"""
+      hybrid CSC sort (top 15 of the 22 col bits sorted globally, carrying entry index, row, value):
+        pass 1  reads int64 col + int64 row + f32 value (20 B), writes 4 x u32 (16 B)
+        pass 2  16 B + 16 B
+      csc2csr: the first partition pass of the bucketed inverse is fused into the CSC bucket kernel; the second one
+        reads (target, source) as 2 x u32 (8 B) and writes 8 B
+    Shapes that leave the hybrid paths (narrow keys, small inputs) are modelled as plain LSD passes."""
     out = []
     kbits = bits_for(M) + bits_for(N)
-    if kbits > 32 and nnz_in >= (1 << 16) and kbits - 14 <= 32:  # the hybrid path (coalesce.cu: hybrid_coalesce)
+    if kbits > 32 and nnz_in >= (1 << 16) and kbits - 15 <= 32:  # the hybrid path (coalesce.cu: hybrid_plan)
         out += [nnz_in * (20 + 12), nnz_in * (12 + 8)]
     else:
         p = max((kbits + 7) // 8, 1)
         out += [nnz_in * (20 + 12)] + [nnz_in * 24] * max(p - 2, 0) + ([nnz_in * 24] if p > 1 else [])
-    pc = max((bits_for(N) + 7) // 8, 1)
-    out += [nnz_out * (20 + 16)] + [nnz_out * 32] * max(pc - 2, 0) + [nnz_out * (16 + 28)]
-    if bits_for(nnz_out) > 20:
-        pi = max((bits_for(nnz_out) - 12 + 7) // 8, 1)
-        out += [nnz_out * 16] * pi
+    if nnz_out >= (1 << 16) and bits_for(N) - 15 <= 8:  # the hybrid CSC sort (transpose.cu: csc_hybrid)
+        out += [nnz_out * (20 + 16), nnz_out * (16 + 16)]
+        if bits_for(nnz_out) > 20:
+            out += [nnz_out * 16] * (max((bits_for(nnz_out) - 12 + 7) // 8, 1) - 1)
+    else:
+        pc = max((bits_for(N) + 7) // 8, 1)
+        out += [nnz_out * (20 + 16)] + [nnz_out * 32] * max(pc - 2, 0) + [nnz_out * (16 + 28)]
+        if bits_for(nnz_out) > 20:
+            out += [nnz_out * 16] * max((bits_for(nnz_out) - 12 + 7) // 8, 1)
     return out
 
 

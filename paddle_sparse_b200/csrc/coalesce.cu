@@ -19,14 +19,6 @@ namespace ps {
 
 enum { DD_INDEX_ONLY = 0, DD_FAST = 1, DD_PTR = 2 };
 
-template <typename T> __device__ __forceinline__ T pay_as(uint32_t p);
-template <> __device__ __forceinline__ float pay_as<float>(uint32_t p) { return __uint_as_float(p); }
-template <> __device__ __forceinline__ int32_t pay_as<int32_t>(uint32_t p) { return (int32_t)p; }
-template <> __device__ __forceinline__ __nv_bfloat16 pay_as<__nv_bfloat16>(uint32_t p) {
-  return __ushort_as_bfloat16((unsigned short)p);
-}
-template <> __device__ __forceinline__ __half pay_as<__half>(uint32_t p) { return __ushort_as_half((unsigned short)p); }
-
 }  // namespace ps
 #include "local_sort.cuh"
 #include "local_sort2.cuh"
@@ -343,7 +335,7 @@ static int hybrid_inspect(const int64_t *row, const int64_t *col, int64_t nnz, i
         row, col, nnz, cbits, hp.R, hp.T, st->gcount, with_max ? st->max_rc : nullptr);
   }
   PS_LAUNCH_OK();
-  ls_derive_kernel<<<1, 1024, 0, s>>>(st->gcount, hp.T, hp.lp, st->bucket_off, st->ghist, st->max_bucket);
+  ls_derive_kernel<<<1, 1024, 0, s>>>(st->gcount, hp.T, hp.lp, st->bucket_off, st->ghist, st->max_bucket, 0, LsChunkOut{});
   PS_LAUNCH_OK();
   return PS_OK;
 }

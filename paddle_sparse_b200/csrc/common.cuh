@@ -163,6 +163,15 @@ template <> struct Limits<int64_t> {
   __device__ static int64_t highest() { return INT64_MAX; }
 };
 
+// a <= 4-byte value as it rides through the sorts: the bits of one 32-bit payload word
+template <typename T> __device__ __forceinline__ T pay_as(uint32_t p);
+template <> __device__ __forceinline__ float pay_as<float>(uint32_t p) { return __uint_as_float(p); }
+template <> __device__ __forceinline__ int32_t pay_as<int32_t>(uint32_t p) { return (int32_t)p; }
+template <> __device__ __forceinline__ __nv_bfloat16 pay_as<__nv_bfloat16>(uint32_t p) {
+  return __ushort_as_bfloat16((unsigned short)p);
+}
+template <> __device__ __forceinline__ __half pay_as<__half>(uint32_t p) { return __ushort_as_half((unsigned short)p); }
+
 // reduce operator on accumulator values; RED is a PS_SUM/PS_MEAN/PS_MIN/PS_MAX constant
 template <int RED, typename A>
 struct Red {

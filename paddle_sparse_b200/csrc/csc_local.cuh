@@ -12,6 +12,7 @@
 #pragma once
 #include "common.cuh"
 #include "radix_sort.cuh"
+#include "local_sort.cuh"
 
 namespace ps {
 
@@ -24,7 +25,7 @@ constexpr int CL_MAX_L = 8;    // low col bits left to the local pass
 constexpr int CL_ROW = 256 / 2;  // counter row in words (two 16-bit counters per word)
 
 // ---- bucket sizes: histogram of col >> shift (one read of the int64 column array)
-__global__ void __launch_bounds__(1024)
+static __global__ void __launch_bounds__(1024)
 cl_bucket_hist_kernel(const int64_t *__restrict__ col, int64_t n, int shift, unsigned nb,
                       unsigned int *__restrict__ gcount /*[nb]*/) {
   extern __shared__ unsigned int cl_sh[];
@@ -67,85 +68,14 @@ cl_bucket_hist_kernel(const int64_t *__restrict__ col, int64_t n, int shift, uns
     if (cl_sh[j]) atomicAdd(&gcount[j], cl_sh[j]);
 }
 
-// ---- one CTA: bucket offsets, the bin bases of the global passes, and the chunk table
-struct ClPlan {
-  int passes, pbegin[2], pbits[2];
-};
-struct ClInfo {       // device-side facts the later kernels read
+// bucket offsets, the bin bases of the global passes and the chunk table come from ls_derive_kernel (local_sort.cuh)
+struct ClInfo {          // device-side facts the later kernels read (LsChunkOut::info)
   unsigned int chunks;   // total number of chunks
   unsigned int n_multi;  // buckets cut into more than one chunk
 };
-__global__ void __launch_bounds__(1024)
-cl_plan_kernel(const unsigned int *__restrict__ gcount, int nb, ClPlan plan, unsigned int *__restrict__ bucket_off /*[nb+1]*/,
-               unsigned int *__restrict__ chunk_start /*[nb+1]*/, unsigned int *__restrict__ chunk_bucket,
-               unsigned int *__restrict__ multi_list /*[nb]*/, unsigned long long *__restrict__ ghist /*[passes][512]*/,
-               ClInfo *__restrict__ info) {
-  __shared__ unsigned int dig[2][RS_MAX_RADIX];
-  __shared__ unsigned int wsum[33];
-  __shared__ unsigned int s_multi;
-  const unsigned tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
-  for (int j = tid; j < 2 * RS_MAX_RADIX; j += 1024) (&dig[0][0])[j] = 0;
-  if (tid == 0) s_multi = 0;
-  __syncthreads();
-  const int per = (nb + 1023) / 1024;  // consecutive buckets per thread
-  unsigned int local = 0, lchunks = 0;
-  for (int q = 0; q < per; ++q) {
-    const int b = tid * per + q;
-    if (b < nb) {
-      const unsigned int c = gcount[b];
-      local += c;
-      lchunks += c > (unsigned)CL_CAP ? (c + CL_CAP - 1) / CL_CAP : 1u;
-      if (c)
-        for (int p = 0; p < plan.passes; ++p) atomicAdd(&dig[p][(b >> plan.pbegin[p]) & ((1 << plan.pbits[p]) - 1)], c);
-    }
-  }
-  unsigned int total, ctotal;
-  const unsigned int excl = block_exclusive_scan<unsigned int, 1024>(local, wsum, &total);
-  const unsigned int cexcl = block_exclusive_scan<unsigned int, 1024>(lchunks, wsum, &ctotal);
-  unsigned int run = excl, crun = cexcl;
-  for (int q = 0; q < per; ++q) {
-    const int b = tid * per + q;
-    if (b < nb) {
-      const unsigned int c = gcount[b];
-      const unsigned int k = c > (unsigned)CL_CAP ? (c + CL_CAP - 1) / CL_CAP : 1u;
-      bucket_off[b] = run;
-      chunk_start[b] = crun;
-      for (unsigned int j = 0; j < k; ++j) chunk_bucket[crun + j] = (unsigned)b;
-      if (k > 1) multi_list[atomicAdd(&s_multi, 1u)] = (unsigned)b;
-      run += c;
-      crun += k;
-    }
-  }
-  if (tid == 1023) {
-    bucket_off[nb] = total;
-    chunk_start[nb] = ctotal;
-  }
-  __syncthreads();
-  if (tid == 0) {
-    info->chunks = ctotal;
-    info->n_multi = s_multi;
-  }
-  if (warp < (unsigned)plan.passes) {  // exclusive scans of the digit histograms: warp p scans pass p
-    unsigned long long v[16], sum = 0;
-    for (int q = 0; q < 16; ++q) {
-      v[q] = dig[warp][lane * 16 + q];
-      sum += v[q];
-    }
-    unsigned long long inc = sum;
-    for (int d = 1; d < 32; d <<= 1) {
-      const unsigned long long o = __shfl_up_sync(0xffffffffu, inc, d);
-      if (lane >= (unsigned)d) inc += o;
-    }
-    unsigned long long r = inc - sum;
-    for (int q = 0; q < 16; ++q) {
-      ghist[warp * RS_MAX_RADIX + lane * 16 + q] = r;
-      r += v[q];
-    }
-  }
-}
 
 // ---- chunks of oversized buckets only: per-chunk digit histogram ...
-__global__ void __launch_bounds__(256)
+static __global__ void __launch_bounds__(256)
 cl_chunk_hist_kernel(const uint32_t *__restrict__ scol, const unsigned int *__restrict__ bucket_off,
                      const unsigned int *__restrict__ chunk_start, const unsigned int *__restrict__ chunk_bucket,
                      const ClInfo *__restrict__ info, unsigned lmask, unsigned int *__restrict__ chunk_hist /*[chunks][256]*/) {
@@ -169,7 +99,7 @@ cl_chunk_hist_kernel(const uint32_t *__restrict__ scol, const unsigned int *__re
 }
 
 // ... turned into every chunk's per-digit offset inside its bucket; also the bucket's colptr / colcount
-__global__ void __launch_bounds__(256)
+static __global__ void __launch_bounds__(256)
 cl_chunk_scan_kernel(const unsigned int *__restrict__ bucket_off, const unsigned int *__restrict__ chunk_start,
                      const unsigned int *__restrict__ multi_list, const ClInfo *__restrict__ info, int L, int64_t N,
                      unsigned int *__restrict__ chunk_hist, int64_t *__restrict__ out_colptr,
@@ -204,6 +134,21 @@ cl_chunk_scan_kernel(const unsigned int *__restrict__ bucket_off, const unsigned
 // loads, ranking, scans, payload loads, write-out).  The payload is staged in TWO rounds through the same two
 // buffers - (entry index) -> csr2csc, t_row; then (row, value) -> t_col, t_value - and the next chunk's metadata and
 // the second round's loads are requested one phase early.
+// csc2csr (storage.py:439-447: argsort(csr2csc), i.e. the inverse permutation) rides along: the kernel knows, for every
+// entry, its CSR position p (the carried index) and its CSC position q (where it is written).
+//   mode 1 (the output fits L2 comfortably): out[p] = q directly.
+//   mode 2: the FIRST partition pass of the bucketed inverse (transpose.cu: invert_perm_impl) is done here - the pairs
+//   (p, q) of a chunk are grouped by the digit `(p >> shift) & mask` in shared memory and appended, one run per digit,
+//   to that digit's region of (tp, tq), whose start is known in closed form (p is a permutation) and whose fill level
+//   is a global cursor.  Order inside a region does not matter: the last stage drops the pairs of a 4,096-entry window
+//   into a shared-memory table.  Saves one full read of csr2csc and one global pass.
+struct ClInverse {
+  int mode;  // 0 = none
+  int shift, bits;
+  unsigned long long *cursor;  // [2^bits], initialised with the regions' starts
+  uint32_t *tp, *tq;
+  int64_t *out;  // mode 1
+};
 struct ClMeta {
   long long chunk;
   unsigned b, boff, bend, start, multi;
@@ -212,10 +157,12 @@ struct ClSmem {
   uint32_t a[CL_CAP];
   uint32_t v[CL_CAP];
   uint8_t dig[CL_CAP];    // low col bits of the sorted slot
-  uint32_t cnt[CL_WARPS][CL_ROW];  // two 16-bit counters per word; later the group's offset inside the digit
+  uint16_t ix[CL_CAP];    // inverse round: sorted slot of the pair that goes to this partition slot
+  uint32_t cnt[CL_WARPS][CL_ROW];  // two 16-bit counters per word; later the group's offset inside the digit;
+                                   // inverse round: [0,256) bin counts / starts, [256,512) global bases
   uint16_t dbase[256];             // start of digit d inside the sorted chunk
   uint32_t gb[256];                // global position of sorted slot j of digit d = gb[d] + j
-  uint32_t scan_tmp[32];
+  uint32_t scan_tmp[40];
   ClMeta meta[2];
 };
 
@@ -237,7 +184,7 @@ __device__ __forceinline__ ClMeta cl_fetch_meta(unsigned long long *ticket, unsi
   return m;
 }
 
-template <bool CARRY, bool HAS_VALUE>
+template <bool CARRY, bool HAS_VALUE, int INV>
 __global__ void __launch_bounds__(CL_THREADS, 4)
 cl_local_kernel(const uint32_t *__restrict__ scol, const uint32_t *__restrict__ sp, const uint32_t *__restrict__ srow,
                 const uint32_t *__restrict__ sval, const unsigned int *__restrict__ bucket_off,
@@ -245,7 +192,7 @@ cl_local_kernel(const uint32_t *__restrict__ scol, const uint32_t *__restrict__ 
                 const unsigned int *__restrict__ chunk_hist, const ClInfo *__restrict__ info, int nb, int L, int64_t N,
                 int64_t *__restrict__ out_csr2csc, int64_t *__restrict__ out_colptr, int64_t *__restrict__ out_colcount,
                 int64_t *__restrict__ out_t_row, int64_t *__restrict__ out_t_col, uint32_t *__restrict__ out_t_val,
-                unsigned long long *ticket) {
+                unsigned long long *ticket, ClInverse inv) {
   constexpr int THREADS = CL_THREADS, ITEMS = CL_ITEMS, WARPS = CL_WARPS;
   static_assert(THREADS == 256 && WARPS == 8, "thread d owns digit d in the scans below");
   extern __shared__ __align__(16) unsigned char cl_raw[];
@@ -346,9 +293,9 @@ cl_local_kernel(const uint32_t *__restrict__ scol, const uint32_t *__restrict__ 
         }
       }
     }
-    // round 2 is requested now: its latency hides behind the write-out of round 1
+    // round 2 is requested now when nothing comes in between: its latency hides behind the write-out of round 1
     uint32_t pb[CARRY && HAS_VALUE ? ITEMS : 1];
-    if (CARRY) {
+    if (CARRY && INV != 2) {
 #pragma unroll
       for (int i = 0; i < ITEMS; ++i) {
         const int j = wb0 + i * 32 + lane;
@@ -357,7 +304,10 @@ cl_local_kernel(const uint32_t *__restrict__ scol, const uint32_t *__restrict__ 
         if (HAS_VALUE) pb[i] = ok ? ld_stream(sval + start + j) : 0u;
       }
     }
+    uint32_t *ibin = &sm.cnt[0][0];   // inverse round: [0,256) counts, then starts
+    uint32_t *igb = ibin + 256;       //                [256,512) global base of the digit's run minus its start
     __syncthreads();
+    if (INV == 2) ibin[tid] = 0;  // every thread is past its reads of the rank counters
     // coalesced write-out: sorted slot j of digit d goes to gb[d] + j (one streaming range when the bucket is one
     // chunk)
     const int64_t colbase = (int64_t)b << L;
@@ -367,12 +317,66 @@ cl_local_kernel(const uint32_t *__restrict__ scol, const uint32_t *__restrict__ 
       if (j < cnt) {
         const unsigned d = sm.dig[j];
         const size_t dst = (size_t)(sm.gb[d] + (uint32_t)j);
-        out_csr2csc[dst] = (int64_t)sm.a[j];
+        const uint32_t p = sm.a[j];
+        out_csr2csc[dst] = (int64_t)p;
         if (CARRY) out_t_row[dst] = colbase + d;
+        if (INV == 1) inv.out[p] = (int64_t)dst;
+      }
+    }
+    if (INV == 2) {
+      // ---- inverse round: pairs (p, q) grouped by the digit of p, one run per digit appended to its region
+      const unsigned imask = (1u << inv.bits) - 1u;
+      uint32_t ir[ITEMS];  // digit | rank << 8
+      __syncthreads();     // the counters are zero
+#pragma unroll
+      for (int k = 0; k < ITEMS; ++k) {
+        const int j = k * THREADS + tid;
+        ir[k] = 0;
+        if (j < cnt) {
+          const unsigned d = (sm.a[j] >> inv.shift) & imask;
+          ir[k] = d | (atomicAdd(&ibin[d], 1u) << 8);  // any order inside a run will do
+        }
+      }
+      __syncthreads();
+      {
+        const uint32_t c = ibin[tid];
+        uint32_t total;
+        const uint32_t st = block_exclusive_scan<uint32_t, THREADS>(c, sm.scan_tmp, &total);
+        const unsigned long long g = c ? atomicAdd(inv.cursor + tid, (unsigned long long)c) : 0ull;
+        ibin[tid] = st;
+        igb[tid] = (uint32_t)g - st;
+      }
+      __syncthreads();
+#pragma unroll
+      for (int k = 0; k < ITEMS; ++k) {
+        const int j = k * THREADS + tid;
+        if (j < cnt) sm.ix[ibin[ir[k] & 255u] + (ir[k] >> 8)] = (uint16_t)j;
+      }
+      __syncthreads();
+#pragma unroll 4
+      for (int k = 0; k < ITEMS; ++k) {
+        const int j2 = k * THREADS + tid;
+        if (j2 < cnt) {
+          const unsigned j = sm.ix[j2];
+          const uint32_t p = sm.a[j];
+          const uint32_t q = sm.gb[sm.dig[j]] + j;
+          const size_t dst = (size_t)(igb[(p >> inv.shift) & imask] + (uint32_t)j2);
+          inv.tp[dst] = p;
+          inv.tq[dst] = q;
+        }
+      }
+      if (CARRY) {
+#pragma unroll
+        for (int i = 0; i < ITEMS; ++i) {
+          const int j = wb0 + i * 32 + lane;
+          const bool ok = i < ie && j < cnt;
+          pa[i] = ok ? ld_stream(srow + start + j) : 0u;
+          if (HAS_VALUE) pb[i] = ok ? ld_stream(sval + start + j) : 0u;
+        }
       }
     }
     if (CARRY) {
-      __syncthreads();  // round 1 is read out of the buffers
+      __syncthreads();  // round 1 (and the inverse round) is read out of the buffers
 #pragma unroll
       for (int i = 0; i < ITEMS; ++i) {
         if (dr[i] != 0xffffffffu) {

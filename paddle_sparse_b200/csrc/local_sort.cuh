@@ -24,7 +24,7 @@ constexpr int LS_MAX_T = 15;                    // 2^15 bucket counters = 128 KB
 // With `max_rc` it is also the constructor's validation pass (storage.py:65-89: max(row), max(col)) - the same
 // 16 bytes per entry are read once for both; entries whose bucket id falls outside [0, 2^T) (out-of-range
 // indices the caller is about to reject) are not counted.
-__global__ void __launch_bounds__(1024)
+static __global__ void __launch_bounds__(1024)
 ls_bucket_hist_kernel(const int64_t *__restrict__ row, const int64_t *__restrict__ col, int64_t n, int cbits, int R,
                       int T, unsigned int *__restrict__ gcount /*[2^T]*/, long long *__restrict__ max_rc /*[2] | null*/) {
   extern __shared__ unsigned int ls_sh[];
@@ -88,45 +88,106 @@ struct LsInspect {
 struct LsPlan {
   int passes, pbegin[2], pbits[2];
 };
-__global__ void __launch_bounds__(1024)
+// One CTA of 32 warps; warp w owns the contiguous bucket segment [w * nb / 32, (w + 1) * nb / 32) and reads it
+// COALESCED (lane l takes buckets seg + k * 32 + l): a per-thread run of consecutive buckets reads with a 128-byte
+// stride between lanes, which made this single-CTA kernel take 70 - 120 us on 2^15 buckets.
+// `chunk_cap` > 0 (the CSC side, csc_local.cuh) also builds the chunk table: a bucket of more than chunk_cap entries
+// is cut into ceil(count / chunk_cap) chunks, every other bucket is one chunk.
+struct LsChunkOut {
+  unsigned int *chunk_start;   // [nb + 1]
+  unsigned int *chunk_bucket;  // [chunks]
+  unsigned int *multi_list;    // [nb]
+  unsigned int *info;          // [0] = chunks, [1] = buckets cut into several chunks
+};
+static __global__ void __launch_bounds__(1024)
 ls_derive_kernel(const unsigned int *__restrict__ gcount, int T, LsPlan plan, unsigned int *__restrict__ bucket_off,
-                 unsigned long long *__restrict__ ghist /*[passes][512]*/, unsigned int *__restrict__ max_bucket) {
+                 unsigned long long *__restrict__ ghist /*[passes][512]*/, unsigned int *__restrict__ max_bucket,
+                 int chunk_cap, LsChunkOut co) {
   __shared__ unsigned int dig[2][RS_MAX_RADIX];  // 32-bit shared atomics are native, 64-bit ones are CAS loops
-  __shared__ unsigned int wsum[33];
-  __shared__ unsigned int smax;
+  __shared__ unsigned int wtot[32], wctot[32];
+  __shared__ unsigned int smax, s_multi;
   const unsigned tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
   for (int j = tid; j < 2 * RS_MAX_RADIX; j += 1024) (&dig[0][0])[j] = 0;
-  if (tid == 0) smax = 0;
+  if (tid == 0) smax = s_multi = 0;
   __syncthreads();
   const int nb = 1 << T;
-  const int per = (nb + 1023) / 1024;  // consecutive buckets per thread
-  unsigned int local = 0, mx = 0;
-  for (int q = 0; q < per; ++q) {
-    const int b = tid * per + q;
-    if (b < nb) {
-      const unsigned int c = gcount[b];
-      local += c;
-      mx = c > mx ? c : mx;
-      if (c) {
-        for (int p = 0; p < plan.passes; ++p)
-          atomicAdd(&dig[p][(b >> plan.pbegin[p]) & ((1 << plan.pbits[p]) - 1)], c);
+  const int seg = (nb + 31) / 32;               // buckets per warp
+  const int rounds = (seg + 31) / 32;           // <= 32 for T <= 15
+  const int seg0 = (int)warp * seg;
+  // Real loops, not unrolled: this kernel runs once on one CTA, so straight-line code costs an instruction-cache miss
+  // per line (a fully unrolled version took 90 us, 4x this one); the second sweep re-reads the counts (cache hits).
+  unsigned int mx = 0, wsum = 0, wcsum = 0;
+  // sweep 1: totals of the warp's segment, largest bucket, digit histograms of the global passes
+#pragma unroll 1
+  for (int k = 0; k < rounds; ++k) {
+    const int b = seg0 + k * 32 + (int)lane;
+    const bool in = k * 32 + (int)lane < seg && b < nb;
+    const unsigned int c = in ? gcount[b] : 0u;
+    wsum += c;
+    wcsum += !in ? 0u : (chunk_cap > 0 && c > (unsigned)chunk_cap ? (c + chunk_cap - 1) / chunk_cap : 1u);
+    mx = c > mx ? c : mx;
+    if (c) {
+      atomicAdd(&dig[0][(b >> plan.pbegin[0]) & ((1 << plan.pbits[0]) - 1)], c);
+      if (plan.passes > 1) atomicAdd(&dig[1][(b >> plan.pbegin[1]) & ((1 << plan.pbits[1]) - 1)], c);
+    }
+  }
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) {
+    const unsigned int o = __shfl_xor_sync(0xffffffffu, mx, d);
+    mx = o > mx ? o : mx;
+    wsum += __shfl_xor_sync(0xffffffffu, wsum, d);
+    wcsum += __shfl_xor_sync(0xffffffffu, wcsum, d);
+  }
+  if (lane == 0) {
+    wtot[warp] = wsum;
+    wctot[warp] = wcsum;
+    atomicMax(&smax, mx);
+  }
+  __syncthreads();
+  unsigned int base = 0, cbase = 0, total = 0, ctotal = 0;
+  for (int w = 0; w < 32; ++w) {
+    if (w < (int)warp) { base += wtot[w]; cbase += wctot[w]; }
+    total += wtot[w];
+    ctotal += wctot[w];
+  }
+  // sweep 2: per round a warp scan of the counts (and of the chunk counts) on top of the running carries
+  unsigned int carry = base, ccarry = cbase;
+#pragma unroll 1
+  for (int k = 0; k < rounds; ++k) {
+    const int b = seg0 + k * 32 + (int)lane;
+    const bool in = k * 32 + (int)lane < seg && b < nb;
+    const unsigned int c = in ? gcount[b] : 0u;
+    const unsigned int ch = !in ? 0u : (chunk_cap > 0 && c > (unsigned)chunk_cap ? (c + chunk_cap - 1) / chunk_cap : 1u);
+    unsigned int inc = c, cinc = ch;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const unsigned int o = __shfl_up_sync(0xffffffffu, inc, d), oc = __shfl_up_sync(0xffffffffu, cinc, d);
+      if (lane >= (unsigned)d) { inc += o; cinc += oc; }
+    }
+    if (in) {
+      bucket_off[b] = carry + inc - c;
+      if (chunk_cap > 0) {
+        const unsigned int cs = ccarry + cinc - ch;
+        co.chunk_start[b] = cs;
+        for (unsigned int j = 0; j < ch; ++j) co.chunk_bucket[cs + j] = (unsigned)b;
+        if (ch > 1) co.multi_list[atomicAdd(&s_multi, 1u)] = (unsigned)b;
       }
     }
+    carry += __shfl_sync(0xffffffffu, inc, 31);
+    ccarry += __shfl_sync(0xffffffffu, cinc, 31);
   }
-  atomicMax(&smax, mx);
-  unsigned int total;
-  const unsigned int excl = block_exclusive_scan<unsigned int, 1024>(local, wsum, &total);
-  unsigned int run = excl;
-  for (int q = 0; q < per; ++q) {
-    const int b = tid * per + q;
-    if (b < nb) {
-      bucket_off[b] = run;
-      run += gcount[b];
+  if (tid == 1023) {
+    bucket_off[nb] = total;
+    if (chunk_cap > 0) co.chunk_start[nb] = ctotal;
+  }
+  __syncthreads();
+  if (tid == 0) {
+    if (max_bucket) *max_bucket = smax;
+    if (chunk_cap > 0) {
+      co.info[0] = ctotal;
+      co.info[1] = s_multi;
     }
   }
-  if (tid == 1023) bucket_off[nb] = total;
-  __syncthreads();
-  if (tid == 0) *max_bucket = smax;
   // exclusive scans of the digit histograms: warp p scans pass p (16 digits per lane)
   if (warp < (unsigned)plan.passes) {
     unsigned long long v[16], sum = 0;

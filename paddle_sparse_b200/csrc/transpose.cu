@@ -18,12 +18,16 @@
 namespace ps {
 
 int csc_variant();  // PS_CSC_HYBRID=0 disables the hybrid CSC sort (bench knob)
+constexpr int INV_WINDOW_BITS = 12;
+__global__ void invert_window_kernel(const uint32_t *__restrict__ target, const uint32_t *__restrict__ source, int64_t n,
+                                     int64_t *__restrict__ out);
+__global__ void dense_key_hist_kernel(long long n, SortPlan plan, unsigned long long *__restrict__ ghist);
 
 // The hybrid CSC sort (csc_local.cuh).  *used = false (nothing written) when the shape rules it out; the caller then
 // runs the LSD pipeline.  `t_row / t_col / t_val` null: csr2csc + colptr / colcount only.
 static int csc_hybrid(const int64_t *row, const int64_t *col, const void *value, int64_t n, int64_t N,
                       int64_t *out_csr2csc, int64_t *out_colptr, int64_t *out_colcount, int64_t *t_row, int64_t *t_col,
-                      void *t_val, bool *used, cudaStream_t s) {
+                      void *t_val, int64_t *out_csc2csr, bool *used, cudaStream_t s) {
   *used = false;
   const int cbits = bits_for(N);
   if (!csc_variant() || n < (int64_t(1) << 16) || cbits < 2) return PS_OK;
@@ -38,7 +42,7 @@ static int csc_hybrid(const int64_t *row, const int64_t *col, const void *value,
   if (gp.passes > 2) return PS_OK;
   const bool carry = t_row != nullptr;
   const int nb = 1 << T;
-  ClPlan plan;
+  LsPlan plan;
   plan.passes = gp.passes;
   for (int p = 0; p < gp.passes; ++p) { plan.pbegin[p] = gp.begin[p]; plan.pbits[p] = gp.bits[p]; }
 
@@ -61,7 +65,8 @@ static int csc_hybrid(const int64_t *row, const int64_t *col, const void *value,
                                                                                                          gcount);
   }
   PS_LAUNCH_OK();
-  cl_plan_kernel<<<1, 1024, 0, s>>>(gcount, nb, plan, bucket_off, chunk_start, chunk_bucket, multi_list, ghist, info);
+  ls_derive_kernel<<<1, 1024, 0, s>>>(gcount, T, plan, bucket_off, ghist, nullptr, CL_CAP,
+                                      LsChunkOut{chunk_start, chunk_bucket, multi_list, reinterpret_cast<unsigned int *>(info)});
   PS_LAUNCH_OK();
 
   // global passes on col bits [L, cbits): (col, entry index[, row, value]) -> u32 arrays in bucket order
@@ -107,22 +112,85 @@ static int csc_hybrid(const int64_t *row, const int64_t *col, const void *value,
                                                      out_colptr, out_colcount);
   PS_LAUNCH_OK();
 
+  // csc2csr rides along (ClInverse): direct scatter when the output stays in L2, else the first partition pass of the
+  // bucketed inverse is fused into the local kernel
+  ClInverse inv{0, 0, 0, nullptr, nullptr, nullptr, out_csc2csr};
+  SortPlan iplan{};
+  uint32_t *tp = nullptr, *tq = nullptr;
+  unsigned long long *ighist = nullptr;
+  if (out_csc2csr) {
+    const int nbits = bits_for(n);
+    if (nbits <= 20) {
+      inv.mode = 1;
+    } else {
+      const int top = nbits - INV_WINDOW_BITS;
+      iplan = make_sort_plan(top, rs_geometry<uint32_t, 1>().rbits);
+      for (int i = 0; i < iplan.passes; ++i) iplan.begin[i] += INV_WINDOW_BITS;
+      PS_SCRATCH(tp_, scratch, uint32_t, n);
+      PS_SCRATCH(tq_, scratch, uint32_t, n);
+      PS_SCRATCH(gh, scratch, unsigned long long, (size_t)iplan.passes * RS_MAX_RADIX);
+      tp = tp_;
+      tq = tq_;
+      ighist = gh;
+      dense_key_hist_kernel<<<iplan.passes, RS_MAX_RADIX, 0, s>>>((long long)n, iplan, ighist);
+      PS_LAUNCH_OK();
+      inv.mode = 2;
+      inv.shift = iplan.begin[0];
+      inv.bits = iplan.bits[0];
+      inv.cursor = ighist;  // row 0: the regions' starts, consumed as fill cursors
+      inv.tp = tp;
+      inv.tq = tq;
+    }
+  }
   const size_t smem = sizeof(ClSmem);
   int grid = sm_count() * 4;
-#define PS_CL(C_, V_)                                                                                              \
+#define PS_CL(C_, V_, I_)                                                                                          \
   do {                                                                                                             \
-    auto kern = cl_local_kernel<C_, V_>;                                                                           \
+    auto kern = cl_local_kernel<C_, V_, I_>;                                                                       \
     PS_FUNC_SMEM(kern, smem);                                                                                      \
     ProfScope prof(PROF_LOCAL_SORT, s);                                                                            \
     kern<<<grid, CL_THREADS, smem, s>>>(scol, sp, srow, sval, bucket_off, chunk_start, chunk_bucket, chunk_hist,  \
                                        info, nb, L, N, out_csr2csc, out_colptr, out_colcount, t_row, t_col,      \
-                                       reinterpret_cast<uint32_t *>(t_val), ticket);                              \
+                                       reinterpret_cast<uint32_t *>(t_val), ticket, inv);                         \
   } while (0)
-  if (carry && value) PS_CL(true, true);
-  else if (carry) PS_CL(true, false);
-  else PS_CL(false, false);
+#define PS_CLI(C_, V_)                         \
+  do {                                         \
+    if (inv.mode == 2) PS_CL(C_, V_, 2);       \
+    else if (inv.mode == 1) PS_CL(C_, V_, 1);  \
+    else PS_CL(C_, V_, 0);                     \
+  } while (0)
+  if (carry && value) PS_CLI(true, true);
+  else if (carry) PS_CLI(true, false);
+  else PS_CLI(false, false);
+#undef PS_CLI
 #undef PS_CL
   PS_LAUNCH_OK();
+  if (inv.mode == 2) {  // the rest of the bucketed inverse: the second partition pass (if any), then the windows
+    const uint32_t *wk = tp, *wv = tq;
+    if (iplan.passes > 1) {
+      PS_SCRATCH(k1, scratch, uint32_t, n);
+      PS_SCRATCH(p1, scratch, uint32_t, n);
+      const RsGeomRt geom = rs_geometry<uint32_t, 1>();
+      const int64_t tiles = ceil_div(n, geom.tile);
+      const size_t words = 32 + (size_t)tiles * (size_t)(1 << geom.rbits);
+      PS_SCRATCH(st, scratch, uint64_t, words);
+      PS_CUDA(cudaMemsetAsync(st, 0, words * sizeof(uint64_t), s));
+      PaySrcN<1> ps_;
+      ps_.s[0] = PaySrc{tq, PSRC_U32};
+      PayDstN<1> pd;
+      pd.d[0] = PayDst{p1, PDST_U32};
+      PS_TRY((rs_dispatch_pass<uint32_t, 1>(geom.rbits, KeySrc{tp, nullptr, KSRC_KEYS, 0}, ps_, KeyDst{k1, nullptr, KDST_KEYS, 0},
+                                            pd, n, iplan.begin[1], iplan.bits[1], 1, ighist + RS_MAX_RADIX, st + 32,
+                                            reinterpret_cast<unsigned long long *>(st), s)));
+      wk = k1;
+      wv = p1;
+    }
+    {
+      ProfScope prof(PROF_INVERT_PERM, s);
+      invert_window_kernel<<<(unsigned)(sm_count() * 4), 512, 0, s>>>(wk, wv, n, out_csc2csr);
+    }
+    PS_LAUNCH_OK();
+  }
   *used = true;
   return PS_OK;
 }
@@ -136,7 +204,6 @@ invert_perm_kernel(const int64_t *__restrict__ perm, int64_t n, int64_t *__restr
 // Second half of the bucketed inverse.  `perm` is a permutation, so after the (target, source) pairs have been
 // partitioned on target >> INV_WINDOW_BITS the pairs of window w sit exactly at [w << BITS, (w + 1) << BITS): one CTA
 // drops the sources into a shared-memory table indexed by the low target bits and writes the window out coalesced.
-constexpr int INV_WINDOW_BITS = 12;
 __global__ void __launch_bounds__(512)
 invert_window_kernel(const uint32_t *__restrict__ target, const uint32_t *__restrict__ source, int64_t n,
                      int64_t *__restrict__ out) {
@@ -258,7 +325,8 @@ int ps_csr2csc(const int64_t *col, int64_t nnz, int64_t N, int64_t *out_csr2csc,
   }
   {
     bool used = false;
-    PS_TRY(csc_hybrid(nullptr, col, nullptr, nnz, N, out_csr2csc, colptr, out_colcount, nullptr, nullptr, nullptr, &used, s));
+    PS_TRY(csc_hybrid(nullptr, col, nullptr, nnz, N, out_csr2csc, colptr, out_colcount, nullptr, nullptr, nullptr, nullptr, &used,
+                      s));
     if (used) return PS_OK;
   }
   const int cbits = bits_for(N);
@@ -306,11 +374,9 @@ int ps_csc_build(const int64_t *row, const int64_t *col, const void *value, int6
   }
   {  // hybrid: two global passes on the top col bits, one local pass that writes every output
     bool used = false;
-    PS_TRY(csc_hybrid(row, col, value, nnz, N, out_csr2csc, colptr, out_colcount, out_t_row, out_t_col, out_t_value, &used, s));
-    if (used) {
-      if (out_csc2csr) PS_TRY(invert_perm_impl(out_csr2csc, nnz, out_csc2csr, s));
-      return PS_OK;
-    }
+    PS_TRY(csc_hybrid(row, col, value, nnz, N, out_csr2csc, colptr, out_colcount, out_t_row, out_t_col, out_t_value,
+                      out_csc2csr, &used, s));
+    if (used) return PS_OK;
   }
   // stable sort by col of (col | entry index, row, value bits): the last pass writes the transposed arrays directly
   const int cbits = bits_for(N);
