@@ -304,20 +304,22 @@ __device__ __forceinline__ void atomic_red_max(int32_t *p, int32_t v) { atomicMa
 __device__ __forceinline__ void atomic_red_min(int64_t *p, int64_t v) { atomicMin((long long *)p, (long long)v); }
 __device__ __forceinline__ void atomic_red_max(int64_t *p, int64_t v) { atomicMax((long long *)p, (long long)v); }
 // IEEE order == signed-int order for non-negative floats and reversed unsigned order for negatives
+// floats ordered through their bit patterns: the SIGN BIT picks the branch (-0.0 belongs with the negatives: `v >= 0`
+// sent it down the signed-integer path, where its pattern is the smallest of all and stuck)
 __device__ __forceinline__ void atomic_red_min(float *p, float v) {
-  if (v >= 0.f) atomicMin(reinterpret_cast<int *>(p), __float_as_int(v));
+  if (__float_as_int(v) >= 0) atomicMin(reinterpret_cast<int *>(p), __float_as_int(v));
   else atomicMax(reinterpret_cast<unsigned int *>(p), __float_as_uint(v));
 }
 __device__ __forceinline__ void atomic_red_max(float *p, float v) {
-  if (v >= 0.f) atomicMax(reinterpret_cast<int *>(p), __float_as_int(v));
+  if (__float_as_int(v) >= 0) atomicMax(reinterpret_cast<int *>(p), __float_as_int(v));
   else atomicMin(reinterpret_cast<unsigned int *>(p), __float_as_uint(v));
 }
 __device__ __forceinline__ void atomic_red_min(double *p, double v) {
-  if (v >= 0.0) atomicMin(reinterpret_cast<long long *>(p), __double_as_longlong(v));
+  if (__double_as_longlong(v) >= 0) atomicMin(reinterpret_cast<long long *>(p), __double_as_longlong(v));
   else atomicMax(reinterpret_cast<unsigned long long *>(p), (unsigned long long)__double_as_longlong(v));
 }
 __device__ __forceinline__ void atomic_red_max(double *p, double v) {
-  if (v >= 0.0) atomicMax(reinterpret_cast<long long *>(p), __double_as_longlong(v));
+  if (__double_as_longlong(v) >= 0) atomicMax(reinterpret_cast<long long *>(p), __double_as_longlong(v));
   else atomicMin(reinterpret_cast<unsigned long long *>(p), (unsigned long long)__double_as_longlong(v));
 }
 

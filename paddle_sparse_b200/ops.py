@@ -17,6 +17,7 @@ from typing import Optional, Tuple
 import torch
 
 from . import _lib
+from . import autograd as _ag
 
 PS_F32, PS_BF16, PS_F16, PS_F64, PS_I32, PS_I64, PS_U8 = range(7)
 _DTYPES = {
@@ -187,6 +188,9 @@ def _value_args(value: Optional[torch.Tensor]):
 def sort_coo(row, col, value, M: int, N: int, want_perm: bool = False):
     """Sort-on-construct (storage.py:158-171): stable sort by row*N + col.
     Returns (row, col, value, perm|None)."""
+    if _ag.needs_grad(value):  # indices by the kernel, values by a differentiable gather
+        r, c, _, perm = sort_coo(row, col, None, M, N, True)
+        return r, c, gather_rows(value, perm), (perm if want_perm else None)
     row, col = _idx(row, "row"), _idx(col, "col")
     value = None if value is None else _dev(value, "value")
     v, dt, w = _value_args(value)
@@ -216,6 +220,12 @@ def coalesce(row, col, value, M: int, N: int, reduce: str = "add", want_rowptr: 
     """coalesce.py:8-29 fused: packed-key radix sort + run detection + segmented reduce.
     Returns (row', col', value'), plus rowptr' (= ind2ptr(row', M), written by the same pass) when asked.
     `inspection`: what coo_inspect left behind for these very arrays (saves a read and a host sync)."""
+    if _ag.needs_grad(value):  # sort (indices), run starts, then gather + segment reduction: both differentiable
+        r, c, _, perm = sort_coo(row, col, None, M, N, True)
+        ptr = _ag.run_starts(r, c)
+        heads = ptr[:-1]
+        out = (r[heads].contiguous(), c[heads].contiguous(), segment_csr(gather_rows(value, perm), ptr, None, reduce))
+        return out + (ind2ptr(out[0], M),) if want_rowptr else out
     row, col = _idx(row, "row"), _idx(col, "col")
     value = None if value is None else _dev(value, "value")
     v, dt, w = _value_args(value)
@@ -235,6 +245,11 @@ def coalesce(row, col, value, M: int, N: int, reduce: str = "add", want_rowptr: 
 
 def coalesce_sorted(row, col, value, reduce: str = "add"):
     """SparseStorage.coalesce on sorted input (storage.py:454-486).  Returns (row', col', value')."""
+    if _ag.needs_grad(value):
+        r, c = _idx(row, "row"), _idx(col, "col")
+        ptr = _ag.run_starts(r, c)
+        heads = ptr[:-1]
+        return r[heads].contiguous(), c[heads].contiguous(), segment_csr(value, ptr, None, reduce)
     row, col = _idx(row, "row"), _idx(col, "col")
     value = None if value is None else _dev(value, "value")
     v, dt, w = _value_args(value)
@@ -272,7 +287,7 @@ def csc_build(row: torch.Tensor, col: torch.Tensor, value: Optional[torch.Tensor
     row, col = _idx(row, "row"), _idx(col, "col")
     value = None if value is None else _dev(value, "value")
     nnz = col.numel()
-    carry = value is not None and nnz > 0 and _row_bytes(value) == 4
+    carry = value is not None and nnz > 0 and _row_bytes(value) == 4 and not _ag.needs_grad(value)
     perm, t_row, t_col = _new(col, nnz), _new(col, nnz), _new(col, nnz)
     colptr = _new(col, N + 1)
     colcount = _new(col, N) if want_colcount else None
@@ -297,6 +312,8 @@ def invert_perm(perm: torch.Tensor) -> torch.Tensor:
 
 def gather_rows(src: torch.Tensor, index: torch.Tensor) -> torch.Tensor:
     """src[index] along dim 0 (storage.py:166-169, 238-241; transpose.py:15; index_select.py:104-108)."""
+    if _ag.needs_grad(src):
+        return _ag.GatherRows.apply(_dev(src, "src"), _idx(index, "index"))
     src, index = _dev(src, "src"), _idx(index, "index")
     out = torch.empty((index.numel(),) + tuple(src.shape[1:]), dtype=src.dtype, device=src.device)
     with torch.cuda.device(src.device):
@@ -307,6 +324,9 @@ def gather_rows(src: torch.Tensor, index: torch.Tensor) -> torch.Tensor:
 
 def transpose_gather(csr2csc_, row, col, value, colptr=None, N: int = 0):
     """transpose.py:9-33: (col[csr2csc], row[csr2csc], value[csr2csc]) in one pass."""
+    if _ag.needs_grad(value):
+        out_row, out_col, _ = transpose_gather(csr2csc_, row, col, None, colptr, N)
+        return out_row, out_col, gather_rows(value, csr2csc_)
     perm, row, col = _idx(csr2csc_, "csr2csc"), _idx(row, "row"), _idx(col, "col")
     value = None if value is None else _dev(value, "value")
     nnz = row.numel()
@@ -324,6 +344,8 @@ def transpose_gather(csr2csc_, row, col, value, colptr=None, N: int = 0):
 def segment_csr(src: torch.Tensor, indptr: torch.Tensor, out=None, reduce: str = "sum") -> torch.Tensor:
     """paddle_scatter.segment_csr(src, indptr, None, reduce) along dim 0 (storage.py:471, reduce.py:51)."""
     assert out is None, "segment_csr: `out` is not supported"
+    if _ag.needs_grad(src):
+        return _ag.SegmentCSR.apply(_dev(src, "src"), _idx(indptr, "indptr"), reduce)
     src, indptr = _dev(src, "src"), _idx(indptr, "indptr")
     S = indptr.numel() - 1
     res = torch.empty((S,) + tuple(src.shape[1:]), dtype=src.dtype, device=src.device)
@@ -340,6 +362,8 @@ def gather_csr(src: torch.Tensor, indptr: torch.Tensor, E: Optional[int] = None)
     S = indptr.numel() - 1
     if E is None:
         E = int(indptr[-1].item())
+    if _ag.needs_grad(src):
+        return _ag.GatherCSR.apply(src, indptr, E)
     out = torch.empty((E,) + tuple(src.shape[1:]), dtype=src.dtype, device=src.device)
     with torch.cuda.device(src.device):
         _lib.call("ps_gather_csr", _p(src), src.element_size() * max(_width(src), 1), _p(indptr), S, E, _p(out),
@@ -352,6 +376,8 @@ def scatter(src: torch.Tensor, index: torch.Tensor, dim: int = 0, out=None, dim_
     """paddle_scatter.scatter(src, index, 0, None, dim_size, reduce) (reduce.py:42).  `count` (optional): the
     histogram of `index` when the caller holds it (a cached colcount) - saves one atomic per entry."""
     assert dim == 0 and out is None and dim_size is not None
+    if _ag.needs_grad(src):
+        return _ag.Scatter.apply(_dev(src, "src"), _idx(index, "index"), dim_size, reduce, count)
     src, index = _dev(src, "src"), _idx(index, "index")
     count = None if count is None else _idx(count, "count")
     assert count is None or count.numel() == dim_size
@@ -365,6 +391,9 @@ def scatter(src: torch.Tensor, index: torch.Tensor, dim: int = 0, out=None, dim_
 def reduce_all(src: torch.Tensor, reduce: str = "sum") -> torch.Tensor:
     """reduce.py:17-27 dim=None: 0-d result of the dense reduction over every element."""
     src = _dev(src, "src")
+    if _ag.needs_grad(src):  # a dense reduction of the value tensor: the framework's own differentiable op
+        reduce = "sum" if reduce == "add" else reduce
+        return {"sum": src.sum, "mean": src.mean, "min": src.min, "max": src.max}[reduce]()
     res = torch.empty(1, dtype=src.dtype, device=src.device)
     with torch.cuda.device(src.device):
         _lib.call("ps_reduce_all", _p(src), dtype_code(src), src.numel(), reduce_code(reduce), _p(res), _stream(src))
@@ -372,7 +401,15 @@ def reduce_all(src: torch.Tensor, reduce: str = "sum") -> torch.Tensor:
 
 
 # ------------------------------------------------------------------ broadcast multiply / add (mul.py:76-119, add.py:12-81)
+def _no_inplace_grad(out, *tensors):
+    if out is not None and _ag.needs_grad(*tensors):
+        raise RuntimeError("in-place operation on values that require grad: use the out-of-place form")
+
+
 def _bc_row(sym, value, rowptr, other, out=None):
+    _no_inplace_grad(out, value, other)
+    if _ag.needs_grad(value, other):
+        return _ag.BroadcastRow.apply(_dev(value, "value"), _idx(rowptr, "rowptr"), _dev(other, "other"), sym == "ps_mul_row")
     value, rowptr, other = _dev(value, "value"), _idx(rowptr, "rowptr"), _dev(other, "other")
     out = torch.empty_like(value) if out is None else out
     with torch.cuda.device(value.device):
@@ -382,6 +419,9 @@ def _bc_row(sym, value, rowptr, other, out=None):
 
 
 def _bc_col(sym, value, col, other, out=None):
+    _no_inplace_grad(out, value, other)
+    if _ag.needs_grad(value, other):
+        return _ag.BroadcastCol.apply(_dev(value, "value"), _idx(col, "col"), _dev(other, "other"), sym == "ps_mul_col")
     value, col, other = _dev(value, "value"), _idx(col, "col"), _dev(other, "other")
     out = torch.empty_like(value) if out is None else out
     with torch.cuda.device(value.device):
@@ -391,6 +431,9 @@ def _bc_col(sym, value, col, other, out=None):
 
 
 def _bc_nnz(sym, value, other, out=None):
+    _no_inplace_grad(out, value, other)
+    if _ag.needs_grad(value, other):  # element-wise on [nnz, ...]: the framework's own differentiable op
+        return value * other if sym == "ps_mul_nnz" else value + other
     value, other = _dev(value, "value"), _dev(other, "other")
     out = torch.empty_like(value) if out is None else out
     with torch.cuda.device(value.device):
@@ -458,6 +501,8 @@ def concat_rows(pieces) -> torch.Tensor:
     for t in pieces:
         if t.dtype != first.dtype or t.shape[1:] != first.shape[1:]:
             raise ValueError("concat_rows: dtypes / trailing shapes differ")
+    if _ag.needs_grad(*pieces):
+        return torch.cat(pieces, dim=0)
     K = len(pieces)
     out = torch.empty((sum(t.shape[0] for t in pieces),) + tuple(first.shape[1:]), dtype=first.dtype,
                       device=first.device)
@@ -506,6 +551,10 @@ def slice_add(x: torch.Tensor, start: int, length: int, delta: int = 0) -> torch
 
 def narrow_cols(row: torch.Tensor, col: torch.Tensor, value: Optional[torch.Tensor], start: int, length: int):
     """narrow.py:53-62: the entries with start <= col < start+length as (row, col - start, value), order kept."""
+    if _ag.needs_grad(value):
+        out_row, out_col, _ = narrow_cols(row, col, None, start, length)
+        sel = ((col >= int(start)) & (col < int(start) + int(length))).nonzero().squeeze(1)
+        return out_row, out_col, gather_rows(value, sel)
     row, col = _idx(row, "row"), _idx(col, "col")
     value = None if value is None else _dev(value, "value")
     nnz = col.numel()
@@ -522,6 +571,9 @@ def narrow_cols(row: torch.Tensor, col: torch.Tensor, value: Optional[torch.Tens
 
 def index_select_fill(old_ptr, minor, value, idx, out_ptr, E: int, want_perm: bool = False):
     """index_select.py:17-33 / 53-67 in one launch.  Returns (major, minor', value', perm|None)."""
+    if _ag.needs_grad(value):
+        major, new_minor, _, perm = index_select_fill(old_ptr, minor, None, idx, out_ptr, E, True)
+        return major, new_minor, gather_rows(value, perm), (perm if want_perm else None)
     old_ptr, minor, idx, out_ptr = _idx(old_ptr), _idx(minor), _idx(idx), _idx(out_ptr)
     value = None if value is None else _dev(value, "value")
     K = idx.numel()

@@ -335,3 +335,20 @@ def test_atomic_rank_order_selftest(ops):
     assert checked >= 10 ** 9 and collided > checked // 10
     if ops._lib.lib().ps_rank_mode() == 0:
         assert bad == 0, f"{bad} of {collided} colliding lane-instances were served out of lane order: set PS_RANK_MODE=match"
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.float64])
+def test_scatter_min_max_with_negative_zero(ops, dtype):
+    """-0.0 must order with the negatives in the bit-pattern atomics of the column reductions (round 2: `v >= 0`
+    sent it down the signed path, where it stuck as the minimum)."""
+    rng = np.random.default_rng(8)
+    n, S = 200_000, 300
+    v = np.round(rng.standard_normal(n) * 2) / 2  # multiples of 0.5: many exact +0.0 / -0.0
+    assert np.signbit(v[v == 0]).any() and (~np.signbit(v[v == 0])).any()
+    idx = rng.integers(0, S, n).astype(I64)
+    src = dev(v, dtype)
+    for red, fn in (("min", np.minimum), ("max", np.maximum)):
+        want = np.full(S, np.inf if red == "min" else -np.inf)
+        fn.at(want, idx, v)
+        got = host(ops.scatter(src, dev(idx), 0, None, S, red)).astype(np.float64)
+        assert np.array_equal(got, want), red  # +0.0 == -0.0 compares equal; everything else must match exactly
