@@ -206,6 +206,14 @@ int ps_coo_match(const int64_t *row, const int64_t *col, int64_t n, const int64_
                  const int64_t *col_b, int64_t M_b, int64_t *out_pos, uint8_t *out_mask,
                  void *stream);
 
+/* ------------------------------------------------------------------ resize / reshape */
+/* storage.py:281-330 `sparse_resize`: out[0:total] = src[0:min(n,total)] followed by `fill` (a pointer array grows by
+ * entries equal to nnz, a count array by zeros; shrinking cuts). */
+int ps_pad_i64(const int64_t *src, int64_t n, int64_t fill, int64_t total, int64_t *out, void *stream);
+/* storage.py:332-368 `sparse_reshape`: idx = old_n * row + col; out_row = idx / new_n, out_col = idx % new_n. */
+int ps_reshape_index(const int64_t *row, const int64_t *col, int64_t n, int64_t old_n, int64_t new_n,
+                     int64_t *out_row, int64_t *out_col, void *stream);
+
 /* ------------------------------------------------------------------ cat */
 /* cat.py:49-276: out = concat_k(src_k[0:lens[k]] + deltas[k]) in one launch per 32 pieces
  * (rows / cols shifted by the running sizes, pointers and permutations by the running nnz).

@@ -216,6 +216,49 @@ class SparseStorage:
     def has_value(self):
         return self._value is not None
 
+    def sparse_resize(self, sparse_sizes):
+        """storage.py:281-330."""
+        assert len(sparse_sizes) == 2
+        nnz = self._col.size
+        d0 = sparse_sizes[0] - self._sparse_sizes[0]
+        rowcount, rowptr = self._rowcount, self._rowptr
+        if d0 > 0:
+            if rowptr is not None:
+                rowptr = np.concatenate([rowptr, np.full(d0, nnz, dtype=I64)])
+            if rowcount is not None:
+                rowcount = np.concatenate([rowcount, np.zeros(d0, dtype=I64)])
+        elif d0 < 0:
+            rowptr = None if rowptr is None else rowptr[:d0]
+            rowcount = None if rowcount is None else rowcount[:d0]
+        d1 = sparse_sizes[1] - self._sparse_sizes[1]
+        colcount, colptr = self._colcount, self._colptr
+        if d1 > 0:
+            if colptr is not None:
+                colptr = np.concatenate([colptr, np.full(d1, nnz, dtype=I64)])
+            if colcount is not None:
+                colcount = np.concatenate([colcount, np.zeros(d1, dtype=I64)])
+        elif d1 < 0:
+            colptr = None if colptr is None else colptr[:d1]
+            colcount = None if colcount is None else colcount[:d1]
+        return SparseStorage(row=self._row, rowptr=rowptr, col=self._col, value=self._value,
+                             sparse_sizes=tuple(sparse_sizes), rowcount=rowcount, colptr=colptr, colcount=colcount,
+                             csr2csc=self._csr2csc, csc2csr=self._csc2csr, is_sorted=True, trust_data=True)
+
+    def sparse_reshape(self, num_rows: int, num_cols: int):
+        """storage.py:332-368."""
+        assert num_rows > 0 or num_rows == -1
+        assert num_cols > 0 or num_cols == -1
+        assert num_rows > 0 or num_cols > 0
+        total = self._sparse_sizes[0] * self._sparse_sizes[1]
+        if num_rows == -1:
+            num_rows = total // num_cols
+        if num_cols == -1:
+            num_cols = total // num_rows
+        assert num_rows * num_cols == total
+        idx = self._sparse_sizes[1] * self.row() + self._col
+        return SparseStorage(row=idx // num_cols, col=idx % num_cols, value=self._value,
+                             sparse_sizes=(num_rows, num_cols), is_sorted=True, trust_data=True)
+
     def sparse_sizes(self):
         return self._sparse_sizes
 

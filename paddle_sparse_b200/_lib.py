@@ -65,6 +65,8 @@ SIGNATURES = {
     "ps_add_row": [c_ptr, c_int, c_i64, c_ptr, c_i64, c_i64, c_ptr, c_ptr, c_ptr],
     "ps_add_col": [c_ptr, c_int, c_i64, c_ptr, c_i64, c_ptr, c_ptr, c_ptr],
     "ps_add_nnz": [c_ptr, c_int, c_i64, c_ptr, c_ptr, c_ptr],
+    "ps_pad_i64": [c_ptr, c_i64, c_i64, c_i64, c_ptr, c_ptr],
+    "ps_reshape_index": [c_ptr, c_ptr, c_i64, c_i64, c_i64, c_ptr, c_ptr, c_ptr],
     "ps_concat_add_i64": [c_ptr, c_ptr, c_ptr, c_i64, c_ptr, c_ptr],
     "ps_concat_bytes": [c_ptr, c_ptr, c_i64, c_ptr, c_ptr],
     "ps_coo_match": [c_ptr, c_ptr, c_i64, c_ptr, c_ptr, c_i64, c_ptr, c_ptr, c_ptr],

@@ -55,6 +55,29 @@ __global__ void __launch_bounds__(256) concat_add_kernel(CatPieces p, int64_t *_
   }
 }
 
+// storage.py:281-330 `sparse_resize`: a pointer / count array grown to `total` entries, the new tail holding `fill`
+// (rowptr / colptr: nnz; rowcount / colcount: 0), or cut to `total` entries.  One launch, one read, one write.
+__global__ void __launch_bounds__(256)
+pad_i64_kernel(const int64_t *__restrict__ src, int64_t n, int64_t fill, int64_t total, int64_t *__restrict__ out) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride)
+    out[i] = i < n ? ld_stream(src + i) : fill;
+}
+
+// storage.py:332-368 `sparse_reshape`: idx = old_N * row + col; row' = idx / new_N, col' = idx % new_N (row-major
+// order is preserved, so the result stays sorted).  One launch instead of five elementwise framework ops.
+__global__ void __launch_bounds__(256)
+reshape_index_kernel(const int64_t *__restrict__ row, const int64_t *__restrict__ col, int64_t n, int64_t old_n,
+                     int64_t new_n, int64_t *__restrict__ out_row, int64_t *__restrict__ out_col) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const int64_t idx = old_n * ld_stream(row + i) + ld_stream(col + i);
+    const int64_t r = idx / new_n;
+    out_row[i] = r;
+    out_col[i] = idx - r * new_n;
+  }
+}
+
 }  // namespace ps
 
 using namespace ps;
@@ -109,6 +132,27 @@ int ps_concat_bytes(const void *const *srcs, const int64_t *nbytes, int64_t K, v
     if (nbytes[k] > 0) PS_CUDA(cudaMemcpyAsync(dst, srcs[k], (size_t)nbytes[k], cudaMemcpyDeviceToDevice, s));
     dst += nbytes[k];
   }
+  return PS_OK;
+}
+
+int ps_pad_i64(const int64_t *src, int64_t n, int64_t fill, int64_t total, int64_t *out, void *stream) {
+  PS_CHECK(n >= 0 && total >= 0, "pad_i64: negative size");
+  if (total == 0) return PS_OK;
+  int64_t blocks = ceil_div(total, 256 * 4);
+  if (blocks > (int64_t)sm_count() * 16) blocks = (int64_t)sm_count() * 16;
+  pad_i64_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(src, n < total ? n : total, fill, total, out);
+  PS_LAUNCH_OK();
+  return PS_OK;
+}
+
+int ps_reshape_index(const int64_t *row, const int64_t *col, int64_t n, int64_t old_n, int64_t new_n, int64_t *out_row,
+                     int64_t *out_col, void *stream) {
+  PS_CHECK(n >= 0 && old_n >= 0 && new_n > 0, "reshape_index: bad sizes");
+  if (n == 0) return PS_OK;
+  int64_t blocks = ceil_div(n, 256 * 4);
+  if (blocks > (int64_t)sm_count() * 16) blocks = (int64_t)sm_count() * 16;
+  reshape_index_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(row, col, n, old_n, new_n, out_row, out_col);
+  PS_LAUNCH_OK();
   return PS_OK;
 }
 

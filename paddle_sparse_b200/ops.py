@@ -478,6 +478,26 @@ def coo_match(row, col, rowptr_b, col_b):
     return pos, mask
 
 
+# ------------------------------------------------------------------ resize / reshape (storage.py:281-368)
+def pad_i64(src: torch.Tensor, total: int, fill: int) -> torch.Tensor:
+    """src grown to `total` entries with `fill` in the new tail, or cut to `total` (sparse_resize)."""
+    src = _idx(src, "src")
+    out = _new(src, total)
+    with torch.cuda.device(src.device):
+        _lib.call("ps_pad_i64", _p(src), src.numel(), int(fill), int(total), _p(out), _stream(src))
+    return out
+
+
+def reshape_index(row: torch.Tensor, col: torch.Tensor, old_n: int, new_n: int):
+    """(idx // new_n, idx % new_n) for idx = old_n * row + col (sparse_reshape)."""
+    row, col = _idx(row, "row"), _idx(col, "col")
+    out_row, out_col = _new(row, row.numel()), _new(row, row.numel())
+    with torch.cuda.device(row.device):
+        _lib.call("ps_reshape_index", _p(row), _p(col), row.numel(), int(old_n), int(new_n), _p(out_row), _p(out_col),
+                  _stream(row))
+    return out_row, out_col
+
+
 # ------------------------------------------------------------------ cat (cat.py:49-276)
 def concat_add(pieces, deltas, skip_first=None) -> torch.Tensor:
     """concat_k(pieces[k][skip_k:] + deltas[k]) in one launch (per 32 pieces); int64, 1-D."""

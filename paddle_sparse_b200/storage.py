@@ -274,29 +274,23 @@ class SparseStorage(object):
 
     # ------------------------------------------------------------------ resize / reshape (storage.py:281-368)
     def sparse_resize(self, sparse_sizes: Tuple[int, int]):
+        """storage.py:281-330: pointers grow by entries equal to nnz, counts by zeros; shrinking cuts; row / col /
+        value and both permutations are shared."""
         assert len(sparse_sizes) == 2
         (old_m, old_n), nnz = self._sparse_sizes, self._col.numel()
 
-        def _grow_ptr(ptr, diff):
-            if ptr is None or diff == 0:
-                return ptr
-            if diff > 0:
-                return torch.cat([ptr, torch.full((diff,), nnz, dtype=ptr.dtype, device=ptr.device)])
-            return ptr[:diff]
+        def ptr(t, size):
+            return t if t is None or t.numel() == size + 1 else ops.pad_i64(t, size + 1, nnz)
 
-        def _grow_count(cnt, diff):
-            if cnt is None or diff == 0:
-                return cnt
-            if diff > 0:
-                return torch.cat([cnt, torch.zeros(diff, dtype=cnt.dtype, device=cnt.device)])
-            return cnt[:diff]
+        def count(t, size):
+            return t if t is None or t.numel() == size else ops.pad_i64(t, size, 0)
 
-        d0, d1 = sparse_sizes[0] - old_m, sparse_sizes[1] - old_n
-        return self._rewrap(sparse_sizes=tuple(sparse_sizes), rowptr=_grow_ptr(self._rowptr, d0),
-                            rowcount=_grow_count(self._rowcount, d0), colptr=_grow_ptr(self._colptr, d1),
-                            colcount=_grow_count(self._colcount, d1))
+        m, n = int(sparse_sizes[0]), int(sparse_sizes[1])
+        return self._rewrap(sparse_sizes=(m, n), rowptr=ptr(self._rowptr, m), rowcount=count(self._rowcount, m),
+                            colptr=ptr(self._colptr, n), colcount=count(self._colcount, n))
 
     def sparse_reshape(self, num_rows: int, num_cols: int):
+        """storage.py:332-368: the same entries read row-major on a (num_rows, num_cols) grid; every cache is dropped."""
         assert num_rows > 0 or num_rows == -1
         assert num_cols > 0 or num_cols == -1
         assert num_rows > 0 or num_cols > 0
@@ -306,9 +300,9 @@ class SparseStorage(object):
         if num_cols == -1:
             num_cols = total // num_rows
         assert num_rows * num_cols == total
-        idx = self.sparse_size(1) * self.row() + self._col
-        return SparseStorage(row=torch.div(idx, num_cols, rounding_mode="floor"), col=idx % num_cols,
-                             value=self._value, sparse_sizes=(num_rows, num_cols), is_sorted=True, trust_data=True)
+        row, col = ops.reshape_index(self.row(), self._col, self.sparse_size(1), num_cols)
+        return SparseStorage(row=row, col=col, value=self._value, sparse_sizes=(num_rows, num_cols), is_sorted=True,
+                             trust_data=True)
 
     # ------------------------------------------------------------------ lazy caches
     def has_rowcount(self) -> bool:

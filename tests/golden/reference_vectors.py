@@ -86,3 +86,8 @@ EYE = dict(square=dict(M=3, N=3, row=[0, 1, 2], rowptr=[0, 1, 2, 3], col=[0, 1, 
 
 # test/test_overload.py:6-22 (value-less matrix, dense operand on either side of + and *)
 OVERLOAD = dict(row=[0, 1, 1, 2, 2], col=[1, 0, 2, 1, 2], other=[1, 2, 3])
+
+# test/test_storage.py:183-200 (test_sparse_reshape)
+SPARSE_RESHAPE = dict(row=[0, 1, 2, 3], col=[0, 1, 2, 3],
+                      steps=[((2, 8), (2, 8), [0, 0, 1, 1], [0, 5, 2, 7]),
+                             ((-1, 4), (4, 4), [0, 1, 2, 3], [0, 1, 2, 3])])

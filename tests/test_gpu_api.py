@@ -113,6 +113,40 @@ def test_storage_set_value_and_copy(ps, dtype):
     assert new.col().tolist() == st.col().tolist() and new.value().float().tolist() == st.value().float().tolist()
 
 
+def test_sparse_resize_and_reshape_match_the_oracle(ps):
+    """storage.py:281-368: golden vectors of test/test_storage.py:183-200, then random matrices with every cache
+    built against the oracle's restatement (which caches survive, their contents, the shared row / col / value)."""
+    g = G.SPARSE_RESHAPE
+    st = ps.SparseStorage(row=ten(g["row"]), col=ten(g["col"]))
+    for args, sizes, row, col in g["steps"]:
+        st = st.sparse_reshape(*args)
+        assert st.sparse_sizes() == sizes and st.row().tolist() == row and st.col().tolist() == col
+    rng = np.random.default_rng(12)
+    M, N = 700, 450
+    key = np.unique(rng.integers(0, M * N, 20000))
+    row, col = (key // N).astype(I64), (key % N).astype(I64)
+    val = rng.random(key.size).astype(np.float32)
+    O = np_ref.SparseStorage(row=row, col=col, value=val, sparse_sizes=(M, N), is_sorted=True)
+    O.rowptr(); O.rowcount(); O.colptr(); O.colcount(); O.csr2csc(); O.csc2csr()
+    A = ps.SparseStorage(row=dev(row), col=dev(col), value=dev(val), sparse_sizes=(M, N), is_sorted=True).fill_cache_()
+    for sizes in ((M + 123, N + 77), (M, N + 5), (M + 1, N), (M, N)):
+        got, want = A.sparse_resize(sizes), O.sparse_resize(sizes)
+        assert got.sparse_sizes() == tuple(sizes) and got.cached_keys() == want.cached_keys()
+        for k in ("rowptr", "rowcount", "colptr", "colcount", "csr2csc", "csc2csr"):
+            assert np.array_equal(host(getattr(got, "_" + k)), getattr(want, "_" + k)), (sizes, k)
+        assert got.col().data_ptr() == A.col().data_ptr() and got.value().data_ptr() == A.value().data_ptr()
+        back = got.sparse_resize((M, N))  # cutting back restores the original pointers and counts
+        for k in ("rowptr", "rowcount", "colptr", "colcount"):
+            assert np.array_equal(host(getattr(back, "_" + k)), getattr(O, "_" + k)), (sizes, k)
+    for shape in ((M * 2, N // 2), (N, M), (-1, 90), (350, -1), (1, M * N)):
+        got, want = A.sparse_reshape(*shape), O.sparse_reshape(*shape)
+        assert got.sparse_sizes() == want.sparse_sizes() and got.num_cached_keys() == 0
+        assert np.array_equal(host(got.row()), want.row()) and np.array_equal(host(got.col()), want.col())
+        assert np.array_equal(host(got.rowptr()), want.rowptr()) and got.value().data_ptr() == A.value().data_ptr()
+    with pytest.raises(AssertionError):
+        A.sparse_reshape(7, 11)
+
+
 def test_storage_dtype_and_placement(ps):
     """storage.py:582-776: type / type_as / to_device / device_as / cuda / pin_memory / is_pinned / share_memory_ /
     is_shared.  Caches travel with the data; a host copy is an inert staging holder."""

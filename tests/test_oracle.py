@@ -335,3 +335,27 @@ def test_reduction_mul_select_consistency_with_dense():
 def test_philox_known_answer():
     # Random123 known-answer test for philox4x32-10: counter = key = 0.
     assert native.philox_u64(0, 0, 0) == (0x6627E8D5 | (0xE169C58D << 32))
+
+
+def test_sparse_reshape_golden_and_resize_restatement():
+    """test/test_storage.py:183-200 pins sparse_reshape; sparse_resize (storage.py:281-330) is pinned only through
+    test_storage.py:145-146 (sizes), so its cache handling is checked against what a fresh build gives."""
+    g = G.SPARSE_RESHAPE
+    st = np_ref.SparseStorage(row=np.array(g["row"], I64), col=np.array(g["col"], I64))
+    for args, sizes, row, col in g["steps"]:
+        st = st.sparse_reshape(*args)
+        assert st.sparse_sizes() == sizes and st.row().tolist() == row and st.col().tolist() == col
+    rng = np.random.default_rng(4)
+    key = np.unique(rng.integers(0, 40 * 30, 300))
+    A = np_ref.SparseStorage(row=(key // 30).astype(I64), col=(key % 30).astype(I64), sparse_sizes=(40, 30),
+                             is_sorted=True)
+    A.rowptr(); A.rowcount(); A.colptr(); A.colcount(); A.csr2csc(); A.csc2csr()
+    for sizes in ((45, 37), (40, 30)):
+        B = A.sparse_resize(sizes)
+        fresh = np_ref.SparseStorage(row=A.row(), col=A.col(), sparse_sizes=sizes, is_sorted=True)
+        assert B.sparse_sizes() == sizes
+        for k in ("rowptr", "rowcount", "colptr", "colcount", "csr2csc", "csc2csr"):
+            assert np.array_equal(getattr(B, "_" + k), getattr(fresh, k)()), k
+    C = A.sparse_resize((45, 37)).sparse_resize((40, 30))  # growing then cutting back restores the caches
+    for k in ("rowptr", "rowcount", "colptr", "colcount"):
+        assert np.array_equal(getattr(C, "_" + k), getattr(A, "_" + k)), k
