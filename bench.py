@@ -603,7 +603,8 @@ def run_ours(args):
             c_row, c_col, c_val, c_rowptr = ps.ops.coalesce(lr, o_col, o_val, rows_local, N, "add", True)
             A = ps.SparseTensor(row=c_row, rowptr=c_rowptr, col=c_col, value=c_val, sparse_sizes=(rows_local, N),
                                 is_sorted=True, trust_data=True)
-            return A.fill_cache_()
+            A.storage.fill_cache_(carry=False)
+            return A
         local_only()
         local_ms, A_full = timed(local_only, max(args.steps // 2, 2))
         # global invariants of the full-size shards (parity gate, second half)

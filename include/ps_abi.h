@@ -143,7 +143,9 @@ int ps_csr2csc(const int64_t *col, int64_t nnz, int64_t N, int64_t *out_csr2csc,
  * (entry index, row, value bits) as payload, so its last pass writes csr2csc AND the transposed arrays
  * out_t_row = col[csr2csc] (the sorted col), out_t_col = row[csr2csc], out_t_value = value[csr2csc] directly:
  * no random gathers.  value (nullable) must be one 4-byte element per entry (value_bytes == 4); out_colptr,
- * out_colcount, out_csc2csr (inverse permutation, bucketed scatter) are nullable. */
+ * out_colcount, out_csc2csr (inverse permutation; rides along with the sort's bucket kernel) are nullable.
+ * out_t_row == NULL (then out_t_col, out_t_value, row and value may be NULL too): nothing is carried - only
+ * csr2csc, colptr, colcount and csc2csr are built (row shards that will not be transposed). */
 int ps_csc_build(const int64_t *row, const int64_t *col, const void *value, int64_t value_bytes,
                  int64_t nnz, int64_t N, int64_t *out_csr2csc, int64_t *out_colptr,
                  int64_t *out_colcount, int64_t *out_csc2csr, int64_t *out_t_row, int64_t *out_t_col,

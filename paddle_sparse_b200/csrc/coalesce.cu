@@ -263,23 +263,31 @@ int ls_variant();  // PS_LS_VARIANT: 2 (default) = counting pass + in-bin compar
 
 static int ls_cap() { return ls_variant() == 1 ? LS_CAP : L2_CAP; }
 
+template <typename T, int RED, bool HAS_VALUE, bool DEDUP, typename KeyT>
+static int ls2_launch(const KeyT *lowkeys, const uint32_t *lowvals, const unsigned int *bucket_off, int nb, int R,
+                      int cbits, int64_t M, int64_t *out_row, int64_t *out_col, void *out_value, int64_t *out_rowptr,
+                      uint64_t *state, long long *d_nnz, cudaStream_t s) {
+  auto kern = ls2_sort_dedup_kernel<T, RED, HAS_VALUE, DEDUP, KeyT>;
+  const size_t smem = sizeof(L2Smem<HAS_VALUE>);
+  PS_FUNC_SMEM(kern, smem);
+  int grid = sm_count() * 2;
+  if (grid > nb) grid = nb;
+  {
+    ProfScope prof(PROF_LOCAL_SORT, s);
+    kern<<<grid, L2_THREADS, smem, s>>>(lowkeys, lowvals, bucket_off, nb, R, cbits, M, out_row, out_col,
+                                       reinterpret_cast<T *>(out_value), out_rowptr, state, d_nnz);
+  }
+  PS_LAUNCH_OK();
+  return PS_OK;
+}
+
 template <typename T, int RED, bool HAS_VALUE, bool DEDUP>
 static int ls_launch(const uint32_t *lowkeys, const uint32_t *lowvals, const unsigned int *bucket_off, int nb, int R,
                      int cbits, int64_t M, int64_t *out_row, int64_t *out_col, void *out_value, int64_t *out_rowptr,
                      uint64_t *state, long long *d_nnz, cudaStream_t s) {
   if (ls_variant() != 1) {
-    auto kern = ls2_sort_dedup_kernel<T, RED, HAS_VALUE, DEDUP>;
-    const size_t smem = sizeof(L2Smem<HAS_VALUE>);
-    PS_FUNC_SMEM(kern, smem);
-    int grid = sm_count() * 2;
-    if (grid > nb) grid = nb;
-    {
-      ProfScope prof(PROF_LOCAL_SORT, s);
-      kern<<<grid, L2_THREADS, smem, s>>>(lowkeys, lowvals, bucket_off, nb, R, cbits, M, out_row, out_col,
-                                         reinterpret_cast<T *>(out_value), out_rowptr, state, d_nnz);
-    }
-    PS_LAUNCH_OK();
-    return PS_OK;
+    return ls2_launch<T, RED, HAS_VALUE, DEDUP, uint32_t>(lowkeys, lowvals, bucket_off, nb, R, cbits, M, out_row, out_col,
+                                                        out_value, out_rowptr, state, d_nnz, s);
   }
   auto kern = ls_sort_dedup_kernel<T, RED, HAS_VALUE, DEDUP>;
   const size_t smem = sizeof(LsSmem<HAS_VALUE>);
@@ -420,6 +428,118 @@ static int hybrid_coalesce(const int64_t *row, const int64_t *col, int64_t nnz, 
 }
 
 // ------------------------------------------------------------------------------------------------
+// Hybrid coalesce for keys whose bucket-local part does not fit 32 bits (row shards of very wide matrices: papers100M
+// shards have 51- to 53-bit keys).  Same scheme - top T key bits by global passes, buckets finished in shared memory -
+// with three differences: T may reach 18 bits (9-bit digits, two passes), the global passes keep the FULL 64-bit key
+// (the bucket kernel takes the low R <= 36 bits itself), and, because 2^T counters no longer fit a shared-memory
+// histogram, the bucket offsets are read off the bucket-sorted keys by boundary detection AFTER the passes.  One host
+// read (the largest bucket) decides; oversized buckets (skew) send the call to the LSD pipeline.
+constexpr int LSW_MAX_T = 18;
+constexpr int LSW_MAX_R = 36;
+
+__global__ void __launch_bounds__(256)
+lsw_bounds_kernel(const uint64_t *__restrict__ keys, int64_t n, int R, int nb, unsigned int *__restrict__ bucket_off) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i0 = (int64_t)blockIdx.x * blockDim.x; i0 < n + 1; i0 += stride) {  // warp-uniform trip count
+    const int64_t i = i0 + threadIdx.x;
+    // bucket of element i (n: one past the last bucket) and of its predecessor (-1 before the first)
+    const int64_t b = i < n ? (int64_t)(ld_stream(keys + i) >> R) : (i == n ? (int64_t)nb : (int64_t)nb + 1);
+    int64_t pb = __shfl_up_sync(0xffffffffu, b, 1);
+    if ((threadIdx.x & 31u) == 0) pb = i == 0 ? -1 : (i <= n ? (int64_t)(ld_stream(keys + i - 1) >> R) : (int64_t)nb + 1);
+    if (i <= n && b != pb)
+      for (int64_t q = pb + 1; q <= b && q <= nb; ++q) bucket_off[q] = (unsigned int)i;  // element i opens buckets (pb, b]
+  }
+}
+
+__global__ void __launch_bounds__(256)
+lsw_max_kernel(const unsigned int *__restrict__ bucket_off, int nb, unsigned int *__restrict__ max_bucket) {
+  unsigned int mx = 0;
+  for (int b = blockIdx.x * blockDim.x + threadIdx.x; b < nb; b += gridDim.x * blockDim.x) {
+    const unsigned int c = bucket_off[b + 1] - bucket_off[b];
+    mx = c > mx ? c : mx;
+  }
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) {
+    const unsigned int o = __shfl_xor_sync(0xffffffffu, mx, d);
+    mx = o > mx ? o : mx;
+  }
+  if ((threadIdx.x & 31u) == 0 && mx) atomicMax(max_bucket, mx);
+}
+
+static int hybrid_coalesce_wide(const int64_t *row, const int64_t *col, int64_t nnz, int rbits, int cbits, int64_t M,
+                                const void *value, int dtype, bool dedup, int reduce, int64_t *out_row, int64_t *out_col,
+                                void *out_value, int64_t *out_rowptr, int64_t *host_nnz_out, bool *used, cudaStream_t s) {
+  *used = false;
+  const int K = rbits + cbits;
+  if (!hybrid_variant() || ls_variant() == 1 || nnz < (int64_t(1) << 16) || K <= 32) return PS_OK;
+  int T = K - LSW_MAX_R > 1 ? K - LSW_MAX_R : 1;
+  const int tmax = LSW_MAX_T < rbits ? LSW_MAX_T : rbits;
+  while (T <= tmax && (double)nnz * (double)(int64_t(1) << (rbits - T)) / (double)(M > 0 ? M : 1) > 0.9 * L2_CAP) ++T;
+  if (T > tmax) return PS_OK;
+  const int R = K - T;
+  if (rs_num_passes<uint64_t>(T) > 2) return PS_OK;
+  int nb = 1 << T;
+  Scratch scratch(s);
+  PS_SCRATCH(k0, scratch, uint64_t, nnz);
+  PS_SCRATCH(p0, scratch, uint32_t, nnz);
+  PS_SCRATCH(skeys, scratch, uint64_t, nnz);
+  PS_SCRATCH(svals, scratch, uint32_t, nnz);
+  KeySrc ksrc{row, col, KSRC_PACK_COO, cbits};
+  PaySrc psrc = value ? PaySrc{value, pay_src_mode(dtype)} : PaySrc{nullptr, PSRC_NONE};
+  PayDst pdst = value ? PayDst{svals, PDST_U32} : PayDst{nullptr, PDST_NONE};
+  PS_TRY(radix_sort_pairs<uint64_t>(ksrc, psrc, nnz, T, k0, nullptr, p0, nullptr, KeyDst{skeys, nullptr, KDST_KEYS, 0}, pdst,
+                                    scratch, s, R, nullptr));
+  PS_SCRATCH(bucket_off, scratch, unsigned int, (size_t)nb + 2);
+  PS_SCRATCH(d_max, scratch, unsigned int, 1);
+  PS_CUDA(cudaMemsetAsync(d_max, 0, sizeof(unsigned int), s));
+  lsw_bounds_kernel<<<sm_count() * 8, 256, 0, s>>>(skeys, nnz, R, nb, bucket_off);
+  PS_LAUNCH_OK();
+  lsw_max_kernel<<<64, 256, 0, s>>>(bucket_off, nb, d_max);
+  PS_LAUNCH_OK();
+  unsigned int h_max = 0;
+  PS_TRY(read_back(&h_max, d_max, sizeof(h_max), s));
+  if (h_max > (unsigned)L2_CAP) return PS_OK;  // skewed rows: the plain LSD sort handles any distribution
+  {
+    const uint64_t top = M > 0 ? ((((uint64_t)(M - 1)) << cbits) | ((uint64_t(1) << cbits) - 1)) >> R : 0;
+    if ((int64_t)top + 1 < nb) nb = (int)top + 1;
+  }
+  PS_SCRATCH(state, scratch, uint64_t, (size_t)nb + 1);
+  PS_CUDA(cudaMemsetAsync(state, 0, sizeof(uint64_t) * ((size_t)nb + 1), s));
+  PS_SCRATCH(d_nnz, scratch, long long, 1);
+  int rc = PS_ERR_ARG;
+#define PS_LW_ARGS skeys, svals, bucket_off, nb, R, cbits, M, out_row, out_col, out_value, out_rowptr, state, d_nnz, s
+#define PS_LW(T_)                                                                                             \
+  do {                                                                                                        \
+    if (dedup) { PS_DISPATCH_REDUCE(reduce, RED, rc = (ls2_launch<T_, RED, true, true, uint64_t>(PS_LW_ARGS))); } \
+    else rc = ls2_launch<T_, PS_SUM, true, false, uint64_t>(PS_LW_ARGS);                                      \
+  } while (0)
+  if (!value) {
+    rc = dedup ? ls2_launch<float, PS_SUM, false, true, uint64_t>(skeys, nullptr, bucket_off, nb, R, cbits, M, out_row,
+                                                                  out_col, nullptr, out_rowptr, state, d_nnz, s)
+               : ls2_launch<float, PS_SUM, false, false, uint64_t>(skeys, nullptr, bucket_off, nb, R, cbits, M, out_row,
+                                                                   out_col, nullptr, out_rowptr, state, d_nnz, s);
+  } else {
+    switch (dtype) {
+      case PS_F32: PS_LW(float); break;
+      case PS_I32: PS_LW(int32_t); break;
+      case PS_BF16: PS_LW(__nv_bfloat16); break;
+      case PS_F16: PS_LW(__half); break;
+      default: break;
+    }
+  }
+#undef PS_LW
+#undef PS_LW_ARGS
+  PS_TRY(rc);
+  if (dedup) {
+    long long h_nnz = 0;
+    PS_TRY(read_back(&h_nnz, d_nnz, sizeof(h_nnz), s));
+    *host_nnz_out = (int64_t)h_nnz;
+  }
+  *used = true;
+  return PS_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
 // sort + (optionally) dedup, shared by ps_sort_coo and ps_coalesce
 template <typename KeyT>
 int sort_impl(const int64_t *row, const int64_t *col, int64_t nnz, KeyGeom g, const void *value, int dtype,
@@ -432,6 +552,9 @@ int sort_impl(const int64_t *row, const int64_t *col, int64_t nnz, KeyGeom g, co
     int64_t ignored = 0;
     PS_TRY(hybrid_coalesce(row, col, nnz, g.rbits, g.cbits, M, value, dtype, dedup, reduce, out_row, out_col, out_value,
                            out_rowptr, dedup ? host_nnz_out : &ignored, &used, pre, pre_max_bucket, s));
+    if (used) return PS_OK;
+    PS_TRY(hybrid_coalesce_wide(row, col, nnz, g.rbits, g.cbits, M, value, dtype, dedup, reduce, out_row, out_col, out_value,
+                                out_rowptr, dedup ? host_nnz_out : &ignored, &used, s));
     if (used) return PS_OK;
   }
   Scratch scratch(s);

@@ -32,10 +32,12 @@ struct L2Meta {
 };
 template <bool HAS_VALUE>
 struct L2Smem {
-  uint32_t skeys[2][L2_CAP];                   // sorted low keys: [slot] = bucket being sorted / awaiting its offset
+  uint32_t skeys[2][L2_CAP];                   // sorted low keys (their top 32 bits): [slot] = bucket being sorted /
+                                               // awaiting its offset
+  uint8_t slo[2][L2_CAP];                      // ... and their low LO <= 4 bits (bucket-local keys of up to 36 bits)
   uint32_t svals[2][HAS_VALUE ? L2_CAP : 4];   // their values
   uint32_t wkeys[L2_CAP];                      // by bin (arrival order inside a bin)
-  uint16_t widx[L2_CAP];                       // arrival index of the entry in that slot
+  uint16_t widx[L2_CAP];                       // low key bits << 12 | arrival index of the entry in that slot
   uint32_t bins[L2_BINS / 2 + 2];              // two 16-bit counters per word; after the scan: bin starts (+ sentinel)
   uint32_t wcnt[L2_ITEMS * L2_WARPS];
   uint32_t scan_tmp[33];
@@ -50,9 +52,13 @@ struct L2Smem {
 // offset from the chain and is written out.  The chain (a decoupled look-back over the buckets) is thereby consumed
 // one whole bucket-sort after it was fed: in round 2's first version, which consumed it at once, 38 % of all warp
 // samples sat at the barrier behind the look-back warp.
-template <typename T, int RED, bool HAS_VALUE, bool DEDUP>
+// KeyT = uint32_t: `lowkeys` holds the bucket-local keys (R <= 32 bits); uint64_t: the full packed keys, of which the
+// low R <= 36 bits are the bucket-local key (shards of very wide matrices: 51- to 53-bit keys whose local part does
+// not fit 32 bits).  The local key is handled as (top 32 bits, low LO = R - 32 bits); the low bits share a 16-bit
+// word with the 12-bit arrival index, so "(key, arrival index) lexicographic" stays two integer compares.
+template <typename T, int RED, bool HAS_VALUE, bool DEDUP, typename KeyT>
 __global__ void __launch_bounds__(L2_THREADS, 2)
-ls2_sort_dedup_kernel(const uint32_t *__restrict__ lowkeys, const uint32_t *__restrict__ lowvals,
+ls2_sort_dedup_kernel(const KeyT *__restrict__ lowkeys, const uint32_t *__restrict__ lowvals,
                       const unsigned int *__restrict__ bucket_off, int nb, int R, int cbits, int64_t M,
                       int64_t *__restrict__ out_row, int64_t *__restrict__ out_col, T *__restrict__ out_value,
                       int64_t *__restrict__ out_rowptr, uint64_t *state /*[0]=ticket,[1..]=buckets*/,
@@ -63,7 +69,10 @@ ls2_sort_dedup_kernel(const uint32_t *__restrict__ lowkeys, const uint32_t *__re
   L2Smem<HAS_VALUE> &sm = *reinterpret_cast<L2Smem<HAS_VALUE> *>(l2_raw);
   const unsigned tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
   const unsigned lt = lanemask_lt();
-  const int binshift = R > L2_BINBITS ? R - L2_BINBITS : 0;
+  const int LO = R > 32 ? R - 32 : 0;                       // low key bits kept beside the 32-bit part
+  const int binshift = (R > L2_BINBITS ? R - L2_BINBITS : 0) - LO;  // applied to the 32-bit part
+  const uint32_t lomask = (1u << LO) - 1u;
+  const uint64_t rmask = R >= 64 ? ~uint64_t(0) : ((uint64_t(1) << R) - 1);
   const uint64_t cmask = (uint64_t(1) << cbits) - 1;
   const uint16_t *bstart16 = reinterpret_cast<const uint16_t *>(sm.bins);
 
@@ -89,12 +98,23 @@ ls2_sort_dedup_kernel(const uint32_t *__restrict__ lowkeys, const uint32_t *__re
       const int cnt = (int)(sm.meta[slot].end - start);
       const int ie = (cnt + THREADS - 1) / THREADS;  // item rows in use (uniform)
       uint32_t *skeys = sm.skeys[slot], *svals = sm.svals[slot];
+      uint8_t *slo = sm.slo[slot];
       // ---- A: keys and values into registers (entry j = i * THREADS + tid: its arrival index)
       uint32_t key[ITEMS], val[HAS_VALUE ? ITEMS : 1];
+      uint32_t klo = 0;  // the low LO bits of the ITEMS keys, 4 bits each
 #pragma unroll
       for (int i = 0; i < ITEMS; ++i) {
         const int j = i * THREADS + (int)tid;
-        key[i] = (i < ie && j < cnt) ? ld_stream(lowkeys + start + j) : 0xffffffffu;
+        key[i] = 0xffffffffu;
+        if (i < ie && j < cnt) {
+          if (sizeof(KeyT) == 8) {
+            const uint64_t low = (uint64_t)ld_stream(lowkeys + start + j) & rmask;
+            key[i] = (uint32_t)(low >> LO);
+            klo |= ((uint32_t)low & lomask) << (4 * i);
+          } else {
+            key[i] = (uint32_t)ld_stream(lowkeys + start + j);
+          }
+        }
       }
       if (HAS_VALUE) {
 #pragma unroll
@@ -161,7 +181,7 @@ ls2_sort_dedup_kernel(const uint32_t *__restrict__ lowkeys, const uint32_t *__re
           if (i < ie && i * THREADS + (int)tid < cnt) {
             const unsigned pos = (unsigned)bstart16[br[i] & 0xffffu] + (br[i] >> 16);
             sm.wkeys[pos] = key[i];
-            sm.widx[pos] = (uint16_t)(i * THREADS + tid);
+            sm.widx[pos] = (uint16_t)((((klo >> (4 * i)) & 15u) << 12) | (unsigned)(i * THREADS + tid));
           }
         }
         __syncthreads();
@@ -170,7 +190,7 @@ ls2_sort_dedup_kernel(const uint32_t *__restrict__ lowkeys, const uint32_t *__re
           if (i < ie && i * THREADS + (int)tid < cnt) {
             const unsigned b = br[i] & 0xffffu;
             const unsigned s_ = bstart16[b], e_ = bstart16[b + 1];
-            const unsigned me = (unsigned)(i * THREADS) + tid;
+            const unsigned me = (((klo >> (4 * i)) & 15u) << 12) | ((unsigned)(i * THREADS) + tid);
             unsigned less = 0;
             if (e_ - s_ > 1) {
               for (unsigned t = s_; t < e_; ++t) {
@@ -180,6 +200,7 @@ ls2_sort_dedup_kernel(const uint32_t *__restrict__ lowkeys, const uint32_t *__re
               }
             }
             skeys[s_ + less] = key[i];
+            if (sizeof(KeyT) == 8) slo[s_ + less] = (uint8_t)((klo >> (4 * i)) & 15u);
             if (HAS_VALUE) svals[s_ + less] = val[i];
           }
         }
@@ -189,6 +210,7 @@ ls2_sort_dedup_kernel(const uint32_t *__restrict__ lowkeys, const uint32_t *__re
           if (i < ie && i * THREADS + (int)tid < cnt) {
             const unsigned pos = (unsigned)bstart16[br[i] & 0xffffu];
             skeys[pos] = key[i];
+            if (sizeof(KeyT) == 8) slo[pos] = (uint8_t)((klo >> (4 * i)) & 15u);
             if (HAS_VALUE) svals[pos] = val[i];
           }
         }
@@ -201,7 +223,7 @@ ls2_sort_dedup_kernel(const uint32_t *__restrict__ lowkeys, const uint32_t *__re
         for (int i = 0; i < ITEMS; ++i) {
           if (i < ie) {
             const int j = i * THREADS + (int)tid;
-            const bool h = j < cnt && (j == 0 || skeys[j] != skeys[j - 1]);
+            const bool h = j < cnt && (j == 0 || skeys[j] != skeys[j - 1] || (sizeof(KeyT) == 8 && slo[j] != slo[j - 1]));
             mine += __popc(__ballot_sync(0xffffffffu, h));
           }
         }
@@ -223,6 +245,10 @@ ls2_sort_dedup_kernel(const uint32_t *__restrict__ lowkeys, const uint32_t *__re
       const int cnt = (int)(sm.meta[ps_].end - start);
       const int ie = (cnt + THREADS - 1) / THREADS;
       const uint32_t *skeys = sm.skeys[ps_], *svals = sm.svals[ps_];
+      const uint8_t *slo = sm.slo[ps_];
+      auto lowkey = [&](int j) -> uint64_t {  // the bucket-local key of sorted slot j
+        return sizeof(KeyT) == 8 ? (((uint64_t)skeys[j] << LO) | slo[j]) : (uint64_t)skeys[j];
+      };
       unsigned heads = 0, below[ITEMS];
       if (DEDUP) {
 #pragma unroll
@@ -230,7 +256,7 @@ ls2_sort_dedup_kernel(const uint32_t *__restrict__ lowkeys, const uint32_t *__re
           below[i] = 0;
           if (i < ie) {  // uniform
             const int j = i * THREADS + (int)tid;
-            const bool h = j < cnt && (j == 0 || skeys[j] != skeys[j - 1]);
+            const bool h = j < cnt && (j == 0 || skeys[j] != skeys[j - 1] || (sizeof(KeyT) == 8 && slo[j] != slo[j - 1]));
             const unsigned bal = __ballot_sync(0xffffffffu, h);
             heads |= (unsigned)h << i;
             below[i] = __popc(bal & lt);
@@ -321,7 +347,7 @@ ls2_sort_dedup_kernel(const uint32_t *__restrict__ lowkeys, const uint32_t *__re
       for (int i = 0; i < ITEMS; ++i) {
         if (!((heads >> i) & 1u)) continue;
         const int j = i * THREADS + (int)tid;
-        const uint32_t lk = skeys[j];
+        const uint64_t lk = lowkey(j);
         const int64_t o = excl + below[i] + (DEDUP ? sm.wcnt[i * WARPS + warp] : 0u);
         const uint64_t full = hi_bits | lk;
         const int64_t r = (int64_t)(full >> cbits);
@@ -331,14 +357,14 @@ ls2_sort_dedup_kernel(const uint32_t *__restrict__ lowkeys, const uint32_t *__re
         if (HAS_VALUE && DEDUP) {
           A acc = to_acc<T>(pay_as<T>(svals[j]));
           int jj = j + 1;
-          while (jj < cnt && skeys[jj] == lk) {
+          while (jj < cnt && lowkey(jj) == lk) {
             acc = Red<RED, A>::op(acc, to_acc<T>(pay_as<T>(svals[jj])));
             ++jj;
           }
           out_value[o] = from_acc<T>(Red<RED, A>::finish(acc, (int64_t)(jj - j)));
         }
         if (out_rowptr) {
-          const int64_t pr = j == 0 ? rlo - 1 : (int64_t)((hi_bits | skeys[j - 1]) >> cbits);
+          const int64_t pr = j == 0 ? rlo - 1 : (int64_t)((hi_bits | lowkey(j - 1)) >> cbits);
           if (r != pr && r <= M) {  // this head opens row r ...
             out_rowptr[r] = o;
             if (r - pr > 1)  // ... and the empty rows before it (rare)
@@ -347,7 +373,7 @@ ls2_sort_dedup_kernel(const uint32_t *__restrict__ lowkeys, const uint32_t *__re
         }
       }
       if (out_rowptr) {  // rows of this bucket after its last entry (all of them when the bucket is empty)
-        const int64_t first = cnt > 0 ? (int64_t)((hi_bits | skeys[cnt - 1]) >> cbits) + 1 : rlo;
+        const int64_t first = cnt > 0 ? (int64_t)((hi_bits | lowkey(cnt - 1)) >> cbits) + 1 : rlo;
         for (int64_t q = first + tid; q < rhi; q += THREADS) out_rowptr[q] = excl + nheads;
       }
       if (DEDUP && pbucket == nb - 1 && tid == 0) *d_nnz_out = (long long)(excl + nheads);

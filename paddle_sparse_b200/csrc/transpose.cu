@@ -357,9 +357,21 @@ int ps_csc_build(const int64_t *row, const int64_t *col, const void *value, int6
   PS_CHECK(nnz < (int64_t(1) << 32), "csc_build: nnz=%lld exceeds the 2^32-1 entries per call this build supports",
            (long long)nnz);
   PS_CHECK(N <= (int64_t(1) << 32), "csc_build: N=%lld exceeds the 2^32 columns this build supports", (long long)N);
+  cudaStream_t s = (cudaStream_t)stream;
+  if (!out_t_row) {  // nothing rides along (row, value may be NULL): csr2csc, colptr, colcount, csc2csr only
+    PS_CHECK(col && out_csr2csc && !out_t_col && !out_t_value, "csc_build: NULL argument");
+    if (nnz > 0) {
+      bool used = false;
+      PS_TRY(csc_hybrid(nullptr, col, nullptr, nnz, N, out_csr2csc, out_colptr, out_colcount, nullptr, nullptr, nullptr,
+                        out_csc2csr, &used, s));
+      if (used) return PS_OK;
+    }
+    PS_TRY(ps_csr2csc(col, nnz, N, out_csr2csc, out_colptr, out_colcount, stream));
+    if (out_csc2csr && nnz > 0) PS_TRY(invert_perm_impl(out_csr2csc, nnz, out_csc2csr, s));
+    return PS_OK;
+  }
   PS_CHECK(row && col && out_csr2csc && out_t_row && out_t_col, "csc_build: NULL argument");
   PS_CHECK(!value || (value_bytes == 4 && out_t_value), "csc_build: carried values are one 4-byte element per entry");
-  cudaStream_t s = (cudaStream_t)stream;
   Scratch scratch(s);
   const bool want_ptr = out_colptr || out_colcount;
   int64_t *colptr = out_colptr;

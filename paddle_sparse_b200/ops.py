@@ -278,13 +278,23 @@ def csr2csc(col: torch.Tensor, N: int, want_colptr: bool = True, want_colcount: 
     return perm, colptr, colcount
 
 
-def csc_build(row: torch.Tensor, col: torch.Tensor, value: Optional[torch.Tensor], N: int,
-              want_colcount: bool = True, want_csc2csr: bool = True):
+def csc_build(row: Optional[torch.Tensor], col: torch.Tensor, value: Optional[torch.Tensor], N: int,
+              want_colcount: bool = True, want_csc2csr: bool = True, carry: bool = True):
     """storage.py:386-447 + transpose.py:9-33 in one call: csr2csc, colptr, colcount, csc2csr and the transposed
     arrays (col[csr2csc], row[csr2csc], value[csr2csc]); the values ride through the sort when they are one 4-byte
     element per entry, else they are gathered once at the end.
     Returns dict(csr2csc, colptr, colcount, csc2csr, t_row, t_col, t_value)."""
-    row, col = _idx(row, "row"), _idx(col, "col")
+    col = _idx(col, "col")
+    if not carry:  # csr2csc, colptr, colcount, csc2csr only: nothing rides along, no transposed arrays
+        nnz = col.numel()
+        perm, colptr = _new(col, nnz), _new(col, N + 1)
+        colcount = _new(col, N) if want_colcount else None
+        inv = _new(col, nnz) if want_csc2csr else None
+        with torch.cuda.device(col.device):
+            _lib.call("ps_csc_build", None, _p(col), None, 0, nnz, N, _p(perm), _p(colptr), _p(colcount), _p(inv), None,
+                      None, None, _stream(col))
+        return dict(csr2csc=perm, colptr=colptr, colcount=colcount, csc2csr=inv, t_row=None, t_col=None, t_value=None)
+    row = _idx(row, "row")
     value = None if value is None else _dev(value, "value")
     nnz = col.numel()
     carry = value is not None and nnz > 0 and _row_bytes(value) == 4 and not _ag.needs_grad(value)
