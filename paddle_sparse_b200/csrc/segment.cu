@@ -15,10 +15,15 @@ namespace ps {
 // G lanes cooperate on one output (segment s, feature f); o = s*width + f.
 // W1: width == 1 known at compile time (the [nnz] value vector of reduce.py:51) - no 64-bit divide per output,
 // and the segment walk is unrolled so that each lane keeps several loads in flight.
+// Long segments (hub rows of power-law graphs) do not ride on G lanes: a group that meets a segment of more than
+// `long_thresh` entries appends its output index to `long_list` and moves on; segment_reduce_long_kernel then gives
+// every listed output a whole CTA.  The reference's segment_csr (paddle_scatter, a port of torch_scatter) walks a
+// segment with a fixed group of lanes whatever its length.
 template <typename T, int RED, int G, bool W1>
 __global__ void __launch_bounds__(256)
 segment_reduce_kernel(const T *__restrict__ src, int64_t width, const int64_t *__restrict__ ptr, int64_t S,
-                      T *__restrict__ out, const uint32_t *__restrict__ perm) {
+                      T *__restrict__ out, const uint32_t *__restrict__ perm, int64_t long_thresh,
+                      unsigned long long *__restrict__ long_list /*[0] = count, [1..] = output indices*/) {
   using A = typename Acc<T>::type;
   const int64_t gid = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / G;
   const int sub = threadIdx.x % G;
@@ -30,6 +35,11 @@ segment_reduce_kernel(const T *__restrict__ src, int64_t width, const int64_t *_
   if (live) {
     lo = ptr[sgm];
     hi = ptr[sgm + 1];
+  }
+  const bool deferred = hi - lo > long_thresh;  // uniform inside the group
+  if (deferred) {
+    if (sub == 0) long_list[1 + atomicAdd(long_list, 1ull)] = (unsigned long long)gid;
+    hi = lo;  // nothing to walk; the store below is suppressed
   }
   A acc = Red<RED, A>::init();
   if (W1) {
@@ -52,7 +62,47 @@ segment_reduce_kernel(const T *__restrict__ src, int64_t width, const int64_t *_
   }
 #pragma unroll
   for (int d = G / 2; d > 0; d >>= 1) acc = Red<RED, A>::op(acc, __shfl_xor_sync(0xffffffffu, acc, d));
-  if (live && sub == 0) out[gid] = from_acc<T>(Red<RED, A>::finish(acc, hi - lo));
+  if (live && sub == 0 && !deferred) out[gid] = from_acc<T>(Red<RED, A>::finish(acc, hi - lo));
+}
+
+// One CTA per listed output: 256 threads walk the segment with four loads in flight each, partial results combined
+// in a fixed order (lane tree, then warp 0 over the 8 warp results): deterministic for a given segment.
+template <typename T, int RED>
+__global__ void __launch_bounds__(256)
+segment_reduce_long_kernel(const T *__restrict__ src, int64_t width, const int64_t *__restrict__ ptr, T *__restrict__ out,
+                           const uint32_t *__restrict__ perm, const unsigned long long *__restrict__ long_list) {
+  using A = typename Acc<T>::type;
+  __shared__ A part[8];
+  const unsigned long long count = long_list[0];
+  for (unsigned long long li = blockIdx.x; li < count; li += gridDim.x) {
+    const int64_t gid = (int64_t)long_list[1 + li];
+    const int64_t sgm = gid / width, f = gid - sgm * width;
+    const int64_t lo = ptr[sgm], hi = ptr[sgm + 1];
+    A acc = Red<RED, A>::init();
+    int64_t e = lo + threadIdx.x;
+    for (; e + 3 * 256 < hi; e += 4 * 256) {
+      T v[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int64_t r = perm ? (int64_t)perm[e + q * 256] : e + q * 256;
+        v[q] = src[r * width + f];
+      }
+#pragma unroll
+      for (int q = 0; q < 4; ++q) acc = Red<RED, A>::op(acc, to_acc<T>(v[q]));
+    }
+    for (; e < hi; e += 256) acc = Red<RED, A>::op(acc, to_acc<T>(src[(perm ? (int64_t)perm[e] : e) * width + f]));
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) acc = Red<RED, A>::op(acc, __shfl_xor_sync(0xffffffffu, acc, d));
+    if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+      A a = threadIdx.x < 8 ? part[threadIdx.x] : Red<RED, A>::init();
+#pragma unroll
+      for (int d = 4; d > 0; d >>= 1) a = Red<RED, A>::op(a, __shfl_xor_sync(0xffffffffu, a, d));
+      if (threadIdx.x == 0) out[gid] = from_acc<T>(Red<RED, A>::finish(a, hi - lo));
+    }
+    __syncthreads();
+  }
 }
 
 template <typename T, int RED>
@@ -67,8 +117,15 @@ static int segment_reduce_typed(const T *src, int64_t width, const int64_t *ptr,
   else if (avg <= 48.0) G = 8;
   const int64_t threads = outputs * G;
   const unsigned blocks = (unsigned)ceil_div(threads, 256);
+  // segments a group of G lanes should not walk alone: more than 128 entries per lane
+  const int64_t long_thresh = 128 * (int64_t)G;
+  const size_t list_cap = (size_t)(E_hint > 0 ? (E_hint / long_thresh + 1) * (width > 0 ? width : 1) : outputs) + 2;
+  Scratch scratch(s);
+  PS_SCRATCH(long_list, scratch, unsigned long long, list_cap < (size_t)outputs + 2 ? list_cap : (size_t)outputs + 2);
+  PS_CUDA(cudaMemsetAsync(long_list, 0, sizeof(unsigned long long), s));
   ProfScope prof(PROF_SEGMENT_REDUCE, s);
-#define PS_SR(G_, W1_) segment_reduce_kernel<T, RED, G_, W1_><<<blocks, 256, 0, s>>>(src, width, ptr, S, out, perm)
+#define PS_SR(G_, W1_) \
+  segment_reduce_kernel<T, RED, G_, W1_><<<blocks, 256, 0, s>>>(src, width, ptr, S, out, perm, long_thresh, long_list)
   if (width == 1) {
     switch (G) {
       case 1: PS_SR(1, true); break;
@@ -85,6 +142,8 @@ static int segment_reduce_typed(const T *src, int64_t width, const int64_t *ptr,
     }
   }
 #undef PS_SR
+  PS_LAUNCH_OK();
+  segment_reduce_long_kernel<T, RED><<<sm_count() * 2, 256, 0, s>>>(src, width, ptr, out, perm, long_list);
   PS_LAUNCH_OK();
   return PS_OK;
 }

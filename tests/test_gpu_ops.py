@@ -352,3 +352,37 @@ def test_scatter_min_max_with_negative_zero(ops, dtype):
         fn.at(want, idx, v)
         got = host(ops.scatter(src, dev(idx), 0, None, S, red)).astype(np.float64)
         assert np.array_equal(got, want), red  # +0.0 == -0.0 compares equal; everything else must match exactly
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16, torch.int64])
+@pytest.mark.parametrize("width", [1, 3])
+def test_segment_csr_long_segments(ops, dtype, width):
+    """Hub rows: one segment holding 30 % of the entries, a few of several thousand, many short and empty ones -
+    the long ones are handed to whole CTAs (segment_reduce_long_kernel), every result must still equal the oracle."""
+    rng = np.random.default_rng(31 + width)
+    S, E = 20_000, 600_000
+    lens = rng.poisson(8, S).astype(I64)
+    lens[rng.integers(0, S, S // 20)] = 0
+    lens[123] = int(0.3 * E)
+    lens[[7, 4000, S - 1]] = [5000, 129, 9000]
+    lens = (lens * (E / lens.sum())).astype(I64)  # keep the proportions, hit roughly E entries
+    ptr = np.concatenate([[0], np.cumsum(lens)]).astype(I64)
+    n = int(ptr[-1])
+    shape = (n,) if width == 1 else (n, width)
+    if dtype == torch.int64:
+        v = rng.integers(-50, 50, shape).astype(np.int64)
+    else:
+        v = (rng.integers(-8, 9, shape) / 4.0).astype(np.float32)  # exactly representable, exact sums
+    src = dev(v, dtype)
+    for red in REDUCES:
+        got = host(ops.segment_csr(src, dev(ptr), None, red)).astype(np.float64)
+        want = np_ref.segment_csr(v.astype(np.float64), ptr, red).astype(np.float64)
+        if dtype == torch.int64 and red == "mean":
+            want = np_ref.segment_csr(v, ptr, red).astype(np.float64)
+        if red == "mean" and dtype != torch.int64:
+            rtol = 8e-3 if dtype == torch.bfloat16 else 1e-6
+            np.testing.assert_allclose(got, want, rtol=rtol, atol=1e-7, err_msg=red)
+        elif dtype == torch.bfloat16 and red in ("sum", "add"):
+            np.testing.assert_allclose(got, want, rtol=8e-3, atol=0.26, err_msg=red)  # one bf16 rounding of an exact sum
+        else:
+            assert np.array_equal(got, want), red
