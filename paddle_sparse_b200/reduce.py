@@ -30,12 +30,17 @@ def reduction(src: SparseTensor, dim: Optional[int] = None, reduce: str = "sum")
 
     if dim == 0:  # reduce.py:40-47
         if value is not None:
-            parked = src.storage.csc_ordered_value()
-            if parked is not None and src.storage.has_colptr():
+            st = src.storage
+            parked = st.csc_ordered_value()
+            if parked is not None and st.has_colptr():
                 # fill_cache_ left value[csr2csc] behind: columns are contiguous runs there, no atomics needed
-                return ops.segment_csr(parked, src.storage.colptr(), None, reduce)
-            count = src.storage._colcount if reduce != "sum" else None  # cached histogram of col, if any
-            return ops.scatter(value, src.storage.col(), 0, None, src.size(1), reduce, count)
+                return ops.segment_csr(parked, st.colptr(), None, reduce)
+            accel = st.column_reduction_accel()
+            if accel is not None:  # the second and later column reductions of one matrix (see the storage method)
+                return ops.segment_csr(accel[0], accel[1], None, reduce)
+            # mean / min / max need the per-column counts: a histogram computed once saves the second atomic per entry
+            count = st.colcount_quiet() if reduce != "sum" else None
+            return ops.scatter(value, st.col(), 0, None, src.size(1), reduce, count)
         if reduce == "sum":
             return src.storage.colcount().to(src.dtype())
         return torch.ones(src.size(1), dtype=src.dtype(), device=src.device())

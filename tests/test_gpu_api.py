@@ -334,6 +334,29 @@ def test_reductions_all_dims(ps, reduce, width):
         ps.reduction(A, 0, "prod")
 
 
+def test_repeated_column_reductions_switch_to_contiguous_columns(ps):
+    """reduce.py:40-42 asked repeatedly on one matrix: the first call is an atomic scatter, the second builds the
+    carrying CSC sort privately and every later one is a segment reduction over colptr - same results, no cache key
+    appears (cached_keys evolves as in the reference), and a new value tensor or clear_cache_ drops the helper."""
+    rng = np.random.default_rng(23)
+    M, N = 3000, 2000
+    row, col, val = _pair(rng, M, N, 150_000)
+    A = ps.SparseTensor(row=dev(row), col=dev(col), value=dev(val), sparse_sizes=(M, N))
+    O = np_ref.SparseTensor(row=row, col=col, value=val.astype(np.float64), sparse_sizes=(M, N))
+    for k, red in enumerate(("sum", "mean", "max", "min", "sum")):
+        got = getattr(A, red)(0)
+        np.testing.assert_allclose(host(got), np_ref.reduction(O, 0, red), rtol=0 if red in ("min", "max") else 2e-6)
+        assert (getattr(A.storage, "_dim0_accel", None) is not None) == (k >= 1)
+        assert A.storage.cached_keys() == []
+    B = A.set_value(A.storage.value() * 2, layout="coo")
+    assert getattr(B.storage, "_dim0_accel", None) is None
+    np.testing.assert_allclose(host(B.sum(0)), 2 * np_ref.reduction(O, 0, "sum"), rtol=2e-6)
+    A.storage.value().mul_(3.0)  # an in-place edit is noticed through the version counter
+    np.testing.assert_allclose(host(A.sum(0)), 3 * np_ref.reduction(O, 0, "sum"), rtol=2e-6)
+    A.clear_cache_()
+    assert getattr(A.storage, "_dim0_accel", None) is None and A.storage._dim0_calls == 0
+
+
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16, torch.float64])
 def test_mul_broadcast(ps, dtype):
     rng = np.random.default_rng(23)
