@@ -176,6 +176,9 @@ struct RsSmem {
   alignas(8) uint64_t mbar;
   uint32_t cnt[WARPS][ROW];  // two 16-bit counters per word: items of (warp, digit); later the group's start in the tile
   uint32_t gbase[RADIX];     // global position of the digit's run minus its offset inside the tile
+  uint16_t part_tot[THREADS / RADIX > 0 ? THREADS / RADIX : 1][RADIX];  // digit totals of each group of warps
+  uint32_t dtot[RADIX];      // items of the digit in this tile
+  uint32_t dstart[RADIX];    // offset of the digit inside the sorted tile
   uint32_t scan_tmp[32];
   long long tile_next;
 };
@@ -441,49 +444,66 @@ rs_pass_kernel(KeySrc ksrc, PaySrcN<NPAY> psrc, KeyDst kdst, PayDstN<NPAY> pdst,
     __syncthreads();
     PS_TL(2);
 
-    // ---- 3: column scans.  Lane l reads the counter of warp l for each of this warp's DPW digits.
-    uint32_t tot = 0;       // digit threads: total of my digit in this tile
-    uint32_t wsum = 0;      // all lanes: total of this warp's DPW digits
-    uint32_t below = 0;     // digit threads: total of this warp's digits below mine
-    uint16_t *col = reinterpret_cast<uint16_t *>(&sm.cnt[lane < (unsigned)WARPS ? lane : 0][0]) + warp * DPW;
+    // ---- 3: prefix over the warps, per digit.  Thread (digit, part) walks the counters of its part of the warps
+    // row-wise (conflict-free, no shuffles: round 1 scanned the digit columns with 5-step shuffle scans, 16 % of a
+    // tile's time), the parts are combined, a block scan over the digit totals gives every digit its offset inside the
+    // sorted tile, and that offset is folded back into the counters, which thereby become the start of every
+    // (warp, digit) group in the tile.
+    constexpr int PARTS = THREADS / RADIX > 0 ? THREADS / RADIX : 1;
+    constexpr int WPP = WARPS / PARTS;            // warps per part
+    constexpr int DW = RADIX / 32;                // warps whose lanes cover the digits once
+    static_assert(THREADS % RADIX == 0 && WARPS % PARTS == 0 && DW <= 32, "digit / part ownership");
+    const unsigned dg = tid % RADIX, part = tid / RADIX;
+    uint16_t *c16 = reinterpret_cast<uint16_t *>(&sm.cnt[part * WPP][0]) + dg;
     {
+      uint32_t run = 0;
 #pragma unroll
-      for (int k = 0; k < DPW; ++k) {
-        const uint32_t c = lane < (unsigned)WARPS ? (uint32_t)col[k] : 0u;
-        uint32_t inc = c;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-          const uint32_t o = __shfl_up_sync(0xffffffffu, inc, d);
-          if (lane >= (unsigned)d) inc += o;
-        }
-        if (lane < (unsigned)WARPS) col[k] = (uint16_t)(inc - c);  // items of digit k in warps < l
-        const uint32_t t = __shfl_sync(0xffffffffu, inc, 31);
-        if (lane == (unsigned)k) { tot = t; below = wsum; }
-        wsum += t;
+      for (int w = 0; w < WPP; ++w) {
+        const uint32_t c = c16[w * (Smem::ROW * 2)];
+        c16[w * (Smem::ROW * 2)] = (uint16_t)run;
+        run += c;
       }
+      sm.part_tot[part][dg] = (uint16_t)run;
     }
-    if (digit_thread)
-      TileState::store(stw + tile * RADIX, RsState::pack(epoch, tile == 0 ? RsState::PREFIX : RsState::AGG, tot));
-    const uint64_t lbw = rs_lb_word(stw, RADIX, tile - 1 - (int64_t)(lane / DPW), epoch);
-    if (lane == 0) sm.scan_tmp[warp] = wsum;
     __syncthreads();
-    uint32_t dexcl;  // digit threads: offset of my digit inside the sorted tile
     {
+      uint32_t dt = 0, before = 0;
+#pragma unroll
+      for (int h = 0; h < PARTS; ++h) {
+        const uint32_t t = sm.part_tot[h][dg];
+        before += h < (int)part ? t : 0u;
+        dt += t;
+      }
+      uint32_t inc = dt;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t o = __shfl_up_sync(0xffffffffu, inc, d);
+        if (lane >= (unsigned)d) inc += o;
+      }
+      if (lane == 31) sm.scan_tmp[warp] = inc;
+      __syncthreads();
       uint32_t wb = 0;
 #pragma unroll
-      for (int w = 0; w < WARPS; ++w) wb += (w < (int)warp) ? sm.scan_tmp[w] : 0u;
-      dexcl = wb + below;
-      // group start of (warp l, digit k) = start of digit k + items of digit k in warps < l
-#pragma unroll
-      for (int k = 0; k < DPW; ++k) {
-        const uint32_t dk = __shfl_sync(0xffffffffu, dexcl, k);
-        if (lane < (unsigned)WARPS) col[k] = (uint16_t)(dk + col[k]);
+      for (int w = 0; w < DW; ++w) wb += (w < (int)(warp % DW)) ? sm.scan_tmp[part * DW + w] : 0u;
+      const uint32_t ds = wb + inc - dt;  // offset of digit dg inside the sorted tile
+      if (part == 0) {
+        sm.dtot[dg] = dt;
+        sm.dstart[dg] = ds;
       }
+      const uint32_t add = ds + before;
+#pragma unroll
+      for (int w = 0; w < WPP; ++w) c16[w * (Smem::ROW * 2)] = (uint16_t)(c16[w * (Smem::ROW * 2)] + add);
     }
     if (tid == 0) sm.tile_next = ticket_ahead;
     PS_TL(3);
     __syncthreads();
     PS_TL(4);
+    // digit threads publish the tile's aggregate and request the first look-back words
+    const uint32_t tot = sm.dtot[my_digit];
+    const uint32_t dexcl = sm.dstart[my_digit];
+    if (digit_thread)
+      TileState::store(stw + tile * RADIX, RsState::pack(epoch, tile == 0 ? RsState::PREFIX : RsState::AGG, tot));
+    const uint64_t lbw = rs_lb_word(stw, RADIX, tile - 1 - (int64_t)(lane / DPW), epoch);
 
     // ---- 4: position inside the sorted tile = group start + rank inside the group; stage
     {
