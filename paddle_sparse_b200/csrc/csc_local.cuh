@@ -316,7 +316,8 @@ cl_local_kernel(const uint32_t *__restrict__ scol, const uint32_t *__restrict__ 
       const int j = k * THREADS + tid;
       if (j < cnt) {
         const unsigned d = sm.dig[j];
-        const size_t dst = (size_t)(sm.gb[d] + (uint32_t)j);
+        // (a bucket that is one chunk goes out as one streaming range: no per-digit base to look up)
+        const size_t dst = (size_t)((multi ? sm.gb[d] : boff) + (uint32_t)j);
         const uint32_t p = sm.a[j];
         out_csr2csc[dst] = (int64_t)p;
         if (CARRY) out_t_row[dst] = colbase + d;
@@ -359,7 +360,7 @@ cl_local_kernel(const uint32_t *__restrict__ scol, const uint32_t *__restrict__ 
         if (j2 < cnt) {
           const unsigned j = sm.ix[j2];
           const uint32_t p = sm.a[j];
-          const uint32_t q = sm.gb[sm.dig[j]] + j;
+          const uint32_t q = (multi ? sm.gb[sm.dig[j]] : boff) + j;
           const size_t dst = (size_t)(igb[(p >> inv.shift) & imask] + (uint32_t)j2);
           inv.tp[dst] = p;
           inv.tq[dst] = q;
@@ -389,7 +390,7 @@ cl_local_kernel(const uint32_t *__restrict__ scol, const uint32_t *__restrict__ 
       for (int k = 0; k < ITEMS; ++k) {
         const int j = k * THREADS + tid;
         if (j < cnt) {
-          const size_t dst = (size_t)(sm.gb[sm.dig[j]] + (uint32_t)j);
+          const size_t dst = (size_t)((multi ? sm.gb[sm.dig[j]] : boff) + (uint32_t)j);
           out_t_col[dst] = (int64_t)sm.a[j];
           if (HAS_VALUE) out_t_val[dst] = sm.v[j];
         }

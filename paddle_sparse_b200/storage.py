@@ -480,7 +480,7 @@ class SparseStorage(object):
         will not transpose (the row-sharded build) turns it off and saves 20 bytes per entry of writes."""
         self.row()
         self.rowptr()
-        self.rowcount()
+        # the CSC side first: its kernels are the long ones, the host prepares the small launches behind them
         if self._csr2csc is None and self._col.numel() > 0:
             if carry:
                 self._build_csc_carry(True)
@@ -491,6 +491,7 @@ class SparseStorage(object):
                     self._colptr = r["colptr"]
                 if self._colcount is None:
                     self._colcount = r["colcount"]
+        self.rowcount()
         self.csr2csc()
         self.colptr()
         self.colcount()
