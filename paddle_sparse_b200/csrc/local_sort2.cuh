@@ -36,8 +36,9 @@ struct L2Smem {
                                                // awaiting its offset
   uint8_t slo[2][L2_CAP];                      // ... and their low LO <= 4 bits (bucket-local keys of up to 36 bits)
   uint32_t svals[2][HAS_VALUE ? L2_CAP : 4];   // their values
-  uint32_t wkeys[L2_CAP];                      // by bin (arrival order inside a bin)
-  uint16_t widx[L2_CAP];                       // low key bits << 12 | arrival index of the entry in that slot
+  uint64_t wk[L2_CAP];                         // by bin (arrival order inside a bin): key's 32-bit part << 16 | its low
+                                               // bits << 12 | arrival index - ONE word, so that "(key, arrival index)
+                                               // lexicographic" is one 64-bit compare in the bin-mate loop
   uint32_t bins[L2_BINS / 2 + 2];              // two 16-bit counters per word; after the scan: bin starts (+ sentinel)
   uint32_t wcnt[L2_ITEMS * L2_WARPS];
   uint32_t scan_tmp[33];
@@ -180,8 +181,7 @@ ls2_sort_dedup_kernel(const KeyT *__restrict__ lowkeys, const uint32_t *__restri
         for (int i = 0; i < ITEMS; ++i) {
           if (i < ie && i * THREADS + (int)tid < cnt) {
             const unsigned pos = (unsigned)bstart16[br[i] & 0xffffu] + (br[i] >> 16);
-            sm.wkeys[pos] = key[i];
-            sm.widx[pos] = (uint16_t)((((klo >> (4 * i)) & 15u) << 12) | (unsigned)(i * THREADS + tid));
+            sm.wk[pos] = ((uint64_t)key[i] << 16) | ((((klo >> (4 * i)) & 15u) << 12) | (unsigned)(i * THREADS + tid));
           }
         }
         __syncthreads();
@@ -190,14 +190,11 @@ ls2_sort_dedup_kernel(const KeyT *__restrict__ lowkeys, const uint32_t *__restri
           if (i < ie && i * THREADS + (int)tid < cnt) {
             const unsigned b = br[i] & 0xffffu;
             const unsigned s_ = bstart16[b], e_ = bstart16[b + 1];
-            const unsigned me = (((klo >> (4 * i)) & 15u) << 12) | ((unsigned)(i * THREADS) + tid);
+            const uint64_t me =
+                ((uint64_t)key[i] << 16) | ((((klo >> (4 * i)) & 15u) << 12) | ((unsigned)(i * THREADS) + tid));
             unsigned less = 0;
             if (e_ - s_ > 1) {
-              for (unsigned t = s_; t < e_; ++t) {
-                const uint32_t k2 = sm.wkeys[t];
-                const unsigned j2 = sm.widx[t];
-                less += (k2 < key[i] || (k2 == key[i] && j2 < me)) ? 1u : 0u;
-              }
+              for (unsigned t = s_; t < e_; ++t) less += sm.wk[t] < me ? 1u : 0u;
             }
             skeys[s_ + less] = key[i];
             if (sizeof(KeyT) == 8) slo[s_ + less] = (uint8_t)((klo >> (4 * i)) & 15u);
@@ -349,10 +346,18 @@ ls2_sort_dedup_kernel(const KeyT *__restrict__ lowkeys, const uint32_t *__restri
         const int j = i * THREADS + (int)tid;
         const uint64_t lk = lowkey(j);
         const int64_t o = excl + below[i] + (DEDUP ? sm.wcnt[i * WARPS + warp] : 0u);
-        const uint64_t full = hi_bits | lk;
-        const int64_t r = (int64_t)(full >> cbits);
+        // R >= cbits (a bucket is a range of whole rows): the row inside the bucket and the column are fields of the
+        // local key itself - 32-bit arithmetic for 32-bit local keys
+        int64_t r;
+        if (sizeof(KeyT) == 8) {
+          const uint64_t full = hi_bits | lk;
+          r = (int64_t)(full >> cbits);
+          out_col[o] = (int64_t)(full & cmask);
+        } else {
+          r = rlo + (int64_t)((uint32_t)lk >> cbits);
+          out_col[o] = (int64_t)((uint32_t)lk & (uint32_t)cmask);
+        }
         out_row[o] = r;
-        out_col[o] = (int64_t)(full & cmask);
         if (HAS_VALUE && !DEDUP) out_value[o] = pay_as<T>(svals[j]);
         if (HAS_VALUE && DEDUP) {
           A acc = to_acc<T>(pay_as<T>(svals[j]));
@@ -364,7 +369,9 @@ ls2_sort_dedup_kernel(const KeyT *__restrict__ lowkeys, const uint32_t *__restri
           out_value[o] = from_acc<T>(Red<RED, A>::finish(acc, (int64_t)(jj - j)));
         }
         if (out_rowptr) {
-          const int64_t pr = j == 0 ? rlo - 1 : (int64_t)((hi_bits | lowkey(j - 1)) >> cbits);
+          const int64_t pr = j == 0 ? rlo - 1
+                                    : (sizeof(KeyT) == 8 ? (int64_t)((hi_bits | lowkey(j - 1)) >> cbits)
+                                                         : rlo + (int64_t)(skeys[j - 1] >> cbits));
           if (r != pr && r <= M) {  // this head opens row r ...
             out_rowptr[r] = o;
             if (r - pr > 1)  // ... and the empty rows before it (rare)
