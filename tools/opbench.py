@@ -1,6 +1,6 @@
 """Consumers of the built storage on the shapes of BASELINE.json configs[2] (Reddit shape: broadcast mul, reductions)
 and configs[3] (sample_adj on the ogbn-products shape), timed on the device against the compulsory bytes of SURVEY.md
-8(d) (figure A).  Run on the GPU box:   python tools/opbench.py [--small]
+8(d) (figure A).  Run on the GPU box:   python tools/opbench.py [--small] [--rmat]
 Prints one JSON line per operation: ms, achieved GB/s on the figure-A bytes, fraction of the measured HBM peak."""
 import json
 import os
@@ -42,10 +42,11 @@ def report(name, ms, nbytes, extra=None):
 
 def main():
     small = "--small" in sys.argv
+    rmat = "--rmat" in sys.argv  # the skewed (R-MAT) generator of SURVEY 8d instead of the uniform one
     # ---- configs[2]: Reddit shape, already coalesced + CSR (build not timed)
     M = N = 232965
     nnz = 114615892 if not small else 8000000
-    row, col, val = ops.synth_coo(0x5EED0003, 0, nnz, M, N, "cuda")
+    row, col, val = ops.synth_coo(0x5EED0003, 0, nnz, M, N, "cuda", rmat=rmat)
     A = ps.SparseTensor(row=row, col=col, value=val, sparse_sizes=(M, N)).coalesce("add")
     st = A.storage
     n = st.col().numel()
@@ -82,7 +83,7 @@ def main():
     # ---- configs[3]: sample_adj on the products shape, 1024 seeds, fanout 25 then 10, replace=False, seed 42
     M = N = 2449029
     nnz = 61859140 if not small else 6000000
-    row, col, val = ops.synth_coo(0x5EED0002, 0, nnz, M, N, "cuda")
+    row, col, val = ops.synth_coo(0x5EED0002, 0, nnz, M, N, "cuda", rmat=rmat)
     A = ps.SparseTensor(row=row, col=col, value=val, sparse_sizes=(M, N)).coalesce("add")
     rowptr, colv = A.storage.rowptr(), A.storage.col()
     g = torch.Generator(device="cuda").manual_seed(1)
