@@ -82,6 +82,18 @@ int ps_rank_mode(void);
 int ps_ind2ptr(const int64_t *ind, int64_t numel, int64_t M, int64_t *out_ptr, void *stream);
 /* csrc/convert.cpp:46-56 `ptr2ind(ptr, E)`; csrc/cuda/convert_cuda.cu:42-68. out_ind[E]. */
 int ps_ptr2ind(const int64_t *ptr, int64_t M, int64_t E, int64_t *out_ind, void *stream);
+/* ps_ptr2ind for callers that may not allocate (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  NO counterpart in the reference.  Same arguments
+ * and the same output as ps_ptr2ind; the per-tile table that call takes from the stream-ordered pool lives here in
+ * a fixed array inside the library's device image (PS_PTR2IND_NOALLOC_SCRATCH_BYTES on every GPU that loads the
+ * library, held until the process exits), so the call performs no cudaMalloc / cudaFree / pool request of any kind.
+ * E > PS_PTR2IND_NOALLOC_MAX_E is rejected with PS_ERR_ARG (use ps_ptr2ind).  All calls on one device share the
+ * array: calls that overlap on the GPU (different streams without an ordering between them) race; calls on one
+ * stream, or ordered by events, are safe.  Nothing in the array has to start at zero - every word a call reads it
+ * has written itself. */
+#define PS_PTR2IND_NOALLOC_MAX_E 2147483648LL            /* 2^20 tiles of 2,048 entries */
+#define PS_PTR2IND_NOALLOC_SCRATCH_BYTES (4194304 + 256) /* one int32 per tile + 1, padded */
+int ps_ptr2ind_noalloc(const int64_t *ptr, int64_t M, int64_t E, int64_t *out_ind, void *stream);
 /* storage.py:373-381 / 405-412: count[i] = ptr[i+1] - ptr[i]. */
 int ps_ptr2count(const int64_t *ptr, int64_t M, int64_t *out_count, void *stream);
 /* storage.py:395-398 (colptr = [0, cumsum(colcount)]) and index_select.py:21-23

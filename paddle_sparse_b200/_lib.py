@@ -39,6 +39,7 @@ SIGNATURES = {
     "ps_rank_mode": [],
     "ps_ind2ptr": [c_ptr, c_i64, c_i64, c_ptr, c_ptr],
     "ps_ptr2ind": [c_ptr, c_i64, c_i64, c_ptr, c_ptr],
+    "ps_ptr2ind_noalloc": [c_ptr, c_i64, c_i64, c_ptr, c_ptr],
     "ps_ptr2count": [c_ptr, c_i64, c_ptr, c_ptr],
     "ps_count2ptr": [c_ptr, c_ptr, c_i64, c_ptr, c_ptr, c_ptr],
     "ps_histogram": [c_ptr, c_i64, c_i64, c_ptr, c_ptr],

@@ -11,6 +11,8 @@
 //   ptr2ind  = load-balanced over OUTPUT tiles: 32-ary warp search for the first/last row
 //              of the tile, row starts scattered into shared memory, block max-scan,
 //              coalesced 128-bit stores.  Degree skew cannot serialise a thread.
+#include <mutex>
+
 #include "common.cuh"
 #include "convert.cuh"
 
@@ -347,6 +349,64 @@ int ps_coo_order(const int64_t *row, const int64_t *col, int64_t nnz, int32_t *h
 int ps_add_scalar(const int64_t *in, int64_t n, int64_t delta, int64_t *out, void *stream) {
   if (n <= 0) return PS_OK;
   add_scalar_kernel<<<(unsigned)ceil_div(n, 256), 256, 0, (cudaStream_t)stream>>>(in, n, delta, out);
+  PS_LAUNCH_OK();
+  return PS_OK;
+}
+
+// ----------------------------------------------------------------------------- ptr2ind without any allocation
+// ps_ptr2ind needs one int32 per output tile (the first segment touching the tile) and takes it from the
+// stream-ordered pool.  Callers that may not allocate (CUDA graph capture, serving loops, harnesses that forbid
+// cudaMalloc) get the same two kernels with that table in a fixed array that lives in the library's device image:
+// every GPU that loads the library holds PS_PTR2IND_NOALLOC_SCRATCH_BYTES of it until the process exits.
+// In host code `g_ptr2ind_bounds` is only the host-side stand-in of the symbol, NOT a device address: the address a
+// kernel may be given comes from cudaGetSymbolAddress, asked once per device with that device current.
+}  // extern "C" (the array and its address table have internal linkage)
+
+namespace {
+constexpr int64_t NOALLOC_MAX_TILES = 1 << 20;                   // tiles of 2,048 entries: E <= 2^31
+constexpr int64_t NOALLOC_WORDS = NOALLOC_MAX_TILES + 64;        // tiles + 1 in use, padded to whole 256-byte lines
+static __device__ __align__(256) int32_t g_ptr2ind_bounds[NOALLOC_WORDS];  // 4 MiB + 256 B per device
+static_assert(sizeof(int32_t) * NOALLOC_WORDS == PS_PTR2IND_NOALLOC_SCRATCH_BYTES, "ps_abi.h states the size");
+
+std::mutex g_noalloc_mu;
+int32_t *g_noalloc_addr[64] = {nullptr};  // per device ordinal: the array's address on THAT device
+
+// the device address of g_ptr2ind_bounds on the current device (resolved on the first call per device)
+int noalloc_bounds(int32_t **out) {
+  int dev = -1;
+  PS_CUDA(cudaGetDevice(&dev));
+  PS_CHECK(dev >= 0 && dev < 64, "ptr2ind_noalloc: device ordinal %d outside this build's table of 64", dev);
+  std::lock_guard<std::mutex> lock(g_noalloc_mu);
+  if (!g_noalloc_addr[dev]) {
+    void *p = nullptr;
+    PS_CUDA(cudaGetSymbolAddress(&p, g_ptr2ind_bounds));
+    PS_CHECK(p != nullptr, "ptr2ind_noalloc: cudaGetSymbolAddress returned a null address on device %d", dev);
+    g_noalloc_addr[dev] = static_cast<int32_t *>(p);
+  }
+  *out = g_noalloc_addr[dev];
+  return PS_OK;
+}
+}  // namespace
+
+extern "C" {
+
+int ps_ptr2ind_noalloc(const int64_t *ptr, int64_t M, int64_t E, int64_t *out_ind, void *stream) {
+  PS_CHECK(M >= 0 && E >= 0, "ptr2ind_noalloc: negative size");
+  PS_CHECK(M < 2147483647LL, "ptr2ind_noalloc: M=%lld exceeds the 2^31-1 rows this build supports", (long long)M);
+  PS_CHECK(E <= (int64_t)PS_PTR2IND_NOALLOC_MAX_E,
+           "ptr2ind_noalloc: E=%lld exceeds the %lld entries the fixed scratch array covers; use ps_ptr2ind",
+           (long long)E, (long long)PS_PTR2IND_NOALLOC_MAX_E);
+  if (E == 0) return PS_OK;
+  PS_CHECK(M > 0, "ptr2ind_noalloc: E > 0 with no rows");
+  constexpr int THREADS = 256, ITEMS = 8;
+  static_assert(THREADS * ITEMS * NOALLOC_MAX_TILES == PS_PTR2IND_NOALLOC_MAX_E, "ps_abi.h states the limit");
+  const int64_t tiles = ceil_div(E, THREADS * ITEMS);
+  int32_t *bounds = nullptr;
+  PS_TRY(noalloc_bounds(&bounds));
+  // nothing has to start at zero: tile_bounds_kernel writes bounds[0 .. tiles] and ptr2ind_kernel reads only those
+  // words, later on the same stream.  Calls that overlap on the GPU (two streams) would race on the array.
+  PS_TRY(tile_bounds_launch(ptr, M, E, THREADS * ITEMS, bounds, (cudaStream_t)stream));
+  ptr2ind_kernel<THREADS, ITEMS><<<(unsigned)tiles, THREADS, 0, (cudaStream_t)stream>>>(ptr, M, E, out_ind, bounds);
   PS_LAUNCH_OK();
   return PS_OK;
 }
