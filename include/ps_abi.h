@@ -122,10 +122,11 @@ int ps_sort_coo(const int64_t *row, const int64_t *col, int64_t nnz, int64_t M, 
                 void *out_value, int64_t *out_perm, void *stream);
 /* storage.py:454-486 `SparseStorage.coalesce(reduce)` on SORTED input: keep the first
  * (row,col) of every run, value' = segment_csr(value, run_starts, reduce).
- * Outputs sized nnz; *host_nnz_out = nnz'.  Synchronises once. */
-int ps_coalesce_sorted(const int64_t *row, const int64_t *col, int64_t nnz, const void *value,
-                       int dtype, int64_t width, int reduce, int64_t *out_row, int64_t *out_col,
-                       void *out_value, int64_t *host_nnz_out, void *stream);
+ * Outputs sized nnz; *host_nnz_out = nnz'.  Synchronises once.  M, N = the sparse sizes (every
+ * row < M, col < N): at most 2^32 each, PS_ERR_ARG beyond (entries are compared as row << 32 | col). */
+int ps_coalesce_sorted(const int64_t *row, const int64_t *col, int64_t nnz, int64_t M, int64_t N,
+                       const void *value, int dtype, int64_t width, int reduce, int64_t *out_row,
+                       int64_t *out_col, void *out_value, int64_t *host_nnz_out, void *stream);
 /* storage.py:65-89 (validation maxima) fused with the first read the coalesce needs: ONE pass over
  * (row, col) yields max(row), max(col) and - when the hybrid plan applies to (nnz, M, N) - the bucket
  * histogram, offsets and pass bases, left in `state` (device, ps_coo_inspect_bytes() bytes, caller-owned).
@@ -285,7 +286,10 @@ int ps_dist_row_histogram(const int64_t *row, int64_t nnz, int shift, int64_t bu
                           int64_t *out_hist, void *stream);
 /* Stable partition of the local tuples by destination rank (row in
  * [splitters[g], splitters[g+1])), G <= 64.  Outputs are grouped by rank in send order;
- * out_counts[G] (device).  splitters is a DEVICE array of G+1 row ids. */
+ * out_counts[G] (device).  splitters is a DEVICE array of G+1 row ids.
+ * CONTRACT: ps_dist_partition and ps_dist_scatter_peer move row and col as 32-bit words: every id must be
+ * < 2^32 (sparse sizes <= 2^32 per dimension).  The entry points do not see the sizes; the host side
+ * (paddle_sparse_b200/dist.py: route_tuples) refuses larger matrices before calling them. */
 int ps_dist_partition(const int64_t *row, const int64_t *col, const void *value, int64_t row_bytes,
                       int64_t nnz, const int64_t *splitters, int G, int64_t *out_row,
                       int64_t *out_col, void *out_value, int64_t *out_counts, void *stream);

@@ -46,7 +46,7 @@ SIGNATURES = {
     "ps_index_max": [c_ptr, c_i64, c_ptr, c_i64, c_ptr, c_ptr],
     "ps_coo_order": [c_ptr, c_ptr, c_i64, c_ptr, c_ptr],
     "ps_sort_coo": [c_ptr, c_ptr, c_i64, c_i64, c_i64, c_ptr, c_int, c_i64, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr],
-    "ps_coalesce_sorted": [c_ptr, c_ptr, c_i64, c_ptr, c_int, c_i64, c_int, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr],
+    "ps_coalesce_sorted": [c_ptr, c_ptr, c_i64, c_i64, c_i64, c_ptr, c_int, c_i64, c_int, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr],
     "ps_coo_inspect_bytes": [],
     "ps_coo_inspect": [c_ptr, c_ptr, c_i64, c_i64, c_i64, c_ptr, c_ptr, c_ptr],
     "ps_coalesce": [c_ptr, c_ptr, c_i64, c_i64, c_i64, c_ptr, c_int, c_i64, c_int, c_ptr, c_ptr, c_ptr, c_ptr,

@@ -700,10 +700,14 @@ int ps_coalesce(const int64_t *row, const int64_t *col, int64_t nnz, int64_t M, 
                              inspect ? inspect_max_bucket : -1);
 }
 
-int ps_coalesce_sorted(const int64_t *row, const int64_t *col, int64_t nnz, const void *value, int dtype, int64_t width,
-                       int reduce, int64_t *out_row, int64_t *out_col, void *out_value, int64_t *host_nnz_out,
-                       void *stream) {
+int ps_coalesce_sorted(const int64_t *row, const int64_t *col, int64_t nnz, int64_t M, int64_t N, const void *value,
+                       int dtype, int64_t width, int reduce, int64_t *out_row, int64_t *out_col, void *out_value,
+                       int64_t *host_nnz_out, void *stream) {
   PS_CHECK(nnz >= 0, "coalesce_sorted: negative size");
+  // adjacent entries are compared as (row << 32 | col): ids of 2^32 and beyond would merge falsely / be masked
+  PS_CHECK(M >= 0 && N >= 0 && M <= (int64_t(1) << 32) && N <= (int64_t(1) << 32),
+           "coalesce_sorted: sparse sizes (%lld, %lld) exceed the 2^32 ids per dimension of the packed comparison",
+           (long long)M, (long long)N);
   PS_CHECK(host_nnz_out != nullptr, "coalesce_sorted: host_nnz_out is NULL");
   PS_CHECK(reduce >= PS_SUM && reduce <= PS_MAX, "coalesce_sorted: bad reduce %d", reduce);
   PS_TRY(check_value_args(value, out_value, dtype, width));
@@ -711,9 +715,7 @@ int ps_coalesce_sorted(const int64_t *row, const int64_t *col, int64_t nnz, cons
   if (nnz == 0) return PS_OK;
   cudaStream_t s = (cudaStream_t)stream;
   Scratch scratch(s);
-  // keys are compared as (row << 32 | col): requires row, col < 2^32 (true for any storage
-  // whose sparse sizes fit the packed-key sort above)
-  const int cbits = 32;
+  const int cbits = 32;  // row, col < 2^32: checked above
   KeySrc sk{row, col, KSRC_PACK_COO, cbits};
   PS_SCRATCH(d_nnz, scratch, long long, 1);
   long long h_nnz = 0;

@@ -36,8 +36,9 @@ static std::vector<ProfPair> g_prof[PROF_COUNT];
 static const char *const g_prof_names[PROF_COUNT] = {"rs_hist_kernel",  "rs_pass_kernel",   "dedup_kernel",
                                                      "ind2ptr_kernel",  "ptr2ind_kernel",   "invert_perm_kernel",
                                                      "transpose_gather_kernel", "segment_reduce_kernel",
-                                                     "gather_rows_kernel", "ls_sort_dedup_kernel",
-                                                     "ls_bucket_hist_kernel"};
+                                                     "gather_rows_kernel", "ls2_sort_dedup_kernel",
+                                                     "ls_bucket_hist_kernel + cl_bucket_hist_kernel",
+                                                     "cl_local_kernel"};
 
 ProfScope::ProfScope(int id, cudaStream_t s) : id_(id), s_(s), slot_(nullptr) {
   if (!g_prof_on.load(std::memory_order_relaxed)) return;

@@ -65,7 +65,8 @@ void count_launch();
 // one kernel family, so bench.py can report the dominant kernel's average duration measured
 // inside the timed region.  Off by default: no events, no overhead.
 enum ProfId { PROF_RS_HIST = 0, PROF_RS_PASS, PROF_DEDUP, PROF_IND2PTR, PROF_PTR2IND, PROF_INVERT_PERM,
-              PROF_TRANSPOSE_GATHER, PROF_SEGMENT_REDUCE, PROF_GATHER, PROF_LOCAL_SORT, PROF_BUCKET_HIST, PROF_COUNT };
+              PROF_TRANSPOSE_GATHER, PROF_SEGMENT_REDUCE, PROF_GATHER, PROF_LOCAL_SORT, PROF_BUCKET_HIST, PROF_CSC_LOCAL,
+              PROF_COUNT };
 struct ProfScope {
   ProfScope(int id, cudaStream_t s);
   ~ProfScope();

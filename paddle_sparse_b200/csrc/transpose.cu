@@ -148,7 +148,7 @@ static int csc_hybrid(const int64_t *row, const int64_t *col, const void *value,
   do {                                                                                                             \
     auto kern = cl_local_kernel<C_, V_, I_>;                                                                       \
     PS_FUNC_SMEM(kern, smem);                                                                                      \
-    ProfScope prof(PROF_LOCAL_SORT, s);                                                                            \
+    ProfScope prof(PROF_CSC_LOCAL, s);                                                                             \
     kern<<<grid, CL_THREADS, smem, s>>>(scol, sp, srow, sval, bucket_off, chunk_start, chunk_bucket, chunk_hist,  \
                                        info, nb, L, N, out_csr2csc, out_colptr, out_colcount, t_row, t_col,      \
                                        reinterpret_cast<uint32_t *>(t_val), ticket, inv);                         \

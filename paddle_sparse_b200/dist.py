@@ -117,6 +117,10 @@ class _PeerBuffers:
         self.tab_row, self.tab_col, self.tab_val = table(self.peer_row), table(self.peer_col), table(self.peer_val)
 
 
+class PeerMemoryUnavailable(RuntimeError):
+    """Raised on EVERY rank of the group when the symmetric receive buffers could not be set up on at least one."""
+
+
 _peer_buffers = {}       # group -> _PeerBuffers
 _peer_unavailable = []   # non-empty once symmetric memory failed to come up: the reason, and NCCL from then on
 
@@ -133,8 +137,21 @@ def _peer_plan(counts: torch.Tensor, value, device, group):
     vb = 0 if value is None else value.element_size() * int(torch.Size(value.shape[1:]).numel())
     buf = _peer_buffers.get(group)
     if buf is None or buf.capacity < need or buf.value_row_bytes < vb:
+        # every rank takes this branch together (need, capacity and vb are the same everywhere), so whether the
+        # buffers came up is agreed COLLECTIVELY: one rank failing (no P2P, an allocation failure while regrowing)
+        # must not leave the others waiting in the first barrier of the exchange
         cap = max(int(need * 1.125) + 1024, 0 if buf is None else buf.capacity)
-        buf = _peer_buffers[group] = _PeerBuffers(group, cap, max(vb, 0 if buf is None else buf.value_row_bytes), device)
+        new, why = None, ""
+        try:
+            new = _PeerBuffers(group, cap, max(vb, 0 if buf is None else buf.value_row_bytes), device)
+        except (RuntimeError, ImportError, AttributeError) as e:
+            why = repr(e)
+        ok = torch.tensor([0 if new is None else 1], dtype=torch.int32, device=device)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)
+        if int(ok.item()) == 0:
+            _peer_buffers.pop(group, None)
+            raise PeerMemoryUnavailable(why or "symmetric memory did not come up on another rank")
+        buf = _peer_buffers[group] = new
     return c, buf, vb
 
 
@@ -209,6 +226,10 @@ def route_tuples(row, col, value, sparse_sizes, group=None, _ops=None):
     if _ops is None:
         from . import ops as _ops
     M = int(sparse_sizes[0])
+    if max(int(sparse_sizes[0]), int(sparse_sizes[1])) > 2 ** 32:
+        # ps_dist_partition / ps_dist_scatter_peer move row and col as 32-bit payload words (csrc/dist.cu)
+        raise ValueError(f"partitioned build: sparse sizes {tuple(sparse_sizes)} exceed the 2^32 ids per dimension "
+                         "the exchange carries")
     G = dist.get_world_size(group)
     shift, buckets = bucket_shift(M)
     hist = _ops.dist_row_histogram(row, shift, buckets)
@@ -220,8 +241,10 @@ def route_tuples(row, col, value, sparse_sizes, group=None, _ops=None):
         try:
             r_row, r_col, r_val, sent, n_recv = partition_exchange_fused(row, col, value, splitters.to(row.device), group)
             return r_row, r_col, r_val, splitters, sent, n_recv
-        except (ImportError, AttributeError) as e:  # no symmetric memory in this torch build
-            _peer_unavailable.append(repr(e))
+        except (PeerMemoryUnavailable, ImportError, AttributeError) as e:  # no symmetric memory / no P2P: all ranks
+            _peer_unavailable.append(repr(e))                                # land here together (_peer_plan)
+            import warnings
+            warnings.warn(f"paddle_sparse_b200.dist: fused peer-memory exchange unavailable ({e}); using NCCL")
     p_row, p_col, p_val, counts = _ops.dist_partition(row, col, value, splitters.to(row.device))
     r_row, r_col, r_val, sent, n_recv, _ = _exchange_auto(p_row, p_col, p_val, counts, group)
     return r_row, r_col, r_val, splitters, sent, n_recv

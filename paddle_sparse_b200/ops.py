@@ -243,8 +243,10 @@ def coalesce(row, col, value, M: int, N: int, reduce: str = "add", want_rowptr: 
     return res + (rowptr,) if want_rowptr else res
 
 
-def coalesce_sorted(row, col, value, reduce: str = "add"):
-    """SparseStorage.coalesce on sorted input (storage.py:454-486).  Returns (row', col', value')."""
+def coalesce_sorted(row, col, value, reduce: str = "add", sparse_sizes=None):
+    """SparseStorage.coalesce on sorted input (storage.py:454-486).  Returns (row', col', value').
+    `sparse_sizes` (M, N): taken from the largest ids when not given (one more launch and sync); ids of 2^32 and
+    beyond are refused by the kernel side."""
     if _ag.needs_grad(value):
         r, c = _idx(row, "row"), _idx(col, "col")
         ptr = _ag.run_starts(r, c)
@@ -257,9 +259,12 @@ def coalesce_sorted(row, col, value, reduce: str = "add"):
     out_row, out_col = _new(row, nnz), _new(row, nnz)
     out_value = None if value is None else torch.empty_like(value)
     h = _host_i64()
+    if sparse_sizes is None:
+        mr, mc = index_max(row, col)
+        sparse_sizes = (mr + 1, mc + 1)
     with torch.cuda.device(row.device):
-        _lib.call("ps_coalesce_sorted", _p(row), _p(col), nnz, _p(v), dt, w, reduce_code(reduce), _p(out_row),
-                  _p(out_col), _p(out_value), h, _stream(row))
+        _lib.call("ps_coalesce_sorted", _p(row), _p(col), nnz, int(sparse_sizes[0]), int(sparse_sizes[1]), _p(v), dt, w,
+                  reduce_code(reduce), _p(out_row), _p(out_col), _p(out_value), h, _stream(row))
     k = int(h[0])
     return out_row[:k], out_col[:k], (None if out_value is None else out_value[:k])
 

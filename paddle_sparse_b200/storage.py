@@ -468,7 +468,7 @@ class SparseStorage(object):
                                  is_sorted=True, trust_data=True)
         if self._col.numel() <= 1:
             return self
-        row, col, value = ops.coalesce_sorted(self.row(), self._col, self._value, reduce)
+        row, col, value = ops.coalesce_sorted(self.row(), self._col, self._value, reduce, self._sparse_sizes)
         if row.numel() == self._col.numel():
             return self
         return SparseStorage(row=row, col=col, value=value, sparse_sizes=self._sparse_sizes, is_sorted=True,

@@ -39,6 +39,14 @@ def test_choose_splitters_balanced_and_row_aligned(G):
     assert max(per) <= 2_000_000 / G + hist.max().item()  # off by at most one bucket
 
 
+def test_route_tuples_refuses_ids_beyond_32_bits():
+    """The exchange carries row / col as 32-bit words (csrc/dist.cu): larger sparse sizes are refused up front."""
+    e = torch.zeros(0, dtype=torch.int64)
+    for sizes in ((2 ** 32 + 1, 8), (8, 2 ** 40)):
+        with pytest.raises(ValueError, match="2\^32"):
+            psd.route_tuples(e, e, None, sizes)
+
+
 def test_choose_splitters_degenerate():
     sp = psd.choose_splitters(torch.zeros(4, dtype=torch.int64), 4, 0, 4)
     assert sp.tolist()[0] == 0 and sp.tolist()[-1] == 4 and all(a <= b for a, b in zip(sp.tolist(), sp.tolist()[1:]))

@@ -163,6 +163,21 @@ def test_coalesce_sorted_and_heavy_duplicates(ops, reduce):
     np.testing.assert_allclose(host(v), want.value(), rtol=2e-5 if reduce in ("sum", "mean") else 0)
 
 
+def test_coalesce_sorted_refuses_ids_beyond_the_packed_comparison(ops):
+    """Entries are compared as row << 32 | col: sparse sizes beyond 2^32 are refused, not truncated; with explicit
+    sizes the result is the same as with sizes taken from the data."""
+    row, col = dev(np.array([0, 0, 1, 1, 1], I64)), dev(np.array([2, 2, 0, 3, 3], I64))
+    val = dev(np.array([1, 2, 3, 4, 5], np.float32))
+    a = ops.coalesce_sorted(row, col, val, "add")
+    b = ops.coalesce_sorted(row, col, val, "add", (1 << 32, 1 << 32))
+    assert host(a[0]).tolist() == host(b[0]).tolist() == [0, 1, 1]
+    assert host(a[1]).tolist() == host(b[1]).tolist() == [2, 0, 3]
+    assert host(a[2]).tolist() == host(b[2]).tolist() == [3.0, 3.0, 9.0]
+    for sizes in (((1 << 32) + 1, 4), (4, 1 << 33)):
+        with pytest.raises(RuntimeError, match="2\^32"):
+            ops.coalesce_sorted(row, col, val, "add", sizes)
+
+
 def test_coalesce_empty_and_single(ops):
     e = dev(np.array([], I64))
     r, c, v = ops.coalesce(e, e, dev(np.array([], np.float32)), 5, 5)

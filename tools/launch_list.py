@@ -1,7 +1,7 @@
 """Summarise one bench step out of an ncu launch list (gpu__time_duration.sum, --csv):
    python tools/launch_list.py launches.csv [first-kernel regex] [must-contain regex] > profiles/rNN_..._launches.txt
 The last complete step (from one launch matching the first regex to the next) that contains a kernel matching the
-second regex (default: the hybrid coalesce's ls_sort_dedup_kernel, i.e. the uniform configs[1] step rather than the
+second regex (default: the hybrid coalesce's ls2_sort_dedup_kernel, i.e. the uniform configs[1] step rather than the
 skewed variant that follows it) is printed launch by launch with its share; generator / torch kernels are left out."""
 import collections
 import csv
@@ -22,7 +22,7 @@ for r in csv.DictReader(lines):
 starts = [i for i, (n, _) in enumerate(rows) if first.search(n)]
 if len(starts) < 2:
     sys.exit("fewer than two steps in the list")
-must = re.compile(sys.argv[3] if len(sys.argv) > 3 else r"^ls_sort_dedup_kernel")
+must = re.compile(sys.argv[3] if len(sys.argv) > 3 else r"^ls2?_sort_dedup_kernel")
 step = None
 for a, b in reversed(list(zip(starts[:-1], starts[1:]))):  # steps that are certainly complete, latest first
     cand = [(n, us) for n, us in rows[a:b] if not skip.search(n)]
