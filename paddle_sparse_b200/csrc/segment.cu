@@ -23,7 +23,8 @@ template <typename T, int RED, int G, bool W1>
 __global__ void __launch_bounds__(256)
 segment_reduce_kernel(const T *__restrict__ src, int64_t width, const int64_t *__restrict__ ptr, int64_t S,
                       T *__restrict__ out, const uint32_t *__restrict__ perm, int64_t long_thresh,
-                      unsigned long long *__restrict__ long_list /*[0] = count, [1..] = output indices*/) {
+                      unsigned long long *__restrict__ long_list /*[0] = count, [1..] = output indices*/,
+                      int vec16 /*src is 16-byte aligned*/) {
   using A = typename Acc<T>::type;
   const int64_t gid = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / G;
   const int sub = threadIdx.x % G;
@@ -44,6 +45,31 @@ segment_reduce_kernel(const T *__restrict__ src, int64_t width, const int64_t *_
   A acc = Red<RED, A>::init();
   if (W1) {
     int64_t e = lo + sub;
+    // 16-byte loads for a full warp on a long enough segment of a <= 4-byte type: a lane takes 4 (f32 / i32) or 8
+    // (bf16 / f16) consecutive entries per load instead of one (the 2-byte reductions were issue-bound at one
+    // element per load: 72 % issue-active, 0.37 of HBM); the unaligned head and tail are one entry per lane
+    constexpr int V = sizeof(T) <= 4 ? 16 / (int)sizeof(T) : 1;
+    if (V > 1 && G == 32 && !perm && vec16 && hi - lo >= 2 * V * G) {
+      const int64_t a0 = (lo + V - 1) / V * V, a1 = hi / V * V;
+      if (e < a0) acc = Red<RED, A>::op(acc, to_acc<T>(src[e]));
+      const uint4 *p16 = reinterpret_cast<const uint4 *>(src);
+      const int64_t vend = a1 / V;
+      int64_t v = a0 / V + sub;
+      auto fold = [&](const uint4 &x) {
+        const T *t = reinterpret_cast<const T *>(&x);
+#pragma unroll
+        for (int k = 0; k < V; ++k) acc = Red<RED, A>::op(acc, to_acc<T>(t[k]));
+      };
+      for (; v + G < vend; v += 2 * G) {
+        const uint4 x = __ldg(p16 + v), y = __ldg(p16 + v + G);
+        fold(x);
+        fold(y);
+      }
+      for (; v < vend; v += G) fold(__ldg(p16 + v));
+      e = a1 + sub;
+      if (e < hi) acc = Red<RED, A>::op(acc, to_acc<T>(src[e]));
+      e = hi;
+    }
     if (!perm) {
       for (; e + 3 * G < hi; e += 4 * G) {
         const T v0 = src[e], v1 = src[e + G], v2 = src[e + 2 * G], v3 = src[e + 3 * G];
@@ -65,21 +91,62 @@ segment_reduce_kernel(const T *__restrict__ src, int64_t width, const int64_t *_
   if (live && sub == 0 && !deferred) out[gid] = from_acc<T>(Red<RED, A>::finish(acc, hi - lo));
 }
 
-// One CTA per listed output: 256 threads walk the segment with four loads in flight each, partial results combined
-// in a fixed order (lane tree, then warp 0 over the 8 warp results): deterministic for a given segment.
+// Listed (long) outputs: a segment is cut into up to SR_SPLIT equal parts of at least SR_PART_MIN entries, CTA
+// (x, part) reduces that part of the segments x, x + gridDim.x, ... into partial[li * SR_SPLIT + part]; the
+// combine kernel folds a segment's partials in part order.  256 threads walk a part with four loads in flight each -
+// 16-byte loads (4 or 8 entries) when the values are a contiguous [nnz] vector of a <= 4-byte type - and their
+// results are combined in a fixed order (lane tree, then warp 0 over the 8 warp results): deterministic for a given
+// segment.  One CTA per segment (round 2's first version) left the hub rows of a power-law graph on the critical
+// path: a 230 K-entry row took ~170 us on its own.
+constexpr int SR_SPLIT = 16;
+constexpr int64_t SR_PART_MIN = 4096;
+__device__ __forceinline__ int sr_parts(int64_t len) {
+  const int64_t p = (len + SR_PART_MIN - 1) / SR_PART_MIN;
+  return (int)(p < 1 ? 1 : (p > SR_SPLIT ? SR_SPLIT : p));
+}
+
 template <typename T, int RED>
 __global__ void __launch_bounds__(256)
-segment_reduce_long_kernel(const T *__restrict__ src, int64_t width, const int64_t *__restrict__ ptr, T *__restrict__ out,
-                           const uint32_t *__restrict__ perm, const unsigned long long *__restrict__ long_list) {
+segment_reduce_long_kernel(const T *__restrict__ src, int64_t width, const int64_t *__restrict__ ptr,
+                           const uint32_t *__restrict__ perm, const unsigned long long *__restrict__ long_list,
+                           typename Acc<T>::type *__restrict__ partial, int vec16) {
   using A = typename Acc<T>::type;
   __shared__ A part[8];
   const unsigned long long count = long_list[0];
+  const int py = blockIdx.y;
   for (unsigned long long li = blockIdx.x; li < count; li += gridDim.x) {
     const int64_t gid = (int64_t)long_list[1 + li];
     const int64_t sgm = gid / width, f = gid - sgm * width;
-    const int64_t lo = ptr[sgm], hi = ptr[sgm + 1];
+    const int64_t lo0 = ptr[sgm], hi0 = ptr[sgm + 1];
+    const int parts = sr_parts(hi0 - lo0);
+    if (py >= parts) continue;  // uniform over the CTA
+    const int64_t lo = lo0 + (hi0 - lo0) * py / parts, hi = lo0 + (hi0 - lo0) * (py + 1) / parts;
     A acc = Red<RED, A>::init();
     int64_t e = lo + threadIdx.x;
+    constexpr int V = sizeof(T) <= 4 ? 16 / (int)sizeof(T) : 1;
+    if (V > 1 && width == 1 && !perm && vec16 && hi - lo >= 2 * V * 256) {
+      const int64_t a0 = (lo + V - 1) / V * V, a1 = hi / V * V;
+      if (e < a0) acc = Red<RED, A>::op(acc, to_acc<T>(src[e]));
+      const uint4 *p16 = reinterpret_cast<const uint4 *>(src);
+      const int64_t vend = a1 / V;
+      int64_t v = a0 / V + threadIdx.x;
+      auto fold = [&](const uint4 &x) {
+        const T *t = reinterpret_cast<const T *>(&x);
+#pragma unroll
+        for (int k = 0; k < V; ++k) acc = Red<RED, A>::op(acc, to_acc<T>(t[k]));
+      };
+      for (; v + 3 * 256 < vend; v += 4 * 256) {
+        uint4 x[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) x[q] = __ldg(p16 + v + q * 256);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) fold(x[q]);
+      }
+      for (; v < vend; v += 256) fold(__ldg(p16 + v));
+      e = a1 + threadIdx.x;
+      if (e < hi) acc = Red<RED, A>::op(acc, to_acc<T>(src[e]));
+      e = hi;
+    }
     for (; e + 3 * 256 < hi; e += 4 * 256) {
       T v[4];
 #pragma unroll
@@ -99,9 +166,28 @@ segment_reduce_long_kernel(const T *__restrict__ src, int64_t width, const int64
       A a = threadIdx.x < 8 ? part[threadIdx.x] : Red<RED, A>::init();
 #pragma unroll
       for (int d = 4; d > 0; d >>= 1) a = Red<RED, A>::op(a, __shfl_xor_sync(0xffffffffu, a, d));
-      if (threadIdx.x == 0) out[gid] = from_acc<T>(Red<RED, A>::finish(a, hi - lo));
+      if (threadIdx.x == 0) partial[li * SR_SPLIT + py] = a;
     }
     __syncthreads();
+  }
+}
+
+template <typename T, int RED>
+__global__ void __launch_bounds__(256)
+segment_reduce_long_finish_kernel(int64_t width, const int64_t *__restrict__ ptr, T *__restrict__ out,
+                                  const unsigned long long *__restrict__ long_list,
+                                  const typename Acc<T>::type *__restrict__ partial) {
+  using A = typename Acc<T>::type;
+  const unsigned long long count = long_list[0];
+  for (unsigned long long li = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; li < count;
+       li += (unsigned long long)gridDim.x * blockDim.x) {
+    const int64_t gid = (int64_t)long_list[1 + li];
+    const int64_t sgm = gid / width;
+    const int64_t len = ptr[sgm + 1] - ptr[sgm];
+    const int parts = sr_parts(len);
+    A a = partial[li * SR_SPLIT];
+    for (int q = 1; q < parts; ++q) a = Red<RED, A>::op(a, partial[li * SR_SPLIT + q]);
+    out[gid] = from_acc<T>(Red<RED, A>::finish(a, len));
   }
 }
 
@@ -123,9 +209,13 @@ static int segment_reduce_typed(const T *src, int64_t width, const int64_t *ptr,
   Scratch scratch(s);
   PS_SCRATCH(long_list, scratch, unsigned long long, list_cap < (size_t)outputs + 2 ? list_cap : (size_t)outputs + 2);
   PS_CUDA(cudaMemsetAsync(long_list, 0, sizeof(unsigned long long), s));
+  using A = typename Acc<T>::type;
+  const size_t n_list = list_cap < (size_t)outputs + 2 ? list_cap : (size_t)outputs + 2;
+  PS_SCRATCH(partial, scratch, A, n_list * SR_SPLIT);
   ProfScope prof(PROF_SEGMENT_REDUCE, s);
 #define PS_SR(G_, W1_) \
-  segment_reduce_kernel<T, RED, G_, W1_><<<blocks, 256, 0, s>>>(src, width, ptr, S, out, perm, long_thresh, long_list)
+  segment_reduce_kernel<T, RED, G_, W1_><<<blocks, 256, 0, s>>>(src, width, ptr, S, out, perm, long_thresh, long_list, \
+                                                                 (reinterpret_cast<uintptr_t>(src) & 15u) == 0)
   if (width == 1) {
     switch (G) {
       case 1: PS_SR(1, true); break;
@@ -143,7 +233,10 @@ static int segment_reduce_typed(const T *src, int64_t width, const int64_t *ptr,
   }
 #undef PS_SR
   PS_LAUNCH_OK();
-  segment_reduce_long_kernel<T, RED><<<sm_count() * 2, 256, 0, s>>>(src, width, ptr, out, perm, long_list);
+  segment_reduce_long_kernel<T, RED><<<dim3((unsigned)sm_count(), SR_SPLIT), 256, 0, s>>>(
+      src, width, ptr, perm, long_list, partial, (reinterpret_cast<uintptr_t>(src) & 15u) == 0);
+  PS_LAUNCH_OK();
+  segment_reduce_long_finish_kernel<T, RED><<<64, 256, 0, s>>>(width, ptr, out, long_list, partial);
   PS_LAUNCH_OK();
   return PS_OK;
 }

@@ -27,7 +27,11 @@ def assert_values(got, want, dtype, exact=False):
         assert np.array_equal(got, want)
         return
     rtol = {torch.bfloat16: 1e-3 * 8, torch.float16: 1e-3, torch.float32: 1e-6, torch.float64: 1e-12}.get(dtype, 0)
-    # bf16 has an 8-bit mantissa: one rounding of the fp32-accumulated result is 2^-9 relative
+    # bf16 keeps 8 significant bits: neighbouring values are 2^-8 .. 2^-7 apart relative to their size, so ONE
+    # rounding of the fp32-accumulated result is already up to 2^-9 = 2e-3 from the exact sum and north_star's 1e-3
+    # cannot be met by any bf16 output.  The op-level tests therefore allow 8e-3 (one ulp, either neighbour); the
+    # config-level test (tests/test_gpu_configs.py) is sharper: within 1 ulp of the fp32 accumulation everywhere and
+    # EQUAL to round_bf16(oracle) on > 99.99 % of the outputs.
     np.testing.assert_allclose(got, want, rtol=rtol, atol=0)
 
 

@@ -242,7 +242,9 @@ def test_lazy_sort_then_coalesce_is_fused_and_equivalent():
 
 @pytest.mark.parametrize("M,N,nnz,dup", [(2449029, 2449029, 70000, 0.2), (2449029, 2449029, 1500000, 0.3),
                                          (3000000, 1 << 22, 400000, 0.0), (1 << 23, 1 << 23, 3000000, 0.05),
-                                         (70000, 2000000, 250000, 0.5)])
+                                         (70000, 2000000, 250000, 0.5),
+                                         # 51- and 53-bit keys (row shards of papers100M): the wide hybrid
+                                         (13882495, 111059956, 2500000, 0.2), (1 << 26, 1 << 27, 300000, 0.3)])
 @pytest.mark.parametrize("dtype,reduce", [(torch.float32, "add"), (torch.float32, "max"), (torch.int32, "mean"),
                                           (torch.bfloat16, "add"), (None, "add")])
 def test_hybrid_coalesce_matches_oracle(ops, M, N, nnz, dup, dtype, reduce):
@@ -282,7 +284,8 @@ def test_hybrid_coalesce_hub_rows_fall_back(ops):
     assert np.array_equal(host(rowptr), np.searchsorted(idx[0], np.arange(M + 1), side="left"))
 
 
-@pytest.mark.parametrize("M,N,nnz,dup", [(2449029, 2449029, 500000, 0.3), (1 << 23, 1 << 22, 2000000, 0.1)])
+@pytest.mark.parametrize("M,N,nnz,dup", [(2449029, 2449029, 500000, 0.3), (1 << 23, 1 << 22, 2000000, 0.1),
+                                         (13882495, 111059956, 1000000, 0.3)])
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16, None])
 def test_hybrid_sort_coo_is_stable(ops, M, N, nnz, dup, dtype):
     """sort-on-construct (storage.py:158-171) on the hybrid path: duplicate keys carry distinct values, so any
@@ -401,3 +404,7 @@ def test_segment_csr_long_segments(ops, dtype, width):
             np.testing.assert_allclose(got, want, rtol=8e-3, atol=0.26, err_msg=red)  # one bf16 rounding of an exact sum
         else:
             assert np.array_equal(got, want), red
+    if width == 1:  # a source that is not 16-byte aligned takes the element-wise loads: same results
+        buf = torch.cat([src[:1], src])
+        for red in ("sum", "max"):
+            assert torch.equal(ops.segment_csr(buf[1:], dev(ptr), None, red), ops.segment_csr(src, dev(ptr), None, red))
