@@ -433,12 +433,25 @@ rs_pass_kernel(KeySrc ksrc, PaySrcN<NPAY> psrc, KeyDst kdst, PayDstN<NPAY> pdst,
     // lane-instances under every collision / bank-conflict pattern, none out of order; rank_bench.cu: ~2 SM
     // cycles per warp instruction against 40 for MATCH.ANY and 17 for eight ballots).  Padding keys of a partial
     // tile are all-ones: the largest digit, and ranked last inside it.
-    unsigned rank[ITEMS];
+    // 1024-thread CTAs are capped at 64 registers: their ranks / slots (< TILE <= 65535) are kept two to a register
+    constexpr bool PACK = THREADS >= 1024;
+    constexpr int NRANK = PACK ? (ITEMS + 1) / 2 : ITEMS;
+    unsigned rank[NRANK];
+    auto slot_of = [&](int i) -> unsigned {
+      if constexpr (PACK) return (rank[i >> 1] >> ((i & 1) * 16)) & 0xffffu;
+      else return rank[i];
+    };
+    if constexpr (PACK) {
+#pragma unroll
+      for (int i = 0; i < NRANK; ++i) rank[i] = 0;
+    }
 #pragma unroll
     for (int i = 0; i < ITEMS; ++i) {
       const unsigned d = (unsigned)(key[i] >> begin_bit) & mask;
       const unsigned sh = (d & 1u) * 16u;
-      rank[i] = (atomicAdd(&my_cnt[d >> 1], 1u << sh) >> sh) & 0xffffu;
+      const unsigned r = (atomicAdd(&my_cnt[d >> 1], 1u << sh) >> sh) & 0xffffu;
+      if constexpr (PACK) rank[i >> 1] |= r << ((i & 1) * 16);
+      else rank[i] = r;
     }
     PS_TL(1);
     __syncthreads();
@@ -509,10 +522,14 @@ rs_pass_kernel(KeySrc ksrc, PaySrcN<NPAY> psrc, KeyDst kdst, PayDstN<NPAY> pdst,
     {
       const uint16_t *my_start = reinterpret_cast<const uint16_t *>(my_cnt);
 #pragma unroll
-      for (int i = 0; i < ITEMS; ++i) rank[i] += (unsigned)my_start[(unsigned)(key[i] >> begin_bit) & mask];
+      for (int i = 0; i < ITEMS; ++i) {
+        const unsigned st = (unsigned)my_start[(unsigned)(key[i] >> begin_bit) & mask];
+        if constexpr (PACK) rank[i >> 1] += st << ((i & 1) * 16);  // start + rank < TILE: no carry into the neighbour
+        else rank[i] += st;
+      }
     }
 #pragma unroll
-    for (int i = 0; i < ITEMS; ++i) sm.keys[rank[i]] = key[i];
+    for (int i = 0; i < ITEMS; ++i) sm.keys[slot_of(i)] = key[i];
     PS_TL(10);
     if (NPAY > 0) {
       const bool landed = any_bulk && bulk_tile(tile);  // uniform: this tile's u32 words came by bulk copy
@@ -537,7 +554,7 @@ rs_pass_kernel(KeySrc ksrc, PaySrcN<NPAY> psrc, KeyDst kdst, PayDstN<NPAY> pdst,
           load_tile_pay_sync<ITEMS>(psrc.s[p], tile_base, warp_base, lane, tile_n, pv);
         }
 #pragma unroll
-        for (int i = 0; i < ITEMS; ++i) sm.pay[p][rank[i]] = pv[i];
+        for (int i = 0; i < ITEMS; ++i) sm.pay[p][slot_of(i)] = pv[i];
       }
     }
     PS_TL(5);

@@ -5,6 +5,8 @@
 // plus the fused broadcast multiplies of mul.py:76-93 and the dense reduction of
 // reduce.py:17-27.  paddle_scatter's source is not part of the reference tree; semantics are
 // restated from its documented behaviour (empty segment / untouched row -> 0).
+#include <cstdlib>
+
 #include "common.cuh"
 #include "convert.cuh"
 #include "segment.cuh"
@@ -19,11 +21,27 @@ namespace ps {
 // `long_thresh` entries appends its output index to `long_list` and moves on; segment_reduce_long_kernel then gives
 // every listed output a whole CTA.  The reference's segment_csr (paddle_scatter, a port of torch_scatter) walks a
 // segment with a fixed group of lanes whatever its length.
+constexpr int SR_SPLIT = 16;
+constexpr int64_t SR_PART_MIN = 4096;
+struct alignas(16) SrTask {
+  int64_t lo, hi;   // the part's range of entries
+  int64_t gid;      // output index (segment * width + feature)
+  uint32_t slot;    // position in the list: partial[slot * SR_SPLIT + q], long_arrive[slot]
+  uint16_t q, parts;
+};
+static_assert(sizeof(SrTask) == 32, "two 16-byte loads per task");
+__device__ __forceinline__ int sr_parts(int64_t len) {
+  const int64_t p = (len + SR_PART_MIN - 1) / SR_PART_MIN;
+  return (int)(p < 1 ? 1 : (p > SR_SPLIT ? SR_SPLIT : p));
+}
+
 template <typename T, int RED, int G, bool W1>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, (W1 && G == 32) ? 8 : 4)  // long [nnz] rows: 32 registers, full occupancy hides the latency
 segment_reduce_kernel(const T *__restrict__ src, int64_t width, const int64_t *__restrict__ ptr, int64_t S,
                       T *__restrict__ out, const uint32_t *__restrict__ perm, int64_t long_thresh,
-                      unsigned long long *__restrict__ long_list /*[0] = count, [1..] = output indices*/,
+                      unsigned long long *__restrict__ long_list /*[0] = count, [1] = tasks, [2..] = output indices*/,
+                      unsigned int *__restrict__ long_arrive /*[slot]: parts of that output finished so far*/,
+                      SrTask *__restrict__ long_tasks /*one record per part of a listed output*/,
                       int vec16 /*src is 16-byte aligned*/) {
   using A = typename Acc<T>::type;
   const int64_t gid = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / G;
@@ -39,7 +57,16 @@ segment_reduce_kernel(const T *__restrict__ src, int64_t width, const int64_t *_
   }
   const bool deferred = hi - lo > long_thresh;  // uniform inside the group
   if (deferred) {
-    if (sub == 0) long_list[1 + atomicAdd(long_list, 1ull)] = (unsigned long long)gid;
+    if (sub == 0) {
+      const unsigned long long slot = atomicAdd(long_list, 1ull);
+      long_list[2 + slot] = (unsigned long long)gid;
+      long_arrive[slot] = 0u;
+      const int parts = sr_parts(hi - lo);
+      const unsigned long long t0 = atomicAdd(long_list + 1, (unsigned long long)parts);
+      for (int q = 0; q < parts; ++q)  // everything a part needs in one 32-byte record: no pointer chasing later
+        long_tasks[t0 + q] = SrTask{lo + (hi - lo) * q / parts, lo + (hi - lo) * (q + 1) / parts, gid, (uint32_t)slot,
+                                    (uint16_t)q, (uint16_t)parts};
+    }
     hi = lo;  // nothing to walk; the store below is suppressed
   }
   A acc = Red<RED, A>::init();
@@ -91,36 +118,33 @@ segment_reduce_kernel(const T *__restrict__ src, int64_t width, const int64_t *_
   if (live && sub == 0 && !deferred) out[gid] = from_acc<T>(Red<RED, A>::finish(acc, hi - lo));
 }
 
-// Listed (long) outputs: a segment is cut into up to SR_SPLIT equal parts of at least SR_PART_MIN entries, CTA
-// (x, part) reduces that part of the segments x, x + gridDim.x, ... into partial[li * SR_SPLIT + part]; the
-// combine kernel folds a segment's partials in part order.  256 threads walk a part with four loads in flight each -
+// Listed (long) outputs: a segment is cut into up to SR_SPLIT equal parts of at least SR_PART_MIN entries; the lister
+// appends one task per part, the CTAs of the long kernel walk the task list (balanced whatever the mix of lengths,
+// and an empty list costs one small launch), each reducing its part into partial[slot * SR_SPLIT + part]; the part
+// that finishes last (arrival counter per listed output, zeroed by the lister) folds the partials in part order.  256 threads walk a part with four loads in flight each -
 // 16-byte loads (4 or 8 entries) when the values are a contiguous [nnz] vector of a <= 4-byte type - and their
 // results are combined in a fixed order (lane tree, then warp 0 over the 8 warp results): deterministic for a given
 // segment.  One CTA per segment (round 2's first version) left the hub rows of a power-law graph on the critical
 // path: a 230 K-entry row took ~170 us on its own.
-constexpr int SR_SPLIT = 16;
-constexpr int64_t SR_PART_MIN = 4096;
-__device__ __forceinline__ int sr_parts(int64_t len) {
-  const int64_t p = (len + SR_PART_MIN - 1) / SR_PART_MIN;
-  return (int)(p < 1 ? 1 : (p > SR_SPLIT ? SR_SPLIT : p));
-}
-
 template <typename T, int RED>
 __global__ void __launch_bounds__(256)
-segment_reduce_long_kernel(const T *__restrict__ src, int64_t width, const int64_t *__restrict__ ptr,
+segment_reduce_long_kernel(const T *__restrict__ src, int64_t width, const int64_t *__restrict__ ptr, T *__restrict__ out,
                            const uint32_t *__restrict__ perm, const unsigned long long *__restrict__ long_list,
-                           typename Acc<T>::type *__restrict__ partial, int vec16) {
+                           unsigned int *__restrict__ long_arrive, const SrTask *__restrict__ long_tasks,
+                           typename Acc<T>::type *partial, int vec16) {
   using A = typename Acc<T>::type;
   __shared__ A part[8];
-  const unsigned long long count = long_list[0];
-  const int py = blockIdx.y;
-  for (unsigned long long li = blockIdx.x; li < count; li += gridDim.x) {
-    const int64_t gid = (int64_t)long_list[1 + li];
-    const int64_t sgm = gid / width, f = gid - sgm * width;
-    const int64_t lo0 = ptr[sgm], hi0 = ptr[sgm + 1];
-    const int parts = sr_parts(hi0 - lo0);
-    if (py >= parts) continue;  // uniform over the CTA
-    const int64_t lo = lo0 + (hi0 - lo0) * py / parts, hi = lo0 + (hi0 - lo0) * (py + 1) / parts;
+  const unsigned long long ntasks = long_list[1];
+  if (blockIdx.x >= ntasks) return;
+  SrTask nxt = long_tasks[blockIdx.x];
+  for (unsigned long long t = blockIdx.x; t < ntasks; t += gridDim.x) {
+    const SrTask task = nxt;
+    if (t + gridDim.x < ntasks) nxt = long_tasks[t + gridDim.x];  // requested before this part's data
+    const unsigned long long li = task.slot;
+    const int py = task.q, parts = task.parts;
+    const int64_t gid = task.gid;
+    const int64_t f = width == 1 ? 0 : gid % width;
+    const int64_t lo = task.lo, hi = task.hi;
     A acc = Red<RED, A>::init();
     int64_t e = lo + threadIdx.x;
     constexpr int V = sizeof(T) <= 4 ? 16 / (int)sizeof(T) : 1;
@@ -166,29 +190,36 @@ segment_reduce_long_kernel(const T *__restrict__ src, int64_t width, const int64
       A a = threadIdx.x < 8 ? part[threadIdx.x] : Red<RED, A>::init();
 #pragma unroll
       for (int d = 4; d > 0; d >>= 1) a = Red<RED, A>::op(a, __shfl_xor_sync(0xffffffffu, a, d));
-      if (threadIdx.x == 0) partial[li * SR_SPLIT + py] = a;
+      if (threadIdx.x == 0) {
+        if (parts == 1) {
+          out[gid] = from_acc<T>(Red<RED, A>::finish(a, hi - lo));
+        } else {
+          // the part that arrives last folds all partials IN PART ORDER: the result does not depend on which one it is
+          volatile A *pv = partial + li * SR_SPLIT;
+          pv[py] = a;
+          __threadfence();
+          if (atomicAdd(&long_arrive[li], 1u) == (unsigned)parts - 1u) {
+            __threadfence();
+            A r = pv[0];
+            for (int q = 1; q < parts; ++q) r = Red<RED, A>::op(r, pv[q]);
+            const int64_t sgm = gid / width;
+            out[gid] = from_acc<T>(Red<RED, A>::finish(r, ptr[sgm + 1] - ptr[sgm]));
+          }
+        }
+      }
     }
     __syncthreads();
   }
 }
 
-template <typename T, int RED>
-__global__ void __launch_bounds__(256)
-segment_reduce_long_finish_kernel(int64_t width, const int64_t *__restrict__ ptr, T *__restrict__ out,
-                                  const unsigned long long *__restrict__ long_list,
-                                  const typename Acc<T>::type *__restrict__ partial) {
-  using A = typename Acc<T>::type;
-  const unsigned long long count = long_list[0];
-  for (unsigned long long li = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; li < count;
-       li += (unsigned long long)gridDim.x * blockDim.x) {
-    const int64_t gid = (int64_t)long_list[1 + li];
-    const int64_t sgm = gid / width;
-    const int64_t len = ptr[sgm + 1] - ptr[sgm];
-    const int parts = sr_parts(len);
-    A a = partial[li * SR_SPLIT];
-    for (int q = 1; q < parts; ++q) a = Red<RED, A>::op(a, partial[li * SR_SPLIT + q]);
-    out[gid] = from_acc<T>(Red<RED, A>::finish(a, len));
+// PS_SEG_VEC (bench knob, read once): 0 = element-wise loads in the main kernel, 1 = 16-byte loads
+static int seg_vec() {
+  static int v = -1;
+  if (v < 0) {
+    const char *e = getenv("PS_SEG_VEC");
+    v = e ? atoi(e) : 1;
   }
+  return v;
 }
 
 template <typename T, int RED>
@@ -207,15 +238,17 @@ static int segment_reduce_typed(const T *src, int64_t width, const int64_t *ptr,
   const int64_t long_thresh = 128 * (int64_t)G;
   const size_t list_cap = (size_t)(E_hint > 0 ? (E_hint / long_thresh + 1) * (width > 0 ? width : 1) : outputs) + 2;
   Scratch scratch(s);
-  PS_SCRATCH(long_list, scratch, unsigned long long, list_cap < (size_t)outputs + 2 ? list_cap : (size_t)outputs + 2);
-  PS_CUDA(cudaMemsetAsync(long_list, 0, sizeof(unsigned long long), s));
+  PS_SCRATCH(long_list, scratch, unsigned long long, (list_cap < (size_t)outputs + 2 ? list_cap : (size_t)outputs + 2) + 2);
+  PS_CUDA(cudaMemsetAsync(long_list, 0, 2 * sizeof(unsigned long long), s));
   using A = typename Acc<T>::type;
   const size_t n_list = list_cap < (size_t)outputs + 2 ? list_cap : (size_t)outputs + 2;
   PS_SCRATCH(partial, scratch, A, n_list * SR_SPLIT);
+  PS_SCRATCH(long_arrive, scratch, unsigned int, n_list);
+  PS_SCRATCH(long_tasks, scratch, SrTask, n_list * SR_SPLIT);
   ProfScope prof(PROF_SEGMENT_REDUCE, s);
 #define PS_SR(G_, W1_) \
   segment_reduce_kernel<T, RED, G_, W1_><<<blocks, 256, 0, s>>>(src, width, ptr, S, out, perm, long_thresh, long_list, \
-                                                                 (reinterpret_cast<uintptr_t>(src) & 15u) == 0)
+                                                                 long_arrive, long_tasks, seg_vec() && (reinterpret_cast<uintptr_t>(src) & 15u) == 0)
   if (width == 1) {
     switch (G) {
       case 1: PS_SR(1, true); break;
@@ -233,10 +266,9 @@ static int segment_reduce_typed(const T *src, int64_t width, const int64_t *ptr,
   }
 #undef PS_SR
   PS_LAUNCH_OK();
-  segment_reduce_long_kernel<T, RED><<<dim3((unsigned)sm_count(), SR_SPLIT), 256, 0, s>>>(
-      src, width, ptr, perm, long_list, partial, (reinterpret_cast<uintptr_t>(src) & 15u) == 0);
-  PS_LAUNCH_OK();
-  segment_reduce_long_finish_kernel<T, RED><<<64, 256, 0, s>>>(width, ptr, out, long_list, partial);
+  segment_reduce_long_kernel<T, RED><<<(unsigned)sm_count() * 8, 256, 0, s>>>(
+      src, width, ptr, out, perm, long_list, long_arrive, long_tasks, partial,
+      (reinterpret_cast<uintptr_t>(src) & 15u) == 0);
   PS_LAUNCH_OK();
   return PS_OK;
 }
