@@ -599,8 +599,11 @@ def run_ours(args):
         del routed
 
         def local_only():
-            lr = ps.ops.add_scalar(o_row, -r0) if r0 else o_row
-            c_row, c_col, c_val, c_rowptr = ps.ops.coalesce(lr, o_col, o_val, rows_local, N, "add", True)
+            if o_row.dtype == torch.int32:  # what the fused exchange delivers: 32-bit global ids
+                c_row, c_col, c_val, c_rowptr = ps.ops.coalesce_u32(o_row, o_col, r0, o_val, rows_local, N, "add", True)
+            else:
+                lr = ps.ops.add_scalar(o_row, -r0) if r0 else o_row
+                c_row, c_col, c_val, c_rowptr = ps.ops.coalesce(lr, o_col, o_val, rows_local, N, "add", True)
             A = ps.SparseTensor(row=c_row, rowptr=c_rowptr, col=c_col, value=c_val, sparse_sizes=(rows_local, N),
                                 is_sorted=True, trust_data=True)
             A.storage.fill_cache_(carry=False)
@@ -667,7 +670,10 @@ def run_ours(args):
             "t_roof_ms": t_roof_ms, "max_tuples_sent_per_gpu": int(sent[0]), "max_tuples_received_per_gpu": int(sent[1]),
             "nvlink_GBps_per_direction": 770.0,
             "exchange_ms": exchange_ms, "single_gpu_same_shape_ms": local_ms,
-            "exchange_GBps_per_direction": sent_bytes / (exchange_ms * 1e-3) / 1e9,
+            # on the wire the fused exchange moves 12 bytes per tuple (32-bit row / col + value), not SURVEY 8e's 20
+            "wire_bytes_per_tuple": 12 if os.environ.get("PS_DIST_EXCHANGE", "fused") == "fused" else 20,
+            "exchange_GBps_per_direction": (12.0 if os.environ.get("PS_DIST_EXCHANGE", "fused") == "fused" else 20.0)
+            * float(sent[0]) / (exchange_ms * 1e-3) / 1e9,
             "scaling_anchor": "single_gpu_same_shape_ms = one GPU building one shard of this shape (the tuples the rank "
                               "owns, no exchange); efficiency = single_gpu_same_shape_ms / ms_per_step",
             "note": "frac = (local figure-A bytes / HBM peak + bytes sent / NVLink peak) / measured step time",

@@ -120,6 +120,13 @@ int ps_coo_order(const int64_t *row, const int64_t *col, int64_t nnz, int32_t *h
 int ps_sort_coo(const int64_t *row, const int64_t *col, int64_t nnz, int64_t M, int64_t N,
                 const void *value, int dtype, int64_t width, int64_t *out_row, int64_t *out_col,
                 void *out_value, int64_t *out_perm, void *stream);
+/* ps_coalesce on tuples held as 32-bit words (what ps_dist_scatter_peer delivers with narrow = 1): entry e is
+ * (row[e] - row_offset, col[e]); same outputs, order and reduction as ps_coalesce on the widened arrays.
+ * row_offset + M <= 2^32, N <= 2^32.  SURVEY.md 8e (no counterpart in the reference: it has no sharded build). */
+int ps_coalesce_u32(const uint32_t *row, const uint32_t *col, int64_t row_offset, int64_t nnz, int64_t M,
+                    int64_t N, const void *value, int dtype, int64_t width, int reduce, int64_t *out_row,
+                    int64_t *out_col, void *out_value, int64_t *out_rowptr, int64_t *host_nnz_out,
+                    void *stream);
 /* storage.py:454-486 `SparseStorage.coalesce(reduce)` on SORTED input: keep the first
  * (row,col) of every run, value' = segment_csr(value, run_starts, reduce).
  * Outputs sized nnz; *host_nnz_out = nnz'.  Synchronises once.  M, N = the sparse sizes (every
@@ -299,13 +306,15 @@ int ps_dist_partition(const int64_t *row, const int64_t *col, const void *value,
  * ranks have exchanged their counts, ps_dist_scatter_peer runs the ONE stable counting pass that carries
  * (row, col, 4-byte value) and stores destination d's run at element bases[d] of peer_row[d] /
  * peer_col[d] / peer_value[d] (device arrays of G base pointers; bases: device, G entries): the tuples
- * cross NVLink as the pass produces them, tile by tile.  row_bytes: 0 (no value) or 4. */
+ * cross NVLink as the pass produces them, tile by tile.  row_bytes: 0 (no value) or 4.  narrow != 0: row and
+ * col are stored as uint32 (peer_row / peer_col then address uint32 elements): 12 instead of 20 bytes per tuple
+ * on the wire; the receiver builds from them with ps_coalesce_u32. */
 int ps_dist_dest(const int64_t *row, int64_t nnz, const int64_t *splitters, int G, uint32_t *out_dest,
                  int64_t *out_counts, void *stream);
 int ps_dist_scatter_peer(const uint32_t *dest, const int64_t *row, const int64_t *col,
                          const void *value, int64_t row_bytes, int64_t nnz, int G, const int64_t *bases,
                          void *const *peer_row, void *const *peer_col, void *const *peer_value,
-                         void *stream);
+                         int narrow, void *stream);
 /* out[i] = in[i] + delta (local <-> global row ids of a shard). */
 int ps_add_scalar(const int64_t *in, int64_t n, int64_t delta, int64_t *out, void *stream);
 

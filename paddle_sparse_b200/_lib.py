@@ -82,7 +82,9 @@ SIGNATURES = {
     "ps_dist_row_histogram": [c_ptr, c_i64, c_int, c_i64, c_ptr, c_ptr],
     "ps_dist_partition": [c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_ptr, c_int, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr],
     "ps_dist_dest": [c_ptr, c_i64, c_ptr, c_int, c_ptr, c_ptr, c_ptr],
-    "ps_dist_scatter_peer": [c_ptr, c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_int, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr],
+    "ps_dist_scatter_peer": [c_ptr, c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_int, c_ptr, c_ptr, c_ptr, c_ptr, c_int, c_ptr],
+    "ps_coalesce_u32": [c_ptr, c_ptr, c_i64, c_i64, c_i64, c_i64, c_ptr, c_int, c_i64, c_int, c_ptr, c_ptr, c_ptr, c_ptr,
+                        c_ptr, c_ptr],
     "ps_add_scalar": [c_ptr, c_i64, c_i64, c_ptr, c_ptr],
     "ps_synth_coo": [c_u64, c_i64, c_i64, c_i64, c_i64, c_ptr, c_ptr, c_ptr, c_ptr],
     "ps_synth_rmat": [c_u64, c_i64, c_i64, c_i64, c_i64, c_ptr, c_ptr, c_ptr, c_ptr],

@@ -379,7 +379,7 @@ static int hybrid_coalesce(const int64_t *row, const int64_t *col, int64_t nnz, 
   PS_SCRATCH(p0, scratch, uint32_t, nnz);
   PS_SCRATCH(lowkeys, scratch, uint32_t, nnz);
   PS_SCRATCH(lowvals, scratch, uint32_t, nnz);
-  KeySrc ksrc{row, col, KSRC_PACK_COO, cbits};
+  KeySrc ksrc{row, col, KSRC_PACK_COO, cbits, 0, (rbits <= 32 && cbits <= 32) ? 1 : 0};
   PaySrc psrc = value ? PaySrc{value, pay_src_mode(dtype)} : PaySrc{nullptr, PSRC_NONE};
   PayDst pdst = value ? PayDst{lowvals, PDST_U32} : PayDst{nullptr, PDST_NONE};
   PS_TRY(radix_sort_pairs<uint64_t>(ksrc, psrc, nnz, T, k0, nullptr, p0, nullptr, KeyDst{lowkeys, nullptr, KDST_LOW32, R},
@@ -466,7 +466,7 @@ lsw_max_kernel(const unsigned int *__restrict__ bucket_off, int nb, unsigned int
   if ((threadIdx.x & 31u) == 0 && mx) atomicMax(max_bucket, mx);
 }
 
-static int hybrid_coalesce_wide(const int64_t *row, const int64_t *col, int64_t nnz, int rbits, int cbits, int64_t M,
+static int hybrid_coalesce_wide(KeySrc ksrc, int64_t nnz, int rbits, int cbits, int64_t M,
                                 const void *value, int dtype, bool dedup, int reduce, int64_t *out_row, int64_t *out_col,
                                 void *out_value, int64_t *out_rowptr, int64_t *host_nnz_out, bool *used, cudaStream_t s) {
   *used = false;
@@ -484,7 +484,6 @@ static int hybrid_coalesce_wide(const int64_t *row, const int64_t *col, int64_t 
   PS_SCRATCH(p0, scratch, uint32_t, nnz);
   PS_SCRATCH(skeys, scratch, uint64_t, nnz);
   PS_SCRATCH(svals, scratch, uint32_t, nnz);
-  KeySrc ksrc{row, col, KSRC_PACK_COO, cbits};
   PaySrc psrc = value ? PaySrc{value, pay_src_mode(dtype)} : PaySrc{nullptr, PSRC_NONE};
   PayDst pdst = value ? PayDst{svals, PDST_U32} : PayDst{nullptr, PDST_NONE};
   PS_TRY(radix_sort_pairs<uint64_t>(ksrc, psrc, nnz, T, k0, nullptr, p0, nullptr, KeyDst{skeys, nullptr, KDST_KEYS, 0}, pdst,
@@ -545,15 +544,20 @@ template <typename KeyT>
 int sort_impl(const int64_t *row, const int64_t *col, int64_t nnz, KeyGeom g, const void *value, int dtype,
               int64_t width, bool dedup, int reduce, int64_t *out_row, int64_t *out_col, void *out_value,
               int64_t *out_perm, int64_t *host_nnz_out, int64_t M, int64_t *out_rowptr, cudaStream_t s,
-              const LsInspect *pre = nullptr, int64_t pre_max_bucket = -1) {
+              const LsInspect *pre = nullptr, int64_t pre_max_bucket = -1, const KeySrc *src32 = nullptr) {
+  // src32: the tuples as 32-bit (global row, col) words with a row offset (what the peer exchange delivers) instead
+  // of the int64 arrays; everything downstream of the first key load is the same
+  KeySrc ksrc = src32 ? *src32 : KeySrc{row, col, KSRC_PACK_COO, g.cbits, 0, (g.rbits <= 32 && g.cbits <= 32) ? 1 : 0};
   const bool fast = value && fast_value(dtype, width) && !out_perm;
   if (sizeof(KeyT) == 8 && (fast || !value) && !out_perm) {  // hybrid path (sort only, or sort + dedup)
     bool used = false;
     int64_t ignored = 0;
-    PS_TRY(hybrid_coalesce(row, col, nnz, g.rbits, g.cbits, M, value, dtype, dedup, reduce, out_row, out_col, out_value,
-                           out_rowptr, dedup ? host_nnz_out : &ignored, &used, pre, pre_max_bucket, s));
-    if (used) return PS_OK;
-    PS_TRY(hybrid_coalesce_wide(row, col, nnz, g.rbits, g.cbits, M, value, dtype, dedup, reduce, out_row, out_col, out_value,
+    if (!src32) {  // (its bucket histogram reads the int64 arrays)
+      PS_TRY(hybrid_coalesce(row, col, nnz, g.rbits, g.cbits, M, value, dtype, dedup, reduce, out_row, out_col, out_value,
+                             out_rowptr, dedup ? host_nnz_out : &ignored, &used, pre, pre_max_bucket, s));
+      if (used) return PS_OK;
+    }
+    PS_TRY(hybrid_coalesce_wide(ksrc, nnz, g.rbits, g.cbits, M, value, dtype, dedup, reduce, out_row, out_col, out_value,
                                 out_rowptr, dedup ? host_nnz_out : &ignored, &used, s));
     if (used) return PS_OK;
   }
@@ -564,7 +568,6 @@ int sort_impl(const int64_t *row, const int64_t *col, int64_t nnz, KeyGeom g, co
   PS_SCRATCH(p0, scratch, uint32_t, nnz);
   PS_SCRATCH(p1, scratch, uint32_t, nnz);
   const int passes = rs_num_passes<KeyT>(g.bits);
-  KeySrc ksrc{row, col, KSRC_PACK_COO, g.cbits};
   PaySrc psrc = fast ? PaySrc{value, pay_src_mode(dtype)} : PaySrc{nullptr, PSRC_IOTA};
 
   if (!dedup) {
@@ -698,6 +701,34 @@ int ps_coalesce(const int64_t *row, const int64_t *col, int64_t nnz, int64_t M, 
   return sort_impl<uint64_t>(row, col, nnz, g, value, dtype, width, true, reduce, out_row, out_col, out_value, nullptr,
                              host_nnz_out, M, out_rowptr, s, reinterpret_cast<const LsInspect *>(inspect),
                              inspect ? inspect_max_bucket : -1);
+}
+
+int ps_coalesce_u32(const uint32_t *row, const uint32_t *col, int64_t row_offset, int64_t nnz, int64_t M, int64_t N,
+                    const void *value, int dtype, int64_t width, int reduce, int64_t *out_row, int64_t *out_col,
+                    void *out_value, int64_t *out_rowptr, int64_t *host_nnz_out, void *stream) {
+  PS_CHECK(nnz >= 0 && M >= 0 && N >= 0 && row_offset >= 0, "coalesce_u32: negative size");
+  PS_CHECK(nnz < (int64_t(1) << 32), "coalesce_u32: nnz=%lld exceeds the 2^32-1 entries per call this build supports",
+           (long long)nnz);
+  PS_CHECK(row_offset + M <= (int64_t(1) << 32) && N <= (int64_t(1) << 32),
+           "coalesce_u32: row_offset + M = %lld or N = %lld exceeds the 2^32 ids a 32-bit word carries",
+           (long long)(row_offset + M), (long long)N);
+  PS_CHECK(host_nnz_out != nullptr, "coalesce_u32: host_nnz_out is NULL");
+  PS_CHECK(reduce >= PS_SUM && reduce <= PS_MAX, "coalesce_u32: bad reduce %d", reduce);
+  PS_TRY(check_value_args(value, out_value, dtype, width));
+  *host_nnz_out = 0;
+  cudaStream_t s = (cudaStream_t)stream;
+  if (nnz == 0) {
+    if (out_rowptr) PS_CUDA(cudaMemsetAsync(out_rowptr, 0, sizeof(int64_t) * (size_t)(M + 1), s));
+    return PS_OK;
+  }
+  KeyGeom g;
+  PS_TRY(key_geometry(M, N, &g));
+  KeySrc src{row, col, KSRC_PACK_COO32, g.cbits, row_offset};
+  if (g.bits <= 32)
+    return sort_impl<uint32_t>(nullptr, nullptr, nnz, g, value, dtype, width, true, reduce, out_row, out_col, out_value,
+                               nullptr, host_nnz_out, M, out_rowptr, s, nullptr, -1, &src);
+  return sort_impl<uint64_t>(nullptr, nullptr, nnz, g, value, dtype, width, true, reduce, out_row, out_col, out_value,
+                             nullptr, host_nnz_out, M, out_rowptr, s, nullptr, -1, &src);
 }
 
 int ps_coalesce_sorted(const int64_t *row, const int64_t *col, int64_t nnz, int64_t M, int64_t N, const void *value,

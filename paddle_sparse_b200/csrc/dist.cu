@@ -159,7 +159,7 @@ int ps_dist_dest(const int64_t *row, int64_t nnz, const int64_t *splitters, int 
 
 int ps_dist_scatter_peer(const uint32_t *dest, const int64_t *row, const int64_t *col, const void *value,
                          int64_t row_bytes, int64_t nnz, int G, const int64_t *bases, void *const *peer_row,
-                         void *const *peer_col, void *const *peer_value, void *stream) {
+                         void *const *peer_col, void *const *peer_value, int narrow, void *stream) {
   PS_CHECK(nnz >= 0 && G >= 1 && G <= 64, "dist_scatter_peer: bad arguments (G must be in [1, 64])");
   PS_CHECK(row_bytes == 0 || row_bytes == 4, "dist_scatter_peer: values must be absent or 4 bytes per entry");
   PS_CHECK(nnz < (int64_t(1) << 32), "dist_scatter_peer: nnz=%lld exceeds 2^32-1 entries per call", (long long)nnz);
@@ -177,8 +177,10 @@ int ps_dist_scatter_peer(const uint32_t *dest, const int64_t *row, const int64_t
   ps_.s[1] = PaySrc{col, PSRC_I64};
   ps_.s[2] = has_v ? PaySrc{value, PSRC_U32} : PaySrc{nullptr, PSRC_NONE};
   PayDstN<3> pd;
-  pd.d[0] = PayDst{const_cast<void **>(peer_row), PDST_I64_BY_DIGIT};
-  pd.d[1] = PayDst{const_cast<void **>(peer_col), PDST_I64_BY_DIGIT};
+  // narrow: row and col cross NVLink as the 32-bit words the pass carries anyway (12 instead of 20 bytes per tuple);
+  // the receiver's coalesce reads them as such (ps_coalesce_u32)
+  pd.d[0] = PayDst{const_cast<void **>(peer_row), narrow ? PDST_U32_BY_DIGIT : PDST_I64_BY_DIGIT};
+  pd.d[1] = PayDst{const_cast<void **>(peer_col), narrow ? PDST_U32_BY_DIGIT : PDST_I64_BY_DIGIT};
   pd.d[2] = has_v ? PayDst{const_cast<void **>(peer_value), PDST_U32_BY_DIGIT} : PayDst{nullptr, PDST_NONE};
   PS_TRY((radix_sort_tuples<uint32_t, 3>(KeySrc{dest, nullptr, KSRC_KEYS, 0}, ps_, nnz, G > 1 ? bits_for(G) : 1, nullptr,
                                          nullptr, none, none, KeyDst{nullptr, nullptr, KDST_NONE, 0}, pd, scratch, s, 0,

@@ -45,7 +45,7 @@ inline SortPlan make_sort_plan(int total_bits, int rbits) {
 }
 
 // ---- where the first pass finds its keys / payload, and where the last one puts them
-enum { KSRC_KEYS = 0, KSRC_PACK_COO = 1, KSRC_I64 = 2 };
+enum { KSRC_KEYS = 0, KSRC_PACK_COO = 1, KSRC_I64 = 2, KSRC_PACK_COO32 = 3 };
 enum { PSRC_U32 = 0, PSRC_IOTA = 1, PSRC_U16 = 2, PSRC_U8 = 3, PSRC_I64 = 4, PSRC_NONE = 5 /* word unused */ };
 enum { PDST_U32 = 0, PDST_I64 = 1, PDST_U16 = 2, PDST_U8 = 3, PDST_NONE = 4,
        // p = device array of one base pointer PER DIGIT (single-pass partitions whose bins live in different
@@ -54,10 +54,12 @@ enum { PDST_U32 = 0, PDST_I64 = 1, PDST_U16 = 2, PDST_U8 = 3, PDST_NONE = 4,
 enum { KDST_NONE = 0, KDST_KEYS = 1, KDST_UNPACK_COO = 2, KDST_I64 = 3, KDST_LOW32 = 4 /* low cbits bits as u32 */ };
 
 struct KeySrc {
-  const void *a;  // keys (KSRC_KEYS), row (KSRC_PACK_COO), the int64 array (KSRC_I64)
-  const void *b;  // col (KSRC_PACK_COO)
+  const void *a;  // keys (KSRC_KEYS), row (KSRC_PACK_COO: int64, KSRC_PACK_COO32: uint32), the int64 array (KSRC_I64)
+  const void *b;  // col (KSRC_PACK_COO / KSRC_PACK_COO32)
   int mode;
   int cbits;
+  int64_t off = 0;  // KSRC_PACK_COO32: subtracted from row (tuples received from peers carry GLOBAL row ids)
+  int lo32 = 0;     // KSRC_PACK_COO: every row and col fits 32 bits, so a pass may read only their low words
 };
 struct PaySrc {
   const void *p;
@@ -80,6 +82,11 @@ __device__ __forceinline__ KeyT load_key(const KeySrc &s, int64_t i) {
   if (s.mode == KSRC_PACK_COO) {
     const uint64_t r = (uint64_t)ld_stream(reinterpret_cast<const int64_t *>(s.a) + i);
     const uint64_t c = (uint64_t)ld_stream(reinterpret_cast<const int64_t *>(s.b) + i);
+    return (KeyT)((r << s.cbits) | c);
+  }
+  if (s.mode == KSRC_PACK_COO32) {
+    const uint64_t r = (uint64_t)ld_stream(reinterpret_cast<const uint32_t *>(s.a) + i) - (uint64_t)s.off;
+    const uint64_t c = (uint64_t)ld_stream(reinterpret_cast<const uint32_t *>(s.b) + i);
     return (KeyT)((r << s.cbits) | c);
   }
   return (KeyT)ld_stream(reinterpret_cast<const int64_t *>(s.a) + i);
@@ -122,8 +129,7 @@ rs_hist_kernel(KeySrc ksrc, int64_t n, SortPlan plan, unsigned long long *__rest
   for (int j = threadIdx.x; j < plan.passes * RS_MAX_RADIX; j += blockDim.x) sh[j] = 0;
   __syncthreads();
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-    const KeyT k = load_key<KeyT>(ksrc, i);
+  auto count = [&](KeyT k) {
 #pragma unroll
     for (int p = 0; p < RS_MAX_PASSES; ++p) {
       if (p < plan.passes) {
@@ -131,7 +137,16 @@ rs_hist_kernel(KeySrc ksrc, int64_t n, SortPlan plan, unsigned long long *__rest
         atomicAdd(&sh[p * RS_MAX_RADIX + d], 1u);
       }
     }
+  };
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  for (; i + 3 * stride < n; i += 4 * stride) {  // four keys in flight per thread: the loop is latency-bound otherwise
+    KeyT k[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) k[q] = load_key<KeyT>(ksrc, i + q * stride);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) count(k[q]);
   }
+  for (; i < n; i += stride) count(load_key<KeyT>(ksrc, i));
   __syncthreads();
   for (int j = threadIdx.x; j < plan.passes * RS_MAX_RADIX; j += blockDim.x)
     if (sh[j]) atomicAdd(&ghist[j], (unsigned long long)sh[j]);
@@ -235,6 +250,19 @@ __device__ __forceinline__ void load_tile_keys(const KeySrc &s, int64_t tile_bas
       const int j = warp_base + i * 32 + lane;
       if (j < tile_n) key[i] = (KeyT)(((uint64_t)key[i] << s.cbits) | (uint64_t)ld_stream(c + j));
     }
+  } else if (s.mode == KSRC_PACK_COO32) {
+    const uint32_t *r = reinterpret_cast<const uint32_t *>(s.a) + tile_base;
+    const uint32_t *c = reinterpret_cast<const uint32_t *>(s.b) + tile_base;
+#pragma unroll
+    for (int i = 0; i < ITEMS; ++i) {
+      const int j = warp_base + i * 32 + lane;
+      key[i] = j < tile_n ? (KeyT)((uint64_t)ld_stream(r + j) - (uint64_t)s.off) : ~KeyT(0);
+    }
+#pragma unroll
+    for (int i = 0; i < ITEMS; ++i) {
+      const int j = warp_base + i * 32 + lane;
+      if (j < tile_n) key[i] = (KeyT)(((uint64_t)key[i] << s.cbits) | (uint64_t)ld_stream(c + j));
+    }
   } else {
     const int64_t *p = reinterpret_cast<const int64_t *>(s.a) + tile_base;
 #pragma unroll
@@ -244,6 +272,47 @@ __device__ __forceinline__ void load_tile_keys(const KeySrc &s, int64_t tile_bas
     }
   }
 }
+
+// 64-bit keys packed from two 32-bit words (KSRC_PACK_COO32, or the low words of KSRC_PACK_COO's int64 arrays): the
+// REQUEST only loads - row word into the key's high half, col word into its low half, no arithmetic on the loaded
+// values, so nothing waits for them at the request site - and the key is put together when the tile is ranked, one
+// whole scatter phase later (rs_finish_raw_keys).  With the shift / or at the request site 26 % of a first pass's
+// warp samples sat there waiting for the column loads, 44 % when the source was 32-bit.
+template <int ITEMS>
+__device__ __forceinline__ void load_tile_raw(const KeySrc &s, int64_t tile_base, int warp_base, unsigned lane,
+                                              int tile_n, uint64_t (&key)[ITEMS]) {
+  const int w = s.mode == KSRC_PACK_COO32 ? 1 : 2;  // 32-bit words per element (little endian: low word first)
+  const uint32_t *r = reinterpret_cast<const uint32_t *>(s.a) + tile_base * w;
+  const uint32_t *c = reinterpret_cast<const uint32_t *>(s.b) + tile_base * w;
+  uint32_t hi[ITEMS], lo[ITEMS];
+#pragma unroll
+  for (int i = 0; i < ITEMS; ++i) {
+    const int j = warp_base + i * 32 + lane;
+    hi[i] = j < tile_n ? ld_stream(r + (size_t)j * w) : 0xffffffffu;
+  }
+#pragma unroll
+  for (int i = 0; i < ITEMS; ++i) {
+    const int j = warp_base + i * 32 + lane;
+    lo[i] = j < tile_n ? ld_stream(c + (size_t)j * w) : 0xffffffffu;
+  }
+#pragma unroll
+  for (int i = 0; i < ITEMS; ++i) asm("mov.b64 %0, {%1, %2};" : "=l"(key[i]) : "r"(lo[i]), "r"(hi[i]));  // register pairing
+}
+template <int ITEMS>
+__device__ __forceinline__ void rs_finish_raw_keys(const KeySrc &s, int warp_base, unsigned lane, int tile_n,
+                                                   uint64_t (&key)[ITEMS]) {
+  const uint32_t off = (uint32_t)s.off;
+#pragma unroll
+  for (int i = 0; i < ITEMS; ++i) {
+    const int j = warp_base + i * 32 + lane;
+    const uint64_t r = (uint64_t)((uint32_t)(key[i] >> 32) - off), c = key[i] & 0xffffffffull;
+    key[i] = j < tile_n ? ((r << s.cbits) | c) : ~uint64_t(0);
+  }
+}
+template <int ITEMS>
+__device__ __forceinline__ void load_tile_raw(const KeySrc &, int64_t, int, unsigned, int, uint32_t (&)[ITEMS]) {}
+template <int ITEMS>
+__device__ __forceinline__ void rs_finish_raw_keys(const KeySrc &, int, unsigned, int, uint32_t (&)[ITEMS]) {}
 
 // payload words whose source is not a plain u32 array (those are prefetched with cp.async)
 template <int ITEMS>
@@ -382,11 +451,13 @@ rs_pass_kernel(KeySrc ksrc, PaySrcN<NPAY> psrc, KeyDst kdst, PayDstN<NPAY> pdst,
   for (int p = 0; p < (NPAY > 0 ? NPAY : 1); ++p)
     pay_bulk[p] = PREFETCH && NPAY > 0 && psrc.s[p].mode == PSRC_U32 &&
                   (reinterpret_cast<uintptr_t>(psrc.s[p].p) & 15u) == 0;
+  const bool raw_keys = sizeof(KeyT) == 8 && (ksrc.mode == KSRC_PACK_COO32 || (ksrc.mode == KSRC_PACK_COO && ksrc.lo32));
   auto bulk_tile = [&](int64_t t) { return PREFETCH && NPAY > 0 && t < tiles && (n - t * TILE) >= TILE; };
   auto request_keys = [&](int64_t t) {
     const int64_t tb = t * TILE;
     const int tn = (int)((n - tb) < TILE ? (n - tb) : TILE);
-    load_tile_keys<KeyT, ITEMS>(ksrc, tb, warp_base, lane, tn, key);
+    if (raw_keys) load_tile_raw<ITEMS>(ksrc, tb, warp_base, lane, tn, key);
+    else load_tile_keys<KeyT, ITEMS>(ksrc, tb, warp_base, lane, tn, key);
   };
   auto request_pay = [&](int64_t t) {  // thread 0 only, after every read of pay_in of the previous tile
     if (!bulk_tile(t)) return;
@@ -426,6 +497,7 @@ rs_pass_kernel(KeySrc ksrc, PaySrcN<NPAY> psrc, KeyDst kdst, PayDstN<NPAY> pdst,
     PS_TL(0);
 #pragma unroll
     for (int q = lane; q < Smem::ROW; q += 32) my_cnt[q] = 0;
+    if (raw_keys) rs_finish_raw_keys<ITEMS>(ksrc, warp_base, lane, tile_n, key);  // the words requested a tile ago
     __syncwarp();
 
     // ---- 2: rank.  Stability needs the lanes of ONE atomic instruction that hit the same counter to be served

@@ -168,13 +168,17 @@ def partition_exchange_fused(row, col, value, splitters: torch.Tensor, group=Non
     bases = recv_base[me].to(row.device)
     n_recv = int(c[:, me].sum())
     buf.h_row.barrier()  # every rank has consumed what the previous exchange left in its buffers
-    ops.dist_scatter_peer(dest, row, col, value, bases, buf.tab_row, buf.tab_col, None if value is None else buf.tab_val)
+    # row and col cross NVLink as 32-bit words (ids < 2^32 on this path: route_tuples checks): 12 instead of 20 bytes
+    # per tuple; they land in the first half of the int64 receive buffers and the shard's coalesce reads them as
+    # such (ops.coalesce_u32), with the shard's first row as offset
+    ops.dist_scatter_peer(dest, row, col, value, bases, buf.tab_row, buf.tab_col, None if value is None else buf.tab_val,
+                          narrow=True)
     buf.h_row.barrier()  # every rank's pass has finished writing into my buffers
     r_val = None
     if value is not None:
         r_val = buf.val[:n_recv * vb].view(value.dtype).reshape((n_recv,) + tuple(value.shape[1:]))
     sent = int(c[me].sum()) - int(c[me][me])
-    return buf.row[:n_recv], buf.col[:n_recv], r_val, sent, n_recv
+    return buf.row.view(torch.int32)[:n_recv], buf.col.view(torch.int32)[:n_recv], r_val, sent, n_recv
 
 
 def exchange_peer(row, col, value, counts: torch.Tensor, group=None):
@@ -259,8 +263,11 @@ def build_partitioned(row, col, value, sparse_sizes, group=None, reduce: str = "
     rank = dist.get_rank(group)
     r_row, r_col, r_val, splitters, sent, n_recv = route_tuples(row, col, value, (M, N), group)
     r0, r1 = int(splitters[rank]), int(splitters[rank + 1])
-    local_row = ops.add_scalar(r_row, -r0) if r0 else r_row
-    c_row, c_col, c_val, c_rowptr = ops.coalesce(local_row, r_col, r_val, max(r1 - r0, 0), N, reduce, True)
+    if r_row.dtype == torch.int32:  # the fused exchange: 32-bit global ids, made local inside the coalesce's first read
+        c_row, c_col, c_val, c_rowptr = ops.coalesce_u32(r_row, r_col, r0, r_val, max(r1 - r0, 0), N, reduce, True)
+    else:
+        local_row = ops.add_scalar(r_row, -r0) if r0 else r_row
+        c_row, c_col, c_val, c_rowptr = ops.coalesce(local_row, r_col, r_val, max(r1 - r0, 0), N, reduce, True)
     A = SparseTensor(row=c_row, rowptr=c_rowptr, col=c_col, value=c_val, sparse_sizes=(max(r1 - r0, 0), N),
                      is_sorted=True, trust_data=True)
     if fill_cache:

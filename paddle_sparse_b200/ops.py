@@ -243,6 +243,29 @@ def coalesce(row, col, value, M: int, N: int, reduce: str = "add", want_rowptr: 
     return res + (rowptr,) if want_rowptr else res
 
 
+def coalesce_u32(row32, col32, row_offset: int, value, M: int, N: int, reduce: str = "add", want_rowptr: bool = False):
+    """`coalesce` on tuples held as 32-bit words: entry e is (row32[e] - row_offset, col32[e]).  This is what the
+    fused peer exchange delivers (GLOBAL row ids, 12 bytes per tuple on the wire); row32 / col32 are int32 tensors
+    whose bits are read as unsigned.  Same results as `coalesce` on the widened, shifted arrays."""
+    for name, t in (("row32", row32), ("col32", col32)):
+        if not (t.is_cuda and t.dtype == torch.int32 and t.is_contiguous()):
+            raise ValueError(f"coalesce_u32: {name} must be a contiguous CUDA int32 tensor")
+    value = None if value is None else _dev(value, "value")
+    v, dt, w = _value_args(value)
+    nnz = row32.numel()
+    out_row = torch.empty(nnz, dtype=torch.int64, device=row32.device)
+    out_col = torch.empty(nnz, dtype=torch.int64, device=row32.device)
+    out_value = None if value is None else torch.empty_like(value)
+    rowptr = torch.empty(M + 1, dtype=torch.int64, device=row32.device) if want_rowptr else None
+    h = _host_i64()
+    with torch.cuda.device(row32.device):
+        _lib.call("ps_coalesce_u32", _p(row32), _p(col32), int(row_offset), nnz, M, N, _p(v), dt, w, reduce_code(reduce),
+                  _p(out_row), _p(out_col), _p(out_value), _p(rowptr), h, _stream(row32))
+    k = int(h[0])
+    res = (out_row[:k], out_col[:k], (None if out_value is None else out_value[:k]))
+    return res + (rowptr,) if want_rowptr else res
+
+
 def coalesce_sorted(row, col, value, reduce: str = "add", sparse_sizes=None):
     """SparseStorage.coalesce on sorted input (storage.py:454-486).  Returns (row', col', value').
     `sparse_sizes` (M, N): taken from the largest ids when not given (one more launch and sync); ids of 2^32 and
@@ -660,17 +683,17 @@ def dist_dest(row: torch.Tensor, splitters: torch.Tensor):
 
 
 def dist_scatter_peer(dest, row, col, value, bases: torch.Tensor, peer_row: torch.Tensor, peer_col: torch.Tensor,
-                      peer_value: Optional[torch.Tensor]) -> None:
+                      peer_value: Optional[torch.Tensor], narrow: bool = False) -> None:
     """The stable partition pass writing destination d's run at element bases[d] of the d-th buffer whose base
     address peer_row / peer_col / peer_value (int64 device tensors of addresses) hold: partition and exchange in
-    one kernel over peer memory."""
+    one kernel over peer memory.  narrow: row / col are stored as 32-bit words (12 bytes per tuple on the wire)."""
     row, col = _idx(row, "row"), _idx(col, "col")
     value = None if value is None else _dev(value, "value")
     G = bases.numel()
     with torch.cuda.device(row.device):
         _lib.call("ps_dist_scatter_peer", _p(dest), _p(row), _p(col), _p(value),
                   0 if value is None else value.element_size() * max(_width(value), 1), row.numel(), G, _p(bases),
-                  _p(peer_row), _p(peer_col), _p(peer_value), _stream(row))
+                  _p(peer_row), _p(peer_col), _p(peer_value), int(bool(narrow)), _stream(row))
 
 
 def add_scalar(x: torch.Tensor, delta: int) -> torch.Tensor:

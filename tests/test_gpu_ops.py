@@ -270,6 +270,32 @@ def test_hybrid_coalesce_matches_oracle(ops, M, N, nnz, dup, dtype, reduce):
             assert np.array_equal(got, want)
 
 
+@pytest.mark.parametrize("M,N,nnz,dup", [(5000, 60000, 30000, 0.3),           # 29-bit keys: 32-bit LSD sort
+                                         (2449029, 2449029, 40000, 0.2),      # 44-bit keys, small: 64-bit LSD sort
+                                         (2449029, 2449029, 900000, 0.3),     # 44-bit keys: the wide hybrid
+                                         (13882495, 111059956, 1500000, 0.2)])  # 51-bit keys (a papers100M row shard)
+@pytest.mark.parametrize("dtype,reduce", [(torch.float32, "add"), (torch.int32, "max"), (None, "add")])
+def test_coalesce_u32_matches_coalesce(ops, M, N, nnz, dup, dtype, reduce):
+    """The form the fused peer exchange feeds: 32-bit GLOBAL row ids with the shard's first row as offset, 32-bit
+    columns.  Same outputs, bit for bit, as `coalesce` on the widened local arrays (which the tests above hold against
+    the oracle)."""
+    rng = np.random.default_rng(nnz + 7)
+    row, col = _random_coo(rng, M, N, nnz, dup)
+    off = 1234567
+    val = None if dtype is None else dev(rng.integers(-40, 40, nnz), dtype)
+    want = ops.coalesce(dev(row), dev(col), val, M, N, reduce, True)
+    row32 = torch.from_numpy((row + off).astype(np.uint32).view(np.int32)).cuda()
+    col32 = torch.from_numpy(col.astype(np.uint32).view(np.int32)).cuda()
+    got = ops.coalesce_u32(row32, col32, off, val, M, N, reduce, True)
+    assert torch.equal(got[0], want[0]) and torch.equal(got[1], want[1]) and torch.equal(got[3], want[3])
+    if dtype is not None:
+        assert torch.equal(got[2], want[2])
+    idx, _ = np_ref.coalesce(np.stack([row, col]), None, M, N, reduce)
+    assert np.array_equal(host(got[0]), idx[0]) and np.array_equal(host(got[1]), idx[1])
+    with pytest.raises(RuntimeError, match="2\^32"):
+        ops.coalesce_u32(row32, col32, (1 << 32) - 5, val, M, N, reduce, True)
+
+
 def test_hybrid_coalesce_hub_rows_fall_back(ops):
     """one bucket beyond the shared-memory capacity (a hub row range): the plain LSD pipeline takes over"""
     rng = np.random.default_rng(9)

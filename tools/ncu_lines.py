@@ -1,5 +1,5 @@
 """Per-source-line warp-stall summary of one kernel in an .ncu-rep (run here, no GPU needed):
-   python tools/ncu_lines.py gpurun_out/prof.ncu-rep <kernel regex> [min_pct]
+   python tools/ncu_lines.py gpurun_out/prof.ncu-rep <kernel regex> [min_pct] [launches of that kernel to skip]
 Reads `ncu --page source --print-source cuda,sass --csv` and prints the CUDA lines that hold the most
 stall samples, with their top stall reasons and executed-instruction counts."""
 import csv
@@ -11,8 +11,9 @@ import sys
 def main():
     rep, pat = sys.argv[1], sys.argv[2]
     min_pct = float(sys.argv[3]) if len(sys.argv) > 3 else 1.0
+    skip = sys.argv[4] if len(sys.argv) > 4 else "0"
     out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "cuda,sass",
-                          "--kernel-name", "regex:" + pat, "--launch-count", "1"], capture_output=True, text=True).stdout
+                          "--kernel-name", "regex:" + pat, "--launch-skip", skip, "--launch-count", "1"], capture_output=True, text=True).stdout
     rows = list(csv.reader(io.StringIO(out)))
     files, cur, head = [], None, None
     for r in rows:

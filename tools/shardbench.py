@@ -44,3 +44,20 @@ for carry in (True, False):
     print(f"G={G} rows {M} nnz {n} -> {A.nnz()} | coalesce {tot[0]:.3f} ms | fill_cache_(carry={carry}) {tot[1]:.3f} ms | "
           f"sum {sum(tot):.3f} ms", flush=True)
     del A
+
+# the same coalesce fed the way the fused exchange feeds it: 32-bit global row ids + offset, 32-bit columns
+off = 3 * M
+row32 = (row + off).to(torch.int32)  # bits of the uint32 value
+col32 = col.to(torch.int32)
+for name, fn in (("int64 local rows", lambda: ops.coalesce(row, col, val, M, N, "add", True)),
+                 ("uint32 global rows + offset", lambda: ops.coalesce_u32(row32, col32, off, val, M, N, "add", True))):
+    for _ in range(2):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        out = fn()
+    e1.record()
+    torch.cuda.synchronize()
+    print(f"coalesce from {name}: {e0.elapsed_time(e1) / reps:.3f} ms -> {out[0].numel()} entries", flush=True)
