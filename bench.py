@@ -608,7 +608,9 @@ def run_ours(args):
                                 is_sorted=True, trust_data=True)
             A.storage.fill_cache_(carry=False)
             return A
+        del out, shard  # the shard of the timed loop: its memory is what the anchor's own working set needs
         local_only()
+        local_only()    # twice: the first call regrows the allocators' pools for this (different) working set
         local_ms, A_full = timed(local_only, max(args.steps // 2, 2))
         # global invariants of the full-size shards (parity gate, second half)
         st = A_full.storage

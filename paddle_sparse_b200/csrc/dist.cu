@@ -49,16 +49,29 @@ dest_kernel(const int64_t *__restrict__ row, int64_t nnz, const int64_t *__restr
   if (threadIdx.x < 64) sc[threadIdx.x] = 0;
   __syncthreads();
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nnz; i += stride) {
-    const int64_t r = ld_stream(row + i);
-    int lo = 0, hi = G - 1;  // largest g with sp[g] <= r
-    while (lo < hi) {
-      const int mid = (lo + hi + 1) >> 1;
-      if (sp[mid] <= r) lo = mid;
-      else hi = mid - 1;
+  // four rows in flight per thread; the lanes of a warp that go to the same rank count themselves with ONE atomic
+  // (with G = 2 every warp-wide atomicAdd used to serialise 16 deep on its two counters)
+  for (int64_t i0 = (int64_t)blockIdx.x * blockDim.x; i0 < nnz; i0 += 4 * stride) {  // warp-uniform trip count
+    int64_t r[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int64_t i = i0 + u * stride + threadIdx.x;
+      r[u] = i < nnz ? ld_stream(row + i) : -1;
     }
-    dest[i] = (uint32_t)lo;
-    atomicAdd(&sc[lo], 1u);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int64_t i = i0 + u * stride + threadIdx.x;
+      int lo = 0, hi = G - 1;  // largest g with sp[g] <= r
+      while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (sp[mid] <= r[u]) lo = mid;
+        else hi = mid - 1;
+      }
+      const int g = i < nnz ? lo : 64;  // 64: nothing to count
+      if (i < nnz) dest[i] = (uint32_t)lo;
+      const unsigned peers = __match_any_sync(0xffffffffu, g);
+      if (g < 64 && (threadIdx.x & 31u) == (unsigned)(__ffs(peers) - 1)) atomicAdd(&sc[g], (unsigned)__popc(peers));
+    }
   }
   __syncthreads();
   if (threadIdx.x < G && sc[threadIdx.x]) atomicAdd(&counts[threadIdx.x], (unsigned long long)sc[threadIdx.x]);
