@@ -70,9 +70,9 @@ int ps_set_device(int dev);
 
 /* Self-test of the hardware behaviour the stable ranking rests on (shared-memory atomics of one warp instruction that
  * hit the same word are served in ascending lane order; csrc/selftest.cu): host_out[0] = lane-instances checked,
- * [1] = of which in collisions, [2] = served OUT of lane order (must be 0).  Synchronises.  ps_rank_mode(): 0 = the
- * sorts rank with one atomic per item, 1 = match-based ranking (environment PS_RANK_MODE=match), which does not
- * depend on that order. */
+ * [1] = of which in collisions, [2] = served OUT of lane order (must be 0: a device that fails must not run the
+ * sorts, they would be unstable).  Synchronises.  ps_rank_mode(): which ranking the sorts use; always 0 = one atomic
+ * per item (a match-based mode that would not depend on the lane order is NOT built). */
 int ps_selftest_atom_order(int64_t *host_out, void *stream);
 int ps_rank_mode(void);
 

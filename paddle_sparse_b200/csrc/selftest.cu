@@ -4,7 +4,8 @@
 // delivers it (6e10 lane-instances in round 1, none out of order).  ps_selftest_atom_order() re-checks it on the
 // device it runs on, with both counter layouts the kernels use (one 32-bit counter per digit; two 16-bit counters
 // packed in a word) under every collision pattern from "all lanes on one counter" to "no collision"; smoke() and a
-// -m gpu test call it, and PS_RANK_MODE=match switches the sorts to match-based ranking, which needs no such order.
+// -m gpu test call it.  There is no second ranking mode in this build: a device that failed the test must not run
+// the sorts at all (they would be unstable), which is what the callers of the test enforce.
 #include <stdlib.h>
 
 #include "common.cuh"
@@ -50,14 +51,7 @@ atom_order_kernel(int iters, int nvals, int stride, int packed, unsigned long lo
   atomicAdd(&out[2], nb);
 }
 
-int rank_mode() {  // 0 = one shared-memory atomic per item (default), 1 = match-based ranking
-  static int v = -1;
-  if (v < 0) {
-    const char *e = getenv("PS_RANK_MODE");
-    v = (e && (e[0] == 'm' || e[0] == '1')) ? 1 : 0;
-  }
-  return v;
-}
+int rank_mode() { return 0; }  // 0 = one shared-memory atomic per item: the only ranking this build has
 
 }  // namespace ps
 
