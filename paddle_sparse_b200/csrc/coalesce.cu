@@ -11,6 +11,9 @@
 // heads, compacts them with a decoupled look-back scan, unpacks row/col to int64 and
 // reduces each run's values in sorted (= stable) order.  Wide / 8-byte values go
 // through the permutation + segment-reduce path instead.
+#include <cstdio>
+#include <cstdlib>
+
 #include "common.cuh"
 #include "radix_sort.cuh"
 #include "segment.cuh"
@@ -22,6 +25,7 @@ enum { DD_INDEX_ONLY = 0, DD_FAST = 1, DD_PTR = 2 };
 }  // namespace ps
 #include "local_sort.cuh"
 #include "local_sort2.cuh"
+#include "refine.cuh"
 namespace ps {
 
 // One tile = THREADS*ITEMS consecutive sorted entries, held in shared memory; thread t looks at entries
@@ -275,9 +279,146 @@ static int ls2_launch(const KeyT *lowkeys, const uint32_t *lowvals, const unsign
   {
     ProfScope prof(PROF_LOCAL_SORT, s);
     kern<<<grid, L2_THREADS, smem, s>>>(lowkeys, lowvals, bucket_off, nb, R, cbits, M, out_row, out_col,
-                                       reinterpret_cast<T *>(out_value), out_rowptr, state, d_nnz);
+                                       reinterpret_cast<T *>(out_value), out_rowptr, state, d_nnz, L2Desc{});
   }
   PS_LAUNCH_OK();
+  return PS_OK;
+}
+
+// the same kernel on buckets given by descriptors (refine.cuh: skewed rows)
+template <typename T, int RED, bool HAS_VALUE, bool DEDUP>
+static int ls2_launch_desc(const uint32_t *lowkeys, const uint32_t *lowvals, L2Desc desc, int nb, int R, int cbits,
+                           int64_t M, int64_t *out_row, int64_t *out_col, void *out_value, int64_t *out_rowptr,
+                           uint64_t *state, long long *d_nnz, cudaStream_t s) {
+  auto kern = ls2_sort_dedup_kernel<T, RED, HAS_VALUE, DEDUP, uint32_t, true>;
+  const size_t smem = sizeof(L2Smem<HAS_VALUE>);
+  PS_FUNC_SMEM(kern, smem);
+  int grid = sm_count() * 2;
+  if (grid > nb) grid = nb;
+  {
+    ProfScope prof(PROF_LOCAL_SORT, s);
+    kern<<<grid, L2_THREADS, smem, s>>>(lowkeys, lowvals, nullptr, nb, R, cbits, M, out_row, out_col,
+                                       reinterpret_cast<T *>(out_value), out_rowptr, state, d_nnz, desc);
+  }
+  PS_LAUNCH_OK();
+  return PS_OK;
+}
+
+static __global__ void set_u32_kernel(uint32_t *p, uint32_t v) { *p = v; }
+
+// PS_REFINE (bench knob, read once): 0 = an oversized bucket sends the whole input to the LSD sort (round 1)
+static int refine_variant() {
+  static int v = -1;
+  if (v < 0) {
+    const char *e = getenv("PS_REFINE");
+    v = e ? atoi(e) : 1;
+  }
+  return v;
+}
+
+// Oversized buckets re-partitioned level by level (refine.cuh).  On return `*nfinal` buckets are described by the
+// sorted arrays of `desc` (start has nfinal + 1 entries); *ok = false: a key with more duplicates than a bucket holds
+// (or a list overflow) - the caller falls back.  One host synchronisation.
+static int refine_buckets(const uint32_t *keys0, const uint32_t *vals0, int64_t nnz, const unsigned int *bucket_off,
+                          int nb, int R, unsigned cap, Scratch &scratch, cudaStream_t s, L2Desc *desc, int *nfinal,
+                          bool *ok) {
+  *ok = false;
+  const bool has_v = vals0 != nullptr;
+  RfLists L;
+  L.seg_cap = (unsigned)(nnz / cap + 2);
+  L.chunk_cap = (unsigned)(nnz / RF_CH + L.seg_cap + 2);
+  L.final_cap = (unsigned)(nb + 4 * (nnz / cap) + 4 * (int64_t)L.seg_cap + 16);
+  const int nlev = (R + 7) / 8;
+  PS_CHECK(nlev >= 1 && nlev <= RF_MAX_LEVELS, "refine: %d local key bits unsupported", R);
+  PS_SCRATCH(ctl, scratch, RfCtl, 1);
+  PS_CUDA(cudaMemsetAsync(ctl, 0, sizeof(RfCtl), s));
+  for (int l = 0; l < RF_MAX_LEVELS + 2; ++l) {
+    L.seg[l] = nullptr;
+    L.chunk_seg[l] = nullptr;
+  }
+  for (int l = 1; l <= nlev; ++l) {
+    PS_SCRATCH(sg, scratch, RfSeg, L.seg_cap);
+    PS_SCRATCH(cs, scratch, uint32_t, L.chunk_cap);
+    L.seg[l] = sg;
+    L.chunk_seg[l] = cs;
+  }
+  PS_SCRATCH(chunk_hist, scratch, unsigned int, (size_t)L.chunk_cap * 256);
+  PS_SCRATCH(seg_dstart, scratch, unsigned int, (size_t)L.seg_cap * 256);
+  PS_SCRATCH(f_start, scratch, uint32_t, L.final_cap);
+  PS_SCRATCH(f_klo, scratch, uint32_t, L.final_cap);
+  PS_SCRATCH(f_khi, scratch, uint32_t, L.final_cap);
+  PS_SCRATCH(f_orig, scratch, uint32_t, L.final_cap);
+  L.f_start = f_start; L.f_klo = f_klo; L.f_khi = f_khi; L.f_orig = f_orig;
+  PS_SCRATCH(keys1, scratch, uint32_t, nnz);
+  PS_SCRATCH(vals1, scratch, uint32_t, has_v ? nnz : 1);
+  uint32_t *kb[2] = {const_cast<uint32_t *>(keys0), keys1};
+  uint32_t *vb[2] = {const_cast<uint32_t *>(vals0), vals1};
+
+  rf_select_kernel<<<(unsigned)ceil_div(nb, 256), 256, 0, s>>>(bucket_off, nb, R, cap, L, ctl);
+  PS_LAUNCH_OK();
+  auto scat_v = rf_scatter_kernel<true>;
+  auto scat_n = rf_scatter_kernel<false>;
+  PS_FUNC_SMEM(scat_v, sizeof(RfSmem));
+  PS_FUNC_SMEM(scat_n, sizeof(RfSmem));
+  for (int l = 1; l <= nlev; ++l) {
+    const int hi = R - 8 * (l - 1);
+    const int lo = hi - 8 > 0 ? hi - 8 : 0;
+    const unsigned dmask = (1u << (hi - lo)) - 1u;
+    const int src = (l - 1) & 1, dst = l & 1;
+    rf_hist_kernel<<<sm_count() * 8, RF_THREADS, 0, s>>>(kb[src], L.seg[l], L.chunk_seg[l], ctl, l, lo, dmask,
+                                                          L.chunk_cap, chunk_hist);
+    PS_LAUNCH_OK();
+    rf_scan_kernel<<<sm_count() * 8, 256, 0, s>>>(L.seg[l], ctl, ctl, l, lo, dmask, cap, L.seg_cap, chunk_hist,
+                                                   seg_dstart, L, nlev);
+    PS_LAUNCH_OK();
+    if (has_v)
+      scat_v<<<sm_count() * 4, RF_THREADS, sizeof(RfSmem), s>>>(kb[src], vb[src], kb[dst], vb[dst], L.seg[l],
+                                                                L.chunk_seg[l], ctl, l, lo, dmask, L.chunk_cap, chunk_hist,
+                                                                seg_dstart);
+    else
+      scat_n<<<sm_count() * 4, RF_THREADS, sizeof(RfSmem), s>>>(kb[src], nullptr, kb[dst], nullptr, L.seg[l],
+                                                                L.chunk_seg[l], ctl, l, lo, dmask, L.chunk_cap, chunk_hist,
+                                                                seg_dstart);
+    PS_LAUNCH_OK();
+  }
+  RfCtl h;
+  PS_TRY(read_back(&h, ctl, sizeof(h), s));
+  if (getenv("PS_REFINE_DEBUG"))
+    fprintf(stderr, "refine: segments %u %u %u %u | chunks %u %u %u %u | final buckets %u (of %d original) | overflow %u\n",
+            h.nseg[1], h.nseg[2], h.nseg[3], h.nseg[4], h.nchunk[1], h.nchunk[2], h.nchunk[3], h.nchunk[4], h.nfinal, nb,
+            h.overflow);
+  if (h.overflow || h.nfinal == 0 || h.nfinal > L.final_cap) return PS_OK;
+  // the final buckets in key order = sorted by their start
+  const int nf = (int)h.nfinal;
+  PS_SCRATCH(s_start, scratch, uint32_t, (size_t)nf + 1);
+  PS_SCRATCH(s_klo, scratch, uint32_t, nf);
+  PS_SCRATCH(s_khi, scratch, uint32_t, nf);
+  PS_SCRATCH(s_orig, scratch, uint32_t, nf);
+  PS_SCRATCH(t_k0, scratch, uint32_t, nf);
+  PS_SCRATCH(t_k1, scratch, uint32_t, nf);
+  PS_SCRATCH(t_p0, scratch, uint32_t, (size_t)nf * 3);
+  PS_SCRATCH(t_p1, scratch, uint32_t, (size_t)nf * 3);
+  uint32_t *tp0[3] = {t_p0, t_p0 + nf, t_p0 + 2 * (size_t)nf}, *tp1[3] = {t_p1, t_p1 + nf, t_p1 + 2 * (size_t)nf};
+  PaySrcN<3> ps_;
+  ps_.s[0] = PaySrc{f_klo, PSRC_U32};
+  ps_.s[1] = PaySrc{f_khi, PSRC_U32};
+  ps_.s[2] = PaySrc{f_orig, PSRC_U32};
+  PayDstN<3> pd;
+  pd.d[0] = PayDst{s_klo, PDST_U32};
+  pd.d[1] = PayDst{s_khi, PDST_U32};
+  pd.d[2] = PayDst{s_orig, PDST_U32};
+  PS_TRY((radix_sort_tuples<uint32_t, 3>(KeySrc{f_start, nullptr, KSRC_KEYS, 0}, ps_, nf, bits_for(nnz), t_k0, t_k1, tp0,
+                                         tp1, KeyDst{s_start, nullptr, KDST_KEYS, 0}, pd, scratch, s)));
+  set_u32_kernel<<<1, 1, 0, s>>>(s_start + nf, (uint32_t)nnz);
+  PS_LAUNCH_OK();
+  desc->start = s_start;
+  desc->klo = s_klo;
+  desc->khi = s_khi;
+  desc->orig = s_orig;
+  desc->keys1 = keys1;
+  desc->vals1 = has_v ? vals1 : nullptr;
+  *nfinal = nf;
+  *ok = true;
   return PS_OK;
 }
 
@@ -370,7 +511,10 @@ static int hybrid_coalesce(const int64_t *row, const int64_t *col, int64_t nnz, 
     PS_TRY(read_back(&h_max, own->max_bucket, sizeof(h_max), s));
     st = own;
   }
-  if (h_max > (unsigned)ls_cap()) return PS_OK;  // skewed rows: the plain LSD sort handles any distribution
+  // skewed rows: oversized buckets are re-partitioned (refine.cuh); PS_REFINE=0 / the old bucket kernel: the plain LSD
+  // sort, which handles any distribution
+  const bool refine = h_max > (unsigned)ls_cap();
+  if (refine && (!refine_variant() || ls_variant() == 1)) return PS_OK;
   const unsigned int *bucket_off = st->bucket_off;
   const unsigned long long *ghist = st->ghist;
 
@@ -391,10 +535,50 @@ static int hybrid_coalesce(const int64_t *row, const int64_t *col, int64_t nnz, 
     const uint64_t top = M > 0 ? ((((uint64_t)(M - 1)) << cbits) | ((uint64_t(1) << cbits) - 1)) >> R : 0;
     if ((int64_t)top + 1 < nb) nb = (int)top + 1;
   }
-  PS_SCRATCH(state, scratch, uint64_t, (size_t)nb + 1);
-  PS_CUDA(cudaMemsetAsync(state, 0, sizeof(uint64_t) * ((size_t)nb + 1), s));
   PS_SCRATCH(d_nnz, scratch, long long, 1);
   int rc = PS_ERR_ARG;
+  if (refine) {
+    L2Desc desc{};
+    int nf = 0;
+    bool ok = false;
+    PS_TRY(refine_buckets(lowkeys, value ? lowvals : nullptr, nnz, bucket_off, nb, R, (unsigned)L2_CAP, scratch, s, &desc,
+                          &nf, &ok));
+    if (!ok) return PS_OK;  // one key with more duplicates than a bucket holds: the LSD sort
+    PS_SCRATCH(dstate, scratch, uint64_t, (size_t)nf + 1);
+    PS_CUDA(cudaMemsetAsync(dstate, 0, sizeof(uint64_t) * ((size_t)nf + 1), s));
+#define PS_LD_ARGS lowkeys, lowvals, desc, nf, R, cbits, M, out_row, out_col, out_value, out_rowptr, dstate, d_nnz, s
+#define PS_LD(T_)                                                                                \
+  do {                                                                                           \
+    if (dedup) { PS_DISPATCH_REDUCE(reduce, RED, rc = (ls2_launch_desc<T_, RED, true, true>(PS_LD_ARGS))); } \
+    else rc = ls2_launch_desc<T_, PS_SUM, true, false>(PS_LD_ARGS);                              \
+  } while (0)
+    if (!value) {
+      rc = dedup ? ls2_launch_desc<float, PS_SUM, false, true>(lowkeys, nullptr, desc, nf, R, cbits, M, out_row, out_col,
+                                                               nullptr, out_rowptr, dstate, d_nnz, s)
+                 : ls2_launch_desc<float, PS_SUM, false, false>(lowkeys, nullptr, desc, nf, R, cbits, M, out_row, out_col,
+                                                                nullptr, out_rowptr, dstate, d_nnz, s);
+    } else {
+      switch (dtype) {
+        case PS_F32: PS_LD(float); break;
+        case PS_I32: PS_LD(int32_t); break;
+        case PS_BF16: PS_LD(__nv_bfloat16); break;
+        case PS_F16: PS_LD(__half); break;
+        default: break;
+      }
+    }
+#undef PS_LD
+#undef PS_LD_ARGS
+    PS_TRY(rc);
+    if (dedup) {
+      long long h_nnz = 0;
+      PS_TRY(read_back(&h_nnz, d_nnz, sizeof(h_nnz), s));
+      *host_nnz_out = (int64_t)h_nnz;
+    }
+    *used = true;
+    return PS_OK;
+  }
+  PS_SCRATCH(state, scratch, uint64_t, (size_t)nb + 1);
+  PS_CUDA(cudaMemsetAsync(state, 0, sizeof(uint64_t) * ((size_t)nb + 1), s));
 #define PS_LS_ARGS lowkeys, lowvals, bucket_off, nb, R, cbits, M, out_row, out_col, out_value, out_rowptr, state, d_nnz, s
 #define PS_LS(T_)                                                                          \
   do {                                                                                     \

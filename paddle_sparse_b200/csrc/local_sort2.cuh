@@ -23,13 +23,67 @@ constexpr int L2_CAP = L2_THREADS * L2_ITEMS;  // 4,096 entries per bucket
 constexpr int L2_WARPS = L2_THREADS / 32;
 constexpr int L2_BINBITS = 12;
 constexpr int L2_BINS = 1 << L2_BINBITS;
+constexpr int L2_HEAVY = 8;  // a bin beyond this many entries: bin mates are ranked by position, not by owner
 static_assert(L2_BINS == L2_THREADS * 8, "the bin scan gives every thread eight bins (four counter words)");
 
 struct L2Meta {
   long long bucket;
   unsigned int start, end;
   int heads;
+  // what the round needs to know about its bucket (filled by l2_fetch_meta)
+  unsigned int orig;      // the top-T-bit bucket the local keys are relative to
+  unsigned int buf;       // which source buffer holds the bucket (refined buckets alternate)
+  int binshift;           // the 12 bin bits of the counting pass start here (applied to the 32-bit key part)
+  long long rlo, rhi;     // rows whose rowptr entries this bucket writes: [rlo, rhi)
 };
+// Buckets given by descriptors (refine.cuh): sorted by start; entry nb of `start` is the total number of entries.
+struct L2Desc {
+  const uint32_t *start, *klo, *khi, *orig;  // orig: original bucket | buffer << 31
+  const void *keys1;                         // buffer 1 (buffer 0 is the kernel's lowkeys / lowvals)
+  const uint32_t *vals1;
+};
+template <bool DESC>
+__device__ __forceinline__ L2Meta l2_fetch_meta(long long b, int nb, const unsigned int *__restrict__ bucket_off,
+                                                const L2Desc &desc, int R, int cbits, int64_t M, int binshift0) {
+  L2Meta m;
+  m.bucket = b;
+  m.start = m.end = 0u;
+  m.heads = 0;
+  m.orig = 0u;
+  m.buf = 0u;
+  m.binshift = binshift0;
+  m.rlo = m.rhi = 0;
+  if (b >= nb) return m;
+  const uint64_t rowmask = (uint64_t(1) << cbits) - 1;
+  if (!DESC) {
+    m.start = bucket_off[b];
+    m.end = bucket_off[b + 1];
+    m.orig = (unsigned)b;
+    m.rlo = (long long)(((uint64_t)b << R) >> cbits);
+    m.rhi = (long long)((((uint64_t)b + 1) << R) >> cbits);
+    if (b == nb - 1 || m.rhi > M + 1) m.rhi = M + 1;
+  } else {
+    m.start = desc.start[b];
+    m.end = desc.start[b + 1];
+    const uint32_t ob = desc.orig[b], klo = desc.klo[b], khi = desc.khi[b];
+    m.orig = ob & 0x7fffffffu;
+    m.buf = ob >> 31;
+    const uint32_t diff = klo ^ khi;  // every key of the bucket shares the bits above the highest set bit of this
+    const int h = diff ? 32 - __clz(diff) : 0;  // number of low bits in which keys of the bucket may differ
+    m.binshift = h > L2_BINBITS ? h - L2_BINBITS : 0;
+    // rows whose first possible key lies in [this bucket's lowest key, the next listed bucket's lowest key)
+    const uint64_t lo = ((uint64_t)m.orig << R) | klo;
+    m.rlo = b == 0 ? 0 : (long long)((lo + rowmask) >> cbits);
+    if (b + 1 < nb) {
+      const uint64_t nx = ((uint64_t)(desc.orig[b + 1] & 0x7fffffffu) << R) | desc.klo[b + 1];
+      m.rhi = (long long)((nx + rowmask) >> cbits);
+      if (m.rhi > M + 1) m.rhi = M + 1;
+    } else {
+      m.rhi = M + 1;
+    }
+  }
+  return m;
+}
 template <bool HAS_VALUE>
 struct L2Smem {
   uint32_t skeys[2][L2_CAP];                   // sorted low keys (their top 32 bits): [slot] = bucket being sorted /
@@ -45,6 +99,7 @@ struct L2Smem {
   unsigned int maxbin, nheads;
   long long excl;
   L2Meta meta[2];
+  L2Meta meta_next;  // fetched mid-round by thread 0, moved into meta[] when the round ends
 };
 
 // DEDUP = false: sort only (sort-on-construct): every entry is kept, the bucket's output offset is its input offset.
@@ -57,13 +112,14 @@ struct L2Smem {
 // low R <= 36 bits are the bucket-local key (shards of very wide matrices: 51- to 53-bit keys whose local part does
 // not fit 32 bits).  The local key is handled as (top 32 bits, low LO = R - 32 bits); the low bits share a 16-bit
 // word with the 12-bit arrival index, so "(key, arrival index) lexicographic" stays two integer compares.
-template <typename T, int RED, bool HAS_VALUE, bool DEDUP, typename KeyT>
+template <typename T, int RED, bool HAS_VALUE, bool DEDUP, typename KeyT, bool DESC = false>
 __global__ void __launch_bounds__(L2_THREADS, 2)
 ls2_sort_dedup_kernel(const KeyT *__restrict__ lowkeys, const uint32_t *__restrict__ lowvals,
                       const unsigned int *__restrict__ bucket_off, int nb, int R, int cbits, int64_t M,
                       int64_t *__restrict__ out_row, int64_t *__restrict__ out_col, T *__restrict__ out_value,
                       int64_t *__restrict__ out_rowptr, uint64_t *state /*[0]=ticket,[1..]=buckets*/,
-                      long long *d_nnz_out) {
+                      long long *d_nnz_out, L2Desc desc) {
+  static_assert(!DESC || sizeof(KeyT) == 4, "descriptor buckets are built for 32-bit local keys");
   using A = typename Acc<T>::type;
   constexpr int THREADS = L2_THREADS, ITEMS = L2_ITEMS, WARPS = L2_WARPS;
   extern __shared__ __align__(16) unsigned char l2_raw[];
@@ -71,7 +127,7 @@ ls2_sort_dedup_kernel(const KeyT *__restrict__ lowkeys, const uint32_t *__restri
   const unsigned tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
   const unsigned lt = lanemask_lt();
   const int LO = R > 32 ? R - 32 : 0;                       // low key bits kept beside the 32-bit part
-  const int binshift = (R > L2_BINBITS ? R - L2_BINBITS : 0) - LO;  // applied to the 32-bit part
+  const int binshift0 = (R > L2_BINBITS ? R - L2_BINBITS : 0) - LO;  // applied to the 32-bit part
   const uint32_t lomask = (1u << LO) - 1u;
   const uint64_t rmask = R >= 64 ? ~uint64_t(0) : ((uint64_t(1) << R) - 1);
   const uint64_t cmask = (uint64_t(1) << cbits) - 1;
@@ -79,12 +135,7 @@ ls2_sort_dedup_kernel(const KeyT *__restrict__ lowkeys, const uint32_t *__restri
 
   if (tid == 0) {  // the first bucket and its range
     const long long b = (long long)atomicAdd((unsigned long long *)state, 1ull);
-    L2Meta m{b, 0u, 0u, 0};
-    if (b < nb) {
-      m.start = bucket_off[b];
-      m.end = bucket_off[b + 1];
-    }
-    sm.meta[0] = m;
+    sm.meta[0] = l2_fetch_meta<DESC>(b, nb, bucket_off, desc, R, cbits, M, binshift0);
   }
   int slot = 0;
   bool pending = false;
@@ -92,11 +143,17 @@ ls2_sort_dedup_kernel(const KeyT *__restrict__ lowkeys, const uint32_t *__restri
     __syncthreads();  // the previous round is completely written out; meta[slot] is filled
     const int64_t bucket = sm.meta[slot].bucket;
     const bool valid = bucket < nb;
-    long long nxt_bucket = 0;  // thread 0: the bucket after this one, kept in registers until the round ends
-    unsigned nxt_start = 0, nxt_end = 0;
+    long long nxt_bucket = 0;  // thread 0: the bucket after this one
     if (valid) {
       const uint32_t start = sm.meta[slot].start;
       const int cnt = (int)(sm.meta[slot].end - start);
+      const int binshift = sm.meta[slot].binshift;
+      const KeyT *kin = lowkeys;
+      const uint32_t *vin = lowvals;
+      if (DESC && sm.meta[slot].buf) {
+        kin = reinterpret_cast<const KeyT *>(desc.keys1);
+        vin = desc.vals1;
+      }
       const int ie = (cnt + THREADS - 1) / THREADS;  // item rows in use (uniform)
       uint32_t *skeys = sm.skeys[slot], *svals = sm.svals[slot];
       uint8_t *slo = sm.slo[slot];
@@ -109,11 +166,11 @@ ls2_sort_dedup_kernel(const KeyT *__restrict__ lowkeys, const uint32_t *__restri
         key[i] = 0xffffffffu;
         if (i < ie && j < cnt) {
           if (sizeof(KeyT) == 8) {
-            const uint64_t low = (uint64_t)ld_stream(lowkeys + start + j) & rmask;
+            const uint64_t low = (uint64_t)ld_stream(kin + start + j) & rmask;
             key[i] = (uint32_t)(low >> LO);
             klo |= ((uint32_t)low & lomask) << (4 * i);
           } else {
-            key[i] = (uint32_t)ld_stream(lowkeys + start + j);
+            key[i] = (uint32_t)ld_stream(kin + start + j);
           }
         }
       }
@@ -121,7 +178,7 @@ ls2_sort_dedup_kernel(const KeyT *__restrict__ lowkeys, const uint32_t *__restri
 #pragma unroll
         for (int i = 0; i < ITEMS; ++i) {
           const int j = i * THREADS + (int)tid;
-          val[i] = (i < ie && j < cnt) ? ld_stream(lowvals + start + j) : 0u;
+          val[i] = (i < ie && j < cnt) ? ld_stream(vin + start + j) : 0u;
         }
       }
       for (int q = tid; q < L2_BINS / 2 + 2; q += THREADS) sm.bins[q] = 0;
@@ -137,7 +194,7 @@ ls2_sort_dedup_kernel(const KeyT *__restrict__ lowkeys, const uint32_t *__restri
       for (int i = 0; i < ITEMS; ++i) {
         br[i] = 0;
         if (i < ie && i * THREADS + (int)tid < cnt) {
-          const unsigned b = key[i] >> binshift;
+          const unsigned b = DESC ? ((key[i] >> binshift) & (unsigned)(L2_BINS - 1)) : (key[i] >> binshift);
           const unsigned sh = (b & 1u) * 16u;
           const unsigned r = (atomicAdd(&sm.bins[b >> 1], 1u << sh) >> sh) & 0xffffu;
           br[i] = b | (r << 16);
@@ -168,10 +225,7 @@ ls2_sort_dedup_kernel(const KeyT *__restrict__ lowkeys, const uint32_t *__restri
         }
         if (lane == 0 && mx > 1) atomicMax(&sm.maxbin, mx);
       }
-      if (tid == 0 && nxt_bucket < nb) {
-        nxt_start = bucket_off[nxt_bucket];
-        nxt_end = bucket_off[nxt_bucket + 1];
-      }
+      if (tid == 0) sm.meta_next = l2_fetch_meta<DESC>(nxt_bucket, nb, bucket_off, desc, R, cbits, M, binshift0);
       __syncthreads();
       // ---- D / E: no bin holds two entries -> the bin start IS the sorted slot.  Otherwise entries go into their bins
       // in arrival order first, and every entry finds its slot = bin start + number of bin mates that sort before it
@@ -185,6 +239,44 @@ ls2_sort_dedup_kernel(const KeyT *__restrict__ lowkeys, const uint32_t *__restri
           }
         }
         __syncthreads();
+        if (sm.maxbin > (unsigned)L2_HEAVY) {
+          // Skewed keys (power-law columns inside a hub row): a bin may hold a hundred entries, and with the entries of a
+          // thread spread at random every warp would walk the longest bin of its lanes for every item.  Here the work
+          // is dealt by POSITION in the bin-ordered array instead: the lanes of a warp sit in the same bin (or in
+          // neighbouring small ones), the walk over the bin mates is a broadcast read of the same words, and a bin of m
+          // entries costs m * m / 32 warp iterations instead of m per warp and item.  The slots go back to the entries'
+          // owners through a 16-bit map laid over the bin counters, which are no longer needed.
+          uint32_t res[ITEMS];
+#pragma unroll
+          for (int k = 0; k < ITEMS; ++k) {
+            const int p = k * THREADS + (int)tid;
+            res[k] = 0xffffffffu;
+            if (k < ie && p < cnt) {
+              const uint64_t me = sm.wk[p];
+              const uint32_t k32 = (uint32_t)(me >> 16);
+              const unsigned b = DESC ? ((k32 >> binshift) & (unsigned)(L2_BINS - 1)) : (k32 >> binshift);
+              const unsigned s_ = bstart16[b], e_ = bstart16[b + 1];
+              unsigned less = 0;
+              for (unsigned t = s_; t < e_; ++t) less += sm.wk[t] < me ? 1u : 0u;
+              res[k] = ((s_ + less) << 12) | ((uint32_t)me & 0xfffu);
+            }
+          }
+          __syncthreads();  // every read of the bin starts is done
+          uint16_t *slotmap = reinterpret_cast<uint16_t *>(sm.bins);
+#pragma unroll
+          for (int k = 0; k < ITEMS; ++k)
+            if (res[k] != 0xffffffffu) slotmap[res[k] & 0xfffu] = (uint16_t)(res[k] >> 12);
+          __syncthreads();
+#pragma unroll
+          for (int i = 0; i < ITEMS; ++i) {
+            if (i < ie && i * THREADS + (int)tid < cnt) {
+              const unsigned pos = slotmap[i * THREADS + (int)tid];
+              skeys[pos] = key[i];
+              if (sizeof(KeyT) == 8) slo[pos] = (uint8_t)((klo >> (4 * i)) & 15u);
+              if (HAS_VALUE) svals[pos] = val[i];
+            }
+          }
+        } else
 #pragma unroll
         for (int i = 0; i < ITEMS; ++i) {
           if (i < ie && i * THREADS + (int)tid < cnt) {
@@ -336,10 +428,9 @@ ls2_sort_dedup_kernel(const KeyT *__restrict__ lowkeys, const uint32_t *__restri
       const int64_t excl = DEDUP ? (int64_t)sm.excl : (int64_t)start;
       const int nheads = DEDUP ? sm.meta[ps_].heads : cnt;
       // output: consecutive lanes hold consecutive heads, coalesced wherever nothing was merged
-      const uint64_t hi_bits = (uint64_t)pbucket << R;
-      const int64_t rlo = (int64_t)(hi_bits >> cbits);  // rows owned by this bucket: [rlo, rhi)
-      int64_t rhi = (int64_t)((((uint64_t)pbucket + 1) << R) >> cbits);
-      if (pbucket == nb - 1 || rhi > M + 1) rhi = M + 1;
+      const uint64_t hi_bits = (uint64_t)sm.meta[ps_].orig << R;
+      const int64_t rbase = (int64_t)(hi_bits >> cbits);  // first row of the original bucket (local keys count from it)
+      const int64_t rlo = sm.meta[ps_].rlo, rhi = sm.meta[ps_].rhi;  // rows owned by this bucket: [rlo, rhi)
 #pragma unroll
       for (int i = 0; i < ITEMS; ++i) {
         if (!((heads >> i) & 1u)) continue;
@@ -354,7 +445,7 @@ ls2_sort_dedup_kernel(const KeyT *__restrict__ lowkeys, const uint32_t *__restri
           r = (int64_t)(full >> cbits);
           out_col[o] = (int64_t)(full & cmask);
         } else {
-          r = rlo + (int64_t)((uint32_t)lk >> cbits);
+          r = rbase + (int64_t)((uint32_t)lk >> cbits);
           out_col[o] = (int64_t)((uint32_t)lk & (uint32_t)cmask);
         }
         out_row[o] = r;
@@ -371,7 +462,7 @@ ls2_sort_dedup_kernel(const KeyT *__restrict__ lowkeys, const uint32_t *__restri
         if (out_rowptr) {
           const int64_t pr = j == 0 ? rlo - 1
                                     : (sizeof(KeyT) == 8 ? (int64_t)((hi_bits | lowkey(j - 1)) >> cbits)
-                                                         : rlo + (int64_t)(skeys[j - 1] >> cbits));
+                                                         : rbase + (int64_t)(skeys[j - 1] >> cbits));
           if (r != pr && r <= M) {  // this head opens row r ...
             out_rowptr[r] = o;
             if (r - pr > 1)  // ... and the empty rows before it (rare)
@@ -380,7 +471,8 @@ ls2_sort_dedup_kernel(const KeyT *__restrict__ lowkeys, const uint32_t *__restri
         }
       }
       if (out_rowptr) {  // rows of this bucket after its last entry (all of them when the bucket is empty)
-        const int64_t first = cnt > 0 ? (int64_t)((hi_bits | lowkey(cnt - 1)) >> cbits) + 1 : rlo;
+        int64_t first = cnt > 0 ? (int64_t)((hi_bits | lowkey(cnt - 1)) >> cbits) + 1 : rlo;
+        if (first < rlo) first = rlo;  // (a refined bucket may start inside a row that an earlier bucket opened)
         for (int64_t q = first + tid; q < rhi; q += THREADS) out_rowptr[q] = excl + nheads;
       }
       if (DEDUP && pbucket == nb - 1 && tid == 0) *d_nnz_out = (long long)(excl + nheads);
@@ -388,7 +480,7 @@ ls2_sort_dedup_kernel(const KeyT *__restrict__ lowkeys, const uint32_t *__restri
     if (!valid) break;
     pending = true;
     __syncthreads();  // every reader of meta[slot ^ 1] (the bucket just written out) is done
-    if (tid == 0) sm.meta[slot ^ 1] = L2Meta{nxt_bucket, nxt_start, nxt_end, 0};
+    if (tid == 0) sm.meta[slot ^ 1] = sm.meta_next;
     slot ^= 1;
   }
 }

@@ -296,6 +296,61 @@ def test_coalesce_u32_matches_coalesce(ops, M, N, nnz, dup, dtype, reduce):
         ops.coalesce_u32(row32, col32, (1 << 32) - 5, val, M, N, reduce, True)
 
 
+@pytest.mark.parametrize("nnz", [300000, 3000000])
+@pytest.mark.parametrize("dtype,reduce", [(torch.float32, "add"), (torch.int32, "max"), (torch.bfloat16, "add"),
+                                          (None, "add")])
+def test_hybrid_coalesce_skewed_rows_are_refined(ops, nnz, dtype, reduce):
+    """Power-law rows (the R-MAT stream of the bench, and hand-made hubs on top of it): buckets beyond a CTA's
+    capacity are re-partitioned level by level (refine.cuh) instead of sending the whole input to the LSD sort.  Row,
+    col, rowptr bit-exact against the oracle, values exact (small integers)."""
+    M = N = 2449029
+    row, col, _ = ops.synth_coo(0x5EED0002, 0, nnz, M, N, "cuda", with_value=False, rmat=True)
+    row, col = host(row).copy(), host(col).copy()
+    rng = np.random.default_rng(nnz)
+    row[: nnz // 10] = 77                      # one row holding 10 % of the entries ...
+    col[: nnz // 40] = rng.integers(5, 9, nnz // 40)   # ... a quarter of them on four columns (thousands of duplicates,
+    row[nnz // 10: nnz // 10 + 5000] = M - 1   # but below the 4,096 a single key may have); the last row is a hub too
+    col[nnz // 10: nnz // 10 + 5000] = rng.integers(0, N, 5000)
+    p = rng.permutation(nnz)
+    row, col = row[p], col[p]
+    val = None if dtype is None else rng.integers(-40, 40, nnz)
+    tv = None if dtype is None else dev(val, dtype)
+    r, c, v, rowptr = ops.coalesce(dev(row), dev(col), tv, M, N, reduce, True)
+    idx, want = np_ref.coalesce(np.stack([row, col]), None if val is None else val.astype(np.float64), M, N, reduce)
+    assert np.array_equal(host(r), idx[0]) and np.array_equal(host(c), idx[1])
+    assert np.array_equal(host(rowptr), np.searchsorted(idx[0], np.arange(M + 1), side="left"))
+    if dtype is not None:
+        got = host(v.to(torch.float64))
+        if dtype == torch.bfloat16:
+            np.testing.assert_allclose(got, want, rtol=8e-3, atol=1e-6)
+        else:
+            assert np.array_equal(got, want)
+    # sort-on-construct on the same stream: stable (duplicate keys carry distinct values)
+    if dtype == torch.float32:
+        order = np.argsort(row * N + col, kind="stable")
+        sv = (np.arange(nnz) % 251).astype(np.float32)
+        r2, c2, v2, _ = ops.sort_coo(dev(row), dev(col), dev(sv), M, N)
+        assert np.array_equal(host(r2), row[order]) and np.array_equal(host(c2), col[order])
+        assert np.array_equal(host(v2), sv[order])
+
+
+def test_hybrid_coalesce_one_key_beyond_a_bucket_falls_back(ops):
+    """A single (row, col) with more duplicates than a bucket holds cannot be split by key bits: the LSD sort takes
+    over, with the same results."""
+    rng = np.random.default_rng(12)
+    M = N = 2449029
+    row = np.concatenate([rng.integers(0, M, 200000), np.full(9000, 1234)]).astype(I64)
+    col = np.concatenate([rng.integers(0, N, 200000), np.full(9000, 4321)]).astype(I64)
+    p = rng.permutation(row.size)
+    row, col = row[p], col[p]
+    val = rng.integers(-5, 6, row.size).astype(np.float32)
+    r, c, v, rowptr = ops.coalesce(dev(row), dev(col), dev(val), M, N, "add", True)
+    idx, want = np_ref.coalesce(np.stack([row, col]), val.astype(np.float64), M, N, "add")
+    assert np.array_equal(host(r), idx[0]) and np.array_equal(host(c), idx[1])
+    assert np.array_equal(host(v).astype(np.float64), want)
+    assert np.array_equal(host(rowptr), np.searchsorted(idx[0], np.arange(M + 1), side="left"))
+
+
 def test_hybrid_coalesce_hub_rows_fall_back(ops):
     """one bucket beyond the shared-memory capacity (a hub row range): the plain LSD pipeline takes over"""
     rng = np.random.default_rng(9)

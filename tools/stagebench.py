@@ -1,5 +1,5 @@
 """Per-API-call device time of the bench step on the configs[1] shape (run on the GPU box):
-   python tools/stagebench.py"""
+   python tools/stagebench.py [--rmat]"""
 import os
 import sys
 
@@ -11,7 +11,7 @@ from paddle_sparse_b200 import ops  # noqa: E402
 
 M = N = 2449029
 NNZ = 61859140
-row, col, val = ops.synth_coo(0x5EED0002, 0, NNZ, M, N, "cuda")
+row, col, val = ops.synth_coo(0x5EED0002, 0, NNZ, M, N, "cuda", rmat="--rmat" in sys.argv)
 
 
 def step(ev):
