@@ -305,8 +305,17 @@ static int ls2_launch_desc(const uint32_t *lowkeys, const uint32_t *lowvals, L2D
 }
 
 static __global__ void set_u32_kernel(uint32_t *p, uint32_t v) { *p = v; }
+static __global__ void coarsen_counts_kernel(const unsigned int *__restrict__ fine, int shift, int nb2,
+                                             unsigned int *__restrict__ coarse) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= nb2) return;
+  unsigned int sum = 0;
+  for (int q = 0; q < (1 << shift); ++q) sum += fine[((size_t)b << shift) + q];
+  coarse[b] = sum;
+}
 
-// PS_REFINE (bench knob, read once): 0 = an oversized bucket sends the whole input to the LSD sort (round 1)
+// PS_REFINE (bench knob, read once): 0 = an oversized bucket sends the whole input to the LSD sort (round 1),
+// 1 (default) = oversized buckets are refined, 2 = refined from a coarser top level (see hybrid_coalesce)
 static int refine_variant() {
   static int v = -1;
   if (v < 0) {
@@ -498,7 +507,7 @@ static int hybrid_coalesce(const int64_t *row, const int64_t *col, int64_t nnz, 
   *used = false;
   HybridPlan hp;
   if (!hybrid_plan(nnz, M, rbits, cbits, &hp)) return PS_OK;
-  const int T = hp.T, R = hp.R;
+  int T = hp.T, R = hp.R;
   int nb = hp.nb;
   Scratch scratch(s);
   const LsInspect *st = pre;
@@ -517,6 +526,32 @@ static int hybrid_coalesce(const int64_t *row, const int64_t *col, int64_t nnz, 
   if (refine && (!refine_variant() || ls_variant() == 1)) return PS_OK;
   const unsigned int *bucket_off = st->bucket_off;
   const unsigned long long *ghist = st->ghist;
+  if (refine && refine_variant() == 2) {
+    // PS_REFINE=2 (measured, NOT the default): start from COARSER buckets (3 fewer top bits, as far as the local key
+    // still fits 32 bits).  Then every bucket goes through the refinement, whose greedy packing also merges the many
+    // light row ranges of a power-law graph into full buckets: 18.5 K final buckets on the R-MAT stream instead of
+    // 30.8 K - but twice the entries reach level 2, and the coalesce takes 3.90 ms against 3.67.  The coarse counts
+    // are sums of the inspection's fine ones.
+    const int tmin = hp.K - 32 > 1 ? hp.K - 32 : 1;
+    int T2 = T - 3 > tmin ? T - 3 : tmin;
+    if (T2 < T) {
+      PS_SCRATCH(co, scratch, LsInspect, 1);
+      const int nb2 = 1 << T2;
+      coarsen_counts_kernel<<<(unsigned)ceil_div(nb2, 256), 256, 0, s>>>(st->gcount, T - T2, nb2, co->gcount);
+      PS_LAUNCH_OK();
+      const SortPlan gp = make_sort_plan(T2, rs_geometry<uint64_t, 1>().rbits);
+      LsPlan lp2;
+      lp2.passes = gp.passes;
+      for (int p = 0; p < 2; ++p) { lp2.pbegin[p] = p < gp.passes ? gp.begin[p] : 0; lp2.pbits[p] = p < gp.passes ? gp.bits[p] : 0; }
+      ls_derive_kernel<<<1, 1024, 0, s>>>(co->gcount, T2, lp2, co->bucket_off, co->ghist, co->max_bucket, 0, LsChunkOut{});
+      PS_LAUNCH_OK();
+      T = T2;
+      R = hp.K - T2;
+      nb = nb2;
+      bucket_off = co->bucket_off;
+      ghist = co->ghist;
+    }
+  }
 
   // global passes on key bits [R, K): the last one keeps only the low R bits of the key
   PS_SCRATCH(k0, scratch, uint64_t, nnz);
