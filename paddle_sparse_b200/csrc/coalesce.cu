@@ -287,7 +287,8 @@ static int ls2_launch(const KeyT *lowkeys, const uint32_t *lowvals, const unsign
 
 // the same kernel on buckets given by descriptors (refine.cuh: skewed rows)
 template <typename T, int RED, bool HAS_VALUE, bool DEDUP>
-static int ls2_launch_desc(const uint32_t *lowkeys, const uint32_t *lowvals, L2Desc desc, int nb, int R, int cbits,
+static int ls2_launch_desc(const uint32_t *lowkeys, const uint32_t *lowvals, const unsigned int *bucket_off /*of the
+                           original buckets*/, L2Desc desc, int nb, int R, int cbits,
                            int64_t M, int64_t *out_row, int64_t *out_col, void *out_value, int64_t *out_rowptr,
                            uint64_t *state, long long *d_nnz, cudaStream_t s) {
   auto kern = ls2_sort_dedup_kernel<T, RED, HAS_VALUE, DEDUP, uint32_t, true>;
@@ -297,7 +298,7 @@ static int ls2_launch_desc(const uint32_t *lowkeys, const uint32_t *lowvals, L2D
   if (grid > nb) grid = nb;
   {
     ProfScope prof(PROF_LOCAL_SORT, s);
-    kern<<<grid, L2_THREADS, smem, s>>>(lowkeys, lowvals, nullptr, nb, R, cbits, M, out_row, out_col,
+    kern<<<grid, L2_THREADS, smem, s>>>(lowkeys, lowvals, bucket_off, nb, R, cbits, M, out_row, out_col,
                                        reinterpret_cast<T *>(out_value), out_rowptr, state, d_nnz, desc);
   }
   PS_LAUNCH_OK();
@@ -363,7 +364,8 @@ static int refine_buckets(const uint32_t *keys0, const uint32_t *vals0, int64_t 
   uint32_t *kb[2] = {const_cast<uint32_t *>(keys0), keys1};
   uint32_t *vb[2] = {const_cast<uint32_t *>(vals0), vals1};
 
-  rf_select_kernel<<<(unsigned)ceil_div(nb, 256), 256, 0, s>>>(bucket_off, nb, R, cap, L, ctl);
+  const int gbits = 32 - R < 3 ? (32 - R > 0 ? 32 - R : 0) : 3;  // neighbours a final bucket may merge: 2^gbits
+  rf_select_kernel<<<(unsigned)ceil_div(ceil_div(nb, 1 << gbits), 256), 256, 0, s>>>(bucket_off, nb, R, gbits, cap, L, ctl);
   PS_LAUNCH_OK();
   auto scat_v = rf_scatter_kernel<true>;
   auto scat_n = rf_scatter_kernel<false>;
@@ -581,17 +583,17 @@ static int hybrid_coalesce(const int64_t *row, const int64_t *col, int64_t nnz, 
     if (!ok) return PS_OK;  // one key with more duplicates than a bucket holds: the LSD sort
     PS_SCRATCH(dstate, scratch, uint64_t, (size_t)nf + 1);
     PS_CUDA(cudaMemsetAsync(dstate, 0, sizeof(uint64_t) * ((size_t)nf + 1), s));
-#define PS_LD_ARGS lowkeys, lowvals, desc, nf, R, cbits, M, out_row, out_col, out_value, out_rowptr, dstate, d_nnz, s
+#define PS_LD_ARGS lowkeys, lowvals, bucket_off, desc, nf, R, cbits, M, out_row, out_col, out_value, out_rowptr, dstate, d_nnz, s
 #define PS_LD(T_)                                                                                \
   do {                                                                                           \
     if (dedup) { PS_DISPATCH_REDUCE(reduce, RED, rc = (ls2_launch_desc<T_, RED, true, true>(PS_LD_ARGS))); } \
     else rc = ls2_launch_desc<T_, PS_SUM, true, false>(PS_LD_ARGS);                              \
   } while (0)
     if (!value) {
-      rc = dedup ? ls2_launch_desc<float, PS_SUM, false, true>(lowkeys, nullptr, desc, nf, R, cbits, M, out_row, out_col,
-                                                               nullptr, out_rowptr, dstate, d_nnz, s)
-                 : ls2_launch_desc<float, PS_SUM, false, false>(lowkeys, nullptr, desc, nf, R, cbits, M, out_row, out_col,
-                                                                nullptr, out_rowptr, dstate, d_nnz, s);
+      rc = dedup ? ls2_launch_desc<float, PS_SUM, false, true>(lowkeys, nullptr, bucket_off, desc, nf, R, cbits, M, out_row,
+                                                               out_col, nullptr, out_rowptr, dstate, d_nnz, s)
+                 : ls2_launch_desc<float, PS_SUM, false, false>(lowkeys, nullptr, bucket_off, desc, nf, R, cbits, M, out_row,
+                                                                out_col, nullptr, out_rowptr, dstate, d_nnz, s);
     } else {
       switch (dtype) {
         case PS_F32: PS_LD(float); break;

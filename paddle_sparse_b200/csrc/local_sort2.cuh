@@ -35,6 +35,9 @@ struct L2Meta {
   unsigned int buf;       // which source buffer holds the bucket (refined buckets alternate)
   int binshift;           // the 12 bin bits of the counting pass start here (applied to the 32-bit key part)
   long long rlo, rhi;     // rows whose rowptr entries this bucket writes: [rlo, rhi)
+  unsigned int nmerge;    // original buckets merged into this one (descriptor buckets of light row ranges) ...
+  unsigned int bnd[7];    // ... and where the 2nd .. 8th of them start: an entry's local key is extended by the
+                          // number of these at or before its position, shifted by R
 };
 // Buckets given by descriptors (refine.cuh): sorted by start; entry nb of `start` is the total number of entries.
 struct L2Desc {
@@ -53,6 +56,7 @@ __device__ __forceinline__ L2Meta l2_fetch_meta(long long b, int nb, const unsig
   m.buf = 0u;
   m.binshift = binshift0;
   m.rlo = m.rhi = 0;
+  m.nmerge = 1u;
   if (b >= nb) return m;
   const uint64_t rowmask = (uint64_t(1) << cbits) - 1;
   if (!DESC) {
@@ -66,8 +70,10 @@ __device__ __forceinline__ L2Meta l2_fetch_meta(long long b, int nb, const unsig
     m.start = desc.start[b];
     m.end = desc.start[b + 1];
     const uint32_t ob = desc.orig[b], klo = desc.klo[b], khi = desc.khi[b];
-    m.orig = ob & 0x7fffffffu;
+    m.orig = ob & 0xffffu;
+    m.nmerge = ((ob >> 16) & 7u) + 1u;
     m.buf = ob >> 31;
+    for (unsigned q = 1; q < m.nmerge; ++q) m.bnd[q - 1] = bucket_off[m.orig + q];
     const uint32_t diff = klo ^ khi;  // every key of the bucket shares the bits above the highest set bit of this
     const int h = diff ? 32 - __clz(diff) : 0;  // number of low bits in which keys of the bucket may differ
     m.binshift = h > L2_BINBITS ? h - L2_BINBITS : 0;
@@ -75,7 +81,7 @@ __device__ __forceinline__ L2Meta l2_fetch_meta(long long b, int nb, const unsig
     const uint64_t lo = ((uint64_t)m.orig << R) | klo;
     m.rlo = b == 0 ? 0 : (long long)((lo + rowmask) >> cbits);
     if (b + 1 < nb) {
-      const uint64_t nx = ((uint64_t)(desc.orig[b + 1] & 0x7fffffffu) << R) | desc.klo[b + 1];
+      const uint64_t nx = ((uint64_t)(desc.orig[b + 1] & 0xffffu) << R) | desc.klo[b + 1];
       m.rhi = (long long)((nx + rowmask) >> cbits);
       if (m.rhi > M + 1) m.rhi = M + 1;
     } else {
@@ -148,6 +154,7 @@ ls2_sort_dedup_kernel(const KeyT *__restrict__ lowkeys, const uint32_t *__restri
       const uint32_t start = sm.meta[slot].start;
       const int cnt = (int)(sm.meta[slot].end - start);
       const int binshift = sm.meta[slot].binshift;
+      const unsigned nmerge = DESC ? sm.meta[slot].nmerge : 1u;
       const KeyT *kin = lowkeys;
       const uint32_t *vin = lowvals;
       if (DESC && sm.meta[slot].buf) {
@@ -171,6 +178,12 @@ ls2_sort_dedup_kernel(const KeyT *__restrict__ lowkeys, const uint32_t *__restri
             klo |= ((uint32_t)low & lomask) << (4 * i);
           } else {
             key[i] = (uint32_t)ld_stream(kin + start + j);
+            if (DESC && nmerge > 1) {
+              uint32_t delta = 0;
+#pragma unroll
+              for (int q = 0; q < 7; ++q) delta += (q + 1 < (int)nmerge && start + (uint32_t)j >= sm.meta[slot].bnd[q]) ? 1u : 0u;
+              key[i] |= delta << R;
+            }
           }
         }
       }
@@ -471,7 +484,8 @@ ls2_sort_dedup_kernel(const KeyT *__restrict__ lowkeys, const uint32_t *__restri
         }
       }
       if (out_rowptr) {  // rows of this bucket after its last entry (all of them when the bucket is empty)
-        int64_t first = cnt > 0 ? (int64_t)((hi_bits | lowkey(cnt - 1)) >> cbits) + 1 : rlo;
+        // (+, not |: the extended keys of a merged bucket carry bits at and above R)
+        int64_t first = cnt > 0 ? (int64_t)((hi_bits + lowkey(cnt - 1)) >> cbits) + 1 : rlo;
         if (first < rlo) first = rlo;  // (a refined bucket may start inside a row that an earlier bucket opened)
         for (int64_t q = first + tid; q < rhi; q += THREADS) out_rowptr[q] = excl + nheads;
       }

@@ -80,15 +80,41 @@ __device__ __forceinline__ void rf_push_seg(const RfLists &L, RfCtl *ctl, int le
   for (unsigned q = 0; q < nch; ++q) L.chunk_seg[level][c0 + q] = s;
 }
 
-// original buckets: small ones are final as they are, oversized ones become the segments of level 1
+// original buckets: oversized ones become the segments of level 1; the others are final, NEIGHBOURS MERGED while they
+// fit one bucket and the bucket-local key has spare bits (a power-law graph has thousands of light row ranges of a
+// few hundred entries each).  A merged bucket's local keys are extended by the original bucket's distance from the
+// first one: (delta << R) | key, which must fit 32 bits - groups of 2^gbits <= 8 aligned neighbours, gbits <= 32 - R.
+// f_orig: first original bucket | (originals merged - 1) << 16 | buffer << 31.
 static __global__ void __launch_bounds__(256)
-rf_select_kernel(const unsigned int *__restrict__ bucket_off, int nb, int R, unsigned cap, RfLists L, RfCtl *ctl) {
+rf_select_kernel(const unsigned int *__restrict__ bucket_off, int nb, int R, int gbits, unsigned cap, RfLists L,
+                 RfCtl *ctl) {
   const uint32_t kmax = R >= 32 ? 0xffffffffu : ((1u << R) - 1u);
-  for (int b = blockIdx.x * blockDim.x + threadIdx.x; b < nb; b += gridDim.x * blockDim.x) {
-    const unsigned s = bucket_off[b], e = bucket_off[b + 1];
-    if (e == s) continue;  // its rows belong to the bucket before it (ownership runs up to the next listed bucket)
-    if (e - s <= cap) rf_push_final(L, ctl, s, 0u, kmax, (uint32_t)b, 0);
-    else rf_push_seg(L, ctl, 1, RF_MAX_LEVELS, s, e, (uint32_t)b, 0u);
+  const int gsz = 1 << gbits;
+  const int groups = (nb + gsz - 1) >> gbits;
+  for (int g = blockIdx.x * blockDim.x + threadIdx.x; g < groups; g += gridDim.x * blockDim.x) {
+    int first = -1, last = -1;
+    unsigned size = 0;
+    for (int q = 0; q <= gsz; ++q) {
+      const int b = (g << gbits) + q;
+      const bool in = q < gsz && b < nb;
+      const unsigned s = in ? bucket_off[b] : 0u, e = in ? bucket_off[b + 1] : 0u;
+      const unsigned sz = e - s;
+      const bool big = sz > cap;
+      if (first >= 0 && (!in || big || size + sz > cap)) {  // close the open run of originals [first, last]
+        rf_push_final(L, ctl, bucket_off[first], 0u, (uint32_t)(((uint64_t)(last - first) << R) | kmax),
+                      (uint32_t)first | ((uint32_t)(last - first) << 16), 0);
+        first = -1;
+        size = 0;
+      }
+      if (!in || sz == 0) continue;  // an empty bucket's rows belong to the bucket listed before it
+      if (big) {
+        rf_push_seg(L, ctl, 1, RF_MAX_LEVELS, s, e, (uint32_t)b, 0u);
+      } else {
+        if (first < 0) first = b;
+        last = b;
+        size += sz;
+      }
+    }
   }
 }
 
