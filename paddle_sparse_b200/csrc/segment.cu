@@ -212,6 +212,307 @@ segment_reduce_long_kernel(const T *__restrict__ src, int64_t width, const int64
   }
 }
 
+// ============================================================================= segment reduce, load-balanced over ENTRIES
+// The kernels above give every segment a group of lanes: a warp's life time (two dependent pointer loads, a few data
+// round trips, the shuffle tree, one store: ~4 us) times the number of warp rounds bounds them, not bytes - which is
+// why bf16 rows took the time of f32 rows (0.37 against 0.67 of HBM).  This one is the merge-path form: a CTA takes a
+// tile of 4,096 CONSECUTIVE entries whatever the segments look like (16 per thread, 16-byte loads), every thread folds
+// the runs of equal segment inside its 16 entries, runs that begin and end inside one thread are written at once, the
+// open runs at the threads' edges are combined by a segmented scan over the 256 threads (left to right: a fixed
+// order), and a segment that crosses tiles leaves one partial per tile: `carry` where it leaves a tile, `head` where
+// it ends; a small second kernel folds them in tile order.  [nnz] vectors of <= 4-byte types, no permutation.
+constexpr int ST_THREADS = 256, ST_ITEMS = 16, ST_TILE = ST_THREADS * ST_ITEMS;
+struct StTile {       // what a tile leaves for the fix-up kernel
+  long long head_seg;  // segment that began in an earlier tile and ENDS in this one (-1: none); its part here: head
+  int carry;           // 0: nothing leaves the tile; 1: the last segment goes on; 2: and it spans the whole tile
+  int pad;
+};
+
+template <typename T, int RED>
+__global__ void __launch_bounds__(ST_THREADS)
+segment_tile_kernel(const T *__restrict__ src, const int64_t *__restrict__ ptr, int64_t S, int64_t E,
+                    const int32_t *__restrict__ bounds, T *__restrict__ out, StTile *__restrict__ tinfo,
+                    typename Acc<T>::type *__restrict__ thead, typename Acc<T>::type *__restrict__ tcarry, int vec16) {
+  using A = typename Acc<T>::type;
+  using R = Red<RED, A>;
+  constexpr int THREADS = ST_THREADS, ITEMS = ST_ITEMS, TILE = ST_TILE, WARPS = THREADS / 32;
+  __shared__ int32_t seg[TILE];
+  __shared__ int32_t aux[40];
+  __shared__ int32_t sh_first[THREADS], sh_last[THREADS];
+  __shared__ A sh_val[THREADS];
+  __shared__ A w_val[WARPS];
+  __shared__ int w_flag[WARPS];
+  __shared__ int sh_before;  // the tile's first segment began in an earlier tile
+  const unsigned tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+  const int64_t tile = blockIdx.x;
+  const int64_t e0 = tile * TILE;
+  const int tile_n = (int)((E - e0) < TILE ? (E - e0) : TILE);
+  const int p0 = (int)tid * ITEMS;
+  const int nvalid = tile_n - p0 < ITEMS ? (tile_n - p0 > 0 ? tile_n - p0 : 0) : ITEMS;
+  // loads that do not depend on the look-up are requested first (a CTA's life is a chain of dependent round trips)
+  const int64_t pbeg = ptr[0], pend = ptr[S];
+  int64_t first_start = 0;  // thread 0: where the tile's first segment starts
+  if (tid == 0) first_start = ptr[bounds[tile]];
+  // ---- the thread's values: requested FIRST, so that their latency overlaps the segment look-up below (one after
+  // the other the two dependent chains made a CTA live ~4.5 us for its 16 KB)
+  constexpr int V = 16 / (int)sizeof(T);  // entries per 16-byte load
+  constexpr int NV = ITEMS / V;
+  const T *base = src + e0 + p0;
+  const bool vec = vec16 && nvalid == ITEMS;
+  uint4 raw[NV];  // only LOADED here: the conversions wait until the look-up is done
+  if (vec) {
+#pragma unroll
+    for (int q = 0; q < NV; ++q) raw[q] = __ldg(reinterpret_cast<const uint4 *>(base) + q);
+  }
+  // ---- segments of my entries.  The usual case - all 16 in ONE segment (rows are long) - is found by two binary
+  // searches of the tile's sorted table of segment starts and needs no per-entry work at all: resolving a segment id
+  // for every entry (expand_tile_owned) cost ~48 instructions per entry and made the kernel issue-bound at 2 TB/s.
+  int32_t own[ITEMS];
+  bool uniform = false;  // all my entries lie in segment own[0]
+  bool masked = false;   // segment starts given by `starts` (else by own[])
+  uint32_t starts = 0;
+  int b_lo = 0, b_hi = 0;  // table entries [b_lo, b_hi) are the starts inside my entries
+  const bool inside = e0 >= pbeg && e0 + TILE <= pend;  // (else some entries may belong to no segment)
+  if (tid < 2) aux[32 + tid] = bounds[tile + tid];
+  __syncthreads();
+  const int32_t s_lo = aux[32], s_hi = aux[33];
+  const int nseg = s_hi - s_lo;
+  if (nseg <= TILE && inside) {  // uniform over the CTA
+    for (int i = tid; i < nseg; i += THREADS) {
+      const int64_t p = ptr[(int64_t)s_lo + 1 + i] - e0;
+      seg[i] = p < 0 ? 0 : (p > TILE ? TILE : (int32_t)p);
+    }
+    __syncthreads();
+    auto count_le = [&](int lo, int hi, int p) {  // first index in [lo, hi] whose start exceeds p
+      while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (seg[mid] <= p) lo = mid + 1;
+        else hi = mid;
+      }
+      return lo;
+    };
+    b_lo = count_le(0, nseg, p0);
+    b_hi = count_le(b_lo, nseg, p0 + ITEMS - 1);
+    own[0] = s_lo + b_lo;
+    // Segment starts inside my entries as a 16-bit mask (a warp runs the slow path below as soon as ONE lane has a
+    // boundary - two warps in three with 492-entry rows - so that path must be cheap for the lanes that have none)
+    for (int b = b_lo; b < b_hi; ++b) starts |= 1u << (seg[b] - p0);  // seg[b] - p0 in [1, ITEMS - 1]
+    masked = true;
+    uniform = starts == 0u;
+  } else {
+    __syncthreads();  // (aux is rewritten by the general look-up)
+    expand_tile_owned<THREADS, ITEMS>(ptr, S, e0, tile_n, seg, aux, bounds, own);
+    if (!inside) {  // entries outside [ptr[0], ptr[S]) belong to no segment (ptr need not cover src): id -1
+#pragma unroll
+      for (int k = 0; k < ITEMS; ++k) {
+        const int64_t e = e0 + p0 + k;
+        if (e < pbeg || e >= pend) own[k] = -1;
+      }
+    }
+  }
+  A v[ITEMS];
+  if (vec) {
+#pragma unroll
+    for (int q = 0; q < NV; ++q) {
+      const T *t = reinterpret_cast<const T *>(&raw[q]);
+#pragma unroll
+      for (int k = 0; k < V; ++k) v[q * V + k] = to_acc<T>(t[k]);
+    }
+  } else {
+#pragma unroll
+    for (int k = 0; k < ITEMS; ++k) v[k] = k < nvalid ? to_acc<T>(base[k]) : R::init();
+  }
+  // ---- runs of equal segment inside the thread
+  int32_t first_seg = -2 - (int32_t)tid, last_seg = -2 - (int32_t)tid;  // an idle thread matches nobody
+  A first_acc = R::init(), acc = R::init();
+  bool single = true;
+  if (uniform && nvalid > 0) {  // one run: a plain sum of my values (entries past the tile's end hold the neutral value)
+    first_seg = last_seg = own[0];
+    A t[ITEMS / 2];
+#pragma unroll
+    for (int k = 0; k < ITEMS / 2; ++k) t[k] = R::op(v[2 * k], v[2 * k + 1]);
+#pragma unroll
+    for (int w = ITEMS / 4; w > 0; w >>= 1)
+#pragma unroll
+      for (int k = 0; k < w; ++k) t[k] = R::op(t[2 * k], t[2 * k + 1]);
+    acc = first_acc = t[0];
+  } else if (masked && nvalid > 0) {
+    int32_t cur = own[0];
+    int b = b_lo, run0 = 0;
+    first_seg = cur;
+#pragma unroll
+    for (int k = 0; k < ITEMS; ++k) {
+      if (k < nvalid) {
+        if ((starts >> k) & 1u) {  // the run of `cur` ended at k - 1
+          if (single) {
+            first_acc = acc;
+            single = false;
+          } else {  // it began and ended inside this thread: complete
+            out[cur] = from_acc<T>(R::finish(acc, (int64_t)(k - run0)));
+          }
+          while (b < b_hi && seg[b] <= p0 + k) ++b;  // (empty segments share a start: the last one holds the entries)
+          cur = s_lo + b;
+          run0 = k;
+          acc = R::init();
+        }
+        acc = R::op(acc, v[k]);
+      }
+    }
+    if (single) first_acc = acc;
+    last_seg = cur;
+  } else if (nvalid > 0) {
+    int32_t cur = own[0];
+    int run0 = 0;
+    first_seg = cur;
+#pragma unroll
+    for (int k = 0; k < ITEMS; ++k) {
+      if (k < nvalid) {
+        if (own[k] != cur) {  // the run of `cur` ended at k - 1
+          if (single) {
+            first_acc = acc;
+            single = false;
+          } else if (cur >= 0) {  // it began and ended inside this thread: complete
+            out[cur] = from_acc<T>(R::finish(acc, (int64_t)(k - run0)));
+          }
+          cur = own[k];
+          run0 = k;
+          acc = R::init();
+        }
+        acc = R::op(acc, v[k]);
+      }
+    }
+    if (single) first_acc = acc;
+    last_seg = cur;
+  }
+  sh_first[tid] = first_seg;
+  sh_last[tid] = last_seg;
+  // (the tile's first entry lies in segment bounds[tile] or, past empty segments, in a later one that starts AT e0)
+  if (tid == 0) sh_before = (nvalid > 0 && first_seg >= 0 && first_seg == bounds[tile] && first_start < e0) ? 1 : 0;
+  __syncthreads();
+  const bool cont = tid > 0 && nvalid > 0 && sh_last[tid - 1] == first_seg;  // my first run began in the thread before
+  // ---- segmented inclusive scan over the threads: x = the run that is open at the thread's right edge
+  A sc = acc;  // (single: the only run; else the last one)
+  int fl = (single && cont) ? 0 : 1;  // 1: the open run starts in this thread
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const A o = __shfl_up_sync(0xffffffffu, sc, d);
+    const int of = __shfl_up_sync(0xffffffffu, fl, d);
+    if (lane >= (unsigned)d) {
+      if (!fl) sc = R::op(o, sc);
+      fl |= of;
+    }
+  }
+  if (lane == 31) {
+    w_val[warp] = sc;
+    w_flag[warp] = fl;
+  }
+  __syncthreads();
+  if (warp == 0) {
+    A ws = lane < WARPS ? w_val[lane] : R::init();
+    int wf = lane < WARPS ? w_flag[lane] : 1;
+#pragma unroll
+    for (int d = 1; d < WARPS; d <<= 1) {
+      const A o = __shfl_up_sync(0xffffffffu, ws, d);
+      const int of = __shfl_up_sync(0xffffffffu, wf, d);
+      if (lane >= (unsigned)d) {
+        if (!wf) ws = R::op(o, ws);
+        wf |= of;
+      }
+    }
+    if (lane < WARPS) w_val[lane] = ws;
+  }
+  __syncthreads();
+  if (warp > 0 && !fl) sc = R::op(w_val[warp - 1], sc);
+  sh_val[tid] = sc;
+  __syncthreads();
+  if (nvalid == 0) return;
+  const int32_t tile_first = sh_first[0];
+  const bool before = sh_before != 0;
+  // ---- (a) my first run ended inside me
+  if (!single && first_seg >= 0) {
+    const A total = cont ? R::op(sh_val[tid - 1], first_acc) : first_acc;
+    if (first_seg == tile_first && before) {
+      thead[tile] = total;
+      tinfo[tile].head_seg = first_seg;
+    } else {
+      out[first_seg] = from_acc<T>(R::finish(total, RED == PS_MEAN ? ptr[first_seg + 1] - ptr[first_seg] : 1));
+    }
+  }
+  // ---- (b) the run open at my right edge: does it go on in the next thread?
+  const bool last_thread = p0 + ITEMS >= tile_n;
+  if (!last_thread && sh_first[tid + 1] == last_seg) return;
+  if (last_seg < 0) return;
+  // (only the thread at the tile's end has to look where its segment ends; a count is needed for the mean alone)
+  const int64_t seg_end = (last_thread || RED == PS_MEAN) ? ptr[last_seg + 1] : 0;
+  if (last_thread && seg_end > e0 + tile_n) {  // it leaves the tile
+    tcarry[tile] = sc;
+    tinfo[tile].carry = (last_seg == tile_first && before) ? 2 : 1;
+    return;
+  }
+  if (last_seg == tile_first && before) {
+    thead[tile] = sc;
+    tinfo[tile].head_seg = last_seg;
+  } else {
+    out[last_seg] = from_acc<T>(R::finish(sc, RED == PS_MEAN ? seg_end - ptr[last_seg] : 1));
+  }
+}
+
+// segments that crossed tiles: the tile where one ENDS folds the partials of the tiles before it, in tile order
+template <typename T, int RED>
+__global__ void __launch_bounds__(256)
+segment_tile_fix_kernel(const int64_t *__restrict__ ptr, int64_t tiles, const StTile *__restrict__ tinfo,
+                        const typename Acc<T>::type *__restrict__ thead,
+                        const typename Acc<T>::type *__restrict__ tcarry, T *__restrict__ out) {
+  using A = typename Acc<T>::type;
+  using R = Red<RED, A>;
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < tiles; t += (int64_t)gridDim.x * blockDim.x) {
+    const long long sgm = tinfo[t].head_seg;
+    if (sgm < 0) continue;
+    // the parts are t0 (carry, not whole), t0 + 1 .. t - 1 (carry, whole), t (head): find t0, then fold left to right
+    int64_t t0 = t - 1;
+    while (t0 > 0 && tinfo[t0].carry == 2) --t0;
+    A acc = tcarry[t0];
+    for (int64_t u = t0 + 1; u < t; ++u) acc = R::op(acc, tcarry[u]);
+    acc = R::op(acc, thead[t]);
+    out[sgm] = from_acc<T>(R::finish(acc, ptr[sgm + 1] - ptr[sgm]));
+  }
+}
+
+// PS_SEG_TILE (bench knob, read once): 1 = the tile kernel above on long [nnz] vectors.  NOT the default: measured on
+// the configs[2] shape (tools/segbench.py, same box) it takes 199 us (f32) / 168 us (bf16) against 104 / 94 us for
+// lanes-per-segment, and 143 / 119 us against 127 / 132 us on the R-MAT stream - four block barriers, two binary
+// searches and a 256-thread segmented scan per 16 KB tile cost more than they balance (first version, which resolved
+// a segment id per entry: 240 us, issue-bound at 2.4 instructions per SM-cycle).
+static int seg_tile() {
+  static int v = -1;
+  if (v < 0) {
+    const char *e = getenv("PS_SEG_TILE");
+    v = e ? atoi(e) : 0;
+  }
+  return v;
+}
+
+template <typename T, int RED>
+static int segment_tile_typed(const T *src, const int64_t *ptr, int64_t S, int64_t E, T *out, cudaStream_t s) {
+  using A = typename Acc<T>::type;
+  const int64_t tiles = ceil_div(E, ST_TILE);
+  Scratch scratch(s);
+  PS_SCRATCH(bounds, scratch, int32_t, tiles + 1);
+  PS_SCRATCH(tinfo, scratch, StTile, tiles);
+  PS_SCRATCH(thead, scratch, A, tiles);
+  PS_SCRATCH(tcarry, scratch, A, tiles);
+  PS_CUDA(cudaMemsetAsync(out, 0, sizeof(T) * (size_t)S, s));  // empty segments: 0 (the torch_scatter convention)
+  PS_CUDA(cudaMemsetAsync(tinfo, 0xff, sizeof(StTile) * (size_t)tiles, s));  // head_seg = -1; carry is set below
+  ProfScope prof(PROF_SEGMENT_REDUCE, s);
+  PS_TRY(tile_bounds_launch(ptr, S, E, ST_TILE, bounds, s));
+  segment_tile_kernel<T, RED><<<(unsigned)tiles, ST_THREADS, 0, s>>>(src, ptr, S, E, bounds, out, tinfo, thead, tcarry,
+                                                                     (reinterpret_cast<uintptr_t>(src) & 15u) == 0);
+  PS_LAUNCH_OK();
+  segment_tile_fix_kernel<T, RED><<<(unsigned)ceil_div(tiles, 256), 256, 0, s>>>(ptr, tiles, tinfo, thead, tcarry, out);
+  PS_LAUNCH_OK();
+  return PS_OK;
+}
+
 // PS_SEG_VEC (bench knob, read once): 0 = element-wise loads in the main kernel, 1 = 16-byte loads
 static int seg_vec() {
   static int v = -1;
@@ -228,6 +529,11 @@ static int segment_reduce_typed(const T *src, int64_t width, const int64_t *ptr,
   const int64_t outputs = S * width;
   if (outputs == 0) return PS_OK;
   const double avg = S > 0 ? (double)E_hint / (double)S : 0.0;
+  if constexpr (sizeof(T) <= 4) {
+    // long [nnz] vectors with rows of 16 entries and more: load-balanced over the entries (E_hint is the length of src)
+    if (seg_tile() && width == 1 && !perm && E_hint >= (int64_t(1) << 16) && avg >= 16.0 && S < 2147483647LL)
+      return segment_tile_typed<T, RED>(src, ptr, S, E_hint, out, s);
+  }
   int G = 32;
   if (width >= 4 || avg <= 2.0) G = 1;
   else if (avg <= 12.0) G = 4;

@@ -43,7 +43,7 @@ def test_route_tuples_refuses_ids_beyond_32_bits():
     """The exchange carries row / col as 32-bit words (csrc/dist.cu): larger sparse sizes are refused up front."""
     e = torch.zeros(0, dtype=torch.int64)
     for sizes in ((2 ** 32 + 1, 8), (8, 2 ** 40)):
-        with pytest.raises(ValueError, match="2\^32"):
+        with pytest.raises(ValueError, match=r"2\^32"):
             psd.route_tuples(e, e, None, sizes)
 
 
