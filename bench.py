@@ -42,7 +42,7 @@ PIPELINE_LOCAL_BYTES_PER_NNZ = 80.6
 CPU_SAMPLE_NNZ = 8_000_000      # bounded CPU sample where the full configuration cannot be timed (N > 1, --quick-cpu)
 REFERENCE_BUDGET_S = 170.0      # the reference arm runs as many full-size steps as fit this (at least one)
 # dram__bytes_read.sum + dram__bytes_write.sum of rs_pass_kernel, average per launch over the 5 launches of one
-# step, from the committed `ncu --set full` capture (profiles/r02l_step_kernels_ncu.txt: 8.21 GB over the 5
+# step, from the committed `ncu --set full` capture (profiles/r02y_step_kernels_ncu.txt: 8.21 GB over the 5
 # launches, against 8.41 GB modelled: the smaller passes partly hit L2): updated whenever the capture is
 NCU_TRAFFIC_PER_LAUNCH = 1.642e9
 
@@ -649,7 +649,7 @@ def run_ours(args):
             "algorithmic_bytes_per_launch": alg / (fam_n / args.steps) if fam_n else None,
             "share_of_step": (fam_ms / args.steps) / ms_prof if ms_prof else None,
             "launches_modelled_per_step": len(per_launch),
-            "traffic_source": "profiles/r02l_step_kernels_ncu.txt (ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum, average per launch)",
+            "traffic_source": "profiles/r02y_step_kernels_ncu.txt (ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum, average per launch)",
         }
         line["roofline"]["traffic"] = NCU_TRAFFIC_PER_LAUNCH
         line["pipeline_roofline"] = {
