@@ -383,11 +383,11 @@ static int refine_buckets(const uint32_t *keys0, const uint32_t *vals0, int64_t 
                                                    seg_dstart, L, nlev);
     PS_LAUNCH_OK();
     if (has_v)
-      scat_v<<<sm_count() * 4, RF_THREADS, sizeof(RfSmem), s>>>(kb[src], vb[src], kb[dst], vb[dst], L.seg[l],
+      scat_v<<<sm_count() * 3, RF_THREADS, sizeof(RfSmem), s>>>(kb[src], vb[src], kb[dst], vb[dst], L.seg[l],
                                                                 L.chunk_seg[l], ctl, l, lo, dmask, L.chunk_cap, chunk_hist,
                                                                 seg_dstart);
     else
-      scat_n<<<sm_count() * 4, RF_THREADS, sizeof(RfSmem), s>>>(kb[src], nullptr, kb[dst], nullptr, L.seg[l],
+      scat_n<<<sm_count() * 3, RF_THREADS, sizeof(RfSmem), s>>>(kb[src], nullptr, kb[dst], nullptr, L.seg[l],
                                                                 L.chunk_seg[l], ctl, l, lo, dmask, L.chunk_cap, chunk_hist,
                                                                 seg_dstart);
     PS_LAUNCH_OK();

@@ -22,6 +22,11 @@ constexpr int CL_CAP = CL_THREADS * CL_ITEMS;  // entries one CTA finishes in sh
 constexpr int CL_WARPS = CL_THREADS / 32;
 constexpr int CL_MAX_T = 15;   // 2^15 bucket counters = 128 KB of shared memory in the histogram
 constexpr int CL_MAX_L = 8;    // low col bits left to the local pass
+#ifndef PS_CL_MINB
+#define PS_CL_MINB 3
+#endif
+constexpr int CL_MINB = PS_CL_MINB;  // CTAs per SM the local pass is compiled for: 3 = 80 registers and no spills (4 = 64
+                                     // registers with 44-52 B of spills: fill_cache_ 2.729 against 2.665 ms)
 constexpr int CL_ROW = 256 / 2;  // counter row in words (two 16-bit counters per word)
 
 // ---- bucket sizes: histogram of col >> shift (one read of the int64 column array)
@@ -185,7 +190,7 @@ __device__ __forceinline__ ClMeta cl_fetch_meta(unsigned long long *ticket, unsi
 }
 
 template <bool CARRY, bool HAS_VALUE, int INV>
-__global__ void __launch_bounds__(CL_THREADS, 4)
+__global__ void __launch_bounds__(CL_THREADS, CL_MINB)
 cl_local_kernel(const uint32_t *__restrict__ scol, const uint32_t *__restrict__ sp, const uint32_t *__restrict__ srow,
                 const uint32_t *__restrict__ sval, const unsigned int *__restrict__ bucket_off,
                 const unsigned int *__restrict__ chunk_start, const unsigned int *__restrict__ chunk_bucket,

@@ -263,7 +263,7 @@ struct RfSmem {
   uint32_t scan_tmp[33];
 };
 template <bool HAS_VALUE>
-static __global__ void __launch_bounds__(RF_THREADS, 4)
+static __global__ void __launch_bounds__(RF_THREADS, 3)  // 80 registers: no spills (28 B at four CTAs per SM)
 rf_scatter_kernel(const uint32_t *__restrict__ src_k, const uint32_t *__restrict__ src_v, uint32_t *__restrict__ dst_k,
                   uint32_t *__restrict__ dst_v, const RfSeg *__restrict__ segs, const uint32_t *__restrict__ chunk_seg,
                   const RfCtl *__restrict__ ctl, int level, int shift, unsigned dmask, unsigned chunk_cap,

@@ -143,7 +143,7 @@ static int csc_hybrid(const int64_t *row, const int64_t *col, const void *value,
     }
   }
   const size_t smem = sizeof(ClSmem);
-  int grid = sm_count() * 4;
+  int grid = sm_count() * CL_MINB;
 #define PS_CL(C_, V_, I_)                                                                                          \
   do {                                                                                                             \
     auto kern = cl_local_kernel<C_, V_, I_>;                                                                       \
