@@ -34,13 +34,31 @@ namespace ps {
 // pairs are staged in shared memory and written out coalesced as int64 row / col + value.  With out_rowptr the
 // kernel also emits rowptr (csrc/convert.cpp:13-43 semantics) of the coalesced result: the head that opens row r
 // fills rowptr[prev_row + 1 .. r], the CTA of the last tile fills the tail.
+// A run of equal keys that crosses tiles (heavy duplicates) is not walked by one thread: every tile reduces its own
+// part - the entries BEFORE its first head continue the previous tile's last run - and leaves it here; the tile where
+// the run ends is found by dedup_cross_kernel, which folds the parts in tile order into the run's output slot.
+// (Round 1 let the head's thread walk the rest of the run through global memory: O(run) on one thread.)
+struct DdCross {
+  uint32_t cont_bits, tail_bits;  // partial reductions (accumulator bits): leading continuation / last head's run
+  uint32_t cont_len, tail_len;
+  long long first_out;            // output slot of the tile's first head (the continued run's slot is first_out - 1)
+  int flags;                      // 1: no head in the tile; 2: the continued run ends here; 4: the last run goes on
+  int pad;
+};
+
 template <typename KeyT, typename T, int RED, int MODE, int THREADS, int ITEMS>
 __global__ void __launch_bounds__(THREADS)
 dedup_kernel(KeySrc ksrc, PaySrc psrc, int64_t n, int cbits, int64_t M, int64_t *__restrict__ out_row,
              int64_t *__restrict__ out_col, T *__restrict__ out_value, int64_t *__restrict__ run_start,
-             int64_t *__restrict__ out_rowptr, uint64_t *state /*[0]=ticket,[1..]=tiles*/, long long *d_nnz_out) {
+             int64_t *__restrict__ out_rowptr, uint64_t *state /*[0]=ticket,[1..]=tiles*/, long long *d_nnz_out,
+             DdCross *__restrict__ cross /*[tiles], DD_FAST only*/) {
   constexpr int TILE = THREADS * ITEMS, WARPS = THREADS / 32;
   using A = typename Acc<T>::type;
+  static_assert(MODE != DD_FAST || sizeof(A) == 4, "partial reductions are kept as 32-bit words");
+  __shared__ int s_fh;            // first head of the tile (tile_n: none)
+  __shared__ A s_part[WARPS];
+  __shared__ int64_t s_gap[8][3];  // long runs of empty rows, filled by the whole CTA: (first row, last row, value)
+  __shared__ int s_ngap;
   __shared__ KeyT s_key[TILE + 2];  // s_key[0] = key preceding the tile, s_key[tile_n + 1] = key following it;
                                     // later the compacted keys
   __shared__ uint32_t s_pay[MODE == DD_FAST ? TILE : 1];
@@ -48,7 +66,11 @@ dedup_kernel(KeySrc ksrc, PaySrc psrc, int64_t n, int cbits, int64_t M, int64_t 
   __shared__ int64_t s_tile, s_excl;
   __shared__ int s_heads;
   const unsigned tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
-  if (tid == 0) s_tile = (int64_t)atomicAdd((unsigned long long *)state, 1ull);
+  if (tid == 0) {
+    s_tile = (int64_t)atomicAdd((unsigned long long *)state, 1ull);
+    s_fh = TILE;
+    s_ngap = 0;
+  }
   __syncthreads();
   const int64_t tile = s_tile;
   const int64_t tile_base = tile * TILE;
@@ -77,6 +99,7 @@ dedup_kernel(KeySrc ksrc, PaySrc psrc, int64_t n, int cbits, int64_t M, int64_t 
     heads |= (unsigned)h << k;
     below[k] = __popc(bal & lt);
     if (lane == 0) s_wcnt[k * WARPS + warp] = __popc(bal);
+    if (MODE == DD_FAST && h) atomicMin(&s_fh, j);
   }
   __syncthreads();
   if (warp == 0) {  // exclusive scan of the ITEMS*WARPS counts, then the look-back for the tile's offset
@@ -113,6 +136,35 @@ dedup_kernel(KeySrc ksrc, PaySrc psrc, int64_t n, int cbits, int64_t M, int64_t 
   const int tile_heads = s_heads;
   const bool last_tile = tile_base + tile_n == n;
   const KeyT cmask = (KeyT)((uint64_t(1) << cbits) - 1);
+  if (MODE == DD_FAST) {  // the entries before the first head continue the previous tile's last run: reduce them
+    const int fh = s_fh < tile_n ? s_fh : tile_n;
+    A part = Red<RED, A>::init();
+#pragma unroll
+    for (int k = 0; k < ITEMS; ++k) {
+      const int j = k * THREADS + tid;
+      if (j < fh) part = Red<RED, A>::op(part, to_acc<T>(pay_as<T>(s_pay[j])));
+    }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) part = Red<RED, A>::op(part, __shfl_xor_sync(0xffffffffu, part, d));
+    if (lane == 0) s_part[warp] = part;
+    __syncthreads();
+    if (tid == 0) {
+      A a = s_part[0];
+      for (int w = 1; w < WARPS; ++w) a = Red<RED, A>::op(a, s_part[w]);
+      DdCross c;
+      memcpy(&c.cont_bits, &a, 4);
+      c.tail_bits = 0;
+      c.cont_len = (uint32_t)fh;
+      c.tail_len = 0;
+      c.first_out = tile_excl;
+      const bool goes_on = !last_tile && s_key[tile_n + 1] == s_key[tile_n];
+      c.flags = (tile_heads == 0 ? 1 : 0) |
+                ((fh > 0 && tile_base > 0 && (tile_heads > 0 || !goes_on)) ? 2 : 0);
+      c.pad = 0;
+      cross[tile] = c;  // (a head whose run leaves the tile adds its part below)
+    }
+    __syncthreads();
+  }
 
   // ---- every head folds its run and opens its row
   KeyT hkey[ITEMS];
@@ -135,21 +187,29 @@ dedup_kernel(KeySrc ksrc, PaySrc psrc, int64_t n, int cbits, int64_t M, int64_t 
         acc = Red<RED, A>::op(acc, to_acc<T>(pay_as<T>(s_pay[jj])));
         ++jj;
       }
-      int64_t len = jj - j;
-      if (jj == tile_n && tile_base + tile_n < n && s_key[tile_n + 1] == key) {  // the run continues past the tile
-        int64_t g = tile_base + tile_n;
-        while (g < n && load_key<KeyT>(ksrc, g) == key) {
-          acc = Red<RED, A>::op(acc, to_acc<T>(pay_as<T>(load_pay(psrc, g))));
-          ++g;
-          ++len;
-        }
+      const int64_t len = jj - j;
+      if (jj == tile_n && tile_base + tile_n < n && s_key[tile_n + 1] == key) {  // the run continues past the tile:
+        memcpy(&cross[tile].tail_bits, &acc, 4);                                  // dedup_cross_kernel finishes it
+        cross[tile].tail_len = (uint32_t)len;
+        cross[tile].flags |= 4;  // (the only writer of this tile's record after the barrier above)
       }
       hacc[k] = Red<RED, A>::finish(acc, len);
     }
     if (out_rowptr) {
       const int64_t r = (int64_t)((uint64_t)key >> cbits);
       const int64_t pr = (tile_base + j == 0) ? -1 : (int64_t)((uint64_t)s_key[j] >> cbits);
-      for (int64_t q = pr + 1; q <= r; ++q) out_rowptr[q] = o;
+      if (r - pr > 64) {  // a long run of empty rows: the whole CTA fills it (below), not this thread
+        const int g = atomicAdd(&s_ngap, 1);
+        if (g < 8) {
+          s_gap[g][0] = pr + 1;
+          s_gap[g][1] = r;
+          s_gap[g][2] = o;
+        } else {
+          for (int64_t q = pr + 1; q <= r; ++q) out_rowptr[q] = o;
+        }
+      } else {
+        for (int64_t q = pr + 1; q <= r; ++q) out_rowptr[q] = o;
+      }
     }
   }
   int64_t last_row = -1;
@@ -178,9 +238,37 @@ dedup_kernel(KeySrc ksrc, PaySrc psrc, int64_t n, int cbits, int64_t M, int64_t 
     out_col[tile_excl + i] = (int64_t)(key & cmask);
     if (MODE == DD_FAST) out_value[tile_excl + i] = pay_as<T>(s_pay[i]);
   }
+  if (out_rowptr) {
+    const int ng = s_ngap < 8 ? s_ngap : 8;  // (visible: two barriers since the heads' loop)
+    for (int g = 0; g < ng; ++g)
+      for (int64_t q = s_gap[g][0] + tid; q <= s_gap[g][1]; q += THREADS) out_rowptr[q] = s_gap[g][2];
+  }
   if (last_tile && out_rowptr) {  // rows after the last entry point at nnz'
     const int64_t total = tile_excl + tile_heads;
     for (int64_t q = s_tile + 1 + tid; q <= M; q += THREADS) out_rowptr[q] = total;
+  }
+}
+
+// runs that crossed tiles: the tile where one ends folds the parts of the tiles before it, in tile order
+template <typename T, int RED>
+static __global__ void __launch_bounds__(256)
+dedup_cross_kernel(const DdCross *__restrict__ cross, int64_t tiles, T *__restrict__ out_value) {
+  using A = typename Acc<T>::type;
+  using R = Red<RED, A>;
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < tiles; t += (int64_t)gridDim.x * blockDim.x) {
+    if (!(cross[t].flags & 2)) continue;
+    int64_t u = t - 1;
+    while (u > 0 && (cross[u].flags & 1)) --u;  // tiles without a head lie wholly inside the run
+    A acc;
+    memcpy(&acc, &cross[u].tail_bits, 4);
+    int64_t len = cross[u].tail_len;
+    for (int64_t w = u + 1; w <= t; ++w) {
+      A part;
+      memcpy(&part, &cross[w].cont_bits, 4);
+      acc = R::op(acc, part);
+      len += cross[w].cont_len;
+    }
+    out_value[cross[t].first_out - 1] = from_acc<T>(R::finish(acc, len));
   }
 }
 
@@ -192,12 +280,19 @@ int dedup_launch(KeySrc ksrc, PaySrc psrc, int64_t n, int cbits, int64_t M, int6
   const int64_t tiles = ceil_div(n, THREADS * ITEMS);
   PS_SCRATCH(state, scratch, uint64_t, tiles + 1);
   PS_CUDA(cudaMemsetAsync(state, 0, sizeof(uint64_t) * (size_t)(tiles + 1), s));
+  PS_SCRATCH(cross, scratch, DdCross, MODE == DD_FAST ? tiles : 1);
   {
     ProfScope prof(PROF_DEDUP, s);
     dedup_kernel<KeyT, T, RED, MODE, THREADS, ITEMS><<<(unsigned)tiles, THREADS, 0, s>>>(
-        ksrc, psrc, n, cbits, M, out_row, out_col, reinterpret_cast<T *>(out_value), run_start, out_rowptr, state, d_nnz);
+        ksrc, psrc, n, cbits, M, out_row, out_col, reinterpret_cast<T *>(out_value), run_start, out_rowptr, state, d_nnz,
+        cross);
   }
   PS_LAUNCH_OK();
+  if (MODE == DD_FAST && tiles > 1) {
+    dedup_cross_kernel<T, RED><<<(unsigned)ceil_div(tiles, 256), 256, 0, s>>>(cross, tiles,
+                                                                              reinterpret_cast<T *>(out_value));
+    PS_LAUNCH_OK();
+  }
   return PS_OK;
 }
 

@@ -178,6 +178,41 @@ def test_coalesce_sorted_refuses_ids_beyond_the_packed_comparison(ops):
             ops.coalesce_sorted(row, col, val, "add", sizes)
 
 
+@pytest.mark.parametrize("reduce", ["add", "mean", "max"])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.int32])
+def test_coalesce_long_runs_and_row_gaps(ops, reduce, dtype):
+    """The LSD pipeline's dedup kernel (32-bit keys): one key repeated 300,000 times - a run that crosses a hundred
+    tiles is reduced tile by tile and folded by dedup_cross_kernel, not walked by one thread - runs that end exactly at
+    tile boundaries, and rows tens of thousands apart (long rowptr gaps are filled by the whole CTA)."""
+    rng = np.random.default_rng(77)
+    M, N = 60000, 50000
+    row = np.concatenate([np.full(300000, 7), np.full(3072 * 3, 41000), np.full(5000, M - 1),
+                          rng.integers(100, 200, 20000)]).astype(I64)
+    col = np.concatenate([np.full(300000, 11), np.full(3072 * 3, 3), rng.integers(0, 4, 5000),
+                          rng.integers(0, N, 20000)]).astype(I64)
+    p = rng.permutation(row.size)
+    row, col = row[p], col[p]
+    val = rng.integers(-3, 4, row.size)
+    r, c, v, rowptr = ops.coalesce(dev(row), dev(col), dev(val, dtype), M, N, reduce, True)
+    idx, want = np_ref.coalesce(np.stack([row, col]), val.astype(np.float64), M, N, reduce)
+    assert np.array_equal(host(r), idx[0]) and np.array_equal(host(c), idx[1])
+    assert np.array_equal(host(rowptr), np.searchsorted(idx[0], np.arange(M + 1), side="left"))
+    got = host(v.to(torch.float64))
+    if dtype == torch.int32 and reduce == "mean":
+        cnt = np_ref.coalesce(np.stack([row, col]), np.ones(row.size), M, N, "sum")[1]
+        tot = np_ref.coalesce(np.stack([row, col]), val.astype(np.float64), M, N, "sum")[1]
+        want = np.trunc(tot / cnt)
+    if reduce == "mean" and dtype == torch.float32:
+        np.testing.assert_allclose(got, want, rtol=1e-6, atol=1e-7)
+    else:
+        assert np.array_equal(got, want)
+    # the same through the sorted-input entry point
+    st = np_ref.SparseStorage(row=row, col=col, value=val.astype(np.float64), sparse_sizes=(M, N))
+    r2, c2, v2 = ops.coalesce_sorted(dev(st.row()), dev(st.col()), dev(st.value(), dtype), reduce, (M, N))
+    assert np.array_equal(host(r2), idx[0]) and np.array_equal(host(c2), idx[1])
+    assert np.array_equal(host(v2.to(torch.float64)), got)
+
+
 def test_coalesce_empty_and_single(ops):
     e = dev(np.array([], I64))
     r, c, v = ops.coalesce(e, e, dev(np.array([], np.float32)), 5, 5)
