@@ -285,6 +285,13 @@ int ps_sample_adj(const int64_t *rowptr, const int64_t *col, int64_t M, int64_t 
                   int64_t *out_rowptr, int64_t *out_col, int64_t *out_n_id, int64_t *out_e_id,
                   int64_t *host_sizes, void *stream);
 
+/* sample.py:10-28 `sample(src, num_neighbors, subset)`: out[i, k] = col[rowptr[s_i] + floor(u * deg(s_i))] with u
+ * uniform in [0, 1) (draws with replacement).  The reference chains rand / mul_ / cast / add_ / index on the
+ * framework's generator; here u of (position i, draw k) is the top 24 bits of Philox4x32-10(seed; (i, k)) * 2^-24.
+ * subset NULL: rows 0 .. S-1.  out [S, num_neighbors]. */
+int ps_sample_uniform(const int64_t *rowptr, const int64_t *col, int64_t nnz, const int64_t *subset, int64_t S,
+                      int64_t num_neighbors, uint64_t seed, int64_t *out, void *stream);
+
 /* ------------------------------------------------------------------ row-range partitioning (multi-GPU) */
 /* SURVEY.md 8e (the reference has no distributed code).  Coarse row histogram used to
  * choose nnz-balanced, row-aligned splitters: out_hist[b] = #{e : row[e] >> shift == b}

@@ -903,6 +903,25 @@ def sample_adj(src: SparseTensor, subset: np.ndarray, num_neighbors: int,
     return out, n_id
 
 
+def sample(src: SparseTensor, num_neighbors: int, subset: Optional[np.ndarray] = None, seed: int = 0) -> np.ndarray:
+    """sample.py:10-28: rand([S, k]) * rowcount -> int64 -> + rowptr -> col[...].  The reference draws from the
+    framework's generator; the draw of (position i, draw k) is pinned here as the top 24 bits of
+    Philox4x32-10(seed; (i, k)) * 2^-24 (a float32 in [0, 1)), the mapping ps_sample_uniform uses; the product in
+    float32, truncated, clamped to the row (the reference would index past it when rand * count rounds up)."""
+    rowptr, col, _ = src.csr()
+    rows = np.arange(rowptr.size - 1) if subset is None else np.asarray(subset)
+    out = np.empty((rows.size, num_neighbors), dtype=np.int64)
+    for i, r in enumerate(rows):
+        lo, deg = int(rowptr[r]), int(rowptr[r + 1] - rowptr[r])
+        for k in range(num_neighbors):
+            u = np.float32(native.philox_u64(seed, i, k) >> 40) * np.float32(1.0 / 16777216.0)
+            off = int(np.float32(u) * np.float32(deg))
+            if off >= deg:
+                off = max(deg - 1, 0)
+            out[i, k] = col[min(lo + off, col.size - 1)]
+    return out
+
+
 # =========================================================================== helpers for tests/bench
 def round_bf16(x: np.ndarray) -> np.ndarray:
     """Round-to-nearest-even float32 -> bfloat16 -> float32 (NumPy has no bf16)."""

@@ -82,6 +82,7 @@ SIGNATURES = {
     "ps_dist_row_histogram": [c_ptr, c_i64, c_int, c_i64, c_ptr, c_ptr],
     "ps_dist_partition": [c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_ptr, c_int, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr],
     "ps_dist_dest": [c_ptr, c_i64, c_ptr, c_int, c_ptr, c_ptr, c_ptr],
+    "ps_sample_uniform": [c_ptr, c_ptr, c_i64, c_ptr, c_i64, c_i64, ctypes.c_uint64, c_ptr, c_ptr],
     "ps_dist_scatter_peer": [c_ptr, c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_int, c_ptr, c_ptr, c_ptr, c_ptr, c_int, c_ptr],
     "ps_coalesce_u32": [c_ptr, c_ptr, c_i64, c_i64, c_i64, c_i64, c_ptr, c_int, c_i64, c_int, c_ptr, c_ptr, c_ptr, c_ptr,
                         c_ptr, c_ptr],

@@ -236,6 +236,30 @@ static inline unsigned blocks_for(int64_t n, int threads = 256) { return (unsign
 
 using namespace ps;
 
+namespace ps {
+// sample.py:10-28 `sample`: out[i, k] = col[rowptr[s_i] + floor(u * deg(s_i))], u uniform in [0, 1) - uniform draws WITH
+// replacement, one launch where the reference chains rand / mul_ / cast / add_ / index.  u of (row position i, draw k)
+// is the top 24 bits of Philox4x32-10(seed; (i, k)) scaled by 2^-24 (a float32 in [0, 1), like the framework's rand);
+// floor(u * deg) is computed in float32 as the reference does and clamped to deg - 1.  A row without entries yields
+// the entry at its (empty) start clamped into the array, as indexing col[rowptr[s]] does in the reference.
+__global__ void __launch_bounds__(256)
+sample_uniform_kernel(const int64_t *__restrict__ rowptr, const int64_t *__restrict__ col, int64_t nnz,
+                      const int64_t *__restrict__ subset, int64_t S, int64_t k, uint64_t seed, int64_t *__restrict__ out) {
+  const int64_t total = S * k;
+  for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < total; q += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t i = q / k, d = q - i * k;
+    const int64_t r = subset ? subset[i] : i;
+    const int64_t lo = rowptr[r], deg = rowptr[r + 1] - lo;
+    const float u = (float)(uint32_t)(philox_u64(seed, (uint64_t)i, (uint32_t)d) >> 40) * (1.0f / 16777216.0f);
+    int64_t off = (int64_t)(u * (float)deg);
+    if (off >= deg) off = deg > 0 ? deg - 1 : 0;
+    int64_t e = lo + off;
+    if (e >= nnz) e = nnz - 1;
+    out[q] = col[e];
+  }
+}
+}  // namespace ps
+
 extern "C" {
 
 int ps_sample_adj_bound(const int64_t *rowptr, const int64_t *idx, int64_t S, int64_t num_neighbors, int replace,
@@ -344,6 +368,19 @@ int ps_sample_adj(const int64_t *rowptr, const int64_t *col, int64_t M, int64_t 
   PS_TRY(read_back(h, d_sizes, sizeof(h), s));
   host_sizes[0] = (int64_t)h[0];
   host_sizes[1] = (int64_t)h[1];
+  return PS_OK;
+}
+
+int ps_sample_uniform(const int64_t *rowptr, const int64_t *col, int64_t nnz, const int64_t *subset, int64_t S,
+                      int64_t num_neighbors, uint64_t seed, int64_t *out, void *stream) {
+  PS_CHECK(S >= 0 && num_neighbors >= 0 && nnz >= 0, "sample_uniform: negative size");
+  if (S == 0 || num_neighbors == 0) return PS_OK;
+  PS_CHECK(nnz > 0, "sample_uniform: the matrix has no entries to draw from");
+  const int64_t total = S * num_neighbors;
+  int64_t b = ceil_div(total, 256);
+  if (b > 16 * (int64_t)sm_count()) b = 16 * (int64_t)sm_count();
+  sample_uniform_kernel<<<(unsigned)b, 256, 0, (cudaStream_t)stream>>>(rowptr, col, nnz, subset, S, num_neighbors, seed, out);
+  PS_LAUNCH_OK();
   return PS_OK;
 }
 

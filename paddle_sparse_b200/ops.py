@@ -103,6 +103,19 @@ def ptr2ind(ptr: torch.Tensor, E: int) -> torch.Tensor:
     return out
 
 
+def sample_uniform(rowptr, col, subset, num_neighbors: int, seed: int = 0) -> torch.Tensor:
+    """sample.py:10-28 in one launch: [S, num_neighbors] neighbours drawn uniformly with replacement (subset None: every
+    row).  Draw (i, k) is a counter-based function of `seed`."""
+    rowptr, col = _idx(rowptr, "rowptr"), _idx(col, "col")
+    subset = None if subset is None else _idx(subset, "subset")
+    S = rowptr.numel() - 1 if subset is None else subset.numel()
+    out = torch.empty((S, int(num_neighbors)), dtype=torch.int64, device=col.device)
+    with torch.cuda.device(col.device):
+        _lib.call("ps_sample_uniform", _p(rowptr), _p(col), col.numel(), _p(subset), S, int(num_neighbors),
+                  ctypes.c_uint64(int(seed) & (2**64 - 1)), _p(out), _stream(col))
+    return out
+
+
 def sample_adj(rowptr, col, idx, num_neighbors: int, replace: bool, seed: int = 0):
     """csrc/sample.cpp:8-24 (the reference throws on GPU tensors; this is the GPU path).
     Returns [out_rowptr, out_col, n_id, e_id]."""

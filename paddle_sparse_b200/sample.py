@@ -17,20 +17,16 @@ def manual_seed(seed: int) -> None:
     _SEED[0] = int(seed)
 
 
-def sample(src: SparseTensor, num_neighbors: int, subset: Optional[torch.Tensor] = None) -> torch.Tensor:
-    """sample.py:10-28: uniform draws with replacement through the framework's RNG."""
+def sample(src: SparseTensor, num_neighbors: int, subset: Optional[torch.Tensor] = None,
+           seed: Optional[int] = None) -> torch.Tensor:
+    """sample.py:10-28: `num_neighbors` uniform draws with replacement per row of `subset` (every row when None), as
+    ONE kernel (ops.sample_uniform) where the reference chains five tensor ops on the framework's generator.  `seed`
+    (extension) pins the Philox stream of this call; otherwise the module's call counter advances it."""
     rowptr, col, _ = src.csr()
-    rowcount = src.storage.rowcount()
-    if subset is not None:
-        rowcount = rowcount[subset]
-        rowptr = rowptr[subset]
-    else:
-        rowptr = rowptr[:-1]
-    rand = torch.rand((rowcount.shape[0], num_neighbors), device=col.device)
-    rand.mul_(rowcount.to(rand.dtype).view(-1, 1))
-    rand = rand.to(torch.int64)
-    rand.add_(rowptr.view(-1, 1))
-    return col[rand]
+    if seed is None:
+        seed = _SEED[0]
+        _SEED[0] += 1
+    return ops.sample_uniform(rowptr, col, subset, num_neighbors, seed)
 
 
 def sample_adj(src: SparseTensor, subset: torch.Tensor, num_neighbors: int, replace: bool = False,

@@ -122,3 +122,30 @@ def test_sample_adj_two_hop_products_like(ops):
     hop2 = _run_gpu(ops, rowptr, col, hop1[2], 10, False, 42)
     want2 = native.sample_adj_port(rowptr, col, want1[2], 10, False, 42)
     assert all(np.array_equal(a, b) for a, b in zip(hop2, want2))
+
+
+@pytest.mark.parametrize("k", [1, 4, 25])
+def test_sample_uniform_matches_the_oracle(ops, k):
+    """sample.py:10-28 as one kernel: bit-exact against the oracle's restatement under the same Philox mapping, with
+    and without `subset`, rows without entries included; every draw is a neighbour of its row."""
+    import torch
+
+    from oracle import np_ref
+    rng = np.random.default_rng(k)
+    M = 300
+    row = np.sort(rng.integers(0, M, 5000)).astype(np.int64)
+    row = row[(row % 7) != 3]  # some rows stay empty
+    col = rng.integers(0, M, row.size).astype(np.int64)
+    A = np_ref.SparseTensor(row=row, col=col, sparse_sizes=(M, M))
+    rowptr, cc, _ = A.csr()
+    d_rowptr, d_col = torch.from_numpy(rowptr).cuda(), torch.from_numpy(cc).cuda()
+    sub = rng.integers(0, M, 64).astype(np.int64)
+    for subset in (None, sub):
+        want = np_ref.sample(A, k, subset, seed=42)
+        got = ops.sample_uniform(d_rowptr, d_col, None if subset is None else torch.from_numpy(subset).cuda(), k, 42)
+        assert np.array_equal(got.cpu().numpy(), want)
+    import paddle_sparse_b200 as ps
+    T = ps.SparseTensor(row=torch.from_numpy(row).cuda(), col=torch.from_numpy(col).cuda(), sparse_sizes=(M, M))
+    out = ps.sample(T, k, torch.from_numpy(sub).cuda(), seed=42)
+    assert np.array_equal(out.cpu().numpy(), np_ref.sample(A, k, sub, seed=42))
+    assert T.sample(k).shape == (M, k)

@@ -359,3 +359,26 @@ def test_sparse_reshape_golden_and_resize_restatement():
     C = A.sparse_resize((45, 37)).sparse_resize((40, 30))  # growing then cutting back restores the caches
     for k in ("rowptr", "rowcount", "colptr", "colcount"):
         assert np.array_equal(getattr(C, "_" + k), getattr(A, "_" + k)), k
+
+
+def test_sample_uniform_restatement():
+    """sample.py:10-28 / test/test_sample.py:8-14: every draw is a neighbour of its row; the pinned Philox mapping is
+    deterministic in (seed, position, draw) and covers a row's neighbours."""
+    row = np.array([0, 0, 2, 2], np.int64)
+    col = np.array([1, 2, 0, 1], np.int64)
+    adj = np_ref.SparseTensor(row=row, col=col, sparse_sizes=(3, 3))
+    out = np_ref.sample(adj, 1)
+    assert out.shape == (3, 1) and out.min() >= 0 and out.max() <= 2  # the reference's own assertion
+    rng = np.random.default_rng(3)
+    r = np.sort(rng.integers(0, 40, 400)).astype(np.int64)
+    c = rng.integers(0, 40, 400).astype(np.int64)
+    A = np_ref.SparseTensor(row=r, col=c, sparse_sizes=(40, 40))
+    rowptr, cc, _ = A.csr()
+    sub = np.array([5, 5, 17, 0, 39], np.int64)
+    a, b = np_ref.sample(A, 6, sub, seed=9), np_ref.sample(A, 6, sub, seed=9)
+    assert np.array_equal(a, b) and not np.array_equal(a, np_ref.sample(A, 6, sub, seed=10))
+    for i, s_ in enumerate(sub):
+        nb = set(cc[rowptr[s_]:rowptr[s_ + 1]].tolist())
+        if nb:
+            assert set(a[i].tolist()) <= nb
+    assert not np.array_equal(a[0], a[1])  # the same row at two positions draws independently
