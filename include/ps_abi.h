@@ -309,16 +309,16 @@ int ps_dist_partition(const int64_t *row, const int64_t *col, const void *value,
                       int64_t *out_col, void *out_value, int64_t *out_counts, void *stream);
 /* The same partition fused with the exchange over peer memory (one process per GPU, receive buffers of
  * all ranks mapped into this process, e.g. CUDA IPC / symmetric memory).  ps_dist_dest: destination rank
- * of every tuple (out_dest[nnz], u32) and the per-destination counts (device, G entries).  After the
+ * of every tuple (out_dest[nnz], one BYTE each: G <= 64) and the per-destination counts (device, G entries).  After the
  * ranks have exchanged their counts, ps_dist_scatter_peer runs the ONE stable counting pass that carries
  * (row, col, 4-byte value) and stores destination d's run at element bases[d] of peer_row[d] /
  * peer_col[d] / peer_value[d] (device arrays of G base pointers; bases: device, G entries): the tuples
  * cross NVLink as the pass produces them, tile by tile.  row_bytes: 0 (no value) or 4.  narrow != 0: row and
  * col are stored as uint32 (peer_row / peer_col then address uint32 elements): 12 instead of 20 bytes per tuple
  * on the wire; the receiver builds from them with ps_coalesce_u32. */
-int ps_dist_dest(const int64_t *row, int64_t nnz, const int64_t *splitters, int G, uint32_t *out_dest,
+int ps_dist_dest(const int64_t *row, int64_t nnz, const int64_t *splitters, int G, uint8_t *out_dest,
                  int64_t *out_counts, void *stream);
-int ps_dist_scatter_peer(const uint32_t *dest, const int64_t *row, const int64_t *col,
+int ps_dist_scatter_peer(const uint8_t *dest, const int64_t *row, const int64_t *col,
                          const void *value, int64_t row_bytes, int64_t nnz, int G, const int64_t *bases,
                          void *const *peer_row, void *const *peer_col, void *const *peer_value,
                          int narrow, void *stream);

@@ -40,9 +40,10 @@ row_hist_global_kernel(const int64_t *__restrict__ row, int64_t nnz, int shift, 
 }
 
 // dest[e] = g with splitters[g] <= row[e] < splitters[g+1]; counts[g] += 1
+template <typename DestT>
 __global__ void __launch_bounds__(256)
 dest_kernel(const int64_t *__restrict__ row, int64_t nnz, const int64_t *__restrict__ splitters, int G,
-            uint32_t *__restrict__ dest, unsigned long long *__restrict__ counts) {
+            DestT *__restrict__ dest, unsigned long long *__restrict__ counts) {
   __shared__ int64_t sp[65];
   __shared__ unsigned int sc[64];
   if (threadIdx.x <= G) sp[threadIdx.x] = splitters[threadIdx.x];
@@ -68,7 +69,7 @@ dest_kernel(const int64_t *__restrict__ row, int64_t nnz, const int64_t *__restr
         else hi = mid - 1;
       }
       const int g = i < nnz ? lo : 64;  // 64: nothing to count
-      if (i < nnz) dest[i] = (uint32_t)lo;
+      if (i < nnz) dest[i] = (DestT)lo;
       const unsigned peers = __match_any_sync(0xffffffffu, g);
       if (g < 64 && (threadIdx.x & 31u) == (unsigned)(__ffs(peers) - 1)) atomicAdd(&sc[g], (unsigned)__popc(peers));
     }
@@ -122,8 +123,8 @@ int ps_dist_partition(const int64_t *row, const int64_t *col, const void *value,
   int64_t blocks = ceil_div(nnz, 256 * 8);
   const int64_t cap = 8 * (int64_t)sm_count();
   if (blocks > cap) blocks = cap;
-  dest_kernel<<<(unsigned)blocks, 256, 0, s>>>(row, nnz, splitters, G, dest,
-                                              reinterpret_cast<unsigned long long *>(out_counts));
+  dest_kernel<uint32_t><<<(unsigned)blocks, 256, 0, s>>>(row, nnz, splitters, G, dest,
+                                                        reinterpret_cast<unsigned long long *>(out_counts));
   PS_LAUNCH_OK();
   const int dbits = G > 1 ? bits_for(G) : 1;
   if (row_bytes == 0 || row_bytes == 4) {
@@ -155,7 +156,7 @@ int ps_dist_partition(const int64_t *row, const int64_t *col, const void *value,
   return PS_OK;
 }
 
-int ps_dist_dest(const int64_t *row, int64_t nnz, const int64_t *splitters, int G, uint32_t *out_dest,
+int ps_dist_dest(const int64_t *row, int64_t nnz, const int64_t *splitters, int G, uint8_t *out_dest,
                  int64_t *out_counts, void *stream) {
   PS_CHECK(nnz >= 0 && G >= 1 && G <= 64, "dist_dest: bad arguments (G must be in [1, 64])");
   cudaStream_t s = (cudaStream_t)stream;
@@ -164,13 +165,13 @@ int ps_dist_dest(const int64_t *row, int64_t nnz, const int64_t *splitters, int 
   int64_t blocks = ceil_div(nnz, 256 * 8);
   const int64_t cap = 8 * (int64_t)sm_count();
   if (blocks > cap) blocks = cap;
-  dest_kernel<<<(unsigned)blocks, 256, 0, s>>>(row, nnz, splitters, G, out_dest,
-                                              reinterpret_cast<unsigned long long *>(out_counts));
+  dest_kernel<uint8_t><<<(unsigned)blocks, 256, 0, s>>>(row, nnz, splitters, G, out_dest,
+                                                       reinterpret_cast<unsigned long long *>(out_counts));
   PS_LAUNCH_OK();
   return PS_OK;
 }
 
-int ps_dist_scatter_peer(const uint32_t *dest, const int64_t *row, const int64_t *col, const void *value,
+int ps_dist_scatter_peer(const uint8_t *dest, const int64_t *row, const int64_t *col, const void *value,
                          int64_t row_bytes, int64_t nnz, int G, const int64_t *bases, void *const *peer_row,
                          void *const *peer_col, void *const *peer_value, int narrow, void *stream) {
   PS_CHECK(nnz >= 0 && G >= 1 && G <= 64, "dist_scatter_peer: bad arguments (G must be in [1, 64])");
@@ -195,7 +196,7 @@ int ps_dist_scatter_peer(const uint32_t *dest, const int64_t *row, const int64_t
   pd.d[0] = PayDst{const_cast<void **>(peer_row), narrow ? PDST_U32_BY_DIGIT : PDST_I64_BY_DIGIT};
   pd.d[1] = PayDst{const_cast<void **>(peer_col), narrow ? PDST_U32_BY_DIGIT : PDST_I64_BY_DIGIT};
   pd.d[2] = has_v ? PayDst{const_cast<void **>(peer_value), PDST_U32_BY_DIGIT} : PayDst{nullptr, PDST_NONE};
-  PS_TRY((radix_sort_tuples<uint32_t, 3>(KeySrc{dest, nullptr, KSRC_KEYS, 0}, ps_, nnz, G > 1 ? bits_for(G) : 1, nullptr,
+  PS_TRY((radix_sort_tuples<uint32_t, 3>(KeySrc{dest, nullptr, KSRC_U8, 0}, ps_, nnz, G > 1 ? bits_for(G) : 1, nullptr,
                                          nullptr, none, none, KeyDst{nullptr, nullptr, KDST_NONE, 0}, pd, scratch, s, 0,
                                          gh)));
   return PS_OK;

@@ -45,7 +45,7 @@ inline SortPlan make_sort_plan(int total_bits, int rbits) {
 }
 
 // ---- where the first pass finds its keys / payload, and where the last one puts them
-enum { KSRC_KEYS = 0, KSRC_PACK_COO = 1, KSRC_I64 = 2, KSRC_PACK_COO32 = 3 };
+enum { KSRC_KEYS = 0, KSRC_PACK_COO = 1, KSRC_I64 = 2, KSRC_PACK_COO32 = 3, KSRC_U8 = 4 /* one byte per key */ };
 enum { PSRC_U32 = 0, PSRC_IOTA = 1, PSRC_U16 = 2, PSRC_U8 = 3, PSRC_I64 = 4, PSRC_NONE = 5 /* word unused */ };
 enum { PDST_U32 = 0, PDST_I64 = 1, PDST_U16 = 2, PDST_U8 = 3, PDST_NONE = 4,
        // p = device array of one base pointer PER DIGIT (single-pass partitions whose bins live in different
@@ -84,6 +84,7 @@ __device__ __forceinline__ KeyT load_key(const KeySrc &s, int64_t i) {
     const uint64_t c = (uint64_t)ld_stream(reinterpret_cast<const int64_t *>(s.b) + i);
     return (KeyT)((r << s.cbits) | c);
   }
+  if (s.mode == KSRC_U8) return (KeyT) reinterpret_cast<const uint8_t *>(s.a)[i];
   if (s.mode == KSRC_PACK_COO32) {
     const uint64_t r = (uint64_t)ld_stream(reinterpret_cast<const uint32_t *>(s.a) + i) - (uint64_t)s.off;
     const uint64_t c = (uint64_t)ld_stream(reinterpret_cast<const uint32_t *>(s.b) + i);
@@ -249,6 +250,13 @@ __device__ __forceinline__ void load_tile_keys(const KeySrc &s, int64_t tile_bas
     for (int i = 0; i < ITEMS; ++i) {
       const int j = warp_base + i * 32 + lane;
       if (j < tile_n) key[i] = (KeyT)(((uint64_t)key[i] << s.cbits) | (uint64_t)ld_stream(c + j));
+    }
+  } else if (s.mode == KSRC_U8) {
+    const uint8_t *p = reinterpret_cast<const uint8_t *>(s.a) + tile_base;
+#pragma unroll
+    for (int i = 0; i < ITEMS; ++i) {
+      const int j = warp_base + i * 32 + lane;
+      key[i] = j < tile_n ? (KeyT)__ldg(p + j) : ~KeyT(0);
     }
   } else if (s.mode == KSRC_PACK_COO32) {
     const uint32_t *r = reinterpret_cast<const uint32_t *>(s.a) + tile_base;

@@ -685,10 +685,10 @@ def dist_partition(row, col, value, splitters: torch.Tensor):
 
 
 def dist_dest(row: torch.Tensor, splitters: torch.Tensor):
-    """Destination rank of every tuple (uint32 stored as int32 bits) and the per-destination counts (device)."""
+    """Destination rank of every tuple (one byte each: at most 64 ranks) and the per-destination counts (device)."""
     row, splitters = _idx(row, "row"), _idx(splitters, "splitters")
     G = splitters.numel() - 1
-    dest = torch.empty(row.numel(), dtype=torch.int32, device=row.device)
+    dest = torch.empty(row.numel(), dtype=torch.uint8, device=row.device)
     counts = _new(row, G)
     with torch.cuda.device(row.device):
         _lib.call("ps_dist_dest", _p(row), row.numel(), _p(splitters), G, _p(dest), _p(counts), _stream(row))
