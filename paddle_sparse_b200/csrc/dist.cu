@@ -18,9 +18,22 @@ row_hist_smem_kernel(const int64_t *__restrict__ row, int64_t nnz, int shift, in
   for (int j = threadIdx.x; j < buckets; j += blockDim.x) sh_hist[j] = 0;
   __syncthreads();
   const int64_t stride = (int64_t)gridDim.x * blockDim.x * 2;
-  for (int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 2; i < nnz; i += stride) {
+  int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 2;
+  // four 16-byte loads in flight per thread: with 128 KB of counters only one CTA fits an SM and one load at a time
+  // left the kernel at 2 TB/s (0.78 ms per 202 M rows)
+  for (; i + 3 * stride + 1 < nnz; i += 4 * stride) {
+    longlong2 v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) v[u] = ld_stream2(row + i + u * stride);  // row is 16-B aligned, i even
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      atomicAdd(&sh_hist[(unsigned)(v[u].x >> shift)], 1u);
+      atomicAdd(&sh_hist[(unsigned)(v[u].y >> shift)], 1u);
+    }
+  }
+  for (; i < nnz; i += stride) {
     if (i + 1 < nnz) {
-      const longlong2 v = ld_stream2(row + i);  // row is 16-B aligned (cudaMalloc / tensor base), i even
+      const longlong2 v = ld_stream2(row + i);
       atomicAdd(&sh_hist[(unsigned)(v.x >> shift)], 1u);
       atomicAdd(&sh_hist[(unsigned)(v.y >> shift)], 1u);
     } else {
