@@ -116,15 +116,31 @@ cl_chunk_scan_kernel(const unsigned int *__restrict__ bucket_off, const unsigned
   for (unsigned m = blockIdx.x; m < n_multi; m += gridDim.x) {
     const unsigned b = multi_list[m];
     const unsigned c0 = chunk_start[b], c1 = chunk_start[b + 1];
+    // column d of the bucket's chunk histograms, eight chunks in flight (a hub column's bucket has hundreds of chunks:
+    // one dependent load per chunk made this kernel take 146 us on the R-MAT stream)
+    unsigned int *colp = chunk_hist + (size_t)c0 * 256 + d;
+    const unsigned nch = c1 - c0;
     unsigned int run = 0;
-    for (unsigned c = c0; c < c1; ++c) {
-      const unsigned int t = chunk_hist[(size_t)c * 256 + d];
-      chunk_hist[(size_t)c * 256 + d] = run;
-      run += t;
+    for (unsigned c = 0; c < nch; c += 8) {
+      unsigned int t[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) t[u] = c + u < nch ? colp[(size_t)(c + u) * 256] : 0u;
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        if (c + u < nch) colp[(size_t)(c + u) * 256] = run;
+        run += t[u];
+      }
     }
     unsigned int total;
     const unsigned int dstart = block_exclusive_scan<unsigned int, 256>(run, warp_sums, &total);
-    for (unsigned c = c0; c < c1; ++c) chunk_hist[(size_t)c * 256 + d] += dstart;
+    for (unsigned c = 0; c < nch; c += 8) {
+      unsigned int t[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) t[u] = c + u < nch ? colp[(size_t)(c + u) * 256] : 0u;
+#pragma unroll
+      for (int u = 0; u < 8; ++u)
+        if (c + u < nch) colp[(size_t)(c + u) * 256] = t[u] + dstart;
+    }
     const int64_t colid = ((int64_t)b << L) + d;
     if (d < (1u << L) && colid <= N) {
       if (out_colptr) out_colptr[colid] = (int64_t)bucket_off[b] + dstart;

@@ -1,5 +1,5 @@
 """Summarise one bench step out of an ncu launch list (gpu__time_duration.sum, --csv):
-   python tools/launch_list.py launches.csv [first-kernel regex] [must-contain regex] > profiles/rNN_..._launches.txt
+   python tools/launch_list.py launches.csv [first-kernel regex] [must-contain regex] [must-not-contain regex]
 The last complete step (from one launch matching the first regex to the next) that contains a kernel matching the
 second regex (default: the hybrid coalesce's ls2_sort_dedup_kernel, i.e. the uniform configs[1] step rather than the
 skewed variant that follows it) is printed launch by launch with its share; generator / torch kernels are left out."""
@@ -23,10 +23,12 @@ starts = [i for i, (n, _) in enumerate(rows) if first.search(n)]
 if len(starts) < 2:
     sys.exit("fewer than two steps in the list")
 must = re.compile(sys.argv[3] if len(sys.argv) > 3 else r"^ls2?_sort_dedup_kernel")
+# the skewed variant of the bench refines its oversized buckets (rf_* kernels): left out by default
+must_not = re.compile(sys.argv[4] if len(sys.argv) > 4 else r"^rf_")
 step = None
 for a, b in reversed(list(zip(starts[:-1], starts[1:]))):  # steps that are certainly complete, latest first
     cand = [(n, us) for n, us in rows[a:b] if not skip.search(n)]
-    if any(must.search(n) for n, _ in cand):
+    if any(must.search(n) for n, _ in cand) and not (must_not.pattern and any(must_not.search(n) for n, _ in cand)):
         step = cand
         break
 if step is None:
